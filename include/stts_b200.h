@@ -1,0 +1,138 @@
+/* stts_b200 -- C ABI of the B200-native Stylish-TTS synthesis forward path.
+ *
+ * The reference (Fannovel16/stylish-tts) has no FFI / plugin interface for this path: its
+ * boundary is the Python nn.Module API.  This header is therefore the
+ * boundary *underneath* the Python module mirrors in stylish_tts_b200/modules; each entry point
+ * names the reference call it replaces (paths relative to src/stylish_tts/train/).
+ *
+ * Conventions
+ *   - every function returns 0 on success or a negative stts_status; stts_last_error() gives text
+ *   - all `d_` pointers are DEVICE pointers, fp32 unless stated; `stream` is a cudaStream_t
+ *   - no hot call allocates, synchronises, or keeps a caller pointer past its return
+ *   - "dense" tensors are the reference layout of ONE utterance ([C, L] row-major, i.e. a B = 1
+ *     slice of [B, C, L]) concatenated over the utterances of the batch; per-utterance element
+ *     offsets follow from the layout set with stts_set_layout (off = C * cumsum(L))
+ *   - the batch is a set of independent utterances ("segments"); statistics never cross them
+ */
+#ifndef STTS_B200_H
+#define STTS_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct stts_ctx stts_ctx;
+
+enum stts_status {
+  STTS_OK = 0,
+  STTS_ERR_BAD_ARG = -1,
+  STTS_ERR_BAD_SHAPE = -2,
+  STTS_ERR_MISSING_WEIGHT = -3,
+  STTS_ERR_NO_LAYOUT = -4,
+  STTS_ERR_CUDA = -5,
+  STTS_ERR_UNSUPPORTED = -6,
+  STTS_ERR_UNVOICED_MIN = -7 /* voiced frames but no f0 > 20 Hz: the reference raises (generator.py:285) */
+};
+
+/* arithmetic of the dense contractions */
+enum stts_precision {
+  STTS_FP32 = 0,   /* CUDA-core fp32 FMA (parity reference on device)                       */
+  STTS_BF16 = 1,   /* tcgen05 kind::f16, bf16 operands, fp32 accumulate; STFT / output heads /
+                      iSTFT stay on the fp32-grade path                                     */
+  STTS_TF32X3 = 2  /* tcgen05 kind::tf32, error-compensated 3-pass split (fp32-grade)       */
+};
+
+/* ---- lifetime ------------------------------------------------------------------------------ */
+int stts_create(stts_ctx** out, int device);
+void stts_destroy(stts_ctx* ctx);
+const char* stts_last_error(const stts_ctx* ctx);
+const char* stts_version(void);
+
+/* ---- weights: state_dict() of the reference modules, key by key -------------------------------
+ * module in {"speech_predictor", "pitch_energy_predictor"}; key is the reference state_dict key
+ * (SURVEY 8b "Checkpoint layout"); h_data is a HOST fp32 buffer, copied.  Unknown keys are kept
+ * but unused (token-rate encoders are served by the Python layer in this round).              */
+int stts_load_tensor(stts_ctx* ctx, const char* module, const char* key, const float* h_data,
+                     const int64_t* shape, int ndim);
+/* folds both weight-norm dialects, builds the K-major fp32 / tf32 hi-lo / bf16 packs and the
+ * STFT / iSTFT bases.  Replaces nothing in the reference (it re-parametrises on every forward). */
+int stts_finalize_weights(stts_ctx* ctx);
+int stts_set_precision(stts_ctx* ctx, int precision);
+
+/* ---- packed layout ---------------------------------------------------------------------------
+ * len_f[b]  = frames at hop 300 (F), len_f4[b] = frames at hop 75 (normally 4 F).  Either may be
+ * NULL.  (Re)allocates and zeroes the context workspace when the layout changes.              */
+int stts_set_layout(stts_ctx* ctx, int n_seg, const int* len_f, const int* len_f4);
+int64_t stts_workspace_bytes(const stts_ctx* ctx);
+
+/* ---- length regulation ------------------------------------------------------------------------
+ * DurationProcessor.prediction_to_duration, utils.py:468-474: logits [n_tokens,16] -> int32.    */
+int stts_durations(stts_ctx* ctx, const float* d_logits, int n_tokens, int32_t* d_dur, void* stream);
+/* DurationProcessor.duration_to_alignment, utils.py:476-489, as indices: for utterance b the
+ * token owning frame f is d_idx[d_cu_frames[b] + f] (= argmax over tokens of the one-hot
+ * alignment column).  d_cu_tok [n_seg+1] are token offsets.  *d_status != 0 if cap too small.   */
+int stts_frame_index(stts_ctx* ctx, const int32_t* d_dur, const int32_t* d_cu_tok, int n_seg,
+                     int32_t* d_cu_frames, int32_t* d_idx, int idx_cap, int32_t* d_status, void* stream);
+
+/* ---- pitch / energy towers --------------------------------------------------------------------
+ * PitchEnergyPredictor.forward lines 111-119 (pitch_energy_predictor.py): 2 x 3
+ * AdaptiveDecoderBlock(320) + 1x1 projections on the cross-attended frames.
+ * d_x: dense [320, F_b]; d_style [n_seg, 64]; outputs dense [sum F].                            */
+int stts_pe_towers(stts_ctx* ctx, const float* d_x, const float* d_style, float* d_pitch,
+                   float* d_energy, void* stream);
+
+/* ---- module-level stages of SpeechPredictor.forward (speech_predictor.py:85-129) --------------
+ * Decoder.forward, decoder.py:47-60.  d_asr dense [128, L_b]; d_f0/d_n dense [sum L];
+ * d_out dense [512, L_b].                                                                      */
+int stts_decoder(stts_ctx* ctx, const float* d_asr, const float* d_f0, const float* d_n,
+                 const float* d_style, float* d_out, void* stream);
+/* PriorEncoder.forward (flow.py:311-315) + ResidualCouplingBlock.forward(reverse=True)
+ * (flow.py:132-151) + post_flow (speech_predictor.py:111).  d_x dense [512, L_b]; d_noise dense
+ * [128, L_b] is the randn_like draw; d_mel dense [512, L_b]; optional d_z_prior/d_z_flow dense
+ * [128, L_b] (may be NULL).                                                                    */
+int stts_prior_flow(stts_ctx* ctx, const float* d_x, const float* d_noise, const float* d_style,
+                    float* d_mel, float* d_z_prior, float* d_z_flow, void* stream);
+/* generate_pcph (generator.py:247-315): d_pitch4 dense [sum L] (Hz per hop-75 frame), d_noise
+ * dense [sum 75 L] raw randn draw, d_init_phase [n_seg] the torch.rand((1,1)) draw per utterance;
+ * d_out dense [sum 75 L].                                                                      */
+int stts_source_pcph(stts_ctx* ctx, const float* d_pitch4, const float* d_noise,
+                     const float* d_init_phase, float* d_out, void* stream);
+/* Generator.forward (generator.py:402-438).  d_mel dense [512, L_b]; outputs: d_audio dense
+ * [sum 75 L]; optional d_logamp / d_phase dense [1025, L_b + 1] (replicate-padded frame
+ * included, like DecoderPrediction.magnitude / .phase).                                         */
+int stts_generator(stts_ctx* ctx, const float* d_mel, const float* d_style, const float* d_pitch4,
+                   const float* d_noise, const float* d_init_phase, float* d_audio, float* d_logamp,
+                   float* d_phase, void* stream);
+
+/* ---- fused frame-rate path --------------------------------------------------------------------
+ * Everything of SpeechPredictor.forward after the token-rate encoders: alignment expansion
+ * (:88,:93), x4 linear upsample (:89-90), decoder, prior, flow^-1, post_flow, generator.
+ * d_enc_tok: token-major text encoding [sum T, 128]; d_cu_tok [n_seg+1]; d_idx / d_cu_frames from
+ * stts_frame_index; d_pitch / d_energy dense [sum F]; d_style [n_seg,64]; noise as above.        */
+int stts_speech_frames(stts_ctx* ctx, const float* d_enc_tok, const int32_t* d_cu_tok,
+                       const int32_t* d_idx, const int32_t* d_cu_frames, const float* d_pitch,
+                       const float* d_energy, const float* d_style, const float* d_noise_prior,
+                       const float* d_noise_source, const float* d_init_phase, float* d_audio,
+                       float* d_logamp, float* d_phase, void* stream);
+/* after a synchronised call: STTS_ERR_UNVOICED_MIN if any utterance hit the reference's error path */
+int stts_check_source_status(stts_ctx* ctx, void* stream);
+
+/* ---- test / profiling hooks -------------------------------------------------------------------
+ * Raw conv-as-GEMM on caller buffers (packed [R, ld] layout of the current hop-75 layout):
+ * Y[r, n] = bias[n] + sum_j sum_c X[r + j - pad, c] * W[n, c, j];  d_w is [N, cin, taps] fp32
+ * (PyTorch Conv1d layout).  backend: stts_precision.  Used by the kernel parity tests.          */
+int stts_test_conv(stts_ctx* ctx, int backend, const float* d_x, int ldx, int cin, int taps, int pad,
+                   const float* h_w, const float* h_bias, int n_out, float* d_y, int ldy, void* stream);
+/* copy a named workspace buffer (packed rows) to d_dst; returns rows*ld written or negative.   */
+int64_t stts_debug_read(stts_ctx* ctx, const char* name, float* d_dst, int64_t cap, int* rows, int* ld,
+                        void* stream);
+int stts_layout_info(const stts_ctx* ctx, int rate, int* rows, int* seg_start /*[n_seg]*/);
+/* number of kernels launched by this context since creation (bench.py "gpu_launches")          */
+int64_t stts_launch_count(const stts_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* STTS_B200_H */

@@ -1,0 +1,245 @@
+// extern "C" surface declared in include/stts_b200.h
+#include <cstring>
+
+#include "../../include/stts_b200.h"
+#include "engine.h"
+
+using namespace stts;
+
+struct stts_ctx {
+  Context c;
+};
+
+namespace {
+struct DeviceGuard {
+  int prev = 0;
+  explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
+  ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+inline cudaStream_t S(void* s) { return reinterpret_cast<cudaStream_t>(s); }
+}  // namespace
+
+extern "C" {
+
+const char* stts_version(void) { return "stts_b200 0.1 (sm_100a)"; }
+
+int stts_create(stts_ctx** out, int device) {
+  if (out == nullptr) return STTS_ERR_BAD_ARG;
+  *out = nullptr;
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || device < 0 || device >= n) return STTS_ERR_CUDA;
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return STTS_ERR_CUDA;
+  if (prop.major != 10) return STTS_ERR_UNSUPPORTED;  // built for sm_100a only, no fallback
+  stts_ctx* ctx = new stts_ctx();
+  ctx->c.device = device;
+  *out = ctx;
+  return STTS_OK;
+}
+
+void stts_destroy(stts_ctx* ctx) {
+  if (ctx == nullptr) return;
+  DeviceGuard g(ctx->c.device);
+  cudaDeviceSynchronize();
+  for (void* p : ctx->c.weight_allocs) cudaFree(p);
+  if (ctx->c.arena) cudaFree(ctx->c.arena);
+  if (ctx->c.h_meta) cudaFreeHost(ctx->c.h_meta);
+  delete ctx;
+}
+
+const char* stts_last_error(const stts_ctx* ctx) { return ctx ? ctx->c.err.c_str() : "null context"; }
+
+int stts_load_tensor(stts_ctx* ctx, const char* module, const char* key, const float* h_data, const int64_t* shape,
+                     int ndim) {
+  if (!ctx || !module || !key || !h_data || ndim < 0 || ndim > 8) return STTS_ERR_BAD_ARG;
+  HostTensor t;
+  int64_t n = 1;
+  for (int i = 0; i < ndim; ++i) { t.shape.push_back(shape[i]); n *= shape[i]; }
+  t.data.assign(h_data, h_data + n);
+  ctx->c.tensors[std::string(module) + "/" + key] = std::move(t);
+  ctx->c.finalized = false;
+  return STTS_OK;
+}
+
+int stts_finalize_weights(stts_ctx* ctx) {
+  if (!ctx) return STTS_ERR_BAD_ARG;
+  DeviceGuard g(ctx->c.device);
+  ctx->c.sig.clear();  // style-FC scratch sizes depend on the packs: force a re-plan
+  return finalize_weights(ctx->c);
+}
+
+int stts_set_precision(stts_ctx* ctx, int precision) {
+  if (!ctx || precision < 0 || precision > 2) return STTS_ERR_BAD_ARG;
+  ctx->c.precision = precision;
+  return STTS_OK;
+}
+
+int stts_set_layout(stts_ctx* ctx, int n_seg, const int* len_f, const int* len_f4) {
+  if (!ctx) return STTS_ERR_BAD_ARG;
+  DeviceGuard g(ctx->c.device);
+  return set_layout(ctx->c, n_seg, len_f, len_f4);
+}
+
+int64_t stts_workspace_bytes(const stts_ctx* ctx) { return ctx ? (int64_t)ctx->c.arena_used : 0; }
+
+int stts_durations(stts_ctx* ctx, const float* d_logits, int n_tokens, int32_t* d_dur, void* stream) {
+  if (!ctx || !d_logits || !d_dur || n_tokens < 0) return STTS_ERR_BAD_ARG;
+  Context& c = ctx->c;
+  DeviceGuard g(c.device);
+  STTS_CK(durations_from_logits(d_logits, n_tokens, d_dur, S(stream)));
+  return STTS_OK;
+}
+
+int stts_frame_index(stts_ctx* ctx, const int32_t* d_dur, const int32_t* d_cu_tok, int n_seg, int32_t* d_cu_frames,
+                     int32_t* d_idx, int idx_cap, int32_t* d_status, void* stream) {
+  if (!ctx || !d_dur || !d_cu_tok || !d_cu_frames || !d_idx || !d_status) return STTS_ERR_BAD_ARG;
+  Context& c = ctx->c;
+  DeviceGuard g(c.device);
+  STTS_CK(frame_index(d_dur, d_cu_tok, n_seg, d_cu_frames, d_idx, idx_cap, d_status, S(stream)));
+  c.launches++;
+  return STTS_OK;
+}
+
+int stts_pe_towers(stts_ctx* ctx, const float* d_x, const float* d_style, float* d_pitch, float* d_energy,
+                   void* stream) {
+  if (!ctx || !d_x || !d_style || !d_pitch || !d_energy) return STTS_ERR_BAD_ARG;
+  DeviceGuard g(ctx->c.device);
+  return run_pe_towers(ctx->c, d_x, d_style, d_pitch, d_energy, S(stream));
+}
+
+int stts_decoder(stts_ctx* ctx, const float* d_asr, const float* d_f0, const float* d_n, const float* d_style,
+                 float* d_out, void* stream) {
+  if (!ctx || !d_asr || !d_f0 || !d_n || !d_style || !d_out) return STTS_ERR_BAD_ARG;
+  DeviceGuard g(ctx->c.device);
+  return run_decoder(ctx->c, d_asr, d_f0, d_n, d_style, d_out, S(stream));
+}
+
+int stts_prior_flow(stts_ctx* ctx, const float* d_x, const float* d_noise, const float* d_style, float* d_mel,
+                    float* d_z_prior, float* d_z_flow, void* stream) {
+  if (!ctx || !d_x || !d_noise || !d_style || !d_mel) return STTS_ERR_BAD_ARG;
+  DeviceGuard g(ctx->c.device);
+  return run_prior_flow(ctx->c, d_x, d_noise, d_style, d_mel, d_z_prior, d_z_flow, S(stream));
+}
+
+int stts_source_pcph(stts_ctx* ctx, const float* d_pitch4, const float* d_noise, const float* d_init_phase,
+                     float* d_out, void* stream) {
+  if (!ctx || !d_pitch4 || !d_noise || !d_init_phase || !d_out) return STTS_ERR_BAD_ARG;
+  DeviceGuard g(ctx->c.device);
+  return run_source(ctx->c, d_pitch4, d_noise, d_init_phase, d_out, S(stream));
+}
+
+int stts_generator(stts_ctx* ctx, const float* d_mel, const float* d_style, const float* d_pitch4,
+                   const float* d_noise, const float* d_init_phase, float* d_audio, float* d_logamp, float* d_phase,
+                   void* stream) {
+  if (!ctx || !d_mel || !d_style || !d_pitch4 || !d_noise || !d_init_phase || !d_audio) return STTS_ERR_BAD_ARG;
+  DeviceGuard g(ctx->c.device);
+  return run_generator(ctx->c, d_mel, d_style, d_pitch4, d_noise, d_init_phase, d_audio, d_logamp, d_phase, S(stream));
+}
+
+int stts_speech_frames(stts_ctx* ctx, const float* d_enc_tok, const int32_t* d_cu_tok, const int32_t* d_idx,
+                       const int32_t* d_cu_frames, const float* d_pitch, const float* d_energy, const float* d_style,
+                       const float* d_noise_prior, const float* d_noise_source, const float* d_init_phase,
+                       float* d_audio, float* d_logamp, float* d_phase, void* stream) {
+  if (!ctx || !d_enc_tok || !d_cu_tok || !d_idx || !d_cu_frames || !d_pitch || !d_energy || !d_style ||
+      !d_noise_prior || !d_noise_source || !d_init_phase || !d_audio)
+    return STTS_ERR_BAD_ARG;
+  DeviceGuard g(ctx->c.device);
+  return run_speech_frames(ctx->c, d_enc_tok, d_cu_tok, d_idx, d_cu_frames, d_pitch, d_energy, d_style, d_noise_prior,
+                           d_noise_source, d_init_phase, d_audio, d_logamp, d_phase, S(stream));
+}
+
+int stts_check_source_status(stts_ctx* ctx, void* stream) {
+  if (!ctx) return STTS_ERR_BAD_ARG;
+  Context& c = ctx->c;
+  if (c.raw.count("META") == 0 || c.h_meta == nullptr) return fail(c, -4, "no layout set");
+  DeviceGuard g(c.device);
+  const int B = c.L4.n_seg;
+  cudaError_t e = cudaMemcpyAsync(c.h_meta, c.raw["META"], (size_t)B * sizeof(SourceMeta), cudaMemcpyDeviceToHost,
+                                  S(stream));
+  if (e == cudaSuccess) e = cudaStreamSynchronize(S(stream));
+  if (e != cudaSuccess) return cuda_fail(c, e, "source status read");
+  for (int b = 0; b < B; ++b)
+    if (c.h_meta[b].error)
+      return fail(c, STTS_ERR_UNVOICED_MIN,
+                  "utterance " + std::to_string(b) + ": voiced frames but no f0 > 20 Hz (reference raises in torch.min)");
+  return STTS_OK;
+}
+
+int stts_test_conv(stts_ctx* ctx, int backend, const float* d_x, int ldx, int cin, int taps, int pad,
+                   const float* h_w, const float* h_bias, int n_out, float* d_y, int ldy, void* stream) {
+  if (!ctx || !d_x || !h_w || !d_y || backend < 0 || backend > 2) return STTS_ERR_BAD_ARG;
+  Context& c = ctx->c;
+  if (c.L4.total() == 0) return fail(c, -4, "no hop-75 layout set");
+  DeviceGuard g(c.device);
+  PackedGemm pg = pack_from_conv_weight(c, h_w, h_bias, n_out, cin, taps, pad);
+  if (pg.cin_pad[0] > ldx) { free_pack(pg); return fail(c, -2, "ldx must cover cin padded to 64"); }
+  Act a;
+  a.f = const_cast<float*>(d_x);
+  a.ld = ldx;
+  a.rows = c.L4.R;
+  // bf16 backend: build a temporary twin of the operand
+  __nv_bfloat16* twin = nullptr;
+  if (backend == 1) {
+    if (cudaMalloc(&twin, (size_t)c.L4.R * ldx * 2) != cudaSuccess) { free_pack(pg); return fail(c, -5, "twin alloc"); }
+    std::vector<float> hx((size_t)c.L4.R * ldx);
+    cudaMemcpy(hx.data(), d_x, hx.size() * 4, cudaMemcpyDeviceToHost);
+    std::vector<__nv_bfloat16> hh(hx.size());
+    for (size_t i = 0; i < hx.size(); ++i) hh[i] = __float2bfloat16_rn(hx[i]);
+    cudaMemcpy(twin, hh.data(), hh.size() * 2, cudaMemcpyHostToDevice);
+    a.h = twin;
+  }
+  Epi e;
+  std::memset(&e, 0, sizeof(e));
+  e.kind = EPI_BIAS;
+  e.out = d_y; e.ldo = ldy; e.col0 = 0;
+  e.scale = 1.f;
+  int r = run_gemm(c, pg, GC_BODY, &a, 0, nullptr, 0, e, c.L4.map(), S(stream), backend);
+  cudaError_t ce = cudaStreamSynchronize(S(stream));
+  if (twin) cudaFree(twin);
+  free_pack(pg);
+  tc_map_cache_clear();
+  if (r != 0) return r;
+  if (ce != cudaSuccess) return cuda_fail(c, ce, "test_conv");
+  return STTS_OK;
+}
+
+int64_t stts_debug_read(stts_ctx* ctx, const char* name, float* d_dst, int64_t cap, int* rows, int* ld,
+                        void* stream) {
+  if (!ctx || !name) return STTS_ERR_BAD_ARG;
+  Context& c = ctx->c;
+  DeviceGuard g(c.device);
+  auto it = c.act.find(name);
+  const float* src = nullptr;
+  int64_t n = 0;
+  if (it != c.act.end()) {
+    src = it->second.f;
+    n = (int64_t)it->second.rows * it->second.ld;
+    if (rows) *rows = it->second.rows;
+    if (ld) *ld = it->second.ld;
+  } else {
+    auto jt = c.raw.find(name);
+    if (jt == c.raw.end()) return fail(c, -1, std::string("unknown buffer ") + name);
+    src = reinterpret_cast<const float*>(jt->second);
+    n = (int64_t)(c.raw_bytes[name] / 4);
+    if (rows) *rows = (int)n;
+    if (ld) *ld = 1;
+  }
+  if (d_dst == nullptr) return n;
+  if (cap < n) return fail(c, -2, "debug_read: destination too small");
+  cudaError_t e = cudaMemcpyAsync(d_dst, src, (size_t)n * 4, cudaMemcpyDeviceToDevice, S(stream));
+  if (e != cudaSuccess) return cuda_fail(c, e, "debug_read");
+  return n;
+}
+
+int stts_layout_info(const stts_ctx* ctx, int rate, int* rows, int* seg_start) {
+  if (!ctx) return STTS_ERR_BAD_ARG;
+  const Layout& L = (rate == 4) ? ctx->c.L4 : ctx->c.LF;
+  if (rows) *rows = L.R;
+  if (seg_start)
+    for (int b = 0; b < L.n_seg; ++b) seg_start[b] = L.seg_start[b];
+  return L.n_seg;
+}
+
+int64_t stts_launch_count(const stts_ctx* ctx) { return ctx ? ctx->c.launches : 0; }
+
+}  // extern "C"

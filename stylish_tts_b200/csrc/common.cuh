@@ -1,0 +1,206 @@
+// Shared declarations for the sm_100a synthesis kernels.
+//
+// Activation layout (DESIGN.md "Data layout in HBM"): every frame-rate tensor is a packed,
+// time-major, channels-last matrix [R, ld] of fp32 (optionally with a bf16 twin used as the
+// tensor-core operand).  Utterances ("segments") are stacked along the row axis; every segment
+// starts on a multiple of TILE_M = 128 rows and is followed by >= GUARD = 16 rows that are
+// never written and therefore stay zero.  A conv1d over time is then a row-shifted implicit
+// GEMM whose zero padding is provided by the guard rows (or by TMA / bounds-check zero fill at
+// the two ends of the buffer), and every 128-row tile belongs to exactly one segment.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+
+#define STTS_TILE_M 128
+#define STTS_GUARD 16
+
+namespace stts {
+
+// Device view of a packed layout (one per frame rate).
+struct RowMap {
+  int R;                 // rows (multiple of 128)
+  int n_tiles;           // R / 128
+  int n_seg;             // utterances
+  const int* tile_seg;   // [n_tiles] segment of the tile, -1 = guard-only tile
+  const int* tile_nvalid;// [n_tiles] valid rows in the tile (0..128)
+  const int* seg_start;  // [n_seg] first row
+  const int* seg_len;    // [n_seg] valid rows
+};
+
+// ----------------------------------------------------------------------------- epilogues
+enum EpiKind : int {
+  EPI_BIAS = 0,        // out = acc + bias
+  EPI_RES_SCALE = 1,   // out = (acc + bias + res) * scale         (AdaptiveDecoderBlock, ada_norm.py:179-182)
+  EPI_SILU = 2,        // out = silu(acc + bias)                    (ConvNeXtBlock pwconv1, generator.py:478-479)
+  EPI_ADD = 3,         // out = res + acc + bias                    (ConvNeXt residual, generator.py:484)
+  EPI_GATE = 4,        // out[i] = tanh(a_2i + g_i) * sigmoid(a_2i+1 + g_{H+i})   (flow.py:7-14)
+  EPI_RESSKIP = 5,     // n<split: out[n] += v ; n>=split: out2[n-split] (+)= v    (flow.py:80-87)
+  EPI_COUPLE = 6,      // out[i] = (out[i] - m_i) * exp(-logs_i), (m,logs) interleaved (flow.py:210-213)
+  EPI_PRIOR = 7,       // out[i] = mean_i + noise[i] * exp(logstd_i)               (flow.py:311-315)
+  EPI_STFT = 8,        // (re,im) interleaved -> out = |X|, out2 = atan2            (generator.py:32-44,407-410)
+};
+
+struct Epi {
+  int kind;
+  int N;                       // logical output columns of the GEMM (pairs count as 2)
+  float* out; int ldo; int col0;
+  __nv_bfloat16* outh; int ldh; int colh0;   // optional bf16 twin of `out`
+  float* out2; int ldo2; int col20;
+  __nv_bfloat16* outh2; int ldh2; int colh20;  // optional bf16 twin of `out2` (EPI_STFT)
+  const float* bias;           // [N] (already permuted for the pair kinds) or null
+  const float* res; int ldr; int rcol0;
+  const float* segvec; int ldseg;            // per-utterance vector, row = segment
+  float scale;
+  int split;                   // EPI_RESSKIP
+  int accumulate2;             // EPI_RESSKIP: out2 += (1) or = (0)
+};
+
+__device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + __expf(-x)); }
+
+// One thread owns row r (valid, segment seg) and NV consecutive output columns starting at n0
+// (n0 % NV == 0, NV even).  Shared by the SIMT and the tcgen05 kernels.
+template <int KIND, int NV>
+__device__ __forceinline__ void epi_apply(const Epi& e, int r, int seg, int n0, const float* acc) {
+  if constexpr (KIND == EPI_BIAS || KIND == EPI_RES_SCALE || KIND == EPI_SILU || KIND == EPI_ADD) {
+    float v[NV];
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int n = n0 + i;
+      float x = acc[i] + ((e.bias != nullptr && n < e.N) ? e.bias[n] : 0.f);
+      if constexpr (KIND == EPI_RES_SCALE) {
+        if (e.res != nullptr && n < e.N) x += e.res[(size_t)r * e.ldr + e.rcol0 + n];
+        x *= e.scale;
+      }
+      if constexpr (KIND == EPI_SILU) x = x / (1.f + expf(-x));
+      if constexpr (KIND == EPI_ADD) {
+        if (n < e.N) x += e.res[(size_t)r * e.ldr + e.rcol0 + n];
+      }
+      v[i] = x;
+    }
+    float* o = e.out + (size_t)r * e.ldo + e.col0 + n0;
+    if (n0 + NV <= e.N && ((((size_t)r * e.ldo + e.col0 + n0) & 3) == 0) && (NV % 4 == 0)) {
+#pragma unroll
+      for (int i = 0; i < NV; i += 4) *reinterpret_cast<float4*>(o + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+    } else {
+#pragma unroll
+      for (int i = 0; i < NV; ++i) if (n0 + i < e.N) o[i] = v[i];
+    }
+    if (e.outh != nullptr) {
+      __nv_bfloat16* oh = e.outh + (size_t)r * e.ldh + e.colh0 + n0;
+#pragma unroll
+      for (int i = 0; i < NV; ++i) if (n0 + i < e.N) oh[i] = __float2bfloat16_rn(v[i]);
+    }
+  } else if constexpr (KIND == EPI_GATE) {
+    const int H = e.N >> 1;
+#pragma unroll
+    for (int i = 0; i < NV; i += 2) {
+      const int n = n0 + i;
+      if (n < e.N) {
+        const int c = n >> 1;
+        const float a = acc[i] + e.bias[n] + e.segvec[(size_t)seg * e.ldseg + c];
+        const float b = acc[i + 1] + e.bias[n + 1] + e.segvec[(size_t)seg * e.ldseg + H + c];
+        const float y = tanhf(a) * (1.f / (1.f + expf(-b)));
+        e.out[(size_t)r * e.ldo + e.col0 + c] = y;
+        if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = __float2bfloat16_rn(y);
+      }
+    }
+  } else if constexpr (KIND == EPI_RESSKIP) {
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int n = n0 + i;
+      if (n < e.N) {
+        const float v = acc[i] + e.bias[n];
+        if (n < e.split) {
+          float* p = e.out + (size_t)r * e.ldo + e.col0 + n;
+          const float y = *p + v;
+          *p = y;
+          if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + n] = __float2bfloat16_rn(y);
+        } else {
+          float* p = e.out2 + (size_t)r * e.ldo2 + e.col20 + (n - e.split);
+          const float y = e.accumulate2 ? (*p + v) : v;
+          *p = y;
+          if (e.outh2 != nullptr) e.outh2[(size_t)r * e.ldh2 + e.colh20 + (n - e.split)] = __float2bfloat16_rn(y);
+        }
+      }
+    }
+  } else if constexpr (KIND == EPI_COUPLE) {
+#pragma unroll
+    for (int i = 0; i < NV; i += 2) {
+      const int n = n0 + i;
+      if (n < e.N) {
+        const int c = n >> 1;
+        const float m = acc[i] + e.bias[n];
+        const float logs = acc[i + 1] + e.bias[n + 1];
+        float* p = e.out + (size_t)r * e.ldo + e.col0 + c;
+        const float y = (*p - m) * expf(-logs);
+        *p = y;
+        if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = __float2bfloat16_rn(y);
+      }
+    }
+  } else if constexpr (KIND == EPI_PRIOR) {
+#pragma unroll
+    for (int i = 0; i < NV; i += 2) {
+      const int n = n0 + i;
+      if (n < e.N) {
+        const int c = n >> 1;
+        const float mean = acc[i] + e.bias[n];
+        const float logstd = acc[i + 1] + e.bias[n + 1];
+        const float nz = e.res[(size_t)r * e.ldr + e.rcol0 + c];
+        const float y = mean + nz * expf(logstd);
+        e.out[(size_t)r * e.ldo + e.col0 + c] = y;
+        if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = __float2bfloat16_rn(y);
+      }
+    }
+  } else if constexpr (KIND == EPI_STFT) {
+#pragma unroll
+    for (int i = 0; i < NV; i += 2) {
+      const int n = n0 + i;
+      if (n < e.N) {
+        const int c = n >> 1;
+        const float re = acc[i], im = acc[i + 1];
+        const float mag = hypotf(re, im);
+        const float d = mag + 1e-9f;
+        const float ph = atan2f(im / d, re / d);
+        e.out[(size_t)r * e.ldo + e.col0 + c] = mag;
+        e.out2[(size_t)r * e.ldo2 + e.col20 + c] = ph;
+        if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = __float2bfloat16_rn(mag);
+        if (e.outh2 != nullptr) e.outh2[(size_t)r * e.ldh2 + e.colh20 + c] = __float2bfloat16_rn(ph);
+      }
+    }
+  }
+}
+
+// ----------------------------------------------------------------------------- conv-as-GEMM
+// Y[r, n] = sum_s sum_j sum_c A_s[r + j - pad_s, col0_s + c] * W[n, koff_s + j * cin_pad_s + c]
+// Up to two K-segments (fused 1x1 shortcut, channel concatenation across buffers).
+struct KSeg {
+  const float* A; int lda; int col0;         // fp32 operand
+  const __nv_bfloat16* Ah; int ldah; int colh0;  // bf16 twin (tensor-core bf16 mode)
+  int taps; int pad; int cin_pad;            // cin_pad % 64 == 0
+  int rows;                                  // rows allocated in A (bounds for zero fill)
+};
+
+struct ConvGemm {
+  KSeg seg[2];
+  int n_kseg;
+  const float* W;                 // [Npad, Ktot] fp32, K-major
+  const __nv_bfloat16* Wh;        // bf16 copy
+  int Ktot;                       // sum taps*cin_pad
+  int Npad;                       // multiple of 128
+  Epi epi;
+};
+
+// ----------------------------------------------------------------------------- small helpers
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+}  // namespace stts

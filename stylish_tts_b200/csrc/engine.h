@@ -1,0 +1,125 @@
+// Context of the synthesis engine: loaded state_dict tensors, prepacked device weights,
+// packed-layout descriptors and the workspace arena.
+#pragma once
+#include <map>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+#include "kernels.h"
+
+namespace stts {
+
+struct HostTensor {
+  std::vector<int64_t> shape;
+  std::vector<float> data;
+  int64_t dim(int i) const { return i < (int)shape.size() ? shape[i] : 1; }
+  int64_t numel() const { int64_t n = 1; for (auto s : shape) n *= s; return n; }
+};
+
+// One prepacked dense contraction: W[Npad, Ktot] K-major in three formats.
+struct PackedGemm {
+  int N = 0, Npad = 0, Ktot = 0;
+  int n_kseg = 0;
+  int taps[2] = {0, 0}, pad[2] = {0, 0}, cin_pad[2] = {0, 0};
+  float* Wf = nullptr;            // exact fp32                     [Npad, Ktot]
+  float* Whl = nullptr;           // tf32 hi rows then lo rows      [2 * Npad, Ktot]
+  __nv_bfloat16* Wh = nullptr;    // bf16                           [Npad, Ktot]
+  float* bias = nullptr;          // [Npad] (zeros when the layer has no bias)
+};
+
+struct Act {          // an activation buffer: fp32 + optional bf16 twin, same ld
+  float* f = nullptr;
+  __nv_bfloat16* h = nullptr;
+  int ld = 0;
+  int rows = 0;
+};
+
+struct Layout {       // host + device description of one frame rate
+  int n_seg = 0, R = 0, n_tiles = 0;
+  std::vector<int> seg_start, seg_len, tile_seg, tile_nvalid, tile_nvalid_p1, tile_seg_p1, cu;  // cu: dense offsets
+  int* d_tile_seg = nullptr; int* d_tile_nvalid = nullptr; int* d_seg_start = nullptr; int* d_seg_len = nullptr;
+  int* d_tile_seg_p1 = nullptr; int* d_tile_nvalid_p1 = nullptr; int* d_seg_len_p1 = nullptr;
+  int* d_cu = nullptr;            // [n_seg + 1] dense offsets (frames)
+  long long* d_off[4] = {nullptr, nullptr, nullptr, nullptr};  // dense element offsets for C = {see engine}
+  int* d_cs = nullptr;            // [n_seg] channel stride (= seg_len)
+  int* d_cs_p1 = nullptr;         // [n_seg] seg_len + 1
+  RowMap map() const { return RowMap{R, n_tiles, n_seg, d_tile_seg, d_tile_nvalid, d_seg_start, d_seg_len}; }
+  RowMap map_p1() const { return RowMap{R, n_tiles, n_seg, d_tile_seg_p1, d_tile_nvalid_p1, d_seg_start, d_seg_len_p1}; }
+  int total() const { return cu.empty() ? 0 : cu.back(); }
+};
+
+enum GemmClass { GC_BODY = 0, GC_ISLAND = 1 };  // ISLAND: STFT, output heads, iSTFT stay fp32-grade
+
+struct Context {
+  int device = 0;
+  int precision = 0;
+  std::string err;
+  int64_t launches = 0;
+  std::map<std::string, HostTensor> tensors;   // "module/key"
+  bool finalized = false;
+
+  // ---- prepacked weights
+  std::map<std::string, PackedGemm> gemm;      // by layer name
+  std::map<std::string, float*> vec;           // small device vectors / matrices by name
+  std::map<std::string, int> vec_len;
+  std::vector<void*> weight_allocs;
+  // style-FC concatenations: row offset of each norm inside the stage matrix
+  std::map<std::string, int> fc_off;
+  int J_dec = 0, J_gen = 0, J_flow = 0, J_pe = 0;
+
+  // ---- layouts + workspace
+  Layout L4, LF;
+  std::vector<int> sig;                        // layout signature
+  char* arena = nullptr; size_t arena_bytes = 0, arena_used = 0;
+  std::map<std::string, Act> act;              // named activation buffers
+  std::map<std::string, void*> raw;            // other named scratch
+  std::map<std::string, size_t> raw_bytes;
+  SourceMeta* h_meta = nullptr;                // pinned
+
+  bool has(const std::string& k) const { return tensors.count(k) != 0; }
+};
+
+// prepack.cu
+int finalize_weights(Context& c);
+PackedGemm pack_from_conv_weight(Context& c, const float* w, const float* bias, int n_out, int cin, int taps, int pad);
+void free_pack(PackedGemm& p);
+
+// pipeline.cu
+int set_layout(Context& c, int n_seg, const int* len_f, const int* len_f4);
+int run_gemm(Context& c, const PackedGemm& pg, int cls, const Act* a0, int a0_col, const Act* a1, int a1_col,
+             const Epi& epi, const RowMap& map, cudaStream_t st, int forced_backend = -1);
+int run_pe_towers(Context& c, const float* d_x, const float* d_style, float* d_pitch, float* d_energy, cudaStream_t st);
+int run_decoder_core(Context& c, const float* d_style, cudaStream_t st);
+int run_decoder(Context& c, const float* d_asr, const float* d_f0, const float* d_n, const float* d_style, float* d_out,
+                cudaStream_t st);
+int run_prior_flow_core(Context& c, const Act& x, const float* d_style, cudaStream_t st);
+int run_prior_flow(Context& c, const float* d_x, const float* d_noise, const float* d_style, float* d_mel,
+                   float* d_z_prior, float* d_z_flow, cudaStream_t st);
+int run_source(Context& c, const float* d_pitch4_dense, const float* d_noise, const float* d_init_phase, float* d_out,
+               cudaStream_t st);
+int run_generator_core(Context& c, const float* d_style, const float* d_noise, const float* d_init_phase,
+                       float* d_audio, float* d_logamp, float* d_phase, cudaStream_t st);
+int run_generator(Context& c, const float* d_mel, const float* d_style, const float* d_pitch4, const float* d_noise,
+                  const float* d_init_phase, float* d_audio, float* d_logamp, float* d_phase, cudaStream_t st);
+int run_speech_frames(Context& c, const float* d_enc_tok, const int* d_cu_tok, const int* d_idx,
+                      const int* d_cu_frames, const float* d_pitch, const float* d_energy, const float* d_style,
+                      const float* d_noise_prior, const float* d_noise_source, const float* d_init_phase,
+                      float* d_audio, float* d_logamp, float* d_phase, cudaStream_t st);
+
+int fail(Context& c, int code, const std::string& msg);
+int cuda_fail(Context& c, cudaError_t e, const char* where);
+
+#define STTS_CK(call)                                                  \
+  do {                                                                 \
+    cudaError_t _e = (call);                                           \
+    if (_e != cudaSuccess) return cuda_fail(c, _e, #call);             \
+    c.launches++;                                                      \
+  } while (0)
+#define STTS_RET(call)                \
+  do {                                \
+    int _r = (call);                  \
+    if (_r != 0) return _r;           \
+  } while (0)
+
+}  // namespace stts

@@ -1,0 +1,422 @@
+// tcgen05 / TMA / TMEM implicit-GEMM conv1d for sm_100a.
+//
+// One CTA computes one 128 x BN output tile of  Y = sum_taps A[r + tap - pad, :] * W[:, tap, :]^T.
+//   warp 0      : TMA producer  (cp.async.bulk.tensor.2d, 128B swizzle, mbarrier complete_tx)
+//   warp 1      : TMEM allocator + MMA issuer (one elected lane, tcgen05.mma.cta_group::1)
+//   warps 2..5  : operand converter during the main loop (fp32 mode only) and epilogue
+//                 (tcgen05.ld 32x32b -> registers -> fused epilogue -> global)
+// Two arithmetic modes:
+//   MODE_BF16   : kind::f16, bf16 operands (bf16 twins of the activations), fp32 accumulate.
+//   MODE_TF32X3 : kind::tf32 with error-compensated operand splitting, x = hi + lo with hi the
+//                 tf32 truncation of x: acc += hi*hi' + hi*lo' + lo*hi'  (~2^-21 relative, i.e.
+//                 fp32-grade).  The activation split is done in shared memory
+//                 by the converter warps (no extra HBM traffic); weight hi/lo are precomputed.
+// The conv zero padding comes from the guard rows of the packed layout and from TMA
+// out-of-bounds zero fill at the two ends of the buffer (signed row coordinate).
+#include <cuda.h>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <tuple>
+
+#include "common.cuh"
+
+namespace stts {
+
+namespace {
+
+// ------------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// Bounded wait: a protocol bug must trap (launch error) instead of hanging the GPU box.
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int tag) {
+  if (mbar_try_wait(bar, parity)) return;
+  uint64_t t0;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  for (;;) {
+    if (mbar_try_wait(bar, parity)) return;
+    uint64_t t1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+    if (t1 - t0 > 2000000000ull) break;  // 2 s
+  }
+  printf("stts gemm_tc: mbarrier timeout tag=%d block=(%d,%d) thread=%d parity=%u\n", tag, blockIdx.x, blockIdx.y,
+         threadIdx.x, parity);
+  __trap();
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, uint64_t* bar, int x, int y) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(x), "r"(y)
+      : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+template <bool TF32>
+__device__ __forceinline__ void tc_mma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
+  if constexpr (TF32) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum)
+        : "memory");
+  } else {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum)
+        : "memory");
+  }
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
+  uint32_t r[16];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// K-major, 128-byte-swizzled shared-memory matrix descriptor (cute::UMMA::SmemDescriptor layout):
+// start>>4 [0,14) | LBO>>4 [16,30) | SBO>>4 [32,46) | version=1 [46,48) | layout SWIZZLE_128B=2 [61,64)
+__device__ __forceinline__ uint64_t make_sdesc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
+  d |= (uint64_t)1 << 16;                 // LBO (unused for swizzled K-major)
+  d |= (uint64_t)(1024 >> 4) << 32;       // SBO: 8 rows * 128 B
+  d |= (uint64_t)1 << 46;                 // descriptor version (Blackwell)
+  d |= (uint64_t)2 << 61;                 // SWIZZLE_128B
+  return d;
+}
+
+enum { MODE_BF16 = 0, MODE_TF32X3 = 1 };
+
+template <int MODE, int BN>
+struct Cfg {
+  static constexpr bool kTF32 = (MODE == MODE_TF32X3);
+  static constexpr int kElem = kTF32 ? 4 : 2;
+  static constexpr int kBK = 128 / kElem;                 // elements per 128-byte swizzle row: 32 / 64
+  static constexpr int kUmmaK = 32 / kElem;               // 8 (tf32) / 16 (bf16)
+  static constexpr int kATile = 128 * 128;                // bytes
+  static constexpr int kBTile = BN * 128;                 // bytes
+  static constexpr int kStageBytes = kTF32 ? (2 * kATile + 2 * kBTile) : (kATile + kBTile);
+  static constexpr int kStages = kTF32 ? (BN == 128 ? 3 : 2) : (BN == 128 ? 6 : 4);
+  static constexpr int kTxBytes = kTF32 ? (kATile + 2 * kBTile) : (kATile + kBTile);
+  static constexpr int kSmem = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+  static constexpr uint32_t kIdesc = (1u << 4) | ((kTF32 ? 2u : 1u) << 7) | ((kTF32 ? 2u : 1u) << 10) |
+                                     ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+};
+
+struct TcParams {
+  int n_kseg;
+  int taps[2], pad[2], cin_chunks[2], col0[2];   // col0 in elements of the operand dtype
+  int n_chunks;
+};
+
+template <int MODE, int BN, int KIND>
+__global__ void __launch_bounds__(192, 1)
+conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant__ CUtensorMap mapA1,
+                    const __grid_constant__ CUtensorMap mapW, const __grid_constant__ CUtensorMap mapWlo,
+                    const TcParams p, const Epi epi, const RowMap map) {
+  using C = Cfg<MODE, BN>;
+  const int tile = blockIdx.y;
+  const int seg = map.tile_seg[tile];
+  if (seg < 0) return;
+  const int nvalid = map.tile_nvalid[tile];
+  const int m0 = tile * 128;
+  const int n0 = blockIdx.x * BN;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::kStages * C::kStageBytes);
+  uint64_t* full = bars;                        // TMA -> consumers
+  uint64_t* empty = bars + C::kStages;          // MMA commit -> TMA
+  uint64_t* conv = bars + 2 * C::kStages;       // converter -> MMA (tf32x3 only)
+  uint64_t* accum = bars + 3 * C::kStages;      // MMA commit -> epilogue
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3 * C::kStages + 1);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < C::kStages; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+      mbar_init(&conv[s], 4);
+    }
+    mbar_init(accum, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"((uint32_t)BN)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  auto stage_ptr = [&](int s) { return smem + (size_t)s * C::kStageBytes; };
+
+  if (warp == 0) {
+    // ------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int ks = 0, tap = 0, cc = 0;
+      int kcol = 0;
+      for (int ch = 0; ch < p.n_chunks; ++ch) {
+        mbar_wait(&empty[stage], phase ^ 1, 1);
+        uint8_t* sp = stage_ptr(stage);
+        mbar_expect_tx(&full[stage], C::kTxBytes);
+        const CUtensorMap* ma = (ks == 0) ? &mapA0 : &mapA1;
+        tma_load_2d(sp, ma, &full[stage], p.col0[ks] + cc * C::kBK, m0 + tap - p.pad[ks]);
+        if constexpr (C::kTF32) {
+          tma_load_2d(sp + 2 * C::kATile, &mapW, &full[stage], kcol, n0);
+          tma_load_2d(sp + 2 * C::kATile + C::kBTile, &mapWlo, &full[stage], kcol, n0);
+        } else {
+          tma_load_2d(sp + C::kATile, &mapW, &full[stage], kcol, n0);
+        }
+        kcol += C::kBK;
+        if (++cc == p.cin_chunks[ks]) { cc = 0; if (++tap == p.taps[ks]) { tap = 0; ++ks; } }
+        if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int ch = 0; ch < p.n_chunks; ++ch) {
+        mbar_wait(&full[stage], phase, 2);
+        if constexpr (C::kTF32) mbar_wait(&conv[stage], phase, 3);
+        tc_fence_after();
+        const uint32_t a_hi = smem_u32(stage_ptr(stage));
+#pragma unroll
+        for (int k = 0; k < C::kBK / C::kUmmaK; ++k) {
+          const uint32_t koff = k * 32;  // bytes inside the 128B swizzle row
+          if constexpr (C::kTF32) {
+            const uint32_t a_lo = a_hi + C::kATile, b_hi = a_hi + 2 * C::kATile, b_lo = b_hi + C::kBTile;
+            // small terms first, then the leading term
+            tc_mma<true>(tmem_base, make_sdesc(a_lo + koff), make_sdesc(b_hi + koff), C::kIdesc, (ch | k) != 0);
+            tc_mma<true>(tmem_base, make_sdesc(a_hi + koff), make_sdesc(b_lo + koff), C::kIdesc, 1);
+            tc_mma<true>(tmem_base, make_sdesc(a_hi + koff), make_sdesc(b_hi + koff), C::kIdesc, 1);
+          } else {
+            const uint32_t b = a_hi + C::kATile;
+            tc_mma<false>(tmem_base, make_sdesc(a_hi + koff), make_sdesc(b + koff), C::kIdesc, (ch | k) != 0);
+          }
+        }
+        tc_commit(&empty[stage]);
+        if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+      }
+      tc_commit(accum);
+    }
+  } else {
+    // ------------------------------------------------------------ converter (tf32x3) + epilogue
+    if constexpr (C::kTF32) {
+      const int ct = threadIdx.x - 64;  // 0..127
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int ch = 0; ch < p.n_chunks; ++ch) {
+        mbar_wait(&full[stage], phase, 4);
+        float4* hi = reinterpret_cast<float4*>(stage_ptr(stage));
+        float4* lo = reinterpret_cast<float4*>(stage_ptr(stage) + C::kATile);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int idx = ct + i * 128;
+          const float4 x = hi[idx];
+          float4 h, l;
+          h.x = __uint_as_float(__float_as_uint(x.x) & 0xFFFFE000u); l.x = x.x - h.x;
+          h.y = __uint_as_float(__float_as_uint(x.y) & 0xFFFFE000u); l.y = x.y - h.y;
+          h.z = __uint_as_float(__float_as_uint(x.z) & 0xFFFFE000u); l.z = x.z - h.z;
+          h.w = __uint_as_float(__float_as_uint(x.w) & 0xFFFFE000u); l.w = x.w - h.w;
+          hi[idx] = h;
+          lo[idx] = l;
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&conv[stage]);
+        if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+      }
+    }
+    mbar_wait(accum, 0, 5);
+    tc_fence_after();
+    const int q = warp & 3;                    // TMEM lane quarter this warp may access
+    const int lr = q * 32 + lane;
+    const int r = m0 + lr;
+    const bool valid = lr < nvalid;
+#pragma unroll 1
+    for (int c = 0; c < BN; c += 16) {
+      if (n0 + c >= epi.N) break;              // warp-uniform
+      float v[16];
+      tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c, v);
+      if (valid) epi_apply<KIND, 16>(epi, r, seg, n0 + c, v);
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)BN) : "memory");
+  }
+}
+
+// ------------------------------------------------------------------ host: tensor maps
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+struct MapKey {
+  const void* base; int rows, ld, elem, box_rows;
+  bool operator<(const MapKey& o) const {
+    return std::tie(base, rows, ld, elem, box_rows) < std::tie(o.base, o.rows, o.ld, o.elem, o.box_rows);
+  }
+};
+std::map<MapKey, CUtensorMap> g_map_cache;
+std::mutex g_map_mutex;
+
+// 2-D row-major [rows, ld] tensor of `elem`-byte elements, box = [128 bytes, box_rows], 128B swizzle.
+bool get_map(const void* base, int rows, int ld, int elem, int box_rows, CUtensorMap* out) {
+  MapKey key{base, rows, ld, elem, box_rows};
+  std::lock_guard<std::mutex> lk(g_map_mutex);
+  auto it = g_map_cache.find(key);
+  if (it != g_map_cache.end()) { *out = it->second; return true; }
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return false;
+  cuuint64_t dims[2] = {(cuuint64_t)ld, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * elem};
+  cuuint32_t box[2] = {(cuuint32_t)(128 / elem), (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUtensorMap m;
+  CUresult r = enc(&m, elem == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                   const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return false;
+  if (g_map_cache.size() > 4096) g_map_cache.clear();
+  g_map_cache[key] = m;
+  *out = m;
+  return true;
+}
+
+template <int MODE, int BN, int KIND>
+cudaError_t launch_one(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
+  using C = Cfg<MODE, BN>;
+  constexpr int elem = C::kElem;
+  CUtensorMap mA[2], mW, mWlo;
+  TcParams p{};
+  p.n_kseg = g.n_kseg;
+  p.n_chunks = 0;
+  for (int s = 0; s < 2; ++s) {
+    const KSeg& ks = g.seg[s < g.n_kseg ? s : 0];
+    const void* base = (MODE == MODE_BF16) ? (const void*)ks.Ah : (const void*)ks.A;
+    const int ld = (MODE == MODE_BF16) ? ks.ldah : ks.lda;
+    if (base == nullptr) return cudaErrorInvalidValue;
+    if (!get_map(base, ks.rows, ld, elem, 128, &mA[s])) return cudaErrorNotSupported;
+    if (s < g.n_kseg) {
+      p.taps[s] = ks.taps;
+      p.pad[s] = ks.pad;
+      p.cin_chunks[s] = ks.cin_pad / C::kBK;
+      p.col0[s] = (MODE == MODE_BF16) ? ks.colh0 : ks.col0;
+      p.n_chunks += ks.taps * p.cin_chunks[s];
+    }
+  }
+  if (MODE == MODE_BF16) {
+    if (!get_map(g.Wh, g.Npad, g.Ktot, 2, BN, &mW)) return cudaErrorNotSupported;
+    mWlo = mW;
+  } else {
+    // W holds hi (tf32-truncated) in rows [0, Npad) and lo in rows [Npad, 2*Npad)
+    if (!get_map(g.W, g.Npad, g.Ktot, 4, BN, &mW)) return cudaErrorNotSupported;
+    if (!get_map(g.W + (size_t)g.Npad * g.Ktot, g.Npad, g.Ktot, 4, BN, &mWlo)) return cudaErrorNotSupported;
+  }
+  auto kern = conv_gemm_tc_kernel<MODE, BN, KIND>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmem);
+    if (e != cudaSuccess) return e;
+    attr_done = true;
+  }
+  dim3 grid((g.epi.N + BN - 1) / BN, map.n_tiles);
+  kern<<<grid, 192, C::kSmem, st>>>(mA[0], mA[1], mW, mWlo, p, g.epi, map);
+  return cudaGetLastError();
+}
+
+template <int MODE, int KIND>
+cudaError_t launch_bn(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
+  // BN = 256 only pays when there are at least two full 128-column tiles to merge.
+  if (MODE == MODE_BF16 && g.epi.N > 128 && g.Npad % 256 == 0) return launch_one<MODE, 256, KIND>(g, map, st);
+  return launch_one<MODE, 128, KIND>(g, map, st);
+}
+
+template <int MODE>
+cudaError_t launch_mode(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
+  switch (g.epi.kind) {
+    case EPI_BIAS: return launch_bn<MODE, EPI_BIAS>(g, map, st);
+    case EPI_RES_SCALE: return launch_bn<MODE, EPI_RES_SCALE>(g, map, st);
+    case EPI_SILU: return launch_bn<MODE, EPI_SILU>(g, map, st);
+    case EPI_ADD: return launch_bn<MODE, EPI_ADD>(g, map, st);
+    case EPI_GATE: return launch_bn<MODE, EPI_GATE>(g, map, st);
+    case EPI_RESSKIP: return launch_bn<MODE, EPI_RESSKIP>(g, map, st);
+    case EPI_COUPLE: return launch_bn<MODE, EPI_COUPLE>(g, map, st);
+    case EPI_PRIOR: return launch_bn<MODE, EPI_PRIOR>(g, map, st);
+    case EPI_STFT: return launch_bn<MODE, EPI_STFT>(g, map, st);
+    default: return cudaErrorInvalidValue;
+  }
+}
+
+}  // namespace
+
+void tc_map_cache_clear() {
+  std::lock_guard<std::mutex> lk(g_map_mutex);
+  g_map_cache.clear();
+}
+
+cudaError_t conv_gemm_tc_bf16(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
+  return launch_mode<MODE_BF16>(g, map, st);
+}
+cudaError_t conv_gemm_tc_tf32x3(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
+  return launch_mode<MODE_TF32X3>(g, map, st);
+}
+
+}  // namespace stts

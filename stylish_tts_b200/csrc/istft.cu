@@ -1,0 +1,89 @@
+// iSTFT vocoder head, train/models/generator.py:425-433 + TorchSTFT.inverse 46-56:
+//   replicate-pad one frame; spec = exp(logamp) * (cos(phase) + i sin(phase));
+//   torch.istft(n_fft 2048, hop 75, win 1200 hann, center=True); tanh.
+// Split in three:  polar_spec (this file) -> inverse-DFT contraction on the GEMM kernel
+// (K = 2 * 1025 interleaved re/im, N = 1200 window taps, basis = irfft * window, prepack.cu)
+// -> ola_tanh (this file): 16-way overlap-add, window-envelope divide, trim, tanh.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace stts {
+
+// spec[r, 2k] = e^la cos(ph), spec[r, 2k+1] = e^la sin(ph).  Row seg_end (one past the last
+// frame, a guard row of the layout) receives the replicate-padded frame.
+__global__ void __launch_bounds__(256) polar_kernel(const float* __restrict__ la, const float* __restrict__ ph, int ld,
+                                                    int n_bins, RowMap map, float* __restrict__ spec, int lds,
+                                                    __nv_bfloat16* __restrict__ spech, int ldsh) {
+  const int tile = blockIdx.x;
+  const int seg = map.tile_seg[tile];
+  if (seg < 0) return;
+  const int nvalid = map.tile_nvalid[tile];
+  const int m0 = tile * 128;
+  const bool last = (m0 + nvalid == map.seg_start[seg] + map.seg_len[seg]);
+  const int rows = nvalid + (last ? 1 : 0);
+  const int total = rows * n_bins;
+  for (int i = blockIdx.y * blockDim.x + threadIdx.x; i < total; i += gridDim.y * blockDim.x) {
+    const int lr = i / n_bins, k = i - lr * n_bins;
+    const int srow = m0 + (lr < nvalid ? lr : nvalid - 1);
+    const float a = expf(la[(size_t)srow * ld + k]);
+    const float p = ph[(size_t)srow * ld + k];
+    float sn, cs;
+    sincosf(p, &sn, &cs);
+    const float re = a * cs, im = a * sn;
+    const size_t o = (size_t)(m0 + lr) * lds + 2 * k;
+    *reinterpret_cast<float2*>(spec + o) = make_float2(re, im);
+    if (spech != nullptr)
+      *reinterpret_cast<__nv_bfloat162*>(spech + (size_t)(m0 + lr) * ldsh + 2 * k) = __floats2bfloat162_rn(re, im);
+  }
+}
+
+cudaError_t polar_spec(const float* logamp, const float* phase, int ld, int n_bins, const RowMap& map, float* spec,
+                       int lds, __nv_bfloat16* spech, int ldsh, cudaStream_t st) {
+  dim3 grid(map.n_tiles, 4);
+  polar_kernel<<<grid, 256, 0, st>>>(logamp, phase, ld, n_bins, map, spec, lds, spech, ldsh);
+  return cudaGetLastError();
+}
+
+// frames[row, n] = window[n] * irfft(spec[row])[424 + n], n in [0, 1200): the only non-zero part
+// of every windowed frame.  Output sample t = 75 h + c of an utterance (after the n_fft/2 trim)
+// receives frame f's tap n = 75 (h - f + 8) + c for f in [h - 7, h + 8], f in [0, L] (L + 1
+// frames exist).  audio = tanh(sum / sum w^2)  with the same index set for the envelope.
+__global__ void __launch_bounds__(256) ola_tanh_kernel(const float* __restrict__ frames, int ldf,
+                                                       const float* __restrict__ wsq, const int* __restrict__ cu4,
+                                                       RowMap map, float* __restrict__ audio) {
+  __shared__ float s_wsq[1200];
+  const int tile = blockIdx.x;
+  const int seg = map.tile_seg[tile];
+  if (seg < 0) return;
+  for (int i = threadIdx.x; i < 1200; i += blockDim.x) s_wsq[i] = wsq[i];
+  __syncthreads();
+  const int nvalid = map.tile_nvalid[tile];
+  const int s0 = map.seg_start[seg], len = map.seg_len[seg];
+  const int h0 = tile * 128 - s0;
+  const size_t base = (size_t)cu4[seg] * 75;
+  const int total = nvalid * 75;
+  for (int i = blockIdx.y * blockDim.x + threadIdx.x; i < total; i += gridDim.y * blockDim.x) {
+    const int lr = i / 75, c = i - lr * 75;
+    const int h = h0 + lr;
+    float acc = 0.f, env = 0.f;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      const int f = h - 7 + j;              // frame index
+      const int n = 75 * (15 - j) + c;      // its tap: 75 (h - f + 8) + c
+      if (f >= 0 && f <= len) {
+        acc += frames[(size_t)(s0 + f) * ldf + n];
+        env += s_wsq[n];
+      }
+    }
+    audio[base + (size_t)h * 75 + c] = tanhf(acc / env);
+  }
+}
+
+cudaError_t ola_tanh(const float* frames, int ldf, const float* wsq, const int* cu4, const RowMap& map, float* audio,
+                     cudaStream_t st) {
+  dim3 grid(map.n_tiles, 4);
+  ola_tanh_kernel<<<grid, 256, 0, st>>>(frames, ldf, wsq, cu4, map, audio);
+  return cudaGetLastError();
+}
+
+}  // namespace stts

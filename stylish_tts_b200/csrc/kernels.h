@@ -1,0 +1,68 @@
+// Internal launcher declarations (one per kernel family).  Every launcher enqueues on the
+// caller's stream, never synchronises and never allocates.
+#pragma once
+#include "common.cuh"
+
+namespace stts {
+
+// ---- conv-as-GEMM (gemm_simt.cu / gemm_tc.cu)
+cudaError_t conv_gemm_simt(const ConvGemm& g, const RowMap& map, cudaStream_t st);
+cudaError_t conv_gemm_tc_bf16(const ConvGemm& g, const RowMap& map, cudaStream_t st);
+cudaError_t conv_gemm_tc_tf32x3(const ConvGemm& g, const RowMap& map, cudaStream_t st);
+void tc_map_cache_clear();
+
+// ---- elementwise.cu
+cudaError_t colstats(const float* x, int ld, int C, const RowMap& map, int mode, float eps, double* scratch,
+                     float* out0, float* out1, cudaStream_t st);
+cudaError_t style_fc(const float* W, const float* bias, const float* s, int J, int K, int B, float* out,
+                     cudaStream_t st);
+cudaError_t adain_act(const float* x, int ldx, int C, const RowMap& map, const float* mean, const float* rstd,
+                      const float* gb, int ldgb, float slope, float* y, int ldy, __nv_bfloat16* yh, int ldyh,
+                      cudaStream_t st);
+cudaError_t expand_tokens(const float* tok, int C, const int* idx, const int* cu_f, const int* tok_off, int div,
+                          const RowMap& map, float* out, int ldo, int col0, __nv_bfloat16* outh, int ldh, int colh0,
+                          cudaStream_t st);
+cudaError_t upsample4(const float* a, const float* b, const int* cu_f, const RowMap& map, float* a4, float* b4,
+                      cudaStream_t st);
+struct F0NDst {  // up to three destinations for the (F0, N) channel pair
+  float* f[3]; int ld[3]; int col[3];
+  __nv_bfloat16* h[3]; int ldh[3];
+};
+cudaError_t f0n_conv(const float* p4, const float* e4, const float* w, const RowMap& map, const F0NDst& d,
+                     cudaStream_t st);
+cudaError_t transpose_in(const float* src, const long long* off, const int* cs, int C, const RowMap& map, float* dst,
+                         int ld, int col0, __nv_bfloat16* dsth, int ldh, int colh0, cudaStream_t st);
+cudaError_t transpose_out(const float* src, int ld, int col0, int C, const RowMap& map, float* dst,
+                          const long long* off, const int* cs, int extra, cudaStream_t st);
+cudaError_t rowvec_copy(float* rowv, float* dense, const int* cu, const RowMap& map, int to_rows, cudaStream_t st);
+cudaError_t dwconv_adaln(const float* x, int ldx, const RowMap& map, int K, const float* wt, const float* bias,
+                         const float* gb, int ldgb, float eps, float* y, int ldy, __nv_bfloat16* yh, int ldyh,
+                         cudaStream_t st);
+cudaError_t adaln2(const float* x, int ldx, const RowMap& map, const float* gb1, const float* gb2, int ldgb, float eps,
+                   float* y1, float* y2, int ldy, __nv_bfloat16* y1h, __nv_bfloat16* y2h, int ldyh, cudaStream_t st);
+cudaError_t grn_apply(float* x, int ldx, int C, const RowMap& map, const float* gx, const float* gamma,
+                      const float* beta, float* scale_scratch, __nv_bfloat16* xh, int ldxh, cudaStream_t st);
+cudaError_t rowdot(const float* x, int ldx, int C, const RowMap& map, const float* w, const float* bias, const int* cu,
+                   float* dense, cudaStream_t st);
+cudaError_t fill(float* p, size_t n, float v, cudaStream_t st);
+
+// ---- length_reg.cu
+cudaError_t durations_from_logits(const float* logits, int n_tokens, int* dur, cudaStream_t st);
+cudaError_t frame_index(const int* dur, const int* cu_tok, int n_seg, int* cu_frames, int* idx, int idx_cap,
+                        int* status, cudaStream_t st);
+
+// ---- source.cu
+struct SourceMeta { int any_voiced; int max_h; int error; int pad; };
+cudaError_t pcph_prefix(const float* p4, const RowMap& map, double* prefix, SourceMeta* meta, cudaStream_t st);
+// src has (R + 16) rows of `ld` floats: logical hop row h of a segment lives at row seg_start + h + 8
+cudaError_t pcph_source(const float* p4, const double* prefix, const SourceMeta* meta, const float* noise,
+                        const float* init_phase, const int* cu4, const RowMap& map, float* src, int ld,
+                        float* dense_out, cudaStream_t st);
+
+// ---- istft.cu
+cudaError_t polar_spec(const float* logamp, const float* phase, int ld, int n_bins, const RowMap& map, float* spec,
+                       int lds, __nv_bfloat16* spech, int ldsh, cudaStream_t st);
+cudaError_t ola_tanh(const float* frames, int ldf, const float* wsq, const int* cu4, const RowMap& map, float* audio,
+                     cudaStream_t st);
+
+}  // namespace stts

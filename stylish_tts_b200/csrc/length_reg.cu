@@ -1,0 +1,105 @@
+// Length regulation: duration logits -> integer durations -> frame -> token index.
+//   DurationProcessor.prediction_to_duration   train/utils.py:468-474
+//   DurationProcessor.duration_to_alignment    train/utils.py:476-489
+// The reference materialises a dense one-hot [T, F] matrix and multiplies with it; here the
+// alignment is the int32 index vector (its argmax over tokens), which is what every consumer
+// needs.  Integer work: bit-exact by construction once the durations agree.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace stts {
+
+__constant__ float kClassToDur[16] = {1, 2, 3, 4, 5, 6, 7, 9, 12, 15, 18, 22, 27, 32, 38, 46};  // utils.py:391-393
+
+__global__ void __launch_bounds__(256) durations_kernel(const float* __restrict__ logits, int n, int* __restrict__ dur) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  float x[16];
+  const float4* p = reinterpret_cast<const float4*>(logits + (size_t)t * 16);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float4 v = p[i];
+    x[4 * i] = v.x; x[4 * i + 1] = v.y; x[4 * i + 2] = v.z; x[4 * i + 3] = v.w;
+  }
+  float m = x[0];
+  int am = 0;
+#pragma unroll
+  for (int i = 1; i < 16; ++i) if (x[i] > m) { m = x[i]; am = i; }   // first maximum, like torch.argmax
+  float e[16], s = 0.f;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) { e[i] = expf(x[i] - m); s += e[i]; }
+  const float inv = 1.f / s;
+  float soft = 0.f;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) soft += (e[i] * inv) * kClassToDur[i];
+  soft = fmaxf(rintf(soft), 1.f);                 // torch.round = half to even
+  const float arg = kClassToDur[am];
+  dur[t] = (int)((arg < 7.f) ? arg : soft);
+}
+
+cudaError_t durations_from_logits(const float* logits, int n_tokens, int* dur, cudaStream_t st) {
+  if (n_tokens <= 0) return cudaSuccess;
+  durations_kernel<<<(n_tokens + 255) / 256, 256, 0, st>>>(logits, n_tokens, dur);
+  return cudaGetLastError();
+}
+
+// cu_frames[b] = sum of the durations of utterances < b (exclusive scan over utterances)
+__global__ void __launch_bounds__(1024) seg_totals_kernel(const int* __restrict__ dur, const int* __restrict__ cu_tok,
+                                                          int n_seg, int* __restrict__ cu_frames) {
+  __shared__ int tot[1024];
+  const int b = threadIdx.x;
+  int s = 0;
+  if (b < n_seg)
+    for (int t = cu_tok[b]; t < cu_tok[b + 1]; ++t) s += dur[t];
+  tot[b] = s;
+  __syncthreads();
+  if (b == 0) {
+    int run = 0;
+    for (int i = 0; i < n_seg; ++i) { const int v = tot[i]; cu_frames[i] = run; run += v; }
+    cu_frames[n_seg] = run;
+  }
+}
+
+// idx[cu_frames[b] + f] = token (local to the utterance) that owns frame f
+__global__ void __launch_bounds__(512) frame_index_kernel(const int* __restrict__ dur, const int* __restrict__ cu_tok,
+                                                          const int* __restrict__ cu_frames, int* __restrict__ idx,
+                                                          int idx_cap, int* __restrict__ status) {
+  __shared__ int sc[512];
+  __shared__ int carry;
+  const int b = blockIdx.x;
+  const int t0 = cu_tok[b], nt = cu_tok[b + 1] - t0;
+  const int f0 = cu_frames[b];
+  if (threadIdx.x == 0) {
+    carry = 0;
+    if (b == gridDim.x - 1 && cu_frames[gridDim.x] > idx_cap) atomicExch(status, 1);
+  }
+  __syncthreads();
+  for (int base = 0; base < nt; base += 512) {
+    const int t = base + threadIdx.x;
+    const int d = (t < nt) ? dur[t0 + t] : 0;
+    sc[threadIdx.x] = d;
+    __syncthreads();
+    for (int o = 1; o < 512; o <<= 1) {       // Hillis-Steele inclusive scan
+      const int v = (threadIdx.x >= o) ? sc[threadIdx.x - o] : 0;
+      __syncthreads();
+      sc[threadIdx.x] += v;
+      __syncthreads();
+    }
+    const int start = carry + sc[threadIdx.x] - d;
+    for (int k = 0; k < d; ++k)
+      if (f0 + start + k < idx_cap) idx[f0 + start + k] = t;
+    __syncthreads();
+    if (threadIdx.x == 511) carry += sc[511];
+    __syncthreads();
+  }
+}
+
+cudaError_t frame_index(const int* dur, const int* cu_tok, int n_seg, int* cu_frames, int* idx, int idx_cap,
+                        int* status, cudaStream_t st) {
+  if (n_seg <= 0 || n_seg > 1024) return cudaErrorInvalidValue;
+  seg_totals_kernel<<<1, 1024, 0, st>>>(dur, cu_tok, n_seg, cu_frames);
+  frame_index_kernel<<<n_seg, 512, 0, st>>>(dur, cu_tok, cu_frames, idx, idx_cap, status);
+  return cudaGetLastError();
+}
+
+}  // namespace stts

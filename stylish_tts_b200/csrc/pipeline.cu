@@ -1,0 +1,582 @@
+// Stage orchestration of the frame-rate synthesis path on the packed layout.
+// Reference call graph: SpeechPredictor.forward speech_predictor.py:85-129 ->
+//   Decoder.forward decoder.py:47-60 -> PriorEncoder flow.py:311-315 ->
+//   ResidualCouplingBlock(reverse) flow.py:132-151 -> post_flow -> Generator.forward
+//   generator.py:402-438;  PitchEnergyPredictor towers pitch_energy_predictor.py:111-119.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+#include "engine.h"
+
+namespace stts {
+
+int fail(Context& c, int code, const std::string& msg) {
+  c.err = msg;
+  return code;
+}
+int cuda_fail(Context& c, cudaError_t e, const char* where) {
+  c.err = std::string("CUDA error '") + cudaGetErrorString(e) + "' at " + where;
+  return -5;
+}
+
+namespace {
+
+size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+struct ArenaPlan {
+  size_t used = 0;
+  size_t take(size_t bytes) {
+    const size_t o = used;
+    used = align_up(used + bytes, 1024);
+    return o;
+  }
+};
+
+void build_layout(Layout& L, int n_seg, const int* len) {
+  L = Layout();
+  L.n_seg = n_seg;
+  L.seg_start.resize(n_seg);
+  L.seg_len.assign(len, len + n_seg);
+  L.cu.assign(n_seg + 1, 0);
+  int pos = 0;
+  for (int b = 0; b < n_seg; ++b) {
+    L.seg_start[b] = pos;
+    L.cu[b + 1] = L.cu[b] + len[b];
+    pos = (pos + len[b] + STTS_GUARD + 127) / 128 * 128;
+  }
+  L.R = pos;
+  L.n_tiles = pos / 128;
+  L.tile_seg.assign(L.n_tiles, -1);
+  L.tile_nvalid.assign(L.n_tiles, 0);
+  L.tile_seg_p1.assign(L.n_tiles, -1);
+  L.tile_nvalid_p1.assign(L.n_tiles, 0);
+  for (int b = 0; b < n_seg; ++b) {
+    for (int r = L.seg_start[b]; r < L.seg_start[b] + len[b]; r += 128) {
+      const int t = r / 128;
+      L.tile_seg[t] = b;
+      L.tile_nvalid[t] = std::min(128, L.seg_start[b] + len[b] - r);
+    }
+    for (int r = L.seg_start[b]; r < L.seg_start[b] + len[b] + 1; r += 128) {
+      const int t = r / 128;
+      L.tile_seg_p1[t] = b;
+      L.tile_nvalid_p1[t] = std::min(128, L.seg_start[b] + len[b] + 1 - r);
+    }
+  }
+}
+
+}  // namespace
+
+// ----------------------------------------------------------------------------- layout + workspace
+int set_layout(Context& c, int n_seg, const int* len_f, const int* len_f4) {
+  if (n_seg <= 0 || n_seg > 1024) return fail(c, -1, "n_seg must be in [1, 1024]");
+  std::vector<int> sig;
+  sig.push_back(n_seg);
+  for (int b = 0; b < n_seg; ++b) {
+    const int f = len_f ? len_f[b] : 0, f4 = len_f4 ? len_f4[b] : 0;
+    if (f < 0 || f4 < 0 || (len_f && f == 0) || (len_f4 && f4 == 0)) return fail(c, -2, "utterance length must be > 0");
+    if (len_f4 && f4 * 75 <= 1024)
+      return fail(c, -2, "utterance shorter than the STFT reflect padding (75 * L must exceed 1024)");
+    sig.push_back(f);
+    sig.push_back(f4);
+  }
+  if (sig == c.sig && c.arena != nullptr) return 0;
+  cudaError_t e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) return cuda_fail(c, e, "set_layout sync");
+  tc_map_cache_clear();
+  std::vector<int> ones(n_seg, 1);
+  build_layout(c.L4, n_seg, len_f4 ? len_f4 : ones.data());
+  build_layout(c.LF, n_seg, len_f ? len_f : ones.data());
+  const bool use4 = len_f4 != nullptr, useF = len_f != nullptr;
+
+  struct Want { std::string name; int rate; int ld; int extra_rows; bool twin; };
+  std::vector<Want> wants;
+  if (use4) {
+    wants = {{"X0", 4, 192, 0, true},   {"ACT0", 4, 192, 0, true},  {"XCa", 4, 640, 0, true},  {"XCb", 4, 640, 0, true},
+             {"ACT", 4, 640, 0, true},  {"Y1", 4, 512, 0, false},   {"NOISE", 4, 128, 0, false}, {"Z", 4, 128, 0, true},
+             {"ZP", 4, 128, 0, false},  {"WH", 4, 128, 0, true},    {"ACTS", 4, 128, 0, true},  {"WOUT", 4, 128, 0, true},
+             {"CATP", 4, 1024, 0, true}, {"SRC", 4, 96, 16, false}, {"HS", 4, 1088, 0, true},   {"HP", 4, 1088, 0, true},
+             {"XG", 4, 512, 0, false},  {"XGN", 4, 512, 0, true},   {"H", 4, 1536, 0, true},    {"AMPN", 4, 512, 0, true},
+             {"PHN", 4, 512, 0, true},  {"LA", 4, 1088, 0, false},  {"PH", 4, 1088, 0, false},  {"SPEC", 4, 2112, 0, false},
+             {"YF", 4, 1216, 0, false}, {"DIN", 4, 512, 0, true}};
+  }
+  if (useF) {
+    std::vector<Want> wf = {{"PX", 1, 320, 0, true},  {"PACT", 1, 320, 0, true}, {"PY1", 1, 320, 0, false},
+                            {"PA", 1, 320, 0, true},  {"PB", 1, 320, 0, true}};
+    wants.insert(wants.end(), wf.begin(), wf.end());
+  }
+  ArenaPlan plan;
+  std::map<std::string, size_t> off_f, off_h;
+  for (auto& w : wants) {
+    const int R = (w.rate == 4 ? c.L4.R : c.LF.R) + w.extra_rows;
+    off_f[w.name] = plan.take((size_t)R * w.ld * 4);
+    if (w.twin) off_h[w.name] = plan.take((size_t)R * w.ld * 2);
+  }
+  struct RawWant { std::string name; size_t bytes; };
+  const int R4 = c.L4.R, RF = c.LF.R, B = n_seg;
+  const int maxR = std::max(R4, RF), max_tiles = maxR / 128;
+  std::vector<RawWant> raws = {
+      {"P4", (size_t)R4 * 4},          {"E4", (size_t)R4 * 4},           {"PREFIX", (size_t)R4 * 8},
+      {"META", (size_t)B * sizeof(SourceMeta)},                          {"STATS", (size_t)max_tiles * 1536 * 2 * 8},
+      {"MEAN", (size_t)B * 1536 * 4},  {"RSTD", (size_t)B * 1536 * 4},   {"GX", (size_t)B * 1536 * 4},
+      {"GSCALE", (size_t)B * 1536 * 4}, {"GB_DEC", (size_t)B * std::max(c.J_dec, 1) * 4},
+      {"GB_GEN", (size_t)B * std::max(c.J_gen, 1) * 4},                  {"GB_FLOW", (size_t)B * std::max(c.J_flow, 1) * 4},
+      {"GB_PE", (size_t)B * std::max(c.J_pe, 1) * 4},                    {"STATUS", 256},
+  };
+  // layout descriptor arrays (ints / long longs)
+  const char* rates[2] = {"4", "F"};
+  for (int k = 0; k < 2; ++k) {
+    const Layout& L = k == 0 ? c.L4 : c.LF;
+    const std::string s = rates[k];
+    raws.push_back({"tile_seg" + s, (size_t)L.n_tiles * 4});
+    raws.push_back({"tile_nvalid" + s, (size_t)L.n_tiles * 4});
+    raws.push_back({"tile_seg_p1" + s, (size_t)L.n_tiles * 4});
+    raws.push_back({"tile_nvalid_p1" + s, (size_t)L.n_tiles * 4});
+    raws.push_back({"seg_start" + s, (size_t)B * 4});
+    raws.push_back({"seg_len" + s, (size_t)B * 4});
+    raws.push_back({"seg_len_p1" + s, (size_t)B * 4});
+    raws.push_back({"cu" + s, (size_t)(B + 1) * 4});
+    raws.push_back({"cs" + s, (size_t)B * 4});
+    raws.push_back({"cs_p1" + s, (size_t)B * 4});
+    for (int j = 0; j < 4; ++j) raws.push_back({"off" + std::to_string(j) + s, (size_t)B * 8});
+  }
+  std::map<std::string, size_t> off_raw;
+  for (auto& r : raws) off_raw[r.name] = plan.take(r.bytes);
+
+  if (plan.used > c.arena_bytes) {
+    if (c.arena) cudaFree(c.arena);
+    c.arena = nullptr;
+    c.arena_bytes = 0;
+    e = cudaMalloc(&c.arena, plan.used);
+    if (e != cudaSuccess) return cuda_fail(c, e, "workspace cudaMalloc");
+    c.arena_bytes = plan.used;
+  }
+  c.arena_used = plan.used;
+  e = cudaMemset(c.arena, 0, plan.used);
+  if (e != cudaSuccess) return cuda_fail(c, e, "workspace memset");
+
+  c.act.clear();
+  c.raw.clear();
+  c.raw_bytes.clear();
+  for (auto& w : wants) {
+    Act a;
+    a.ld = w.ld;
+    a.rows = (w.rate == 4 ? c.L4.R : c.LF.R) + w.extra_rows;
+    a.f = reinterpret_cast<float*>(c.arena + off_f[w.name]);
+    a.h = w.twin ? reinterpret_cast<__nv_bfloat16*>(c.arena + off_h[w.name]) : nullptr;
+    c.act[w.name] = a;
+  }
+  for (auto& r : raws) { c.raw[r.name] = c.arena + off_raw[r.name]; c.raw_bytes[r.name] = r.bytes; }
+
+  auto up = [&](const std::string& name, const void* h, size_t bytes) {
+    if (bytes) cudaMemcpy(c.raw[name], h, bytes, cudaMemcpyHostToDevice);
+  };
+  for (int k = 0; k < 2; ++k) {
+    Layout& L = k == 0 ? c.L4 : c.LF;
+    const std::string s = rates[k];
+    std::vector<int> len_p1(B), cs(B), cs_p1(B);
+    for (int b = 0; b < B; ++b) { len_p1[b] = L.seg_len[b] + 1; cs[b] = L.seg_len[b]; cs_p1[b] = L.seg_len[b] + 1; }
+    up("tile_seg" + s, L.tile_seg.data(), (size_t)L.n_tiles * 4);
+    up("tile_nvalid" + s, L.tile_nvalid.data(), (size_t)L.n_tiles * 4);
+    up("tile_seg_p1" + s, L.tile_seg_p1.data(), (size_t)L.n_tiles * 4);
+    up("tile_nvalid_p1" + s, L.tile_nvalid_p1.data(), (size_t)L.n_tiles * 4);
+    up("seg_start" + s, L.seg_start.data(), (size_t)B * 4);
+    up("seg_len" + s, L.seg_len.data(), (size_t)B * 4);
+    up("seg_len_p1" + s, len_p1.data(), (size_t)B * 4);
+    up("cu" + s, L.cu.data(), (size_t)(B + 1) * 4);
+    up("cs" + s, cs.data(), (size_t)B * 4);
+    up("cs_p1" + s, cs_p1.data(), (size_t)B * 4);
+    // dense element offsets: j = 0: C = 128, 1: C = 512, 2: C = 1025 with L + 1 frames, 3: C = 320
+    const int Cs[4] = {128, 512, 1025, 320};
+    for (int j = 0; j < 4; ++j) {
+      std::vector<long long> off(B);
+      for (int b = 0; b < B; ++b) off[b] = (long long)Cs[j] * (L.cu[b] + (j == 2 ? b : 0));
+      up("off" + std::to_string(j) + s, off.data(), (size_t)B * 8);
+      L.d_off[j] = reinterpret_cast<long long*>(c.raw["off" + std::to_string(j) + s]);
+    }
+    L.d_tile_seg = (int*)c.raw["tile_seg" + s];
+    L.d_tile_nvalid = (int*)c.raw["tile_nvalid" + s];
+    L.d_tile_seg_p1 = (int*)c.raw["tile_seg_p1" + s];
+    L.d_tile_nvalid_p1 = (int*)c.raw["tile_nvalid_p1" + s];
+    L.d_seg_start = (int*)c.raw["seg_start" + s];
+    L.d_seg_len = (int*)c.raw["seg_len" + s];
+    L.d_seg_len_p1 = (int*)c.raw["seg_len_p1" + s];
+    L.d_cu = (int*)c.raw["cu" + s];
+    L.d_cs = (int*)c.raw["cs" + s];
+    L.d_cs_p1 = (int*)c.raw["cs_p1" + s];
+  }
+  if (c.h_meta == nullptr) cudaMallocHost(&c.h_meta, 1024 * sizeof(SourceMeta));
+  e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) return cuda_fail(c, e, "set_layout upload");
+  c.sig = sig;
+  return 0;
+}
+
+// ----------------------------------------------------------------------------- GEMM dispatch
+int run_gemm(Context& c, const PackedGemm& pg, int cls, const Act* a0, int a0_col, const Act* a1, int a1_col,
+             const Epi& epi_in, const RowMap& map, cudaStream_t st, int forced_backend) {
+  int backend = forced_backend;
+  if (backend < 0) {
+    if (c.precision == 0) backend = 0;
+    else if (c.precision == 1) backend = (cls == GC_ISLAND) ? 2 : 1;
+    else backend = 2;
+  }
+  ConvGemm g;
+  std::memset(&g, 0, sizeof(g));
+  g.n_kseg = pg.n_kseg;
+  const Act* as[2] = {a0, a1};
+  const int cols[2] = {a0_col, a1_col};
+  for (int s = 0; s < pg.n_kseg; ++s) {
+    if (as[s] == nullptr) return fail(c, -1, "run_gemm: missing operand");
+    KSeg& k = g.seg[s];
+    k.A = as[s]->f; k.lda = as[s]->ld; k.col0 = cols[s];
+    k.Ah = as[s]->h; k.ldah = as[s]->ld; k.colh0 = cols[s];
+    k.taps = pg.taps[s]; k.pad = pg.pad[s]; k.cin_pad = pg.cin_pad[s];
+    k.rows = as[s]->rows;
+    if (cols[s] + k.cin_pad > as[s]->ld) return fail(c, -2, "run_gemm: K slice exceeds the operand row");
+    if (backend == 1 && k.Ah == nullptr) return fail(c, -1, "run_gemm: bf16 twin missing");
+  }
+  g.W = (backend == 2) ? pg.Whl : pg.Wf;
+  g.Wh = pg.Wh;
+  g.Ktot = pg.Ktot;
+  g.Npad = pg.Npad;
+  g.epi = epi_in;
+  g.epi.N = pg.N;
+  if (g.epi.bias == nullptr && g.epi.kind != EPI_STFT) g.epi.bias = pg.bias;
+  cudaError_t e;
+  if (backend == 0) e = conv_gemm_simt(g, map, st);
+  else if (backend == 1) e = conv_gemm_tc_bf16(g, map, st);
+  else e = conv_gemm_tc_tf32x3(g, map, st);
+  if (e != cudaSuccess) return cuda_fail(c, e, "conv_gemm launch");
+  c.launches++;
+  return 0;
+}
+
+namespace {
+
+struct Stage {
+  Context& c;
+  cudaStream_t st;
+  bool twins;
+  Stage(Context& ctx, cudaStream_t s) : c(ctx), st(s), twins(ctx.precision == 1) {}
+  Act& A(const char* n) { return c.act[n]; }
+  template <typename T> T* R(const char* n) { return reinterpret_cast<T*>(c.raw[n]); }
+  __nv_bfloat16* tw(const Act& a) const { return twins ? a.h : nullptr; }
+  Epi epi(int kind, const Act& dst, int col0) const {
+    Epi e;
+    std::memset(&e, 0, sizeof(e));
+    e.kind = kind;
+    e.out = dst.f; e.ldo = dst.ld; e.col0 = col0;
+    e.outh = tw(dst); e.ldh = dst.ld; e.colh0 = col0;
+    e.scale = 1.f;
+    return e;
+  }
+};
+
+// AdaptiveDecoderBlock on packed rows (ada_norm.py:165-182).
+//   in:  `x` (C_in channels, operand of the optional fused 1x1 shortcut, cin_pad = x pad)
+//   out: dst[:, dst_col : dst_col + C_out] = (conv2(act(norm2(conv1(act(norm1(x)))))) + shortcut(x)) / sqrt(2)
+int ada_block(Stage& S, const std::string& name, const Act& x, int cin, int cout, Act& act1, Act& y1, Act& act2,
+              Act& dst, int dst_col, const float* gb, int ldgb, const RowMap& map) {
+  Context& c = S.c;
+  const PackedGemm& g1 = c.gemm[name + ".conv1"];
+  const PackedGemm& g2 = c.gemm[name + ".conv2"];
+  float* mean = S.R<float>("MEAN");
+  float* rstd = S.R<float>("RSTD");
+  double* stats = S.R<double>("STATS");
+  STTS_CK(colstats(x.f, x.ld, cin, map, 0, 1e-5f, stats, mean, rstd, S.st));
+  c.launches++;
+  STTS_CK(adain_act(x.f, x.ld, cin, map, mean, rstd, gb + c.fc_off[name + ".norm1"], ldgb, 0.2f, act1.f, act1.ld,
+                    S.tw(act1), act1.ld, S.st));
+  {
+    Epi e = S.epi(EPI_BIAS, y1, 0);
+    e.outh = nullptr;
+    STTS_RET(run_gemm(c, g1, GC_BODY, &act1, 0, nullptr, 0, e, map, S.st));
+  }
+  STTS_CK(colstats(y1.f, y1.ld, cout, map, 0, 1e-5f, stats, mean, rstd, S.st));
+  c.launches++;
+  STTS_CK(adain_act(y1.f, y1.ld, cout, map, mean, rstd, gb + c.fc_off[name + ".norm2"], ldgb, 0.2f, act2.f, act2.ld,
+                    S.tw(act2), act2.ld, S.st));
+  {
+    Epi e = S.epi(EPI_RES_SCALE, dst, dst_col);
+    e.scale = 0.70710678118654752440f;
+    if (g2.n_kseg == 1) { e.res = x.f; e.ldr = x.ld; e.rcol0 = 0; }   // identity shortcut
+    STTS_RET(run_gemm(c, g2, GC_BODY, &act2, 0, (g2.n_kseg == 2) ? &x : nullptr, 0, e, map, S.st));
+  }
+  return 0;
+}
+
+}  // namespace
+
+// ----------------------------------------------------------------------------- pitch / energy towers
+int run_pe_towers(Context& c, const float* d_x, const float* d_style, float* d_pitch, float* d_energy,
+                  cudaStream_t st) {
+  if (!c.finalized || c.J_pe == 0) return fail(c, -3, "pitch_energy_predictor weights not loaded");
+  if (c.LF.total() == 0 || c.act.count("PX") == 0) return fail(c, -4, "no hop-300 layout set");
+  Stage S(c, st);
+  const RowMap map = c.LF.map();
+  Act &px = S.A("PX"), &pact = S.A("PACT"), &py1 = S.A("PY1"), &pa = S.A("PA"), &pb = S.A("PB");
+  float* gb = S.R<float>("GB_PE");
+  STTS_CK(style_fc(c.vec["pe.fc_W"], c.vec["pe.fc_b"], d_style, c.J_pe, 64, c.LF.n_seg, gb, st));
+  STTS_CK(transpose_in(d_x, c.LF.d_off[3], c.LF.d_cs, 320, map, px.f, px.ld, 0, S.tw(px), px.ld, 0, st));
+  const char* tw[2] = {"F0", "N"};
+  for (int t = 0; t < 2; ++t) {
+    const std::string base = std::string("pe.") + tw[t];
+    STTS_RET(ada_block(S, base + "0", px, 320, 320, pact, py1, pact, pa, 0, gb, c.J_pe, map));
+    STTS_RET(ada_block(S, base + "1", pa, 320, 320, pact, py1, pact, pb, 0, gb, c.J_pe, map));
+    STTS_RET(ada_block(S, base + "2", pb, 320, 320, pact, py1, pact, pa, 0, gb, c.J_pe, map));
+    STTS_CK(rowdot(pa.f, pa.ld, 320, map, c.vec[t == 0 ? "pe.F0_proj_w" : "pe.N_proj_w"],
+                   c.vec[t == 0 ? "pe.F0_proj_b" : "pe.N_proj_b"], c.LF.d_cu, t == 0 ? d_pitch : d_energy, st));
+  }
+  return 0;
+}
+
+// ----------------------------------------------------------------------------- decoder
+// Expects X0 = [asr(128) | F0 | N] and XCa/XCb columns 576, 577 = (F0, N) already assembled.
+// Leaves the decoder output in XCa[:, 0:512].
+int run_decoder_core(Context& c, const float* d_style, cudaStream_t st) {
+  if (!c.finalized || c.J_dec == 0) return fail(c, -3, "speech_predictor weights not loaded");
+  Stage S(c, st);
+  const RowMap map = c.L4.map();
+  Act &x0 = S.A("X0"), &act0 = S.A("ACT0"), &xa = S.A("XCa"), &xb = S.A("XCb"), &act = S.A("ACT"), &y1 = S.A("Y1");
+  float* gb = S.R<float>("GB_DEC");
+  STTS_CK(style_fc(c.vec["dec.fc_W"], c.vec["dec.fc_b"], d_style, c.J_dec, 64, c.L4.n_seg, gb, st));
+  // asr_res = Conv1d(128, 64, 1)(asr)  (decoder.py:43-45,54) into both ping-pong buffers
+  for (Act* dst : {&xa, &xb}) {
+    Epi e = S.epi(EPI_BIAS, *dst, 512);
+    STTS_RET(run_gemm(c, c.gemm["dec.asr_res"], GC_BODY, &x0, 0, nullptr, 0, e, map, st));
+  }
+  STTS_RET(ada_block(S, "dec.encode", x0, 130, 512, act0, y1, act, xa, 0, gb, c.J_dec, map));
+  for (int i = 0; i < 4; ++i) {
+    Act& src = (i % 2 == 0) ? xa : xb;
+    Act& dst = (i % 2 == 0) ? xb : xa;
+    STTS_RET(ada_block(S, "dec.decode" + std::to_string(i), src, 578, 512, act, y1, act, dst, 0, gb, c.J_dec, map));
+  }
+  return 0;
+}
+
+static int assemble_f0n(Context& c, Stage& S, cudaStream_t st) {
+  Act &x0 = S.A("X0"), &xa = S.A("XCa"), &xb = S.A("XCb");
+  F0NDst d;
+  std::memset(&d, 0, sizeof(d));
+  Act* dst[3] = {&x0, &xa, &xb};
+  const int col[3] = {128, 576, 576};
+  for (int k = 0; k < 3; ++k) {
+    d.f[k] = dst[k]->f; d.ld[k] = dst[k]->ld; d.col[k] = col[k];
+    d.h[k] = S.tw(*dst[k]); d.ldh[k] = dst[k]->ld;
+  }
+  STTS_CK(f0n_conv(S.R<float>("P4"), S.R<float>("E4"), c.vec["dec.f0n_w"], c.L4.map(), d, st));
+  return 0;
+}
+
+int run_decoder(Context& c, const float* d_asr, const float* d_f0, const float* d_n, const float* d_style, float* d_out,
+                cudaStream_t st) {
+  if (c.L4.total() == 0 || c.act.count("X0") == 0) return fail(c, -4, "no hop-75 layout set");
+  Stage S(c, st);
+  const RowMap map = c.L4.map();
+  Act& x0 = S.A("X0");
+  STTS_CK(transpose_in(d_asr, c.L4.d_off[0], c.L4.d_cs, 128, map, x0.f, x0.ld, 0, S.tw(x0), x0.ld, 0, st));
+  STTS_CK(rowvec_copy(S.R<float>("P4"), const_cast<float*>(d_f0), c.L4.d_cu, map, 1, st));
+  STTS_CK(rowvec_copy(S.R<float>("E4"), const_cast<float*>(d_n), c.L4.d_cu, map, 1, st));
+  STTS_RET(assemble_f0n(c, S, st));
+  STTS_RET(run_decoder_core(c, d_style, st));
+  Act& xa = S.A("XCa");
+  STTS_CK(transpose_out(xa.f, xa.ld, 0, 512, map, d_out, c.L4.d_off[1], c.L4.d_cs, 0, st));
+  return 0;
+}
+
+// ----------------------------------------------------------------------------- prior + flow^-1 + post_flow
+// `x`: decoder output (512 channels at columns 0..511); NOISE holds the packed randn draw.
+// Results: ZP = z_text (prior sample), Z = z after the reversed flow, CATP[:, 0:512] = mel.
+int run_prior_flow_core(Context& c, const Act& x, const float* d_style, cudaStream_t st) {
+  if (!c.finalized || c.J_flow == 0) return fail(c, -3, "speech_predictor weights not loaded");
+  Stage S(c, st);
+  const RowMap map = c.L4.map();
+  Act &z = S.A("Z"), &zp = S.A("ZP"), &wh = S.A("WH"), &acts = S.A("ACTS"), &wout = S.A("WOUT"), &catp = S.A("CATP");
+  Act& noise = S.A("NOISE");
+  float* g = S.R<float>("GB_FLOW");
+  STTS_CK(style_fc(c.vec["flow.fc_W"], c.vec["flow.fc_b"], d_style, c.J_flow, 64, c.L4.n_seg, g, st));
+  {  // z = mean + noise * exp(logstd)   (flow.py:311-315)
+    Epi e = S.epi(EPI_PRIOR, z, 0);
+    e.res = noise.f; e.ldr = noise.ld; e.rcol0 = 0;
+    STTS_RET(run_gemm(c, c.gemm["prior"], GC_BODY, &x, 0, nullptr, 0, e, map, st));
+  }
+  STTS_CK(cudaMemcpyAsync(zp.f, z.f, (size_t)z.rows * z.ld * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  // reversed(self.flows): Flip first, then coupling layer i = 7 .. 0  (flow.py:138-142)
+  for (int step = 1; step <= 8; ++step) {
+    const int i = 8 - step;
+    const std::string nm = "flow" + std::to_string(i);
+    const int z0col = 64 * (step % 2), z1col = 64 * ((step + 1) % 2);
+    const float* gi = g + c.fc_off[nm + ".cond"];
+    {  // h = pre(z0)
+      Epi e = S.epi(EPI_BIAS, wh, 0);
+      STTS_RET(run_gemm(c, c.gemm[nm + ".pre"], GC_BODY, &z, z0col, nullptr, 0, e, map, st));
+    }
+    for (int l = 0; l < 4; ++l) {
+      {  // acts = tanh . sigmoid (in_layer(x) + g_l)
+        Epi e = S.epi(EPI_GATE, acts, 0);
+        e.segvec = gi + l * 256;
+        e.ldseg = c.J_flow;
+        STTS_RET(run_gemm(c, c.gemm[nm + ".in" + std::to_string(l)], GC_BODY, &wh, 0, nullptr, 0, e, map, st));
+      }
+      {  // x += res ; output += skip
+        Epi e = S.epi(EPI_RESSKIP, wh, 0);
+        e.split = (l < 3) ? 128 : 0;
+        e.out2 = wout.f; e.ldo2 = wout.ld; e.col20 = 0;
+        e.outh2 = S.tw(wout); e.ldh2 = wout.ld; e.colh20 = 0;
+        e.accumulate2 = (l > 0) ? 1 : 0;
+        STTS_RET(run_gemm(c, c.gemm[nm + ".rs" + std::to_string(l)], GC_BODY, &acts, 0, nullptr, 0, e, map, st));
+      }
+    }
+    {  // z1 = (z1 - m) * exp(-logs)
+      Epi e = S.epi(EPI_COUPLE, z, z1col);
+      STTS_RET(run_gemm(c, c.gemm[nm + ".proj"], GC_BODY, &wout, 0, nullptr, 0, e, map, st));
+    }
+  }
+  {  // mel = post_flow(z)
+    Epi e = S.epi(EPI_BIAS, catp, 0);
+    STTS_RET(run_gemm(c, c.gemm["post_flow"], GC_BODY, &z, 0, nullptr, 0, e, map, st));
+  }
+  return 0;
+}
+
+int run_prior_flow(Context& c, const float* d_x, const float* d_noise, const float* d_style, float* d_mel,
+                   float* d_z_prior, float* d_z_flow, cudaStream_t st) {
+  if (c.L4.total() == 0 || c.act.count("DIN") == 0) return fail(c, -4, "no hop-75 layout set");
+  Stage S(c, st);
+  const RowMap map = c.L4.map();
+  Act &din = S.A("DIN"), &noise = S.A("NOISE");
+  STTS_CK(transpose_in(d_x, c.L4.d_off[1], c.L4.d_cs, 512, map, din.f, din.ld, 0, S.tw(din), din.ld, 0, st));
+  STTS_CK(transpose_in(d_noise, c.L4.d_off[0], c.L4.d_cs, 128, map, noise.f, noise.ld, 0, nullptr, 0, 0, st));
+  STTS_RET(run_prior_flow_core(c, din, d_style, st));
+  Act &catp = S.A("CATP"), &z = S.A("Z"), &zp = S.A("ZP");
+  STTS_CK(transpose_out(catp.f, catp.ld, 0, 512, map, d_mel, c.L4.d_off[1], c.L4.d_cs, 0, st));
+  if (d_z_prior) STTS_CK(transpose_out(zp.f, zp.ld, 0, 128, map, d_z_prior, c.L4.d_off[0], c.L4.d_cs, 0, st));
+  if (d_z_flow) STTS_CK(transpose_out(z.f, z.ld, 0, 128, map, d_z_flow, c.L4.d_off[0], c.L4.d_cs, 0, st));
+  return 0;
+}
+
+// ----------------------------------------------------------------------------- source
+// expects P4 (pitch per hop-75 frame, packed rows)
+static int source_core(Context& c, Stage& S, const float* d_noise, const float* d_init_phase, float* d_dense_out,
+                       cudaStream_t st) {
+  const RowMap map = c.L4.map();
+  Act& src = S.A("SRC");
+  STTS_CK(pcph_prefix(S.R<float>("P4"), map, S.R<double>("PREFIX"), S.R<SourceMeta>("META"), st));
+  STTS_CK(pcph_source(S.R<float>("P4"), S.R<double>("PREFIX"), S.R<SourceMeta>("META"), d_noise, d_init_phase,
+                      c.L4.d_cu, map, src.f, src.ld, d_dense_out, st));
+  return 0;
+}
+
+int run_source(Context& c, const float* d_pitch4_dense, const float* d_noise, const float* d_init_phase, float* d_out,
+               cudaStream_t st) {
+  if (c.L4.total() == 0 || c.act.count("SRC") == 0) return fail(c, -4, "no hop-75 layout set");
+  Stage S(c, st);
+  STTS_CK(rowvec_copy(S.R<float>("P4"), const_cast<float*>(d_pitch4_dense), c.L4.d_cu, c.L4.map(), 1, st));
+  return source_core(c, S, d_noise, d_init_phase, d_out, st);
+}
+
+// ----------------------------------------------------------------------------- generator
+// expects CATP[:, 0:512] = mel and P4 = pitch (packed rows)
+int run_generator_core(Context& c, const float* d_style, const float* d_noise, const float* d_init_phase,
+                       float* d_audio, float* d_logamp, float* d_phase, cudaStream_t st) {
+  if (!c.finalized || c.J_gen == 0) return fail(c, -3, "speech_predictor weights not loaded");
+  Stage S(c, st);
+  const RowMap map = c.L4.map();
+  const RowMap map_p1 = c.L4.map_p1();
+  Act &src = S.A("SRC"), &hs = S.A("HS"), &hp = S.A("HP"), &catp = S.A("CATP"), &xg = S.A("XG"), &xgn = S.A("XGN");
+  Act &h = S.A("H"), &ampn = S.A("AMPN"), &phn = S.A("PHN"), &la = S.A("LA"), &ph = S.A("PH"), &spec = S.A("SPEC");
+  Act& yf = S.A("YF");
+  float* gb = S.R<float>("GB_GEN");
+  STTS_CK(style_fc(c.vec["gen.fc_W"], c.vec["gen.fc_b"], d_style, c.J_gen, 64, c.L4.n_seg, gb, st));
+  STTS_RET(source_core(c, S, d_noise, d_init_phase, nullptr, st));
+  {  // STFT of the source -> |X|, atan2 phase   (generator.py:407-410)
+    Epi e = S.epi(EPI_STFT, hs, 0);
+    e.out2 = hp.f; e.ldo2 = hp.ld; e.col20 = 0;
+    e.outh2 = S.tw(hp); e.ldh2 = hp.ld; e.colh20 = 0;
+    STTS_RET(run_gemm(c, c.gemm["stft"], GC_ISLAND, &src, 0, nullptr, 0, e, map, st));
+  }
+  {  // amp / phase prior convs (k7) into the concat buffer   (generator.py:412-413)
+    Epi e = S.epi(EPI_BIAS, catp, 512);
+    STTS_RET(run_gemm(c, c.gemm["gen.amp_prior"], GC_BODY, &hs, 0, nullptr, 0, e, map, st));
+    Epi e2 = S.epi(EPI_BIAS, catp, 768);
+    STTS_RET(run_gemm(c, c.gemm["gen.phase_prior"], GC_BODY, &hp, 0, nullptr, 0, e2, map, st));
+  }
+  {  // projector 1x1 on cat[mel, logamp_prior, phase_prior]   (generator.py:414)
+    Epi e = S.epi(EPI_BIAS, xg, 0);
+    e.outh = nullptr;
+    STTS_RET(run_gemm(c, c.gemm["gen.projector"], GC_BODY, &catp, 0, nullptr, 0, e, map, st));
+  }
+  for (int i = 0; i < 4; ++i) {  // ConvNeXt blocks (generator.py:469-485)
+    const std::string nm = "gen.cnx" + std::to_string(i);
+    STTS_CK(dwconv_adaln(xg.f, xg.ld, map, c.vec_len[nm + ".dw_k"], c.vec[nm + ".dw_w"], c.vec[nm + ".dw_b"],
+                         gb + c.fc_off[nm + ".norm"], c.J_gen, 1e-6f, xgn.f, xgn.ld, S.tw(xgn), xgn.ld, st));
+    {
+      Epi e = S.epi(EPI_SILU, h, 0);
+      e.outh = nullptr;
+      STTS_RET(run_gemm(c, c.gemm[nm + ".pw1"], GC_BODY, &xgn, 0, nullptr, 0, e, map, st));
+    }
+    STTS_CK(colstats(h.f, h.ld, 1536, map, 1, 0.f, S.R<double>("STATS"), S.R<float>("GX"), nullptr, st));
+    c.launches++;
+    STTS_CK(grn_apply(h.f, h.ld, 1536, map, S.R<float>("GX"), c.vec[nm + ".grn_gamma"], c.vec[nm + ".grn_beta"],
+                      S.R<float>("GSCALE"), S.tw(h), h.ld, st));
+    c.launches++;
+    {
+      Epi e = S.epi(EPI_ADD, xg, 0);
+      e.outh = nullptr;
+      e.res = xg.f; e.ldr = xg.ld; e.rcol0 = 0;
+      STTS_RET(run_gemm(c, c.gemm[nm + ".pw2"], GC_BODY, &h, 0, nullptr, 0, e, map, st));
+    }
+  }
+  // two AdaLN heads + output convs k7 over cat[AdaLN(x), prior]   (generator.py:417-423)
+  STTS_CK(adaln2(xg.f, xg.ld, map, gb + c.fc_off["gen.amp_norm"], gb + c.fc_off["gen.phase_norm"], c.J_gen, 1e-5f,
+                 ampn.f, phn.f, ampn.ld, S.tw(ampn), S.tw(phn), ampn.ld, st));
+  {
+    Epi e = S.epi(EPI_BIAS, la, 0);
+    STTS_RET(run_gemm(c, c.gemm["gen.amp_head"], GC_ISLAND, &ampn, 0, &catp, 512, e, map, st));
+    Epi e2 = S.epi(EPI_BIAS, ph, 0);
+    STTS_RET(run_gemm(c, c.gemm["gen.phase_head"], GC_ISLAND, &phn, 0, &catp, 768, e2, map, st));
+  }
+  // replicate pad + exp / cos / sin -> inverse DFT x window -> overlap-add, envelope, tanh
+  STTS_CK(polar_spec(la.f, ph.f, la.ld, 1025, map, spec.f, spec.ld, nullptr, 0, st));
+  {
+    Epi e = S.epi(EPI_BIAS, yf, 0);
+    STTS_RET(run_gemm(c, c.gemm["istft"], GC_ISLAND, &spec, 0, nullptr, 0, e, map_p1, st));
+  }
+  STTS_CK(ola_tanh(yf.f, yf.ld, c.vec["wsq"], c.L4.d_cu, map, d_audio, st));
+  if (d_logamp) STTS_CK(transpose_out(la.f, la.ld, 0, 1025, map, d_logamp, c.L4.d_off[2], c.L4.d_cs_p1, 1, st));
+  if (d_phase) STTS_CK(transpose_out(ph.f, ph.ld, 0, 1025, map, d_phase, c.L4.d_off[2], c.L4.d_cs_p1, 1, st));
+  return 0;
+}
+
+int run_generator(Context& c, const float* d_mel, const float* d_style, const float* d_pitch4, const float* d_noise,
+                  const float* d_init_phase, float* d_audio, float* d_logamp, float* d_phase, cudaStream_t st) {
+  if (c.L4.total() == 0 || c.act.count("CATP") == 0) return fail(c, -4, "no hop-75 layout set");
+  Stage S(c, st);
+  const RowMap map = c.L4.map();
+  Act& catp = S.A("CATP");
+  STTS_CK(transpose_in(d_mel, c.L4.d_off[1], c.L4.d_cs, 512, map, catp.f, catp.ld, 0, S.tw(catp), catp.ld, 0, st));
+  STTS_CK(rowvec_copy(S.R<float>("P4"), const_cast<float*>(d_pitch4), c.L4.d_cu, map, 1, st));
+  return run_generator_core(c, d_style, d_noise, d_init_phase, d_audio, d_logamp, d_phase, st);
+}
+
+// ----------------------------------------------------------------------------- fused frame-rate path
+int run_speech_frames(Context& c, const float* d_enc_tok, const int* d_cu_tok, const int* d_idx,
+                      const int* d_cu_frames, const float* d_pitch, const float* d_energy, const float* d_style,
+                      const float* d_noise_prior, const float* d_noise_source, const float* d_init_phase,
+                      float* d_audio, float* d_logamp, float* d_phase, cudaStream_t st) {
+  if (c.L4.total() == 0 || c.LF.total() == 0 || c.act.count("X0") == 0) return fail(c, -4, "no layout set");
+  Stage S(c, st);
+  const RowMap map = c.L4.map();
+  Act &x0 = S.A("X0"), &noise = S.A("NOISE"), &xa = S.A("XCa");
+  // text_encoding @ alignment.repeat_interleave(4)  ==  gather   (speech_predictor.py:88,93)
+  STTS_CK(expand_tokens(d_enc_tok, 128, d_idx, d_cu_frames, d_cu_tok, 4, map, x0.f, x0.ld, 0, S.tw(x0), x0.ld, 0, st));
+  STTS_CK(upsample4(d_pitch, d_energy, d_cu_frames, map, S.R<float>("P4"), S.R<float>("E4"), st));
+  STTS_RET(assemble_f0n(c, S, st));
+  STTS_CK(transpose_in(d_noise_prior, c.L4.d_off[0], c.L4.d_cs, 128, map, noise.f, noise.ld, 0, nullptr, 0, 0, st));
+  STTS_RET(run_decoder_core(c, d_style, st));
+  STTS_RET(run_prior_flow_core(c, xa, d_style, st));
+  return run_generator_core(c, d_style, d_noise_source, d_init_phase, d_audio, d_logamp, d_phase, st);
+}
+
+}  // namespace stts

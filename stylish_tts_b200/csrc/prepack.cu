@@ -1,0 +1,481 @@
+// Host-side weight preparation (runs once, at stts_finalize_weights):
+//   * folds both weight-norm dialects: parametrizations.weight.original0/1
+//     (ada_norm.py:158-163, decoder.py:35-45, pitch_energy_predictor.py:42-54) and legacy
+//     weight_g / weight_v (flow.py:40,52,60);  w = v * g / ||v||, norm over all dims but 0
+//   * re-lays every dense layer as a K-major matrix W[Npad, taps * cin_pad] in three formats
+//     (exact fp32, tf32 hi/lo split, bf16), with the row permutations the fused epilogues need
+//     (tanh/sigmoid pairs, mean/logstd pairs, re/im pairs) and zero padding of K and N
+//   * concatenates the Linear(style) layers of each stage into one matrix
+//   * builds the STFT / iSTFT contraction bases of TorchSTFT (generator.py:23-56)
+#include <cmath>
+#include <cstring>
+
+#include "engine.h"
+
+namespace stts {
+
+namespace {
+
+const double kPi = 3.14159265358979323846;
+
+uint16_t f2bf(float f) {
+  uint32_t u;
+  std::memcpy(&u, &f, 4);
+  if ((u & 0x7FFFFFFFu) > 0x7F800000u) return (uint16_t)((u >> 16) | 0x40);
+  const uint32_t r = 0x7FFFu + ((u >> 16) & 1u);
+  return (uint16_t)((u + r) >> 16);
+}
+float trunc_tf32(float f) {
+  uint32_t u;
+  std::memcpy(&u, &f, 4);
+  u &= 0xFFFFE000u;
+  std::memcpy(&f, &u, 4);
+  return f;
+}
+
+template <typename T>
+T* dev_upload(Context& c, const T* h, size_t n) {
+  T* d = nullptr;
+  if (cudaMalloc(&d, n * sizeof(T)) != cudaSuccess) return nullptr;
+  cudaMemcpy(d, h, n * sizeof(T), cudaMemcpyHostToDevice);
+  c.weight_allocs.push_back(d);
+  return d;
+}
+
+struct Builder {
+  int N = 0, Npad = 0, Ktot = 0, n_kseg = 0;
+  int taps[2] = {0, 0}, pad[2] = {0, 0}, cin_pad[2] = {0, 0};
+  std::vector<float> W, bias;
+  void init(int n, int nk, const int* t, const int* p, const int* cp) {
+    N = n;
+    Npad = (n + 127) / 128 * 128;
+    n_kseg = nk;
+    Ktot = 0;
+    for (int s = 0; s < nk; ++s) { taps[s] = t[s]; pad[s] = p[s]; cin_pad[s] = cp[s]; Ktot += t[s] * cp[s]; }
+    W.assign((size_t)Npad * Ktot, 0.f);
+    bias.assign(Npad, 0.f);
+  }
+  int koff(int s) const { return s == 0 ? 0 : taps[0] * cin_pad[0]; }
+  // w: [n_src, cin_total, k] (k = taps[s]; Linear weights have k = 1)
+  void rows(int s, const HostTensor& w, int src0, int n, int cin0, int cin_cnt, int dst0, int dstride) {
+    const int cin_total = (int)w.dim(1), k = (int)w.dim(2);
+    for (int i = 0; i < n; ++i) {
+      float* d = &W[(size_t)(dst0 + i * dstride) * Ktot + koff(s)];
+      const float* src = &w.data[(size_t)(src0 + i) * cin_total * k];
+      for (int cc = 0; cc < cin_cnt; ++cc)
+        for (int j = 0; j < k; ++j) d[(size_t)j * cin_pad[s] + cc] = src[(size_t)(cin0 + cc) * k + j];
+    }
+  }
+  void set_bias(const HostTensor& b, int src0, int n, int dst0, int dstride) {
+    for (int i = 0; i < n; ++i) bias[dst0 + i * dstride] = b.data[src0 + i];
+  }
+  PackedGemm upload(Context& c) const {
+    PackedGemm p;
+    p.N = N; p.Npad = Npad; p.Ktot = Ktot; p.n_kseg = n_kseg;
+    for (int s = 0; s < 2; ++s) { p.taps[s] = taps[s]; p.pad[s] = pad[s]; p.cin_pad[s] = cin_pad[s]; }
+    const size_t n = (size_t)Npad * Ktot;
+    std::vector<float> hl(2 * n);
+    std::vector<uint16_t> bf(n);
+    for (size_t i = 0; i < n; ++i) {
+      const float hi = trunc_tf32(W[i]);
+      hl[i] = hi;
+      hl[n + i] = trunc_tf32(W[i] - hi);
+      bf[i] = f2bf(W[i]);
+    }
+    p.Wf = dev_upload(c, W.data(), n);
+    p.Whl = dev_upload(c, hl.data(), 2 * n);
+    p.Wh = reinterpret_cast<__nv_bfloat16*>(dev_upload(c, bf.data(), n));
+    p.bias = dev_upload(c, bias.data(), (size_t)Npad);
+    return p;
+  }
+};
+
+int pad64(int c) { return (c + 63) / 64 * 64; }
+
+}  // namespace
+
+void free_pack(PackedGemm& p) {
+  cudaFree(p.Wf); cudaFree(p.Whl); cudaFree(p.Wh); cudaFree(p.bias);
+  p = PackedGemm();
+}
+
+// used by stts_test_conv: pack an arbitrary Conv1d weight [n_out, cin, taps]
+PackedGemm pack_from_conv_weight(Context& c, const float* w, const float* bias, int n_out, int cin, int taps, int pad) {
+  HostTensor t;
+  t.shape = {n_out, cin, taps};
+  t.data.assign(w, w + (size_t)n_out * cin * taps);
+  Builder b;
+  const int tp[2] = {taps, 0}, pd[2] = {pad, 0}, cp[2] = {pad64(cin), 0};
+  b.init(n_out, 1, tp, pd, cp);
+  b.rows(0, t, 0, n_out, 0, cin, 0, 1);
+  if (bias != nullptr) for (int i = 0; i < n_out; ++i) b.bias[i] = bias[i];
+  Context tmp;  // allocations owned by the returned pack, not by the context
+  PackedGemm p = b.upload(tmp);
+  return p;
+}
+
+namespace {
+
+struct Loader {
+  Context& c;
+  std::string module;
+  bool ok = true;
+  std::string missing;
+  const HostTensor* get(const std::string& key) {
+    auto it = c.tensors.find(module + "/" + key);
+    if (it == c.tensors.end()) { if (ok) missing = module + "/" + key; ok = false; return nullptr; }
+    return &it->second;
+  }
+  bool has(const std::string& key) const { return c.tensors.count(module + "/" + key) != 0; }
+  // effective weight as [N, Cin, k]
+  HostTensor weight(const std::string& p) {
+    HostTensor out;
+    const HostTensor *g = nullptr, *v = nullptr;
+    if (has(p + "parametrizations.weight.original0")) {
+      g = get(p + "parametrizations.weight.original0");
+      v = get(p + "parametrizations.weight.original1");
+    } else if (has(p + "weight_g")) {
+      g = get(p + "weight_g");
+      v = get(p + "weight_v");
+    } else {
+      v = get(p + "weight");
+    }
+    if (v == nullptr) { out.shape = {0, 0, 0}; return out; }
+    out.shape = {v->dim(0), v->dim(1), v->dim(2)};
+    out.data = v->data;
+    if (g != nullptr) {
+      const int64_t n = v->dim(0), per = v->numel() / n;
+      for (int64_t i = 0; i < n; ++i) {
+        double ss = 0.0;
+        for (int64_t j = 0; j < per; ++j) { const double x = v->data[i * per + j]; ss += x * x; }
+        const float scale = g->data[i] / (float)std::sqrt(ss);
+        for (int64_t j = 0; j < per; ++j) out.data[i * per + j] = v->data[i * per + j] * scale;
+      }
+    }
+    return out;
+  }
+};
+
+void put_vec(Context& c, const std::string& name, const std::vector<float>& v) {
+  c.vec[name] = dev_upload(c, v.data(), v.size());
+  c.vec_len[name] = (int)v.size();
+}
+
+// concatenated Linear(style) layers of a stage: rows appended in call order
+struct FcCat {
+  std::vector<float> W, b;
+  int J = 0;
+  int add(const HostTensor& w, const HostTensor& bias) {
+    const int off = J;
+    W.insert(W.end(), w.data.begin(), w.data.end());
+    b.insert(b.end(), bias.data.begin(), bias.data.end());
+    J += (int)w.dim(0);
+    return off;
+  }
+};
+
+// AdaptiveDecoderBlock (ada_norm.py:142-182): conv1, conv2 (+ fused 1x1 shortcut), two AdaIN FCs
+bool pack_ada_block(Context& c, Loader& L, const std::string& p, const std::string& name, int cin, int cout,
+                    int cin_pad, FcCat& fc) {
+  const HostTensor w1 = L.weight(p + "conv1."), w2 = L.weight(p + "conv2.");
+  const HostTensor *b1 = L.get(p + "conv1.bias"), *b2 = L.get(p + "conv2.bias");
+  const HostTensor *n1w = L.get(p + "norm1.fc.weight"), *n1b = L.get(p + "norm1.fc.bias");
+  const HostTensor *n2w = L.get(p + "norm2.fc.weight"), *n2b = L.get(p + "norm2.fc.bias");
+  if (!L.ok) return false;
+  Builder a;
+  { const int t[2] = {3, 0}, pd[2] = {1, 0}, cp[2] = {cin_pad, 0}; a.init(cout, 1, t, pd, cp); }
+  a.rows(0, w1, 0, cout, 0, cin, 0, 1);
+  a.set_bias(*b1, 0, cout, 0, 1);
+  c.gemm[name + ".conv1"] = a.upload(c);
+  Builder b;
+  const bool learned = L.has(p + "conv1x1.parametrizations.weight.original0");
+  if (learned) {
+    const HostTensor wsc = L.weight(p + "conv1x1.");
+    const int t[2] = {3, 1}, pd[2] = {1, 0}, cp[2] = {pad64(cout), cin_pad};
+    b.init(cout, 2, t, pd, cp);
+    b.rows(0, w2, 0, cout, 0, cout, 0, 1);
+    b.rows(1, wsc, 0, cout, 0, cin, 0, 1);
+  } else {
+    const int t[2] = {3, 0}, pd[2] = {1, 0}, cp[2] = {pad64(cout), 0};
+    b.init(cout, 1, t, pd, cp);
+    b.rows(0, w2, 0, cout, 0, cout, 0, 1);
+  }
+  b.set_bias(*b2, 0, cout, 0, 1);
+  c.gemm[name + ".conv2"] = b.upload(c);
+  c.fc_off[name + ".norm1"] = fc.add(*n1w, *n1b);
+  c.fc_off[name + ".norm2"] = fc.add(*n2w, *n2b);
+  return true;
+}
+
+}  // namespace
+
+int finalize_weights(Context& c) {
+  for (void* p : c.weight_allocs) cudaFree(p);
+  c.weight_allocs.clear();
+  c.gemm.clear(); c.vec.clear(); c.vec_len.clear(); c.fc_off.clear();
+  c.finalized = false;
+
+  // ======================================================================= speech_predictor
+  Loader L{c, "speech_predictor"};
+  if (c.has("speech_predictor/decoder.encode.conv1.bias")) {
+    FcCat fc;
+    // ---- decoder (decoder.py:7-60)
+    if (!pack_ada_block(c, L, "decoder.encode.", "dec.encode", 130, 512, 192, fc))
+      return fail(c, -3, "missing weight " + L.missing);
+    for (int i = 0; i < 4; ++i)
+      if (!pack_ada_block(c, L, "decoder.decode." + std::to_string(i) + ".", "dec.decode" + std::to_string(i), 578,
+                          512, 640, fc))
+        return fail(c, -3, "missing weight " + L.missing);
+    c.J_dec = fc.J;
+    put_vec(c, "dec.fc_W", fc.W);
+    put_vec(c, "dec.fc_b", fc.b);
+    {
+      const HostTensor wf = L.weight("decoder.F0_conv."), wn = L.weight("decoder.N_conv.");
+      const HostTensor *bf = L.get("decoder.F0_conv.bias"), *bn = L.get("decoder.N_conv.bias");
+      const HostTensor wr = L.weight("decoder.asr_res.0.");
+      const HostTensor* br = L.get("decoder.asr_res.0.bias");
+      if (!L.ok) return fail(c, -3, "missing weight " + L.missing);
+      put_vec(c, "dec.f0n_w", {wf.data[0], wf.data[1], wf.data[2], bf->data[0], wn.data[0], wn.data[1], wn.data[2],
+                               bn->data[0]});
+      Builder b;
+      const int t[2] = {1, 0}, pd[2] = {0, 0}, cp[2] = {128, 0};
+      b.init(64, 1, t, pd, cp);
+      b.rows(0, wr, 0, 64, 0, 128, 0, 1);
+      b.set_bias(*br, 0, 64, 0, 1);
+      c.gemm["dec.asr_res"] = b.upload(c);
+    }
+    // ---- prior encoder (flow.py:296-315): (mean_i, logstd_i) interleaved rows
+    {
+      const HostTensor *wm = L.get("prior_encoder.proj_mean.weight"), *bm = L.get("prior_encoder.proj_mean.bias");
+      const HostTensor *ws = L.get("prior_encoder.proj_logstd.weight"), *bs = L.get("prior_encoder.proj_logstd.bias");
+      if (!L.ok) return fail(c, -3, "missing weight " + L.missing);
+      Builder b;
+      const int t[2] = {1, 0}, pd[2] = {0, 0}, cp[2] = {512, 0};
+      b.init(256, 1, t, pd, cp);
+      b.rows(0, *wm, 0, 128, 0, 512, 0, 2);
+      b.rows(0, *ws, 0, 128, 0, 512, 1, 2);
+      b.set_bias(*bm, 0, 128, 0, 2);
+      b.set_bias(*bs, 0, 128, 1, 2);
+      c.gemm["prior"] = b.upload(c);
+    }
+    // ---- flow (flow.py:99-226): 8 coupling layers x (pre, 4 x (in_layer k5, res_skip), proj)
+    {
+      FcCat ffc;
+      for (int i = 0; i < 8; ++i) {
+        const std::string q = "flow.flows." + std::to_string(2 * i) + ".";
+        const std::string nm = "flow" + std::to_string(i);
+        const HostTensor *wp = L.get(q + "pre.weight"), *bp = L.get(q + "pre.bias");
+        if (!L.ok) return fail(c, -3, "missing weight " + L.missing);
+        {
+          Builder b;
+          const int t[2] = {1, 0}, pd[2] = {0, 0}, cp[2] = {64, 0};
+          b.init(128, 1, t, pd, cp);
+          b.rows(0, *wp, 0, 128, 0, 64, 0, 1);
+          b.set_bias(*bp, 0, 128, 0, 1);
+          c.gemm[nm + ".pre"] = b.upload(c);
+        }
+        for (int l = 0; l < 4; ++l) {
+          const std::string ls = std::to_string(l);
+          const HostTensor wi = L.weight(q + "enc.in_layers." + ls + ".");
+          const HostTensor* bi = L.get(q + "enc.in_layers." + ls + ".bias");
+          const HostTensor wr = L.weight(q + "enc.res_skip_layers." + ls + ".");
+          const HostTensor* br = L.get(q + "enc.res_skip_layers." + ls + ".bias");
+          if (!L.ok) return fail(c, -3, "missing weight " + L.missing);
+          {  // rows interleaved (tanh_i, sigmoid_i) for the fused gate epilogue
+            Builder b;
+            const int t[2] = {5, 0}, pd[2] = {2, 0}, cp[2] = {128, 0};
+            b.init(256, 1, t, pd, cp);
+            b.rows(0, wi, 0, 128, 0, 128, 0, 2);
+            b.rows(0, wi, 128, 128, 0, 128, 1, 2);
+            b.set_bias(*bi, 0, 128, 0, 2);
+            b.set_bias(*bi, 128, 128, 1, 2);
+            c.gemm[nm + ".in" + ls] = b.upload(c);
+          }
+          {
+            const int nrs = (int)wr.dim(0);  // 256, last layer 128
+            Builder b;
+            const int t[2] = {1, 0}, pd[2] = {0, 0}, cp[2] = {128, 0};
+            b.init(nrs, 1, t, pd, cp);
+            b.rows(0, wr, 0, nrs, 0, 128, 0, 1);
+            b.set_bias(*br, 0, nrs, 0, 1);
+            c.gemm[nm + ".rs" + ls] = b.upload(c);
+          }
+        }
+        const HostTensor wc = L.weight(q + "enc.cond_layer.");
+        const HostTensor* bc = L.get(q + "enc.cond_layer.bias");
+        const HostTensor *wm = L.get(q + "proj_mean.weight"), *bm = L.get(q + "proj_mean.bias");
+        const HostTensor *ws = L.get(q + "proj_logstd.weight"), *bs = L.get(q + "proj_logstd.bias");
+        if (!L.ok) return fail(c, -3, "missing weight " + L.missing);
+        c.fc_off[nm + ".cond"] = ffc.add(wc, *bc);
+        Builder b;
+        const int t[2] = {1, 0}, pd[2] = {0, 0}, cp[2] = {128, 0};
+        b.init(128, 1, t, pd, cp);
+        b.rows(0, *wm, 0, 64, 0, 128, 0, 2);
+        b.rows(0, *ws, 0, 64, 0, 128, 1, 2);
+        b.set_bias(*bm, 0, 64, 0, 2);
+        b.set_bias(*bs, 0, 64, 1, 2);
+        c.gemm[nm + ".proj"] = b.upload(c);
+      }
+      c.J_flow = ffc.J;
+      put_vec(c, "flow.fc_W", ffc.W);
+      put_vec(c, "flow.fc_b", ffc.b);
+      const HostTensor *wpf = L.get("post_flow.weight"), *bpf = L.get("post_flow.bias");
+      if (!L.ok) return fail(c, -3, "missing weight " + L.missing);
+      Builder b;
+      const int t[2] = {1, 0}, pd[2] = {0, 0}, cp[2] = {128, 0};
+      b.init(512, 1, t, pd, cp);
+      b.rows(0, *wpf, 0, 512, 0, 128, 0, 1);
+      b.set_bias(*bpf, 0, 512, 0, 1);
+      c.gemm["post_flow"] = b.upload(c);
+    }
+    // ---- generator (generator.py:339-438)
+    {
+      FcCat gfc;
+      const char* prior_names[2] = {"generator.amp_prior_conv.", "generator.phase_prior_conv."};
+      for (int h = 0; h < 2; ++h) {
+        const HostTensor* w = L.get(std::string(prior_names[h]) + "weight");
+        const HostTensor* bb = L.get(std::string(prior_names[h]) + "bias");
+        if (!L.ok) return fail(c, -3, "missing weight " + L.missing);
+        Builder b;
+        const int t[2] = {7, 0}, pd[2] = {3, 0}, cp[2] = {1088, 0};
+        b.init(256, 1, t, pd, cp);
+        b.rows(0, *w, 0, 256, 0, 1025, 0, 1);
+        b.set_bias(*bb, 0, 256, 0, 1);
+        c.gemm[h == 0 ? "gen.amp_prior" : "gen.phase_prior"] = b.upload(c);
+      }
+      {
+        const HostTensor *w = L.get("generator.projector.weight"), *bb = L.get("generator.projector.bias");
+        if (!L.ok) return fail(c, -3, "missing weight " + L.missing);
+        Builder b;
+        const int t[2] = {1, 0}, pd[2] = {0, 0}, cp[2] = {1024, 0};
+        b.init(512, 1, t, pd, cp);
+        b.rows(0, *w, 0, 512, 0, 1024, 0, 1);
+        b.set_bias(*bb, 0, 512, 0, 1);
+        c.gemm["gen.projector"] = b.upload(c);
+      }
+      for (int i = 0; i < 4; ++i) {
+        const std::string q = "generator.convnext." + std::to_string(i) + ".";
+        const std::string nm = "gen.cnx" + std::to_string(i);
+        const HostTensor *dw = L.get(q + "dwconv.weight"), *db = L.get(q + "dwconv.bias");
+        const HostTensor *nw = L.get(q + "norm.fc.weight"), *nb = L.get(q + "norm.fc.bias");
+        const HostTensor *w1 = L.get(q + "pwconv1.weight"), *b1 = L.get(q + "pwconv1.bias");
+        const HostTensor *w2 = L.get(q + "pwconv2.weight"), *b2 = L.get(q + "pwconv2.bias");
+        const HostTensor *gg = L.get(q + "grn.gamma"), *gb = L.get(q + "grn.beta");
+        if (!L.ok) return fail(c, -3, "missing weight " + L.missing);
+        const int k = (int)dw->dim(2);
+        std::vector<float> wt((size_t)k * 512);
+        for (int ch = 0; ch < 512; ++ch)
+          for (int j = 0; j < k; ++j) wt[(size_t)j * 512 + ch] = dw->data[(size_t)ch * k + j];
+        put_vec(c, nm + ".dw_w", wt);
+        put_vec(c, nm + ".dw_b", db->data);
+        put_vec(c, nm + ".grn_gamma", gg->data);
+        put_vec(c, nm + ".grn_beta", gb->data);
+        c.vec_len[nm + ".dw_k"] = k;
+        c.fc_off[nm + ".norm"] = gfc.add(*nw, *nb);
+        {
+          Builder b;
+          const int t[2] = {1, 0}, pd[2] = {0, 0}, cp[2] = {512, 0};
+          b.init(1536, 1, t, pd, cp);
+          b.rows(0, *w1, 0, 1536, 0, 512, 0, 1);
+          b.set_bias(*b1, 0, 1536, 0, 1);
+          c.gemm[nm + ".pw1"] = b.upload(c);
+        }
+        {
+          Builder b;
+          const int t[2] = {1, 0}, pd[2] = {0, 0}, cp[2] = {1536, 0};
+          b.init(512, 1, t, pd, cp);
+          b.rows(0, *w2, 0, 512, 0, 1536, 0, 1);
+          b.set_bias(*b2, 0, 512, 0, 1);
+          c.gemm[nm + ".pw2"] = b.upload(c);
+        }
+      }
+      const char* heads[2] = {"amp", "phase"};
+      for (int h = 0; h < 2; ++h) {
+        const std::string hn = heads[h];
+        const HostTensor *nw = L.get("generator." + hn + "_final_layer_norm.fc.weight");
+        const HostTensor *nb = L.get("generator." + hn + "_final_layer_norm.fc.bias");
+        const HostTensor *w = L.get("generator." + hn + "_output_conv.weight");
+        const HostTensor *bb = L.get("generator." + hn + "_output_conv.bias");
+        if (!L.ok) return fail(c, -3, "missing weight " + L.missing);
+        c.fc_off["gen." + hn + "_norm"] = gfc.add(*nw, *nb);
+        // K-seg 0: AdaLN(x) (512 ch), K-seg 1: the prior conv output (256 ch) -- torch.cat order
+        Builder b;
+        const int t[2] = {7, 7}, pd[2] = {3, 3}, cp[2] = {512, 256};
+        b.init(1025, 2, t, pd, cp);
+        b.rows(0, *w, 0, 1025, 0, 512, 0, 1);
+        b.rows(1, *w, 0, 1025, 512, 256, 0, 1);
+        b.set_bias(*bb, 0, 1025, 0, 1);
+        c.gemm["gen." + hn + "_head"] = b.upload(c);
+      }
+      c.J_gen = gfc.J;
+      put_vec(c, "gen.fc_W", gfc.W);
+      put_vec(c, "gen.fc_b", gfc.b);
+    }
+    // ---- STFT / iSTFT bases (TorchSTFT: n_fft 2048, hop 75, hann(1200) centred in the frame)
+    {
+      std::vector<double> win(1200);
+      std::vector<float> wsq(1200);
+      for (int n = 0; n < 1200; ++n) {
+        win[n] = (double)(float)(0.5 - 0.5 * std::cos(2.0 * kPi * n / 1200.0));  // torch.hann_window (periodic), fp32
+        wsq[n] = (float)win[n] * (float)win[n];
+      }
+      put_vec(c, "wsq", wsq);
+      auto ang = [](int k, int np) { return 2.0 * kPi * (double)((long long)k * np % 2048) / 2048.0; };
+      {  // forward: rows (re_k, im_k) interleaved; K = 16 hop-taps x 75 samples (padded to 96)
+        Builder b;
+        const int t[2] = {16, 0}, pd[2] = {0, 0}, cp[2] = {96, 0};
+        b.init(2050, 1, t, pd, cp);
+        for (int k = 0; k <= 1024; ++k)
+          for (int n = 0; n < 1200; ++n) {
+            const int j = n / 75, cc = n % 75;
+            const double a = ang(k, 424 + n);
+            b.W[(size_t)(2 * k) * b.Ktot + j * 96 + cc] = (float)(win[n] * std::cos(a));
+            b.W[(size_t)(2 * k + 1) * b.Ktot + j * 96 + cc] = (float)(-win[n] * std::sin(a));
+          }
+        c.gemm["stft"] = b.upload(c);
+      }
+      {  // inverse: irfft (1/N, Hermitian doubling, imag of DC / Nyquist ignored) x window
+        Builder b;
+        const int t[2] = {1, 0}, pd[2] = {0, 0}, cp[2] = {2112, 0};
+        b.init(1200, 1, t, pd, cp);
+        for (int n = 0; n < 1200; ++n)
+          for (int k = 0; k <= 1024; ++k) {
+            const double ck = (k == 0 || k == 1024) ? 1.0 : 2.0;
+            const double a = ang(k, 424 + n);
+            b.W[(size_t)n * b.Ktot + 2 * k] = (float)(ck * win[n] * std::cos(a) / 2048.0);
+            b.W[(size_t)n * b.Ktot + 2 * k + 1] =
+                (k == 0 || k == 1024) ? 0.f : (float)(-ck * win[n] * std::sin(a) / 2048.0);
+          }
+        c.gemm["istft"] = b.upload(c);
+      }
+    }
+  }
+
+  // ======================================================================= pitch_energy_predictor
+  Loader P{c, "pitch_energy_predictor"};
+  if (c.has("pitch_energy_predictor/F0.0.conv1.bias")) {
+    FcCat fc;
+    const char* tw[2] = {"F0", "N"};
+    for (int t = 0; t < 2; ++t)
+      for (int i = 0; i < 3; ++i) {
+        const std::string p = std::string(tw[t]) + "." + std::to_string(i) + ".";
+        if (!pack_ada_block(c, P, p, std::string("pe.") + tw[t] + std::to_string(i), 320, 320, 320, fc))
+          return fail(c, -3, "missing weight " + P.missing);
+      }
+    c.J_pe = fc.J;
+    put_vec(c, "pe.fc_W", fc.W);
+    put_vec(c, "pe.fc_b", fc.b);
+    const HostTensor *wf = P.get("F0_proj.weight"), *bf = P.get("F0_proj.bias");
+    const HostTensor *wn = P.get("N_proj.weight"), *bn = P.get("N_proj.bias");
+    if (!P.ok) return fail(c, -3, "missing weight " + P.missing);
+    put_vec(c, "pe.F0_proj_w", wf->data);
+    put_vec(c, "pe.F0_proj_b", bf->data);
+    put_vec(c, "pe.N_proj_w", wn->data);
+    put_vec(c, "pe.N_proj_b", bn->data);
+  }
+  if (cudaDeviceSynchronize() != cudaSuccess) return fail(c, -5, "cuda error while uploading weights");
+  c.finalized = true;
+  return 0;
+}
+
+}  // namespace stts
