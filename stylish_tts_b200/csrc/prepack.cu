@@ -244,6 +244,8 @@ int finalize_weights(Context& c) {
       b.set_bias(*br, 0, 64, 0, 1);
       c.gemm["dec.asr_res"] = b.upload(c);
     }
+  }
+  if (c.has("speech_predictor/prior_encoder.proj_mean.weight")) {
     // ---- prior encoder (flow.py:296-315): (mean_i, logstd_i) interleaved rows
     {
       const HostTensor *wm = L.get("prior_encoder.proj_mean.weight"), *bm = L.get("prior_encoder.proj_mean.bias");
@@ -328,6 +330,8 @@ int finalize_weights(Context& c) {
       b.set_bias(*bpf, 0, 512, 0, 1);
       c.gemm["post_flow"] = b.upload(c);
     }
+  }
+  if (c.has("speech_predictor/generator.projector.weight")) {
     // ---- generator (generator.py:339-438)
     {
       FcCat gfc;

@@ -1,0 +1,203 @@
+"""Thin torch-facing wrapper over the C ABI: torch supplies device memory and streams, the
+library does the work.  Every method enqueues on torch's current stream."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, Iterable, Optional, Sequence
+
+import torch
+
+from . import _lib
+
+PRECISIONS = {"fp32": 0, "bf16": 1, "tf32x3": 2}
+
+
+class SttsError(RuntimeError):
+    pass
+
+
+def _ptr(t: Optional[torch.Tensor], dtype=torch.float32) -> Optional[int]:
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise SttsError("expected a CUDA tensor")
+    if t.dtype != dtype:
+        raise SttsError(f"expected dtype {dtype}, got {t.dtype}")
+    if not t.is_contiguous():
+        raise SttsError("expected a contiguous tensor")
+    return t.data_ptr()
+
+
+class Engine:
+    """One context per device: prepacked weights + workspace for one packed layout at a time."""
+
+    def __init__(self, device: Optional[torch.device] = None):
+        self.lib = _lib.load()
+        if not torch.cuda.is_available():
+            raise SttsError("no CUDA device: the synthesis path has no CPU fallback")
+        self.device = torch.device(device if device is not None else "cuda:0")
+        if self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
+        h = C.c_void_p()
+        rc = self.lib.stts_create(C.byref(h), self.device.index)
+        if rc != 0:
+            raise SttsError(f"stts_create failed ({rc}): needs an sm_100 (B200) device")
+        self.h = h
+        self.n_seg = 0
+        self.len_f: Optional[Sequence[int]] = None
+        self.len_f4: Optional[Sequence[int]] = None
+        self.precision = "fp32"
+
+    def __del__(self):
+        try:
+            if getattr(self, "h", None):
+                self.lib.stts_destroy(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+    # ------------------------------------------------------------------ helpers
+    def _check(self, rc: int):
+        if rc < 0:
+            msg = self.lib.stts_last_error(self.h).decode()
+            if rc == -2:
+                raise ValueError(msg)
+            if rc == -7:
+                raise RuntimeError(msg)  # same type torch.min raises on an empty tensor
+            raise SttsError(f"stts error {rc}: {msg}")
+        return rc
+
+    def _stream(self) -> int:
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    # ------------------------------------------------------------------ weights
+    def load_state(self, module: str, sd: Dict[str, torch.Tensor], prefix: str = ""):
+        for k, v in sd.items():
+            t = v.detach().to("cpu", torch.float32).contiguous()
+            shape = (C.c_int64 * max(t.dim(), 1))(*t.shape)
+            self._check(self.lib.stts_load_tensor(self.h, module.encode(), (prefix + k).encode(), t.data_ptr(), shape,
+                                                  t.dim()))
+
+    def finalize(self):
+        self._check(self.lib.stts_finalize_weights(self.h))
+        self.n_seg = 0
+
+    def set_precision(self, name: str):
+        self._check(self.lib.stts_set_precision(self.h, PRECISIONS[name]))
+        self.precision = name
+
+    # ------------------------------------------------------------------ layout
+    def set_layout(self, len_f: Optional[Iterable[int]], len_f4: Optional[Iterable[int]]):
+        lf = [int(x) for x in len_f] if len_f is not None else None
+        l4 = [int(x) for x in len_f4] if len_f4 is not None else None
+        n = len(lf if lf is not None else l4)
+        a = (C.c_int * n)(*lf) if lf is not None else None
+        b = (C.c_int * n)(*l4) if l4 is not None else None
+        with torch.cuda.device(self.device):
+            self._check(self.lib.stts_set_layout(self.h, n, a, b))
+        self.n_seg, self.len_f, self.len_f4 = n, lf, l4
+
+    def workspace_bytes(self) -> int:
+        return int(self.lib.stts_workspace_bytes(self.h))
+
+    def launch_count(self) -> int:
+        return int(self.lib.stts_launch_count(self.h))
+
+    # ------------------------------------------------------------------ length regulation
+    def durations(self, logits: torch.Tensor) -> torch.Tensor:
+        """[n_tokens, 16] logits -> int32 durations (utils.py:468-474)."""
+        logits = logits.contiguous()
+        n = logits.shape[0]
+        out = torch.empty(n, dtype=torch.int32, device=self.device)
+        self._check(self.lib.stts_durations(self.h, _ptr(logits), n, _ptr(out, torch.int32), self._stream()))
+        return out
+
+    def frame_index(self, dur: torch.Tensor, cu_tok: torch.Tensor, cap: int):
+        n_seg = cu_tok.numel() - 1
+        cu_frames = torch.empty(n_seg + 1, dtype=torch.int32, device=self.device)
+        idx = torch.empty(max(cap, 1), dtype=torch.int32, device=self.device)
+        status = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self._check(self.lib.stts_frame_index(self.h, _ptr(dur, torch.int32), _ptr(cu_tok, torch.int32), n_seg,
+                                              _ptr(cu_frames, torch.int32), _ptr(idx, torch.int32), cap,
+                                              _ptr(status, torch.int32), self._stream()))
+        return cu_frames, idx, status
+
+    # ------------------------------------------------------------------ stages (dense tensors, see header)
+    def pe_towers(self, x: torch.Tensor, style: torch.Tensor):
+        tot = sum(self.len_f)
+        pitch = torch.empty(tot, device=self.device)
+        energy = torch.empty(tot, device=self.device)
+        self._check(self.lib.stts_pe_towers(self.h, _ptr(x), _ptr(style), _ptr(pitch), _ptr(energy), self._stream()))
+        return pitch, energy
+
+    def decoder(self, asr, f0, n, style):
+        out = torch.empty(512 * sum(self.len_f4), device=self.device)
+        self._check(self.lib.stts_decoder(self.h, _ptr(asr), _ptr(f0), _ptr(n), _ptr(style), _ptr(out), self._stream()))
+        return out
+
+    def prior_flow(self, x, noise, style, want_z: bool = False):
+        tot = sum(self.len_f4)
+        mel = torch.empty(512 * tot, device=self.device)
+        zp = torch.empty(128 * tot, device=self.device) if want_z else None
+        zf = torch.empty(128 * tot, device=self.device) if want_z else None
+        self._check(self.lib.stts_prior_flow(self.h, _ptr(x), _ptr(noise), _ptr(style), _ptr(mel), _ptr(zp), _ptr(zf),
+                                             self._stream()))
+        return mel, zp, zf
+
+    def source_pcph(self, pitch4, noise, init_phase):
+        out = torch.empty(75 * sum(self.len_f4), device=self.device)
+        self._check(self.lib.stts_source_pcph(self.h, _ptr(pitch4), _ptr(noise), _ptr(init_phase), _ptr(out),
+                                              self._stream()))
+        return out
+
+    def generator(self, mel, style, pitch4, noise, init_phase, want_spec: bool = True):
+        tot = sum(self.len_f4)
+        audio = torch.empty(75 * tot, device=self.device)
+        la = torch.empty(1025 * (tot + self.n_seg), device=self.device) if want_spec else None
+        ph = torch.empty(1025 * (tot + self.n_seg), device=self.device) if want_spec else None
+        self._check(self.lib.stts_generator(self.h, _ptr(mel), _ptr(style), _ptr(pitch4), _ptr(noise),
+                                            _ptr(init_phase), _ptr(audio), _ptr(la), _ptr(ph), self._stream()))
+        return audio, la, ph
+
+    def speech_frames(self, enc_tok, cu_tok, idx, cu_frames, pitch, energy, style, noise_prior, noise_source,
+                      init_phase, want_spec: bool = False):
+        tot = sum(self.len_f4)
+        audio = torch.empty(75 * tot, device=self.device)
+        la = torch.empty(1025 * (tot + self.n_seg), device=self.device) if want_spec else None
+        ph = torch.empty(1025 * (tot + self.n_seg), device=self.device) if want_spec else None
+        self._check(self.lib.stts_speech_frames(
+            self.h, _ptr(enc_tok), _ptr(cu_tok, torch.int32), _ptr(idx, torch.int32), _ptr(cu_frames, torch.int32),
+            _ptr(pitch), _ptr(energy), _ptr(style), _ptr(noise_prior), _ptr(noise_source), _ptr(init_phase),
+            _ptr(audio), _ptr(la), _ptr(ph), self._stream()))
+        return audio, la, ph
+
+    def check_source_status(self):
+        self._check(self.lib.stts_check_source_status(self.h, self._stream()))
+
+    # ------------------------------------------------------------------ test hooks
+    def test_conv(self, backend: str, x: torch.Tensor, cin: int, w: torch.Tensor, bias: Optional[torch.Tensor],
+                  pad: int, ldy: int) -> torch.Tensor:
+        """x: packed [R, ldx]; w: [N, cin, taps] (CPU or CUDA); returns packed [R, ldy]."""
+        n_out, _, taps = w.shape
+        wc = w.detach().to("cpu", torch.float32).contiguous()
+        bc = bias.detach().to("cpu", torch.float32).contiguous() if bias is not None else None
+        y = torch.zeros((x.shape[0], ldy), device=self.device)
+        self._check(self.lib.stts_test_conv(self.h, PRECISIONS[backend], _ptr(x), x.shape[1], cin, taps, pad,
+                                            wc.data_ptr(), bc.data_ptr() if bc is not None else None, n_out, _ptr(y),
+                                            ldy, self._stream()))
+        return y
+
+    def debug_read(self, name: str) -> torch.Tensor:
+        rows, ld = C.c_int(), C.c_int()
+        n = self._check(self.lib.stts_debug_read(self.h, name.encode(), None, 0, C.byref(rows), C.byref(ld), None))
+        out = torch.empty(n, device=self.device)
+        self._check(self.lib.stts_debug_read(self.h, name.encode(), _ptr(out), n, C.byref(rows), C.byref(ld),
+                                             self._stream()))
+        return out.view(rows.value, ld.value) if ld.value > 1 else out
+
+    def layout_info(self, rate: int):
+        n = self.n_seg
+        rows = C.c_int()
+        starts = (C.c_int * max(n, 1))()
+        self._check(self.lib.stts_layout_info(self.h, rate, C.byref(rows), starts))
+        return rows.value, list(starts)[:n]
