@@ -1,0 +1,132 @@
+"""Stage-by-stage parity of the CUDA path against the golden intermediates of the live reference
+(tests/golden/tiny.safetensors).  Each stage is fed the *reference's* inputs, so errors do not
+accumulate and a failing stage is pinpointed.  Used by tests/test_stages_gpu.py and runnable as
+``python -m tests.stage_runner [precision]`` (prints every error, writes gpurun_out/stages_*.json)."""
+import json
+import math
+import os
+import sys
+
+import torch
+
+from tests.util import ROOT, gold, gpu_nets, maxabs
+
+
+def _wrapdiff(a, b):
+    d = (a.double().cpu() - b.double().cpu()).abs()
+    return torch.minimum(d, (d - 2 * math.pi).abs())
+
+
+def run(precision="fp32"):
+    g = gold("tiny")
+    dev = "cuda:0"
+    nets = gpu_nets()
+    sp, pep = nets["speech_predictor"], nets["pitch_energy_predictor"]
+    eng = sp.engine()
+    eng.set_precision(precision)
+    peng = pep.engine()
+    peng.set_precision(precision)
+    res = {}
+
+    def rec(name, got, want, wrap=False):
+        want = want.reshape(got.shape) if want.numel() == got.numel() else want
+        d = _wrapdiff(got, want) if wrap else (got.double().cpu() - want.double().cpu()).abs()
+        res[name] = {"max_abs": float(d.max()), "ref_absmax": float(want.abs().max()),
+                     "rel": float(d.max()) / max(1e-12, float(want.abs().max())),
+                     "frac_gt_1e-3": float((d > 1e-3).double().mean())}
+
+    dur = g["duration_in"].to(torch.int64)
+    F_ = int(dur.sum())
+    F4 = 4 * F_
+    tokens = g["tokens"].to(dev)[None]
+    lens = torch.tensor([tokens.shape[1]], device=dev)
+    idx = torch.repeat_interleave(torch.arange(dur.numel()), dur).to(dev)
+    alignment = torch.zeros(1, dur.numel(), F_, device=dev)
+    alignment[0, idx, torch.arange(F_, device=dev)] = 1
+
+    style = g["tap.sp_style"].to(dev).contiguous()
+    init = g["noise.phase"].to(dev).reshape(-1)[:1].contiguous()
+
+    def sec_length_regulation():  # length regulation
+        from stylish_tts_b200.modules import DurationProcessor
+        proc = DurationProcessor(16, 50).to(dev)
+        d_pred = proc.prediction_to_duration(g["tap.dur_logits"][0].to(dev))[: tokens.shape[1]]
+        res["duration_pred"] = {"max_abs": float((d_pred.cpu().to(torch.int32) - g["duration_pred"]).abs().max()),
+                                "ref_absmax": float(g["duration_pred"].max()), "rel": 0.0, "frac_gt_1e-3": 0.0}
+        al = proc.duration_to_alignment(dur.to(dev).float())
+        res["alignment"] = {"max_abs": float((al - alignment[0]).abs().max()), "ref_absmax": 1.0, "rel": 0.0,
+                            "frac_gt_1e-3": 0.0}
+
+    def sec_pitch___energy_towers_on_the_reference_s():  # pitch / energy towers on the reference's cross-attended frames
+        peng.set_layout([F_], None)
+        pitch, energy = peng.pe_towers(g["tap.pe_cross"].to(dev).contiguous().view(-1), g["tap.pe_style"].to(dev))
+        rec("pe_towers.pitch", pitch, g["out.pitch"])
+        rec("pe_towers.energy", energy, g["out.energy"])
+        # full module (token-rate torch + native towers)
+        p2, e2 = pep(g["tap.pe_text"].to(dev), lens, alignment, g["tap.pe_style"].to(dev))
+        rec("PitchEnergyPredictor.pitch", p2, g["out.pitch"])
+
+    def sec_decoder():  # decoder
+        asr = (g["tap.sp_text"].to(dev) @ alignment.repeat_interleave(4, dim=2)).contiguous()
+        x, _ = sp.decoder(asr, g["tap.pitch4"].to(dev), g["tap.energy4"].to(dev), g["tap.sp_style"].to(dev))
+        rec("decoder", x, g["tap.dec_out"])
+
+    def sec_prior___flow___post_flow():  # prior + flow + post_flow
+        eng.set_layout(None, [F4])
+        mel, zp, zf = eng.prior_flow(g["tap.dec_out"].to(dev).contiguous().view(-1),
+                                     g["noise.prior"].to(dev).contiguous().view(-1), style.view(-1), want_z=True)
+        rec("z_prior", zp, g["tap.z_prior"])
+        rec("z_flow", zf, g["tap.z_flow"])
+        rec("mel", mel, g["tap.mel"])
+
+    def sec_source():  # source
+        src = eng.source_pcph(g["tap.pitch4"].to(dev).contiguous().view(-1),
+                              g["noise.source"].to(dev).contiguous().view(-1), init)
+        rec("source", src, g["tap.source"])
+
+    def sec_generator__fed_the_reference_mel_():  # generator (fed the reference mel)
+        audio, la, ph = eng.generator(g["tap.mel"].to(dev).contiguous().view(-1), style.view(-1),
+                                      g["tap.pitch4"].to(dev).contiguous().view(-1),
+                                      g["noise.source"].to(dev).contiguous().view(-1), init)
+        rows, starts = eng.layout_info(4)
+        s0 = starts[0]
+        hs = eng.debug_read("HS")[s0: s0 + F4, :1025].t()
+        hp = eng.debug_read("HP")[s0: s0 + F4, :1025].t()
+        rec("har_spec", hs, g["tap.har_spec"][0])
+        rec("har_phase(wrapped)", hp, g["tap.har_phase"][0], wrap=True)
+        rec("gen_convnext", eng.debug_read("XG")[s0: s0 + F4, :512].t(), g["tap.gen_convnext"][0])
+        rec("gen.logamp", la.view(1025, F4 + 1), g["out.logamp"][0])
+        rec("gen.phase", ph.view(1025, F4 + 1), g["out.phase"][0])
+        rec("gen.audio", audio, g["out.audio"])
+
+    def sec_SpeechPredictor_module_end_to_end__nativ():  # SpeechPredictor module end to end (native frame-rate path, reference pitch/energy)
+        sp.noise_override = {k[6:]: v for k, v in g.items() if k.startswith("noise.")}
+        pred = sp(tokens, lens, alignment, g["out.pitch"].to(dev), g["out.energy"].to(dev))
+        sp.noise_override = None
+        rec("SpeechPredictor.audio", pred.audio, g["out.audio"])
+        rec("SpeechPredictor.logamp", pred.magnitude, g["out.logamp"])
+
+    with torch.no_grad():
+        for fn in (sec_length_regulation, sec_pitch___energy_towers_on_the_reference_s, sec_decoder,
+                   sec_prior___flow___post_flow, sec_source, sec_generator__fed_the_reference_mel_,
+                   sec_SpeechPredictor_module_end_to_end__nativ):
+            try:
+                fn()
+            except Exception as e:  # keep going: one trip to the GPU box should report every stage
+                res[fn.__name__ + ".EXCEPTION"] = {"max_abs": float("inf"), "ref_absmax": 0.0, "rel": float("inf"),
+                                                   "frac_gt_1e-3": 1.0, "error": repr(e)[:500]}
+    os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+    with open(os.path.join(ROOT, "gpurun_out", f"stages_{precision}.json"), "w") as f:
+        json.dump(res, f, indent=1)
+    return res
+
+
+if __name__ == "__main__":
+    prec = sys.argv[1] if len(sys.argv) > 1 else "fp32"
+    out = run(prec)
+    for k, v in out.items():
+        if "error" in v:
+            print(prec, k, v["error"])
+            continue
+        print(f"{prec:7s} {k:32s} max_abs {v['max_abs']:.3e}  rel {v['rel']:.3e}  |ref| {v['ref_absmax']:.3e}  "
+              f"frac>1e-3 {v['frac_gt_1e-3']:.2e}")

@@ -1,0 +1,124 @@
+"""GPU: full synthesis (Synthesizer = user-facing API) against golden audio from the live
+reference, ragged-batch == per-utterance semantics, and size-independent properties."""
+import json
+import os
+
+import pytest
+import torch
+
+from tests.util import ROOT, case_noise, gold, maxabs, synthesizer
+
+pytestmark = pytest.mark.gpu
+
+
+def _case(g, prefix=""):
+    tokens = g[prefix + "tokens"]
+    dur = g[prefix + "duration_in"].to(torch.int64)
+    noise = case_noise(int(dur.sum()), int(g[prefix + "seed"]))
+    return tokens, dur, noise
+
+
+def _log(name, val):
+    os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+    with open(os.path.join(ROOT, "gpurun_out", "e2e_errors.jsonl"), "a") as f:
+        f.write(json.dumps({name: val}) + "\n")
+
+
+@pytest.mark.parametrize("precision,tol", [("fp32", 1e-4), ("tf32x3", 1e-4), ("bf16", 2e-3)])
+def test_golden_single_utterances(precision, tol):
+    syn = synthesizer(precision)
+    for name in ("tiny", "short", "c1"):
+        g = gold(name)
+        tokens, dur, noise = _case(g)
+        out = syn.synthesize([tokens], durations=[dur], noise=[noise])
+        syn.check()
+        err = maxabs(out["audio"][0], g["out.audio"].reshape(-1))
+        perr = maxabs(out["pitch"][0], g["out.pitch"].reshape(-1))
+        _log(f"{precision}.{name}", {"audio": err, "pitch": perr})
+        assert torch.equal(out["duration_pred"][0].cpu().to(torch.int32), g["duration_pred"]), name
+        assert out["audio"][0].numel() == 300 * int(dur.sum())
+        assert err <= tol, (precision, name, err)
+
+
+@pytest.mark.parametrize("precision,tol", [("fp32", 1e-4), ("bf16", 2e-3)])
+def test_ragged_batch_equals_b1_loop(precision, tol):
+    syn = synthesizer(precision)
+    g = gold("batch3")
+    cases = [_case(g, f"{i}.") for i in range(3)]
+    out = syn.synthesize([c[0] for c in cases], durations=[c[1] for c in cases], noise=[c[2] for c in cases])
+    syn.check()
+    for i in range(3):
+        err = maxabs(out["audio"][i], g[f"{i}.out.audio"].reshape(-1))
+        _log(f"{precision}.batch3.{i}", err)
+        assert err <= tol, (i, err)
+        assert maxabs(out["pitch"][i], g[f"{i}.out.pitch"].reshape(-1)) <= (2e-2 if precision == "fp32" else 2.0)
+
+
+def test_batch_order_invariance_and_determinism():
+    syn = synthesizer("fp32")
+    g = gold("batch3")
+    cases = [_case(g, f"{i}.") for i in range(3)]
+    a = syn.synthesize([c[0] for c in cases], durations=[c[1] for c in cases], noise=[c[2] for c in cases])
+    b = syn.synthesize([c[0] for c in cases], durations=[c[1] for c in cases], noise=[c[2] for c in cases])
+    perm = [2, 0, 1]
+    c = syn.synthesize([cases[i][0] for i in perm], durations=[cases[i][1] for i in perm],
+                       noise=[cases[i][2] for i in perm])
+    for i in range(3):
+        assert torch.equal(a["audio"][i], b["audio"][i])                    # run-to-run bit stable
+    for j, i in enumerate(perm):
+        assert maxabs(c["audio"][j], a["audio"][i]) <= 2e-6                 # utterances do not interact
+
+
+def test_predicted_durations_path_and_audio_length():
+    syn = synthesizer("fp32")
+    g = gold("tiny")
+    tokens, _, _ = _case(g)
+    out = syn.synthesize([tokens])
+    f = int(g["duration_pred"].sum())
+    assert out["frames"] == [f]
+    assert out["audio"][0].numel() == 300 * f
+    assert bool(torch.isfinite(out["audio"][0]).all())
+    assert float(out["audio"][0].abs().max()) <= 1.0
+
+
+def test_module_api_matches_reference_signatures():
+    from tests.util import gpu_nets
+    from stylish_tts_b200.modules import ExportModel
+    nets = gpu_nets()
+    g = gold("tiny")
+    tokens, dur, noise = _case(g)
+    dev = "cuda:0"
+    em = ExportModel(**nets, device=dev)
+    idx = torch.repeat_interleave(torch.arange(dur.numel()), dur)
+    al = torch.zeros(1, dur.numel(), int(dur.sum()), device=dev)
+    al[0, idx.to(dev), torch.arange(int(dur.sum()), device=dev)] = 1
+    nets["speech_predictor"].engine().set_precision("fp32")
+    nets["pitch_energy_predictor"].engine().set_precision("fp32")
+    nets["speech_predictor"].noise_override = noise
+    audio = em(tokens[None].to(dev), torch.tensor([tokens.numel()], device=dev), al)
+    nets["speech_predictor"].noise_override = None
+    assert audio.shape == (300 * int(dur.sum()),)
+    assert maxabs(audio, g["out.audio"].reshape(-1)) <= 1e-4
+
+
+def test_reference_error_path_voiced_without_f0_above_20():
+    from stylish_tts_b200.engine import Engine
+    eng = Engine("cuda:0")
+    eng.set_layout(None, [40])
+    p = torch.zeros(40, device="cuda:0")
+    p[5] = 15.0
+    eng.source_pcph(p, torch.zeros(3000, device="cuda:0"), torch.zeros(1, device="cuda:0"))
+    with pytest.raises(RuntimeError):
+        eng.check_source_status()
+    p[:] = 0.0                                        # all unvoiced -> noise only, no error
+    n = torch.randn(3000, device="cuda:0")
+    out = eng.source_pcph(p, n, torch.zeros(1, device="cuda:0"))
+    eng.check_source_status()
+    assert maxabs(out, 0.01 * n) <= 1e-9
+
+
+def test_too_short_utterance_raises_like_torch_stft():
+    from stylish_tts_b200.engine import Engine
+    eng = Engine("cuda:0")
+    with pytest.raises(ValueError):
+        eng.set_layout(None, [13])                    # 75 * 13 = 975 <= 1024: reflect pad impossible
