@@ -129,6 +129,12 @@ int stts_test_conv(stts_ctx* ctx, int backend, const float* d_x, int ldx, int ci
 int64_t stts_debug_read(stts_ctx* ctx, const char* name, float* d_dst, int64_t cap, int* rows, int* ld,
                         void* stream);
 int stts_layout_info(const stts_ctx* ctx, int rate, int* rows, int* seg_start /*[n_seg]*/);
+/* per-GEMM CUDA-event timing (bench.py roofline): stts_set_profiling(ctx, 1) starts recording an
+ * event pair around every conv-as-GEMM launch on the launching stream; stts_profile_json
+ * synchronises the device and returns a JSON array of {name, backend, launches, ms, flops}
+ * (algorithmic FLOPs = 2 * valid rows * N * un-padded K) aggregated per layer, and clears.      */
+int stts_set_profiling(stts_ctx* ctx, int on);
+const char* stts_profile_json(stts_ctx* ctx);
 /* number of kernels launched by this context since creation (bench.py "gpu_launches")          */
 int64_t stts_launch_count(const stts_ctx* ctx);
 

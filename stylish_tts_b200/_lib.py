@@ -34,6 +34,8 @@ SIGNATURES = {
     "stts_debug_read": (_i64, [_vp, C.c_char_p, _fp, _i64, C.POINTER(_i), C.POINTER(_i), _vp]),
     "stts_layout_info": (_i, [_vp, _i, C.POINTER(_i), C.POINTER(_i)]),
     "stts_launch_count": (_i64, [_vp]),
+    "stts_set_profiling": (_i, [_vp, _i]),
+    "stts_profile_json": (C.c_char_p, [_vp]),
 }
 
 _lib = None

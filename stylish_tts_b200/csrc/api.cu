@@ -1,4 +1,5 @@
 // extern "C" surface declared in include/stts_b200.h
+#include <cstdio>
 #include <cstring>
 
 #include "../../include/stts_b200.h"
@@ -238,6 +239,48 @@ int stts_layout_info(const stts_ctx* ctx, int rate, int* rows, int* seg_start) {
   if (seg_start)
     for (int b = 0; b < L.n_seg; ++b) seg_start[b] = L.seg_start[b];
   return L.n_seg;
+}
+
+int stts_set_profiling(stts_ctx* ctx, int on) {
+  if (!ctx) return STTS_ERR_BAD_ARG;
+  Context& c = ctx->c;
+  DeviceGuard g(c.device);
+  cudaDeviceSynchronize();
+  for (auto& r : c.prof) { c.ev_pool.push_back(r.e0); c.ev_pool.push_back(r.e1); }
+  c.prof.clear();
+  c.prof_on = on != 0;
+  return STTS_OK;
+}
+
+const char* stts_profile_json(stts_ctx* ctx) {
+  if (!ctx) return "[]";
+  Context& c = ctx->c;
+  DeviceGuard g(c.device);
+  cudaDeviceSynchronize();
+  struct Agg { double ms = 0, flops = 0; long n = 0; int backend = 0; };
+  std::map<std::string, Agg> agg;
+  for (auto& r : c.prof) {
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, r.e0, r.e1);
+    Agg& a = agg[r.name + "#" + std::to_string(r.backend)];
+    a.ms += ms; a.flops += r.flops; a.n++; a.backend = r.backend;
+    c.ev_pool.push_back(r.e0);
+    c.ev_pool.push_back(r.e1);
+  }
+  c.prof.clear();
+  static thread_local std::string out;
+  out = "[";
+  bool first = true;
+  for (auto& kv : agg) {
+    char buf[512];
+    const std::string nm = kv.first.substr(0, kv.first.find('#'));
+    snprintf(buf, sizeof(buf), "%s{\"name\":\"%s\",\"backend\":%d,\"launches\":%ld,\"ms\":%.6f,\"flops\":%.1f}",
+             first ? "" : ",", nm.c_str(), kv.second.backend, kv.second.n, kv.second.ms, kv.second.flops);
+    out += buf;
+    first = false;
+  }
+  out += "]";
+  return out.c_str();
 }
 
 int64_t stts_launch_count(const stts_ctx* ctx) { return ctx ? ctx->c.launches : 0; }

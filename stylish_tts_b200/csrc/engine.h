@@ -26,6 +26,8 @@ struct PackedGemm {
   float* Whl = nullptr;           // tf32 hi rows then lo rows      [2 * Npad, Ktot]
   __nv_bfloat16* Wh = nullptr;    // bf16                           [Npad, Ktot]
   float* bias = nullptr;          // [Npad] (zeros when the layer has no bias)
+  std::string name;               // layer name (profiling)
+  double k_real = 0;              // un-padded K (algorithmic FLOPs = 2 * rows * N * k_real)
 };
 
 struct Act {          // an activation buffer: fp32 + optional bf16 twin, same ld
@@ -76,6 +78,11 @@ struct Context {
   std::map<std::string, void*> raw;            // other named scratch
   std::map<std::string, size_t> raw_bytes;
   SourceMeta* h_meta = nullptr;                // pinned
+  // ---- optional per-GEMM CUDA-event profiling (bench.py roofline)
+  bool prof_on = false;
+  struct ProfRec { std::string name; cudaEvent_t e0, e1; double flops; int backend; };
+  std::vector<ProfRec> prof;
+  std::vector<cudaEvent_t> ev_pool;
 
   bool has(const std::string& k) const { return tensors.count(k) != 0; }
 };

@@ -221,6 +221,8 @@ int run_gemm(Context& c, const PackedGemm& pg, int cls, const Act* a0, int a0_co
     else if (c.precision == 1) backend = (cls == GC_ISLAND) ? 2 : 1;
     else backend = 2;
   }
+  const long long map_valid_rows = (map.seg_len == c.LF.d_seg_len) ? c.LF.total()
+                                   : (map.seg_len == c.L4.d_seg_len_p1 ? c.L4.total() + c.L4.n_seg : c.L4.total());
   ConvGemm g;
   std::memset(&g, 0, sizeof(g));
   g.n_kseg = pg.n_kseg;
@@ -244,10 +246,23 @@ int run_gemm(Context& c, const PackedGemm& pg, int cls, const Act* a0, int a0_co
   g.epi.N = pg.N;
   if (g.epi.bias == nullptr && g.epi.kind != EPI_STFT) g.epi.bias = pg.bias;
   cudaError_t e;
+  Context::ProfRec pr;
+  if (c.prof_on) {
+    auto get_ev = [&]() {
+      cudaEvent_t ev;
+      if (!c.ev_pool.empty()) { ev = c.ev_pool.back(); c.ev_pool.pop_back(); }
+      else cudaEventCreate(&ev);
+      return ev;
+    };
+    pr.name = pg.name; pr.e0 = get_ev(); pr.e1 = get_ev(); pr.backend = backend;
+    pr.flops = 2.0 * (double)map_valid_rows * (double)pg.N * pg.k_real;
+    cudaEventRecord(pr.e0, st);
+  }
   if (backend == 0) e = conv_gemm_simt(g, map, st);
   else if (backend == 1) e = conv_gemm_tc_bf16(g, map, st);
   else e = conv_gemm_tc_tf32x3(g, map, st);
   if (e != cudaSuccess) return cuda_fail(c, e, "conv_gemm launch");
+  if (c.prof_on) { cudaEventRecord(pr.e1, st); c.prof.push_back(pr); }
   c.launches++;
   return 0;
 }

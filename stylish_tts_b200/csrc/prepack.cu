@@ -46,6 +46,8 @@ struct Builder {
   int N = 0, Npad = 0, Ktot = 0, n_kseg = 0;
   int taps[2] = {0, 0}, pad[2] = {0, 0}, cin_pad[2] = {0, 0};
   std::vector<float> W, bias;
+  double k_real = 0;
+  std::vector<int> row_k;
   void init(int n, int nk, const int* t, const int* p, const int* cp) {
     N = n;
     Npad = (n + 127) / 128 * 128;
@@ -54,11 +56,13 @@ struct Builder {
     for (int s = 0; s < nk; ++s) { taps[s] = t[s]; pad[s] = p[s]; cin_pad[s] = cp[s]; Ktot += t[s] * cp[s]; }
     W.assign((size_t)Npad * Ktot, 0.f);
     bias.assign(Npad, 0.f);
+    row_k.assign(Npad, 0);
   }
   int koff(int s) const { return s == 0 ? 0 : taps[0] * cin_pad[0]; }
   // w: [n_src, cin_total, k] (k = taps[s]; Linear weights have k = 1)
   void rows(int s, const HostTensor& w, int src0, int n, int cin0, int cin_cnt, int dst0, int dstride) {
     const int cin_total = (int)w.dim(1), k = (int)w.dim(2);
+    for (int i = 0; i < n; ++i) row_k[dst0 + i * dstride] += cin_cnt * k;
     for (int i = 0; i < n; ++i) {
       float* d = &W[(size_t)(dst0 + i * dstride) * Ktot + koff(s)];
       const float* src = &w.data[(size_t)(src0 + i) * cin_total * k];
@@ -72,6 +76,7 @@ struct Builder {
   PackedGemm upload(Context& c) const {
     PackedGemm p;
     p.N = N; p.Npad = Npad; p.Ktot = Ktot; p.n_kseg = n_kseg;
+    { double kk = k_real; for (int i = 0; i < N && kk == 0; ++i) kk = row_k[i] > kk ? row_k[i] : kk; p.k_real = kk; }
     for (int s = 0; s < 2; ++s) { p.taps[s] = taps[s]; p.pad[s] = pad[s]; p.cin_pad[s] = cin_pad[s]; }
     const size_t n = (size_t)Npad * Ktot;
     std::vector<float> hl(2 * n);
@@ -424,7 +429,24 @@ int finalize_weights(Context& c) {
         wsq[n] = (float)win[n] * (float)win[n];
       }
       put_vec(c, "wsq", wsq);
-      auto ang = [](int k, int np) { return 2.0 * kPi * (double)((long long)k * np % 2048) / 2048.0; };
+      // exact twiddles: cos / sin of 2 pi m / 2048 with m reduced to the first octant, so that the
+      // imaginary rows of the DC and Nyquist bins are exactly zero (atan2(+0, -x) = +pi, as pocketfft)
+      auto cs = [](int k, int np, double* c_out, double* s_out) {
+        int m = (int)((long long)k * np % 2048);
+        const int q = m / 512;           // quadrant
+        const int r = m % 512;
+        double c0, s0;
+        if (r == 0) { c0 = 1.0; s0 = 0.0; }
+        else if (r == 256) { c0 = s0 = std::sqrt(0.5); }
+        else if (r < 256) { c0 = std::cos(2.0 * kPi * r / 2048.0); s0 = std::sin(2.0 * kPi * r / 2048.0); }
+        else { c0 = std::sin(2.0 * kPi * (512 - r) / 2048.0); s0 = std::cos(2.0 * kPi * (512 - r) / 2048.0); }
+        switch (q) {
+          case 0: *c_out = c0; *s_out = s0; break;
+          case 1: *c_out = -s0; *s_out = c0; break;
+          case 2: *c_out = -c0; *s_out = -s0; break;
+          default: *c_out = s0; *s_out = -c0; break;
+        }
+      };
       {  // forward: rows (re_k, im_k) interleaved; K = 16 hop-taps x 75 samples (padded to 96)
         Builder b;
         const int t[2] = {16, 0}, pd[2] = {0, 0}, cp[2] = {96, 0};
@@ -432,10 +454,12 @@ int finalize_weights(Context& c) {
         for (int k = 0; k <= 1024; ++k)
           for (int n = 0; n < 1200; ++n) {
             const int j = n / 75, cc = n % 75;
-            const double a = ang(k, 424 + n);
-            b.W[(size_t)(2 * k) * b.Ktot + j * 96 + cc] = (float)(win[n] * std::cos(a));
-            b.W[(size_t)(2 * k + 1) * b.Ktot + j * 96 + cc] = (float)(-win[n] * std::sin(a));
+            double ca, sa;
+            cs(k, 424 + n, &ca, &sa);
+            b.W[(size_t)(2 * k) * b.Ktot + j * 96 + cc] = (float)(win[n] * ca);
+            b.W[(size_t)(2 * k + 1) * b.Ktot + j * 96 + cc] = (sa == 0.0) ? 0.f : (float)(-win[n] * sa);
           }
+        b.k_real = 1200;
         c.gemm["stft"] = b.upload(c);
       }
       {  // inverse: irfft (1/N, Hermitian doubling, imag of DC / Nyquist ignored) x window
@@ -445,11 +469,13 @@ int finalize_weights(Context& c) {
         for (int n = 0; n < 1200; ++n)
           for (int k = 0; k <= 1024; ++k) {
             const double ck = (k == 0 || k == 1024) ? 1.0 : 2.0;
-            const double a = ang(k, 424 + n);
-            b.W[(size_t)n * b.Ktot + 2 * k] = (float)(ck * win[n] * std::cos(a) / 2048.0);
+            double ca, sa;
+            cs(k, 424 + n, &ca, &sa);
+            b.W[(size_t)n * b.Ktot + 2 * k] = (float)(ck * win[n] * ca / 2048.0);
             b.W[(size_t)n * b.Ktot + 2 * k + 1] =
-                (k == 0 || k == 1024) ? 0.f : (float)(-ck * win[n] * std::sin(a) / 2048.0);
+                (k == 0 || k == 1024 || sa == 0.0) ? 0.f : (float)(-ck * win[n] * sa / 2048.0);
           }
+        b.k_real = 2050;
         c.gemm["istft"] = b.upload(c);
       }
     }
@@ -477,6 +503,7 @@ int finalize_weights(Context& c) {
     put_vec(c, "pe.N_proj_w", wn->data);
     put_vec(c, "pe.N_proj_b", bn->data);
   }
+  for (auto& kv : c.gemm) kv.second.name = kv.first;
   if (cudaDeviceSynchronize() != cudaSuccess) return fail(c, -5, "cuda error while uploading weights");
   c.finalized = true;
   return 0;

@@ -174,6 +174,14 @@ class Engine:
     def check_source_status(self):
         self._check(self.lib.stts_check_source_status(self.h, self._stream()))
 
+    def set_profiling(self, on: bool):
+        self._check(self.lib.stts_set_profiling(self.h, 1 if on else 0))
+
+    def profile(self):
+        """Per-layer GEMM timings recorded since set_profiling(True) (synchronises)."""
+        import json
+        return json.loads(self.lib.stts_profile_json(self.h).decode())
+
     # ------------------------------------------------------------------ test hooks
     def test_conv(self, backend: str, x: torch.Tensor, cin: int, w: torch.Tensor, bias: Optional[torch.Tensor],
                   pad: int, ldy: int) -> torch.Tensor:

@@ -19,6 +19,11 @@ import torch
 import torch.nn.functional as F
 from torch import nn
 
+# The reference path is fp32; PyTorch's default lets cuDNN convolutions run in TF32, which alone
+# breaks the 1e-4 parity bar (SURVEY.md section 8c).  The token-rate modules therefore pin fp32.
+torch.backends.cudnn.allow_tf32 = False
+torch.backends.cuda.matmul.allow_tf32 = False
+
 
 def length_mask(lengths: torch.Tensor, max_len: int) -> torch.Tensor:
     """[B, max_len] True inside the utterance (utils.py:52-56)."""

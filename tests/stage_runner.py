@@ -9,7 +9,7 @@ import sys
 
 import torch
 
-from tests.util import ROOT, gold, gpu_nets, maxabs
+from tests.util import ROOT, fixture_sds, gold, gpu_nets, maxabs
 
 
 def _wrapdiff(a, b):
@@ -92,6 +92,18 @@ def run(precision="fp32"):
         s0 = starts[0]
         hs = eng.debug_read("HS")[s0: s0 + F4, :1025].t()
         hp = eng.debug_read("HP")[s0: s0 + F4, :1025].t()
+        catp = eng.debug_read("CATP")[s0: s0 + F4]
+        sd = {k: v.to(dev).double() for k, v in fixture_sds()["speech_predictor"].items() if k.startswith("generator.")}
+        F = torch.nn.functional
+        lp = F.conv1d(g["tap.har_spec"].to(dev).double(), sd["generator.amp_prior_conv.weight"],
+                      sd["generator.amp_prior_conv.bias"], padding=3)[0]
+        pp = F.conv1d(g["tap.har_phase"].to(dev).double(), sd["generator.phase_prior_conv.weight"],
+                      sd["generator.phase_prior_conv.bias"], padding=3)[0]
+        rec("logamp_prior", catp[:, 512:768].t(), lp)
+        rec("phase_prior", catp[:, 768:1024].t(), pp)
+        d_un = (hp.double().cpu() - g["tap.har_phase"][0].double()).abs()
+        res["har_phase.unwrapped_flips"] = {"max_abs": float((d_un > 3.0).sum()), "ref_absmax": float(d_un.numel()),
+                                            "rel": float((d_un > 3.0).double().mean()), "frac_gt_1e-3": 0.0}
         rec("har_spec", hs, g["tap.har_spec"][0])
         rec("har_phase(wrapped)", hp, g["tap.har_phase"][0], wrap=True)
         rec("gen_convnext", eng.debug_read("XG")[s0: s0 + F4, :512].t(), g["tap.gen_convnext"][0])
