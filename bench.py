@@ -1,0 +1,310 @@
+#!/usr/bin/env python
+"""Headline benchmark: audio-seconds synthesized per wall-second (1/RTF) of the Stylish-TTS
+synthesis forward path on B200 (BASELINE.json metric), workload = BASELINE configs[1]
+(batch 32 mixed-length utterances, 0.25-10 s, random-init fixture weights, synthetic phonemes).
+
+  python bench.py --gpus N --steps K --warmup W            our arm (CUDA path)
+  python bench.py --impl reference ...                      the reference's CPU path (oracle port,
+                                                            bounded sample) on the box's host cores
+One JSON line on stdout from rank 0.  See DESIGN.md "Measurement" for the definitions.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+METRIC = "audio-sec synthesized per sec (1/RTF)"
+UNIT = "audio_s/s"
+BATCH = 32
+FLOP_PER_F4_FRAME = 74.07e6          # frame-rate conv + linear FLOPs per hop-75 frame
+FLOP_PER_F_FRAME = 8.0e6             # pitch / energy towers per hop-300 frame
+FLOP_PER_TOKEN = 35e6 * 3            # three text encoders + predictors, per token (approx., 8d)
+
+
+def workload(rank: int, batch: int = BATCH):
+    """BASELINE configs[1]: `batch` utterances, lengths uniform in [0.25, 10] s, seeded per rank."""
+    from stylish_tts_b200 import fixture
+    secs = fixture.mixed_lengths(batch, seed=rank)
+    items = fixture.synth_batch(secs, seed=rank)
+    tokens = [it[0] for it in items]
+    durs = [it[1] for it in items]
+    frames = [it[2] for it in items]
+    return tokens, durs, frames
+
+
+def algorithmic_flops(tokens, frames) -> float:
+    return (sum(frames) * 4 * FLOP_PER_F4_FRAME + sum(frames) * FLOP_PER_F_FRAME
+            + sum(int(t.numel()) for t in tokens) * FLOP_PER_TOKEN)
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        p = json.load(open(path))
+        return {"hbm_gbs": p["hbm_gbs"], "bf16_burst": p["bf16_tflops"], "bf16_sustained": p["bf16_tflops_sustained"],
+                "source": "MEASURED_PEAKS.json"}
+    return {"hbm_gbs": 6650.0, "bf16_burst": 1590.0, "bf16_sustained": 1400.0, "source": "fallback (B200_PROFILING.md)"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except Exception:
+                continue
+            for n, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_port_throughput(tokens, durs, frames, budget_s: float, seed: int = 0):
+    """The reference's CPU path (oracle port = pinned restatement of the reference PyTorch forward,
+    B = 1 loop exactly like stage_type.py:491-512) on a bounded sample of the same workload."""
+    from oracle import stylish_port as port
+    from stylish_tts_b200 import fixture
+    sds = fixture.fixture_nets(fixture.load_manifest(), seed=0)
+    torch.set_num_threads(os.cpu_count() or 1)
+    order = sorted(range(len(frames)), key=lambda i: frames[i])
+    pick = [order[len(order) // 2], order[len(order) // 4], order[(3 * len(order)) // 4], order[-1], order[0]]
+    done_audio, t_total, used = 0.0, 0.0, []
+    g = torch.Generator().manual_seed(seed)
+    with torch.no_grad():
+        # warm-up on the smallest utterance (thread pools, allocator)
+        i0 = order[0]
+        port.synthesize(sds, tokens[i0][None], torch.tensor([tokens[i0].numel()]), fixture.draw_noise(frames[i0], g),
+                        duration=durs[i0].float())
+        for i in pick:
+            noise = fixture.draw_noise(frames[i], g)
+            t0 = time.perf_counter()
+            port.synthesize(sds, tokens[i][None], torch.tensor([tokens[i].numel()]), noise, duration=durs[i].float())
+            t_total += time.perf_counter() - t0
+            done_audio += 300.0 * frames[i] / 24000.0
+            used.append(i)
+            if t_total > budget_s:
+                break
+    return done_audio / t_total, torch.get_num_threads(), \
+        f"{len(used)} utterances of the batch ({done_audio:.1f} audio-s, B=1 loop), {t_total:.1f} s CPU wall"
+
+
+def run_reference_arm(args, rank: int, world: int):
+    """`--impl reference`: the reference's own CPU implementation of the path (oracle port; the
+    reference checkout does not exist on the GPU box), all host threads, bounded sample per step."""
+    if rank != 0:
+        return
+    tokens, durs, frames = workload(0)
+    vals = []
+    sample = ""
+    for s in range(args.warmup + args.steps):
+        v, cores, sample = cpu_port_throughput(tokens, durs, frames, budget_s=args.cpu_budget / 2, seed=s)
+        if s >= args.warmup:
+            vals.append(v)
+    v = sum(vals) / len(vals)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": None, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"BASELINE configs[1]: batch {BATCH} mixed 0.25-10 s utterances, B=1 loop (bounded sample)"},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32", "tf32x3"])
+    ap.add_argument("--cpu-budget", type=float, default=20.0, help="seconds of CPU work for the cpu_baseline leg")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-flush", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else max(args.warmup, 0)
+
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        return run_reference_arm(args, rank, world)
+    if args.gpus > 1 and world == 1:
+        raise SystemExit("launch multi-GPU runs with torch.distributed.run (one rank per GPU)")
+
+    import torch.distributed as dist
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    from stylish_tts_b200 import fixture
+    from stylish_tts_b200.config import ModelConfig
+    from stylish_tts_b200.modules import build_model
+    from stylish_tts_b200.synth import Synthesizer
+
+    sds = fixture.fixture_nets(fixture.load_manifest(), seed=0)
+    nets = build_model(ModelConfig())
+    for k, m in nets.items():
+        m.load_state_dict(sds[k])
+    syn = Synthesizer(nets, device=dev, precision=args.precision)
+    eng = syn.engine
+
+    tokens, durs, frames = workload(rank)
+    audio_s = 300.0 * sum(frames) / 24000.0
+    tok_host = [t.pin_memory() for t in tokens]
+    dur_host = [d.to(torch.int32).pin_memory() for d in durs]
+    tok_dev = [t.to(dev) for t in tokens]
+    dur_dev = [d.to(dev, torch.int32) for d in durs]
+    audio_host = torch.empty(300 * sum(frames), dtype=torch.float32).pin_memory()
+    flush_buf = None if args.no_flush else torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def step_resident():
+        if flush_buf is not None:
+            flush_buf.fill_(1)
+        return syn.synthesize(tok_dev, durations=dur_dev, frames=frames)
+
+    def step_e2e():
+        if flush_buf is not None:
+            flush_buf.fill_(1)
+        out = syn.synthesize(tok_host, durations=dur_host, frames=frames)
+        audio_host.copy_(out["audio_flat"], non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return out
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    for _ in range(args.warmup):
+        step_resident()
+    syn.check()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    eng.set_profiling(True)
+    l0 = eng.launch_count()
+    ms_total = timed(step_resident, args.steps)
+    launches = eng.launch_count() - l0
+    prof = eng.profile()
+    eng.set_profiling(False)
+    clocks = sampler.stop() if rank == 0 else None
+
+    for _ in range(2):
+        step_e2e()
+    ms_e2e = timed(step_e2e, args.steps)
+
+    tot_audio = torch.tensor([audio_s], device=dev, dtype=torch.float64)
+    tot_launch = torch.tensor([float(launches)], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(tot_audio)
+        dist.all_reduce(tot_launch)
+    value = float(tot_audio.item()) * args.steps / (ms_total / 1e3)
+    e2e_value = float(tot_audio.item()) * args.steps / (ms_e2e / 1e3)
+
+    if rank == 0:
+        pk = peaks()
+        tc = [p for p in prof if p["backend"] == (1 if args.precision == "bf16" else (2 if args.precision == "tf32x3" else 0))]
+        tc_ms = sum(p["ms"] for p in tc)
+        tc_fl = sum(p["flops"] for p in tc)
+        top = max(prof, key=lambda p: p["ms"]) if prof else None
+        peak_tf = pk["bf16_sustained"]
+        achieved = (tc_fl / (tc_ms / 1e3) / 1e12) if tc_ms > 0 else 0.0
+        roofline = {
+            "bound": "tensor", "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s",
+            "frac": achieved / peak_tf if peak_tf else None, "traffic": None,
+            "kernel": "conv_gemm_tc_kernel (tcgen05/TMA implicit-GEMM conv1d), all launches of the timed region"
+                      if args.precision != "fp32" else "conv_gemm_simt_kernel",
+            "peak_source": pk["source"] + " bf16_tflops_sustained",
+            "gemm_ms_per_step": sum(p["ms"] for p in prof) / args.steps,
+            "gemm_share_of_step": sum(p["ms"] for p in prof) / ms_total,
+            "top_layer": {"name": top["name"], "ms_per_step": top["ms"] / args.steps,
+                          "tflops": top["flops"] / (top["ms"] / 1e3) / 1e12} if top else None,
+            "step_tflops_algorithmic": algorithmic_flops(tokens, frames) * args.steps / (ms_total / 1e3) / 1e12,
+        }
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            v, cores, sample = cpu_port_throughput(tokens, durs, frames, budget_s=args.cpu_budget)
+            cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": {"bf16": "bf16", "fp32": "f32", "tf32x3": "tf32x3"}[args.precision],
+            "data": "synthetic",
+            "config": {"workload": f"BASELINE configs[1]: batch {BATCH} mixed-length utterances 0.25-10 s per GPU "
+                                   f"({audio_s:.1f} audio-s, {sum(int(t.numel()) for t in tokens)} phonemes), default model.yml, "
+                                   "fixture (seeded random-init) weights, synthetic durations",
+                       "precision": args.precision, "parallelism": f"utterance-sharded x{world}, no collective in the forward",
+                       "l2": "256 MiB flush write before every step; per-step working set >> 126 MB L2"
+                             if flush_buf is not None else "no flush",
+                       "workspace_bytes": eng.workspace_bytes()},
+            "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
+                    "h2d_bytes_per_step": int(sum(t.numel() * 8 for t in tokens) + sum(d.numel() * 4 for d in durs)),
+                    "d2h_bytes_per_step": int(audio_host.numel() * 4)},
+            "gpu_launches": int(tot_launch.item()),
+            "roofline": roofline,
+            "cpu_baseline": cpu,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

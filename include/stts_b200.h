@@ -106,6 +106,13 @@ int stts_generator(stts_ctx* ctx, const float* d_mel, const float* d_style, cons
                    const float* d_noise, const float* d_init_phase, float* d_audio, float* d_logamp,
                    float* d_phase, void* stream);
 
+/* Generator.forward from generator.py:412 on, with the STFT of the source (|X| and atan2 phase,
+ * dense [1025, L_b], generator.py:407-410) supplied by the caller.  Test / analysis entry: the
+ * phase of near-real bins is rounding noise in the reference (DESIGN.md "ill-conditioned phase"). */
+int stts_generator_from_stft(stts_ctx* ctx, const float* d_mel, const float* d_style,
+                             const float* d_har_spec, const float* d_har_phase, float* d_audio,
+                             float* d_logamp, float* d_phase, void* stream);
+
 /* ---- fused frame-rate path --------------------------------------------------------------------
  * Everything of SpeechPredictor.forward after the token-rate encoders: alignment expansion
  * (:88,:93), x4 linear upsample (:89-90), decoder, prior, flow^-1, post_flow, generator.

@@ -62,7 +62,7 @@ class ReplayRNG:
         torch.randn_like, torch.randn, torch.rand = self.saved
 
 
-def ref_synthesize(nets, proc, tokens, lengths, noise, duration, taps):
+def ref_synthesize(nets, proc, tokens, lengths, noise, duration, taps, exact_frame0=False):
     """stage_type.py:483-523 for one utterance, with hooks recording the SURVEY 8a intermediates."""
     sp = nets.speech_predictor
     pe = nets.pitch_energy_predictor
@@ -86,6 +86,9 @@ def ref_synthesize(nets, proc, tokens, lengths, noise, duration, taps):
     hooks.append(sp.post_flow.register_forward_hook(rec("mel", lambda o: o.mT)))
     hooks.append(sp.generator.amp_prior_conv.register_forward_pre_hook(rec_in("har_spec")))
     hooks.append(sp.generator.phase_prior_conv.register_forward_pre_hook(rec_in("har_phase")))
+    if exact_frame0:  # the real reference with the exact (real-valued) frame-0 spectrum phase
+        hooks.append(sp.generator.phase_prior_conv.register_forward_pre_hook(
+            lambda m, i: (port.exact_frame0_phase(i[0]),)))
     hooks.append(sp.generator.projector.register_forward_hook(rec("gen_proj")))
     hooks.append(sp.generator.convnext[3].register_forward_hook(rec("gen_convnext")))
     hooks.append(pe.prosody_encoder.register_forward_hook(rec("pe_prosody")))
@@ -138,6 +141,14 @@ def run_case(name, nets, sds, proc, tokens, dur, seed, pin, keep_taps):
     ref = ref_synthesize(nets, proc, tk, ln, noise, dur, rtaps)
     with torch.no_grad():
         got = port.synthesize(sds, tk, ln, noise, duration=dur.to(torch.float32), taps=ptaps)
+    ref_x0 = ref_synthesize(nets, proc, tk, ln, noise, dur, {}, exact_frame0=True)
+    with torch.no_grad():
+        got_x0 = port.synthesize(sds, tk, ln, noise, duration=dur.to(torch.float32), exact_frame0=True)
+    compare(f"{name}.audio_x0", got_x0["audio"], ref_x0["audio"], pin)
+    ref["audio_x0"] = ref_x0["audio"]
+    ref["logamp_x0"] = ref_x0["logamp"]
+    d0 = (ref_x0["audio"] - ref["audio"]).abs()[0, 0]
+    print(f"    reference raw vs exact-frame-0: max {float(d0.max()):.3e}; beyond sample 7500: {float(d0[7500:].max()) if d0.numel() > 7500 else 0:.3e}")
     print(f"  case {name}: T={tokens.shape[0]} F={n_frames} audio absmax={float(ref['audio'].abs().max()):.4f} "
           f"voiced frac={float((rtaps['pitch4'] > 10).float().mean()):.2f}")
     for k in ("audio", "logamp", "phase", "pitch", "energy"):
@@ -189,6 +200,7 @@ def main():
     ref, taps, noise, out = run_case("tiny", nets, sds, proc, tokens, dur, 101, pin, True)
     for k, v in ref.items():
         out[f"out.{k}"] = v.float().contiguous()
+    del out["out.logamp_x0"]
     for k, v in taps.items():
         out[f"tap.{k}"] = v.float().contiguous()
     for k, v in noise.items():
@@ -201,6 +213,7 @@ def main():
     dur = fixture.synth_durations(5, 20, g)
     ref, taps, noise, out = run_case("short", nets, sds, proc, tokens, dur, 102, pin, False)
     out["out.audio"] = ref["audio"].contiguous()
+    out["out.audio_x0"] = ref["audio_x0"].contiguous()
     out["out.pitch"] = ref["pitch"].contiguous()
     save_file(out, os.path.join(GOLD, "short.safetensors"))
 
@@ -212,6 +225,8 @@ def main():
     out["out.audio"] = ref["audio"].contiguous()
     out["out.pitch"] = ref["pitch"].contiguous()
     out["out.energy"] = ref["energy"].contiguous()
+    out["out.audio_x0"] = ref["audio_x0"].contiguous()
+    out["out.logamp_x0_s16"] = ref["logamp_x0"][:, :, ::16].contiguous()
     out["out.logamp_s16"] = ref["logamp"][:, :, ::16].contiguous()
     out["out.phase_s16"] = ref["phase"][:, :, ::16].contiguous()
     out["tap.mel_s16"] = taps["mel"][:, :, ::16].contiguous()
@@ -228,6 +243,7 @@ def main():
         for k, v in o.items():
             out[f"{i}.{k}"] = v
         out[f"{i}.out.audio"] = ref["audio"].contiguous()
+        out[f"{i}.out.audio_x0"] = ref["audio_x0"].contiguous()
         out[f"{i}.out.pitch"] = ref["pitch"].contiguous()
         out[f"{i}.out.energy"] = ref["energy"].contiguous()
     save_file(out, os.path.join(GOLD, "batch3.safetensors"))

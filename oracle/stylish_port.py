@@ -422,13 +422,31 @@ def convnext_block(sd: SD, p: str, x: Tensor, style: Tensor) -> Tensor:
     return x + y.transpose(1, 2)
 
 
+def exact_frame0_phase(har_phase: Tensor) -> Tensor:
+    """Frame 0 of torch.stft(center=True, reflect) is centred on sample 0: the windowed frame is
+    even about its centre, so X_k is exactly real and the reference's atan2 there is FFT rounding
+    noise (0 or +-pi with a random sign).  This returns the mathematically exact phase for that
+    frame (atan2(+0, Re): 0 for Re > 0, +pi for Re < 0) and leaves every other frame untouched.
+    It is a *documented variant* of the oracle used where an implementation-independent target
+    is needed (DESIGN.md "ill-conditioned phase"); the default oracle stays the raw reference."""
+    out = har_phase.clone()
+    f0 = out[:, :, 0]
+    out[:, :, 0] = torch.where(f0.abs() > (math.pi / 2), torch.full_like(f0, math.pi), torch.zeros_like(f0))
+    return out
+
+
 def generator(sd: SD, p: str, mel: Tensor, style: Tensor, pitch: Tensor,
-              noise: Tensor, init_phase: Tensor, taps: Optional[Dict[str, Tensor]] = None):
+              noise: Tensor, init_phase: Tensor, taps: Optional[Dict[str, Tensor]] = None,
+              exact_frame0: bool = False, stft_override: Optional[Tuple[Tensor, Tensor]] = None):
     """generator.py:402-438 -> (audio [B,1,75L], logamp [B,1025,L+1], phase [B,1025,L+1]).
     The ``energy`` argument of the reference is unused."""
     pit = pitch.unsqueeze(1)
     prior = generate_pcph(pit, (pit > 10.0).float(), noise, init_phase).squeeze(1)
     har_spec, har_phase = stft_mag_phase(prior)
+    if stft_override is not None:
+        har_spec, har_phase = stft_override
+    if exact_frame0:
+        har_phase = exact_frame0_phase(har_phase)
     la_prior = F.conv1d(har_spec, sd[p + "amp_prior_conv.weight"], sd[p + "amp_prior_conv.bias"], padding=3)
     ph_prior = F.conv1d(har_phase, sd[p + "phase_prior_conv.weight"], sd[p + "phase_prior_conv.bias"], padding=3)
     x = F.conv1d(torch.cat([mel, la_prior, ph_prior], dim=1), sd[p + "projector.weight"], sd[p + "projector.bias"])
@@ -458,7 +476,7 @@ def upsample4(x: Tensor) -> Tensor:
 
 def speech_predictor(sd: SD, tokens: Tensor, lengths: Tensor, alignment: Tensor, pitch: Tensor,
                      energy: Tensor, noise: Dict[str, Tensor],
-                     taps: Optional[Dict[str, Tensor]] = None):
+                     taps: Optional[Dict[str, Tensor]] = None, exact_frame0: bool = False):
     """speech_predictor.py:85-129, inference branch (audio_gt is None).
 
     ``noise`` holds the three reference draws in call order: "prior" [B,128,4F] (flow.py:314),
@@ -477,11 +495,13 @@ def speech_predictor(sd: SD, tokens: Tensor, lengths: Tensor, alignment: Tensor,
     if taps is not None:
         taps.update(sp_text=enc, sp_style=style, dec_out=x, z_prior=z, z_flow=z2, mel=mel,
                     pitch4=pitch4, energy4=energy4)
-    return generator(sd, "generator.", mel, style, pitch4, noise["source"], noise["phase"], taps)
+    return generator(sd, "generator.", mel, style, pitch4, noise["source"], noise["phase"], taps,
+                     exact_frame0=exact_frame0)
 
 
 def synthesize(nets: Mapping[str, SD], tokens: Tensor, lengths: Tensor, noise: Dict[str, Tensor],
-               duration: Optional[Tensor] = None, taps: Optional[Dict[str, Tensor]] = None):
+               duration: Optional[Tensor] = None, taps: Optional[Dict[str, Tensor]] = None,
+               exact_frame0: bool = False):
     """The B = 1 inference recipe of stage_type.py:483-523 / export_model.py:35-45.
 
     ``nets`` maps the five module names to their state dicts.  If ``duration`` [T] is given it
@@ -496,7 +516,8 @@ def synthesize(nets: Mapping[str, SD], tokens: Tensor, lengths: Tensor, noise: D
     pe_enc, _, _ = text_encoder(nets["pe_text_encoder"], "", tokens, lengths)
     pe_style = text_style_encoder(nets["pe_text_style_encoder"], "", pe_enc, lengths)
     pitch, energy = pitch_energy_predictor(nets["pitch_energy_predictor"], pe_enc, lengths, alignment, pe_style, taps)
-    audio, la, ph = speech_predictor(nets["speech_predictor"], tokens, lengths, alignment, pitch, energy, noise, taps)
+    audio, la, ph = speech_predictor(nets["speech_predictor"], tokens, lengths, alignment, pitch, energy, noise, taps,
+                                     exact_frame0=exact_frame0)
     if taps is not None:
         taps.update(dur_logits=logits, pe_text=pe_enc, pe_style=pe_style)
     return dict(audio=audio, logamp=la, phase=ph, duration=dur_pred, pitch=pitch, energy=energy)

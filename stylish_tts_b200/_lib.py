@@ -28,6 +28,7 @@ SIGNATURES = {
     "stts_prior_flow": (_i, [_vp, _fp, _fp, _fp, _fp, _fp, _fp, _vp]),
     "stts_source_pcph": (_i, [_vp, _fp, _fp, _fp, _fp, _vp]),
     "stts_generator": (_i, [_vp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _vp]),
+    "stts_generator_from_stft": (_i, [_vp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _vp]),
     "stts_speech_frames": (_i, [_vp] + [_fp] * 13 + [_vp]),
     "stts_check_source_status": (_i, [_vp, _vp]),
     "stts_test_conv": (_i, [_vp, _i, _fp, _i, _i, _i, _i, _fp, _fp, _i, _fp, _i, _vp]),

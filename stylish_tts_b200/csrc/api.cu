@@ -137,6 +137,14 @@ int stts_generator(stts_ctx* ctx, const float* d_mel, const float* d_style, cons
   return run_generator(ctx->c, d_mel, d_style, d_pitch4, d_noise, d_init_phase, d_audio, d_logamp, d_phase, S(stream));
 }
 
+int stts_generator_from_stft(stts_ctx* ctx, const float* d_mel, const float* d_style, const float* d_har_spec,
+                             const float* d_har_phase, float* d_audio, float* d_logamp, float* d_phase, void* stream) {
+  if (!ctx || !d_mel || !d_style || !d_har_spec || !d_har_phase || !d_audio) return STTS_ERR_BAD_ARG;
+  DeviceGuard g(ctx->c.device);
+  return run_generator_from_stft(ctx->c, d_mel, d_style, d_har_spec, d_har_phase, d_audio, d_logamp, d_phase,
+                                 S(stream));
+}
+
 int stts_speech_frames(stts_ctx* ctx, const float* d_enc_tok, const int32_t* d_cu_tok, const int32_t* d_idx,
                        const int32_t* d_cu_frames, const float* d_pitch, const float* d_energy, const float* d_style,
                        const float* d_noise_prior, const float* d_noise_source, const float* d_init_phase,

@@ -54,6 +54,7 @@ struct Epi {
   float scale;
   int split;                   // EPI_RESSKIP
   int accumulate2;             // EPI_RESSKIP: out2 += (1) or = (0)
+  const int* seg_start;        // EPI_STFT: first row of every segment (frame 0 is real by symmetry)
 };
 
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + __expf(-x)); }
@@ -158,7 +159,10 @@ __device__ __forceinline__ void epi_apply(const Epi& e, int r, int seg, int n0, 
       const int n = n0 + i;
       if (n < e.N) {
         const int c = n >> 1;
-        const float re = acc[i], im = acc[i + 1];
+        // Frame 0 of an utterance is centred on sample 0 of the reflect-padded signal, so its
+        // windowed frame is even about the centre and X_k is exactly real: the reference's Im is
+        // pure FFT rounding noise there (random +-pi for Re < 0).  Return the exact value.
+        const float re = acc[i], im = (e.seg_start != nullptr && r == e.seg_start[seg]) ? 0.f : acc[i + 1];
         const float mag = hypotf(re, im);
         const float d = mag + 1e-9f;
         const float ph = atan2f(im / d, re / d);

@@ -107,6 +107,11 @@ int run_source(Context& c, const float* d_pitch4_dense, const float* d_noise, co
                cudaStream_t st);
 int run_generator_core(Context& c, const float* d_style, const float* d_noise, const float* d_init_phase,
                        float* d_audio, float* d_logamp, float* d_phase, cudaStream_t st);
+int run_generator_tail(Context& c, const float* d_style, float* d_audio, float* d_logamp, float* d_phase,
+                       cudaStream_t st);
+int run_generator_from_stft(Context& c, const float* d_mel, const float* d_style, const float* d_har_spec,
+                            const float* d_har_phase, float* d_audio, float* d_logamp, float* d_phase,
+                            cudaStream_t st);
 int run_generator(Context& c, const float* d_mel, const float* d_style, const float* d_pitch4, const float* d_noise,
                   const float* d_init_phase, float* d_audio, float* d_logamp, float* d_phase, cudaStream_t st);
 int run_speech_frames(Context& c, const float* d_enc_tok, const int* d_cu_tok, const int* d_idx,

@@ -186,8 +186,9 @@ int set_layout(Context& c, int n_seg, const int* len_f, const int* len_f4) {
     up("cu" + s, L.cu.data(), (size_t)(B + 1) * 4);
     up("cs" + s, cs.data(), (size_t)B * 4);
     up("cs_p1" + s, cs_p1.data(), (size_t)B * 4);
-    // dense element offsets: j = 0: C = 128, 1: C = 512, 2: C = 1025 with L + 1 frames, 3: C = 320
-    const int Cs[4] = {128, 512, 1025, 320};
+    // dense element offsets: j = 0: C = 128, 1: C = 512, 2: C = 1025 with L + 1 frames,
+    // 3: C = 320 (hop-300 layout) / C = 1025 (hop-75 layout)
+    const int Cs[4] = {128, 512, 1025, k == 0 ? 1025 : 320};
     for (int j = 0; j < 4; ++j) {
       std::vector<long long> off(B);
       for (int b = 0; b < B; ++b) off[b] = (long long)Cs[j] * (L.cu[b] + (j == 2 ? b : 0));
@@ -509,8 +510,24 @@ int run_generator_core(Context& c, const float* d_style, const float* d_noise, c
     Epi e = S.epi(EPI_STFT, hs, 0);
     e.out2 = hp.f; e.ldo2 = hp.ld; e.col20 = 0;
     e.outh2 = S.tw(hp); e.ldh2 = hp.ld; e.colh20 = 0;
+    e.seg_start = c.L4.d_seg_start;
     STTS_RET(run_gemm(c, c.gemm["stft"], GC_ISLAND, &src, 0, nullptr, 0, e, map, st));
   }
+  return run_generator_tail(c, d_style, d_audio, d_logamp, d_phase, st);
+}
+
+// Generator.forward from the prior convs on (generator.py:412-433): expects HS / HP (|X| and phase of
+// the source), CATP[:, 0:512] = mel and GB_GEN (style FCs).
+int run_generator_tail(Context& c, const float* d_style, float* d_audio, float* d_logamp, float* d_phase,
+                       cudaStream_t st) {
+  Stage S(c, st);
+  const RowMap map = c.L4.map();
+  const RowMap map_p1 = c.L4.map_p1();
+  Act &hs = S.A("HS"), &hp = S.A("HP"), &catp = S.A("CATP"), &xg = S.A("XG"), &xgn = S.A("XGN");
+  Act &h = S.A("H"), &ampn = S.A("AMPN"), &phn = S.A("PHN"), &la = S.A("LA"), &ph = S.A("PH"), &spec = S.A("SPEC");
+  Act& yf = S.A("YF");
+  float* gb = S.R<float>("GB_GEN");
+  (void)d_style;
   {  // amp / phase prior convs (k7) into the concat buffer   (generator.py:412-413)
     Epi e = S.epi(EPI_BIAS, catp, 512);
     STTS_RET(run_gemm(c, c.gemm["gen.amp_prior"], GC_BODY, &hs, 0, nullptr, 0, e, map, st));
@@ -573,6 +590,23 @@ int run_generator(Context& c, const float* d_mel, const float* d_style, const fl
   STTS_CK(transpose_in(d_mel, c.L4.d_off[1], c.L4.d_cs, 512, map, catp.f, catp.ld, 0, S.tw(catp), catp.ld, 0, st));
   STTS_CK(rowvec_copy(S.R<float>("P4"), const_cast<float*>(d_pitch4), c.L4.d_cu, map, 1, st));
   return run_generator_core(c, d_style, d_noise, d_init_phase, d_audio, d_logamp, d_phase, st);
+}
+
+// test / analysis entry: Generator.forward with the source STFT supplied by the caller
+int run_generator_from_stft(Context& c, const float* d_mel, const float* d_style, const float* d_har_spec,
+                            const float* d_har_phase, float* d_audio, float* d_logamp, float* d_phase,
+                            cudaStream_t st) {
+  if (!c.finalized || c.J_gen == 0) return fail(c, -3, "speech_predictor weights not loaded");
+  if (c.L4.total() == 0 || c.act.count("CATP") == 0) return fail(c, -4, "no hop-75 layout set");
+  Stage S(c, st);
+  const RowMap map = c.L4.map();
+  Act &catp = S.A("CATP"), &hs = S.A("HS"), &hp = S.A("HP");
+  STTS_CK(style_fc(c.vec["gen.fc_W"], c.vec["gen.fc_b"], d_style, c.J_gen, 64, c.L4.n_seg, S.R<float>("GB_GEN"), st));
+  STTS_CK(transpose_in(d_mel, c.L4.d_off[1], c.L4.d_cs, 512, map, catp.f, catp.ld, 0, S.tw(catp), catp.ld, 0, st));
+  // dense [1025, L] per utterance: element offsets 1025 * cu[b] are not tabulated, derive from C = 1025 view
+  STTS_CK(transpose_in(d_har_spec, c.L4.d_off[3], c.L4.d_cs, 1025, map, hs.f, hs.ld, 0, S.tw(hs), hs.ld, 0, st));
+  STTS_CK(transpose_in(d_har_phase, c.L4.d_off[3], c.L4.d_cs, 1025, map, hp.f, hp.ld, 0, S.tw(hp), hp.ld, 0, st));
+  return run_generator_tail(c, d_style, d_audio, d_logamp, d_phase, st);
 }
 
 // ----------------------------------------------------------------------------- fused frame-rate path

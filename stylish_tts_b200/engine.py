@@ -159,6 +159,15 @@ class Engine:
                                             _ptr(init_phase), _ptr(audio), _ptr(la), _ptr(ph), self._stream()))
         return audio, la, ph
 
+    def generator_from_stft(self, mel, style, har_spec, har_phase):
+        tot = sum(self.len_f4)
+        audio = torch.empty(75 * tot, device=self.device)
+        la = torch.empty(1025 * (tot + self.n_seg), device=self.device)
+        ph = torch.empty(1025 * (tot + self.n_seg), device=self.device)
+        self._check(self.lib.stts_generator_from_stft(self.h, _ptr(mel), _ptr(style), _ptr(har_spec), _ptr(har_phase),
+                                                      _ptr(audio), _ptr(la), _ptr(ph), self._stream()))
+        return audio, la, ph
+
     def speech_frames(self, enc_tok, cu_tok, idx, cu_frames, pitch, energy, style, noise_prior, noise_source,
                       init_phase, want_spec: bool = False):
         tot = sum(self.len_f4)

@@ -45,7 +45,7 @@ class Synthesizer:
     @torch.no_grad()
     def synthesize(self, tokens: Sequence[torch.Tensor], durations: Optional[Sequence[torch.Tensor]] = None,
                    noise: Optional[Sequence[Dict[str, torch.Tensor]]] = None, want_spec: bool = False,
-                   want_intermediates: bool = False) -> Dict[str, object]:
+                   want_intermediates: bool = False, frames: Optional[Sequence[int]] = None) -> Dict[str, object]:
         """tokens[b]: int64 [T_b] (host or device).  durations[b]: optional integer durations
         overriding the predicted ones (they are still predicted and returned).  noise[b]:
         optional dict(prior [1,128,4F], source [1,1,300F], phase [1,1]) -- the three reference
@@ -69,7 +69,8 @@ class Synthesizer:
             dur_used = torch.zeros((B, Tmax), dtype=torch.int32, device=dev)
             for b, d in enumerate(durations):
                 dur_used[b, : T[b]] = d.to(dev, torch.int32, non_blocking=True)
-            F_list = [int(d.sum()) for d in durations]                      # host-known: no device sync
+            # host-known frame counts: no device sync (pass `frames` when the durations live on the device)
+            F_list = [int(f) for f in frames] if frames is not None else [int(d.sum()) for d in durations]
         else:
             dur_used = dur_pred
             F_list = [int(v) for v in dur_pred.sum(dim=1).tolist()]          # the one unavoidable D2H

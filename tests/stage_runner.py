@@ -110,17 +110,32 @@ def run(precision="fp32"):
         rec("gen.logamp", la.view(1025, F4 + 1), g["out.logamp"][0])
         rec("gen.phase", ph.view(1025, F4 + 1), g["out.phase"][0])
         rec("gen.audio", audio, g["out.audio"])
+        rec("gen.audio_x0", audio, g["out.audio_x0"])
+        rec("gen.audio_after_7500", audio[7500:], g["out.audio"].reshape(-1)[7500:])
+
+    def sec_generator_from_reference_stft():  # strict: generator fed the reference's own |X| / phase
+        audio, la, ph = eng.generator_from_stft(g["tap.mel"].to(dev).contiguous().view(-1), style.view(-1),
+                                                g["tap.har_spec"].to(dev).contiguous().view(-1),
+                                                g["tap.har_phase"].to(dev).contiguous().view(-1))
+        rows, starts = eng.layout_info(4)
+        s0 = starts[0]
+        rec("strict.gen_convnext", eng.debug_read("XG")[s0: s0 + F4, :512].t(), g["tap.gen_convnext"][0])
+        rec("strict.logamp", la.view(1025, F4 + 1), g["out.logamp"][0])
+        rec("strict.phase", ph.view(1025, F4 + 1), g["out.phase"][0])
+        rec("strict.audio", audio, g["out.audio"])
 
     def sec_SpeechPredictor_module_end_to_end__nativ():  # SpeechPredictor module end to end (native frame-rate path, reference pitch/energy)
         sp.noise_override = {k[6:]: v for k, v in g.items() if k.startswith("noise.")}
         pred = sp(tokens, lens, alignment, g["out.pitch"].to(dev), g["out.energy"].to(dev))
         sp.noise_override = None
         rec("SpeechPredictor.audio", pred.audio, g["out.audio"])
+        rec("SpeechPredictor.audio_x0", pred.audio, g["out.audio_x0"])
         rec("SpeechPredictor.logamp", pred.magnitude, g["out.logamp"])
 
     with torch.no_grad():
         for fn in (sec_length_regulation, sec_pitch___energy_towers_on_the_reference_s, sec_decoder,
                    sec_prior___flow___post_flow, sec_source, sec_generator__fed_the_reference_mel_,
+                   sec_generator_from_reference_stft,
                    sec_SpeechPredictor_module_end_to_end__nativ):
             try:
                 fn()

@@ -9,9 +9,13 @@ pytestmark = pytest.mark.gpu
 FP32_REL = {
     "pe_towers.pitch": 2e-5, "pe_towers.energy": 2e-5, "PitchEnergyPredictor.pitch": 5e-5,
     "decoder": 2e-5, "z_prior": 2e-5, "z_flow": 5e-5, "mel": 5e-5, "source": 2e-5,
-    "har_spec": 2e-5, "gen_convnext": 5e-5, "gen.logamp": 5e-5,
+    "har_spec": 2e-5, "logamp_prior": 2e-5, "strict.gen_convnext": 5e-5, "strict.logamp": 5e-5,
 }
-FP32_ABS = {"gen.audio": 1e-4, "SpeechPredictor.audio": 1e-4, "duration_pred": 0.0, "alignment": 0.0}
+# "strict.*": generator fed the reference's own STFT -> compared with the raw reference output.
+# "*_x0": full path compared with the reference run with the exact (real) frame-0 phase, because the
+# raw reference's frame-0 phase is FFT rounding noise (DESIGN.md "ill-conditioned phase").
+FP32_ABS = {"strict.audio": 1e-4, "gen.audio_x0": 1e-4, "SpeechPredictor.audio_x0": 1e-4,
+            "gen.audio_after_7500": 1.5e-4, "duration_pred": 0.0, "alignment": 0.0}
 
 
 def _check(res, rel_scale, audio_tol):
@@ -22,8 +26,9 @@ def _check(res, rel_scale, audio_tol):
     for k, tol in FP32_ABS.items():
         t = audio_tol if "audio" in k else tol
         assert res[k]["max_abs"] <= t, (k, res[k])
-    # atan2 phase of near-silent bins is ill-conditioned in the reference itself: bound the outliers
-    assert res["har_phase(wrapped)"]["frac_gt_1e-3"] <= 2e-3 * rel_scale, res["har_phase(wrapped)"]
+    # phase modulo 2 pi everywhere; +-pi sign flips are only tolerated in frame 0 (<= 1025 bins)
+    assert res["har_phase(wrapped)"]["max_abs"] <= 2e-3 * rel_scale, res["har_phase(wrapped)"]
+    assert res["har_phase.unwrapped_flips"]["max_abs"] <= 1025, res["har_phase.unwrapped_flips"]
 
 
 def test_stages_fp32():
@@ -41,6 +46,7 @@ def test_stages_bf16():
     res = run("bf16")
     bad = [k for k in res if k.endswith(".EXCEPTION")]
     assert not bad, {k: res[k].get("error") for k in bad}
-    assert res["gen.audio"]["max_abs"] <= 2e-3, res["gen.audio"]
-    assert res["SpeechPredictor.audio"]["max_abs"] <= 2e-3, res["SpeechPredictor.audio"]
+    assert res["strict.audio"]["max_abs"] <= 2e-3, res["strict.audio"]
+    assert res["gen.audio_x0"]["max_abs"] <= 2e-3, res["gen.audio_x0"]
+    assert res["SpeechPredictor.audio_x0"]["max_abs"] <= 2e-3, res["SpeechPredictor.audio_x0"]
     assert res["duration_pred"]["max_abs"] == 0.0
