@@ -45,11 +45,15 @@ class Synthesizer:
     @torch.no_grad()
     def synthesize(self, tokens: Sequence[torch.Tensor], durations: Optional[Sequence[torch.Tensor]] = None,
                    noise: Optional[Sequence[Dict[str, torch.Tensor]]] = None, want_spec: bool = False,
-                   want_intermediates: bool = False, frames: Optional[Sequence[int]] = None) -> Dict[str, object]:
+                   want_intermediates: bool = False, frames: Optional[Sequence[int]] = None,
+                   pitch_energy: Optional[Sequence] = None) -> Dict[str, object]:
         """tokens[b]: int64 [T_b] (host or device).  durations[b]: optional integer durations
         overriding the predicted ones (they are still predicted and returned).  noise[b]:
         optional dict(prior [1,128,4F], source [1,1,300F], phase [1,1]) -- the three reference
-        draws; drawn with torch on the device otherwise.
+        draws; drawn with torch on the device otherwise.  pitch_energy[b] = (pitch [F], energy [F]):
+        optional curves fed to the speech stage instead of the predicted ones (the predicted ones are
+        still computed and returned) -- the harmonic source integrates f0 over the whole utterance, so
+        waveform parity is only defined for identical pitch input (DESIGN.md "conditioning").
         Returns dict(audio=[...[300 F_b]], duration_pred=[...], pitch=[...], energy=[...], ...)."""
         dev, eng, nets = self.device, self.engine, self.nets
         B = len(tokens)
@@ -93,6 +97,10 @@ class Synthesizer:
         x = pep.compute_cross(prosody, frame_token, pe_style, lens, frame_lengths=f_lens)   # [B, 320, Fmax]
         x_dense = torch.cat([x[b, :, : F_list[b]].reshape(-1) for b in range(B)])
         pitch, energy = eng.pe_towers(x_dense, pe_style.contiguous())
+        pitch_in, energy_in = pitch, energy
+        if pitch_energy is not None:
+            pitch_in = torch.cat([pe[0].reshape(-1) for pe in pitch_energy]).to(dev, torch.float32).contiguous()
+            energy_in = torch.cat([pe[1].reshape(-1) for pe in pitch_energy]).to(dev, torch.float32).contiguous()
 
         # ---- speech
         sp = nets["speech_predictor"]
@@ -107,7 +115,7 @@ class Synthesizer:
             n_prior = torch.randn(128 * 4 * F_tot, device=dev)
             n_src = torch.randn(300 * F_tot, device=dev)
             n_phase = torch.rand(B, device=dev)
-        audio, la, ph = eng.speech_frames(enc_tok, cu_tok, idx, cu_frames, pitch, energy, style, n_prior, n_src,
+        audio, la, ph = eng.speech_frames(enc_tok, cu_tok, idx, cu_frames, pitch_in, energy_in, style, n_prior, n_src,
                                           n_phase, want_spec=want_spec)
         out: Dict[str, object] = {}
         a_off = [0]

@@ -1,5 +1,11 @@
 """GPU: full synthesis (Synthesizer = user-facing API) against golden audio from the live
-reference, ragged-batch == per-utterance semantics, and size-independent properties."""
+reference, ragged-batch == per-utterance semantics, and size-independent properties.
+
+Waveform comparisons feed the reference's pitch / energy curves to the speech stage (the predicted
+curves are checked separately, to a relative tolerance): generate_pcph integrates f0 over the whole
+utterance and multiplies by up to 16 harmonics, so a 1e-7 relative change of the pitch moves the
+reference's own waveform by 8e-3 on the 5 s fixture (measured on the oracle).  The target
+is the reference run with the exact (real) frame-0 STFT phase, "audio_x0", for the same reason."""
 import json
 import os
 
@@ -30,7 +36,11 @@ def test_golden_single_utterances(precision, tol):
     for name in ("tiny", "short", "c1"):
         g = gold(name)
         tokens, dur, noise = _case(g)
-        out = syn.synthesize([tokens], durations=[dur], noise=[noise])
+        out = syn.synthesize([tokens], durations=[dur], noise=[noise],
+                             pitch_energy=[(g["out.pitch"], g["out.energy"])] if "out.energy" in g else None)
+        if "out.energy" not in g:       # "short" stores no energy: take the predicted one, inject the pitch
+            out = syn.synthesize([tokens], durations=[dur], noise=[noise],
+                                 pitch_energy=[(g["out.pitch"], out["energy"][0])])
         syn.check()
         # target: the reference with the exact frame-0 phase (its raw frame-0 phase is rounding noise,
         # DESIGN.md "ill-conditioned phase"); the raw reference is matched beyond the affected span
@@ -39,6 +49,7 @@ def test_golden_single_utterances(precision, tol):
         perr = maxabs(out["pitch"][0], g["out.pitch"].reshape(-1))
         _log(f"{precision}.{name}", {"audio_x0": err, "audio_raw_after_7500": raw, "pitch": perr})
         assert raw <= 1.5 * tol, (precision, name, raw)
+        assert perr <= (2e-5 if precision == "fp32" else (1e-4 if precision == "tf32x3" else 2e-2)) * 300, (name, perr)
         assert torch.equal(out["duration_pred"][0].cpu().to(torch.int32), g["duration_pred"]), name
         assert out["audio"][0].numel() == 300 * int(dur.sum())
         assert err <= tol, (precision, name, err)
@@ -49,7 +60,9 @@ def test_ragged_batch_equals_b1_loop(precision, tol):
     syn = synthesizer(precision)
     g = gold("batch3")
     cases = [_case(g, f"{i}.") for i in range(3)]
-    out = syn.synthesize([c[0] for c in cases], durations=[c[1] for c in cases], noise=[c[2] for c in cases])
+    pe = [(g[f"{i}.out.pitch"], g[f"{i}.out.energy"]) for i in range(3)]
+    out = syn.synthesize([c[0] for c in cases], durations=[c[1] for c in cases], noise=[c[2] for c in cases],
+                         pitch_energy=pe)
     syn.check()
     for i in range(3):
         err = maxabs(out["audio"][i], g[f"{i}.out.audio_x0"].reshape(-1))
@@ -100,9 +113,14 @@ def test_module_api_matches_reference_signatures():
     nets["pitch_energy_predictor"].engine().set_precision("fp32")
     nets["speech_predictor"].noise_override = noise
     audio = em(tokens[None].to(dev), torch.tensor([tokens.numel()], device=dev), al)
-    nets["speech_predictor"].noise_override = None
     assert audio.shape == (300 * int(dur.sum()),)
-    assert maxabs(audio, g["out.audio_x0"].reshape(-1)) <= 1e-4
+    # ExportModel feeds its own predicted pitch to the source, which integrates it (see module doc):
+    # the waveform is only loosely comparable; the strict comparison uses the reference pitch
+    pred = nets["speech_predictor"](tokens[None].to(dev), torch.tensor([tokens.numel()], device=dev), al,
+                                    g["out.pitch"].to(dev), g["out.energy"].to(dev))
+    nets["speech_predictor"].noise_override = None
+    assert maxabs(pred.audio, g["out.audio_x0"]) <= 1e-4
+    assert maxabs(audio, g["out.audio_x0"].reshape(-1)) <= 0.1
 
 
 def test_reference_error_path_voiced_without_f0_above_20():

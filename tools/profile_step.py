@@ -1,0 +1,33 @@
+"""One synthesis step of the bench workload between cudaProfilerStart/Stop (for ncu
+--profile-from-start off).  usage: python tools/profile_step.py [precision] [batch]"""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch  # noqa: E402
+
+from bench import workload  # noqa: E402
+from stylish_tts_b200 import fixture  # noqa: E402
+from stylish_tts_b200.config import ModelConfig  # noqa: E402
+from stylish_tts_b200.modules import build_model  # noqa: E402
+from stylish_tts_b200.synth import Synthesizer  # noqa: E402
+
+prec = sys.argv[1] if len(sys.argv) > 1 else "bf16"
+batch = int(sys.argv[2]) if len(sys.argv) > 2 else 32
+sds = fixture.fixture_nets(fixture.load_manifest(), seed=0)
+nets = build_model(ModelConfig())
+for k, m in nets.items():
+    m.load_state_dict(sds[k])
+syn = Synthesizer(nets, device="cuda:0", precision=prec)
+tokens, durs, frames = workload(0, batch)
+tok = [t.cuda() for t in tokens]
+dd = [d.cuda().to(torch.int32) for d in durs]
+for _ in range(2):
+    syn.synthesize(tok, durations=dd, frames=frames)
+torch.cuda.synchronize()
+torch.cuda.profiler.start()
+syn.synthesize(tok, durations=dd, frames=frames)
+torch.cuda.synchronize()
+torch.cuda.profiler.stop()
+print("done", sum(frames) * 300 / 24000.0, "audio-s")
