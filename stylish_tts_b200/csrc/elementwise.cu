@@ -202,8 +202,10 @@ __global__ void __launch_bounds__(256) upsample4_kernel(const float* __restrict_
   const float l0 = 1.f - l1;
   const int o = cu_f[seg];
   const size_t r = (size_t)tile * 128 + lr;
-  a4[r] = l0 * a[o + i0] + l1 * a[o + i1];
-  b4[r] = l0 * b[o + i0] + l1 * b[o + i1];
+  // rounding order of ATen's CPU kernel (verified bit-exact on 16k samples): t = l1 * x1 rounded,
+  // then fma(l0, x0, t).  The pitch curve feeds a phase integrator x 16 harmonics, so 1 ulp matters.
+  a4[r] = __fmaf_rn(l0, a[o + i0], __fmul_rn(l1, a[o + i1]));
+  b4[r] = __fmaf_rn(l0, b[o + i0], __fmul_rn(l1, b[o + i1]));
 }
 
 cudaError_t upsample4(const float* a, const float* b, const int* cu_f, const RowMap& map, float* a4, float* b4,

@@ -117,6 +117,13 @@ __device__ __forceinline__ uint64_t make_sdesc(uint32_t smem_addr) {
   return d;
 }
 
+// round-to-nearest tf32 (unbiased split: the 3-pass error then grows like sqrt(K), not K)
+__device__ __forceinline__ float rna_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+
 enum { MODE_BF16 = 0, MODE_TF32X3 = 1 };
 
 template <int MODE, int BN>
@@ -255,10 +262,10 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
           const int idx = ct + i * 128;
           const float4 x = hi[idx];
           float4 h, l;
-          h.x = __uint_as_float(__float_as_uint(x.x) & 0xFFFFE000u); l.x = x.x - h.x;
-          h.y = __uint_as_float(__float_as_uint(x.y) & 0xFFFFE000u); l.y = x.y - h.y;
-          h.z = __uint_as_float(__float_as_uint(x.z) & 0xFFFFE000u); l.z = x.z - h.z;
-          h.w = __uint_as_float(__float_as_uint(x.w) & 0xFFFFE000u); l.w = x.w - h.w;
+          h.x = rna_tf32(x.x); l.x = rna_tf32(x.x - h.x);
+          h.y = rna_tf32(x.y); l.y = rna_tf32(x.y - h.y);
+          h.z = rna_tf32(x.z); l.z = rna_tf32(x.z - h.z);
+          h.w = rna_tf32(x.w); l.w = rna_tf32(x.w - h.w);
           hi[idx] = h;
           lo[idx] = l;
         }

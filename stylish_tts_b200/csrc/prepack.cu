@@ -25,9 +25,12 @@ uint16_t f2bf(float f) {
   const uint32_t r = 0x7FFFu + ((u >> 16) & 1u);
   return (uint16_t)((u + r) >> 16);
 }
+// round-to-nearest (ties away) to the 10-bit tf32 mantissa, like cvt.rna.tf32.f32: unbiased, so the
+// split error of the 3-pass product grows like sqrt(K) instead of K
 float trunc_tf32(float f) {
   uint32_t u;
   std::memcpy(&u, &f, 4);
+  if ((u & 0x7F800000u) != 0x7F800000u) u += 0x1000u;
   u &= 0xFFFFE000u;
   std::memcpy(&f, &u, 4);
   return f;

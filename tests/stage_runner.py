@@ -17,8 +17,32 @@ def _wrapdiff(a, b):
     return torch.minimum(d, (d - 2 * math.pi).abs())
 
 
-def run(precision="fp32"):
-    g = gold("tiny")
+def oracle_case(tokens, dur, seed):
+    """A golden-style dict for an arbitrary case, produced by the CPU oracle port at run time
+    (used for sizes whose intermediates are too large to commit, e.g. the 5 s C1 utterance)."""
+    from oracle import stylish_port as port
+    from stylish_tts_b200 import fixture
+    from tests.util import case_noise
+    noise = case_noise(int(dur.sum()), seed)
+    sds = fixture_sds()
+    tk, ln = tokens[None], torch.tensor([tokens.numel()])
+    taps = {}
+    with torch.no_grad():
+        ref = port.synthesize(sds, tk, ln, noise, duration=dur.float(), taps=taps)
+        ref_x0 = port.synthesize(sds, tk, ln, noise, duration=dur.float(), exact_frame0=True)
+    g = {"tokens": tokens, "duration_in": dur.to(torch.int32), "duration_pred": ref["duration"].to(torch.int32)}
+    for k in ("audio", "logamp", "phase", "pitch", "energy"):
+        g["out." + k] = ref[k].float().contiguous()
+    g["out.audio_x0"] = ref_x0["audio"].contiguous()
+    for k, v in taps.items():
+        g["tap." + k] = v.float().contiguous()
+    for k, v in noise.items():
+        g["noise." + k] = v.contiguous()
+    return g
+
+
+def run(precision="fp32", g=None, tag=""):
+    g = gold("tiny") if g is None else g
     dev = "cuda:0"
     nets = gpu_nets()
     sp, pep = nets["speech_predictor"], nets["pitch_energy_predictor"]
@@ -143,14 +167,18 @@ def run(precision="fp32"):
                 res[fn.__name__ + ".EXCEPTION"] = {"max_abs": float("inf"), "ref_absmax": 0.0, "rel": float("inf"),
                                                    "frac_gt_1e-3": 1.0, "error": repr(e)[:500]}
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
-    with open(os.path.join(ROOT, "gpurun_out", f"stages_{precision}.json"), "w") as f:
+    with open(os.path.join(ROOT, "gpurun_out", f"stages_{precision}{tag}.json"), "w") as f:
         json.dump(res, f, indent=1)
     return res
 
 
 if __name__ == "__main__":
     prec = sys.argv[1] if len(sys.argv) > 1 else "fp32"
-    out = run(prec)
+    if len(sys.argv) > 2:          # python -m tests.stage_runner fp32 c1  -> oracle-generated C1 intermediates
+        gc = gold(sys.argv[2])
+        out = run(prec, oracle_case(gc["tokens"], gc["duration_in"].to(torch.int64), int(gc["seed"])), "_" + sys.argv[2])
+    else:
+        out = run(prec)
     for k, v in out.items():
         if "error" in v:
             print(prec, k, v["error"])
