@@ -175,6 +175,105 @@ __device__ __forceinline__ void epi_apply(const Epi& e, int r, int seg, int n0, 
   }
 }
 
+// ----------------------------------------------------------------------------- coalesced epilogue
+// Lane-per-column-pair form used by the tcgen05 kernel after the accumulator tile has been
+// transposed through shared memory: one lane owns accumulator columns (n, n + 1), n even, and
+// walks down the rows of its warp's 32-row slice, so every global access of a warp is one
+// contiguous 128 / 256-byte segment of a row.  Column constants (bias, style vector) are loaded
+// once per 64-column slab.
+template <int KIND>
+struct EpiPair {
+  float b0, b1, g0, g1;
+  int n;           // even accumulator column
+  bool v0, v1;     // column n / n + 1 inside the logical N
+  __device__ __forceinline__ void init(const Epi& e, int seg, int n_) {
+    n = n_;
+    v0 = n < e.N; v1 = n + 1 < e.N;
+    b0 = (e.bias != nullptr && v0) ? e.bias[n] : 0.f;
+    b1 = (e.bias != nullptr && v1) ? e.bias[n + 1] : 0.f;
+    g0 = g1 = 0.f;
+    if constexpr (KIND == EPI_GATE) {
+      if (v0) {
+        g0 = e.segvec[(size_t)seg * e.ldseg + (n >> 1)];
+        g1 = e.segvec[(size_t)seg * e.ldseg + (e.N >> 1) + (n >> 1)];
+      }
+    }
+  }
+  static __device__ __forceinline__ void store2(float* o, __nv_bfloat16* oh, float x0, float x1, bool both) {
+    if (both) {
+      *reinterpret_cast<float2*>(o) = make_float2(x0, x1);
+      if (oh != nullptr) *reinterpret_cast<__nv_bfloat162*>(oh) = __floats2bfloat162_rn(x0, x1);
+    } else {
+      o[0] = x0;
+      if (oh != nullptr) oh[0] = __float2bfloat16_rn(x0);
+    }
+  }
+  __device__ __forceinline__ void apply(const Epi& e, int r, int seg, int seg_first_row, float a0, float a1) const {
+    if (!v0) return;
+    if constexpr (KIND == EPI_BIAS || KIND == EPI_RES_SCALE || KIND == EPI_SILU || KIND == EPI_ADD) {
+      float x0 = a0 + b0, x1 = a1 + b1;
+      if constexpr (KIND == EPI_RES_SCALE) {
+        if (e.res != nullptr) {
+          const float* rp = e.res + (size_t)r * e.ldr + e.rcol0 + n;
+          if (v1) { const float2 t = *reinterpret_cast<const float2*>(rp); x0 += t.x; x1 += t.y; }
+          else x0 += rp[0];
+        }
+        x0 *= e.scale; x1 *= e.scale;
+      }
+      if constexpr (KIND == EPI_SILU) { x0 = x0 / (1.f + expf(-x0)); x1 = x1 / (1.f + expf(-x1)); }
+      if constexpr (KIND == EPI_ADD) {
+        const float* rp = e.res + (size_t)r * e.ldr + e.rcol0 + n;
+        if (v1) { const float2 t = *reinterpret_cast<const float2*>(rp); x0 += t.x; x1 += t.y; }
+        else x0 += rp[0];
+      }
+      store2(e.out + (size_t)r * e.ldo + e.col0 + n, e.outh ? e.outh + (size_t)r * e.ldh + e.colh0 + n : nullptr, x0, x1, v1);
+    } else if constexpr (KIND == EPI_RESSKIP) {
+      const float x0 = a0 + b0, x1 = a1 + b1;
+      if (n < e.split) {
+        float* p = e.out + (size_t)r * e.ldo + e.col0 + n;
+        float y0 = p[0] + x0, y1 = v1 ? p[1] + x1 : 0.f;
+        store2(p, e.outh ? e.outh + (size_t)r * e.ldh + e.colh0 + n : nullptr, y0, y1, v1);
+      } else {
+        const int m = n - e.split;
+        float* p = e.out2 + (size_t)r * e.ldo2 + e.col20 + m;
+        float y0 = x0, y1 = x1;
+        if (e.accumulate2) { y0 += p[0]; if (v1) y1 += p[1]; }
+        store2(p, e.outh2 ? e.outh2 + (size_t)r * e.ldh2 + e.colh20 + m : nullptr, y0, y1, v1);
+      }
+    } else {
+      const int c = n >> 1;   // pair kinds: one output column per accumulator pair
+      if constexpr (KIND == EPI_GATE) {
+        const float a = a0 + b0 + g0, b = a1 + b1 + g1;
+        const float y = tanhf(a) * (1.f / (1.f + expf(-b)));
+        e.out[(size_t)r * e.ldo + e.col0 + c] = y;
+        if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = __float2bfloat16_rn(y);
+      } else if constexpr (KIND == EPI_COUPLE) {
+        const float m = a0 + b0, logs = a1 + b1;
+        float* p = e.out + (size_t)r * e.ldo + e.col0 + c;
+        const float y = (*p - m) * expf(-logs);
+        *p = y;
+        if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = __float2bfloat16_rn(y);
+      } else if constexpr (KIND == EPI_PRIOR) {
+        const float mean = a0 + b0, logstd = a1 + b1;
+        const float nz = e.res[(size_t)r * e.ldr + e.rcol0 + c];
+        const float y = mean + nz * expf(logstd);
+        e.out[(size_t)r * e.ldo + e.col0 + c] = y;
+        if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = __float2bfloat16_rn(y);
+      } else if constexpr (KIND == EPI_STFT) {
+        // frame 0 of an utterance is exactly real (see epi_apply)
+        const float re = a0, im = (r == seg_first_row) ? 0.f : a1;
+        const float mag = hypotf(re, im);
+        const float d = mag + 1e-9f;
+        const float ph = atan2f(im / d, re / d);
+        e.out[(size_t)r * e.ldo + e.col0 + c] = mag;
+        e.out2[(size_t)r * e.ldo2 + e.col20 + c] = ph;
+        if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = __float2bfloat16_rn(mag);
+        if (e.outh2 != nullptr) e.outh2[(size_t)r * e.ldh2 + e.colh20 + c] = __float2bfloat16_rn(ph);
+      }
+    }
+  }
+};
+
 // ----------------------------------------------------------------------------- conv-as-GEMM
 // Y[r, n] = sum_s sum_j sum_c A_s[r + j - pad_s, col0_s + c] * W[n, koff_s + j * cin_pad_s + c]
 // Up to two K-segments (fused 1x1 shortcut, channel concatenation across buffers).

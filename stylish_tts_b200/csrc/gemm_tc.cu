@@ -105,6 +105,25 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
   for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
 
+// 64 consecutive accumulator columns of this thread's TMEM lane (4 x 32x32b.x16, one wait)
+__device__ __forceinline__ void tmem_ld64(uint32_t taddr, float* v) {
+  uint32_t r[64];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(r[16 * i + 0]), "=r"(r[16 * i + 1]), "=r"(r[16 * i + 2]), "=r"(r[16 * i + 3]), "=r"(r[16 * i + 4]),
+          "=r"(r[16 * i + 5]), "=r"(r[16 * i + 6]), "=r"(r[16 * i + 7]), "=r"(r[16 * i + 8]), "=r"(r[16 * i + 9]),
+          "=r"(r[16 * i + 10]), "=r"(r[16 * i + 11]), "=r"(r[16 * i + 12]), "=r"(r[16 * i + 13]),
+          "=r"(r[16 * i + 14]), "=r"(r[16 * i + 15])
+        : "r"(taddr + 16u * i));
+  }
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 64; ++i) v[i] = __uint_as_float(r[i]);
+}
+constexpr int kStgLd = 66;   // staging row stride in floats (even: float2 aligned; 66 % 32 = 2: conflict-free 64-bit)
+
 // K-major, 128-byte-swizzled shared-memory matrix descriptor (cute::UMMA::SmemDescriptor layout):
 // start>>4 [0,14) | LBO>>4 [16,30) | SBO>>4 [32,46) | version=1 [46,48) | layout SWIZZLE_128B=2 [61,64)
 __device__ __forceinline__ uint64_t make_sdesc(uint32_t smem_addr) {
@@ -277,16 +296,31 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
     }
     mbar_wait(accum, 0, 5);
     tc_fence_after();
+    // All TMA writes and all MMAs of this CTA have completed: the pipeline stages are free and are
+    // reused as the transpose staging area (4 warps x 32 rows x 66 floats).
     const int q = warp & 3;                    // TMEM lane quarter this warp may access
-    const int lr = q * 32 + lane;
-    const int r = m0 + lr;
-    const bool valid = lr < nvalid;
+    float* stg = reinterpret_cast<float*>(smem) + q * (32 * kStgLd);
+    const int row0 = m0 + q * 32;
+    int nrows = nvalid - q * 32;
+    nrows = nrows < 0 ? 0 : (nrows > 32 ? 32 : nrows);
+    const int seg_first = (epi.seg_start != nullptr) ? epi.seg_start[seg] : -1;
 #pragma unroll 1
-    for (int c = 0; c < BN; c += 16) {
+    for (int c = 0; c < BN; c += 64) {
       if (n0 + c >= epi.N) break;              // warp-uniform
-      float v[16];
-      tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c, v);
-      if (valid) epi_apply<KIND, 16>(epi, r, seg, n0 + c, v);
+      float v[64];
+      tmem_ld64(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c, v);
+      __syncwarp();                            // previous slab fully consumed
+#pragma unroll
+      for (int j = 0; j < 64; j += 2)
+        *reinterpret_cast<float2*>(stg + lane * kStgLd + j) = make_float2(v[j], v[j + 1]);
+      __syncwarp();
+      EpiPair<KIND> ep;
+      ep.init(epi, seg, n0 + c + 2 * lane);
+#pragma unroll 4
+      for (int rr = 0; rr < nrows; ++rr) {
+        const float2 a = *reinterpret_cast<const float2*>(stg + rr * kStgLd + 2 * lane);
+        ep.apply(epi, row0 + rr, seg, seg_first, a.x, a.y);
+      }
     }
     tc_fence_before();
   }
