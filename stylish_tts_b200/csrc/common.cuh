@@ -199,6 +199,33 @@ struct EpiPair {
       }
     }
   }
+  // Kinds that read memory (residual / read-modify-write) prefetch it for all rows of the slab
+  // before the accumulators are touched: 32 independent 256-byte loads in flight per warp.
+  static constexpr bool kHasPre = (KIND == EPI_RES_SCALE || KIND == EPI_ADD || KIND == EPI_RESSKIP ||
+                                   KIND == EPI_COUPLE || KIND == EPI_PRIOR);
+  __device__ __forceinline__ float2 pre(const Epi& e, int r) const {
+    float2 t = make_float2(0.f, 0.f);
+    if (!v0) return t;
+    if constexpr (KIND == EPI_RES_SCALE || KIND == EPI_ADD) {
+      if (e.res != nullptr) {
+        const float* rp = e.res + (size_t)r * e.ldr + e.rcol0 + n;
+        if (v1) t = *reinterpret_cast<const float2*>(rp); else t.x = rp[0];
+      }
+    } else if constexpr (KIND == EPI_RESSKIP) {
+      if (n < e.split) {
+        const float* p = e.out + (size_t)r * e.ldo + e.col0 + n;
+        if (v1) t = *reinterpret_cast<const float2*>(p); else t.x = p[0];
+      } else if (e.accumulate2) {
+        const float* p = e.out2 + (size_t)r * e.ldo2 + e.col20 + (n - e.split);
+        if (v1) t = *reinterpret_cast<const float2*>(p); else t.x = p[0];
+      }
+    } else if constexpr (KIND == EPI_COUPLE) {
+      t.x = e.out[(size_t)r * e.ldo + e.col0 + (n >> 1)];
+    } else if constexpr (KIND == EPI_PRIOR) {
+      t.x = e.res[(size_t)r * e.ldr + e.rcol0 + (n >> 1)];
+    }
+    return t;
+  }
   static __device__ __forceinline__ void store2(float* o, __nv_bfloat16* oh, float x0, float x1, bool both) {
     if (both) {
       *reinterpret_cast<float2*>(o) = make_float2(x0, x1);
@@ -208,36 +235,27 @@ struct EpiPair {
       if (oh != nullptr) oh[0] = __float2bfloat16_rn(x0);
     }
   }
-  __device__ __forceinline__ void apply(const Epi& e, int r, int seg, int seg_first_row, float a0, float a1) const {
+  __device__ __forceinline__ void apply(const Epi& e, int r, int seg, int seg_first_row, float a0, float a1,
+                                        float2 t) const {
     if (!v0) return;
     if constexpr (KIND == EPI_BIAS || KIND == EPI_RES_SCALE || KIND == EPI_SILU || KIND == EPI_ADD) {
       float x0 = a0 + b0, x1 = a1 + b1;
       if constexpr (KIND == EPI_RES_SCALE) {
-        if (e.res != nullptr) {
-          const float* rp = e.res + (size_t)r * e.ldr + e.rcol0 + n;
-          if (v1) { const float2 t = *reinterpret_cast<const float2*>(rp); x0 += t.x; x1 += t.y; }
-          else x0 += rp[0];
-        }
-        x0 *= e.scale; x1 *= e.scale;
+        x0 = (x0 + t.x) * e.scale; x1 = (x1 + t.y) * e.scale;
       }
       if constexpr (KIND == EPI_SILU) { x0 = x0 / (1.f + expf(-x0)); x1 = x1 / (1.f + expf(-x1)); }
-      if constexpr (KIND == EPI_ADD) {
-        const float* rp = e.res + (size_t)r * e.ldr + e.rcol0 + n;
-        if (v1) { const float2 t = *reinterpret_cast<const float2*>(rp); x0 += t.x; x1 += t.y; }
-        else x0 += rp[0];
-      }
+      if constexpr (KIND == EPI_ADD) { x0 += t.x; x1 += t.y; }
       store2(e.out + (size_t)r * e.ldo + e.col0 + n, e.outh ? e.outh + (size_t)r * e.ldh + e.colh0 + n : nullptr, x0, x1, v1);
     } else if constexpr (KIND == EPI_RESSKIP) {
       const float x0 = a0 + b0, x1 = a1 + b1;
       if (n < e.split) {
         float* p = e.out + (size_t)r * e.ldo + e.col0 + n;
-        float y0 = p[0] + x0, y1 = v1 ? p[1] + x1 : 0.f;
+        const float y0 = t.x + x0, y1 = t.y + x1;
         store2(p, e.outh ? e.outh + (size_t)r * e.ldh + e.colh0 + n : nullptr, y0, y1, v1);
       } else {
         const int m = n - e.split;
         float* p = e.out2 + (size_t)r * e.ldo2 + e.col20 + m;
-        float y0 = x0, y1 = x1;
-        if (e.accumulate2) { y0 += p[0]; if (v1) y1 += p[1]; }
+        const float y0 = x0 + t.x, y1 = x1 + t.y;   // t = 0 when not accumulating
         store2(p, e.outh2 ? e.outh2 + (size_t)r * e.ldh2 + e.colh20 + m : nullptr, y0, y1, v1);
       }
     } else {
@@ -250,13 +268,12 @@ struct EpiPair {
       } else if constexpr (KIND == EPI_COUPLE) {
         const float m = a0 + b0, logs = a1 + b1;
         float* p = e.out + (size_t)r * e.ldo + e.col0 + c;
-        const float y = (*p - m) * expf(-logs);
+        const float y = (t.x - m) * expf(-logs);
         *p = y;
         if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = __float2bfloat16_rn(y);
       } else if constexpr (KIND == EPI_PRIOR) {
         const float mean = a0 + b0, logstd = a1 + b1;
-        const float nz = e.res[(size_t)r * e.ldr + e.rcol0 + c];
-        const float y = mean + nz * expf(logstd);
+        const float y = mean + t.x * expf(logstd);
         e.out[(size_t)r * e.ldo + e.col0 + c] = y;
         if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = __float2bfloat16_rn(y);
       } else if constexpr (KIND == EPI_STFT) {

@@ -307,19 +307,39 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
 #pragma unroll 1
     for (int c = 0; c < BN; c += 64) {
       if (n0 + c >= epi.N) break;              // warp-uniform
-      float v[64];
-      tmem_ld64(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c, v);
-      __syncwarp();                            // previous slab fully consumed
-#pragma unroll
-      for (int j = 0; j < 64; j += 2)
-        *reinterpret_cast<float2*>(stg + lane * kStgLd + j) = make_float2(v[j], v[j + 1]);
-      __syncwarp();
       EpiPair<KIND> ep;
       ep.init(epi, seg, n0 + c + 2 * lane);
-#pragma unroll 4
-      for (int rr = 0; rr < nrows; ++rr) {
-        const float2 a = *reinterpret_cast<const float2*>(stg + rr * kStgLd + 2 * lane);
-        ep.apply(epi, row0 + rr, seg, seg_first, a.x, a.y);
+      {
+        float v[64];
+        tmem_ld64(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c, v);
+        __syncwarp();                            // previous slab fully consumed
+#pragma unroll
+        for (int j = 0; j < 64; j += 2)
+          *reinterpret_cast<float2*>(stg + lane * kStgLd + j) = make_float2(v[j], v[j + 1]);
+      }
+      __syncwarp();
+      if constexpr (EpiPair<KIND>::kHasPre) {
+        // two batches of 16 rows: 16 independent row loads in flight per warp, registers bounded
+#pragma unroll 1
+        for (int rb = 0; rb < 32; rb += 16) {
+          float2 pre[16];
+#pragma unroll
+          for (int rr = 0; rr < 16; ++rr)
+            if (rb + rr < nrows) pre[rr] = ep.pre(epi, row0 + rb + rr);
+#pragma unroll
+          for (int rr = 0; rr < 16; ++rr) {
+            if (rb + rr < nrows) {
+              const float2 a = *reinterpret_cast<const float2*>(stg + (rb + rr) * kStgLd + 2 * lane);
+              ep.apply(epi, row0 + rb + rr, seg, seg_first, a.x, a.y, pre[rr]);
+            }
+          }
+        }
+      } else {
+#pragma unroll 8
+        for (int rr = 0; rr < nrows; ++rr) {
+          const float2 a = *reinterpret_cast<const float2*>(stg + rr * kStgLd + 2 * lane);
+          ep.apply(epi, row0 + rr, seg, seg_first, a.x, a.y, make_float2(0.f, 0.f));
+        }
       }
     }
     tc_fence_before();

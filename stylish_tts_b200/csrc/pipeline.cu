@@ -5,7 +5,10 @@
 //   generator.py:402-438;  PitchEnergyPredictor towers pitch_energy_predictor.py:111-119.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
+
+#include <cuda_profiler_api.h>
 
 #include "engine.h"
 
@@ -259,9 +262,15 @@ int run_gemm(Context& c, const PackedGemm& pg, int cls, const Act* a0, int a0_co
     pr.flops = 2.0 * (double)map_valid_rows * (double)pg.N * pg.k_real;
     cudaEventRecord(pr.e0, st);
   }
+  // STTS_PROFILE_LAYER=<layer name>: bracket only that layer with cudaProfilerStart/Stop so that
+  // `ncu --profile-from-start off` captures exactly one named GEMM (tools/profile_step.py layer mode)
+  static const char* prof_layer = std::getenv("STTS_PROFILE_LAYER");
+  const bool bracket = prof_layer != nullptr && pg.name == prof_layer;
+  if (bracket) { cudaStreamSynchronize(st); cudaProfilerStart(); }
   if (backend == 0) e = conv_gemm_simt(g, map, st);
   else if (backend == 1) e = conv_gemm_tc_bf16(g, map, st);
   else e = conv_gemm_tc_tf32x3(g, map, st);
+  if (bracket) { cudaStreamSynchronize(st); cudaProfilerStop(); }
   if (e != cudaSuccess) return cuda_fail(c, e, "conv_gemm launch");
   if (c.prof_on) { cudaEventRecord(pr.e1, st); c.prof.push_back(pr); }
   c.launches++;
