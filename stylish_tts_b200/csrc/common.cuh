@@ -181,8 +181,13 @@ __device__ __forceinline__ void epi_apply(const Epi& e, int r, int seg, int n0, 
 // walks down the rows of its warp's 32-row slice, so every global access of a warp is one
 // contiguous 128 / 256-byte segment of a row.  Column constants (bias, style vector) are loaded
 // once per 64-column slab.
-template <int KIND>
+template <int KIND, bool FAST>
 struct EpiPair {
+  static __device__ __forceinline__ float ex(float x) { if constexpr (FAST) return __expf(x); else return expf(x); }
+  static __device__ __forceinline__ float th(float x) {
+    if constexpr (FAST) { float y; asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; } else return tanhf(x);
+  }
+  static __device__ __forceinline__ float dv(float a, float b) { if constexpr (FAST) return __fdividef(a, b); else return a / b; }
   float b0, b1, g0, g1;
   int n;           // even accumulator column
   bool v0, v1;     // column n / n + 1 inside the logical N
@@ -243,7 +248,7 @@ struct EpiPair {
       if constexpr (KIND == EPI_RES_SCALE) {
         x0 = (x0 + t.x) * e.scale; x1 = (x1 + t.y) * e.scale;
       }
-      if constexpr (KIND == EPI_SILU) { x0 = x0 / (1.f + expf(-x0)); x1 = x1 / (1.f + expf(-x1)); }
+      if constexpr (KIND == EPI_SILU) { x0 = dv(x0, 1.f + ex(-x0)); x1 = dv(x1, 1.f + ex(-x1)); }
       if constexpr (KIND == EPI_ADD) { x0 += t.x; x1 += t.y; }
       store2(e.out + (size_t)r * e.ldo + e.col0 + n, e.outh ? e.outh + (size_t)r * e.ldh + e.colh0 + n : nullptr, x0, x1, v1);
     } else if constexpr (KIND == EPI_RESSKIP) {
@@ -262,18 +267,18 @@ struct EpiPair {
       const int c = n >> 1;   // pair kinds: one output column per accumulator pair
       if constexpr (KIND == EPI_GATE) {
         const float a = a0 + b0 + g0, b = a1 + b1 + g1;
-        const float y = tanhf(a) * (1.f / (1.f + expf(-b)));
+        const float y = th(a) * dv(1.f, 1.f + ex(-b));
         e.out[(size_t)r * e.ldo + e.col0 + c] = y;
         if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = __float2bfloat16_rn(y);
       } else if constexpr (KIND == EPI_COUPLE) {
         const float m = a0 + b0, logs = a1 + b1;
         float* p = e.out + (size_t)r * e.ldo + e.col0 + c;
-        const float y = (t.x - m) * expf(-logs);
+        const float y = (t.x - m) * ex(-logs);
         *p = y;
         if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = __float2bfloat16_rn(y);
       } else if constexpr (KIND == EPI_PRIOR) {
         const float mean = a0 + b0, logstd = a1 + b1;
-        const float y = mean + t.x * expf(logstd);
+        const float y = mean + t.x * ex(logstd);
         e.out[(size_t)r * e.ldo + e.col0 + c] = y;
         if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = __float2bfloat16_rn(y);
       } else if constexpr (KIND == EPI_STFT) {

@@ -75,28 +75,37 @@ cudaError_t colstats(const float* x, int ld, int C, const RowMap& map, int mode,
 __global__ void __launch_bounds__(128) style_fc_kernel(const float* __restrict__ W, const float* __restrict__ bias,
                                                        const float* __restrict__ s, int J, int K, int B,
                                                        float* __restrict__ out) {
-  extern __shared__ float sh[];  // [B, K]
-  for (int i = threadIdx.x; i < B * K; i += blockDim.x) sh[i] = s[i];
+  extern __shared__ float sh[];  // W tile [128][K + 1] (coalesced load, conflict-free rows) + s [B, K]
+  float* sw = sh;
+  float* ss = sh + 128 * (K + 1);
+  const int j0 = blockIdx.x * 128;
+  const int nj = (J - j0 < 128) ? (J - j0) : 128;
+  for (int i = threadIdx.x; i < nj * K; i += 128) {
+    const int row = i / K, col = i - row * K;
+    sw[row * (K + 1) + col] = W[(size_t)j0 * K + i];
+  }
+  for (int i = threadIdx.x; i < B * K; i += 128) ss[i] = s[i];
   __syncthreads();
-  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = j0 + threadIdx.x;
   if (j >= J) return;
-  const float* w = W + (size_t)j * K;
+  const float* w = sw + threadIdx.x * (K + 1);
   const float bj = bias[j];
   for (int b = 0; b < B; ++b) {
     float acc = 0.f;
-    for (int k = 0; k < K; ++k) acc = fmaf(w[k], sh[b * K + k], acc);
+    for (int k = 0; k < K; ++k) acc = fmaf(w[k], ss[b * K + k], acc);
     out[(size_t)b * J + j] = acc + bj;
   }
 }
 
 cudaError_t style_fc(const float* W, const float* bias, const float* s, int J, int K, int B, float* out,
                      cudaStream_t st) {
-  // B*K floats of shared memory; chunk the batch so it always fits in 48 KB
-  const int maxB = 12288 / K;
+  // chunk the batch so W tile + style rows fit in 48 KB of shared memory
+  const int maxB = (48 * 1024 - 128 * (K + 1) * (int)sizeof(float)) / (K * (int)sizeof(float));
+  if (maxB < 1) return cudaErrorInvalidValue;
   for (int b0 = 0; b0 < B; b0 += maxB) {
     const int nb = (B - b0 < maxB) ? (B - b0) : maxB;
-    style_fc_kernel<<<(J + 127) / 128, 128, (size_t)nb * K * sizeof(float), st>>>(W, bias, s + (size_t)b0 * K, J, K, nb,
-                                                                                  out + (size_t)b0 * J);
+    const size_t smem = (size_t)(128 * (K + 1) + nb * K) * sizeof(float);
+    style_fc_kernel<<<(J + 127) / 128, 128, smem, st>>>(W, bias, s + (size_t)b0 * K, J, K, nb, out + (size_t)b0 * J);
   }
   return cudaGetLastError();
 }
@@ -104,44 +113,44 @@ cudaError_t style_fc(const float* W, const float* bias, const float* s, int J, i
 // ============================================================================ AdaIN + LeakyReLU
 // y = leaky_relu((1 + gamma) * (x - mean) * rstd + beta, 0.2)      ada_norm.py:135-139,170-176
 // gb is the style-FC output row of this norm: gamma = gb[seg, 0:C], beta = gb[seg, C:2C].
+// grid (tile, channel chunk of 128); thread = (row group 0..3, channel pair 0..63): every warp access
+// is 256 contiguous bytes of one row; per-channel constants live in registers.  C is even.
 __global__ void __launch_bounds__(256) adain_act_kernel(const float* __restrict__ x, int ldx, int C, RowMap map,
                                                         const float* __restrict__ mean, const float* __restrict__ rstd,
                                                         const float* __restrict__ gb, int ldgb, float slope,
                                                         float* __restrict__ y, int ldy, __nv_bfloat16* __restrict__ yh,
                                                         int ldyh) {
-  extern __shared__ float sh[];  // mean[C], scale[C], beta[C]
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
   if (seg < 0) return;
   const int nvalid = map.tile_nvalid[tile];
-  float* s_mean = sh;
-  float* s_scale = sh + C;
-  float* s_beta = sh + 2 * C;
-  for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    s_mean[c] = mean[(size_t)seg * C + c];
-    s_scale[c] = rstd[(size_t)seg * C + c];
-    s_beta[c] = gb[(size_t)seg * ldgb + C + c];
-  }
-  __syncthreads();
+  const int c = blockIdx.y * 128 + 2 * (threadIdx.x & 63);
+  if (c >= C) return;
+  const int rg = threadIdx.x >> 6;
+  const float2 mu = *reinterpret_cast<const float2*>(mean + (size_t)seg * C + c);
+  const float2 rs = *reinterpret_cast<const float2*>(rstd + (size_t)seg * C + c);
   const float* g = gb + (size_t)seg * ldgb;
-  const int total = nvalid * C;
+  const float ga0 = 1.f + g[c], ga1 = 1.f + g[c + 1], be0 = g[C + c], be1 = g[C + c + 1];
   const size_t base = (size_t)tile * 128;
-  for (int i = threadIdx.x; i < total; i += blockDim.x) {
-    const int lr = i / C, c = i - lr * C;
+#pragma unroll 4
+  for (int lr = rg; lr < nvalid; lr += 4) {
     const size_t r = base + lr;
-    const float n = (x[r * ldx + c] - s_mean[c]) * s_scale[c];
-    float v = (1.f + g[c]) * n + s_beta[c];
-    v = v > 0.f ? v : v * slope;
-    y[r * ldy + c] = v;
-    if (yh != nullptr) yh[r * ldyh + c] = __float2bfloat16_rn(v);
+    const float2 v = *reinterpret_cast<const float2*>(x + r * ldx + c);
+    float a = ga0 * ((v.x - mu.x) * rs.x) + be0;
+    float b = ga1 * ((v.y - mu.y) * rs.y) + be1;
+    a = a > 0.f ? a : a * slope;
+    b = b > 0.f ? b : b * slope;
+    *reinterpret_cast<float2*>(y + r * ldy + c) = make_float2(a, b);
+    if (yh != nullptr) *reinterpret_cast<__nv_bfloat162*>(yh + r * ldyh + c) = __floats2bfloat162_rn(a, b);
   }
 }
 
 cudaError_t adain_act(const float* x, int ldx, int C, const RowMap& map, const float* mean, const float* rstd,
                       const float* gb, int ldgb, float slope, float* y, int ldy, __nv_bfloat16* yh, int ldyh,
                       cudaStream_t st) {
-  adain_act_kernel<<<map.n_tiles, 256, 3 * C * sizeof(float), st>>>(x, ldx, C, map, mean, rstd, gb, ldgb, slope, y, ldy,
-                                                                    yh, ldyh);
+  if ((C & 1) || (ldx & 1) || (ldy & 1) || (ldgb & 1)) return cudaErrorInvalidValue;
+  dim3 grid(map.n_tiles, (C + 127) / 128);
+  adain_act_kernel<<<grid, 256, 0, st>>>(x, ldx, C, map, mean, rstd, gb, ldgb, slope, y, ldy, yh, ldyh);
   return cudaGetLastError();
 }
 

@@ -156,6 +156,8 @@ struct Cfg {
   static constexpr int kStageBytes = kTF32 ? (2 * kATile + 2 * kBTile) : (kATile + kBTile);
   static constexpr int kStages = kTF32 ? (BN == 128 ? 3 : 2) : (BN == 128 ? 6 : 4);
   static constexpr int kTxBytes = kTF32 ? (kATile + 2 * kBTile) : (kATile + kBTile);
+  static constexpr int kEpiWarps = BN / 16;                // one 64-column slab x 32-row quarter per warp
+  static constexpr int kThreads = 64 + 32 * kEpiWarps;
   static constexpr int kSmem = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
   static constexpr uint32_t kIdesc = (1u << 4) | ((kTF32 ? 2u : 1u) << 7) | ((kTF32 ? 2u : 1u) << 10) |
                                      ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
@@ -168,7 +170,7 @@ struct TcParams {
 };
 
 template <int MODE, int BN, int KIND>
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(64 + 2 * BN, 1)
 conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant__ CUtensorMap mapA1,
                     const __grid_constant__ CUtensorMap mapW, const __grid_constant__ CUtensorMap mapWlo,
                     const TcParams p, const Epi epi, const RowMap map) {
@@ -194,7 +196,7 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
     for (int s = 0; s < C::kStages; ++s) {
       mbar_init(&full[s], 1);
       mbar_init(&empty[s], 1);
-      mbar_init(&conv[s], 4);
+      mbar_init(&conv[s], C::kEpiWarps);
     }
     mbar_init(accum, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -269,7 +271,8 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
   } else {
     // ------------------------------------------------------------ converter (tf32x3) + epilogue
     if constexpr (C::kTF32) {
-      const int ct = threadIdx.x - 64;  // 0..127
+      const int ct = threadIdx.x - 64;  // 0 .. 32 * kEpiWarps - 1
+      constexpr int kConvThreads = 32 * C::kEpiWarps;
       int stage = 0;
       uint32_t phase = 0;
       for (int ch = 0; ch < p.n_chunks; ++ch) {
@@ -277,8 +280,8 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
         float4* hi = reinterpret_cast<float4*>(stage_ptr(stage));
         float4* lo = reinterpret_cast<float4*>(stage_ptr(stage) + C::kATile);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int idx = ct + i * 128;
+        for (int i = 0; i < 1024 / kConvThreads; ++i) {
+          const int idx = ct + i * kConvThreads;
           const float4 x = hi[idx];
           float4 h, l;
           h.x = rna_tf32(x.x); l.x = rna_tf32(x.x - h.x);
@@ -297,17 +300,18 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
     mbar_wait(accum, 0, 5);
     tc_fence_after();
     // All TMA writes and all MMAs of this CTA have completed: the pipeline stages are free and are
-    // reused as the transpose staging area (4 warps x 32 rows x 66 floats).
-    const int q = warp & 3;                    // TMEM lane quarter this warp may access
-    float* stg = reinterpret_cast<float*>(smem) + q * (32 * kStgLd);
+    // reused as the transpose staging area (one 32 x 66-float block per epilogue warp).  Warp ew
+    // owns TMEM lane quarter q = warp % 4 (hardware rule) and the 64-column slab ew / 4.
+    const int ew = warp - 2;
+    const int q = warp & 3;
+    float* stg = reinterpret_cast<float*>(smem) + ew * (32 * kStgLd);
     const int row0 = m0 + q * 32;
     int nrows = nvalid - q * 32;
     nrows = nrows < 0 ? 0 : (nrows > 32 ? 32 : nrows);
     const int seg_first = (epi.seg_start != nullptr) ? epi.seg_start[seg] : -1;
-#pragma unroll 1
-    for (int c = 0; c < BN; c += 64) {
-      if (n0 + c >= epi.N) break;              // warp-uniform
-      EpiPair<KIND> ep;
+    const int c = (ew >> 2) * 64;
+    if (n0 + c < epi.N) {                      // warp-uniform
+      EpiPair<KIND, MODE == MODE_BF16> ep;
       ep.init(epi, seg, n0 + c + 2 * lane);
       {
         float v[64];
@@ -318,7 +322,7 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
           *reinterpret_cast<float2*>(stg + lane * kStgLd + j) = make_float2(v[j], v[j + 1]);
       }
       __syncwarp();
-      if constexpr (EpiPair<KIND>::kHasPre) {
+      if constexpr (EpiPair<KIND, false>::kHasPre) {
         // two batches of 16 rows: 16 independent row loads in flight per warp, registers bounded
 #pragma unroll 1
         for (int rb = 0; rb < 32; rb += 16) {
@@ -439,7 +443,7 @@ cudaError_t launch_one(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
     attr_done = true;
   }
   dim3 grid((g.epi.N + BN - 1) / BN, map.n_tiles);
-  kern<<<grid, 192, C::kSmem, st>>>(mA[0], mA[1], mW, mWlo, p, g.epi, map);
+  kern<<<grid, C::kThreads, C::kSmem, st>>>(mA[0], mA[1], mW, mWlo, p, g.epi, map);
   return cudaGetLastError();
 }
 
