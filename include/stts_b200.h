@@ -67,6 +67,17 @@ int stts_set_precision(stts_ctx* ctx, int precision);
 int stts_set_layout(stts_ctx* ctx, int n_seg, const int* len_f, const int* len_f4);
 int64_t stts_workspace_bytes(const stts_ctx* ctx);
 
+/* ---- token-rate encoders ------------------------------------------------------------------------
+ * len_t[b] = phoneme tokens of utterance b (pad tokens included, like text_lengths).              */
+int stts_set_token_layout(stts_ctx* ctx, int n_seg, const int* len_t);
+/* TextEncoder.forward, text_encoder.py:433-462.  which: "speech_predictor" (its text_encoder.*),
+ * "pe_text_encoder", "duration_predictor" (its text_encoder.*) -- the module the weights were
+ * loaded under.  d_tokens int32 [sum T] (utterances concatenated).  Outputs, token-major dense and
+ * either may be NULL: d_mu_tok [sum T, inter_dim] (= mu.transpose(1,2)), d_x_tok [sum T, 128].
+ * Always fp32-grade arithmetic (the duration logits decide integer durations).                     */
+int stts_text_encoder(stts_ctx* ctx, const char* which, const int32_t* d_tokens, float* d_mu_tok,
+                      float* d_x_tok, void* stream);
+
 /* ---- length regulation ------------------------------------------------------------------------
  * DurationProcessor.prediction_to_duration, utils.py:468-474: logits [n_tokens,16] -> int32.    */
 int stts_durations(stts_ctx* ctx, const float* d_logits, int n_tokens, int32_t* d_dur, void* stream);

@@ -44,6 +44,7 @@ void stts_destroy(stts_ctx* ctx) {
   cudaDeviceSynchronize();
   for (void* p : ctx->c.weight_allocs) cudaFree(p);
   if (ctx->c.arena) cudaFree(ctx->c.arena);
+  if (ctx->c.tarena) cudaFree(ctx->c.tarena);
   if (ctx->c.h_meta) cudaFreeHost(ctx->c.h_meta);
   delete ctx;
 }
@@ -73,6 +74,23 @@ int stts_set_precision(stts_ctx* ctx, int precision) {
   if (!ctx || precision < 0 || precision > 2) return STTS_ERR_BAD_ARG;
   ctx->c.precision = precision;
   return STTS_OK;
+}
+
+int stts_set_token_layout(stts_ctx* ctx, int n_seg, const int* len_t) {
+  if (!ctx) return STTS_ERR_BAD_ARG;
+  DeviceGuard g(ctx->c.device);
+  return set_token_layout(ctx->c, n_seg, len_t);
+}
+
+int stts_text_encoder(stts_ctx* ctx, const char* which, const int32_t* d_tokens, float* d_mu_tok, float* d_x_tok,
+                      void* stream) {
+  if (!ctx || !which || !d_tokens) return STTS_ERR_BAD_ARG;
+  DeviceGuard g(ctx->c.device);
+  const std::string w(which);
+  const char* nm = w == "speech_predictor" ? "te.sp" : (w == "pe_text_encoder" ? "te.pe"
+                   : (w == "duration_predictor" ? "te.dp" : nullptr));
+  if (nm == nullptr) return fail(ctx->c, STTS_ERR_BAD_ARG, "stts_text_encoder: unknown module " + w);
+  return run_text_encoder(ctx->c, nm, d_tokens, d_mu_tok, d_x_tok, S(stream));
 }
 
 int stts_set_layout(stts_ctx* ctx, int n_seg, const int* len_f, const int* len_f4) {

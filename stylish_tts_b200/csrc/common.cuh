@@ -39,6 +39,8 @@ enum EpiKind : int {
   EPI_COUPLE = 6,      // out[i] = (out[i] - m_i) * exp(-logs_i), (m,logs) interleaved (flow.py:210-213)
   EPI_PRIOR = 7,       // out[i] = mean_i + noise[i] * exp(logstd_i)               (flow.py:311-315)
   EPI_STFT = 8,        // (re,im) interleaved -> out = |X|, out2 = atan2            (generator.py:32-44,407-410)
+  EPI_RELU = 9,        // out = relu(acc + bias)                    (FFN conv_1, text_encoder.py:305-329)
+  EPI_GELU = 10,       // out = gelu(acc + bias), exact erf form   (BasicConvNeXtBlock, conv_next.py:18-51)
 };
 
 struct Epi {
@@ -63,7 +65,8 @@ __device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + __expf
 // (n0 % NV == 0, NV even).  Shared by the SIMT and the tcgen05 kernels.
 template <int KIND, int NV>
 __device__ __forceinline__ void epi_apply(const Epi& e, int r, int seg, int n0, const float* acc) {
-  if constexpr (KIND == EPI_BIAS || KIND == EPI_RES_SCALE || KIND == EPI_SILU || KIND == EPI_ADD) {
+  if constexpr (KIND == EPI_BIAS || KIND == EPI_RES_SCALE || KIND == EPI_SILU || KIND == EPI_ADD ||
+                KIND == EPI_RELU || KIND == EPI_GELU) {
     float v[NV];
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
@@ -74,6 +77,8 @@ __device__ __forceinline__ void epi_apply(const Epi& e, int r, int seg, int n0, 
         x *= e.scale;
       }
       if constexpr (KIND == EPI_SILU) x = x / (1.f + expf(-x));
+      if constexpr (KIND == EPI_RELU) x = fmaxf(x, 0.f);
+      if constexpr (KIND == EPI_GELU) x = 0.5f * x * (1.f + erff(x * 0.70710678118654752440f));
       if constexpr (KIND == EPI_ADD) {
         if (n < e.N) x += e.res[(size_t)r * e.ldr + e.rcol0 + n];
       }
@@ -243,13 +248,19 @@ struct EpiPair {
   __device__ __forceinline__ void apply(const Epi& e, int r, int seg, int seg_first_row, float a0, float a1,
                                         float2 t) const {
     if (!v0) return;
-    if constexpr (KIND == EPI_BIAS || KIND == EPI_RES_SCALE || KIND == EPI_SILU || KIND == EPI_ADD) {
+    if constexpr (KIND == EPI_BIAS || KIND == EPI_RES_SCALE || KIND == EPI_SILU || KIND == EPI_ADD ||
+                  KIND == EPI_RELU || KIND == EPI_GELU) {
       float x0 = a0 + b0, x1 = a1 + b1;
       if constexpr (KIND == EPI_RES_SCALE) {
         x0 = (x0 + t.x) * e.scale; x1 = (x1 + t.y) * e.scale;
       }
       if constexpr (KIND == EPI_SILU) { x0 = dv(x0, 1.f + ex(-x0)); x1 = dv(x1, 1.f + ex(-x1)); }
       if constexpr (KIND == EPI_ADD) { x0 += t.x; x1 += t.y; }
+      if constexpr (KIND == EPI_RELU) { x0 = fmaxf(x0, 0.f); x1 = fmaxf(x1, 0.f); }
+      if constexpr (KIND == EPI_GELU) {
+        x0 = 0.5f * x0 * (1.f + erff(x0 * 0.70710678118654752440f));
+        x1 = 0.5f * x1 * (1.f + erff(x1 * 0.70710678118654752440f));
+      }
       store2(e.out + (size_t)r * e.ldo + e.col0 + n, e.outh ? e.outh + (size_t)r * e.ldh + e.colh0 + n : nullptr, x0, x1, v1);
     } else if constexpr (KIND == EPI_RESSKIP) {
       const float x0 = a0 + b0, x1 = a1 + b1;

@@ -72,6 +72,13 @@ struct Context {
 
   // ---- layouts + workspace
   Layout L4, LF;
+  // token-rate layout + its own arena (stts_set_token_layout)
+  Layout LT;
+  std::vector<int> tsig;
+  char* tarena = nullptr; size_t tarena_bytes = 0;
+  std::map<std::string, Act> tact;
+  std::map<std::string, void*> traw;
+  int max_t = 0;
   std::vector<int> sig;                        // layout signature
   char* arena = nullptr; size_t arena_bytes = 0, arena_used = 0;
   std::map<std::string, Act> act;              // named activation buffers
@@ -93,6 +100,7 @@ PackedGemm pack_from_conv_weight(Context& c, const float* w, const float* bias, 
 void free_pack(PackedGemm& p);
 
 // pipeline.cu
+void build_layout(Layout& L, int n_seg, const int* len);
 int set_layout(Context& c, int n_seg, const int* len_f, const int* len_f4);
 int run_gemm(Context& c, const PackedGemm& pg, int cls, const Act* a0, int a0_col, const Act* a1, int a1_col,
              const Epi& epi, const RowMap& map, cudaStream_t st, int forced_backend = -1);
@@ -118,6 +126,11 @@ int run_speech_frames(Context& c, const float* d_enc_tok, const int* d_cu_tok, c
                       const int* d_cu_frames, const float* d_pitch, const float* d_energy, const float* d_style,
                       const float* d_noise_prior, const float* d_noise_source, const float* d_init_phase,
                       float* d_audio, float* d_logamp, float* d_phase, cudaStream_t st);
+
+// token_pipeline.cu / prepack_tokens.cu
+int set_token_layout(Context& c, int n_seg, const int* len_t);
+int run_text_encoder(Context& c, const std::string& name, const int* d_tokens, float* d_mu_tok, float* d_x_tok,
+                     cudaStream_t st);
 
 int fail(Context& c, int code, const std::string& msg);
 int cuda_fail(Context& c, cudaError_t e, const char* where);

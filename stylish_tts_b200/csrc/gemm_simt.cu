@@ -158,6 +158,8 @@ cudaError_t conv_gemm_simt(const ConvGemm& g, const RowMap& map, cudaStream_t st
     case EPI_COUPLE: return launch_kind<EPI_COUPLE>(g, map, st);
     case EPI_PRIOR: return launch_kind<EPI_PRIOR>(g, map, st);
     case EPI_STFT: return launch_kind<EPI_STFT>(g, map, st);
+    case EPI_RELU: return launch_kind<EPI_RELU>(g, map, st);
+    case EPI_GELU: return launch_kind<EPI_GELU>(g, map, st);
     default: return cudaErrorInvalidValue;
   }
 }

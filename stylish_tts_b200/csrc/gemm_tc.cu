@@ -466,6 +466,8 @@ cudaError_t launch_mode(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
     case EPI_COUPLE: return launch_bn<MODE, EPI_COUPLE>(g, map, st);
     case EPI_PRIOR: return launch_bn<MODE, EPI_PRIOR>(g, map, st);
     case EPI_STFT: return launch_bn<MODE, EPI_STFT>(g, map, st);
+    case EPI_RELU: return launch_bn<MODE, EPI_RELU>(g, map, st);
+    case EPI_GELU: return launch_bn<MODE, EPI_GELU>(g, map, st);
     default: return cudaErrorInvalidValue;
   }
 }

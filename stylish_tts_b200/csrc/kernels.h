@@ -46,6 +46,19 @@ cudaError_t rowdot(const float* x, int ldx, int C, const RowMap& map, const floa
                    float* dense, cudaStream_t st);
 cudaError_t fill(float* p, size_t n, float v, cudaStream_t st);
 
+// ---- token_rate.cu
+cudaError_t embed_tokens(const int* tok, const int* cu_tok, const float* table, int C, int n_vocab, const RowMap& map,
+                         float* x, int ldx, cudaStream_t st);
+cudaError_t row_ln(const float* x, int ldx, int C, const RowMap& map, const float* gamma, const float* beta,
+                   int seg_stride, float eps, int relu, float* y, int ldy, cudaStream_t st);
+cudaError_t rope_inplace(float* x, int ldx, int col0, int blk, int n_blocks, int H, int D, int rd, const RowMap& map,
+                         cudaStream_t st);
+cudaError_t attention(const float* Q, int ldq, int qcol, const float* K, int ldk, int kcol, const float* V, int ldv,
+                      int vcol, int H, int D, float scale, const RowMap& qmap, const RowMap& kmap, int max_tq,
+                      int max_tk, const int* q_tok, const int* q_cu, int band, float* out, int ldo, cudaStream_t st);
+cudaError_t rows_to_dense(const float* src, int ld, int C, const RowMap& map, const int* cu, float* dst,
+                          cudaStream_t st);
+
 // ---- length_reg.cu
 cudaError_t durations_from_logits(const float* logits, int n_tokens, int* dur, cudaStream_t st);
 cudaError_t frame_index(const int* dur, const int* cu_tok, int n_seg, int* cu_frames, int* idx, int idx_cap,

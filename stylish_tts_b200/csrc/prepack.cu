@@ -215,6 +215,77 @@ bool pack_ada_block(Context& c, Loader& L, const std::string& p, const std::stri
   return true;
 }
 
+
+// one dense conv / Linear as a single-segment pack: [n_out, cin, k] -> K-major, cin padded to 64
+bool pack_simple(Context& c, Loader& L, const std::string& key, const std::string& name, int pad) {
+  const HostTensor w = L.weight(key + ".");
+  const HostTensor* b = L.has(key + ".bias") ? L.get(key + ".bias") : nullptr;
+  if (!L.ok || w.numel() == 0) return false;
+  const int n = (int)w.dim(0), cin = (int)w.dim(1), k = (int)w.dim(2);
+  Builder bd;
+  const int t[2] = {k, 0}, pd[2] = {pad, 0}, cp[2] = {pad64(cin), 0};
+  bd.init(n, 1, t, pd, cp);
+  bd.rows(0, w, 0, n, 0, cin, 0, 1);
+  if (b != nullptr) bd.set_bias(*b, 0, n, 0, 1);
+  c.gemm[name] = bd.upload(c);
+  return true;
+}
+
+// TextEncoder (text_encoder.py:396-462) under key prefix `kp` of module L.module -> packs named `nm.*`
+bool pack_text_encoder(Context& c, Loader& L, const std::string& kp, const std::string& nm) {
+  const HostTensor* emb = L.get(kp + "emb.weight");
+  if (!L.ok) return false;
+  const int C = (int)emb->dim(1);
+  {
+    std::vector<float> e(emb->data);
+    const float sc = std::sqrt((float)C);       // emb(x) * sqrt(n_channels): same fp32 product as on the device
+    for (auto& v : e) v *= sc;
+    put_vec(c, nm + ".emb", e);
+    c.vec_len[nm + ".vocab"] = (int)emb->dim(0);
+  }
+  for (int i = 0; i < 3; ++i) {
+    const std::string k = kp + "prenet.conv_layers." + std::to_string(i), n = nm + ".pre" + std::to_string(i);
+    if (!pack_simple(c, L, k, n, 2)) return false;
+    const HostTensor *g = L.get(kp + "prenet.norm_layers." + std::to_string(i) + ".gamma");
+    const HostTensor *b = L.get(kp + "prenet.norm_layers." + std::to_string(i) + ".beta");
+    if (!L.ok) return false;
+    put_vec(c, n + ".g", g->data);
+    put_vec(c, n + ".b", b->data);
+  }
+  if (!pack_simple(c, L, kp + "prenet.proj", nm + ".preproj", 0)) return false;
+  int n_layers = 0;
+  while (L.has(kp + "encoder.attn_layers." + std::to_string(n_layers) + ".conv_q.weight")) ++n_layers;
+  c.vec_len[nm + ".layers"] = n_layers;
+  for (int l = 0; l < n_layers; ++l) {
+    const std::string a = kp + "encoder.attn_layers." + std::to_string(l) + ".", n = nm + ".l" + std::to_string(l);
+    const HostTensor wq = L.weight(a + "conv_q."), wk = L.weight(a + "conv_k."), wv = L.weight(a + "conv_v.");
+    const HostTensor *bq = L.get(a + "conv_q.bias"), *bk = L.get(a + "conv_k.bias"), *bv = L.get(a + "conv_v.bias");
+    if (!L.ok) return false;
+    Builder b;
+    const int t[2] = {1, 0}, pd[2] = {0, 0}, cp[2] = {pad64(C), 0};
+    b.init(3 * C, 1, t, pd, cp);
+    b.rows(0, wq, 0, C, 0, C, 0, 1);      b.set_bias(*bq, 0, C, 0, 1);
+    b.rows(0, wk, 0, C, 0, C, C, 1);      b.set_bias(*bk, 0, C, C, 1);
+    b.rows(0, wv, 0, C, 0, C, 2 * C, 1);  b.set_bias(*bv, 0, C, 2 * C, 1);
+    c.gemm[n + ".qkv"] = b.upload(c);
+    if (!pack_simple(c, L, a + "conv_o", n + ".o", 0)) return false;
+    const std::string f = kp + "encoder.ffn_layers." + std::to_string(l) + ".";
+    const HostTensor w1 = L.weight(f + "conv_1.");
+    if (!L.ok) return false;
+    const int k = (int)w1.dim(2);
+    if (!pack_simple(c, L, f + "conv_1", n + ".ff1", k / 2)) return false;
+    if (!pack_simple(c, L, f + "conv_2", n + ".ff2", k / 2)) return false;
+    for (int j = 1; j <= 2; ++j) {
+      const std::string nk = kp + "encoder.norm_layers_" + std::to_string(j) + "." + std::to_string(l) + ".";
+      const HostTensor *g = L.get(nk + "gamma"), *be = L.get(nk + "beta");
+      if (!L.ok) return false;
+      put_vec(c, n + ".n" + std::to_string(j) + ".g", g->data);
+      put_vec(c, n + ".n" + std::to_string(j) + ".b", be->data);
+    }
+  }
+  return pack_simple(c, L, kp + "proj_m", nm + ".projm", 0);
+}
+
 }  // namespace
 
 int finalize_weights(Context& c) {
@@ -505,6 +576,18 @@ int finalize_weights(Context& c) {
     put_vec(c, "pe.F0_proj_b", bf->data);
     put_vec(c, "pe.N_proj_w", wn->data);
     put_vec(c, "pe.N_proj_b", bn->data);
+  }
+  // ======================================================================= token-rate encoders
+  {
+    struct Slot { const char* module; const char* kp; const char* nm; };
+    const Slot slots[3] = {{"speech_predictor", "text_encoder.", "te.sp"},
+                           {"pe_text_encoder", "", "te.pe"},
+                           {"duration_predictor", "text_encoder.", "te.dp"}};
+    for (const Slot& sl : slots) {
+      if (!c.has(std::string(sl.module) + "/" + sl.kp + "emb.weight")) continue;
+      Loader T{c, sl.module};
+      if (!pack_text_encoder(c, T, sl.kp, sl.nm)) return fail(c, -3, "missing weight " + T.missing);
+    }
   }
   for (auto& kv : c.gemm) kv.second.name = kv.first;
   if (cudaDeviceSynchronize() != cudaSuccess) return fail(c, -5, "cuda error while uploading weights");

@@ -1,0 +1,135 @@
+// Token-rate stage orchestration on the packed token layout.
+//   TextEncoder.forward   train/models/text_encoder.py:433-462
+//     emb * sqrt(C) -> ConvReluNorm prenet (36-86) -> Encoder (332-393): n x [MHA + LN, FFN + LN] -> proj_m
+// All dense contractions are conv-as-GEMM launches of the island class (fp32-grade in every
+// precision mode: the duration logits decide integer durations).
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+#include "engine.h"
+
+namespace stts {
+
+namespace {
+size_t up1k(size_t x) { return (x + 1023) / 1024 * 1024; }
+}
+
+int set_token_layout(Context& c, int n_seg, const int* len_t) {
+  if (n_seg <= 0 || n_seg > 1024 || len_t == nullptr) return fail(c, -1, "set_token_layout: bad arguments");
+  std::vector<int> sig(len_t, len_t + n_seg);
+  int max_t = 0;
+  for (int b = 0; b < n_seg; ++b) {
+    if (len_t[b] <= 0) return fail(c, -2, "utterance token count must be > 0");
+    max_t = std::max(max_t, len_t[b]);
+  }
+  if (sig == c.tsig && c.tarena != nullptr) return 0;
+  cudaError_t e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) return cuda_fail(c, e, "set_token_layout sync");
+  tc_map_cache_clear();
+  build_layout(c.LT, n_seg, len_t);
+  c.max_t = max_t;
+  const int R = c.LT.R, B = n_seg, nt = c.LT.n_tiles;
+  struct Want { const char* name; int ld; };
+  const Want wants[] = {{"TA", 128}, {"TB", 128}, {"TC", 128}, {"TX", 128}, {"TO", 128}, {"TQKV", 384},
+                        {"TH", 512}, {"TMU", 256}};
+  size_t used = 0;
+  std::map<std::string, size_t> off;
+  for (const Want& w : wants) { off[w.name] = used; used += up1k((size_t)R * w.ld * 4); }
+  const char* ints[] = {"tile_seg", "tile_nvalid", "seg_start", "seg_len", "cu"};
+  const size_t int_bytes[] = {(size_t)nt * 4, (size_t)nt * 4, (size_t)B * 4, (size_t)B * 4, (size_t)(B + 1) * 4};
+  for (int i = 0; i < 5; ++i) { off[ints[i]] = used; used += up1k(int_bytes[i]); }
+  if (used > c.tarena_bytes) {
+    if (c.tarena) cudaFree(c.tarena);
+    c.tarena = nullptr; c.tarena_bytes = 0;
+    e = cudaMalloc(&c.tarena, used);
+    if (e != cudaSuccess) return cuda_fail(c, e, "token workspace cudaMalloc");
+    c.tarena_bytes = used;
+  }
+  e = cudaMemset(c.tarena, 0, used);
+  if (e != cudaSuccess) return cuda_fail(c, e, "token workspace memset");
+  c.tact.clear(); c.traw.clear();
+  for (const Want& w : wants) {
+    Act a; a.ld = w.ld; a.rows = R; a.f = reinterpret_cast<float*>(c.tarena + off[w.name]); a.h = nullptr;
+    c.tact[w.name] = a;
+  }
+  Layout& L = c.LT;
+  const void* srcs[] = {L.tile_seg.data(), L.tile_nvalid.data(), L.seg_start.data(), L.seg_len.data(), L.cu.data()};
+  for (int i = 0; i < 5; ++i) {
+    c.traw[ints[i]] = c.tarena + off[ints[i]];
+    cudaMemcpy(c.traw[ints[i]], srcs[i], int_bytes[i], cudaMemcpyHostToDevice);
+  }
+  L.d_tile_seg = (int*)c.traw["tile_seg"]; L.d_tile_nvalid = (int*)c.traw["tile_nvalid"];
+  L.d_seg_start = (int*)c.traw["seg_start"]; L.d_seg_len = (int*)c.traw["seg_len"]; L.d_cu = (int*)c.traw["cu"];
+  e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) return cuda_fail(c, e, "set_token_layout upload");
+  c.tsig = sig;
+  return 0;
+}
+
+namespace {
+Epi mk_epi(int kind, const Act& dst, int col0) {
+  Epi e;
+  std::memset(&e, 0, sizeof(e));
+  e.kind = kind; e.out = dst.f; e.ldo = dst.ld; e.col0 = col0; e.scale = 1.f;
+  return e;
+}
+}  // namespace
+
+// d_tokens: int32 [sum T] utterances concatenated.  Outputs (either may be null), token-major dense:
+// d_mu_tok [sum T, inter] = proj_m(h), d_x_tok [sum T, C] = h.   Also leaves h in TX and mu in TMU.
+int run_text_encoder(Context& c, const std::string& nm, const int* d_tokens, float* d_mu_tok, float* d_x_tok,
+                     cudaStream_t st) {
+  if (!c.finalized || c.vec.count(nm + ".emb") == 0) return fail(c, -3, "text encoder weights not loaded: " + nm);
+  if (c.LT.total() == 0 || c.tact.count("TX") == 0) return fail(c, -4, "no token layout set");
+  const RowMap map = c.LT.map();
+  Act &ta = c.tact["TA"], &tb = c.tact["TB"], &tcb = c.tact["TC"], &tx = c.tact["TX"], &to = c.tact["TO"];
+  Act &tqkv = c.tact["TQKV"], &th = c.tact["TH"], &tmu = c.tact["TMU"];
+  const int C = 128, H = 8, D = C / H, rd = D / 2;
+  STTS_CK(embed_tokens(d_tokens, c.LT.d_cu, c.vec[nm + ".emb"], C, c.vec_len[nm + ".vocab"], map, ta.f, ta.ld, st));
+  // ---- prenet: 3 x (conv k5 -> channel LayerNorm (eps 1e-4) -> ReLU), then x + proj(y)
+  const Act* y = &ta;
+  Act* pp[2] = {&tb, &tcb};
+  for (int i = 0; i < 3; ++i) {
+    const std::string n = nm + ".pre" + std::to_string(i);
+    Act& dst = *pp[i & 1];
+    STTS_RET(run_gemm(c, c.gemm[n], GC_ISLAND, y, 0, nullptr, 0, mk_epi(EPI_BIAS, dst, 0), map, st));
+    STTS_CK(row_ln(dst.f, dst.ld, C, map, c.vec[n + ".g"], c.vec[n + ".b"], 0, 1e-4f, 1, dst.f, dst.ld, st));
+    y = &dst;
+  }
+  {
+    Epi e = mk_epi(EPI_ADD, tx, 0);
+    e.res = ta.f; e.ldr = ta.ld; e.rcol0 = 0;
+    STTS_RET(run_gemm(c, c.gemm[nm + ".preproj"], GC_ISLAND, y, 0, nullptr, 0, e, map, st));
+  }
+  // ---- encoder layers
+  const int n_layers = c.vec_len[nm + ".layers"];
+  const float scale = 1.0f / std::sqrt((float)D);
+  for (int l = 0; l < n_layers; ++l) {
+    const std::string n = nm + ".l" + std::to_string(l);
+    STTS_RET(run_gemm(c, c.gemm[n + ".qkv"], GC_ISLAND, &tx, 0, nullptr, 0, mk_epi(EPI_BIAS, tqkv, 0), map, st));
+    STTS_CK(rope_inplace(tqkv.f, tqkv.ld, 0, C, 2, H, D, rd, map, st));
+    STTS_CK(attention(tqkv.f, tqkv.ld, 0, tqkv.f, tqkv.ld, C, tqkv.f, tqkv.ld, 2 * C, H, D, scale, map, map, c.max_t,
+                      c.max_t, nullptr, nullptr, 0, to.f, to.ld, st));
+    {
+      Epi e = mk_epi(EPI_ADD, tb, 0);
+      e.res = tx.f; e.ldr = tx.ld; e.rcol0 = 0;
+      STTS_RET(run_gemm(c, c.gemm[n + ".o"], GC_ISLAND, &to, 0, nullptr, 0, e, map, st));
+    }
+    STTS_CK(row_ln(tb.f, tb.ld, C, map, c.vec[n + ".n1.g"], c.vec[n + ".n1.b"], 0, 1e-4f, 0, tx.f, tx.ld, st));
+    STTS_RET(run_gemm(c, c.gemm[n + ".ff1"], GC_ISLAND, &tx, 0, nullptr, 0, mk_epi(EPI_RELU, th, 0), map, st));
+    {
+      Epi e = mk_epi(EPI_ADD, tb, 0);
+      e.res = tx.f; e.ldr = tx.ld; e.rcol0 = 0;
+      STTS_RET(run_gemm(c, c.gemm[n + ".ff2"], GC_ISLAND, &th, 0, nullptr, 0, e, map, st));
+    }
+    STTS_CK(row_ln(tb.f, tb.ld, C, map, c.vec[n + ".n2.g"], c.vec[n + ".n2.b"], 0, 1e-4f, 0, tx.f, tx.ld, st));
+  }
+  const PackedGemm& pm = c.gemm[nm + ".projm"];
+  STTS_RET(run_gemm(c, pm, GC_ISLAND, &tx, 0, nullptr, 0, mk_epi(EPI_BIAS, tmu, 0), map, st));
+  if (d_mu_tok) STTS_CK(rows_to_dense(tmu.f, tmu.ld, pm.N, map, c.LT.d_cu, d_mu_tok, st));
+  if (d_x_tok) STTS_CK(rows_to_dense(tx.f, tx.ld, C, map, c.LT.d_cu, d_x_tok, st));
+  return 0;
+}
+
+}  // namespace stts

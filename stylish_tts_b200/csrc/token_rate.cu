@@ -1,0 +1,257 @@
+// Token-rate kernels (<= 510 phonemes per utterance) on the packed token layout: embedding gather,
+// row LayerNorm family, partial rotary embedding and multi-head attention.  Reference:
+//   TextEncoder            train/models/text_encoder.py:396-462 (Encoder 332-393, MHA 171-296,
+//                          RotaryPositionalEmbeddings 89-168, channel LayerNorm 15-33, FFN 305-329)
+//   AdaptiveLayerNorm      train/models/ada_norm.py:185-201
+// The dense contractions of these modules (1x1 / k3 / k5 convs) run on the conv-as-GEMM kernels;
+// only what is not a GEMM lives here.  A packed token buffer has the same geometry as the
+// frame-rate buffers (common.cuh): utterances start on multiples of 128 rows, guard rows stay zero,
+// so `x * x_mask` of the reference is the identity and conv zero padding is free.
+#include "kernels.h"
+
+namespace stts {
+
+// ------------------------------------------------------------------------------ embedding
+// x[row(seg, t), :] = table[tok[cu_tok[seg] + t], :]   (table already scaled by sqrt(C))
+__global__ void __launch_bounds__(128) embed_kernel(const int* __restrict__ tok, const int* __restrict__ cu_tok,
+                                                    const float* __restrict__ table, int C, int n_vocab, RowMap map,
+                                                    float* __restrict__ x, int ldx) {
+  const int tile = blockIdx.x;
+  const int seg = map.tile_seg[tile];
+  if (seg < 0) return;
+  const int nvalid = map.tile_nvalid[tile];
+  const int t0 = tile * 128 - map.seg_start[seg];
+  for (int i = threadIdx.x; i < nvalid * C; i += blockDim.x) {
+    const int lr = i / C, c = i - lr * C;
+    int id = tok[cu_tok[seg] + t0 + lr];
+    id = id < 0 ? 0 : (id >= n_vocab ? n_vocab - 1 : id);
+    x[(size_t)(tile * 128 + lr) * ldx + c] = table[(size_t)id * C + c];
+  }
+}
+
+cudaError_t embed_tokens(const int* tok, const int* cu_tok, const float* table, int C, int n_vocab, const RowMap& map,
+                         float* x, int ldx, cudaStream_t st) {
+  embed_kernel<<<map.n_tiles, 128, 0, st>>>(tok, cu_tok, table, C, n_vocab, map, x, ldx);
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------ row LayerNorm
+// y = act(affine((x - mean) * rsqrt(var + eps)))  over the C channels of one row, biased variance,
+// two-pass in registers (one warp per row, C <= 512).
+//   seg_stride == 0 : affine = gamma[c] * n + beta[c]                (channel LayerNorm / nn.LayerNorm)
+//   seg_stride  > 0 : affine = (1 + g[seg, c]) * n + g[seg, C + c]   (AdaptiveLayerNorm, g = style FC row)
+__global__ void __launch_bounds__(256) row_ln_kernel(const float* x, int ldx, int C, RowMap map,
+                                                     const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                     int seg_stride, float eps, int relu, float* y,
+                                                     int ldy) {  // x may alias y (in place)
+  const int tile = blockIdx.x;
+  const int seg = map.tile_seg[tile];
+  if (seg < 0) return;
+  const int nvalid = map.tile_nvalid[tile];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const float* ga = seg_stride ? gamma + (size_t)seg * seg_stride : gamma;
+  const float* be = seg_stride ? gamma + (size_t)seg * seg_stride + C : beta;
+  for (int lr = warp; lr < nvalid; lr += 8) {
+    const size_t r = (size_t)tile * 128 + lr;
+    float v[16];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const int c = lane + 32 * i;
+      v[i] = (c < C) ? x[r * ldx + c] : 0.f;
+      s += v[i];
+    }
+    const float mean = warp_sum(s) / (float)C;
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const int c = lane + 32 * i;
+      const float d = (c < C) ? v[i] - mean : 0.f;
+      q += d * d;
+    }
+    const float rstd = rsqrtf(warp_sum(q) / (float)C + eps);
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const int c = lane + 32 * i;
+      if (c < C) {
+        const float n = (v[i] - mean) * rstd;
+        float o = seg_stride ? (1.f + ga[c]) * n + be[c] : n * ga[c] + be[c];
+        if (relu) o = fmaxf(o, 0.f);
+        y[r * ldy + c] = o;
+      }
+    }
+  }
+}
+
+cudaError_t row_ln(const float* x, int ldx, int C, const RowMap& map, const float* gamma, const float* beta,
+                   int seg_stride, float eps, int relu, float* y, int ldy, cudaStream_t st) {
+  if (C > 512) return cudaErrorInvalidValue;
+  row_ln_kernel<<<map.n_tiles, 256, 0, st>>>(x, ldx, C, map, gamma, beta, seg_stride, eps, relu, y, ldy);
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------ partial RoPE
+// In place on `n_blocks` column blocks of H heads x D features starting at columns col0 + b * blk:
+// the first rd features of every head are rotated (half-split form, theta_i = 10000^(-2i/rd)),
+// position = row index inside the utterance.  text_encoder.py:89-168,200-201.
+__global__ void __launch_bounds__(256) rope_kernel(float* __restrict__ x, int ldx, int col0, int blk, int n_blocks,
+                                                   int H, int D, int rd, RowMap map) {
+  const int tile = blockIdx.x;
+  const int seg = map.tile_seg[tile];
+  if (seg < 0) return;
+  const int nvalid = map.tile_nvalid[tile];
+  const int h = rd >> 1;
+  const int per_row = n_blocks * H * h;
+  const int pos0 = tile * 128 - map.seg_start[seg];
+  for (int i = threadIdx.x; i < nvalid * per_row; i += blockDim.x) {
+    const int lr = i / per_row;
+    int k = i - lr * per_row;
+    const int b = k / (H * h);
+    k -= b * H * h;
+    const int hd = k / h, j = k - hd * h;
+    const float inv = 1.0f / powf(10000.f, (float)(2 * j) / (float)rd);
+    const float ang = (float)(pos0 + lr) * inv;
+    float sn, cs;
+    sincosf(ang, &sn, &cs);
+    float* p = x + (size_t)(tile * 128 + lr) * ldx + col0 + b * blk + hd * D;
+    const float a = p[j], bb = p[j + h];
+    p[j] = a * cs - bb * sn;
+    p[j + h] = bb * cs + a * sn;
+  }
+}
+
+cudaError_t rope_inplace(float* x, int ldx, int col0, int blk, int n_blocks, int H, int D, int rd, const RowMap& map,
+                         cudaStream_t st) {
+  rope_kernel<<<map.n_tiles, 256, 0, st>>>(x, ldx, col0, blk, n_blocks, H, D, rd, map);
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------ attention
+// out[q, hd*D : (hd+1)*D] = softmax_k(scale * <Q_q, K_k> + bias(q, k)) V_k over the keys of the same
+// utterance.  One CTA = (16 queries, head, utterance), 128 threads, fp32 throughout.
+//   band > 0: bias = -1e4 where |k - q_tok[q]| <= band  (the reference's inverted monotonic band,
+//   pitch_energy_predictor.py:194-212 + text_encoder.py:255-262)
+constexpr int kAttQ = 16;
+__global__ void __launch_bounds__(128) attention_kernel(const float* __restrict__ Q, int ldq, int qcol,
+                                                        const float* __restrict__ K, int ldk, int kcol,
+                                                        const float* __restrict__ V, int ldv, int vcol, int D,
+                                                        float scale, RowMap qmap, RowMap kmap,
+                                                        const int* __restrict__ q_tok, const int* __restrict__ q_cu,
+                                                        int band, float* __restrict__ out, int ldo) {
+  extern __shared__ float sh[];
+  const int seg = blockIdx.z, hd = blockIdx.y;
+  const int Tq = qmap.seg_len[seg], Tk = kmap.seg_len[seg];
+  const int q0 = blockIdx.x * kAttQ;
+  if (q0 >= Tq) return;
+  const int nq = (Tq - q0 < kAttQ) ? (Tq - q0) : kAttQ;
+  const int qrow0 = qmap.seg_start[seg] + q0, krow0 = kmap.seg_start[seg];
+  const int Tkp = (Tk + 3) & ~3;
+  float* sq = sh;                    // [kAttQ][D]
+  float* sc = sh + kAttQ * D;        // [kAttQ][Tkp]
+  for (int i = threadIdx.x; i < kAttQ * D; i += blockDim.x) {
+    const int qi = i / D, d = i - qi * D;
+    sq[i] = (qi < nq) ? Q[(size_t)(qrow0 + qi) * ldq + qcol + hd * D + d] * scale : 0.f;
+  }
+  __syncthreads();
+  // ---- scores
+  for (int j = threadIdx.x; j < Tk; j += blockDim.x) {
+    const float* kp = K + (size_t)(krow0 + j) * ldk + kcol + hd * D;
+    float acc[kAttQ];
+#pragma unroll
+    for (int i = 0; i < kAttQ; ++i) acc[i] = 0.f;
+    for (int d = 0; d < D; d += 4) {
+      const float4 kv = *reinterpret_cast<const float4*>(kp + d);
+#pragma unroll
+      for (int i = 0; i < kAttQ; ++i) {
+        const float4 qv = *reinterpret_cast<const float4*>(sq + i * D + d);
+        acc[i] = fmaf(qv.x, kv.x, acc[i]);
+        acc[i] = fmaf(qv.y, kv.y, acc[i]);
+        acc[i] = fmaf(qv.z, kv.z, acc[i]);
+        acc[i] = fmaf(qv.w, kv.w, acc[i]);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < kAttQ; ++i) {
+      float b = 0.f;
+      if (band > 0 && i < nq) {
+        const int tau = q_tok[q_cu[seg] + q0 + i];
+        if (j >= tau - band && j <= tau + band) b = -1e4f;
+      }
+      sc[i * Tkp + j] = acc[i] + b;
+    }
+  }
+  __syncthreads();
+  // ---- softmax (one warp per 4 queries)
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int i = warp; i < nq; i += 4) {
+    float* row = sc + i * Tkp;
+    float m = -3.0e38f;
+    for (int j = lane; j < Tk; j += 32) m = fmaxf(m, row[j]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    float s = 0.f;
+    for (int j = lane; j < Tk; j += 32) {
+      const float e = expf(row[j] - m);
+      row[j] = e;
+      s += e;
+    }
+    s = warp_sum(s);
+    const float inv = 1.f / s;
+    for (int j = lane; j < Tk; j += 32) row[j] *= inv;
+  }
+  __syncthreads();
+  // ---- P V
+  for (int idx = threadIdx.x; idx < nq * D; idx += blockDim.x) {
+    const int i = idx / D, d = idx - i * D;
+    const float* vp = V + (size_t)krow0 * ldv + vcol + hd * D + d;
+    const float* pr = sc + i * Tkp;
+    float a0 = 0.f, a1 = 0.f;
+    int j = 0;
+    for (; j + 2 <= Tk; j += 2) {
+      a0 = fmaf(pr[j], vp[(size_t)j * ldv], a0);
+      a1 = fmaf(pr[j + 1], vp[(size_t)(j + 1) * ldv], a1);
+    }
+    if (j < Tk) a0 = fmaf(pr[j], vp[(size_t)j * ldv], a0);
+    out[(size_t)(qrow0 + i) * ldo + hd * D + d] = a0 + a1;
+  }
+}
+
+cudaError_t attention(const float* Q, int ldq, int qcol, const float* K, int ldk, int kcol, const float* V, int ldv,
+                      int vcol, int H, int D, float scale, const RowMap& qmap, const RowMap& kmap, int max_tq,
+                      int max_tk, const int* q_tok, const int* q_cu, int band, float* out, int ldo, cudaStream_t st) {
+  if (D % 4 != 0) return cudaErrorInvalidValue;
+  const size_t smem = (size_t)(kAttQ * D + kAttQ * ((max_tk + 3) & ~3)) * sizeof(float);
+  static size_t configured = 0;
+  if (smem > 48 * 1024 && smem > configured) {
+    cudaError_t e = cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    configured = smem;
+  }
+  dim3 grid((max_tq + kAttQ - 1) / kAttQ, H, qmap.n_seg);
+  attention_kernel<<<grid, 128, smem, st>>>(Q, ldq, qcol, K, ldk, kcol, V, ldv, vcol, D, scale, qmap, kmap, q_tok, q_cu,
+                                            band, out, ldo);
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------ packed rows -> token-major dense
+// dst[(cu[seg] + t) * C + c] = src[row(seg, t), c]: the utterances' rows concatenated without gaps
+__global__ void __launch_bounds__(256) rows_to_dense_kernel(const float* __restrict__ src, int ld, int C, RowMap map,
+                                                            const int* __restrict__ cu, float* __restrict__ dst) {
+  const int tile = blockIdx.x;
+  const int seg = map.tile_seg[tile];
+  if (seg < 0) return;
+  const int nvalid = map.tile_nvalid[tile];
+  const int t0 = tile * 128 - map.seg_start[seg];
+  for (int i = threadIdx.x; i < nvalid * C; i += blockDim.x) {
+    const int lr = i / C, c = i - lr * C;
+    dst[(size_t)(cu[seg] + t0 + lr) * C + c] = src[(size_t)(tile * 128 + lr) * ld + c];
+  }
+}
+
+cudaError_t rows_to_dense(const float* src, int ld, int C, const RowMap& map, const int* cu, float* dst,
+                          cudaStream_t st) {
+  rows_to_dense_kernel<<<map.n_tiles, 256, 0, st>>>(src, ld, C, map, cu, dst);
+  return cudaGetLastError();
+}
+
+}  // namespace stts

@@ -47,6 +47,7 @@ class Engine:
         self.len_f: Optional[Sequence[int]] = None
         self.len_f4: Optional[Sequence[int]] = None
         self.precision = "fp32"
+        self.len_t: Sequence[int] = []
 
     def __del__(self):
         try:
@@ -96,6 +97,26 @@ class Engine:
         with torch.cuda.device(self.device):
             self._check(self.lib.stts_set_layout(self.h, n, a, b))
         self.n_seg, self.len_f, self.len_f4 = n, lf, l4
+
+    def set_token_layout(self, len_t: Iterable[int]):
+        lt = [int(x) for x in len_t]
+        with torch.cuda.device(self.device):
+            self._check(self.lib.stts_set_token_layout(self.h, len(lt), (C.c_int * len(lt))(*lt)))
+        self.len_t = lt
+
+    # ------------------------------------------------------------------ token-rate encoders
+    def text_encoder(self, which: str, tokens: torch.Tensor, inter_dim: int, want_mu: bool = True, want_x: bool = True):
+        """TextEncoder.forward (text_encoder.py:433-462) on the current token layout.  tokens: int32
+        [sum T] concatenated.  Returns token-major (mu [sum T, inter_dim], x [sum T, 128])."""
+        n = int(tokens.numel())
+        if n != sum(self.len_t):
+            raise ValueError("token count does not match the token layout")
+        tokens = tokens.to(torch.int32).contiguous()
+        mu = torch.empty((n, inter_dim), dtype=torch.float32, device=self.device) if want_mu else None
+        x = torch.empty((n, 128), dtype=torch.float32, device=self.device) if want_x else None
+        self._check(self.lib.stts_text_encoder(self.h, which.encode(), _ptr(tokens, torch.int32), _ptr(mu), _ptr(x),
+                                               self._stream()))
+        return mu, x
 
     def workspace_bytes(self) -> int:
         return int(self.lib.stts_workspace_bytes(self.h))

@@ -353,6 +353,7 @@ class SpeechPredictor(_EngineOwner):
     def forward(self, texts, text_lengths, alignment, pitch, energy, audio_gt=None):
         if audio_gt is not None:
             raise NotImplementedError("the posterior (training) branch is outside the synthesis forward path")
+        self.text_encoder.attach_native(self.engine(), "speech_predictor")
         enc, _, _ = self.text_encoder(texts, text_lengths)
         style = self.style_encoder(enc, text_lengths)
         b, _, t = enc.shape

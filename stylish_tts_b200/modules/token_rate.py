@@ -153,17 +153,70 @@ class _Transformer(nn.Module):
         return x * x_mask
 
 
+def _pack_tokens(x: torch.Tensor, lengths):
+    """padded [B, Tmax] + host lengths -> concatenated [sum T] and the boolean validity mask [B, Tmax]."""
+    pos = torch.arange(x.shape[1], device=x.device)[None, :]
+    valid = pos < torch.as_tensor(lengths, device=x.device)[:, None]
+    return x[valid], valid
+
+
 class TextEncoder(nn.Module):
+    """text_encoder.py:396-462.  The arithmetic runs in libstts_b200 (stts_text_encoder: embedding,
+    prenet, 8 x [RoPE attention + LN, conv FFN + LN], proj_m on the packed token layout); this module
+    holds the parameters in the reference layout.  ``forward_torch`` is the op-by-op torch statement
+    of the same computation, kept for the CPU host tests of the state_dict layout only."""
+
     def __init__(self, *, inter_dim, config):
         super().__init__()
         self.n_channels = config.hidden_dim
+        self.inter_dim = inter_dim
         self.emb = nn.Embedding(config.tokens, self.n_channels)
         self.prenet = _Prenet(self.n_channels, kernel_size=5, n_layers=3)
         self.encoder = _Transformer(self.n_channels, config.filter_channels, config.heads, config.layers,
                                     config.kernel_size)
         self.proj_m = nn.Conv1d(self.n_channels, inter_dim, 1)
+        object.__setattr__(self, "_native", None)
 
-    def forward(self, x, x_lengths, spks=None):
+    # ---- native engine plumbing
+    def attach_native(self, engine, which: str):
+        """Use a context that already holds this encoder's weights under module name ``which``."""
+        object.__setattr__(self, "_native", (engine, which, False))
+
+    def load_state_dict(self, state_dict, strict: bool = True, assign: bool = False):
+        object.__setattr__(self, "_native", None)
+        return super().load_state_dict(state_dict, strict=strict, assign=assign)
+
+    def _engine(self):
+        if self._native is None:
+            from ..engine import Engine
+            dev = self.emb.weight.device
+            if dev.type != "cuda":
+                raise RuntimeError("stylish_tts_b200 modules run on a B200 only (no CPU fallback)")
+            eng = Engine(dev)
+            eng.load_state("pe_text_encoder", self.state_dict())
+            eng.finalize()
+            object.__setattr__(self, "_native", (eng, "pe_text_encoder", True))
+        return self._native[0], self._native[1]
+
+    def encode_packed(self, tokens_cat: torch.Tensor, lengths):
+        """tokens_cat int [sum T]; lengths: host ints.  -> token-major (mu [sum T, inter], h [sum T, 128])."""
+        eng, which = self._engine()
+        eng.set_token_layout(lengths)
+        return eng.text_encoder(which, tokens_cat, self.inter_dim)
+
+    def forward(self, x, x_lengths, spks=None, host_lengths=None):
+        # host_lengths: the same lengths as Python ints, when the caller has them (saves a D2H sync)
+        lengths = [int(v) for v in (host_lengths if host_lengths is not None else x_lengths.tolist())]
+        b, tmax = x.shape
+        tok, valid = _pack_tokens(x, lengths)
+        mu_t, h_t = self.encode_packed(tok, lengths)
+        mu = torch.zeros((b, tmax, self.inter_dim), dtype=torch.float32, device=x.device)
+        h = torch.zeros((b, tmax, self.n_channels), dtype=torch.float32, device=x.device)
+        mu[valid] = mu_t
+        h[valid] = h_t
+        return mu.transpose(1, 2), h.transpose(1, 2), valid.unsqueeze(1).to(torch.float32)
+
+    def forward_torch(self, x, x_lengths, spks=None):
         h = (self.emb(x) * math.sqrt(self.n_channels)).transpose(1, 2)
         x_mask = length_mask(x_lengths, h.shape[2]).unsqueeze(1).to(h.dtype)
         h = self.encoder(self.prenet(h, x_mask), x_mask)
@@ -259,7 +312,34 @@ class DurationPredictor(nn.Module):
                                               dropout=duration_config.dropout)
         self.duration_proj = _LinearNorm(inter_dim + style_dim, duration_config.duration_classes)
 
-    def forward(self, texts, text_lengths):
-        enc, _, _ = self.text_encoder(texts, text_lengths)
+    def load_state_dict(self, state_dict, strict: bool = True, assign: bool = False):
+        object.__setattr__(self, "_eng", None)
+        return super().load_state_dict(state_dict, strict=strict, assign=assign)
+
+    def attach_engine(self, engine):
+        """Use a context that already holds this module's weights as "duration_predictor"."""
+        object.__setattr__(self, "_eng", engine)
+
+    def _engine(self):
+        if getattr(self, "_eng", None) is None:
+            from ..engine import Engine
+            dev = self.duration_proj.linear_layer.weight.device
+            if dev.type != "cuda":
+                raise RuntimeError("stylish_tts_b200 modules run on a B200 only (no CPU fallback)")
+            eng = Engine(dev)
+            eng.load_state("duration_predictor", self.state_dict())
+            eng.finalize()
+            object.__setattr__(self, "_eng", eng)
+        return self._eng
+
+    def forward(self, texts, text_lengths, host_lengths=None):
+        self.text_encoder.attach_native(self._engine(), "duration_predictor")
+        enc, _, _ = self.text_encoder(texts, text_lengths, host_lengths=host_lengths)
+        style = self.style_encoder(enc, text_lengths)
+        return self.duration_proj(self.prosody_encoder(enc, style, text_lengths))
+
+    def forward_torch(self, texts, text_lengths):
+        """Op-by-op torch statement of the same computation (CPU host tests of the mirror only)."""
+        enc, _, _ = self.text_encoder.forward_torch(texts, text_lengths)
         style = self.style_encoder(enc, text_lengths)
         return self.duration_proj(self.prosody_encoder(enc, style, text_lengths))

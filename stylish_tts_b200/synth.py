@@ -34,7 +34,11 @@ class Synthesizer:
     def reload_weights(self):
         self.engine.load_state("speech_predictor", self.nets["speech_predictor"].state_dict())
         self.engine.load_state("pitch_energy_predictor", self.nets["pitch_energy_predictor"].state_dict())
+        self.engine.load_state("pe_text_encoder", self.nets["pe_text_encoder"].state_dict())
+        self.engine.load_state("duration_predictor", self.nets["duration_predictor"].state_dict())
         self.engine.finalize()
+        self.nets["pe_text_encoder"].attach_native(self.engine, "pe_text_encoder")
+        self.nets["duration_predictor"].attach_engine(self.engine)
         self.nets["speech_predictor"].attach_engine(self.engine)
         self.nets["pitch_energy_predictor"].attach_engine(self.engine)
 
@@ -65,7 +69,7 @@ class Synthesizer:
         lens = torch.tensor(T, dtype=torch.int64, device=dev)
 
         # ---- durations (duration_predictor + prediction_to_duration)
-        logits = nets["duration_predictor"](tok, lens)                      # [B, Tmax, 16]
+        logits = nets["duration_predictor"](tok, lens, host_lengths=T)                      # [B, Tmax, 16]
         dur_all = eng.durations(logits.reshape(B * Tmax, 16)).view(B, Tmax)  # int32
         valid = torch.arange(Tmax, device=dev)[None, :] < lens[:, None]
         dur_pred = dur_all * valid
@@ -84,7 +88,7 @@ class Synthesizer:
         eng.set_layout(F_list, [4 * f for f in F_list])
 
         # ---- pitch / energy
-        pe_enc, _, _ = nets["pe_text_encoder"](tok, lens)
+        pe_enc, _, _ = nets["pe_text_encoder"](tok, lens, host_lengths=T)
         pe_style = nets["pe_text_style_encoder"](pe_enc, lens)
         pep = nets["pitch_energy_predictor"]
         prosody = pep.prosody_encoder(pe_enc, pe_style, lens)
@@ -104,7 +108,8 @@ class Synthesizer:
 
         # ---- speech
         sp = nets["speech_predictor"]
-        enc, _, _ = sp.text_encoder(tok, lens)
+        sp.text_encoder.attach_native(eng, "speech_predictor")
+        enc, _, _ = sp.text_encoder(tok, lens, host_lengths=T)
         style = sp.style_encoder(enc, lens).contiguous()
         enc_tok = enc.transpose(1, 2).contiguous().view(B * Tmax, 128)
         if noise is not None:

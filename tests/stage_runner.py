@@ -81,6 +81,14 @@ def run(precision="fp32", g=None, tag=""):
         res["alignment"] = {"max_abs": float((al - alignment[0]).abs().max()), "ref_absmax": 1.0, "rel": 0.0,
                             "frac_gt_1e-3": 0.0}
 
+    def sec_text_encoders():  # native token-rate text encoders (stts_text_encoder) + duration logits
+        sp.text_encoder.attach_native(eng, "speech_predictor")
+        enc, _, _ = sp.text_encoder(tokens, lens)
+        rec("sp_text", enc, g["tap.sp_text"])
+        pe_enc, _, _ = nets["pe_text_encoder"](tokens, lens)
+        rec("pe_text", pe_enc, g["tap.pe_text"])
+        rec("dur_logits", nets["duration_predictor"](tokens, lens), g["tap.dur_logits"])
+
     def sec_pitch___energy_towers_on_the_reference_s():  # pitch / energy towers on the reference's cross-attended frames
         peng.set_layout([F_], None)
         pitch, energy = peng.pe_towers(g["tap.pe_cross"].to(dev).contiguous().view(-1), g["tap.pe_style"].to(dev))
@@ -157,7 +165,7 @@ def run(precision="fp32", g=None, tag=""):
         rec("SpeechPredictor.logamp", pred.magnitude, g["out.logamp"])
 
     with torch.no_grad():
-        for fn in (sec_length_regulation, sec_pitch___energy_towers_on_the_reference_s, sec_decoder,
+        for fn in (sec_length_regulation, sec_text_encoders, sec_pitch___energy_towers_on_the_reference_s, sec_decoder,
                    sec_prior___flow___post_flow, sec_source, sec_generator__fed_the_reference_mel_,
                    sec_generator_from_reference_stft,
                    sec_SpeechPredictor_module_end_to_end__nativ):

@@ -46,10 +46,10 @@ def test_token_rate_mirrors_equal_oracle(cpu_nets):
     t = fixture.synth_tokens(14, g)
     tk, ln = t[None], torch.tensor([14])
     with torch.no_grad():
-        a = cpu_nets["duration_predictor"](tk, ln)
+        a = cpu_nets["duration_predictor"].forward_torch(tk, ln)
         b = port.duration_predictor(sds["duration_predictor"], tk, ln)
         assert float((a - b).abs().max()) <= 1e-6
-        e1, _, _ = cpu_nets["pe_text_encoder"](tk, ln)
+        e1, _, _ = cpu_nets["pe_text_encoder"].forward_torch(tk, ln)
         e2, _, _ = port.text_encoder(sds["pe_text_encoder"], "", tk, ln)
         assert float((e1 - e2).abs().max()) <= 1e-6
         s1 = cpu_nets["pe_text_style_encoder"](e1, ln)
@@ -66,8 +66,8 @@ def test_padded_batch_has_per_utterance_semantics(cpu_nets):
         tk[i, : t.numel()] = t
     ln = torch.tensor([7, 19, 12])
     with torch.no_grad():
-        a = cpu_nets["duration_predictor"](tk, ln)
-        enc, _, _ = cpu_nets["pe_text_encoder"](tk, ln)
+        a = cpu_nets["duration_predictor"].forward_torch(tk, ln)
+        enc, _, _ = cpu_nets["pe_text_encoder"].forward_torch(tk, ln)
         sty = cpu_nets["pe_text_style_encoder"](enc, ln)
         for i, t in enumerate(toks):
             n = t.numel()
@@ -92,7 +92,7 @@ def test_cross_attention_ragged_mode_equals_b1(cpu_nets):
         ft[i, : Fs[i]] = port.duration_to_indices(durs[i].float())
     ln, fl = torch.tensor(Ts), torch.tensor(Fs)
     with torch.no_grad():
-        enc, _, _ = cpu_nets["pe_text_encoder"](tk, ln)
+        enc, _, _ = cpu_nets["pe_text_encoder"].forward_torch(tk, ln)
         sty = cpu_nets["pe_text_style_encoder"](enc, ln)
         pros = pep.prosody_encoder(enc, sty, ln)
         x = pep.compute_cross(pros, ft, sty, ln, frame_lengths=fl)
