@@ -78,6 +78,14 @@ int stts_set_token_layout(stts_ctx* ctx, int n_seg, const int* len_t);
 int stts_text_encoder(stts_ctx* ctx, const char* which, const int32_t* d_tokens, float* d_mu_tok,
                       float* d_x_tok, void* stream);
 
+/* ProsodyEncoder.forward, prosody_encoder.py:63-81.  which: "duration_predictor" or
+ * "pitch_energy_predictor" (their prosody_encoder.*).  d_enc_tok token-major dense [sum T, d_model]
+ * (= text encoding .transpose(1,2)), d_style [n_seg, 64]; d_out_tok [sum T, d_model + 64] (may be
+ * NULL); d_logits_tok [sum T, 16] = DurationPredictor.duration_proj of the result
+ * (duration_predictor.py:30-36; "duration_predictor" only, may be NULL).                            */
+int stts_prosody_encoder(stts_ctx* ctx, const char* which, const float* d_enc_tok, const float* d_style,
+                         float* d_out_tok, float* d_logits_tok, void* stream);
+
 /* ---- length regulation ------------------------------------------------------------------------
  * DurationProcessor.prediction_to_duration, utils.py:468-474: logits [n_tokens,16] -> int32.    */
 int stts_durations(stts_ctx* ctx, const float* d_logits, int n_tokens, int32_t* d_dur, void* stream);

@@ -93,6 +93,16 @@ int stts_text_encoder(stts_ctx* ctx, const char* which, const int32_t* d_tokens,
   return run_text_encoder(ctx->c, nm, d_tokens, d_mu_tok, d_x_tok, S(stream));
 }
 
+int stts_prosody_encoder(stts_ctx* ctx, const char* which, const float* d_enc_tok, const float* d_style,
+                         float* d_out_tok, float* d_logits_tok, void* stream) {
+  if (!ctx || !which || !d_enc_tok || !d_style) return STTS_ERR_BAD_ARG;
+  DeviceGuard g(ctx->c.device);
+  const std::string w(which);
+  const char* nm = w == "duration_predictor" ? "pr.dp" : (w == "pitch_energy_predictor" ? "pr.pe" : nullptr);
+  if (nm == nullptr) return fail(ctx->c, STTS_ERR_BAD_ARG, "stts_prosody_encoder: unknown module " + w);
+  return run_prosody_encoder(ctx->c, nm, d_enc_tok, d_style, d_out_tok, d_logits_tok, S(stream));
+}
+
 int stts_set_layout(stts_ctx* ctx, int n_seg, const int* len_f, const int* len_f4) {
   if (!ctx) return STTS_ERR_BAD_ARG;
   DeviceGuard g(ctx->c.device);

@@ -132,6 +132,9 @@ int set_token_layout(Context& c, int n_seg, const int* len_t);
 int run_text_encoder(Context& c, const std::string& name, const int* d_tokens, float* d_mu_tok, float* d_x_tok,
                      cudaStream_t st);
 
+int run_prosody_encoder(Context& c, const std::string& name, const float* d_enc_tok, const float* d_style,
+                        float* d_out_tok, float* d_logits_tok, cudaStream_t st);
+
 int fail(Context& c, int code, const std::string& msg);
 int cuda_fail(Context& c, cudaError_t e, const char* where);
 

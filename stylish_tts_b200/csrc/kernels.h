@@ -56,6 +56,9 @@ cudaError_t rope_inplace(float* x, int ldx, int col0, int blk, int n_blocks, int
 cudaError_t attention(const float* Q, int ldq, int qcol, const float* K, int ldk, int kcol, const float* V, int ldv,
                       int vcol, int H, int D, float scale, const RowMap& qmap, const RowMap& kmap, int max_tq,
                       int max_tk, const int* q_tok, const int* q_cu, int band, float* out, int ldo, cudaStream_t st);
+cudaError_t dense_to_rows(const float* src, int C, const RowMap& map, const int* cu, float* dst, int ld, int col0,
+                          cudaStream_t st);
+cudaError_t seg_broadcast(const float* vec, int C, const RowMap& map, float* dst, int ld, int col0, cudaStream_t st);
 cudaError_t rows_to_dense(const float* src, int ld, int C, const RowMap& map, const int* cu, float* dst,
                           cudaStream_t st);
 

@@ -286,6 +286,48 @@ bool pack_text_encoder(Context& c, Loader& L, const std::string& kp, const std::
   return pack_simple(c, L, kp + "proj_m", nm + ".projm", 0);
 }
 
+
+// ProsodyEncoder (prosody_encoder.py:10-81) under key prefix `kp` -> packs `nm.*`; its AdaLN style FCs
+// are concatenated into nm.fc_W / nm.fc_b (one style_fc launch per call)
+bool pack_prosody(Context& c, Loader& L, const std::string& kp, const std::string& nm) {
+  int n_layers = 0;
+  while (L.has(kp + "attn_layers." + std::to_string(n_layers) + ".conv_q.weight")) ++n_layers;
+  if (n_layers == 0) return false;
+  c.vec_len[nm + ".layers"] = n_layers;
+  FcCat fc;
+  for (int l = 0; l < n_layers; ++l) {
+    const std::string a = kp + "attn_layers." + std::to_string(l) + ".", n = nm + ".l" + std::to_string(l);
+    const HostTensor wq = L.weight(a + "conv_q."), wk = L.weight(a + "conv_k."), wv = L.weight(a + "conv_v.");
+    const HostTensor *bq = L.get(a + "conv_q.bias"), *bk = L.get(a + "conv_k.bias"), *bv = L.get(a + "conv_v.bias");
+    if (!L.ok) return false;
+    const int hid = (int)wq.dim(0);
+    c.vec_len[nm + ".hid"] = hid;
+    Builder b;
+    const int t[2] = {1, 0}, pd[2] = {0, 0}, cp[2] = {pad64(hid), 0};
+    b.init(3 * hid, 1, t, pd, cp);
+    b.rows(0, wq, 0, hid, 0, hid, 0, 1);        b.set_bias(*bq, 0, hid, 0, 1);
+    b.rows(0, wk, 0, hid, 0, hid, hid, 1);      b.set_bias(*bk, 0, hid, hid, 1);
+    b.rows(0, wv, 0, hid, 0, hid, 2 * hid, 1);  b.set_bias(*bv, 0, hid, 2 * hid, 1);
+    c.gemm[n + ".qkv"] = b.upload(c);
+    if (!pack_simple(c, L, a + "conv_o", n + ".o", 0)) return false;
+    const std::string f = kp + "ffn_layers." + std::to_string(l) + ".";
+    if (!pack_simple(c, L, f + "conv_1", n + ".ff1", 0)) return false;
+    if (!pack_simple(c, L, f + "conv_2", n + ".ff2", 0)) return false;
+    if (!pack_simple(c, L, kp + "proj_layers." + std::to_string(l), n + ".proj", 0)) return false;
+    c.vec_len[nm + ".dmodel"] = c.gemm[n + ".proj"].N;
+    for (int j = 1; j <= 2; ++j) {
+      const std::string nk = kp + "norm_layers_" + std::to_string(j) + "." + std::to_string(l) + ".fc.";
+      const HostTensor *w = L.get(nk + "weight"), *bb = L.get(nk + "bias");
+      if (!L.ok) return false;
+      c.fc_off[n + ".n" + std::to_string(j)] = fc.add(*w, *bb);
+    }
+  }
+  c.vec_len[nm + ".J"] = fc.J;
+  put_vec(c, nm + ".fc_W", fc.W);
+  put_vec(c, nm + ".fc_b", fc.b);
+  return true;
+}
+
 }  // namespace
 
 int finalize_weights(Context& c) {
@@ -587,6 +629,18 @@ int finalize_weights(Context& c) {
       if (!c.has(std::string(sl.module) + "/" + sl.kp + "emb.weight")) continue;
       Loader T{c, sl.module};
       if (!pack_text_encoder(c, T, sl.kp, sl.nm)) return fail(c, -3, "missing weight " + T.missing);
+    }
+    const Slot pslots[2] = {{"duration_predictor", "prosody_encoder.", "pr.dp"},
+                            {"pitch_energy_predictor", "prosody_encoder.", "pr.pe"}};
+    for (const Slot& sl : pslots) {
+      if (!c.has(std::string(sl.module) + "/" + sl.kp + "attn_layers.0.conv_q.weight")) continue;
+      Loader T{c, sl.module};
+      if (!pack_prosody(c, T, sl.kp, sl.nm)) return fail(c, -3, "missing weight " + T.missing);
+    }
+    if (c.has("duration_predictor/duration_proj.linear_layer.weight")) {
+      Loader T{c, "duration_predictor"};
+      if (!pack_simple(c, T, "duration_proj.linear_layer", "pr.dp.head", 0))
+        return fail(c, -3, "missing weight " + T.missing);
     }
   }
   for (auto& kv : c.gemm) kv.second.name = kv.first;

@@ -32,13 +32,16 @@ int set_token_layout(Context& c, int n_seg, const int* len_t) {
   const int R = c.LT.R, B = n_seg, nt = c.LT.n_tiles;
   struct Want { const char* name; int ld; };
   const Want wants[] = {{"TA", 128}, {"TB", 128}, {"TC", 128}, {"TX", 128}, {"TO", 128}, {"TQKV", 384},
-                        {"TH", 512}, {"TMU", 256}};
+                        {"TH", 512}, {"TMU", 256},
+                        // prosody encoders (hid <= 320)
+                        {"PX", 320}, {"PY", 320}, {"PB", 320}, {"PO", 320}, {"PQKV", 960}, {"PH", 640}, {"PL", 64}};
   size_t used = 0;
   std::map<std::string, size_t> off;
   for (const Want& w : wants) { off[w.name] = used; used += up1k((size_t)R * w.ld * 4); }
   const char* ints[] = {"tile_seg", "tile_nvalid", "seg_start", "seg_len", "cu"};
   const size_t int_bytes[] = {(size_t)nt * 4, (size_t)nt * 4, (size_t)B * 4, (size_t)B * 4, (size_t)(B + 1) * 4};
   for (int i = 0; i < 5; ++i) { off[ints[i]] = used; used += up1k(int_bytes[i]); }
+  off["GBT"] = used; used += up1k((size_t)B * 8192 * 4);   // style-FC rows of the prosody AdaLNs (J <= 8192)
   if (used > c.tarena_bytes) {
     if (c.tarena) cudaFree(c.tarena);
     c.tarena = nullptr; c.tarena_bytes = 0;
@@ -63,6 +66,7 @@ int set_token_layout(Context& c, int n_seg, const int* len_t) {
   L.d_seg_start = (int*)c.traw["seg_start"]; L.d_seg_len = (int*)c.traw["seg_len"]; L.d_cu = (int*)c.traw["cu"];
   e = cudaDeviceSynchronize();
   if (e != cudaSuccess) return cuda_fail(c, e, "set_token_layout upload");
+  c.traw["GBT"] = c.tarena + off["GBT"];
   c.tsig = sig;
   return 0;
 }
@@ -129,6 +133,55 @@ int run_text_encoder(Context& c, const std::string& nm, const int* d_tokens, flo
   STTS_RET(run_gemm(c, pm, GC_ISLAND, &tx, 0, nullptr, 0, mk_epi(EPI_BIAS, tmu, 0), map, st));
   if (d_mu_tok) STTS_CK(rows_to_dense(tmu.f, tmu.ld, pm.N, map, c.LT.d_cu, d_mu_tok, st));
   if (d_x_tok) STTS_CK(rows_to_dense(tx.f, tx.ld, C, map, c.LT.d_cu, d_x_tok, st));
+  return 0;
+}
+
+// ProsodyEncoder.forward, prosody_encoder.py:63-81.  d_enc_tok token-major dense [sum T, d_model];
+// d_style [n_seg, 64]; d_out_tok [sum T, hid] (hid = d_model + 64); optional d_logits_tok [sum T, 16]
+// (DurationPredictor.duration_proj, duration_predictor.py:30-36) when the head was packed.
+int run_prosody_encoder(Context& c, const std::string& nm, const float* d_enc_tok, const float* d_style,
+                        float* d_out_tok, float* d_logits_tok, cudaStream_t st) {
+  if (!c.finalized || c.vec.count(nm + ".fc_W") == 0) return fail(c, -3, "prosody encoder weights not loaded: " + nm);
+  if (c.LT.total() == 0 || c.tact.count("PX") == 0) return fail(c, -4, "no token layout set");
+  const RowMap map = c.LT.map();
+  const int hid = c.vec_len[nm + ".hid"], dm = c.vec_len[nm + ".dmodel"], J = c.vec_len[nm + ".J"];
+  const int n_layers = c.vec_len[nm + ".layers"], H = 2, D = hid / H, rd = D / 2, sty = hid - dm;
+  if (hid > 320 || J > 8192 || sty != 64) return fail(c, -6, "prosody encoder: unsupported width");
+  Act &px = c.tact["PX"], &py = c.tact["PY"], &pb = c.tact["PB"], &po = c.tact["PO"], &pqkv = c.tact["PQKV"];
+  Act &ph = c.tact["PH"], &pl = c.tact["PL"];
+  float* gb = reinterpret_cast<float*>(c.traw["GBT"]);
+  STTS_CK(style_fc(c.vec[nm + ".fc_W"], c.vec[nm + ".fc_b"], d_style, J, 64, c.LT.n_seg, gb, st));
+  STTS_CK(dense_to_rows(d_enc_tok, dm, map, c.LT.d_cu, px.f, px.ld, 0, st));
+  STTS_CK(seg_broadcast(d_style, sty, map, px.f, px.ld, dm, st));
+  const float scale = 1.0f / std::sqrt((float)D);
+  for (int l = 0; l < n_layers; ++l) {
+    const std::string n = nm + ".l" + std::to_string(l);
+    STTS_RET(run_gemm(c, c.gemm[n + ".qkv"], GC_ISLAND, &px, 0, nullptr, 0, mk_epi(EPI_BIAS, pqkv, 0), map, st));
+    STTS_CK(rope_inplace(pqkv.f, pqkv.ld, 0, hid, 2, H, D, rd, map, st));
+    STTS_CK(attention(pqkv.f, pqkv.ld, 0, pqkv.f, pqkv.ld, hid, pqkv.f, pqkv.ld, 2 * hid, H, D, scale, map, map,
+                      c.max_t, c.max_t, nullptr, nullptr, 0, po.f, po.ld, st));
+    {
+      Epi e = mk_epi(EPI_ADD, pb, 0);
+      e.res = px.f; e.ldr = px.ld; e.rcol0 = 0;
+      STTS_RET(run_gemm(c, c.gemm[n + ".o"], GC_ISLAND, &po, 0, nullptr, 0, e, map, st));
+    }
+    STTS_CK(row_ln(pb.f, pb.ld, hid, map, gb + c.fc_off[n + ".n1"], nullptr, J, 1e-5f, 0, py.f, py.ld, st));
+    STTS_RET(run_gemm(c, c.gemm[n + ".ff1"], GC_ISLAND, &py, 0, nullptr, 0, mk_epi(EPI_RELU, ph, 0), map, st));
+    {
+      Epi e = mk_epi(EPI_ADD, pb, 0);
+      e.res = py.f; e.ldr = py.ld; e.rcol0 = 0;
+      STTS_RET(run_gemm(c, c.gemm[n + ".ff2"], GC_ISLAND, &ph, 0, nullptr, 0, e, map, st));
+    }
+    STTS_CK(row_ln(pb.f, pb.ld, hid, map, gb + c.fc_off[n + ".n2"], nullptr, J, 1e-5f, 0, py.f, py.ld, st));
+    // x = cat([proj(x), style]): the style columns of PX are still in place
+    STTS_RET(run_gemm(c, c.gemm[n + ".proj"], GC_ISLAND, &py, 0, nullptr, 0, mk_epi(EPI_BIAS, px, 0), map, st));
+  }
+  if (d_out_tok) STTS_CK(rows_to_dense(px.f, px.ld, hid, map, c.LT.d_cu, d_out_tok, st));
+  if (d_logits_tok) {
+    if (c.gemm.count(nm + ".head") == 0) return fail(c, -3, "duration head not loaded");
+    STTS_RET(run_gemm(c, c.gemm[nm + ".head"], GC_ISLAND, &px, 0, nullptr, 0, mk_epi(EPI_BIAS, pl, 0), map, st));
+    STTS_CK(rows_to_dense(pl.f, pl.ld, 16, map, c.LT.d_cu, d_logits_tok, st));
+  }
   return 0;
 }
 

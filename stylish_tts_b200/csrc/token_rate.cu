@@ -254,4 +254,43 @@ cudaError_t rows_to_dense(const float* src, int ld, int C, const RowMap& map, co
   return cudaGetLastError();
 }
 
+// token-major dense [sum T, C] -> packed rows, columns [col0, col0 + C)
+__global__ void __launch_bounds__(256) dense_to_rows_kernel(const float* __restrict__ src, int C, RowMap map,
+                                                            const int* __restrict__ cu, float* __restrict__ dst,
+                                                            int ld, int col0) {
+  const int tile = blockIdx.x;
+  const int seg = map.tile_seg[tile];
+  if (seg < 0) return;
+  const int nvalid = map.tile_nvalid[tile];
+  const int t0 = tile * 128 - map.seg_start[seg];
+  for (int i = threadIdx.x; i < nvalid * C; i += blockDim.x) {
+    const int lr = i / C, c = i - lr * C;
+    dst[(size_t)(tile * 128 + lr) * ld + col0 + c] = src[(size_t)(cu[seg] + t0 + lr) * C + c];
+  }
+}
+
+cudaError_t dense_to_rows(const float* src, int C, const RowMap& map, const int* cu, float* dst, int ld, int col0,
+                          cudaStream_t st) {
+  dense_to_rows_kernel<<<map.n_tiles, 256, 0, st>>>(src, C, map, cu, dst, ld, col0);
+  return cudaGetLastError();
+}
+
+// dst[row, col0 + j] = vec[seg, j]  (style broadcast to every token: torch.cat([x, style.expand]), prosody_encoder.py:66-67)
+__global__ void __launch_bounds__(256) seg_broadcast_kernel(const float* __restrict__ vec, int C, RowMap map,
+                                                            float* __restrict__ dst, int ld, int col0) {
+  const int tile = blockIdx.x;
+  const int seg = map.tile_seg[tile];
+  if (seg < 0) return;
+  const int nvalid = map.tile_nvalid[tile];
+  for (int i = threadIdx.x; i < nvalid * C; i += blockDim.x) {
+    const int lr = i / C, c = i - lr * C;
+    dst[(size_t)(tile * 128 + lr) * ld + col0 + c] = vec[(size_t)seg * C + c];
+  }
+}
+
+cudaError_t seg_broadcast(const float* vec, int C, const RowMap& map, float* dst, int ld, int col0, cudaStream_t st) {
+  seg_broadcast_kernel<<<map.n_tiles, 256, 0, st>>>(vec, C, map, dst, ld, col0);
+  return cudaGetLastError();
+}
+
 }  // namespace stts

@@ -118,6 +118,21 @@ class Engine:
                                                self._stream()))
         return mu, x
 
+    def prosody_encoder(self, which: str, enc_tok: torch.Tensor, style: torch.Tensor, hid: int,
+                        want_logits: bool = False):
+        """ProsodyEncoder.forward (prosody_encoder.py:63-81) on the current token layout.  enc_tok
+        token-major [sum T, d_model]; style [B, 64].  Returns (out [sum T, hid], logits [sum T, 16] | None)."""
+        n = int(enc_tok.shape[0])
+        if n != sum(self.len_t):
+            raise ValueError("token count does not match the token layout")
+        enc_tok = enc_tok.to(torch.float32).contiguous()
+        style = style.to(torch.float32).contiguous()
+        out = torch.empty((n, hid), dtype=torch.float32, device=self.device)
+        logits = torch.empty((n, 16), dtype=torch.float32, device=self.device) if want_logits else None
+        self._check(self.lib.stts_prosody_encoder(self.h, which.encode(), _ptr(enc_tok), _ptr(style), _ptr(out),
+                                                  _ptr(logits), self._stream()))
+        return out, logits
+
     def workspace_bytes(self) -> int:
         return int(self.lib.stts_workspace_bytes(self.h))
 

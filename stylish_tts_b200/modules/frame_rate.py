@@ -310,6 +310,7 @@ class PitchEnergyPredictor(_EngineOwner):
 
     def forward(self, text_encoding, text_lengths, alignment, style):
         frame_token = alignment.argmax(dim=1)
+        self.prosody_encoder.attach_native(self.engine(), "pitch_energy_predictor")
         prosody = self.prosody_encoder(text_encoding, style, text_lengths)
         x = self.compute_cross(prosody, frame_token, style, text_lengths)
         b, _, f = x.shape

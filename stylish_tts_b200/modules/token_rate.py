@@ -279,7 +279,44 @@ class ProsodyEncoder(nn.Module):
         self.norm_layers_2 = nn.ModuleList([StyleLayerNorm(sty_dim, hid) for _ in range(nlayers)])
         self.proj_layers = nn.ModuleList([nn.Conv1d(hid, d_model, 1) for _ in range(nlayers)])
 
-    def forward(self, x, style, x_lengths):
+    def attach_native(self, engine, which: str):
+        """Use a context that holds this encoder's weights as ``which``/prosody_encoder.*"""
+        object.__setattr__(self, "_native", (engine, which))
+
+    def _engine(self):
+        if getattr(self, "_native", None) is None:
+            from ..engine import Engine
+            dev = self.proj_layers[0].weight.device
+            if dev.type != "cuda":
+                raise RuntimeError("stylish_tts_b200 modules run on a B200 only (no CPU fallback)")
+            eng = Engine(dev)
+            eng.load_state("pitch_energy_predictor", self.state_dict(), prefix="prosody_encoder.")
+            eng.finalize()
+            object.__setattr__(self, "_native", (eng, "pitch_energy_predictor"))
+        return self._native
+
+    def load_state_dict(self, state_dict, strict: bool = True, assign: bool = False):
+        object.__setattr__(self, "_native", None)
+        return super().load_state_dict(state_dict, strict=strict, assign=assign)
+
+    @property
+    def hidden(self) -> int:
+        return self.proj_layers[0].weight.shape[1]
+
+    def forward(self, x, style, x_lengths, host_lengths=None):
+        """prosody_encoder.py:63-81 in libstts_b200 (stts_prosody_encoder).  x [B, d_model, T] -> [B, T, hid]."""
+        lengths = [int(v) for v in (host_lengths if host_lengths is not None else x_lengths.tolist())]
+        eng, which = self._engine()
+        b, _, tmax = x.shape
+        pos = torch.arange(tmax, device=x.device)[None, :]
+        valid = pos < torch.as_tensor(lengths, device=x.device)[:, None]
+        eng.set_token_layout(lengths)
+        out_t, _ = eng.prosody_encoder(which, x.transpose(1, 2)[valid], style, self.hidden)
+        out = torch.zeros((b, tmax, self.hidden), dtype=torch.float32, device=x.device)
+        out[valid] = out_t
+        return out
+
+    def forward_torch(self, x, style, x_lengths):
         x_mask = length_mask(x_lengths, x.shape[2]).unsqueeze(1).to(x.dtype)
         pair = x_mask.unsqueeze(2) * x_mask.unsqueeze(-1)
         sty = style.unsqueeze(2).expand(-1, -1, x.shape[2])
@@ -333,13 +370,25 @@ class DurationPredictor(nn.Module):
         return self._eng
 
     def forward(self, texts, text_lengths, host_lengths=None):
-        self.text_encoder.attach_native(self._engine(), "duration_predictor")
-        enc, _, _ = self.text_encoder(texts, text_lengths, host_lengths=host_lengths)
-        style = self.style_encoder(enc, text_lengths)
-        return self.duration_proj(self.prosody_encoder(enc, style, text_lengths))
+        """duration_predictor.py:30-36: text encoder and prosody encoder + duration_proj run in
+        libstts_b200 on the packed token layout; the (tiny) style encoder is still a torch module."""
+        eng = self._engine()
+        lengths = [int(v) for v in (host_lengths if host_lengths is not None else text_lengths.tolist())]
+        self.text_encoder.attach_native(eng, "duration_predictor")
+        b, tmax = texts.shape
+        tok, valid = _pack_tokens(texts, lengths)
+        mu_t, _ = self.text_encoder.encode_packed(tok, lengths)
+        enc = torch.zeros((b, tmax, mu_t.shape[1]), dtype=torch.float32, device=texts.device)
+        enc[valid] = mu_t
+        style = self.style_encoder(enc.transpose(1, 2), text_lengths)
+        _, logits_t = eng.prosody_encoder("duration_predictor", mu_t, style, self.prosody_encoder.hidden,
+                                          want_logits=True)
+        logits = torch.zeros((b, tmax, logits_t.shape[1]), dtype=torch.float32, device=texts.device)
+        logits[valid] = logits_t
+        return logits
 
     def forward_torch(self, texts, text_lengths):
         """Op-by-op torch statement of the same computation (CPU host tests of the mirror only)."""
         enc, _, _ = self.text_encoder.forward_torch(texts, text_lengths)
         style = self.style_encoder(enc, text_lengths)
-        return self.duration_proj(self.prosody_encoder(enc, style, text_lengths))
+        return self.duration_proj(self.prosody_encoder.forward_torch(enc, style, text_lengths))

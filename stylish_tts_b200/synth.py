@@ -91,7 +91,8 @@ class Synthesizer:
         pe_enc, _, _ = nets["pe_text_encoder"](tok, lens, host_lengths=T)
         pe_style = nets["pe_text_style_encoder"](pe_enc, lens)
         pep = nets["pitch_energy_predictor"]
-        prosody = pep.prosody_encoder(pe_enc, pe_style, lens)
+        pep.prosody_encoder.attach_native(eng, "pitch_energy_predictor")
+        prosody = pep.prosody_encoder(pe_enc, pe_style, lens, host_lengths=T)
         Fmax = max(F_list)
         f_lens = torch.tensor(F_list, dtype=torch.int64, device=dev)
         # padded [B, Fmax] frame -> token map from the packed index vector

@@ -88,6 +88,9 @@ def run(precision="fp32", g=None, tag=""):
         pe_enc, _, _ = nets["pe_text_encoder"](tokens, lens)
         rec("pe_text", pe_enc, g["tap.pe_text"])
         rec("dur_logits", nets["duration_predictor"](tokens, lens), g["tap.dur_logits"])
+        pep.prosody_encoder.attach_native(peng, "pitch_energy_predictor")
+        rec("pe_prosody", pep.prosody_encoder(g["tap.pe_text"].to(dev), g["tap.pe_style"].to(dev), lens),
+            g["tap.pe_prosody"])
 
     def sec_pitch___energy_towers_on_the_reference_s():  # pitch / energy towers on the reference's cross-attended frames
         peng.set_layout([F_], None)

@@ -94,7 +94,7 @@ def test_cross_attention_ragged_mode_equals_b1(cpu_nets):
     with torch.no_grad():
         enc, _, _ = cpu_nets["pe_text_encoder"].forward_torch(tk, ln)
         sty = cpu_nets["pe_text_style_encoder"](enc, ln)
-        pros = pep.prosody_encoder(enc, sty, ln)
+        pros = pep.prosody_encoder.forward_torch(enc, sty, ln)
         x = pep.compute_cross(pros, ft, sty, ln, frame_lengths=fl)
         for i in range(2):
             taps = {}
