@@ -263,7 +263,9 @@ def main():
 
     if rank == 0:
         pk = peaks()
-        tc = [p for p in prof if p["backend"] == (1 if args.precision == "bf16" else (2 if args.precision == "tf32x3" else 0))]
+        # every tcgen05 conv-as-GEMM launch of the timed region (bf16, bf16x3 and tf32x3 backends; the
+        # split modes count their ALGORITHMIC FLOPs once, not per pass); fp32 mode = the CUDA-core kernel
+        tc = [p for p in prof if (p["backend"] in (1, 2, 3) if args.precision != "fp32" else p["backend"] == 0)]
         tc_ms = sum(p["ms"] for p in tc)
         tc_fl = sum(p["flops"] for p in tc)
         top = max(prof, key=lambda p: p["ms"]) if prof else None

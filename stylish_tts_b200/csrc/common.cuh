@@ -50,6 +50,7 @@ struct Epi {
   __nv_bfloat16* outh; int ldh; int colh0;   // optional bf16 twin of `out`
   float* out2; int ldo2; int col20;
   __nv_bfloat16* outh2; int ldh2; int colh20;  // optional bf16 twin of `out2` (EPI_STFT)
+  __nv_bfloat16* outl; __nv_bfloat16* outl2;   // optional bf16 residual twins (x - bf16(x)) of out / out2: bf16x3 operands
   const float* bias;           // [N] (already permuted for the pair kinds) or null
   const float* res; int ldr; int rcol0;
   const float* segvec; int ldseg;            // per-utterance vector, row = segment
@@ -60,6 +61,10 @@ struct Epi {
 };
 
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + __expf(-x)); }
+// bf16 residual of x: bf16(x - float(bf16(x))).  x = hi + lo to ~2^-17 relative (bf16x3 operand split)
+__device__ __forceinline__ __nv_bfloat16 bf16_lo(float x) {
+  return __float2bfloat16_rn(x - __bfloat162float(__float2bfloat16_rn(x)));
+}
 
 // One thread owns row r (valid, segment seg) and NV consecutive output columns starting at n0
 // (n0 % NV == 0, NV even).  Shared by the SIMT and the tcgen05 kernels.
@@ -236,13 +241,16 @@ struct EpiPair {
     }
     return t;
   }
-  static __device__ __forceinline__ void store2(float* o, __nv_bfloat16* oh, float x0, float x1, bool both) {
+  static __device__ __forceinline__ void store2(float* o, __nv_bfloat16* oh, float x0, float x1, bool both,
+                                                __nv_bfloat16* ol = nullptr) {
     if (both) {
       *reinterpret_cast<float2*>(o) = make_float2(x0, x1);
       if (oh != nullptr) *reinterpret_cast<__nv_bfloat162*>(oh) = __floats2bfloat162_rn(x0, x1);
+      if (ol != nullptr) { ol[0] = bf16_lo(x0); ol[1] = bf16_lo(x1); }
     } else {
       o[0] = x0;
       if (oh != nullptr) oh[0] = __float2bfloat16_rn(x0);
+      if (ol != nullptr) ol[0] = bf16_lo(x0);
     }
   }
   __device__ __forceinline__ void apply(const Epi& e, int r, int seg, int seg_first_row, float a0, float a1,
@@ -261,7 +269,8 @@ struct EpiPair {
         x0 = 0.5f * x0 * (1.f + erff(x0 * 0.70710678118654752440f));
         x1 = 0.5f * x1 * (1.f + erff(x1 * 0.70710678118654752440f));
       }
-      store2(e.out + (size_t)r * e.ldo + e.col0 + n, e.outh ? e.outh + (size_t)r * e.ldh + e.colh0 + n : nullptr, x0, x1, v1);
+      store2(e.out + (size_t)r * e.ldo + e.col0 + n, e.outh ? e.outh + (size_t)r * e.ldh + e.colh0 + n : nullptr, x0, x1, v1,
+             e.outl ? e.outl + (size_t)r * e.ldh + e.colh0 + n : nullptr);
     } else if constexpr (KIND == EPI_RESSKIP) {
       const float x0 = a0 + b0, x1 = a1 + b1;
       if (n < e.split) {
@@ -302,6 +311,8 @@ struct EpiPair {
         e.out2[(size_t)r * e.ldo2 + e.col20 + c] = ph;
         if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = __float2bfloat16_rn(mag);
         if (e.outh2 != nullptr) e.outh2[(size_t)r * e.ldh2 + e.colh20 + c] = __float2bfloat16_rn(ph);
+        if (e.outl != nullptr) e.outl[(size_t)r * e.ldh + e.colh0 + c] = bf16_lo(mag);
+        if (e.outl2 != nullptr) e.outl2[(size_t)r * e.ldh2 + e.colh20 + c] = bf16_lo(ph);
       }
     }
   }
@@ -313,6 +324,7 @@ struct EpiPair {
 struct KSeg {
   const float* A; int lda; int col0;         // fp32 operand
   const __nv_bfloat16* Ah; int ldah; int colh0;  // bf16 twin (tensor-core bf16 mode)
+  const __nv_bfloat16* Al;                   // bf16 residual twin (bf16x3 mode), same geometry as Ah
   int taps; int pad; int cin_pad;            // cin_pad % 64 == 0
   int rows;                                  // rows allocated in A (bounds for zero fill)
 };
@@ -322,6 +334,7 @@ struct ConvGemm {
   int n_kseg;
   const float* W;                 // [Npad, Ktot] fp32, K-major
   const __nv_bfloat16* Wh;        // bf16 copy
+  const __nv_bfloat16* Wl;        // bf16 residual W - bf16(W)  (bf16x3 mode)
   int Ktot;                       // sum taps*cin_pad
   int Npad;                       // multiple of 128
   Epi epi;

@@ -483,7 +483,8 @@ __global__ void __launch_bounds__(256) adaln2_kernel(const float* __restrict__ x
                                                      const float* __restrict__ gb1, const float* __restrict__ gb2,
                                                      int ldgb, float eps, float* __restrict__ y1,
                                                      float* __restrict__ y2, int ldy, __nv_bfloat16* __restrict__ y1h,
-                                                     __nv_bfloat16* __restrict__ y2h, int ldyh) {
+                                                     __nv_bfloat16* __restrict__ y2h, int ldyh,
+                                                     __nv_bfloat16* __restrict__ y1l, __nv_bfloat16* __restrict__ y2l) {
   constexpr int C = 512;
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
@@ -520,6 +521,10 @@ __global__ void __launch_bounds__(256) adaln2_kernel(const float* __restrict__ x
         *reinterpret_cast<__nv_bfloat162*>(y1h + r * ldyh + c) = __floats2bfloat162_rn(o1[0], o1[1]);
         *reinterpret_cast<__nv_bfloat162*>(y1h + r * ldyh + c + 2) = __floats2bfloat162_rn(o1[2], o1[3]);
       }
+      if (y1l != nullptr) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) y1l[r * ldyh + c + j] = bf16_lo(o1[j]);
+      }
       if (y2 != nullptr) {
         const float4 g2 = *reinterpret_cast<const float4*>(gb2 + (size_t)seg * ldgb + c);
         const float4 b2 = *reinterpret_cast<const float4*>(gb2 + (size_t)seg * ldgb + C + c);
@@ -530,14 +535,19 @@ __global__ void __launch_bounds__(256) adaln2_kernel(const float* __restrict__ x
           *reinterpret_cast<__nv_bfloat162*>(y2h + r * ldyh + c) = __floats2bfloat162_rn(o2[0], o2[1]);
           *reinterpret_cast<__nv_bfloat162*>(y2h + r * ldyh + c + 2) = __floats2bfloat162_rn(o2[2], o2[3]);
         }
+        if (y2l != nullptr) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) y2l[r * ldyh + c + j] = bf16_lo(o2[j]);
+        }
       }
     }
   }
 }
 
 cudaError_t adaln2(const float* x, int ldx, const RowMap& map, const float* gb1, const float* gb2, int ldgb, float eps,
-                   float* y1, float* y2, int ldy, __nv_bfloat16* y1h, __nv_bfloat16* y2h, int ldyh, cudaStream_t st) {
-  adaln2_kernel<<<map.n_tiles, 256, 0, st>>>(x, ldx, map, gb1, gb2, ldgb, eps, y1, y2, ldy, y1h, y2h, ldyh);
+                   float* y1, float* y2, int ldy, __nv_bfloat16* y1h, __nv_bfloat16* y2h, int ldyh, __nv_bfloat16* y1l,
+                   __nv_bfloat16* y2l, cudaStream_t st) {
+  adaln2_kernel<<<map.n_tiles, 256, 0, st>>>(x, ldx, map, gb1, gb2, ldgb, eps, y1, y2, ldy, y1h, y2h, ldyh, y1l, y2l);
   return cudaGetLastError();
 }
 
@@ -616,6 +626,27 @@ __global__ void __launch_bounds__(256) rowdot_kernel(const float* __restrict__ x
 cudaError_t rowdot(const float* x, int ldx, int C, const RowMap& map, const float* w, const float* bias, const int* cu,
                    float* dense, cudaStream_t st) {
   rowdot_kernel<<<map.n_tiles, 256, 0, st>>>(x, ldx, C, map, w, bias, cu, dense);
+  return cudaGetLastError();
+}
+
+// bf16 hi / residual twins of the first C columns of the valid rows, recomputed from the fp32 master
+__global__ void __launch_bounds__(256) twin_refresh_kernel(const float* __restrict__ f, int ld, int C, RowMap map,
+                                                           __nv_bfloat16* __restrict__ h, __nv_bfloat16* __restrict__ l) {
+  const int tile = blockIdx.x;
+  if (map.tile_seg[tile] < 0) return;
+  const int nvalid = map.tile_nvalid[tile];
+  for (int i = blockIdx.y * blockDim.x + threadIdx.x; i < nvalid * C; i += gridDim.y * blockDim.x) {
+    const int lr = i / C, c = i - lr * C;
+    const size_t o = (size_t)(tile * 128 + lr) * ld + c;
+    const float x = f[o];
+    if (h != nullptr) h[o] = __float2bfloat16_rn(x);
+    if (l != nullptr) l[o] = bf16_lo(x);
+  }
+}
+cudaError_t twin_refresh(const float* f, int ld, int C, const RowMap& map, __nv_bfloat16* h, __nv_bfloat16* l,
+                         cudaStream_t st) {
+  dim3 grid(map.n_tiles, 4);
+  twin_refresh_kernel<<<grid, 256, 0, st>>>(f, ld, C, map, h, l);
   return cudaGetLastError();
 }
 

@@ -25,6 +25,7 @@ struct PackedGemm {
   float* Wf = nullptr;            // exact fp32                     [Npad, Ktot]
   float* Whl = nullptr;           // tf32 hi rows then lo rows      [2 * Npad, Ktot]
   __nv_bfloat16* Wh = nullptr;    // bf16                           [Npad, Ktot]
+  __nv_bfloat16* Wl = nullptr;    // bf16 residual W - bf16(W)      [Npad, Ktot]
   float* bias = nullptr;          // [Npad] (zeros when the layer has no bias)
   std::string name;               // layer name (profiling)
   double k_real = 0;              // un-padded K (algorithmic FLOPs = 2 * rows * N * k_real)
@@ -33,6 +34,7 @@ struct PackedGemm {
 struct Act {          // an activation buffer: fp32 + optional bf16 twin, same ld
   float* f = nullptr;
   __nv_bfloat16* h = nullptr;
+  __nv_bfloat16* l = nullptr;   // bf16 residual twin (operands of the bf16x3 island GEMMs)
   int ld = 0;
   int rows = 0;
 };

@@ -143,19 +143,21 @@ __device__ __forceinline__ float rna_tf32(float x) {
   return __uint_as_float(r);
 }
 
-enum { MODE_BF16 = 0, MODE_TF32X3 = 1 };
+enum { MODE_BF16 = 0, MODE_TF32X3 = 1, MODE_BF16X3 = 2 };
 
 template <int MODE, int BN>
 struct Cfg {
   static constexpr bool kTF32 = (MODE == MODE_TF32X3);
+  static constexpr bool kSplit = (MODE != MODE_BF16);     // hi / lo operand pairs, 3 MMAs per k-step
   static constexpr int kElem = kTF32 ? 4 : 2;
   static constexpr int kBK = 128 / kElem;                 // elements per 128-byte swizzle row: 32 / 64
   static constexpr int kUmmaK = 32 / kElem;               // 8 (tf32) / 16 (bf16)
   static constexpr int kATile = 128 * 128;                // bytes
   static constexpr int kBTile = BN * 128;                 // bytes
-  static constexpr int kStageBytes = kTF32 ? (2 * kATile + 2 * kBTile) : (kATile + kBTile);
-  static constexpr int kStages = kTF32 ? (BN == 128 ? 3 : 2) : (BN == 128 ? 6 : 4);
-  static constexpr int kTxBytes = kTF32 ? (kATile + 2 * kBTile) : (kATile + kBTile);
+  static constexpr int kStageBytes = kSplit ? (2 * kATile + 2 * kBTile) : (kATile + kBTile);
+  static constexpr int kStages = kSplit ? (BN == 128 ? 3 : 2) : (BN == 128 ? 6 : 4);
+  // tf32x3: the A residual is computed in shared memory by the converter warps; bf16x3: it is loaded
+  static constexpr int kTxBytes = kTF32 ? (kATile + 2 * kBTile) : (kSplit ? 2 * kATile + 2 * kBTile : kATile + kBTile);
   static constexpr int kEpiWarps = BN / 16;                // one 64-column slab x 32-row quarter per warp
   static constexpr int kThreads = 64 + 32 * kEpiWarps;
   static constexpr int kSmem = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
@@ -172,6 +174,7 @@ struct TcParams {
 template <int MODE, int BN, int KIND>
 __global__ void __launch_bounds__(64 + 2 * BN, 1)
 conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant__ CUtensorMap mapA1,
+                    const __grid_constant__ CUtensorMap mapA0lo, const __grid_constant__ CUtensorMap mapA1lo,
                     const __grid_constant__ CUtensorMap mapW, const __grid_constant__ CUtensorMap mapWlo,
                     const TcParams p, const Epi epi, const RowMap map) {
   using C = Cfg<MODE, BN>;
@@ -228,7 +231,11 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
         mbar_expect_tx(&full[stage], C::kTxBytes);
         const CUtensorMap* ma = (ks == 0) ? &mapA0 : &mapA1;
         tma_load_2d(sp, ma, &full[stage], p.col0[ks] + cc * C::kBK, m0 + tap - p.pad[ks]);
-        if constexpr (C::kTF32) {
+        if constexpr (C::kSplit) {
+          if constexpr (!C::kTF32) {
+            const CUtensorMap* ml = (ks == 0) ? &mapA0lo : &mapA1lo;
+            tma_load_2d(sp + C::kATile, ml, &full[stage], p.col0[ks] + cc * C::kBK, m0 + tap - p.pad[ks]);
+          }
           tma_load_2d(sp + 2 * C::kATile, &mapW, &full[stage], kcol, n0);
           tma_load_2d(sp + 2 * C::kATile + C::kBTile, &mapWlo, &full[stage], kcol, n0);
         } else {
@@ -252,12 +259,12 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
 #pragma unroll
         for (int k = 0; k < C::kBK / C::kUmmaK; ++k) {
           const uint32_t koff = k * 32;  // bytes inside the 128B swizzle row
-          if constexpr (C::kTF32) {
+          if constexpr (C::kSplit) {
             const uint32_t a_lo = a_hi + C::kATile, b_hi = a_hi + 2 * C::kATile, b_lo = b_hi + C::kBTile;
             // small terms first, then the leading term
-            tc_mma<true>(tmem_base, make_sdesc(a_lo + koff), make_sdesc(b_hi + koff), C::kIdesc, (ch | k) != 0);
-            tc_mma<true>(tmem_base, make_sdesc(a_hi + koff), make_sdesc(b_lo + koff), C::kIdesc, 1);
-            tc_mma<true>(tmem_base, make_sdesc(a_hi + koff), make_sdesc(b_hi + koff), C::kIdesc, 1);
+            tc_mma<C::kTF32>(tmem_base, make_sdesc(a_lo + koff), make_sdesc(b_hi + koff), C::kIdesc, (ch | k) != 0);
+            tc_mma<C::kTF32>(tmem_base, make_sdesc(a_hi + koff), make_sdesc(b_lo + koff), C::kIdesc, 1);
+            tc_mma<C::kTF32>(tmem_base, make_sdesc(a_hi + koff), make_sdesc(b_hi + koff), C::kIdesc, 1);
           } else {
             const uint32_t b = a_hi + C::kATile;
             tc_mma<false>(tmem_base, make_sdesc(a_hi + koff), make_sdesc(b + koff), C::kIdesc, (ch | k) != 0);
@@ -409,29 +416,38 @@ template <int MODE, int BN, int KIND>
 cudaError_t launch_one(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
   using C = Cfg<MODE, BN>;
   constexpr int elem = C::kElem;
-  CUtensorMap mA[2], mW, mWlo;
+  CUtensorMap mA[2], mAlo[2], mW, mWlo;
   TcParams p{};
   p.n_kseg = g.n_kseg;
   p.n_chunks = 0;
   for (int s = 0; s < 2; ++s) {
     const KSeg& ks = g.seg[s < g.n_kseg ? s : 0];
-    const void* base = (MODE == MODE_BF16) ? (const void*)ks.Ah : (const void*)ks.A;
-    const int ld = (MODE == MODE_BF16) ? ks.ldah : ks.lda;
+    const void* base = (MODE == MODE_TF32X3) ? (const void*)ks.A : (const void*)ks.Ah;
+    const int ld = (MODE == MODE_TF32X3) ? ks.lda : ks.ldah;
     if (base == nullptr) return cudaErrorInvalidValue;
     if (!get_map(base, ks.rows, ld, elem, 128, &mA[s])) return cudaErrorNotSupported;
+    mAlo[s] = mA[s];
+    if (MODE == MODE_BF16X3) {
+      if (ks.Al == nullptr) return cudaErrorInvalidValue;
+      if (!get_map(ks.Al, ks.rows, ld, elem, 128, &mAlo[s])) return cudaErrorNotSupported;
+    }
     if (s < g.n_kseg) {
       p.taps[s] = ks.taps;
       p.pad[s] = ks.pad;
       p.cin_chunks[s] = ks.cin_pad / C::kBK;
-      p.col0[s] = (MODE == MODE_BF16) ? ks.colh0 : ks.col0;
+      p.col0[s] = (MODE == MODE_TF32X3) ? ks.col0 : ks.colh0;
       p.n_chunks += ks.taps * p.cin_chunks[s];
     }
   }
   if (MODE == MODE_BF16) {
     if (!get_map(g.Wh, g.Npad, g.Ktot, 2, BN, &mW)) return cudaErrorNotSupported;
     mWlo = mW;
+  } else if (MODE == MODE_BF16X3) {
+    if (g.Wl == nullptr) return cudaErrorInvalidValue;
+    if (!get_map(g.Wh, g.Npad, g.Ktot, 2, BN, &mW)) return cudaErrorNotSupported;
+    if (!get_map(g.Wl, g.Npad, g.Ktot, 2, BN, &mWlo)) return cudaErrorNotSupported;
   } else {
-    // W holds hi (tf32-truncated) in rows [0, Npad) and lo in rows [Npad, 2*Npad)
+    // W holds hi (tf32-rounded) in rows [0, Npad) and lo in rows [Npad, 2*Npad)
     if (!get_map(g.W, g.Npad, g.Ktot, 4, BN, &mW)) return cudaErrorNotSupported;
     if (!get_map(g.W + (size_t)g.Npad * g.Ktot, g.Npad, g.Ktot, 4, BN, &mWlo)) return cudaErrorNotSupported;
   }
@@ -443,7 +459,7 @@ cudaError_t launch_one(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
     attr_done = true;
   }
   dim3 grid((g.epi.N + BN - 1) / BN, map.n_tiles);
-  kern<<<grid, C::kThreads, C::kSmem, st>>>(mA[0], mA[1], mW, mWlo, p, g.epi, map);
+  kern<<<grid, C::kThreads, C::kSmem, st>>>(mA[0], mA[1], mAlo[0], mAlo[1], mW, mWlo, p, g.epi, map);
   return cudaGetLastError();
 }
 
@@ -484,6 +500,9 @@ cudaError_t conv_gemm_tc_bf16(const ConvGemm& g, const RowMap& map, cudaStream_t
 }
 cudaError_t conv_gemm_tc_tf32x3(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
   return launch_mode<MODE_TF32X3>(g, map, st);
+}
+cudaError_t conv_gemm_tc_bf16x3(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
+  return launch_mode<MODE_BF16X3>(g, map, st);
 }
 
 }  // namespace stts

@@ -112,10 +112,15 @@ int set_layout(Context& c, int n_seg, const int* len_f, const int* len_f4) {
   }
   ArenaPlan plan;
   std::map<std::string, size_t> off_f, off_h;
+  // bf16 residual twins (x - bf16(x)) of the operands of the island GEMMs: bf16x3 mode
+  const char* lo_names[] = {"AMPN", "PHN", "CATP", "SPEC", "HS", "HP"};
+  auto wants_lo = [&](const std::string& n) { for (const char* q : lo_names) if (n == q) return true; return false; };
+  std::map<std::string, size_t> off_l;
   for (auto& w : wants) {
     const int R = (w.rate == 4 ? c.L4.R : c.LF.R) + w.extra_rows;
     off_f[w.name] = plan.take((size_t)R * w.ld * 4);
-    if (w.twin) off_h[w.name] = plan.take((size_t)R * w.ld * 2);
+    if (w.twin || wants_lo(w.name)) off_h[w.name] = plan.take((size_t)R * w.ld * 2);
+    if (wants_lo(w.name)) off_l[w.name] = plan.take((size_t)R * w.ld * 2);
   }
   struct RawWant { std::string name; size_t bytes; };
   const int R4 = c.L4.R, RF = c.LF.R, B = n_seg;
@@ -168,7 +173,8 @@ int set_layout(Context& c, int n_seg, const int* len_f, const int* len_f4) {
     a.ld = w.ld;
     a.rows = (w.rate == 4 ? c.L4.R : c.LF.R) + w.extra_rows;
     a.f = reinterpret_cast<float*>(c.arena + off_f[w.name]);
-    a.h = w.twin ? reinterpret_cast<__nv_bfloat16*>(c.arena + off_h[w.name]) : nullptr;
+    a.h = off_h.count(w.name) ? reinterpret_cast<__nv_bfloat16*>(c.arena + off_h[w.name]) : nullptr;
+    a.l = off_l.count(w.name) ? reinterpret_cast<__nv_bfloat16*>(c.arena + off_l[w.name]) : nullptr;
     c.act[w.name] = a;
   }
   for (auto& r : raws) { c.raw[r.name] = c.arena + off_raw[r.name]; c.raw_bytes[r.name] = r.bytes; }
@@ -239,6 +245,14 @@ int run_gemm(Context& c, const PackedGemm& pg, int cls, const Act* a0, int a0_co
     if (c.precision == 0) backend = 0;
     else if (c.precision == 1) backend = (cls == GC_ISLAND) ? 2 : 1;
     else backend = 2;
+    // bf16 mode: an island whose operands carry bf16 hi / residual twins runs as bf16x3
+    // (hi*hi + hi*lo + lo*hi, ~2^-17 relative: half the tensor time of tf32x3)
+    if (c.precision == 1 && backend == 2 && pg.Wl != nullptr) {
+      bool ok = true;
+      const Act* ops[2] = {a0, a1};
+      for (int s = 0; s < pg.n_kseg; ++s) ok = ok && ops[s] != nullptr && ops[s]->h != nullptr && ops[s]->l != nullptr;
+      if (ok) backend = 3;
+    }
   }
   const long long map_valid_rows = (map.seg_len == c.LF.d_seg_len) ? c.LF.total()
                                    : (map.seg_len == c.LT.d_seg_len) ? c.LT.total()
@@ -253,6 +267,7 @@ int run_gemm(Context& c, const PackedGemm& pg, int cls, const Act* a0, int a0_co
     KSeg& k = g.seg[s];
     k.A = as[s]->f; k.lda = as[s]->ld; k.col0 = cols[s];
     k.Ah = as[s]->h; k.ldah = as[s]->ld; k.colh0 = cols[s];
+    k.Al = as[s]->l;
     k.taps = pg.taps[s]; k.pad = pg.pad[s]; k.cin_pad = pg.cin_pad[s];
     k.rows = as[s]->rows;
     if (cols[s] + k.cin_pad > as[s]->ld) return fail(c, -2, "run_gemm: K slice exceeds the operand row");
@@ -260,6 +275,7 @@ int run_gemm(Context& c, const PackedGemm& pg, int cls, const Act* a0, int a0_co
   }
   g.W = (backend == 2) ? pg.Whl : pg.Wf;
   g.Wh = pg.Wh;
+  g.Wl = pg.Wl;
   g.Ktot = pg.Ktot;
   g.Npad = pg.Npad;
   g.epi = epi_in;
@@ -285,6 +301,7 @@ int run_gemm(Context& c, const PackedGemm& pg, int cls, const Act* a0, int a0_co
   if (bracket) { cudaStreamSynchronize(st); cudaProfilerStart(); }
   if (backend == 0) e = conv_gemm_simt(g, map, st);
   else if (backend == 1) e = conv_gemm_tc_bf16(g, map, st);
+  else if (backend == 3) e = conv_gemm_tc_bf16x3(g, map, st);
   else e = conv_gemm_tc_tf32x3(g, map, st);
   if (bracket) { cudaStreamSynchronize(st); cudaProfilerStop(); }
   if (e != cudaSuccess) return cuda_fail(c, e, "conv_gemm launch");
@@ -309,6 +326,7 @@ struct Stage {
     e.kind = kind;
     e.out = dst.f; e.ldo = dst.ld; e.col0 = col0;
     e.outh = tw(dst); e.ldh = dst.ld; e.colh0 = col0;
+    e.outl = twins ? dst.l : nullptr;
     e.scale = 1.f;
     return e;
   }
@@ -535,6 +553,7 @@ int run_generator_core(Context& c, const float* d_style, const float* d_noise, c
     Epi e = S.epi(EPI_STFT, hs, 0);
     e.out2 = hp.f; e.ldo2 = hp.ld; e.col20 = 0;
     e.outh2 = S.tw(hp); e.ldh2 = hp.ld; e.colh20 = 0;
+    e.outl2 = S.twins ? hp.l : nullptr;
     e.seg_start = c.L4.d_seg_start;
     STTS_RET(run_gemm(c, c.gemm["stft"], GC_ISLAND, &src, 0, nullptr, 0, e, map, st));
   }
@@ -590,7 +609,8 @@ int run_generator_tail(Context& c, const float* d_style, float* d_audio, float* 
   }
   // two AdaLN heads + output convs k7 over cat[AdaLN(x), prior]   (generator.py:417-423)
   STTS_CK(adaln2(xg.f, xg.ld, map, gb + c.fc_off["gen.amp_norm"], gb + c.fc_off["gen.phase_norm"], c.J_gen, 1e-5f,
-                 ampn.f, phn.f, ampn.ld, S.tw(ampn), S.tw(phn), ampn.ld, st));
+                 ampn.f, phn.f, ampn.ld, S.tw(ampn), S.tw(phn), ampn.ld, S.twins ? ampn.l : nullptr,
+                 S.twins ? phn.l : nullptr, st));
   {
     Epi e = S.epi(EPI_BIAS, la, 0);
     STTS_RET(run_gemm(c, c.gemm["gen.amp_head"], GC_ISLAND, &ampn, 0, &catp, 512, e, map, st));
@@ -598,7 +618,7 @@ int run_generator_tail(Context& c, const float* d_style, float* d_audio, float* 
     STTS_RET(run_gemm(c, c.gemm["gen.phase_head"], GC_ISLAND, &phn, 0, &catp, 768, e2, map, st));
   }
   // replicate pad + exp / cos / sin -> inverse DFT x window -> overlap-add, envelope, tanh
-  STTS_CK(polar_spec(la.f, ph.f, la.ld, 1025, map, spec.f, spec.ld, nullptr, 0, st));
+  STTS_CK(polar_spec(la.f, ph.f, la.ld, 1025, map, spec.f, spec.ld, S.tw(spec), spec.ld, S.twins ? spec.l : nullptr, st));
   {
     Epi e = S.epi(EPI_BIAS, yf, 0);
     STTS_RET(run_gemm(c, c.gemm["istft"], GC_ISLAND, &spec, 0, nullptr, 0, e, map_p1, st));
@@ -634,6 +654,10 @@ int run_generator_from_stft(Context& c, const float* d_mel, const float* d_style
   // dense [1025, L] per utterance: element offsets 1025 * cu[b] are not tabulated, derive from C = 1025 view
   STTS_CK(transpose_in(d_har_spec, c.L4.d_off[3], c.L4.d_cs, 1025, map, hs.f, hs.ld, 0, S.tw(hs), hs.ld, 0, st));
   STTS_CK(transpose_in(d_har_phase, c.L4.d_off[3], c.L4.d_cs, 1025, map, hp.f, hp.ld, 0, S.tw(hp), hp.ld, 0, st));
+  if (S.twins) {
+    STTS_CK(twin_refresh(hs.f, hs.ld, 1025, map, nullptr, hs.l, st));
+    STTS_CK(twin_refresh(hp.f, hp.ld, 1025, map, nullptr, hp.l, st));
+  }
   return run_generator_tail(c, d_style, d_audio, d_logamp, d_phase, st);
 }
 

@@ -83,16 +83,21 @@ struct Builder {
     for (int s = 0; s < 2; ++s) { p.taps[s] = taps[s]; p.pad[s] = pad[s]; p.cin_pad[s] = cin_pad[s]; }
     const size_t n = (size_t)Npad * Ktot;
     std::vector<float> hl(2 * n);
-    std::vector<uint16_t> bf(n);
+    std::vector<uint16_t> bf(n), bl(n);
     for (size_t i = 0; i < n; ++i) {
       const float hi = trunc_tf32(W[i]);
       hl[i] = hi;
       hl[n + i] = trunc_tf32(W[i] - hi);
       bf[i] = f2bf(W[i]);
+      uint32_t u = (uint32_t)bf[i] << 16;
+      float bh;
+      std::memcpy(&bh, &u, 4);
+      bl[i] = f2bf(W[i] - bh);
     }
     p.Wf = dev_upload(c, W.data(), n);
     p.Whl = dev_upload(c, hl.data(), 2 * n);
     p.Wh = reinterpret_cast<__nv_bfloat16*>(dev_upload(c, bf.data(), n));
+    p.Wl = reinterpret_cast<__nv_bfloat16*>(dev_upload(c, bl.data(), n));
     p.bias = dev_upload(c, bias.data(), (size_t)Npad);
     return p;
   }
@@ -103,7 +108,7 @@ int pad64(int c) { return (c + 63) / 64 * 64; }
 }  // namespace
 
 void free_pack(PackedGemm& p) {
-  cudaFree(p.Wf); cudaFree(p.Whl); cudaFree(p.Wh); cudaFree(p.bias);
+  cudaFree(p.Wf); cudaFree(p.Whl); cudaFree(p.Wh); cudaFree(p.Wl); cudaFree(p.bias);
   p = PackedGemm();
 }
 
