@@ -165,6 +165,7 @@ def main():
     ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU work for the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-flush", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="launch every step eagerly (no CUDA graph replay)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else max(args.warmup, 0)
 
@@ -204,15 +205,22 @@ def main():
     audio_host = torch.empty(300 * sum(frames), dtype=torch.float32).pin_memory()
     flush_buf = None if args.no_flush else torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
+    use_graph = not args.no_graph
+
     def step_resident():
         if flush_buf is not None:
             flush_buf.fill_(1)
-        return syn.synthesize(tok_dev, durations=dur_dev, frames=frames)
+        return syn.synthesize(tok_dev, durations=dur_dev, frames=frames, graph=use_graph)
+
+    def step_eager():
+        if flush_buf is not None:
+            flush_buf.fill_(1)
+        return syn.synthesize(tok_dev, durations=dur_dev, frames=frames, graph=False)
 
     def step_e2e():
         if flush_buf is not None:
             flush_buf.fill_(1)
-        out = syn.synthesize(tok_host, durations=dur_host, frames=frames)
+        out = syn.synthesize(tok_host, durations=dur_host, frames=frames, graph=use_graph)
         audio_host.copy_(out["audio_flat"], non_blocking=True)
         torch.cuda.current_stream().synchronize()
         return out
@@ -241,13 +249,20 @@ def main():
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
+    ms_total = timed(step_resident, args.steps)
+    clocks = sampler.stop() if rank == 0 else None
+    # Per-GEMM CUDA events cannot be recorded inside a graph replay: the roofline pass times the same
+    # K steps again, launched eagerly (same kernels, same inputs), with an event pair around every
+    # conv-as-GEMM launch.  Kernel launches are counted on this eager pass (one step = the same
+    # launches the graph replays).
+    for _ in range(2):
+        step_eager()
     eng.set_profiling(True)
     l0 = eng.launch_count()
-    ms_total = timed(step_resident, args.steps)
+    ms_eager = timed(step_eager, args.steps)
     launches = eng.launch_count() - l0
     prof = eng.profile()
     eng.set_profiling(False)
-    clocks = sampler.stop() if rank == 0 else None
 
     for _ in range(2):
         step_e2e()
@@ -278,7 +293,8 @@ def main():
                       if args.precision != "fp32" else "conv_gemm_simt_kernel",
             "peak_source": pk["source"] + " bf16_tflops_sustained",
             "gemm_ms_per_step": sum(p["ms"] for p in prof) / args.steps,
-            "gemm_share_of_step": sum(p["ms"] for p in prof) / ms_total,
+            "gemm_share_of_step": sum(p["ms"] for p in prof) / ms_eager,
+            "eager_ms_per_step": ms_eager / args.steps,
             "top_layer": {"name": top["name"], "ms_per_step": top["ms"] / args.steps,
                           "tflops": top["flops"] / (top["ms"] / 1e3) / 1e12} if top else None,
             "step_tflops_algorithmic": algorithmic_flops(tokens, frames) * args.steps / (ms_total / 1e3) / 1e12,
@@ -295,7 +311,7 @@ def main():
             "config": {"workload": f"BASELINE configs[1]: batch {BATCH} mixed-length utterances 0.25-10 s per GPU "
                                    f"({audio_s:.1f} audio-s, {sum(int(t.numel()) for t in tokens)} phonemes), default model.yml, "
                                    "fixture (seeded random-init) weights, synthetic durations",
-                       "precision": args.precision, "parallelism": f"utterance-sharded x{world}, no collective in the forward",
+                       "precision": args.precision, "launch": "CUDA graph replay per step" if use_graph else "eager", "parallelism": f"utterance-sharded x{world}, no collective in the forward",
                        "l2": "256 MiB flush write before every step; per-step working set >> 126 MB L2"
                              if flush_buf is not None else "no flush",
                        "workspace_bytes": eng.workspace_bytes()},

@@ -35,13 +35,23 @@ int set_token_layout(Context& c, int n_seg, const int* len_t) {
                         {"TH", 512}, {"TMU", 256},
                         // prosody encoders (hid <= 320)
                         {"PX", 320}, {"PY", 320}, {"PB", 320}, {"PO", 320}, {"PQKV", 960}, {"PH", 640}, {"PL", 64}};
+  // three independent buffer sets ("slots"): the speech / pitch-energy / duration chains only share
+  // the tokens, so the host may enqueue them on three streams (synth.py) without aliasing scratch
   size_t used = 0;
   std::map<std::string, size_t> off;
-  for (const Want& w : wants) { off[w.name] = used; used += up1k((size_t)R * w.ld * 4); }
+  for (int slot = 0; slot < 3; ++slot)
+    for (const Want& w : wants) {
+      off[std::string(w.name) + "#" + std::to_string(slot)] = used;
+      used += up1k((size_t)R * w.ld * 4);
+    }
   const char* ints[] = {"tile_seg", "tile_nvalid", "seg_start", "seg_len", "cu"};
   const size_t int_bytes[] = {(size_t)nt * 4, (size_t)nt * 4, (size_t)B * 4, (size_t)B * 4, (size_t)(B + 1) * 4};
   for (int i = 0; i < 5; ++i) { off[ints[i]] = used; used += up1k(int_bytes[i]); }
-  off["GBT"] = used; used += up1k((size_t)B * 8192 * 4);   // style-FC rows of the prosody AdaLNs (J <= 8192)
+  for (int slot = 0; slot < 3; ++slot) {   // style-FC rows of the prosody AdaLNs (J <= 8192)
+    off["GBT#" + std::to_string(slot)] = used;
+    used += up1k((size_t)B * 8192 * 4);
+  }
+
   if (used > c.tarena_bytes) {
     if (c.tarena) cudaFree(c.tarena);
     c.tarena = nullptr; c.tarena_bytes = 0;
@@ -52,10 +62,12 @@ int set_token_layout(Context& c, int n_seg, const int* len_t) {
   e = cudaMemset(c.tarena, 0, used);
   if (e != cudaSuccess) return cuda_fail(c, e, "token workspace memset");
   c.tact.clear(); c.traw.clear();
-  for (const Want& w : wants) {
-    Act a; a.ld = w.ld; a.rows = R; a.f = reinterpret_cast<float*>(c.tarena + off[w.name]); a.h = nullptr;
-    c.tact[w.name] = a;
-  }
+  for (int slot = 0; slot < 3; ++slot)
+    for (const Want& w : wants) {
+      const std::string key = std::string(w.name) + "#" + std::to_string(slot);
+      Act a; a.ld = w.ld; a.rows = R; a.f = reinterpret_cast<float*>(c.tarena + off[key]); a.h = nullptr;
+      c.tact[key] = a;
+    }
   Layout& L = c.LT;
   const void* srcs[] = {L.tile_seg.data(), L.tile_nvalid.data(), L.seg_start.data(), L.seg_len.data(), L.cu.data()};
   for (int i = 0; i < 5; ++i) {
@@ -66,7 +78,7 @@ int set_token_layout(Context& c, int n_seg, const int* len_t) {
   L.d_seg_start = (int*)c.traw["seg_start"]; L.d_seg_len = (int*)c.traw["seg_len"]; L.d_cu = (int*)c.traw["cu"];
   e = cudaDeviceSynchronize();
   if (e != cudaSuccess) return cuda_fail(c, e, "set_token_layout upload");
-  c.traw["GBT"] = c.tarena + off["GBT"];
+  for (int slot = 0; slot < 3; ++slot) c.traw["GBT#" + std::to_string(slot)] = c.tarena + off["GBT#" + std::to_string(slot)];
   c.tsig = sig;
   return 0;
 }
@@ -85,10 +97,11 @@ Epi mk_epi(int kind, const Act& dst, int col0) {
 int run_text_encoder(Context& c, const std::string& nm, const int* d_tokens, float* d_mu_tok, float* d_x_tok,
                      cudaStream_t st) {
   if (!c.finalized || c.vec.count(nm + ".emb") == 0) return fail(c, -3, "text encoder weights not loaded: " + nm);
-  if (c.LT.total() == 0 || c.tact.count("TX") == 0) return fail(c, -4, "no token layout set");
+  if (c.LT.total() == 0 || c.tact.count("TX#0") == 0) return fail(c, -4, "no token layout set");
   const RowMap map = c.LT.map();
-  Act &ta = c.tact["TA"], &tb = c.tact["TB"], &tcb = c.tact["TC"], &tx = c.tact["TX"], &to = c.tact["TO"];
-  Act &tqkv = c.tact["TQKV"], &th = c.tact["TH"], &tmu = c.tact["TMU"];
+  const std::string sl = nm == "te.sp" ? "#0" : (nm == "te.pe" ? "#1" : "#2");
+  Act &ta = c.tact["TA" + sl], &tb = c.tact["TB" + sl], &tcb = c.tact["TC" + sl], &tx = c.tact["TX" + sl];
+  Act &to = c.tact["TO" + sl], &tqkv = c.tact["TQKV" + sl], &th = c.tact["TH" + sl], &tmu = c.tact["TMU" + sl];
   const int C = 128, H = 8, D = C / H, rd = D / 2;
   STTS_CK(embed_tokens(d_tokens, c.LT.d_cu, c.vec[nm + ".emb"], C, c.vec_len[nm + ".vocab"], map, ta.f, ta.ld, st));
   // ---- prenet: 3 x (conv k5 -> channel LayerNorm (eps 1e-4) -> ReLU), then x + proj(y)
@@ -142,14 +155,15 @@ int run_text_encoder(Context& c, const std::string& nm, const int* d_tokens, flo
 int run_prosody_encoder(Context& c, const std::string& nm, const float* d_enc_tok, const float* d_style,
                         float* d_out_tok, float* d_logits_tok, cudaStream_t st) {
   if (!c.finalized || c.vec.count(nm + ".fc_W") == 0) return fail(c, -3, "prosody encoder weights not loaded: " + nm);
-  if (c.LT.total() == 0 || c.tact.count("PX") == 0) return fail(c, -4, "no token layout set");
+  if (c.LT.total() == 0 || c.tact.count("PX#0") == 0) return fail(c, -4, "no token layout set");
+  const std::string sl = nm == "pr.pe" ? "#1" : "#2";
   const RowMap map = c.LT.map();
   const int hid = c.vec_len[nm + ".hid"], dm = c.vec_len[nm + ".dmodel"], J = c.vec_len[nm + ".J"];
   const int n_layers = c.vec_len[nm + ".layers"], H = 2, D = hid / H, rd = D / 2, sty = hid - dm;
   if (hid > 320 || J > 8192 || sty != 64) return fail(c, -6, "prosody encoder: unsupported width");
-  Act &px = c.tact["PX"], &py = c.tact["PY"], &pb = c.tact["PB"], &po = c.tact["PO"], &pqkv = c.tact["PQKV"];
-  Act &ph = c.tact["PH"], &pl = c.tact["PL"];
-  float* gb = reinterpret_cast<float*>(c.traw["GBT"]);
+  Act &px = c.tact["PX" + sl], &py = c.tact["PY" + sl], &pb = c.tact["PB" + sl], &po = c.tact["PO" + sl];
+  Act &pqkv = c.tact["PQKV" + sl], &ph = c.tact["PH" + sl], &pl = c.tact["PL" + sl];
+  float* gb = reinterpret_cast<float*>(c.traw["GBT" + sl]);
   STTS_CK(style_fc(c.vec[nm + ".fc_W"], c.vec[nm + ".fc_b"], d_style, J, 64, c.LT.n_seg, gb, st));
   STTS_CK(dense_to_rows(d_enc_tok, dm, map, c.LT.d_cu, px.f, px.ld, 0, st));
   STTS_CK(seg_broadcast(d_style, sty, map, px.f, px.ld, dm, st));

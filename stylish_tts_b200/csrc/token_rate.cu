@@ -51,7 +51,7 @@ __global__ void __launch_bounds__(256) row_ln_kernel(const float* x, int ldx, in
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const float* ga = seg_stride ? gamma + (size_t)seg * seg_stride : gamma;
   const float* be = seg_stride ? gamma + (size_t)seg * seg_stride + C : beta;
-  for (int lr = warp; lr < nvalid; lr += 8) {
+  for (int lr = warp + 8 * blockIdx.y; lr < nvalid; lr += 8 * gridDim.y) {
     const size_t r = (size_t)tile * 128 + lr;
     float v[16];
     float s = 0.f;
@@ -86,7 +86,7 @@ __global__ void __launch_bounds__(256) row_ln_kernel(const float* x, int ldx, in
 cudaError_t row_ln(const float* x, int ldx, int C, const RowMap& map, const float* gamma, const float* beta,
                    int seg_stride, float eps, int relu, float* y, int ldy, cudaStream_t st) {
   if (C > 512) return cudaErrorInvalidValue;
-  row_ln_kernel<<<map.n_tiles, 256, 0, st>>>(x, ldx, C, map, gamma, beta, seg_stride, eps, relu, y, ldy);
+  row_ln_kernel<<<dim3(map.n_tiles, 4), 256, 0, st>>>(x, ldx, C, map, gamma, beta, seg_stride, eps, relu, y, ldy);
   return cudaGetLastError();
 }
 
@@ -103,7 +103,7 @@ __global__ void __launch_bounds__(256) rope_kernel(float* __restrict__ x, int ld
   const int h = rd >> 1;
   const int per_row = n_blocks * H * h;
   const int pos0 = tile * 128 - map.seg_start[seg];
-  for (int i = threadIdx.x; i < nvalid * per_row; i += blockDim.x) {
+  for (int i = blockIdx.y * blockDim.x + threadIdx.x; i < nvalid * per_row; i += gridDim.y * blockDim.x) {
     const int lr = i / per_row;
     int k = i - lr * per_row;
     const int b = k / (H * h);
@@ -122,7 +122,7 @@ __global__ void __launch_bounds__(256) rope_kernel(float* __restrict__ x, int ld
 
 cudaError_t rope_inplace(float* x, int ldx, int col0, int blk, int n_blocks, int H, int D, int rd, const RowMap& map,
                          cudaStream_t st) {
-  rope_kernel<<<map.n_tiles, 256, 0, st>>>(x, ldx, col0, blk, n_blocks, H, D, rd, map);
+  rope_kernel<<<dim3(map.n_tiles, 8), 256, 0, st>>>(x, ldx, col0, blk, n_blocks, H, D, rd, map);
   return cudaGetLastError();
 }
 

@@ -153,11 +153,35 @@ class _Transformer(nn.Module):
         return x * x_mask
 
 
-def _pack_tokens(x: torch.Tensor, lengths):
-    """padded [B, Tmax] + host lengths -> concatenated [sum T] and the boolean validity mask [B, Tmax]."""
-    pos = torch.arange(x.shape[1], device=x.device)[None, :]
-    valid = pos < torch.as_tensor(lengths, device=x.device)[:, None]
-    return x[valid], valid
+class TokenPack:
+    """Host-known utterance lengths of a padded [B, Tmax] batch plus the device index vectors that
+    move between the padded layout and the concatenated [sum T] layout the C library takes.  Built
+    once per batch shape (H2D copies happen here, never inside a forward: the forwards stay free of
+    host synchronisation and are CUDA-graph capturable)."""
+
+    def __init__(self, lengths, tmax: int, device):
+        self.lengths = [int(v) for v in lengths]
+        self.tmax = int(tmax)
+        idx = [b * self.tmax + t for b, n in enumerate(self.lengths) for t in range(n)]
+        self.flat_idx = torch.tensor(idx, dtype=torch.int64).to(device)
+        self.n = len(idx)
+
+    @staticmethod
+    def of(host_lengths, x_lengths, tmax, device) -> "TokenPack":
+        if isinstance(host_lengths, TokenPack):
+            return host_lengths
+        lengths = host_lengths if host_lengths is not None else x_lengths.tolist()
+        return TokenPack(lengths, tmax, device)
+
+    def gather(self, padded: torch.Tensor) -> torch.Tensor:
+        """[B, Tmax, ...] -> [sum T, ...]"""
+        return padded.reshape((-1,) + tuple(padded.shape[2:])).index_select(0, self.flat_idx)
+
+    def scatter(self, rows: torch.Tensor, b: int) -> torch.Tensor:
+        """[sum T, C] -> zero-padded [B, Tmax, C]"""
+        out = torch.zeros((b * self.tmax, rows.shape[1]), dtype=rows.dtype, device=rows.device)
+        out.index_copy_(0, self.flat_idx, rows)
+        return out.view(b, self.tmax, rows.shape[1])
 
 
 class TextEncoder(nn.Module):
@@ -205,16 +229,14 @@ class TextEncoder(nn.Module):
         return eng.text_encoder(which, tokens_cat, self.inter_dim)
 
     def forward(self, x, x_lengths, spks=None, host_lengths=None):
-        # host_lengths: the same lengths as Python ints, when the caller has them (saves a D2H sync)
-        lengths = [int(v) for v in (host_lengths if host_lengths is not None else x_lengths.tolist())]
+        # host_lengths: the same lengths as Python ints or a TokenPack, when the caller has them
+        # (saves the D2H sync of x_lengths.tolist())
         b, tmax = x.shape
-        tok, valid = _pack_tokens(x, lengths)
-        mu_t, h_t = self.encode_packed(tok, lengths)
-        mu = torch.zeros((b, tmax, self.inter_dim), dtype=torch.float32, device=x.device)
-        h = torch.zeros((b, tmax, self.n_channels), dtype=torch.float32, device=x.device)
-        mu[valid] = mu_t
-        h[valid] = h_t
-        return mu.transpose(1, 2), h.transpose(1, 2), valid.unsqueeze(1).to(torch.float32)
+        pack = TokenPack.of(host_lengths, x_lengths, tmax, x.device)
+        mu_t, h_t = self.encode_packed(pack.gather(x), pack.lengths)
+        valid = torch.arange(tmax, device=x.device)[None, :] < x_lengths[:, None]
+        return (pack.scatter(mu_t, b).transpose(1, 2), pack.scatter(h_t, b).transpose(1, 2),
+                valid.unsqueeze(1).to(torch.float32))
 
     def forward_torch(self, x, x_lengths, spks=None):
         h = (self.emb(x) * math.sqrt(self.n_channels)).transpose(1, 2)
@@ -305,16 +327,12 @@ class ProsodyEncoder(nn.Module):
 
     def forward(self, x, style, x_lengths, host_lengths=None):
         """prosody_encoder.py:63-81 in libstts_b200 (stts_prosody_encoder).  x [B, d_model, T] -> [B, T, hid]."""
-        lengths = [int(v) for v in (host_lengths if host_lengths is not None else x_lengths.tolist())]
         eng, which = self._engine()
         b, _, tmax = x.shape
-        pos = torch.arange(tmax, device=x.device)[None, :]
-        valid = pos < torch.as_tensor(lengths, device=x.device)[:, None]
-        eng.set_token_layout(lengths)
-        out_t, _ = eng.prosody_encoder(which, x.transpose(1, 2)[valid], style, self.hidden)
-        out = torch.zeros((b, tmax, self.hidden), dtype=torch.float32, device=x.device)
-        out[valid] = out_t
-        return out
+        pack = TokenPack.of(host_lengths, x_lengths, tmax, x.device)
+        eng.set_token_layout(pack.lengths)
+        out_t, _ = eng.prosody_encoder(which, pack.gather(x.transpose(1, 2)), style, self.hidden)
+        return pack.scatter(out_t, b)
 
     def forward_torch(self, x, style, x_lengths):
         x_mask = length_mask(x_lengths, x.shape[2]).unsqueeze(1).to(x.dtype)
@@ -373,19 +391,14 @@ class DurationPredictor(nn.Module):
         """duration_predictor.py:30-36: text encoder and prosody encoder + duration_proj run in
         libstts_b200 on the packed token layout; the (tiny) style encoder is still a torch module."""
         eng = self._engine()
-        lengths = [int(v) for v in (host_lengths if host_lengths is not None else text_lengths.tolist())]
         self.text_encoder.attach_native(eng, "duration_predictor")
         b, tmax = texts.shape
-        tok, valid = _pack_tokens(texts, lengths)
-        mu_t, _ = self.text_encoder.encode_packed(tok, lengths)
-        enc = torch.zeros((b, tmax, mu_t.shape[1]), dtype=torch.float32, device=texts.device)
-        enc[valid] = mu_t
-        style = self.style_encoder(enc.transpose(1, 2), text_lengths)
+        pack = TokenPack.of(host_lengths, text_lengths, tmax, texts.device)
+        mu_t, _ = self.text_encoder.encode_packed(pack.gather(texts), pack.lengths)
+        style = self.style_encoder(pack.scatter(mu_t, b).transpose(1, 2), text_lengths)
         _, logits_t = eng.prosody_encoder("duration_predictor", mu_t, style, self.prosody_encoder.hidden,
                                           want_logits=True)
-        logits = torch.zeros((b, tmax, logits_t.shape[1]), dtype=torch.float32, device=texts.device)
-        logits[valid] = logits_t
-        return logits
+        return pack.scatter(logits_t, b)
 
     def forward_torch(self, texts, text_lengths):
         """Op-by-op torch statement of the same computation (CPU host tests of the mirror only)."""

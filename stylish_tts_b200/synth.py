@@ -16,11 +16,12 @@ from torch import nn
 from .config import ModelConfig
 from .engine import Engine
 from .modules.frame_rate import build_model
+from .modules.token_rate import TokenPack
 
 
 class Synthesizer:
     def __init__(self, nets: Optional[Dict[str, nn.Module]] = None, device="cuda:0", precision: str = "fp32",
-                 model_config=None):
+                 model_config=None, use_graphs: bool = False):
         self.device = torch.device(device)
         self.nets = nets if nets is not None else build_model(model_config or ModelConfig())
         for m in self.nets.values():
@@ -28,10 +29,14 @@ class Synthesizer:
             for p in m.parameters():
                 p.requires_grad_(False)
         self.engine = Engine(self.device)
+        self._side_streams = (torch.cuda.Stream(self.device), torch.cuda.Stream(self.device))
+        self.use_graphs = use_graphs
+        self._graphs, self._packs, self._finfo = {}, {}, {}
         self.reload_weights()
         self.engine.set_precision(precision)
 
     def reload_weights(self):
+        self._graphs.clear() if hasattr(self, "_graphs") else None
         self.engine.load_state("speech_predictor", self.nets["speech_predictor"].state_dict())
         self.engine.load_state("pitch_energy_predictor", self.nets["pitch_energy_predictor"].state_dict())
         self.engine.load_state("pe_text_encoder", self.nets["pe_text_encoder"].state_dict())
@@ -44,13 +49,14 @@ class Synthesizer:
 
     def set_precision(self, precision: str):
         self.engine.set_precision(precision)
+        self._graphs.clear()          # captured graphs bake the kernel variants of the old precision
 
     # ------------------------------------------------------------------ the call
     @torch.no_grad()
     def synthesize(self, tokens: Sequence[torch.Tensor], durations: Optional[Sequence[torch.Tensor]] = None,
                    noise: Optional[Sequence[Dict[str, torch.Tensor]]] = None, want_spec: bool = False,
                    want_intermediates: bool = False, frames: Optional[Sequence[int]] = None,
-                   pitch_energy: Optional[Sequence] = None) -> Dict[str, object]:
+                   pitch_energy: Optional[Sequence] = None, graph: Optional[bool] = None) -> Dict[str, object]:
         """tokens[b]: int64 [T_b] (host or device).  durations[b]: optional integer durations
         overriding the predicted ones (they are still predicted and returned).  noise[b]:
         optional dict(prior [1,128,4F], source [1,1,300F], phase [1,1]) -- the three reference
@@ -58,28 +64,119 @@ class Synthesizer:
         optional curves fed to the speech stage instead of the predicted ones (the predicted ones are
         still computed and returned) -- the harmonic source integrates f0 over the whole utterance, so
         waveform parity is only defined for identical pitch input (DESIGN.md "conditioning").
+        graph: replay a CUDA graph captured for this batch shape (token counts, frame counts).  Needs
+        host-known frame counts (``durations`` + ``frames``) and torch-drawn noise; default = the
+        Synthesizer's ``use_graphs`` setting.  Outputs of a graph call live in the graph's static
+        buffers: consume (or clone) them before the next call with the same shape.
         Returns dict(audio=[...[300 F_b]], duration_pred=[...], pitch=[...], energy=[...], ...)."""
-        dev, eng, nets = self.device, self.engine, self.nets
+        dev = self.device
         B = len(tokens)
         T = [int(t.numel()) for t in tokens]
         Tmax = max(T)
-        tok = torch.zeros((B, Tmax), dtype=torch.int64, device=dev)
-        for b, t in enumerate(tokens):
-            tok[b, : T[b]] = t.to(dev, non_blocking=True)
-        lens = torch.tensor(T, dtype=torch.int64, device=dev)
-
-        # ---- durations (duration_predictor + prediction_to_duration)
-        logits = nets["duration_predictor"](tok, lens, host_lengths=T)                      # [B, Tmax, 16]
-        dur_all = eng.durations(logits.reshape(B * Tmax, 16)).view(B, Tmax)  # int32
-        valid = torch.arange(Tmax, device=dev)[None, :] < lens[:, None]
-        dur_pred = dur_all * valid
+        pack = self._token_pack(T, Tmax)
+        # one H2D copy of the concatenated tokens, then a device scatter into the padded batch
+        tok_cat = torch.cat([t.reshape(-1) for t in tokens]).to(dev, torch.int64, non_blocking=True)
+        tok = torch.zeros(B * Tmax, dtype=torch.int64, device=dev).index_copy_(0, pack.flat_idx, tok_cat).view(B, Tmax)
+        dur_used, F_list = None, None
         if durations is not None:
-            dur_used = torch.zeros((B, Tmax), dtype=torch.int32, device=dev)
-            for b, d in enumerate(durations):
-                dur_used[b, : T[b]] = d.to(dev, torch.int32, non_blocking=True)
+            dur_cat = torch.cat([d.reshape(-1) for d in durations]).to(dev, torch.int32, non_blocking=True)
+            dur_used = torch.zeros(B * Tmax, dtype=torch.int32, device=dev).index_copy_(0, pack.flat_idx, dur_cat)
+            dur_used = dur_used.view(B, Tmax)
             # host-known frame counts: no device sync (pass `frames` when the durations live on the device)
             F_list = [int(f) for f in frames] if frames is not None else [int(d.sum()) for d in durations]
+        use_graph = self.use_graphs if graph is None else graph
+        if (use_graph and F_list is not None and noise is None and pitch_energy is None and not want_intermediates):
+            res = self._graphed(tok, pack, dur_used, F_list, want_spec)
         else:
+            res = self._core(tok, pack, dur_used, F_list, noise, pitch_energy, want_spec, want_intermediates)
+        return self._package(res, T, want_spec)
+
+    def _token_pack(self, T, Tmax) -> TokenPack:
+        key = (tuple(T), Tmax)
+        if key not in self._packs:
+            if len(self._packs) > 64:
+                self._packs.clear()
+            self._packs[key] = TokenPack(T, Tmax, self.device)
+            self._packs[key].lens = torch.tensor(T, dtype=torch.int64).to(self.device)
+        return self._packs[key]
+
+    def _frame_info(self, F_list):
+        key = tuple(F_list)
+        if key not in self._finfo:
+            if len(self._finfo) > 64:
+                self._finfo.clear()
+            self._finfo[key] = torch.tensor(F_list, dtype=torch.int64).to(self.device)
+        return self._finfo[key]
+
+    def _graphed(self, tok, pack, dur_used, F_list, want_spec):
+        """One CUDA graph per batch shape: the whole step (three token-rate chains on forked streams,
+        length regulation, frame-rate path) is replayed with no host work between kernels."""
+        key = (tuple(pack.lengths), tuple(F_list), bool(want_spec))
+        ent = self._graphs.get(key)
+        if ent is None:
+            if len(self._graphs) >= 8:
+                self._graphs.clear()
+            s_tok, s_dur = tok.clone(), dur_used.clone()
+            self._frame_info(F_list)
+            cur = torch.cuda.current_stream(self.device)
+            warm = torch.cuda.Stream(self.device)
+            warm.wait_stream(cur)
+            with torch.cuda.stream(warm):        # allocations, layouts, lazy attribute setup happen here
+                for _ in range(2):
+                    self._core(s_tok, pack, s_dur, F_list, None, None, want_spec, False)
+            cur.wait_stream(warm)
+            torch.cuda.synchronize(self.device)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                res = self._core(s_tok, pack, s_dur, F_list, None, None, want_spec, False)
+            ent = (g, s_tok, s_dur, res)
+            self._graphs[key] = ent
+        g, s_tok, s_dur, res = ent
+        s_tok.copy_(tok)
+        s_dur.copy_(dur_used)
+        g.replay()
+        return res
+
+    def _core(self, tok, pack, dur_used, F_list, noise, pitch_energy, want_spec, want_intermediates):
+        """The device work of one step.  Free of host synchronisation when F_list is given."""
+        dev, eng, nets = self.device, self.engine, self.nets
+        B, Tmax = tok.shape
+        T = pack.lengths
+        lens = pack.lens
+        capturing = torch.cuda.is_current_stream_capturing()
+        # The duration, pitch/energy and speech chains only share the tokens: enqueue them on three
+        # streams (their kernels are small and latency-bound at token rate) and join before the
+        # frame-rate path.  The C library keeps one scratch set per chain (token_pipeline.cu).
+        cur = torch.cuda.current_stream(dev)
+        s_dp, s_sp = self._side_streams
+        s_dp.wait_stream(cur)
+        s_sp.wait_stream(cur)
+
+        # ---- durations (duration_predictor + prediction_to_duration)            [stream s_dp]
+        with torch.cuda.stream(s_dp):
+            logits = nets["duration_predictor"](tok, lens, host_lengths=pack)                   # [B, Tmax, 16]
+            dur_all = eng.durations(logits.reshape(B * Tmax, 16)).view(B, Tmax)  # int32
+        # ---- speech text / style encoders                                        [stream s_sp]
+        sp = nets["speech_predictor"]
+        with torch.cuda.stream(s_sp):
+            sp.text_encoder.attach_native(eng, "speech_predictor")
+            enc, _, _ = sp.text_encoder(tok, lens, host_lengths=pack)
+            style = sp.style_encoder(enc, lens).contiguous()
+            enc_tok = enc.transpose(1, 2).contiguous().view(B * Tmax, 128)
+        # ---- pitch / energy token-rate part                                      [current stream]
+        pe_enc, _, _ = nets["pe_text_encoder"](tok, lens, host_lengths=pack)
+        pe_style = nets["pe_text_style_encoder"](pe_enc, lens)
+        pep = nets["pitch_energy_predictor"]
+        pep.prosody_encoder.attach_native(eng, "pitch_energy_predictor")
+        prosody = pep.prosody_encoder(pe_enc, pe_style, lens, host_lengths=pack)
+
+        cur.wait_stream(s_dp)
+        if not capturing:
+            for t_ in (logits, dur_all):
+                t_.record_stream(cur)
+        valid = torch.arange(Tmax, device=dev)[None, :] < lens[:, None]
+        dur_pred = dur_all * valid
+        if dur_used is None:
             dur_used = dur_pred
             F_list = [int(v) for v in dur_pred.sum(dim=1).tolist()]          # the one unavoidable D2H (SURVEY 7.1)
         F_tot = sum(F_list)
@@ -87,14 +184,9 @@ class Synthesizer:
         cu_frames, idx, _ = eng.frame_index(dur_used.contiguous().view(-1), cu_tok, F_tot)
         eng.set_layout(F_list, [4 * f for f in F_list])
 
-        # ---- pitch / energy
-        pe_enc, _, _ = nets["pe_text_encoder"](tok, lens, host_lengths=T)
-        pe_style = nets["pe_text_style_encoder"](pe_enc, lens)
-        pep = nets["pitch_energy_predictor"]
-        pep.prosody_encoder.attach_native(eng, "pitch_energy_predictor")
-        prosody = pep.prosody_encoder(pe_enc, pe_style, lens, host_lengths=T)
+        # ---- pitch / energy frame-rate part
         Fmax = max(F_list)
-        f_lens = torch.tensor(F_list, dtype=torch.int64, device=dev)
+        f_lens = self._frame_info(F_list)
         # padded [B, Fmax] frame -> token map from the packed index vector
         pos = torch.arange(Fmax, device=dev)[None, :]
         gather = (cu_frames[:-1].to(torch.int64)[:, None] + pos).clamp_(max=max(F_tot - 1, 0))
@@ -107,12 +199,11 @@ class Synthesizer:
             pitch_in = torch.cat([pe[0].reshape(-1) for pe in pitch_energy]).to(dev, torch.float32).contiguous()
             energy_in = torch.cat([pe[1].reshape(-1) for pe in pitch_energy]).to(dev, torch.float32).contiguous()
 
-        # ---- speech
-        sp = nets["speech_predictor"]
-        sp.text_encoder.attach_native(eng, "speech_predictor")
-        enc, _, _ = sp.text_encoder(tok, lens, host_lengths=T)
-        style = sp.style_encoder(enc, lens).contiguous()
-        enc_tok = enc.transpose(1, 2).contiguous().view(B * Tmax, 128)
+        # ---- speech frame-rate path
+        cur.wait_stream(s_sp)
+        if not capturing:
+            for t_ in (enc, style, enc_tok):
+                t_.record_stream(cur)
         if noise is not None:
             n_prior = torch.cat([n["prior"].reshape(-1) for n in noise]).to(dev)
             n_src = torch.cat([n["source"].reshape(-1) for n in noise]).to(dev)
@@ -123,6 +214,15 @@ class Synthesizer:
             n_phase = torch.rand(B, device=dev)
         audio, la, ph = eng.speech_frames(enc_tok, cu_tok, idx, cu_frames, pitch_in, energy_in, style, n_prior, n_src,
                                           n_phase, want_spec=want_spec)
+        res = dict(audio=audio, la=la, ph=ph, dur_pred=dur_pred, pitch=pitch, energy=energy, frames=F_list)
+        if want_intermediates:
+            res.update(pe_cross=x, pe_style=pe_style, sp_style=style, sp_text=enc, pe_text=pe_enc, dur_logits=logits)
+        return res
+
+    @staticmethod
+    def _package(res, T, want_spec) -> Dict[str, object]:
+        B, F_list = len(T), res["frames"]
+        audio, la, ph, dur_pred, pitch, energy = (res[k] for k in ("audio", "la", "ph", "dur_pred", "pitch", "energy"))
         out: Dict[str, object] = {}
         a_off = [0]
         for f in F_list:
@@ -143,10 +243,9 @@ class Synthesizer:
                 s_off.append(s_off[-1] + 1025 * (4 * f + 1))
             out["logamp"] = [la[s_off[b]: s_off[b + 1]].view(1025, 4 * F_list[b] + 1) for b in range(B)]
             out["phase"] = [ph[s_off[b]: s_off[b + 1]].view(1025, 4 * F_list[b] + 1) for b in range(B)]
-        if want_intermediates:
-            out["pe_cross"] = x
-            out["pe_style"], out["sp_style"], out["sp_text"], out["pe_text"] = pe_style, style, enc, pe_enc
-            out["dur_logits"] = logits
+        for k in ("pe_cross", "pe_style", "sp_style", "sp_text", "pe_text", "dur_logits"):
+            if k in res:
+                out[k] = res[k]
         return out
 
     def check(self):

@@ -26,6 +26,14 @@ dd = [d.cuda().to(torch.int32) for d in durs]
 for _ in range(2):
     syn.synthesize(tok, durations=dd, frames=frames)
 torch.cuda.synchronize()
+import time
+torch.cuda.synchronize()
+t0 = time.perf_counter()
+syn.synthesize(tok, durations=dd, frames=frames)
+t1 = time.perf_counter()
+torch.cuda.synchronize()
+t2 = time.perf_counter()
+print(f"host enqueue {1e3 * (t1 - t0):.2f} ms, until device idle {1e3 * (t2 - t0):.2f} ms")
 layer_mode = bool(os.environ.get("STTS_PROFILE_LAYER"))   # the library brackets the named GEMM itself
 if not layer_mode:
     torch.cuda.profiler.start()
