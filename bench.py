@@ -288,7 +288,11 @@ def main():
         achieved = (tc_fl / (tc_ms / 1e3) / 1e12) if tc_ms > 0 else 0.0
         roofline = {
             "bound": "tensor", "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s",
-            "frac": achieved / peak_tf if peak_tf else None, "traffic": None,
+            "frac": achieved / peak_tf if peak_tf else None,
+            # dram__bytes_read.sum + dram__bytes_write.sum of the largest GEMM launch (gen.amp_head) from the
+            # `ncu --set full` capture committed as profiles/r1_full_gen.amp_head.ncu-rep (per launch)
+            "traffic": 198.710016e6 + 202.619136e6 if args.precision == "bf16" else None,
+            "traffic_kernel": "gen.amp_head (algorithmic 161 MB in + 215 MB out)",
             "kernel": "conv_gemm_tc_kernel (tcgen05/TMA implicit-GEMM conv1d), all launches of the timed region"
                       if args.precision != "fp32" else "conv_gemm_simt_kernel",
             "peak_source": pk["source"] + " bf16_tflops_sustained",
