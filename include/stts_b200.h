@@ -86,6 +86,15 @@ int stts_text_encoder(stts_ctx* ctx, const char* which, const int32_t* d_tokens,
 int stts_prosody_encoder(stts_ctx* ctx, const char* which, const float* d_enc_tok, const float* d_style,
                          float* d_out_tok, float* d_logits_tok, void* stream);
 
+/* TextStyleEncoder.forward, text_style_encoder.py:20-26 (conv k7, BasicConvNeXtBlock x n
+ * conv_next.py:18-51, mean over the utterance).  which: "speech_predictor" (its style_encoder.*),
+ * "pe_text_style_encoder", "duration_predictor" (its style_encoder.*).  d_enc_tok token-major dense
+ * [sum T, inter_dim], or NULL = the mu rows stts_text_encoder of the same chain just produced
+ * (speech_predictor <- speech_predictor, pe_text_style_encoder <- pe_text_encoder,
+ * duration_predictor <- duration_predictor).  d_style [n_seg, 64].                                   */
+int stts_text_style_encoder(stts_ctx* ctx, const char* which, const float* d_enc_tok, float* d_style,
+                            void* stream);
+
 /* ---- length regulation ------------------------------------------------------------------------
  * DurationProcessor.prediction_to_duration, utils.py:468-474: logits [n_tokens,16] -> int32.    */
 int stts_durations(stts_ctx* ctx, const float* d_logits, int n_tokens, int32_t* d_dur, void* stream);
@@ -98,9 +107,19 @@ int stts_frame_index(stts_ctx* ctx, const int32_t* d_dur, const int32_t* d_cu_to
 /* ---- pitch / energy towers --------------------------------------------------------------------
  * PitchEnergyPredictor.forward lines 111-119 (pitch_energy_predictor.py): 2 x 3
  * AdaptiveDecoderBlock(320) + 1x1 projections on the cross-attended frames.
- * d_x: dense [320, F_b]; d_style [n_seg, 64]; outputs dense [sum F].                            */
+ * d_x: dense [320, F_b] (NULL = take the frames stts_pe_cross left in the workspace);
+ * d_style [n_seg, 64]; outputs dense [sum F].                                                    */
 int stts_pe_towers(stts_ctx* ctx, const float* d_x, const float* d_style, float* d_pitch,
                    float* d_energy, void* stream);
+/* PitchEnergyPredictor.compute_cross, pitch_energy_predictor.py:83-102: tokens gathered to frames,
+ * query / key AdaptiveLayerNorm, 8-head cross attention (partial RoPE, inverted +-5 band bias),
+ * depthwise k5 + SiLU + 1x1, (base + attention) / sqrt 2.  Needs both the token layout and the
+ * hop-300 layout.  d_prosody_tok token-major dense [sum T, 320] or NULL = the rows
+ * stts_prosody_encoder("pitch_energy_predictor") just produced; d_idx / d_cu_frames from
+ * stts_frame_index.  The result stays in the workspace as the input of stts_pe_towers (call it with
+ * d_x = NULL); d_x (may be NULL) additionally receives it dense [320, F_b].                          */
+int stts_pe_cross(stts_ctx* ctx, const float* d_prosody_tok, const float* d_style, const int32_t* d_idx,
+                  const int32_t* d_cu_frames, float* d_x, void* stream);
 
 /* ---- module-level stages of SpeechPredictor.forward (speech_predictor.py:85-129) --------------
  * Decoder.forward, decoder.py:47-60.  d_asr dense [128, L_b]; d_f0/d_n dense [sum L];

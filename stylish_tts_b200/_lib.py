@@ -24,6 +24,8 @@ SIGNATURES = {
     "stts_set_token_layout": (_i, [_vp, _i, C.POINTER(_i)]),
     "stts_text_encoder": (_i, [_vp, C.c_char_p, _fp, _fp, _fp, _vp]),
     "stts_prosody_encoder": (_i, [_vp, C.c_char_p, _fp, _fp, _fp, _fp, _vp]),
+    "stts_text_style_encoder": (_i, [_vp, C.c_char_p, _fp, _fp, _vp]),
+    "stts_pe_cross": (_i, [_vp, _fp, _fp, _fp, _fp, _fp, _vp]),
     "stts_durations": (_i, [_vp, _fp, _i, _fp, _vp]),
     "stts_frame_index": (_i, [_vp, _fp, _fp, _i, _fp, _fp, _i, _fp, _vp]),
     "stts_pe_towers": (_i, [_vp, _fp, _fp, _fp, _fp, _vp]),

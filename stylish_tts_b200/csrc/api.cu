@@ -103,6 +103,23 @@ int stts_prosody_encoder(stts_ctx* ctx, const char* which, const float* d_enc_to
   return run_prosody_encoder(ctx->c, nm, d_enc_tok, d_style, d_out_tok, d_logits_tok, S(stream));
 }
 
+int stts_text_style_encoder(stts_ctx* ctx, const char* which, const float* d_enc_tok, float* d_style, void* stream) {
+  if (!ctx || !which || !d_style) return STTS_ERR_BAD_ARG;
+  DeviceGuard g(ctx->c.device);
+  const std::string w(which);
+  const char* nm = w == "speech_predictor" ? "se.sp" : (w == "pe_text_style_encoder" ? "se.pe"
+                   : (w == "duration_predictor" ? "se.dp" : nullptr));
+  if (nm == nullptr) return fail(ctx->c, STTS_ERR_BAD_ARG, "stts_text_style_encoder: unknown module " + w);
+  return run_style_encoder(ctx->c, nm, d_enc_tok, d_style, S(stream));
+}
+
+int stts_pe_cross(stts_ctx* ctx, const float* d_prosody_tok, const float* d_style, const int32_t* d_idx,
+                  const int32_t* d_cu_frames, float* d_x, void* stream) {
+  if (!ctx || !d_style || !d_idx || !d_cu_frames) return STTS_ERR_BAD_ARG;
+  DeviceGuard g(ctx->c.device);
+  return run_pe_cross(ctx->c, d_prosody_tok, d_style, d_idx, d_cu_frames, d_x, S(stream));
+}
+
 int stts_set_layout(stts_ctx* ctx, int n_seg, const int* len_f, const int* len_f4) {
   if (!ctx) return STTS_ERR_BAD_ARG;
   DeviceGuard g(ctx->c.device);
@@ -131,7 +148,7 @@ int stts_frame_index(stts_ctx* ctx, const int32_t* d_dur, const int32_t* d_cu_to
 
 int stts_pe_towers(stts_ctx* ctx, const float* d_x, const float* d_style, float* d_pitch, float* d_energy,
                    void* stream) {
-  if (!ctx || !d_x || !d_style || !d_pitch || !d_energy) return STTS_ERR_BAD_ARG;
+  if (!ctx || !d_style || !d_pitch || !d_energy) return STTS_ERR_BAD_ARG;
   DeviceGuard g(ctx->c.device);
   return run_pe_towers(ctx->c, d_x, d_style, d_pitch, d_energy, S(stream));
 }

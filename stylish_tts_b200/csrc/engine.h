@@ -137,6 +137,11 @@ int run_text_encoder(Context& c, const std::string& name, const int* d_tokens, f
 int run_prosody_encoder(Context& c, const std::string& name, const float* d_enc_tok, const float* d_style,
                         float* d_out_tok, float* d_logits_tok, cudaStream_t st);
 
+int run_style_encoder(Context& c, const std::string& name, const float* d_enc_tok, float* d_style_out,
+                      cudaStream_t st);
+int run_pe_cross(Context& c, const float* d_prosody_tok, const float* d_style, const int* d_idx, const int* d_cu_frames,
+                 float* d_x_out, cudaStream_t st);
+
 int fail(Context& c, int code, const std::string& msg);
 int cuda_fail(Context& c, cudaError_t e, const char* where);
 

@@ -63,6 +63,8 @@ cudaError_t attention(const float* Q, int ldq, int qcol, const float* K, int ldk
 cudaError_t dense_to_rows(const float* src, int C, const RowMap& map, const int* cu, float* dst, int ld, int col0,
                           cudaStream_t st);
 cudaError_t seg_broadcast(const float* vec, int C, const RowMap& map, float* dst, int ld, int col0, cudaStream_t st);
+cudaError_t dwconv_rows(const float* x, int ldx, int C, int K, const float* w, const float* b, const RowMap& map,
+                        int act, float* y, int ldy, cudaStream_t st);
 cudaError_t rows_to_dense(const float* src, int ld, int C, const RowMap& map, const int* cu, float* dst,
                           cudaStream_t st);
 

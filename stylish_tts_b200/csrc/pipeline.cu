@@ -377,7 +377,9 @@ int run_pe_towers(Context& c, const float* d_x, const float* d_style, float* d_p
   Act &px = S.A("PX"), &pact = S.A("PACT"), &py1 = S.A("PY1"), &pa = S.A("PA"), &pb = S.A("PB");
   float* gb = S.R<float>("GB_PE");
   STTS_CK(style_fc(c.vec["pe.fc_W"], c.vec["pe.fc_b"], d_style, c.J_pe, 64, c.LF.n_seg, gb, st));
-  STTS_CK(transpose_in(d_x, c.LF.d_off[3], c.LF.d_cs, 320, map, px.f, px.ld, 0, S.tw(px), px.ld, 0, st));
+  // d_x == NULL: the cross-attention block (run_pe_cross) already left its rows in PX
+  if (d_x != nullptr)
+    STTS_CK(transpose_in(d_x, c.LF.d_off[3], c.LF.d_cs, 320, map, px.f, px.ld, 0, S.tw(px), px.ld, 0, st));
   const char* tw[2] = {"F0", "N"};
   for (int t = 0; t < 2; ++t) {
     const std::string base = std::string("pe.") + tw[t];

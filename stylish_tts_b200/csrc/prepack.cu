@@ -333,6 +333,69 @@ bool pack_prosody(Context& c, Loader& L, const std::string& kp, const std::strin
   return true;
 }
 
+
+// TextStyleEncoder (text_style_encoder.py:6-26, conv_next.py:4-51) under key prefix `kp` -> `nm.*`
+bool pack_style_encoder(Context& c, Loader& L, const std::string& kp, const std::string& nm) {
+  if (!pack_simple(c, L, kp + "conv_in", nm + ".in", 3)) return false;
+  int n_blocks = 0;
+  while (L.has(kp + "blocks." + std::to_string(n_blocks) + ".dwconv.weight")) ++n_blocks;
+  c.vec_len[nm + ".blocks"] = n_blocks;
+  for (int i = 0; i < n_blocks; ++i) {
+    const std::string k = kp + "blocks." + std::to_string(i) + ".", n = nm + ".b" + std::to_string(i);
+    const HostTensor *dw = L.get(k + "dwconv.weight"), *db = L.get(k + "dwconv.bias");
+    const HostTensor *nw = L.get(k + "norm.weight"), *nb = L.get(k + "norm.bias");
+    const HostTensor *gg = L.get(k + "grn.gamma"), *gb = L.get(k + "grn.beta");
+    if (!L.ok) return false;
+    put_vec(c, n + ".dw_w", dw->data);      // [C, 1, K] row-major == [C][K]
+    put_vec(c, n + ".dw_b", db->data);
+    c.vec_len[n + ".dw_k"] = (int)dw->dim(2);
+    put_vec(c, n + ".ln_g", nw->data);
+    put_vec(c, n + ".ln_b", nb->data);
+    put_vec(c, n + ".grn_gamma", gg->data);
+    put_vec(c, n + ".grn_beta", gb->data);
+    if (!pack_simple(c, L, k + "pwconv1", n + ".pw1", 0)) return false;
+    if (!pack_simple(c, L, k + "pwconv2", n + ".pw2", 0)) return false;
+  }
+  return true;
+}
+
+// cross-attention block of PitchEnergyPredictor (pitch_energy_predictor.py:38-102): query/key AdaLN
+// FCs, q and (k | v) projections, output projection, depthwise k5 + SiLU + 1x1 post net
+bool pack_pe_cross(Context& c, Loader& L, const std::string& nm) {
+  FcCat fc;
+  const HostTensor *qw = L.get("query_norm.fc.weight"), *qb = L.get("query_norm.fc.bias");
+  const HostTensor *kw = L.get("key_norm.fc.weight"), *kb = L.get("key_norm.fc.bias");
+  if (!L.ok) return false;
+  c.fc_off[nm + ".qn"] = fc.add(*qw, *qb);
+  c.fc_off[nm + ".kn"] = fc.add(*kw, *kb);
+  c.vec_len[nm + ".J"] = fc.J;
+  put_vec(c, nm + ".fc_W", fc.W);
+  put_vec(c, nm + ".fc_b", fc.b);
+  if (!pack_simple(c, L, "cross_attention.conv_q", nm + ".q", 0)) return false;
+  {
+    const HostTensor wk = L.weight("cross_attention.conv_k."), wv = L.weight("cross_attention.conv_v.");
+    const HostTensor *bk = L.get("cross_attention.conv_k.bias"), *bv = L.get("cross_attention.conv_v.bias");
+    if (!L.ok) return false;
+    const int C = (int)wk.dim(0);
+    Builder b;
+    const int t[2] = {1, 0}, pd[2] = {0, 0}, cp[2] = {pad64(C), 0};
+    b.init(2 * C, 1, t, pd, cp);
+    b.rows(0, wk, 0, C, 0, C, 0, 1);  b.set_bias(*bk, 0, C, 0, 1);
+    b.rows(0, wv, 0, C, 0, C, C, 1);  b.set_bias(*bv, 0, C, C, 1);
+    c.gemm[nm + ".kv"] = b.upload(c);
+  }
+  if (!pack_simple(c, L, "cross_attention.conv_o", nm + ".o", 0)) return false;
+  {
+    const HostTensor dw = L.weight("cross_post.0.");
+    const HostTensor* db = L.get("cross_post.0.bias");
+    if (!L.ok) return false;
+    put_vec(c, nm + ".dw_w", dw.data);
+    put_vec(c, nm + ".dw_b", db->data);
+    c.vec_len[nm + ".dw_k"] = (int)dw.dim(2);
+  }
+  return pack_simple(c, L, "cross_post.2", nm + ".post", 0);
+}
+
 }  // namespace
 
 int finalize_weights(Context& c) {
@@ -641,6 +704,18 @@ int finalize_weights(Context& c) {
       if (!c.has(std::string(sl.module) + "/" + sl.kp + "attn_layers.0.conv_q.weight")) continue;
       Loader T{c, sl.module};
       if (!pack_prosody(c, T, sl.kp, sl.nm)) return fail(c, -3, "missing weight " + T.missing);
+    }
+    const Slot sslots[3] = {{"speech_predictor", "style_encoder.", "se.sp"},
+                            {"pe_text_style_encoder", "", "se.pe"},
+                            {"duration_predictor", "style_encoder.", "se.dp"}};
+    for (const Slot& sl : sslots) {
+      if (!c.has(std::string(sl.module) + "/" + sl.kp + "conv_in.weight")) continue;
+      Loader T{c, sl.module};
+      if (!pack_style_encoder(c, T, sl.kp, sl.nm)) return fail(c, -3, "missing weight " + T.missing);
+    }
+    if (c.has("pitch_energy_predictor/cross_attention.conv_q.weight")) {
+      Loader T{c, "pitch_energy_predictor"};
+      if (!pack_pe_cross(c, T, "pe.cross")) return fail(c, -3, "missing weight " + T.missing);
     }
     if (c.has("duration_predictor/duration_proj.linear_layer.weight")) {
       Loader T{c, "duration_predictor"};

@@ -34,7 +34,9 @@ int set_token_layout(Context& c, int n_seg, const int* len_t) {
   const Want wants[] = {{"TA", 128}, {"TB", 128}, {"TC", 128}, {"TX", 128}, {"TO", 128}, {"TQKV", 384},
                         {"TH", 512}, {"TMU", 256},
                         // prosody encoders (hid <= 320)
-                        {"PX", 320}, {"PY", 320}, {"PB", 320}, {"PO", 320}, {"PQKV", 960}, {"PH", 640}, {"PL", 64}};
+                        {"PX", 320}, {"PY", 320}, {"PB", 320}, {"PO", 320}, {"PQKV", 960}, {"PH", 640}, {"PL", 64},
+                        // style encoders (64 / 256 channels)
+                        {"SX", 64}, {"SY", 64}, {"SH", 256}};
   // three independent buffer sets ("slots"): the speech / pitch-energy / duration chains only share
   // the tokens, so the host may enqueue them on three streams (synth.py) without aliasing scratch
   size_t used = 0;
@@ -50,7 +52,14 @@ int set_token_layout(Context& c, int n_seg, const int* len_t) {
   for (int slot = 0; slot < 3; ++slot) {   // style-FC rows of the prosody AdaLNs (J <= 8192)
     off["GBT#" + std::to_string(slot)] = used;
     used += up1k((size_t)B * 8192 * 4);
+    // style-encoder statistics: per-tile fp64 partials (sum, sum sq) x 256 ch, per-utterance vectors
+    off["SSTAT#" + std::to_string(slot)] = used;
+    used += up1k((size_t)nt * 256 * 2 * 8);
+    off["SVEC#" + std::to_string(slot)] = used;
+    used += up1k((size_t)B * 256 * 4 * 4);
   }
+  off["GBC"] = used;                        // style-FC rows of the cross-attention query / key AdaLNs
+  used += up1k((size_t)B * 2048 * 4);
 
   if (used > c.tarena_bytes) {
     if (c.tarena) cudaFree(c.tarena);
@@ -78,7 +87,10 @@ int set_token_layout(Context& c, int n_seg, const int* len_t) {
   L.d_seg_start = (int*)c.traw["seg_start"]; L.d_seg_len = (int*)c.traw["seg_len"]; L.d_cu = (int*)c.traw["cu"];
   e = cudaDeviceSynchronize();
   if (e != cudaSuccess) return cuda_fail(c, e, "set_token_layout upload");
-  for (int slot = 0; slot < 3; ++slot) c.traw["GBT#" + std::to_string(slot)] = c.tarena + off["GBT#" + std::to_string(slot)];
+  for (int slot = 0; slot < 3; ++slot)
+    for (const char* nmv : {"GBT#", "SSTAT#", "SVEC#"})
+      c.traw[nmv + std::to_string(slot)] = c.tarena + off[nmv + std::to_string(slot)];
+  c.traw["GBC"] = c.tarena + off["GBC"];
   c.tsig = sig;
   return 0;
 }
@@ -196,6 +208,96 @@ int run_prosody_encoder(Context& c, const std::string& nm, const float* d_enc_to
     STTS_RET(run_gemm(c, c.gemm[nm + ".head"], GC_ISLAND, &px, 0, nullptr, 0, mk_epi(EPI_BIAS, pl, 0), map, st));
     STTS_CK(rows_to_dense(pl.f, pl.ld, 16, map, c.LT.d_cu, d_logits_tok, st));
   }
+  return 0;
+}
+
+// TextStyleEncoder.forward, text_style_encoder.py:20-26: conv k7 -> n x BasicConvNeXtBlock (dwconv k7,
+// LayerNorm eps 1e-6, Linear + GELU, GRN over time, Linear, residual; conv_next.py:18-51) -> mean over
+// the utterance.  d_enc_tok token-major dense [sum T, inter] or NULL = use the mu rows the text encoder
+// of the same chain left in its TMU buffer.  d_style_out [n_seg, 64].
+int run_style_encoder(Context& c, const std::string& nm, const float* d_enc_tok, float* d_style_out, cudaStream_t st) {
+  if (!c.finalized || c.gemm.count(nm + ".in") == 0) return fail(c, -3, "style encoder weights not loaded: " + nm);
+  if (c.LT.total() == 0 || c.tact.count("SX#0") == 0) return fail(c, -4, "no token layout set");
+  const RowMap map = c.LT.map();
+  const std::string sl = nm == "se.sp" ? "#0" : (nm == "se.pe" ? "#1" : "#2");
+  Act &tmu = c.tact["TMU" + sl], &sx = c.tact["SX" + sl], &sy = c.tact["SY" + sl], &sh = c.tact["SH" + sl];
+  const PackedGemm& gin = c.gemm[nm + ".in"];
+  const int inter = (int)(gin.k_real / gin.taps[0] + 0.5);
+  if (d_enc_tok) STTS_CK(dense_to_rows(d_enc_tok, inter, map, c.LT.d_cu, tmu.f, tmu.ld, 0, st));
+  STTS_RET(run_gemm(c, gin, GC_ISLAND, &tmu, 0, nullptr, 0, mk_epi(EPI_BIAS, sx, 0), map, st));
+  double* stat = reinterpret_cast<double*>(c.traw["SSTAT" + sl]);
+  float* vec = reinterpret_cast<float*>(c.traw["SVEC" + sl]);
+  const int B = c.LT.n_seg;
+  float *gx = vec, *gscale = vec + (size_t)B * 256, *mean = vec + (size_t)2 * B * 256, *rstd = vec + (size_t)3 * B * 256;
+  const int n_blocks = c.vec_len[nm + ".blocks"];
+  for (int i = 0; i < n_blocks; ++i) {
+    const std::string n = nm + ".b" + std::to_string(i);
+    STTS_CK(dwconv_rows(sx.f, sx.ld, 64, c.vec_len[n + ".dw_k"], c.vec[n + ".dw_w"], c.vec[n + ".dw_b"], map, 0, sy.f,
+                        sy.ld, st));
+    STTS_CK(row_ln(sy.f, sy.ld, 64, map, c.vec[n + ".ln_g"], c.vec[n + ".ln_b"], 0, 1e-6f, 0, sy.f, sy.ld, st));
+    STTS_RET(run_gemm(c, c.gemm[n + ".pw1"], GC_ISLAND, &sy, 0, nullptr, 0, mk_epi(EPI_GELU, sh, 0), map, st));
+    STTS_CK(colstats(sh.f, sh.ld, 256, map, 1, 0.f, stat, gx, nullptr, st));
+    c.launches++;
+    STTS_CK(grn_apply(sh.f, sh.ld, 256, map, gx, c.vec[n + ".grn_gamma"], c.vec[n + ".grn_beta"], gscale, nullptr, 0, st));
+    c.launches++;
+    {
+      Epi e = mk_epi(EPI_ADD, sx, 0);
+      e.res = sx.f; e.ldr = sx.ld; e.rcol0 = 0;
+      STTS_RET(run_gemm(c, c.gemm[n + ".pw2"], GC_ISLAND, &sh, 0, nullptr, 0, e, map, st));
+    }
+  }
+  STTS_CK(colstats(sx.f, sx.ld, 64, map, 0, 1e-5f, stat, mean, rstd, st));
+  c.launches++;
+  STTS_CK(cudaMemcpyAsync(d_style_out, mean, (size_t)B * 64 * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  return 0;
+}
+
+// Cross-attention block of PitchEnergyPredictor.compute_cross, pitch_energy_predictor.py:83-102:
+//   base = prosody gathered to frames; q = AdaLN_q(base), k = AdaLN_k(prosody); 8-head attention with
+//   partial RoPE and the inverted +-window band bias; conv_o; depthwise k5 + SiLU + 1x1; (base + att) / sqrt 2.
+// d_prosody_tok token-major dense [sum T, 320] or NULL = the rows the prosody encoder left in PX (slot 1).
+// Result: packed rows of the hop-300 layout in PX (the input buffer of the pitch / energy towers);
+// optional d_x_out dense [320, F_b] per utterance.
+int run_pe_cross(Context& c, const float* d_prosody_tok, const float* d_style, const int* d_idx, const int* d_cu_frames,
+                 float* d_x_out, cudaStream_t st) {
+  const std::string nm = "pe.cross";
+  if (!c.finalized || c.vec.count(nm + ".fc_W") == 0) return fail(c, -3, "cross-attention weights not loaded");
+  if (c.LT.total() == 0 || c.tact.count("PX#1") == 0) return fail(c, -4, "no token layout set");
+  if (c.LF.total() == 0 || c.act.count("PX") == 0) return fail(c, -4, "no hop-300 layout set");
+  if (c.LT.n_seg != c.LF.n_seg) return fail(c, -2, "token and frame layouts disagree on the number of utterances");
+  const RowMap tmap = c.LT.map(), fmap = c.LF.map();
+  const int C = 320, H = 8, D = 40, rd = 20, J = c.vec_len[nm + ".J"];
+  Act &tpx = c.tact["PX#1"], &tpy = c.tact["PY#1"], &tkv = c.tact["PQKV#1"];
+  Act &px = c.act["PX"], &pact = c.act["PACT"], &py1 = c.act["PY1"], &pa = c.act["PA"], &pb = c.act["PB"];
+  float* gb = reinterpret_cast<float*>(c.traw["GBC"]);
+  if (J > 2048) return fail(c, -6, "cross-attention: style FC too wide");
+  STTS_CK(style_fc(c.vec[nm + ".fc_W"], c.vec[nm + ".fc_b"], d_style, J, 64, c.LT.n_seg, gb, st));
+  if (d_prosody_tok) STTS_CK(dense_to_rows(d_prosody_tok, C, tmap, c.LT.d_cu, tpx.f, tpx.ld, 0, st));
+  // base: gather tokens -> frames.  expand_tokens reads a token-major dense matrix; the packed rows of
+  // an utterance are contiguous, so the packed buffer is addressed with seg_start as the token offset
+  STTS_CK(expand_tokens(tpx.f, tpx.ld, d_idx, d_cu_frames, c.LT.d_seg_start, 1, fmap, pa.f, pa.ld, 0, nullptr, 0, 0, st));
+  STTS_CK(row_ln(pa.f, pa.ld, C, fmap, gb + c.fc_off[nm + ".qn"], nullptr, J, 1e-5f, 0, pb.f, pb.ld, st));
+  STTS_CK(row_ln(tpx.f, tpx.ld, C, tmap, gb + c.fc_off[nm + ".kn"], nullptr, J, 1e-5f, 0, tpy.f, tpy.ld, st));
+  Epi eq = mk_epi(EPI_BIAS, pact, 0);
+  STTS_RET(run_gemm(c, c.gemm[nm + ".q"], GC_ISLAND, &pb, 0, nullptr, 0, eq, fmap, st));
+  STTS_RET(run_gemm(c, c.gemm[nm + ".kv"], GC_ISLAND, &tpy, 0, nullptr, 0, mk_epi(EPI_BIAS, tkv, 0), tmap, st));
+  STTS_CK(rope_inplace(pact.f, pact.ld, 0, C, 1, H, D, rd, fmap, st));
+  STTS_CK(rope_inplace(tkv.f, tkv.ld, 0, C, 1, H, D, rd, tmap, st));
+  int max_f = 0;
+  for (int v : c.LF.seg_len) max_f = std::max(max_f, v);
+  STTS_CK(attention(pact.f, pact.ld, 0, tkv.f, tkv.ld, 0, tkv.f, tkv.ld, C, H, D, 1.0f / std::sqrt((float)D), fmap, tmap,
+                    max_f, c.max_t, d_idx, d_cu_frames, 5, py1.f, py1.ld, st));
+  STTS_RET(run_gemm(c, c.gemm[nm + ".o"], GC_ISLAND, &py1, 0, nullptr, 0, mk_epi(EPI_BIAS, pb, 0), fmap, st));
+  STTS_CK(dwconv_rows(pb.f, pb.ld, C, c.vec_len[nm + ".dw_k"], c.vec[nm + ".dw_w"], c.vec[nm + ".dw_b"], fmap, 1, pact.f,
+                      pact.ld, st));
+  {
+    Epi e = mk_epi(EPI_RES_SCALE, px, 0);
+    e.res = pa.f; e.ldr = pa.ld; e.rcol0 = 0;
+    e.scale = 0.70710678118654752440f;
+    e.outh = (c.precision == 1) ? px.h : nullptr; e.ldh = px.ld; e.colh0 = 0;
+    STTS_RET(run_gemm(c, c.gemm[nm + ".post"], GC_ISLAND, &pact, 0, nullptr, 0, e, fmap, st));
+  }
+  if (d_x_out) STTS_CK(transpose_out(px.f, px.ld, 0, C, fmap, d_x_out, c.LF.d_off[3], c.LF.d_cs, 0, st));
   return 0;
 }
 

@@ -254,6 +254,38 @@ cudaError_t rows_to_dense(const float* src, int ld, int C, const RowMap& map, co
   return cudaGetLastError();
 }
 
+// ------------------------------------------------------------------------------ depthwise conv over rows
+// y[r, c] = act(b[c] + sum_j w[c, j] * x[r + j - K/2, c]), rows outside the utterance read as zero.
+// BasicConvNeXtBlock.dwconv k7 (conv_next.py:18-51) and cross_post[0] k5 + SiLU
+// (pitch_energy_predictor.py:56-78).  act: 0 = none, 1 = SiLU.
+__global__ void __launch_bounds__(256) dwconv_rows_kernel(const float* __restrict__ x, int ldx, int C, int K,
+                                                          const float* __restrict__ w, const float* __restrict__ b,
+                                                          RowMap map, int act, float* __restrict__ y, int ldy) {
+  const int tile = blockIdx.x;
+  const int seg = map.tile_seg[tile];
+  if (seg < 0) return;
+  const int nvalid = map.tile_nvalid[tile];
+  const int s0 = map.seg_start[seg], s1 = s0 + map.seg_len[seg];
+  const int half = K >> 1;
+  for (int i = blockIdx.y * blockDim.x + threadIdx.x; i < nvalid * C; i += gridDim.y * blockDim.x) {
+    const int lr = i / C, c = i - lr * C;
+    const int r = tile * 128 + lr;
+    float acc = b[c];
+    for (int j = 0; j < K; ++j) {
+      const int rr = r + j - half;
+      if (rr >= s0 && rr < s1) acc = fmaf(w[c * K + j], x[(size_t)rr * ldx + c], acc);
+    }
+    if (act == 1) acc = acc / (1.f + expf(-acc));
+    y[(size_t)r * ldy + c] = acc;
+  }
+}
+
+cudaError_t dwconv_rows(const float* x, int ldx, int C, int K, const float* w, const float* b, const RowMap& map,
+                        int act, float* y, int ldy, cudaStream_t st) {
+  dwconv_rows_kernel<<<dim3(map.n_tiles, 4), 256, 0, st>>>(x, ldx, C, K, w, b, map, act, y, ldy);
+  return cudaGetLastError();
+}
+
 // token-major dense [sum T, C] -> packed rows, columns [col0, col0 + C)
 __global__ void __launch_bounds__(256) dense_to_rows_kernel(const float* __restrict__ src, int C, RowMap map,
                                                             const int* __restrict__ cu, float* __restrict__ dst,

@@ -119,7 +119,7 @@ class Engine:
         return mu, x
 
     def prosody_encoder(self, which: str, enc_tok: torch.Tensor, style: torch.Tensor, hid: int,
-                        want_logits: bool = False):
+                        want_logits: bool = False, want_out: bool = True):
         """ProsodyEncoder.forward (prosody_encoder.py:63-81) on the current token layout.  enc_tok
         token-major [sum T, d_model]; style [B, 64].  Returns (out [sum T, hid], logits [sum T, 16] | None)."""
         n = int(enc_tok.shape[0])
@@ -127,11 +127,37 @@ class Engine:
             raise ValueError("token count does not match the token layout")
         enc_tok = enc_tok.to(torch.float32).contiguous()
         style = style.to(torch.float32).contiguous()
-        out = torch.empty((n, hid), dtype=torch.float32, device=self.device)
+        out = torch.empty((n, hid), dtype=torch.float32, device=self.device) if want_out else None
         logits = torch.empty((n, 16), dtype=torch.float32, device=self.device) if want_logits else None
         self._check(self.lib.stts_prosody_encoder(self.h, which.encode(), _ptr(enc_tok), _ptr(style), _ptr(out),
                                                   _ptr(logits), self._stream()))
         return out, logits
+
+    def text_style_encoder(self, which: str, enc_tok: Optional[torch.Tensor]) -> torch.Tensor:
+        """TextStyleEncoder.forward (text_style_encoder.py:20-26) on the current token layout.
+        enc_tok token-major [sum T, inter_dim], or None = the mu rows the text encoder of the same
+        chain just left in the workspace.  Returns style [B, 64]."""
+        if enc_tok is not None:
+            if int(enc_tok.shape[0]) != sum(self.len_t):
+                raise ValueError("token count does not match the token layout")
+            enc_tok = enc_tok.to(torch.float32).contiguous()
+        style = torch.empty((len(self.len_t), 64), dtype=torch.float32, device=self.device)
+        self._check(self.lib.stts_text_style_encoder(self.h, which.encode(), _ptr(enc_tok), _ptr(style),
+                                                     self._stream()))
+        return style
+
+    def pe_cross(self, prosody_tok: Optional[torch.Tensor], style: torch.Tensor, idx: torch.Tensor,
+                 cu_frames: torch.Tensor, want_dense: bool = False) -> Optional[torch.Tensor]:
+        """PitchEnergyPredictor.compute_cross (pitch_energy_predictor.py:83-102) on the current token
+        and hop-300 layouts.  The result stays in the workspace for ``pe_towers(None, style)``;
+        ``want_dense`` also returns it as flat dense [320, F_b] per utterance."""
+        if prosody_tok is not None:
+            prosody_tok = prosody_tok.to(torch.float32).contiguous()
+        style = style.to(torch.float32).contiguous()
+        x = torch.empty(320 * sum(self.len_f), device=self.device) if want_dense else None
+        self._check(self.lib.stts_pe_cross(self.h, _ptr(prosody_tok), _ptr(style), _ptr(idx, torch.int32),
+                                           _ptr(cu_frames, torch.int32), _ptr(x), self._stream()))
+        return x
 
     def workspace_bytes(self) -> int:
         return int(self.lib.stts_workspace_bytes(self.h))

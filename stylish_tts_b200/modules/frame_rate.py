@@ -29,7 +29,8 @@ from torch.nn.utils.parametrizations import weight_norm
 
 from ..config import check_supported
 from ..engine import Engine
-from .token_rate import (MultiHeadAttention, ProsodyEncoder, StyleLayerNorm, TextEncoder, TextStyleEncoder)
+from .token_rate import (MultiHeadAttention, ProsodyEncoder, StyleLayerNorm, TextEncoder, TextStyleEncoder,
+                         TokenPack)
 
 
 def _legacy_weight_norm(m: nn.Module) -> nn.Module:
@@ -309,14 +310,23 @@ class PitchEnergyPredictor(_EngineOwner):
         return (base + att) / math.sqrt(2.0)
 
     def forward(self, text_encoding, text_lengths, alignment, style):
-        frame_token = alignment.argmax(dim=1)
-        self.prosody_encoder.attach_native(self.engine(), "pitch_energy_predictor")
-        prosody = self.prosody_encoder(text_encoding, style, text_lengths)
-        x = self.compute_cross(prosody, frame_token, style, text_lengths)
-        b, _, f = x.shape
+        """pitch_energy_predictor.py:104-119 in libstts_b200: prosody encoder, cross-attention block
+        (stts_pe_cross) and the two towers.  ``compute_cross`` above is the torch statement of the
+        cross block, kept for the CPU host tests."""
+        b, _, t = text_encoding.shape
+        f = alignment.shape[2]
+        dev = text_encoding.device
         eng = self.engine()
+        lengths = [int(v) for v in text_lengths.tolist()]
+        eng.set_token_layout(lengths)
         eng.set_layout([f] * b, None)
-        pitch, energy = eng.pe_towers(_dense(x), _dense(style))
+        pack = TokenPack(lengths, t, dev)
+        eng.prosody_encoder("pitch_energy_predictor", pack.gather(text_encoding.transpose(1, 2)), style,
+                            self.prosody_encoder.hidden)
+        idx = alignment.argmax(dim=1).to(torch.int32).contiguous().view(-1)   # one-hot columns -> token index
+        cu_frames = torch.arange(b + 1, device=dev, dtype=torch.int32) * f
+        eng.pe_cross(None, style, idx, cu_frames)
+        pitch, energy = eng.pe_towers(None, _dense(style))
         return pitch.view(b, f), energy.view(b, f)
 
 
@@ -356,6 +366,7 @@ class SpeechPredictor(_EngineOwner):
             raise NotImplementedError("the posterior (training) branch is outside the synthesis forward path")
         self.text_encoder.attach_native(self.engine(), "speech_predictor")
         enc, _, _ = self.text_encoder(texts, text_lengths)
+        self.style_encoder.attach_native(self.engine(), "speech_predictor")
         style = self.style_encoder(enc, text_lengths)
         b, _, t = enc.shape
         f = alignment.shape[2]

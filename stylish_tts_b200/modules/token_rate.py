@@ -277,12 +277,44 @@ class _ConvNeXt1d(nn.Module):
 
 
 class TextStyleEncoder(nn.Module):
+    """text_style_encoder.py:6-26.  The arithmetic runs in libstts_b200 (stts_text_style_encoder: conv
+    k7, ConvNeXt blocks with GRN over the utterance, mean over time); ``forward_torch`` is the torch
+    statement of the same computation for the CPU host tests of the state_dict layout."""
+
     def __init__(self, inter_dim, style_dim, config):
         super().__init__()
         self.conv_in = nn.Conv1d(inter_dim, style_dim, kernel_size=7, padding=3)
         self.blocks = nn.ModuleList([_ConvNeXt1d(style_dim, style_dim * 4) for _ in range(config.layers)])
+        object.__setattr__(self, "_native", None)
 
-    def forward(self, x, lengths):
+    def attach_native(self, engine, which: str):
+        """Use a context that already holds this encoder's weights under module name ``which``."""
+        object.__setattr__(self, "_native", (engine, which))
+
+    def load_state_dict(self, state_dict, strict: bool = True, assign: bool = False):
+        object.__setattr__(self, "_native", None)
+        return super().load_state_dict(state_dict, strict=strict, assign=assign)
+
+    def _engine(self):
+        if self._native is None:
+            from ..engine import Engine
+            dev = self.conv_in.weight.device
+            if dev.type != "cuda":
+                raise RuntimeError("stylish_tts_b200 modules run on a B200 only (no CPU fallback)")
+            eng = Engine(dev)
+            eng.load_state("pe_text_style_encoder", self.state_dict())
+            eng.finalize()
+            object.__setattr__(self, "_native", (eng, "pe_text_style_encoder"))
+        return self._native
+
+    def forward(self, x, lengths, host_lengths=None):
+        eng, which = self._engine()
+        b, _, tmax = x.shape
+        pack = TokenPack.of(host_lengths, lengths, tmax, x.device)
+        eng.set_token_layout(pack.lengths)
+        return eng.text_style_encoder(which, pack.gather(x.transpose(1, 2)))
+
+    def forward_torch(self, x, lengths):
         m = length_mask(lengths, x.shape[2]).unsqueeze(1).to(x.dtype)
         x = self.conv_in(x * m) * m
         for blk in self.blocks:
@@ -388,14 +420,14 @@ class DurationPredictor(nn.Module):
         return self._eng
 
     def forward(self, texts, text_lengths, host_lengths=None):
-        """duration_predictor.py:30-36: text encoder and prosody encoder + duration_proj run in
-        libstts_b200 on the packed token layout; the (tiny) style encoder is still a torch module."""
+        """duration_predictor.py:30-36: text encoder, style encoder, prosody encoder + duration_proj
+        all run in libstts_b200 on the packed token layout."""
         eng = self._engine()
         self.text_encoder.attach_native(eng, "duration_predictor")
         b, tmax = texts.shape
         pack = TokenPack.of(host_lengths, text_lengths, tmax, texts.device)
         mu_t, _ = self.text_encoder.encode_packed(pack.gather(texts), pack.lengths)
-        style = self.style_encoder(pack.scatter(mu_t, b).transpose(1, 2), text_lengths)
+        style = eng.text_style_encoder("duration_predictor", None)     # reads the mu rows left by the text encoder
         _, logits_t = eng.prosody_encoder("duration_predictor", mu_t, style, self.prosody_encoder.hidden,
                                           want_logits=True)
         return pack.scatter(logits_t, b)
@@ -403,5 +435,5 @@ class DurationPredictor(nn.Module):
     def forward_torch(self, texts, text_lengths):
         """Op-by-op torch statement of the same computation (CPU host tests of the mirror only)."""
         enc, _, _ = self.text_encoder.forward_torch(texts, text_lengths)
-        style = self.style_encoder(enc, text_lengths)
+        style = self.style_encoder.forward_torch(enc, text_lengths)
         return self.duration_proj(self.prosody_encoder.forward_torch(enc, style, text_lengths))

@@ -3,8 +3,10 @@
 The reference synthesises one utterance at a time (validate_duration, train/stage_type.py:483-523;
 ExportModel, train/models/export_model.py:35-45).  ``Synthesizer.synthesize`` runs the same chain
 for a ragged batch with *per-utterance* semantics (every norm / GRN / STFT edge sees only its own
-utterance): token-rate encoders on a padded batch with exact masking, the
-frame-rate path on the packed layout of the C library.  One context holds both weight sets.
+utterance): the token-rate encoders on the packed token layout and the
+frame-rate path on the packed frame layouts of the C library.  One context holds every weight set;
+between the input tokens and the output waveform every kernel is a libstts_b200 launch (torch
+only draws the three noise tensors).
 """
 from __future__ import annotations
 
@@ -31,6 +33,7 @@ class Synthesizer:
         self.engine = Engine(self.device)
         self._side_streams = (torch.cuda.Stream(self.device), torch.cuda.Stream(self.device))
         self.use_graphs = use_graphs
+        self.model_config = model_config or ModelConfig()
         self._graphs, self._packs, self._finfo = {}, {}, {}
         self.reload_weights()
         self.engine.set_precision(precision)
@@ -40,9 +43,11 @@ class Synthesizer:
         self.engine.load_state("speech_predictor", self.nets["speech_predictor"].state_dict())
         self.engine.load_state("pitch_energy_predictor", self.nets["pitch_energy_predictor"].state_dict())
         self.engine.load_state("pe_text_encoder", self.nets["pe_text_encoder"].state_dict())
+        self.engine.load_state("pe_text_style_encoder", self.nets["pe_text_style_encoder"].state_dict())
         self.engine.load_state("duration_predictor", self.nets["duration_predictor"].state_dict())
         self.engine.finalize()
         self.nets["pe_text_encoder"].attach_native(self.engine, "pe_text_encoder")
+        self.nets["pe_text_style_encoder"].attach_native(self.engine, "pe_text_style_encoder")
         self.nets["duration_predictor"].attach_engine(self.engine)
         self.nets["speech_predictor"].attach_engine(self.engine)
         self.nets["pitch_energy_predictor"].attach_engine(self.engine)
@@ -70,18 +75,13 @@ class Synthesizer:
         buffers: consume (or clone) them before the next call with the same shape.
         Returns dict(audio=[...[300 F_b]], duration_pred=[...], pitch=[...], energy=[...], ...)."""
         dev = self.device
-        B = len(tokens)
         T = [int(t.numel()) for t in tokens]
-        Tmax = max(T)
-        pack = self._token_pack(T, Tmax)
-        # one H2D copy of the concatenated tokens, then a device scatter into the padded batch
-        tok_cat = torch.cat([t.reshape(-1) for t in tokens]).to(dev, torch.int64, non_blocking=True)
-        tok = torch.zeros(B * Tmax, dtype=torch.int64, device=dev).index_copy_(0, pack.flat_idx, tok_cat).view(B, Tmax)
+        pack = self._token_pack(T, max(T))
+        # one H2D copy of the concatenated tokens: every stage works on the packed [sum T] token order
+        tok = torch.cat([t.reshape(-1) for t in tokens]).to(dev, torch.int32, non_blocking=True)
         dur_used, F_list = None, None
         if durations is not None:
-            dur_cat = torch.cat([d.reshape(-1) for d in durations]).to(dev, torch.int32, non_blocking=True)
-            dur_used = torch.zeros(B * Tmax, dtype=torch.int32, device=dev).index_copy_(0, pack.flat_idx, dur_cat)
-            dur_used = dur_used.view(B, Tmax)
+            dur_used = torch.cat([d.reshape(-1) for d in durations]).to(dev, torch.int32, non_blocking=True)
             # host-known frame counts: no device sync (pass `frames` when the durations live on the device)
             F_list = [int(f) for f in frames] if frames is not None else [int(d.sum()) for d in durations]
         use_graph = self.use_graphs if graph is None else graph
@@ -96,8 +96,14 @@ class Synthesizer:
         if key not in self._packs:
             if len(self._packs) > 64:
                 self._packs.clear()
-            self._packs[key] = TokenPack(T, Tmax, self.device)
-            self._packs[key].lens = torch.tensor(T, dtype=torch.int64).to(self.device)
+            pk = TokenPack(T, Tmax, self.device)
+            pk.lens = torch.tensor(T, dtype=torch.int64).to(self.device)
+            cu = [0]
+            for n in T:
+                cu.append(cu[-1] + n)
+            pk.cu = torch.tensor(cu, dtype=torch.int32).to(self.device)          # token offsets of the packed order
+            pk.seg_id = torch.repeat_interleave(torch.arange(len(T)), torch.tensor(T)).to(self.device)
+            self._packs[key] = pk
         return self._packs[key]
 
     def _frame_info(self, F_list):
@@ -138,12 +144,14 @@ class Synthesizer:
         return res
 
     def _core(self, tok, pack, dur_used, F_list, noise, pitch_energy, want_spec, want_intermediates):
-        """The device work of one step.  Free of host synchronisation when F_list is given."""
-        dev, eng, nets = self.device, self.engine, self.nets
-        B, Tmax = tok.shape
-        T = pack.lengths
-        lens = pack.lens
+        """The device work of one step: every stage is a libstts_b200 call on the packed layouts.
+        tok / dur_used: int32 [sum T] in packed token order.  Free of host synchronisation when
+        F_list is given."""
+        dev, eng = self.device, self.engine
+        mc = self.model_config
+        B = len(pack.lengths)
         capturing = torch.cuda.is_current_stream_capturing()
+        eng.set_token_layout(pack.lengths)
         # The duration, pitch/energy and speech chains only share the tokens: enqueue them on three
         # streams (their kernels are small and latency-bound at token rate) and join before the
         # frame-rate path.  The C library keeps one scratch set per chain (token_pipeline.cu).
@@ -152,48 +160,39 @@ class Synthesizer:
         s_dp.wait_stream(cur)
         s_sp.wait_stream(cur)
 
-        # ---- durations (duration_predictor + prediction_to_duration)            [stream s_dp]
+        # ---- durations: text encoder -> style -> prosody + duration_proj -> argmax rule   [stream s_dp]
         with torch.cuda.stream(s_dp):
-            logits = nets["duration_predictor"](tok, lens, host_lengths=pack)                   # [B, Tmax, 16]
-            dur_all = eng.durations(logits.reshape(B * Tmax, 16)).view(B, Tmax)  # int32
-        # ---- speech text / style encoders                                        [stream s_sp]
-        sp = nets["speech_predictor"]
+            dp_mu, _ = eng.text_encoder("duration_predictor", tok, mc.inter_dim, want_x=False)
+            dp_style = eng.text_style_encoder("duration_predictor", None)
+            _, logits = eng.prosody_encoder("duration_predictor", dp_mu, dp_style, mc.inter_dim + mc.style_dim,
+                                            want_logits=True, want_out=False)
+            dur_pred = eng.durations(logits)                                    # int32 [sum T]
+        # ---- speech text / style encoders                                                 [stream s_sp]
         with torch.cuda.stream(s_sp):
-            sp.text_encoder.attach_native(eng, "speech_predictor")
-            enc, _, _ = sp.text_encoder(tok, lens, host_lengths=pack)
-            style = sp.style_encoder(enc, lens).contiguous()
-            enc_tok = enc.transpose(1, 2).contiguous().view(B * Tmax, 128)
-        # ---- pitch / energy token-rate part                                      [current stream]
-        pe_enc, _, _ = nets["pe_text_encoder"](tok, lens, host_lengths=pack)
-        pe_style = nets["pe_text_style_encoder"](pe_enc, lens)
-        pep = nets["pitch_energy_predictor"]
-        pep.prosody_encoder.attach_native(eng, "pitch_energy_predictor")
-        prosody = pep.prosody_encoder(pe_enc, pe_style, lens, host_lengths=pack)
+            enc_tok, _ = eng.text_encoder("speech_predictor", tok, mc.inter_dim, want_x=False)
+            style = eng.text_style_encoder("speech_predictor", None)
+        # ---- pitch / energy token-rate part                                               [current stream]
+        pe_inter = mc.pitch_energy_predictor.inter_dim
+        pe_mu, _ = eng.text_encoder("pe_text_encoder", tok, pe_inter, want_x=False)
+        pe_style = eng.text_style_encoder("pe_text_style_encoder", None)
+        prosody, _ = eng.prosody_encoder("pitch_energy_predictor", pe_mu, pe_style, pe_inter + mc.style_dim,
+                                         want_out=want_intermediates)
 
         cur.wait_stream(s_dp)
         if not capturing:
-            for t_ in (logits, dur_all):
+            for t_ in (dp_mu, dp_style, logits, dur_pred):
                 t_.record_stream(cur)
-        valid = torch.arange(Tmax, device=dev)[None, :] < lens[:, None]
-        dur_pred = dur_all * valid
         if dur_used is None:
             dur_used = dur_pred
-            F_list = [int(v) for v in dur_pred.sum(dim=1).tolist()]          # the one unavoidable D2H
+            per_utt = torch.zeros(B, dtype=torch.int64, device=dev).index_add_(0, pack.seg_id, dur_pred.to(torch.int64))
+            F_list = [int(v) for v in per_utt.tolist()]                         # the one unavoidable D2H
         F_tot = sum(F_list)
-        cu_tok = torch.arange(B + 1, device=dev, dtype=torch.int32) * Tmax    # token offsets into the padded batch
-        cu_frames, idx, _ = eng.frame_index(dur_used.contiguous().view(-1), cu_tok, F_tot)
+        cu_frames, idx, _ = eng.frame_index(dur_used, pack.cu, F_tot)
         eng.set_layout(F_list, [4 * f for f in F_list])
 
-        # ---- pitch / energy frame-rate part
-        Fmax = max(F_list)
-        f_lens = self._frame_info(F_list)
-        # padded [B, Fmax] frame -> token map from the packed index vector
-        pos = torch.arange(Fmax, device=dev)[None, :]
-        gather = (cu_frames[:-1].to(torch.int64)[:, None] + pos).clamp_(max=max(F_tot - 1, 0))
-        frame_token = torch.where(pos < f_lens[:, None], idx[:F_tot].to(torch.int64)[gather], torch.zeros_like(gather))
-        x = pep.compute_cross(prosody, frame_token, pe_style, lens, frame_lengths=f_lens)   # [B, 320, Fmax]
-        x_dense = torch.cat([x[b, :, : F_list[b]].reshape(-1) for b in range(B)])
-        pitch, energy = eng.pe_towers(x_dense, pe_style.contiguous())
+        # ---- pitch / energy frame-rate part: cross attention over the alignment, then the two towers
+        x = eng.pe_cross(None, pe_style, idx, cu_frames, want_dense=want_intermediates)
+        pitch, energy = eng.pe_towers(None, pe_style)
         pitch_in, energy_in = pitch, energy
         if pitch_energy is not None:
             pitch_in = torch.cat([pe[0].reshape(-1) for pe in pitch_energy]).to(dev, torch.float32).contiguous()
@@ -202,7 +201,7 @@ class Synthesizer:
         # ---- speech frame-rate path
         cur.wait_stream(s_sp)
         if not capturing:
-            for t_ in (enc, style, enc_tok):
+            for t_ in (enc_tok, style):
                 t_.record_stream(cur)
         if noise is not None:
             n_prior = torch.cat([n["prior"].reshape(-1) for n in noise]).to(dev)
@@ -212,11 +211,12 @@ class Synthesizer:
             n_prior = torch.randn(128 * 4 * F_tot, device=dev)
             n_src = torch.randn(300 * F_tot, device=dev)
             n_phase = torch.rand(B, device=dev)
-        audio, la, ph = eng.speech_frames(enc_tok, cu_tok, idx, cu_frames, pitch_in, energy_in, style, n_prior, n_src,
+        audio, la, ph = eng.speech_frames(enc_tok, pack.cu, idx, cu_frames, pitch_in, energy_in, style, n_prior, n_src,
                                           n_phase, want_spec=want_spec)
         res = dict(audio=audio, la=la, ph=ph, dur_pred=dur_pred, pitch=pitch, energy=energy, frames=F_list)
-        if want_intermediates:
-            res.update(pe_cross=x, pe_style=pe_style, sp_style=style, sp_text=enc, pe_text=pe_enc, dur_logits=logits)
+        if want_intermediates:   # token-major [sum T, C] / flat dense [320, F_b] per utterance
+            res.update(pe_cross=x, pe_style=pe_style, sp_style=style, sp_text=enc_tok, pe_text=pe_mu,
+                       pe_prosody=prosody, dur_logits=logits)
         return res
 
     @staticmethod
@@ -231,7 +231,10 @@ class Synthesizer:
         out["audio_offsets"] = a_off
         out["audio"] = [audio[a_off[b]: a_off[b + 1]] for b in range(B)]
         out["frames"] = F_list
-        out["duration_pred"] = [dur_pred[b, : T[b]] for b in range(B)]
+        t_off = [0]
+        for n in T:
+            t_off.append(t_off[-1] + n)
+        out["duration_pred"] = [dur_pred[t_off[b]: t_off[b + 1]] for b in range(B)]
         f_off = [0]
         for f in F_list:
             f_off.append(f_off[-1] + f)
@@ -243,7 +246,7 @@ class Synthesizer:
                 s_off.append(s_off[-1] + 1025 * (4 * f + 1))
             out["logamp"] = [la[s_off[b]: s_off[b + 1]].view(1025, 4 * F_list[b] + 1) for b in range(B)]
             out["phase"] = [ph[s_off[b]: s_off[b + 1]].view(1025, 4 * F_list[b] + 1) for b in range(B)]
-        for k in ("pe_cross", "pe_style", "sp_style", "sp_text", "pe_text", "dur_logits"):
+        for k in ("pe_cross", "pe_style", "sp_style", "sp_text", "pe_text", "pe_prosody", "dur_logits"):
             if k in res:
                 out[k] = res[k]
         return out

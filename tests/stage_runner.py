@@ -91,6 +91,18 @@ def run(precision="fp32", g=None, tag=""):
         pep.prosody_encoder.attach_native(peng, "pitch_energy_predictor")
         rec("pe_prosody", pep.prosody_encoder(g["tap.pe_text"].to(dev), g["tap.pe_style"].to(dev), lens),
             g["tap.pe_prosody"])
+        # native style encoders (stts_text_style_encoder) on the reference's text encodings
+        sp.style_encoder.attach_native(eng, "speech_predictor")
+        rec("sp_style", sp.style_encoder(g["tap.sp_text"].to(dev), lens), g["tap.sp_style"])
+        rec("pe_style", nets["pe_text_style_encoder"](g["tap.pe_text"].to(dev), lens), g["tap.pe_style"])
+        # native cross-attention block (stts_pe_cross) on the reference's prosody encoding
+        peng.set_token_layout([tokens.shape[1]])
+        peng.set_layout([F_], None)
+        cu_f = torch.tensor([0, F_], dtype=torch.int32, device=dev)
+        pros_tok = g["tap.pe_prosody"].to(dev).reshape(tokens.shape[1], -1).contiguous()
+        xc = peng.pe_cross(pros_tok, g["tap.pe_style"].to(dev), idx.to(torch.int32).contiguous(), cu_f,
+                           want_dense=True)
+        rec("pe_cross", xc, g["tap.pe_cross"])
 
     def sec_pitch___energy_towers_on_the_reference_s():  # pitch / energy towers on the reference's cross-attended frames
         peng.set_layout([F_], None)

@@ -52,7 +52,7 @@ def test_token_rate_mirrors_equal_oracle(cpu_nets):
         e1, _, _ = cpu_nets["pe_text_encoder"].forward_torch(tk, ln)
         e2, _, _ = port.text_encoder(sds["pe_text_encoder"], "", tk, ln)
         assert float((e1 - e2).abs().max()) <= 1e-6
-        s1 = cpu_nets["pe_text_style_encoder"](e1, ln)
+        s1 = cpu_nets["pe_text_style_encoder"].forward_torch(e1, ln)
         s2 = port.text_style_encoder(sds["pe_text_style_encoder"], "", e2, ln)
         assert float((s1 - s2).abs().max()) <= 1e-6
 
@@ -68,7 +68,7 @@ def test_padded_batch_has_per_utterance_semantics(cpu_nets):
     with torch.no_grad():
         a = cpu_nets["duration_predictor"].forward_torch(tk, ln)
         enc, _, _ = cpu_nets["pe_text_encoder"].forward_torch(tk, ln)
-        sty = cpu_nets["pe_text_style_encoder"](enc, ln)
+        sty = cpu_nets["pe_text_style_encoder"].forward_torch(enc, ln)
         for i, t in enumerate(toks):
             n = t.numel()
             b = port.duration_predictor(sds["duration_predictor"], t[None], torch.tensor([n]))
@@ -93,7 +93,7 @@ def test_cross_attention_ragged_mode_equals_b1(cpu_nets):
     ln, fl = torch.tensor(Ts), torch.tensor(Fs)
     with torch.no_grad():
         enc, _, _ = cpu_nets["pe_text_encoder"].forward_torch(tk, ln)
-        sty = cpu_nets["pe_text_style_encoder"](enc, ln)
+        sty = cpu_nets["pe_text_style_encoder"].forward_torch(enc, ln)
         pros = pep.prosody_encoder.forward_torch(enc, sty, ln)
         x = pep.compute_cross(pros, ft, sty, ln, frame_lengths=fl)
         for i in range(2):

@@ -8,6 +8,7 @@ pytestmark = pytest.mark.gpu
 # relative (to the tensor's abs-max) tolerances per stage in the fp32-grade modes
 FP32_REL = {
     "sp_text": 2e-5, "pe_text": 2e-5, "dur_logits": 5e-5, "pe_prosody": 2e-5,
+    "sp_style": 2e-5, "pe_style": 2e-5, "pe_cross": 2e-5,
     "pe_towers.pitch": 2e-5, "pe_towers.energy": 2e-5, "PitchEnergyPredictor.pitch": 5e-5,
     "decoder": 2e-5, "z_prior": 2e-5, "z_flow": 5e-5, "mel": 5e-5, "source": 2e-5,
     "har_spec": 2e-5, "logamp_prior": 5e-5,   # K = 7 175 contraction of OUR |X| (chained STFT error)
