@@ -166,6 +166,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-flush", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="launch every step eagerly (no CUDA graph replay)")
+    ap.add_argument("--lanes", type=int, default=2,
+                    help="batches in flight per GPU (SynthesizerPool lanes: own context + CUDA graph + stream each)")
+    ap.add_argument("--layers", default=None, help="write the per-layer GEMM table of the eager pass to this file")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else max(args.warmup, 0)
 
@@ -188,13 +191,14 @@ def main():
     from stylish_tts_b200 import fixture
     from stylish_tts_b200.config import ModelConfig
     from stylish_tts_b200.modules import build_model
-    from stylish_tts_b200.synth import Synthesizer
+    from stylish_tts_b200.synth import SynthesizerPool
 
     sds = fixture.fixture_nets(fixture.load_manifest(), seed=0)
     nets = build_model(ModelConfig())
     for k, m in nets.items():
         m.load_state_dict(sds[k])
-    syn = Synthesizer(nets, device=dev, precision=args.precision)
+    pool = SynthesizerPool(nets, device=dev, precision=args.precision, lanes=max(1, args.lanes), use_graphs=False)
+    syn = pool.lanes[0]
     eng = syn.engine
 
     tokens, durs, frames = workload(rank)
@@ -203,28 +207,32 @@ def main():
     dur_host = [d.to(torch.int32).pin_memory() for d in durs]
     tok_dev = [t.to(dev) for t in tokens]
     dur_dev = [d.to(dev, torch.int32) for d in durs]
-    audio_host = torch.empty(300 * sum(frames), dtype=torch.float32).pin_memory()
+    audio_host = [torch.empty(300 * sum(frames), dtype=torch.float32).pin_memory() for _ in pool.lanes]
     flush_buf = None if args.no_flush else torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
     use_graph = not args.no_graph
 
-    def step_resident():
+    # One step = one batch of the workload.  Steps are submitted round-robin to the pool's lanes: batch
+    # i + 1 may start while batch i is still running (independent batches; every one of the K steps runs
+    # to completion inside the timed region, which ends with pool.drain() + a device synchronisation).
+    def flush(lane):
         if flush_buf is not None:
-            flush_buf.fill_(1)
-        return syn.synthesize(tok_dev, durations=dur_dev, frames=frames, graph=use_graph)
+            with torch.cuda.stream(pool.streams[lane]):
+                flush_buf.fill_(1)
+
+    def step_resident():
+        flush(pool._next)
+        return pool.submit(tok_dev, durations=dur_dev, frames=frames, graph=use_graph)
 
     def step_eager():
         if flush_buf is not None:
             flush_buf.fill_(1)
         return syn.synthesize(tok_dev, durations=dur_dev, frames=frames, graph=False)
 
-    def step_e2e():
-        if flush_buf is not None:
-            flush_buf.fill_(1)
-        out = syn.synthesize(tok_host, durations=dur_host, frames=frames, graph=use_graph)
-        audio_host.copy_(out["audio_flat"], non_blocking=True)
-        torch.cuda.current_stream().synchronize()
-        return out
+    def step_e2e():   # inputs from pinned host memory, waveform back to pinned host memory, every step
+        lane = pool._next
+        flush(lane)
+        return pool.submit(tok_host, durations=dur_host, frames=frames, out_host=audio_host[lane], graph=use_graph)
 
     def barrier():
         if world > 1:
@@ -237,6 +245,7 @@ def main():
         e0.record()
         for _ in range(steps):
             fn()
+        pool.drain()
         e1.record()
         barrier()
         ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
@@ -244,9 +253,10 @@ def main():
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item())
 
-    for _ in range(args.warmup):
+    for _ in range(max(args.warmup, len(pool.lanes))):     # every lane warms up (and captures its graph)
         step_resident()
-    syn.check()
+    pool.synchronize()
+    pool.check()
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
@@ -265,9 +275,11 @@ def main():
     prof = eng.profile()
     eng.set_profiling(False)
 
-    for _ in range(2):
+    for _ in range(2 * len(pool.lanes)):
         step_e2e()
+    pool.synchronize()
     ms_e2e = timed(step_e2e, args.steps)
+    pool.synchronize()
 
     tot_audio = torch.tensor([audio_s], device=dev, dtype=torch.float64)
     tot_launch = torch.tensor([float(launches)], device=dev, dtype=torch.float64)
@@ -285,6 +297,12 @@ def main():
         tc_ms = sum(p["ms"] for p in tc)
         tc_fl = sum(p["flops"] for p in tc)
         top = max(prof, key=lambda p: p["ms"]) if prof else None
+        if args.layers:
+            with open(args.layers, "w") as f:
+                f.write("| layer | backend | ms/step | TFLOP/s (algorithmic) |\n|---|---|---|---|\n")
+                for p in sorted(prof, key=lambda p: -p["ms"]):
+                    f.write(f"| {p['name']} | {p['backend']} | {p['ms'] / args.steps:.4f} | "
+                            f"{p['flops'] / max(p['ms'], 1e-9) / 1e9:.1f} |\n")
         peak_tf = pk["bf16_sustained"]
         achieved = (tc_fl / (tc_ms / 1e3) / 1e12) if tc_ms > 0 else 0.0
         roofline = {
@@ -316,14 +334,15 @@ def main():
             "config": {"workload": f"BASELINE configs[1]: batch {BATCH} mixed-length utterances 0.25-10 s per GPU "
                                    f"({audio_s:.1f} audio-s, {sum(int(t.numel()) for t in tokens)} phonemes), default model.yml, "
                                    "fixture (seeded random-init) weights, synthetic durations",
-                       "precision": args.precision, "launch": "CUDA graph replay per step" if use_graph else "eager", "parallelism": f"utterance-sharded x{world}, no collective in the forward",
+                       "precision": args.precision, "launch": ("CUDA graph replay per step" if use_graph else "eager") +
+                                 f", {len(pool.lanes)} batches in flight (round-robin lanes, own context + stream each)", "parallelism": f"utterance-sharded x{world}, no collective in the forward",
                        "l2": "256 MiB flush write before every step; per-step working set >> 126 MB L2"
                              if flush_buf is not None else "no flush",
                        "workspace_bytes": eng.workspace_bytes()},
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
                     "h2d_bytes_per_step": int(sum(t.numel() * 8 for t in tokens) + sum(d.numel() * 4 for d in durs)),
-                    "d2h_bytes_per_step": int(audio_host.numel() * 4)},
+                    "d2h_bytes_per_step": int(audio_host[0].numel() * 4)},
             "gpu_launches": int(tot_launch.item()),
             "roofline": roofline,
             "cpu_baseline": cpu,

@@ -10,6 +10,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <stdint.h>
 
 #define STTS_TILE_M 128
@@ -50,7 +51,9 @@ struct Epi {
   __nv_bfloat16* outh; int ldh; int colh0;   // optional bf16 twin of `out`
   float* out2; int ldo2; int col20;
   __nv_bfloat16* outh2; int ldh2; int colh20;  // optional bf16 twin of `out2` (EPI_STFT)
-  __nv_bfloat16* outl; __nv_bfloat16* outl2;   // optional bf16 residual twins (x - bf16(x)) of out / out2: bf16x3 operands
+  // optional fp16 split twins of out / out2 (same ldh / colh geometry): g = fp16(x), l = fp16(x - g).
+  // x = g + l to ~2^-22 relative: operands of the f16x3 island GEMMs (g alone: the one-pass fp16 GEMM)
+  __half* outg; __half* outl; __half* outg2; __half* outl2;
   const float* bias;           // [N] (already permuted for the pair kinds) or null
   const float* res; int ldr; int rcol0;
   const float* segvec; int ldseg;            // per-utterance vector, row = segment
@@ -61,9 +64,13 @@ struct Epi {
 };
 
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + __expf(-x)); }
-// bf16 residual of x: bf16(x - float(bf16(x))).  x = hi + lo to ~2^-17 relative (bf16x3 operand split)
-__device__ __forceinline__ __nv_bfloat16 bf16_lo(float x) {
-  return __float2bfloat16_rn(x - __bfloat162float(__float2bfloat16_rn(x)));
+// fp16 split of x: g = fp16(x), l = fp16(x - g); x = g + l to ~2^-22 relative (|x| < 65504; below
+// 2^-3 the residual is an fp16 subnormal: absolute error <= 2^-25).  Operand split of the f16x3 GEMMs.
+__device__ __forceinline__ void f16_split(float x, __half* g, __half* l) {
+  x = fminf(fmaxf(x, -65504.f), 65504.f);    // saturate instead of inf (NaN passes through)
+  const __half h = __float2half_rn(x);
+  *g = h;
+  *l = __float2half_rn(x - __half2float(h));
 }
 
 // One thread owns row r (valid, segment seg) and NV consecutive output columns starting at n0
@@ -242,15 +249,19 @@ struct EpiPair {
     return t;
   }
   static __device__ __forceinline__ void store2(float* o, __nv_bfloat16* oh, float x0, float x1, bool both,
-                                                __nv_bfloat16* ol = nullptr) {
+                                                __half* og = nullptr, __half* ol = nullptr) {
     if (both) {
       *reinterpret_cast<float2*>(o) = make_float2(x0, x1);
       if (oh != nullptr) *reinterpret_cast<__nv_bfloat162*>(oh) = __floats2bfloat162_rn(x0, x1);
-      if (ol != nullptr) { ol[0] = bf16_lo(x0); ol[1] = bf16_lo(x1); }
+      if (og != nullptr) {
+        const __half2 g = __floats2half2_rn(x0, x1);
+        *reinterpret_cast<__half2*>(og) = g;
+        *reinterpret_cast<__half2*>(ol) = __floats2half2_rn(x0 - __low2float(g), x1 - __high2float(g));
+      }
     } else {
       o[0] = x0;
       if (oh != nullptr) oh[0] = __float2bfloat16_rn(x0);
-      if (ol != nullptr) ol[0] = bf16_lo(x0);
+      if (og != nullptr) f16_split(x0, og, ol);
     }
   }
   __device__ __forceinline__ void apply(const Epi& e, int r, int seg, int seg_first_row, float a0, float a1,
@@ -270,7 +281,8 @@ struct EpiPair {
         x1 = 0.5f * x1 * (1.f + erff(x1 * 0.70710678118654752440f));
       }
       store2(e.out + (size_t)r * e.ldo + e.col0 + n, e.outh ? e.outh + (size_t)r * e.ldh + e.colh0 + n : nullptr, x0, x1, v1,
-             e.outl ? e.outl + (size_t)r * e.ldh + e.colh0 + n : nullptr);
+             e.outg ? e.outg + (size_t)r * e.ldh + e.colh0 + n : nullptr,
+             e.outg ? e.outl + (size_t)r * e.ldh + e.colh0 + n : nullptr);
     } else if constexpr (KIND == EPI_RESSKIP) {
       const float x0 = a0 + b0, x1 = a1 + b1;
       if (n < e.split) {
@@ -311,8 +323,10 @@ struct EpiPair {
         e.out2[(size_t)r * e.ldo2 + e.col20 + c] = ph;
         if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = __float2bfloat16_rn(mag);
         if (e.outh2 != nullptr) e.outh2[(size_t)r * e.ldh2 + e.colh20 + c] = __float2bfloat16_rn(ph);
-        if (e.outl != nullptr) e.outl[(size_t)r * e.ldh + e.colh0 + c] = bf16_lo(mag);
-        if (e.outl2 != nullptr) e.outl2[(size_t)r * e.ldh2 + e.colh20 + c] = bf16_lo(ph);
+        if (e.outg != nullptr)
+          f16_split(mag, e.outg + (size_t)r * e.ldh + e.colh0 + c, e.outl + (size_t)r * e.ldh + e.colh0 + c);
+        if (e.outg2 != nullptr)
+          f16_split(ph, e.outg2 + (size_t)r * e.ldh2 + e.colh20 + c, e.outl2 + (size_t)r * e.ldh2 + e.colh20 + c);
       }
     }
   }
@@ -324,7 +338,7 @@ struct EpiPair {
 struct KSeg {
   const float* A; int lda; int col0;         // fp32 operand
   const __nv_bfloat16* Ah; int ldah; int colh0;  // bf16 twin (tensor-core bf16 mode)
-  const __nv_bfloat16* Al;                   // bf16 residual twin (bf16x3 mode), same geometry as Ah
+  const __half* Ag; const __half* Al; int ldag;  // fp16 split twins g / l (f16 and f16x3 modes), columns as colh0
   int taps; int pad; int cin_pad;            // cin_pad % 64 == 0
   int rows;                                  // rows allocated in A (bounds for zero fill)
 };
@@ -334,7 +348,10 @@ struct ConvGemm {
   int n_kseg;
   const float* W;                 // [Npad, Ktot] fp32, K-major
   const __nv_bfloat16* Wh;        // bf16 copy
-  const __nv_bfloat16* Wl;        // bf16 residual W - bf16(W)  (bf16x3 mode)
+  const __half* Wg;               // fp16(W * wscale)                       (f16 / f16x3 modes)
+  const __half* Wl;               // fp16(W * wscale - Wg)                  (f16x3 mode)
+  float acc_scale;                // accumulators are multiplied by this before the epilogue (1 / wscale / a-scale)
+  int f16;                        // 16-bit operands are the fp16 twins (Ag, Al, Wg, Wl) instead of the bf16 ones
   int Ktot;                       // sum taps*cin_pad
   int Npad;                       // multiple of 128
   Epi epi;

@@ -482,9 +482,9 @@ cudaError_t dwconv_adaln(const float* x, int ldx, const RowMap& map, int K, cons
 __global__ void __launch_bounds__(256) adaln2_kernel(const float* __restrict__ x, int ldx, RowMap map,
                                                      const float* __restrict__ gb1, const float* __restrict__ gb2,
                                                      int ldgb, float eps, float* __restrict__ y1,
-                                                     float* __restrict__ y2, int ldy, __nv_bfloat16* __restrict__ y1h,
-                                                     __nv_bfloat16* __restrict__ y2h, int ldyh,
-                                                     __nv_bfloat16* __restrict__ y1l, __nv_bfloat16* __restrict__ y2l) {
+                                                     float* __restrict__ y2, int ldy, __half* __restrict__ y1g,
+                                                     __half* __restrict__ y2g, int ldyh,
+                                                     __half* __restrict__ y1l, __half* __restrict__ y2l) {
   constexpr int C = 512;
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
@@ -517,13 +517,9 @@ __global__ void __launch_bounds__(256) adaln2_kernel(const float* __restrict__ x
       const float o1[4] = {(1.f + g1.x) * n[0] + b1.x, (1.f + g1.y) * n[1] + b1.y, (1.f + g1.z) * n[2] + b1.z,
                            (1.f + g1.w) * n[3] + b1.w};
       *reinterpret_cast<float4*>(y1 + r * ldy + c) = make_float4(o1[0], o1[1], o1[2], o1[3]);
-      if (y1h != nullptr) {
-        *reinterpret_cast<__nv_bfloat162*>(y1h + r * ldyh + c) = __floats2bfloat162_rn(o1[0], o1[1]);
-        *reinterpret_cast<__nv_bfloat162*>(y1h + r * ldyh + c + 2) = __floats2bfloat162_rn(o1[2], o1[3]);
-      }
-      if (y1l != nullptr) {
+      if (y1g != nullptr) {   // fp16 split twins: the operands of the output-head GEMMs
 #pragma unroll
-        for (int j = 0; j < 4; ++j) y1l[r * ldyh + c + j] = bf16_lo(o1[j]);
+        for (int j = 0; j < 4; ++j) f16_split(o1[j], y1g + r * ldyh + c + j, y1l + r * ldyh + c + j);
       }
       if (y2 != nullptr) {
         const float4 g2 = *reinterpret_cast<const float4*>(gb2 + (size_t)seg * ldgb + c);
@@ -531,13 +527,9 @@ __global__ void __launch_bounds__(256) adaln2_kernel(const float* __restrict__ x
         const float o2[4] = {(1.f + g2.x) * n[0] + b2.x, (1.f + g2.y) * n[1] + b2.y, (1.f + g2.z) * n[2] + b2.z,
                              (1.f + g2.w) * n[3] + b2.w};
         *reinterpret_cast<float4*>(y2 + r * ldy + c) = make_float4(o2[0], o2[1], o2[2], o2[3]);
-        if (y2h != nullptr) {
-          *reinterpret_cast<__nv_bfloat162*>(y2h + r * ldyh + c) = __floats2bfloat162_rn(o2[0], o2[1]);
-          *reinterpret_cast<__nv_bfloat162*>(y2h + r * ldyh + c + 2) = __floats2bfloat162_rn(o2[2], o2[3]);
-        }
-        if (y2l != nullptr) {
+        if (y2g != nullptr) {
 #pragma unroll
-          for (int j = 0; j < 4; ++j) y2l[r * ldyh + c + j] = bf16_lo(o2[j]);
+          for (int j = 0; j < 4; ++j) f16_split(o2[j], y2g + r * ldyh + c + j, y2l + r * ldyh + c + j);
         }
       }
     }
@@ -545,9 +537,9 @@ __global__ void __launch_bounds__(256) adaln2_kernel(const float* __restrict__ x
 }
 
 cudaError_t adaln2(const float* x, int ldx, const RowMap& map, const float* gb1, const float* gb2, int ldgb, float eps,
-                   float* y1, float* y2, int ldy, __nv_bfloat16* y1h, __nv_bfloat16* y2h, int ldyh, __nv_bfloat16* y1l,
-                   __nv_bfloat16* y2l, cudaStream_t st) {
-  adaln2_kernel<<<map.n_tiles, 256, 0, st>>>(x, ldx, map, gb1, gb2, ldgb, eps, y1, y2, ldy, y1h, y2h, ldyh, y1l, y2l);
+                   float* y1, float* y2, int ldy, __half* y1g, __half* y2g, int ldyh, __half* y1l, __half* y2l,
+                   cudaStream_t st) {
+  adaln2_kernel<<<map.n_tiles, 256, 0, st>>>(x, ldx, map, gb1, gb2, ldgb, eps, y1, y2, ldy, y1g, y2g, ldyh, y1l, y2l);
   return cudaGetLastError();
 }
 
@@ -629,9 +621,9 @@ cudaError_t rowdot(const float* x, int ldx, int C, const RowMap& map, const floa
   return cudaGetLastError();
 }
 
-// bf16 hi / residual twins of the first C columns of the valid rows, recomputed from the fp32 master
+// fp16 split twins of the first C columns of the valid rows, recomputed from the fp32 master
 __global__ void __launch_bounds__(256) twin_refresh_kernel(const float* __restrict__ f, int ld, int C, RowMap map,
-                                                           __nv_bfloat16* __restrict__ h, __nv_bfloat16* __restrict__ l) {
+                                                           __half* __restrict__ h, __half* __restrict__ l) {
   const int tile = blockIdx.x;
   if (map.tile_seg[tile] < 0) return;
   const int nvalid = map.tile_nvalid[tile];
@@ -639,12 +631,10 @@ __global__ void __launch_bounds__(256) twin_refresh_kernel(const float* __restri
     const int lr = i / C, c = i - lr * C;
     const size_t o = (size_t)(tile * 128 + lr) * ld + c;
     const float x = f[o];
-    if (h != nullptr) h[o] = __float2bfloat16_rn(x);
-    if (l != nullptr) l[o] = bf16_lo(x);
+    f16_split(x, h + o, l + o);
   }
 }
-cudaError_t twin_refresh(const float* f, int ld, int C, const RowMap& map, __nv_bfloat16* h, __nv_bfloat16* l,
-                         cudaStream_t st) {
+cudaError_t twin_refresh(const float* f, int ld, int C, const RowMap& map, __half* h, __half* l, cudaStream_t st) {
   dim3 grid(map.n_tiles, 4);
   twin_refresh_kernel<<<grid, 256, 0, st>>>(f, ld, C, map, h, l);
   return cudaGetLastError();

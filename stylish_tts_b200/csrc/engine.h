@@ -25,7 +25,9 @@ struct PackedGemm {
   float* Wf = nullptr;            // exact fp32                     [Npad, Ktot]
   float* Whl = nullptr;           // tf32 hi rows then lo rows      [2 * Npad, Ktot]
   __nv_bfloat16* Wh = nullptr;    // bf16                           [Npad, Ktot]
-  __nv_bfloat16* Wl = nullptr;    // bf16 residual W - bf16(W)      [Npad, Ktot]
+  __half* Wg = nullptr;           // fp16(W * wscale)               [Npad, Ktot]
+  __half* Wl = nullptr;           // fp16(W * wscale - Wg)          [Npad, Ktot]
+  float wscale = 1.f;             // power of two
   float* bias = nullptr;          // [Npad] (zeros when the layer has no bias)
   std::string name;               // layer name (profiling)
   double k_real = 0;              // un-padded K (algorithmic FLOPs = 2 * rows * N * k_real)
@@ -34,7 +36,10 @@ struct PackedGemm {
 struct Act {          // an activation buffer: fp32 + optional bf16 twin, same ld
   float* f = nullptr;
   __nv_bfloat16* h = nullptr;
-  __nv_bfloat16* l = nullptr;   // bf16 residual twin (operands of the bf16x3 island GEMMs)
+  __half* g = nullptr;          // fp16 split twins g = fp16(s x), l = fp16(s x - g): operands of the
+  __half* l = nullptr;          //   island GEMMs (f16x3; g alone for the one-pass fp16 GEMM)
+  int ldg = 0;                  // row pitch of g / l (elements)
+  float gscale = 1.f;           // s: power-of-two pre-scale of the fp16 twins
   int ld = 0;
   int rows = 0;
 };

@@ -143,7 +143,9 @@ __device__ __forceinline__ float rna_tf32(float x) {
   return __uint_as_float(r);
 }
 
-enum { MODE_BF16 = 0, MODE_TF32X3 = 1, MODE_BF16X3 = 2 };
+// MODE_BF16 doubles as the one-pass fp16 GEMM (runtime instruction-descriptor formats), MODE_F16X3 is
+// the three-pass fp16 split (hi*hi + hi*lo + lo*hi, fp32-grade), MODE_TF32X3 the tf32 split on fp32 operands
+enum { MODE_BF16 = 0, MODE_TF32X3 = 1, MODE_F16X3 = 2 };
 
 template <int MODE, int BN>
 struct Cfg {
@@ -156,19 +158,21 @@ struct Cfg {
   static constexpr int kBTile = BN * 128;                 // bytes
   static constexpr int kStageBytes = kSplit ? (2 * kATile + 2 * kBTile) : (kATile + kBTile);
   static constexpr int kStages = kSplit ? (BN == 128 ? 3 : 2) : (BN == 128 ? 6 : 4);
-  // tf32x3: the A residual is computed in shared memory by the converter warps; bf16x3: it is loaded
+  // tf32x3: the A residual is computed in shared memory by the converter warps; f16x3: it is loaded
   static constexpr int kTxBytes = kTF32 ? (kATile + 2 * kBTile) : (kSplit ? 2 * kATile + 2 * kBTile : kATile + kBTile);
   static constexpr int kEpiWarps = BN / 16;                // one 64-column slab x 32-row quarter per warp
   static constexpr int kThreads = 64 + 32 * kEpiWarps;
   static constexpr int kSmem = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
-  static constexpr uint32_t kIdesc = (1u << 4) | ((kTF32 ? 2u : 1u) << 7) | ((kTF32 ? 2u : 1u) << 10) |
-                                     ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+  // instruction descriptor without the A / B format fields (bits 7-9, 10-12: 0 = f16, 1 = bf16, 2 = tf32)
+  static constexpr uint32_t kIdescBase = (1u << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
 };
 
 struct TcParams {
   int n_kseg;
   int taps[2], pad[2], cin_chunks[2], col0[2];   // col0 in elements of the operand dtype
   int n_chunks;
+  uint32_t ab_fmt;      // operand format of the MMAs: 0 = f16, 1 = bf16, 2 = tf32
+  float acc_scale;      // accumulators * acc_scale before the epilogue (power-of-two operand scaling undone)
 };
 
 template <int MODE, int BN, int KIND>
@@ -215,6 +219,7 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  const uint32_t idesc = C::kIdescBase | (p.ab_fmt << 7) | (p.ab_fmt << 10);
 
   auto stage_ptr = [&](int s) { return smem + (size_t)s * C::kStageBytes; };
 
@@ -262,12 +267,12 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
           if constexpr (C::kSplit) {
             const uint32_t a_lo = a_hi + C::kATile, b_hi = a_hi + 2 * C::kATile, b_lo = b_hi + C::kBTile;
             // small terms first, then the leading term
-            tc_mma<C::kTF32>(tmem_base, make_sdesc(a_lo + koff), make_sdesc(b_hi + koff), C::kIdesc, (ch | k) != 0);
-            tc_mma<C::kTF32>(tmem_base, make_sdesc(a_hi + koff), make_sdesc(b_lo + koff), C::kIdesc, 1);
-            tc_mma<C::kTF32>(tmem_base, make_sdesc(a_hi + koff), make_sdesc(b_hi + koff), C::kIdesc, 1);
+            tc_mma<C::kTF32>(tmem_base, make_sdesc(a_lo + koff), make_sdesc(b_hi + koff), idesc, (ch | k) != 0);
+            tc_mma<C::kTF32>(tmem_base, make_sdesc(a_hi + koff), make_sdesc(b_lo + koff), idesc, 1);
+            tc_mma<C::kTF32>(tmem_base, make_sdesc(a_hi + koff), make_sdesc(b_hi + koff), idesc, 1);
           } else {
             const uint32_t b = a_hi + C::kATile;
-            tc_mma<false>(tmem_base, make_sdesc(a_hi + koff), make_sdesc(b + koff), C::kIdesc, (ch | k) != 0);
+            tc_mma<false>(tmem_base, make_sdesc(a_hi + koff), make_sdesc(b + koff), idesc, (ch | k) != 0);
           }
         }
         tc_commit(&empty[stage]);
@@ -326,7 +331,7 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
         __syncwarp();                            // previous slab fully consumed
 #pragma unroll
         for (int j = 0; j < 64; j += 2)
-          *reinterpret_cast<float2*>(stg + lane * kStgLd + j) = make_float2(v[j], v[j + 1]);
+          *reinterpret_cast<float2*>(stg + lane * kStgLd + j) = make_float2(v[j] * p.acc_scale, v[j + 1] * p.acc_scale);
       }
       __syncwarp();
       if constexpr (EpiPair<KIND, false>::kHasPre) {
@@ -422,12 +427,13 @@ cudaError_t launch_one(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
   p.n_chunks = 0;
   for (int s = 0; s < 2; ++s) {
     const KSeg& ks = g.seg[s < g.n_kseg ? s : 0];
-    const void* base = (MODE == MODE_TF32X3) ? (const void*)ks.A : (const void*)ks.Ah;
-    const int ld = (MODE == MODE_TF32X3) ? ks.lda : ks.ldah;
+    const bool f16 = (MODE == MODE_F16X3) || (MODE == MODE_BF16 && g.f16);
+    const void* base = (MODE == MODE_TF32X3) ? (const void*)ks.A : (f16 ? (const void*)ks.Ag : (const void*)ks.Ah);
+    const int ld = (MODE == MODE_TF32X3) ? ks.lda : (f16 ? ks.ldag : ks.ldah);
     if (base == nullptr) return cudaErrorInvalidValue;
     if (!get_map(base, ks.rows, ld, elem, 128, &mA[s])) return cudaErrorNotSupported;
     mAlo[s] = mA[s];
-    if (MODE == MODE_BF16X3) {
+    if (MODE == MODE_F16X3) {
       if (ks.Al == nullptr) return cudaErrorInvalidValue;
       if (!get_map(ks.Al, ks.rows, ld, elem, 128, &mAlo[s])) return cudaErrorNotSupported;
     }
@@ -439,14 +445,22 @@ cudaError_t launch_one(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
       p.n_chunks += ks.taps * p.cin_chunks[s];
     }
   }
+  p.acc_scale = 1.f;
   if (MODE == MODE_BF16) {
-    if (!get_map(g.Wh, g.Npad, g.Ktot, 2, BN, &mW)) return cudaErrorNotSupported;
+    const void* w = g.f16 ? (const void*)g.Wg : (const void*)g.Wh;
+    if (w == nullptr) return cudaErrorInvalidValue;
+    if (!get_map(w, g.Npad, g.Ktot, 2, BN, &mW)) return cudaErrorNotSupported;
     mWlo = mW;
-  } else if (MODE == MODE_BF16X3) {
-    if (g.Wl == nullptr) return cudaErrorInvalidValue;
-    if (!get_map(g.Wh, g.Npad, g.Ktot, 2, BN, &mW)) return cudaErrorNotSupported;
+    p.ab_fmt = g.f16 ? 0u : 1u;
+    if (g.f16) p.acc_scale = g.acc_scale;
+  } else if (MODE == MODE_F16X3) {
+    if (g.Wg == nullptr || g.Wl == nullptr) return cudaErrorInvalidValue;
+    if (!get_map(g.Wg, g.Npad, g.Ktot, 2, BN, &mW)) return cudaErrorNotSupported;
     if (!get_map(g.Wl, g.Npad, g.Ktot, 2, BN, &mWlo)) return cudaErrorNotSupported;
+    p.ab_fmt = 0u;
+    p.acc_scale = g.acc_scale;
   } else {
+    p.ab_fmt = 2u;
     // W holds hi (tf32-rounded) in rows [0, Npad) and lo in rows [Npad, 2*Npad)
     if (!get_map(g.W, g.Npad, g.Ktot, 4, BN, &mW)) return cudaErrorNotSupported;
     if (!get_map(g.W + (size_t)g.Npad * g.Ktot, g.Npad, g.Ktot, 4, BN, &mWlo)) return cudaErrorNotSupported;
@@ -501,8 +515,8 @@ cudaError_t conv_gemm_tc_bf16(const ConvGemm& g, const RowMap& map, cudaStream_t
 cudaError_t conv_gemm_tc_tf32x3(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
   return launch_mode<MODE_TF32X3>(g, map, st);
 }
-cudaError_t conv_gemm_tc_bf16x3(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
-  return launch_mode<MODE_BF16X3>(g, map, st);
+cudaError_t conv_gemm_tc_f16x3(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
+  return launch_mode<MODE_F16X3>(g, map, st);
 }
 
 }  // namespace stts

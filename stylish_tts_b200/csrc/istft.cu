@@ -13,8 +13,8 @@ namespace stts {
 // frame, a guard row of the layout) receives the replicate-padded frame.
 __global__ void __launch_bounds__(256) polar_kernel(const float* __restrict__ la, const float* __restrict__ ph, int ld,
                                                     int n_bins, RowMap map, float* __restrict__ spec, int lds,
-                                                    __nv_bfloat16* __restrict__ spech, int ldsh,
-                                                    __nv_bfloat16* __restrict__ specl) {
+                                                    __half* __restrict__ specg, int ldsh,
+                                                    __half* __restrict__ specl, float gscale) {
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
   if (seg < 0) return;
@@ -33,19 +33,18 @@ __global__ void __launch_bounds__(256) polar_kernel(const float* __restrict__ la
     const float re = a * cs, im = a * sn;
     const size_t o = (size_t)(m0 + lr) * lds + 2 * k;
     *reinterpret_cast<float2*>(spec + o) = make_float2(re, im);
-    if (spech != nullptr)
-      *reinterpret_cast<__nv_bfloat162*>(spech + (size_t)(m0 + lr) * ldsh + 2 * k) = __floats2bfloat162_rn(re, im);
-    if (specl != nullptr) {
-      specl[(size_t)(m0 + lr) * ldsh + 2 * k] = bf16_lo(re);
-      specl[(size_t)(m0 + lr) * ldsh + 2 * k + 1] = bf16_lo(im);
+    if (specg != nullptr) {   // fp16 split twins (pre-scaled by gscale: e^logamp may exceed the fp16 range)
+      const size_t og = (size_t)(m0 + lr) * ldsh + 2 * k;
+      f16_split(re * gscale, specg + og, specl + og);
+      f16_split(im * gscale, specg + og + 1, specl + og + 1);
     }
   }
 }
 
 cudaError_t polar_spec(const float* logamp, const float* phase, int ld, int n_bins, const RowMap& map, float* spec,
-                       int lds, __nv_bfloat16* spech, int ldsh, __nv_bfloat16* specl, cudaStream_t st) {
+                       int lds, __half* specg, int ldsh, __half* specl, float gscale, cudaStream_t st) {
   dim3 grid(map.n_tiles, 4);
-  polar_kernel<<<grid, 256, 0, st>>>(logamp, phase, ld, n_bins, map, spec, lds, spech, ldsh, specl);
+  polar_kernel<<<grid, 256, 0, st>>>(logamp, phase, ld, n_bins, map, spec, lds, specg, ldsh, specl, gscale);
   return cudaGetLastError();
 }
 

@@ -9,7 +9,7 @@ namespace stts {
 cudaError_t conv_gemm_simt(const ConvGemm& g, const RowMap& map, cudaStream_t st);
 cudaError_t conv_gemm_tc_bf16(const ConvGemm& g, const RowMap& map, cudaStream_t st);
 cudaError_t conv_gemm_tc_tf32x3(const ConvGemm& g, const RowMap& map, cudaStream_t st);
-cudaError_t conv_gemm_tc_bf16x3(const ConvGemm& g, const RowMap& map, cudaStream_t st);
+cudaError_t conv_gemm_tc_f16x3(const ConvGemm& g, const RowMap& map, cudaStream_t st);
 void tc_map_cache_clear();
 
 // ---- elementwise.cu
@@ -40,15 +40,14 @@ cudaError_t dwconv_adaln(const float* x, int ldx, const RowMap& map, int K, cons
                          const float* gb, int ldgb, float eps, float* y, int ldy, __nv_bfloat16* yh, int ldyh,
                          cudaStream_t st);
 cudaError_t adaln2(const float* x, int ldx, const RowMap& map, const float* gb1, const float* gb2, int ldgb, float eps,
-                   float* y1, float* y2, int ldy, __nv_bfloat16* y1h, __nv_bfloat16* y2h, int ldyh, __nv_bfloat16* y1l,
-                   __nv_bfloat16* y2l, cudaStream_t st);
+                   float* y1, float* y2, int ldy, __half* y1g, __half* y2g, int ldyh, __half* y1l, __half* y2l,
+                   cudaStream_t st);
 cudaError_t grn_apply(float* x, int ldx, int C, const RowMap& map, const float* gx, const float* gamma,
                       const float* beta, float* scale_scratch, __nv_bfloat16* xh, int ldxh, cudaStream_t st);
 cudaError_t rowdot(const float* x, int ldx, int C, const RowMap& map, const float* w, const float* bias, const int* cu,
                    float* dense, cudaStream_t st);
 cudaError_t fill(float* p, size_t n, float v, cudaStream_t st);
-cudaError_t twin_refresh(const float* f, int ld, int C, const RowMap& map, __nv_bfloat16* h, __nv_bfloat16* l,
-                         cudaStream_t st);
+cudaError_t twin_refresh(const float* f, int ld, int C, const RowMap& map, __half* h, __half* l, cudaStream_t st);
 
 // ---- token_rate.cu
 cudaError_t embed_tokens(const int* tok, const int* cu_tok, const float* table, int C, int n_vocab, const RowMap& map,
@@ -79,11 +78,11 @@ cudaError_t pcph_prefix(const float* p4, const RowMap& map, double* prefix, Sour
 // src has (R + 16) rows of `ld` floats: logical hop row h of a segment lives at row seg_start + h + 8
 cudaError_t pcph_source(const float* p4, const double* prefix, const SourceMeta* meta, const float* noise,
                         const float* init_phase, const int* cu4, const RowMap& map, float* src, int ld,
-                        float* dense_out, cudaStream_t st);
+                        __half* srcg, __half* srcl, int ldg, float gscale, float* dense_out, cudaStream_t st);
 
 // ---- istft.cu
 cudaError_t polar_spec(const float* logamp, const float* phase, int ld, int n_bins, const RowMap& map, float* spec,
-                       int lds, __nv_bfloat16* spech, int ldsh, __nv_bfloat16* specl, cudaStream_t st);
+                       int lds, __half* specg, int ldsh, __half* specl, float gscale, cudaStream_t st);
 cudaError_t ola_tanh(const float* frames, int ldf, const float* wsq, const int* cu4, const RowMap& map, float* audio,
                      cudaStream_t st);
 

@@ -83,21 +83,30 @@ struct Builder {
     for (int s = 0; s < 2; ++s) { p.taps[s] = taps[s]; p.pad[s] = pad[s]; p.cin_pad[s] = cin_pad[s]; }
     const size_t n = (size_t)Npad * Ktot;
     std::vector<float> hl(2 * n);
-    std::vector<uint16_t> bf(n), bl(n);
+    std::vector<uint16_t> bf(n);
+    std::vector<__half> hg(n), hlo(n);
+    // fp16 split of W * wscale, wscale the power of two that puts max |W| into [2^13, 2^14): the
+    // residuals of all but vanishing weights stay normal fp16 numbers (x = g + l to ~2^-22)
+    float wmax = 0.f;
+    for (size_t i = 0; i < n; ++i) wmax = std::fmax(wmax, std::fabs(W[i]));
+    int ex = 0;
+    if (wmax > 0.f) { std::frexp(wmax, &ex); }     // wmax = m * 2^ex, m in [0.5, 1)
+    const float wscale = std::ldexp(1.0f, 14 - ex);
+    p.wscale = wscale;
     for (size_t i = 0; i < n; ++i) {
       const float hi = trunc_tf32(W[i]);
       hl[i] = hi;
       hl[n + i] = trunc_tf32(W[i] - hi);
       bf[i] = f2bf(W[i]);
-      uint32_t u = (uint32_t)bf[i] << 16;
-      float bh;
-      std::memcpy(&bh, &u, 4);
-      bl[i] = f2bf(W[i] - bh);
+      const float ws = W[i] * wscale;
+      hg[i] = __float2half_rn(ws);
+      hlo[i] = __float2half_rn(ws - __half2float(hg[i]));
     }
     p.Wf = dev_upload(c, W.data(), n);
     p.Whl = dev_upload(c, hl.data(), 2 * n);
     p.Wh = reinterpret_cast<__nv_bfloat16*>(dev_upload(c, bf.data(), n));
-    p.Wl = reinterpret_cast<__nv_bfloat16*>(dev_upload(c, bl.data(), n));
+    p.Wg = reinterpret_cast<__half*>(dev_upload(c, reinterpret_cast<const uint16_t*>(hg.data()), n));
+    p.Wl = reinterpret_cast<__half*>(dev_upload(c, reinterpret_cast<const uint16_t*>(hlo.data()), n));
     p.bias = dev_upload(c, bias.data(), (size_t)Npad);
     return p;
   }
@@ -108,7 +117,7 @@ int pad64(int c) { return (c + 63) / 64 * 64; }
 }  // namespace
 
 void free_pack(PackedGemm& p) {
-  cudaFree(p.Wf); cudaFree(p.Whl); cudaFree(p.Wh); cudaFree(p.Wl); cudaFree(p.bias);
+  cudaFree(p.Wf); cudaFree(p.Whl); cudaFree(p.Wh); cudaFree(p.Wg); cudaFree(p.Wl); cudaFree(p.bias);
   p = PackedGemm();
 }
 
@@ -631,20 +640,23 @@ int finalize_weights(Context& c) {
           default: *c_out = s0; *s_out = -c0; break;
         }
       };
-      {  // forward: rows (re_k, im_k) interleaved; K = 16 hop-taps x 75 samples (padded to 96)
+      // forward: rows (re_k, im_k) interleaved; K = 16 hop-taps x 75 samples, each tap padded to 96
+      // columns for the fp32 / tf32 operand ("stft") and to 128 for the 16-bit operand ("stft16": one
+      // 128-byte swizzle row holds 64 fp16 values, so a tap must be a multiple of 64 columns)
+      for (int cpad : {96, 128}) {
         Builder b;
-        const int t[2] = {16, 0}, pd[2] = {0, 0}, cp[2] = {96, 0};
+        const int t[2] = {16, 0}, pd[2] = {0, 0}, cp[2] = {cpad, 0};
         b.init(2050, 1, t, pd, cp);
         for (int k = 0; k <= 1024; ++k)
           for (int n = 0; n < 1200; ++n) {
             const int j = n / 75, cc = n % 75;
             double ca, sa;
             cs(k, 424 + n, &ca, &sa);
-            b.W[(size_t)(2 * k) * b.Ktot + j * 96 + cc] = (float)(win[n] * ca);
-            b.W[(size_t)(2 * k + 1) * b.Ktot + j * 96 + cc] = (sa == 0.0) ? 0.f : (float)(-win[n] * sa);
+            b.W[(size_t)(2 * k) * b.Ktot + j * cpad + cc] = (float)(win[n] * ca);
+            b.W[(size_t)(2 * k + 1) * b.Ktot + j * cpad + cc] = (sa == 0.0) ? 0.f : (float)(-win[n] * sa);
           }
         b.k_real = 1200;
-        c.gemm["stft"] = b.upload(c);
+        c.gemm[cpad == 96 ? "stft" : "stft16"] = b.upload(c);
       }
       {  // inverse: irfft (1/N, Hermitian doubling, imag of DC / Nyquist ignored) x window
         Builder b;

@@ -88,7 +88,8 @@ __global__ void __launch_bounds__(256) pcph_source_kernel(const float* __restric
                                                           const float* __restrict__ init_phase,
                                                           const int* __restrict__ cu4, RowMap map,
                                                           float* __restrict__ src, int ld,
-                                                          float* __restrict__ dense_out) {
+                                                          __half* __restrict__ srcg, __half* __restrict__ srcl,
+                                                          int ldg, float gscale, float* __restrict__ dense_out) {
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
   if (seg < 0) return;
@@ -131,14 +132,17 @@ __global__ void __launch_bounds__(256) pcph_source_kernel(const float* __restric
     }
     val += 0.01f * noise[dense_base + t];
     src[(size_t)(s0 + h + 8) * ld + c] = val;
+    if (srcg != nullptr)   // fp16 split twins of the STFT operand (pre-scaled: |val| < ~5)
+      f16_split(val * gscale, srcg + (size_t)(s0 + h + 8) * ldg + c, srcl + (size_t)(s0 + h + 8) * ldg + c);
     if (dense_out != nullptr && interior) dense_out[dense_base + t] = val;
   }
 }
 
 cudaError_t pcph_source(const float* p4, const double* prefix, const SourceMeta* meta, const float* noise,
                         const float* init_phase, const int* cu4, const RowMap& map, float* src, int ld,
-                        float* dense_out, cudaStream_t st) {
-  pcph_source_kernel<<<map.n_tiles, 256, 0, st>>>(p4, prefix, meta, noise, init_phase, cu4, map, src, ld, dense_out);
+                        __half* srcg, __half* srcl, int ldg, float gscale, float* dense_out, cudaStream_t st) {
+  pcph_source_kernel<<<map.n_tiles, 256, 0, st>>>(p4, prefix, meta, noise, init_phase, cu4, map, src, ld, srcg, srcl,
+                                                  ldg, gscale, dense_out);
   return cudaGetLastError();
 }
 

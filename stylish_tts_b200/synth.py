@@ -254,3 +254,54 @@ class Synthesizer:
     def check(self):
         """Raises RuntimeError if an utterance hit the reference's torch.min-of-empty error path."""
         self.engine.check_source_status()
+
+
+class SynthesizerPool:
+    """Throughput mode: ``lanes`` independent Synthesizers (own C context, workspace, CUDA graphs and
+    streams; the nn.Modules are shared) fed round-robin.  Batches are independent, so the token-rate
+    chains of batch i + 1 (small, latency-bound kernels) overlap the frame-rate GEMMs of batch i on the
+    same GPU.  ``submit`` enqueues one batch and returns immediately; a lane is reused only after its
+    previous batch (including the optional device -> host copy of the waveform) has finished."""
+
+    def __init__(self, nets=None, device="cuda:0", precision: str = "fp32", model_config=None, lanes: int = 2,
+                 use_graphs: bool = True):
+        self.device = torch.device(device)
+        first = Synthesizer(nets, device, precision, model_config, use_graphs)
+        self.lanes = [first] + [Synthesizer(first.nets, device, precision, model_config, use_graphs)
+                                for _ in range(lanes - 1)]
+        self.streams = [torch.cuda.Stream(self.device) for _ in range(lanes)]
+        self._done = [None] * lanes
+        self._next = 0
+
+    def submit(self, tokens, durations=None, frames=None, out_host: Optional[torch.Tensor] = None, **kw):
+        """Enqueue one batch on the next lane.  ``out_host``: pinned [sum 300 F] buffer that receives the
+        concatenated waveform.  Returns (result dict, event recorded after the batch's last operation)."""
+        i = self._next
+        self._next = (i + 1) % len(self.lanes)
+        if self._done[i] is not None:
+            self._done[i].synchronize()          # the lane's static graph buffers / host buffer are free again
+        s = self.streams[i]
+        s.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(s):
+            out = self.lanes[i].synthesize(tokens, durations=durations, frames=frames, **kw)
+            if out_host is not None:
+                out_host.copy_(out["audio_flat"], non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(s)
+        self._done[i] = ev
+        return out, ev
+
+    def drain(self):
+        """Make the current stream wait for every lane (no host synchronisation)."""
+        cur = torch.cuda.current_stream(self.device)
+        for s in self.streams:
+            cur.wait_stream(s)
+
+    def synchronize(self):
+        for ev in self._done:
+            if ev is not None:
+                ev.synchronize()
+
+    def check(self):
+        for lane in self.lanes:
+            lane.check()

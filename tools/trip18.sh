@@ -1,0 +1,5 @@
+mkdir -p gpurun_out; rm -f gpurun_out/rc.txt
+timeout 600 python bench.py --steps 5 --warmup 3 --no-cpu-baseline --layers gpurun_out/layers_bf16.md > gpurun_out/bench_bf16.json 2> gpurun_out/bench_bf16.err; echo "bench rc=$?" >> gpurun_out/rc.txt
+timeout 300 python tools/profile_step.py bf16 > gpurun_out/profile_plain.log 2>&1 && \
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv --log-file gpurun_out/launches_bf16.csv python tools/profile_step.py bf16 > gpurun_out/ncu.log 2>&1; echo "ncu rc=$?" >> gpurun_out/rc.txt
+cat gpurun_out/rc.txt
