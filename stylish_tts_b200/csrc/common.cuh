@@ -61,6 +61,9 @@ struct Epi {
   int split;                   // EPI_RESSKIP
   int accumulate2;             // EPI_RESSKIP: out2 += (1) or = (0)
   const int* seg_start;        // EPI_STFT: first row of every segment (frame 0 is real by symmetry)
+  // EPI_SILU, tcgen05 kernel only: per-(tile, row quarter) column sums of squares of the activated output,
+  // [n_tiles * 4, colss_ld] fp32 -- the L2-over-time statistic of GRN without re-reading the tensor
+  float* colss; int colss_ld;
 };
 
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + __expf(-x)); }
@@ -206,6 +209,7 @@ struct EpiPair {
   }
   static __device__ __forceinline__ float dv(float a, float b) { if constexpr (FAST) return __fdividef(a, b); else return a / b; }
   float b0, b1, g0, g1;
+  float ss0, ss1;  // EPI_SILU: running sum of squares of the two columns over the slab's rows
   int n;           // even accumulator column
   bool v0, v1;     // column n / n + 1 inside the logical N
   __device__ __forceinline__ void init(const Epi& e, int seg, int n_) {
@@ -214,6 +218,7 @@ struct EpiPair {
     b0 = (e.bias != nullptr && v0) ? e.bias[n] : 0.f;
     b1 = (e.bias != nullptr && v1) ? e.bias[n + 1] : 0.f;
     g0 = g1 = 0.f;
+    ss0 = ss1 = 0.f;
     if constexpr (KIND == EPI_GATE) {
       if (v0) {
         g0 = e.segvec[(size_t)seg * e.ldseg + (n >> 1)];
@@ -251,21 +256,32 @@ struct EpiPair {
   static __device__ __forceinline__ void store2(float* o, __nv_bfloat16* oh, float x0, float x1, bool both,
                                                 __half* og = nullptr, __half* ol = nullptr) {
     if (both) {
-      *reinterpret_cast<float2*>(o) = make_float2(x0, x1);
+      if (o != nullptr) *reinterpret_cast<float2*>(o) = make_float2(x0, x1);
       if (oh != nullptr) *reinterpret_cast<__nv_bfloat162*>(oh) = __floats2bfloat162_rn(x0, x1);
       if (og != nullptr) {
         const __half2 g = __floats2half2_rn(x0, x1);
         *reinterpret_cast<__half2*>(og) = g;
-        *reinterpret_cast<__half2*>(ol) = __floats2half2_rn(x0 - __low2float(g), x1 - __high2float(g));
+        if (ol != nullptr)
+          *reinterpret_cast<__half2*>(ol) = __floats2half2_rn(x0 - __low2float(g), x1 - __high2float(g));
       }
     } else {
-      o[0] = x0;
+      if (o != nullptr) o[0] = x0;
       if (oh != nullptr) oh[0] = __float2bfloat16_rn(x0);
-      if (og != nullptr) f16_split(x0, og, ol);
+      if (og != nullptr) { __half lo; f16_split(x0, og, ol != nullptr ? ol : &lo); }
+    }
+  }
+  // after the last row of the slab: per-(tile, quarter) column statistics
+  __device__ __forceinline__ void finish(const Epi& e, int tile, int q) const {
+    if constexpr (KIND == EPI_SILU) {
+      if (e.colss != nullptr && v0) {
+        float* p = e.colss + (size_t)(tile * 4 + q) * e.colss_ld + n;
+        p[0] = ss0;
+        if (v1) p[1] = ss1;
+      }
     }
   }
   __device__ __forceinline__ void apply(const Epi& e, int r, int seg, int seg_first_row, float a0, float a1,
-                                        float2 t) const {
+                                        float2 t) {
     if (!v0) return;
     if constexpr (KIND == EPI_BIAS || KIND == EPI_RES_SCALE || KIND == EPI_SILU || KIND == EPI_ADD ||
                   KIND == EPI_RELU || KIND == EPI_GELU) {
@@ -273,16 +289,20 @@ struct EpiPair {
       if constexpr (KIND == EPI_RES_SCALE) {
         x0 = (x0 + t.x) * e.scale; x1 = (x1 + t.y) * e.scale;
       }
-      if constexpr (KIND == EPI_SILU) { x0 = dv(x0, 1.f + ex(-x0)); x1 = dv(x1, 1.f + ex(-x1)); }
+      if constexpr (KIND == EPI_SILU) {
+        x0 = dv(x0, 1.f + ex(-x0)); x1 = dv(x1, 1.f + ex(-x1));
+        ss0 = fmaf(x0, x0, ss0); ss1 = fmaf(x1, x1, ss1);
+      }
       if constexpr (KIND == EPI_ADD) { x0 += t.x; x1 += t.y; }
       if constexpr (KIND == EPI_RELU) { x0 = fmaxf(x0, 0.f); x1 = fmaxf(x1, 0.f); }
       if constexpr (KIND == EPI_GELU) {
         x0 = 0.5f * x0 * (1.f + erff(x0 * 0.70710678118654752440f));
         x1 = 0.5f * x1 * (1.f + erff(x1 * 0.70710678118654752440f));
       }
-      store2(e.out + (size_t)r * e.ldo + e.col0 + n, e.outh ? e.outh + (size_t)r * e.ldh + e.colh0 + n : nullptr, x0, x1, v1,
+      store2(e.out ? e.out + (size_t)r * e.ldo + e.col0 + n : nullptr,
+             e.outh ? e.outh + (size_t)r * e.ldh + e.colh0 + n : nullptr, x0, x1, v1,
              e.outg ? e.outg + (size_t)r * e.ldh + e.colh0 + n : nullptr,
-             e.outg ? e.outl + (size_t)r * e.ldh + e.colh0 + n : nullptr);
+             (e.outg && e.outl) ? e.outl + (size_t)r * e.ldh + e.colh0 + n : nullptr);
     } else if constexpr (KIND == EPI_RESSKIP) {
       const float x0 = a0 + b0, x1 = a1 + b1;
       if (n < e.split) {
@@ -323,10 +343,13 @@ struct EpiPair {
         e.out2[(size_t)r * e.ldo2 + e.col20 + c] = ph;
         if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = __float2bfloat16_rn(mag);
         if (e.outh2 != nullptr) e.outh2[(size_t)r * e.ldh2 + e.colh20 + c] = __float2bfloat16_rn(ph);
+        __half lo;
         if (e.outg != nullptr)
-          f16_split(mag, e.outg + (size_t)r * e.ldh + e.colh0 + c, e.outl + (size_t)r * e.ldh + e.colh0 + c);
+          f16_split(mag, e.outg + (size_t)r * e.ldh + e.colh0 + c,
+                    e.outl != nullptr ? e.outl + (size_t)r * e.ldh + e.colh0 + c : &lo);
         if (e.outg2 != nullptr)
-          f16_split(ph, e.outg2 + (size_t)r * e.ldh2 + e.colh20 + c, e.outl2 + (size_t)r * e.ldh2 + e.colh20 + c);
+          f16_split(ph, e.outg2 + (size_t)r * e.ldh2 + e.colh20 + c,
+                    e.outl2 != nullptr ? e.outl2 + (size_t)r * e.ldh2 + e.colh20 + c : &lo);
       }
     }
   }
@@ -348,6 +371,7 @@ struct ConvGemm {
   int n_kseg;
   const float* W;                 // [Npad, Ktot] fp32, K-major
   const __nv_bfloat16* Wh;        // bf16 copy
+  const __nv_bfloat16* Wh_seg;    // optional per-utterance bf16 weights [n_seg * Npad, Ktot] (GRN folded into pw2)
   const __half* Wg;               // fp16(W * wscale)                       (f16 / f16x3 modes)
   const __half* Wl;               // fp16(W * wscale - Wg)                  (f16x3 mode)
   float acc_scale;                // accumulators are multiplied by this before the epilogue (1 / wscale / a-scale)

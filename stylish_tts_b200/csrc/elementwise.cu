@@ -479,6 +479,25 @@ cudaError_t dwconv_adaln(const float* x, int ldx, const RowMap& map, int K, cons
 // ============================================================================ AdaLN on rows (two heads)
 // amp/phase_final_layer_norm (generator.py:417-421): one LayerNorm (eps) statistic per row shared
 // by two style-conditioned affine maps.  One warp per row, C = 512.
+// four consecutive values -> fp16 twin g (8-byte store) and, optionally, the residual twin l
+__device__ __forceinline__ void split4(const float* o, __half* g, __half* l) {
+  float c[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) c[j] = fminf(fmaxf(o[j], -65504.f), 65504.f);
+  const __half2 g0 = __floats2half2_rn(c[0], c[1]), g1 = __floats2half2_rn(c[2], c[3]);
+  uint2 pk;
+  pk.x = *reinterpret_cast<const uint32_t*>(&g0);
+  pk.y = *reinterpret_cast<const uint32_t*>(&g1);
+  *reinterpret_cast<uint2*>(g) = pk;
+  if (l != nullptr) {
+    const __half2 l0 = __floats2half2_rn(c[0] - __low2float(g0), c[1] - __high2float(g0));
+    const __half2 l1 = __floats2half2_rn(c[2] - __low2float(g1), c[3] - __high2float(g1));
+    pk.x = *reinterpret_cast<const uint32_t*>(&l0);
+    pk.y = *reinterpret_cast<const uint32_t*>(&l1);
+    *reinterpret_cast<uint2*>(l) = pk;
+  }
+}
+
 __global__ void __launch_bounds__(256) adaln2_kernel(const float* __restrict__ x, int ldx, RowMap map,
                                                      const float* __restrict__ gb1, const float* __restrict__ gb2,
                                                      int ldgb, float eps, float* __restrict__ y1,
@@ -516,21 +535,15 @@ __global__ void __launch_bounds__(256) adaln2_kernel(const float* __restrict__ x
       const float4 b1 = *reinterpret_cast<const float4*>(gb1 + (size_t)seg * ldgb + C + c);
       const float o1[4] = {(1.f + g1.x) * n[0] + b1.x, (1.f + g1.y) * n[1] + b1.y, (1.f + g1.z) * n[2] + b1.z,
                            (1.f + g1.w) * n[3] + b1.w};
-      *reinterpret_cast<float4*>(y1 + r * ldy + c) = make_float4(o1[0], o1[1], o1[2], o1[3]);
-      if (y1g != nullptr) {   // fp16 split twins: the operands of the output-head GEMMs
-#pragma unroll
-        for (int j = 0; j < 4; ++j) f16_split(o1[j], y1g + r * ldyh + c + j, y1l + r * ldyh + c + j);
-      }
-      if (y2 != nullptr) {
+      if (y1 != nullptr) *reinterpret_cast<float4*>(y1 + r * ldy + c) = make_float4(o1[0], o1[1], o1[2], o1[3]);
+      if (y1g != nullptr) split4(o1, y1g + r * ldyh + c, y1l ? y1l + r * ldyh + c : nullptr);
+      if (gb2 != nullptr) {
         const float4 g2 = *reinterpret_cast<const float4*>(gb2 + (size_t)seg * ldgb + c);
         const float4 b2 = *reinterpret_cast<const float4*>(gb2 + (size_t)seg * ldgb + C + c);
         const float o2[4] = {(1.f + g2.x) * n[0] + b2.x, (1.f + g2.y) * n[1] + b2.y, (1.f + g2.z) * n[2] + b2.z,
                              (1.f + g2.w) * n[3] + b2.w};
-        *reinterpret_cast<float4*>(y2 + r * ldy + c) = make_float4(o2[0], o2[1], o2[2], o2[3]);
-        if (y2g != nullptr) {
-#pragma unroll
-          for (int j = 0; j < 4; ++j) f16_split(o2[j], y2g + r * ldyh + c + j, y2l + r * ldyh + c + j);
-        }
+        if (y2 != nullptr) *reinterpret_cast<float4*>(y2 + r * ldy + c) = make_float4(o2[0], o2[1], o2[2], o2[3]);
+        if (y2g != nullptr) split4(o2, y2g + r * ldyh + c, y2l ? y2l + r * ldyh + c : nullptr);
       }
     }
   }
@@ -561,6 +574,53 @@ __global__ void __launch_bounds__(256) grn_scale_kernel(const float* __restrict_
   const float denom = tot / (float)C + 1e-6f;
   for (int c = threadIdx.x; c < C; c += blockDim.x)
     scale[(size_t)seg * C + c] = 1.f + gamma[c] * (gx[(size_t)seg * C + c] / denom);
+}
+
+// GRN statistic from the partials the pw1 epilogue left (Epi::colss): Gx[c] = sqrt(sum over the
+// utterance's (tile, quarter) rows); grn_scale_kernel then forms 1 + gamma * Gx / (mean_c Gx + 1e-6).
+// Deterministic: fixed summation order, fp64 accumulation.  CTA = 64 channels x 4 interleaved row parts.
+__global__ void __launch_bounds__(256) grn_gx_partials_kernel(const float* __restrict__ colss, int ld, int C,
+                                                              RowMap map, float* __restrict__ gx) {
+  __shared__ double part[4][64];
+  const int seg = blockIdx.x;
+  const int cl = threadIdx.x & 63, pt = threadIdx.x >> 6;
+  const int c = blockIdx.y * 64 + cl;
+  const int t0 = 4 * (map.seg_start[seg] / 128), nt = 4 * ((map.seg_len[seg] + 127) / 128);
+  double q = 0.0;
+  if (c < C)
+    for (int t = pt; t < nt; t += 4) q += (double)colss[(size_t)(t0 + t) * ld + c];
+  part[pt][cl] = q;
+  __syncthreads();
+  if (pt == 0 && c < C) gx[(size_t)seg * C + c] = (float)sqrt(part[0][cl] + part[1][cl] + part[2][cl] + part[3][cl]);
+}
+
+cudaError_t grn_scale_partials(const float* colss, int ld, int C, const RowMap& map, const float* gamma, float* gx,
+                               float* scale, cudaStream_t st) {
+  grn_gx_partials_kernel<<<dim3(map.n_seg, (C + 63) / 64), 256, 0, st>>>(colss, ld, C, map, gx);
+  grn_scale_kernel<<<map.n_seg, 256, 0, st>>>(gx, C, gamma, scale);
+  return cudaGetLastError();
+}
+
+// Per-utterance pw2 weights with the GRN scale folded in: Wu[u, n, k] = bf16(W[n, k] * scale[u, k])
+// (pwconv2(x * s + beta) = (W diag(s)) x + W beta: the W beta term is added to the bias at prepack).
+__global__ void __launch_bounds__(256) grn_weights_kernel(const float* __restrict__ W, int N, int K,
+                                                          const float* __restrict__ scale,
+                                                          __nv_bfloat16* __restrict__ Wu) {
+  const int u = blockIdx.y;
+  const size_t total = (size_t)N * K / 2;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const size_t e = 2 * i;
+    const int k = (int)(e % K);
+    const float2 w = *reinterpret_cast<const float2*>(W + e);
+    const float2 sc = *reinterpret_cast<const float2*>(scale + (size_t)u * K + k);
+    *reinterpret_cast<__nv_bfloat162*>(Wu + (size_t)u * N * K + e) = __floats2bfloat162_rn(w.x * sc.x, w.y * sc.y);
+  }
+}
+
+cudaError_t grn_weights(const float* W, int N, int K, const float* scale, int n_seg, __nv_bfloat16* Wu, cudaStream_t st) {
+  if (K % 2 != 0) return cudaErrorInvalidValue;
+  grn_weights_kernel<<<dim3(148, n_seg), 256, 0, st>>>(W, N, K, scale, Wu);
+  return cudaGetLastError();
 }
 
 __global__ void __launch_bounds__(256) seg_affine_kernel(float* __restrict__ x, int ldx, int C, RowMap map,

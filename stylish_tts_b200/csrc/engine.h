@@ -86,6 +86,7 @@ struct Context {
   std::map<std::string, Act> tact;
   std::map<std::string, void*> traw;
   int max_t = 0;
+  std::map<int, float2*> rope_tab;   // rd -> (cos, sin) table [kRopePositions][rd / 2] (token_pipeline.cu)
   std::vector<int> sig;                        // layout signature
   char* arena = nullptr; size_t arena_bytes = 0, arena_used = 0;
   std::map<std::string, Act> act;              // named activation buffers
@@ -110,7 +111,8 @@ void free_pack(PackedGemm& p);
 void build_layout(Layout& L, int n_seg, const int* len);
 int set_layout(Context& c, int n_seg, const int* len_f, const int* len_f4);
 int run_gemm(Context& c, const PackedGemm& pg, int cls, const Act* a0, int a0_col, const Act* a1, int a1_col,
-             const Epi& epi, const RowMap& map, cudaStream_t st, int forced_backend = -1);
+             const Epi& epi, const RowMap& map, cudaStream_t st, int forced_backend = -1,
+             const __nv_bfloat16* seg_weights = nullptr);   // per-utterance bf16 weights [n_seg * Npad, Ktot]
 int run_pe_towers(Context& c, const float* d_x, const float* d_style, float* d_pitch, float* d_energy, cudaStream_t st);
 int run_decoder_core(Context& c, const float* d_style, cudaStream_t st);
 int run_decoder(Context& c, const float* d_asr, const float* d_f0, const float* d_n, const float* d_style, float* d_out,

@@ -147,7 +147,11 @@ __device__ __forceinline__ float rna_tf32(float x) {
 // the three-pass fp16 split (hi*hi + hi*lo + lo*hi, fp32-grade), MODE_TF32X3 the tf32 split on fp32 operands
 enum { MODE_BF16 = 0, MODE_TF32X3 = 1, MODE_F16X3 = 2 };
 
-template <int MODE, int BN>
+// OCC = 2 (bf16 mode, BN = 128 only): half the pipeline depth so that two CTAs share an SM (2 x 97 KB
+// shared memory, 2 x 128 TMEM columns, 2 x 320 threads x <= 96 registers): the epilogue of one CTA
+// overlaps the TMA / MMA main loop of the other -- pays for the short-K GEMMs, whose tiles spend as
+// long in the epilogue as in the main loop.
+template <int MODE, int BN, int OCC = 1>
 struct Cfg {
   static constexpr bool kTF32 = (MODE == MODE_TF32X3);
   static constexpr bool kSplit = (MODE != MODE_BF16);     // hi / lo operand pairs, 3 MMAs per k-step
@@ -157,7 +161,7 @@ struct Cfg {
   static constexpr int kATile = 128 * 128;                // bytes
   static constexpr int kBTile = BN * 128;                 // bytes
   static constexpr int kStageBytes = kSplit ? (2 * kATile + 2 * kBTile) : (kATile + kBTile);
-  static constexpr int kStages = kSplit ? (BN == 128 ? 3 : 2) : (BN == 128 ? 6 : 4);
+  static constexpr int kStages = kSplit ? (BN == 128 ? 3 : 2) : (OCC == 2 ? 3 : (BN == 128 ? 6 : 4));
   // tf32x3: the A residual is computed in shared memory by the converter warps; f16x3: it is loaded
   static constexpr int kTxBytes = kTF32 ? (kATile + 2 * kBTile) : (kSplit ? 2 * kATile + 2 * kBTile : kATile + kBTile);
   static constexpr int kEpiWarps = BN / 16;                // one 64-column slab x 32-row quarter per warp
@@ -171,17 +175,18 @@ struct TcParams {
   int n_kseg;
   int taps[2], pad[2], cin_chunks[2], col0[2];   // col0 in elements of the operand dtype
   int n_chunks;
+  int w_seg_rows;       // > 0: the weights are per utterance, utterance u at rows [u * w_seg_rows, ...)
   uint32_t ab_fmt;      // operand format of the MMAs: 0 = f16, 1 = bf16, 2 = tf32
   float acc_scale;      // accumulators * acc_scale before the epilogue (power-of-two operand scaling undone)
 };
 
-template <int MODE, int BN, int KIND>
-__global__ void __launch_bounds__(64 + 2 * BN, 1)
+template <int MODE, int BN, int KIND, int OCC = 1>
+__global__ void __launch_bounds__(64 + 2 * BN, OCC)
 conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant__ CUtensorMap mapA1,
                     const __grid_constant__ CUtensorMap mapA0lo, const __grid_constant__ CUtensorMap mapA1lo,
                     const __grid_constant__ CUtensorMap mapW, const __grid_constant__ CUtensorMap mapWlo,
                     const TcParams p, const Epi epi, const RowMap map) {
-  using C = Cfg<MODE, BN>;
+  using C = Cfg<MODE, BN, OCC>;
   const int tile = blockIdx.y;
   const int seg = map.tile_seg[tile];
   if (seg < 0) return;
@@ -230,6 +235,7 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
       uint32_t phase = 0;
       int ks = 0, tap = 0, cc = 0;
       int kcol = 0;
+      const int wrow = n0 + seg * p.w_seg_rows;
       for (int ch = 0; ch < p.n_chunks; ++ch) {
         mbar_wait(&empty[stage], phase ^ 1, 1);
         uint8_t* sp = stage_ptr(stage);
@@ -241,10 +247,10 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
             const CUtensorMap* ml = (ks == 0) ? &mapA0lo : &mapA1lo;
             tma_load_2d(sp + C::kATile, ml, &full[stage], p.col0[ks] + cc * C::kBK, m0 + tap - p.pad[ks]);
           }
-          tma_load_2d(sp + 2 * C::kATile, &mapW, &full[stage], kcol, n0);
-          tma_load_2d(sp + 2 * C::kATile + C::kBTile, &mapWlo, &full[stage], kcol, n0);
+          tma_load_2d(sp + 2 * C::kATile, &mapW, &full[stage], kcol, wrow);
+          tma_load_2d(sp + 2 * C::kATile + C::kBTile, &mapWlo, &full[stage], kcol, wrow);
         } else {
-          tma_load_2d(sp + C::kATile, &mapW, &full[stage], kcol, n0);
+          tma_load_2d(sp + C::kATile, &mapW, &full[stage], kcol, wrow);
         }
         kcol += C::kBK;
         if (++cc == p.cin_chunks[ks]) { cc = 0; if (++tap == p.taps[ks]) { tap = 0; ++ks; } }
@@ -357,6 +363,7 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
           ep.apply(epi, row0 + rr, seg, seg_first, a.x, a.y, make_float2(0.f, 0.f));
         }
       }
+      ep.finish(epi, tile, q);
     }
     tc_fence_before();
   }
@@ -417,9 +424,9 @@ bool get_map(const void* base, int rows, int ld, int elem, int box_rows, CUtenso
   return true;
 }
 
-template <int MODE, int BN, int KIND>
+template <int MODE, int BN, int KIND, int OCC = 1>
 cudaError_t launch_one(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
-  using C = Cfg<MODE, BN>;
+  using C = Cfg<MODE, BN, OCC>;
   constexpr int elem = C::kElem;
   CUtensorMap mA[2], mAlo[2], mW, mWlo;
   TcParams p{};
@@ -447,9 +454,11 @@ cudaError_t launch_one(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
   }
   p.acc_scale = 1.f;
   if (MODE == MODE_BF16) {
-    const void* w = g.f16 ? (const void*)g.Wg : (const void*)g.Wh;
+    const bool per_seg = !g.f16 && g.Wh_seg != nullptr;
+    const void* w = g.f16 ? (const void*)g.Wg : (per_seg ? (const void*)g.Wh_seg : (const void*)g.Wh);
     if (w == nullptr) return cudaErrorInvalidValue;
-    if (!get_map(w, g.Npad, g.Ktot, 2, BN, &mW)) return cudaErrorNotSupported;
+    if (!get_map(w, per_seg ? g.Npad * map.n_seg : g.Npad, g.Ktot, 2, BN, &mW)) return cudaErrorNotSupported;
+    p.w_seg_rows = per_seg ? g.Npad : 0;
     mWlo = mW;
     p.ab_fmt = g.f16 ? 0u : 1u;
     if (g.f16) p.acc_scale = g.acc_scale;
@@ -465,7 +474,7 @@ cudaError_t launch_one(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
     if (!get_map(g.W, g.Npad, g.Ktot, 4, BN, &mW)) return cudaErrorNotSupported;
     if (!get_map(g.W + (size_t)g.Npad * g.Ktot, g.Npad, g.Ktot, 4, BN, &mWlo)) return cudaErrorNotSupported;
   }
-  auto kern = conv_gemm_tc_kernel<MODE, BN, KIND>;
+  auto kern = conv_gemm_tc_kernel<MODE, BN, KIND, OCC>;
   static bool attr_done = false;
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmem);
@@ -477,8 +486,23 @@ cudaError_t launch_one(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
   return cudaGetLastError();
 }
 
+// STTS_OCC2=<n>: bf16-mode GEMMs with at most n K chunks (64 columns each) run as BN = 128, two CTAs
+// per SM (-1 = never).
+int occ2_max_chunks() {
+  static const int v = [] {
+    const char* e = std::getenv("STTS_OCC2");
+    return e != nullptr ? std::atoi(e) : -1;
+  }();
+  return v;
+}
+
 template <int MODE, int KIND>
 cudaError_t launch_bn(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
+  if constexpr (MODE == MODE_BF16) {
+    int chunks = 0;
+    for (int s = 0; s < g.n_kseg; ++s) chunks += g.seg[s].taps * (g.seg[s].cin_pad / 64);
+    if (chunks <= occ2_max_chunks()) return launch_one<MODE, 128, KIND, 2>(g, map, st);
+  }
   // BN = 256 only pays when there are at least two full 128-column tiles to merge.
   if (MODE == MODE_BF16 && g.epi.N > 128 && g.Npad % 256 == 0) return launch_one<MODE, 256, KIND>(g, map, st);
   return launch_one<MODE, 128, KIND>(g, map, st);

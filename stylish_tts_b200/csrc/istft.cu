@@ -9,7 +9,9 @@
 
 namespace stts {
 
-// spec[r, 2k] = e^la cos(ph), spec[r, 2k+1] = e^la sin(ph).  Row seg_end (one past the last
+// spec[r, 2k] = e^la cos(ph), spec[r, 2k+1] = e^la sin(ph); any of the fp32 master `spec`, the fp16
+// twin `specg` and its residual `specl` may be null (only what the inverse-DFT GEMM of the current
+// precision mode reads is written).  Row seg_end (one past the last
 // frame, a guard row of the layout) receives the replicate-padded frame.
 __global__ void __launch_bounds__(256) polar_kernel(const float* __restrict__ la, const float* __restrict__ ph, int ld,
                                                     int n_bins, RowMap map, float* __restrict__ spec, int lds,
@@ -32,11 +34,14 @@ __global__ void __launch_bounds__(256) polar_kernel(const float* __restrict__ la
     sincosf(p, &sn, &cs);
     const float re = a * cs, im = a * sn;
     const size_t o = (size_t)(m0 + lr) * lds + 2 * k;
-    *reinterpret_cast<float2*>(spec + o) = make_float2(re, im);
-    if (specg != nullptr) {   // fp16 split twins (pre-scaled by gscale: e^logamp may exceed the fp16 range)
+    if (spec != nullptr) *reinterpret_cast<float2*>(spec + o) = make_float2(re, im);
+    if (specg != nullptr) {   // fp16 twins (pre-scaled by gscale: e^logamp may exceed the fp16 range)
       const size_t og = (size_t)(m0 + lr) * ldsh + 2 * k;
-      f16_split(re * gscale, specg + og, specl + og);
-      f16_split(im * gscale, specg + og + 1, specl + og + 1);
+      const float sr = fminf(fmaxf(re * gscale, -65504.f), 65504.f), si = fminf(fmaxf(im * gscale, -65504.f), 65504.f);
+      const __half2 g = __floats2half2_rn(sr, si);
+      *reinterpret_cast<__half2*>(specg + og) = g;
+      if (specl != nullptr)
+        *reinterpret_cast<__half2*>(specl + og) = __floats2half2_rn(sr - __low2float(g), si - __high2float(g));
     }
   }
 }

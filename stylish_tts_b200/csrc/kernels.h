@@ -44,6 +44,9 @@ cudaError_t adaln2(const float* x, int ldx, const RowMap& map, const float* gb1,
                    cudaStream_t st);
 cudaError_t grn_apply(float* x, int ldx, int C, const RowMap& map, const float* gx, const float* gamma,
                       const float* beta, float* scale_scratch, __nv_bfloat16* xh, int ldxh, cudaStream_t st);
+cudaError_t grn_scale_partials(const float* colss, int ld, int C, const RowMap& map, const float* gamma, float* gx,
+                               float* scale, cudaStream_t st);
+cudaError_t grn_weights(const float* W, int N, int K, const float* scale, int n_seg, __nv_bfloat16* Wu, cudaStream_t st);
 cudaError_t rowdot(const float* x, int ldx, int C, const RowMap& map, const float* w, const float* bias, const int* cu,
                    float* dense, cudaStream_t st);
 cudaError_t fill(float* p, size_t n, float v, cudaStream_t st);
@@ -57,8 +60,10 @@ cudaError_t row_ln(const float* x, int ldx, int C, const RowMap& map, const floa
 cudaError_t rope_inplace(float* x, int ldx, int col0, int blk, int n_blocks, int H, int D, int rd, const RowMap& map,
                          cudaStream_t st);
 cudaError_t attention(const float* Q, int ldq, int qcol, const float* K, int ldk, int kcol, const float* V, int ldv,
-                      int vcol, int H, int D, float scale, const RowMap& qmap, const RowMap& kmap, int max_tq,
-                      int max_tk, const int* q_tok, const int* q_cu, int band, float* out, int ldo, cudaStream_t st);
+                      int vcol, int H, int D, float scale, int rd, const float2* rope_tab, const RowMap& qmap,
+                      const RowMap& kmap, int max_tq, int max_tk, const int* q_tok, const int* q_cu, int band, float* out,
+                      int ldo, cudaStream_t st);
+cudaError_t rope_table(float2* tab, int n_pos, int rd, cudaStream_t st);
 cudaError_t dense_to_rows(const float* src, int C, const RowMap& map, const int* cu, float* dst, int ld, int col0,
                           cudaStream_t st);
 cudaError_t seg_broadcast(const float* vec, int C, const RowMap& map, float* dst, int ld, int col0, cudaStream_t st);

@@ -144,6 +144,10 @@ int set_layout(Context& c, int n_seg, const int* len_f, const int* len_f4) {
       {"GB_GEN", (size_t)B * std::max(c.J_gen, 1) * 4},                  {"GB_FLOW", (size_t)B * std::max(c.J_flow, 1) * 4},
       {"GB_PE", (size_t)B * std::max(c.J_pe, 1) * 4},                    {"STATUS", 256},
   };
+  if (use4) {   // GRN folded into pw2: sum-of-squares partials of the pw1 epilogue, per-utterance bf16 weights
+    raws.push_back({"COLSS", (size_t)(R4 / 128) * 4 * 1536 * 4});
+    raws.push_back({"WGRN", (size_t)B * 512 * 1536 * 2});
+  }
   // layout descriptor arrays (ints / long longs)
   const char* rates[2] = {"4", "F"};
   for (int k = 0; k < 2; ++k) {
@@ -263,7 +267,8 @@ bool one_pass_island(const std::string& name) {
 }  // namespace
 
 int run_gemm(Context& c, const PackedGemm& pg, int cls, const Act* a0, int a0_col, const Act* a1, int a1_col,
-             const Epi& epi_in, const RowMap& map, cudaStream_t st, int forced_backend) {
+             const Epi& epi_in, const RowMap& map, cudaStream_t st, int forced_backend,
+             const __nv_bfloat16* seg_weights) {
   int backend = forced_backend;
   // STTS_FORCE_ISLAND=tok1,tok2: layers whose name contains a token run fp32-grade in bf16 mode too
   // (precision experiments; the shipped classification is the `cls` argument)
@@ -317,6 +322,8 @@ int run_gemm(Context& c, const PackedGemm& pg, int cls, const Act* a0, int a0_co
   }
   g.W = (backend == 2) ? pg.Whl : pg.Wf;
   g.Wh = pg.Wh;
+  g.Wh_seg = (backend == 1) ? seg_weights : nullptr;
+  if (seg_weights != nullptr && backend != 1) return fail(c, -1, "run_gemm: per-utterance weights need the bf16 backend");
   g.Wg = pg.Wg;
   g.Wl = pg.Wl;
   g.f16 = backend == 4;
@@ -604,6 +611,8 @@ int run_generator_core(Context& c, const float* d_style, const float* d_noise, c
     e.outh2 = S.tw(hp); e.ldh2 = hp.ld; e.colh20 = 0;
     e.outg2 = S.twins ? hp.g : nullptr;
     e.outl2 = S.twins ? hp.l : nullptr;
+    if (one_pass_island("gen.amp_prior")) e.outl = nullptr;      // residual twins only for three-pass consumers
+    if (one_pass_island("gen.phase_prior")) e.outl2 = nullptr;
     e.seg_start = c.L4.d_seg_start;
     // bf16 mode: fp16 split operand (75 samples per row padded to 128 columns) -> the "stft16" pack
     STTS_RET(run_gemm(c, c.gemm[S.twins ? "stft16" : "stft"], GC_ISLAND, &src, 0, nullptr, 0, e, map, st));
@@ -628,8 +637,10 @@ int run_generator_tail(Context& c, const float* d_style, float* d_audio, float* 
     // rounding (step 1.6e-2 rad near +-pi) is the largest single contributor to the bf16-mode
     // waveform error (measured: max over the golden cases 2.46e-3 -> 1.64e-3)
     Epi e = S.epi(EPI_BIAS, catp, 512);
+    if (one_pass_island("gen.amp_head")) e.outl = nullptr;
     STTS_RET(run_gemm(c, c.gemm["gen.amp_prior"], GC_ISLAND, &hs, 0, nullptr, 0, e, map, st));
     Epi e2 = S.epi(EPI_BIAS, catp, 768);
+    if (one_pass_island("gen.phase_head")) e2.outl = nullptr;
     STTS_RET(run_gemm(c, c.gemm["gen.phase_prior"], GC_ISLAND, &hp, 0, nullptr, 0, e2, map, st));
   }
   {  // projector 1x1 on cat[mel, logamp_prior, phase_prior]   (generator.py:414)
@@ -641,6 +652,27 @@ int run_generator_tail(Context& c, const float* d_style, float* d_audio, float* 
     const std::string nm = "gen.cnx" + std::to_string(i);
     STTS_CK(dwconv_adaln(xg.f, xg.ld, map, c.vec_len[nm + ".dw_k"], c.vec[nm + ".dw_w"], c.vec[nm + ".dw_b"],
                          gb + c.fc_off[nm + ".norm"], c.J_gen, 1e-6f, xgn.f, xgn.ld, S.tw(xgn), xgn.ld, st));
+    if (S.twins) {
+      // bf16 mode: GRN without touching H again.  The pw1 epilogue keeps only the bf16 twin of H and
+      // leaves per-(tile, quarter) column sums of squares; GRN's per-utterance channel scale is folded
+      // into a per-utterance copy of the pw2 weights, its beta into the pw2 bias (prepack).
+      float* colss = S.R<float>("COLSS");
+      __nv_bfloat16* wu = S.R<__nv_bfloat16>("WGRN");
+      Epi e = S.epi(EPI_SILU, h, 0);
+      e.out = nullptr;
+      e.colss = colss; e.colss_ld = 1536;
+      STTS_RET(run_gemm(c, c.gemm[nm + ".pw1"], GC_BODY, &xgn, 0, nullptr, 0, e, map, st));
+      STTS_CK(grn_scale_partials(colss, 1536, 1536, map, c.vec[nm + ".grn_gamma"], S.R<float>("GX"),
+                                 S.R<float>("GSCALE"), st));
+      STTS_CK(grn_weights(c.gemm[nm + ".pw2"].Wf, 512, 1536, S.R<float>("GSCALE"), c.L4.n_seg, wu, st));
+      c.launches += 3;
+      Epi e2 = S.epi(EPI_ADD, xg, 0);
+      e2.outh = nullptr;
+      e2.res = xg.f; e2.ldr = xg.ld; e2.rcol0 = 0;
+      e2.bias = c.vec[nm + ".pw2_bias_grn"];
+      STTS_RET(run_gemm(c, c.gemm[nm + ".pw2"], GC_BODY, &h, 0, nullptr, 0, e2, map, st, -1, wu));
+      continue;
+    }
     {
       Epi e = S.epi(EPI_SILU, h, 0);
       e.outh = nullptr;
@@ -660,8 +692,9 @@ int run_generator_tail(Context& c, const float* d_style, float* d_audio, float* 
   }
   // two AdaLN heads + output convs k7 over cat[AdaLN(x), prior]   (generator.py:417-423)
   STTS_CK(adaln2(xg.f, xg.ld, map, gb + c.fc_off["gen.amp_norm"], gb + c.fc_off["gen.phase_norm"], c.J_gen, 1e-5f,
-                 ampn.f, phn.f, ampn.ld, S.twins ? ampn.g : nullptr, S.twins ? phn.g : nullptr, ampn.ld, ampn.l, phn.l,
-                 st));
+                 S.twins ? nullptr : ampn.f, S.twins ? nullptr : phn.f, ampn.ld, S.twins ? ampn.g : nullptr,
+                 S.twins ? phn.g : nullptr, ampn.ld, one_pass_island("gen.amp_head") ? nullptr : ampn.l,
+                 one_pass_island("gen.phase_head") ? nullptr : phn.l, st));   // bf16 mode: only what the heads read
   {
     Epi e = S.epi(EPI_BIAS, la, 0);
     STTS_RET(run_gemm(c, c.gemm["gen.amp_head"], GC_ISLAND, &ampn, 0, &catp, 512, e, map, st));
@@ -669,8 +702,8 @@ int run_generator_tail(Context& c, const float* d_style, float* d_audio, float* 
     STTS_RET(run_gemm(c, c.gemm["gen.phase_head"], GC_ISLAND, &phn, 0, &catp, 768, e2, map, st));
   }
   // replicate pad + exp / cos / sin -> inverse DFT x window -> overlap-add, envelope, tanh
-  STTS_CK(polar_spec(la.f, ph.f, la.ld, 1025, map, spec.f, spec.ld, S.twins ? spec.g : nullptr, spec.ld, spec.l,
-                     spec.gscale, st));
+  STTS_CK(polar_spec(la.f, ph.f, la.ld, 1025, map, S.twins ? nullptr : spec.f, spec.ld, S.twins ? spec.g : nullptr,
+                     spec.ld, one_pass_island("istft") ? nullptr : spec.l, spec.gscale, st));
   {
     Epi e = S.epi(EPI_BIAS, yf, 0);
     STTS_RET(run_gemm(c, c.gemm["istft"], GC_ISLAND, &spec, 0, nullptr, 0, e, map_p1, st));

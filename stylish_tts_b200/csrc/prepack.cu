@@ -589,6 +589,14 @@ int finalize_weights(Context& c) {
           b.rows(0, *w2, 0, 512, 0, 1536, 0, 1);
           b.set_bias(*b2, 0, 512, 0, 1);
           c.gemm[nm + ".pw2"] = b.upload(c);
+          // GRN folded into pw2 (bf16 mode): pw2(x * s + beta) = (W diag(s)) x + (W beta + bias)
+          std::vector<float> bg(512);
+          for (int n = 0; n < 512; ++n) {
+            double acc = b2->data[n];
+            for (int kk = 0; kk < 1536; ++kk) acc += (double)w2->data[(size_t)n * 1536 + kk] * (double)gb->data[kk];
+            bg[n] = (float)acc;
+          }
+          put_vec(c, nm + ".pw2_bias_grn", bg);
         }
       }
       const char* heads[2] = {"amp", "phase"};

@@ -23,6 +23,7 @@ int set_token_layout(Context& c, int n_seg, const int* len_t) {
     if (len_t[b] <= 0) return fail(c, -2, "utterance token count must be > 0");
     max_t = std::max(max_t, len_t[b]);
   }
+  if (max_t > 2048) return fail(c, -6, "utterance longer than 2048 tokens (attention score rows live in shared memory)");
   if (sig == c.tsig && c.tarena != nullptr) return 0;
   cudaError_t e = cudaDeviceSynchronize();
   if (e != cudaSuccess) return cuda_fail(c, e, "set_token_layout sync");
@@ -96,6 +97,19 @@ int set_token_layout(Context& c, int n_seg, const int* len_t) {
 }
 
 namespace {
+constexpr int kRopePositions = 16384;   // longest utterance in tokens or hop-300 frames (54 s of audio per 4800 frames)
+// (cos, sin) table of the partial RoPE for `rd` rotated features, built on first use (the warm-up
+// passes of a CUDA-graph capture run eagerly, so no allocation happens while capturing)
+const float2* rope_tab(Context& c, int rd, cudaStream_t st) {
+  auto it = c.rope_tab.find(rd);
+  if (it != c.rope_tab.end()) return it->second;
+  float2* tab = nullptr;
+  if (cudaMalloc(&tab, (size_t)kRopePositions * (rd / 2) * sizeof(float2)) != cudaSuccess) return nullptr;
+  if (rope_table(tab, kRopePositions, rd, st) != cudaSuccess) { cudaFree(tab); return nullptr; }
+  c.rope_tab[rd] = tab;
+  return tab;
+}
+
 Epi mk_epi(int kind, const Act& dst, int col0) {
   Epi e;
   std::memset(&e, 0, sizeof(e));
@@ -137,8 +151,8 @@ int run_text_encoder(Context& c, const std::string& nm, const int* d_tokens, flo
   for (int l = 0; l < n_layers; ++l) {
     const std::string n = nm + ".l" + std::to_string(l);
     STTS_RET(run_gemm(c, c.gemm[n + ".qkv"], GC_ISLAND, &tx, 0, nullptr, 0, mk_epi(EPI_BIAS, tqkv, 0), map, st));
-    STTS_CK(rope_inplace(tqkv.f, tqkv.ld, 0, C, 2, H, D, rd, map, st));
-    STTS_CK(attention(tqkv.f, tqkv.ld, 0, tqkv.f, tqkv.ld, C, tqkv.f, tqkv.ld, 2 * C, H, D, scale, map, map, c.max_t,
+    // partial RoPE of q / k is applied inside the attention kernel while it stages the rows
+    STTS_CK(attention(tqkv.f, tqkv.ld, 0, tqkv.f, tqkv.ld, C, tqkv.f, tqkv.ld, 2 * C, H, D, scale, rd, rope_tab(c, rd, st), map, map, c.max_t,
                       c.max_t, nullptr, nullptr, 0, to.f, to.ld, st));
     {
       Epi e = mk_epi(EPI_ADD, tb, 0);
@@ -183,8 +197,7 @@ int run_prosody_encoder(Context& c, const std::string& nm, const float* d_enc_to
   for (int l = 0; l < n_layers; ++l) {
     const std::string n = nm + ".l" + std::to_string(l);
     STTS_RET(run_gemm(c, c.gemm[n + ".qkv"], GC_ISLAND, &px, 0, nullptr, 0, mk_epi(EPI_BIAS, pqkv, 0), map, st));
-    STTS_CK(rope_inplace(pqkv.f, pqkv.ld, 0, hid, 2, H, D, rd, map, st));
-    STTS_CK(attention(pqkv.f, pqkv.ld, 0, pqkv.f, pqkv.ld, hid, pqkv.f, pqkv.ld, 2 * hid, H, D, scale, map, map,
+    STTS_CK(attention(pqkv.f, pqkv.ld, 0, pqkv.f, pqkv.ld, hid, pqkv.f, pqkv.ld, 2 * hid, H, D, scale, rd, rope_tab(c, rd, st), map, map,
                       c.max_t, c.max_t, nullptr, nullptr, 0, po.f, po.ld, st));
     {
       Epi e = mk_epi(EPI_ADD, pb, 0);
@@ -281,11 +294,10 @@ int run_pe_cross(Context& c, const float* d_prosody_tok, const float* d_style, c
   Epi eq = mk_epi(EPI_BIAS, pact, 0);
   STTS_RET(run_gemm(c, c.gemm[nm + ".q"], GC_ISLAND, &pb, 0, nullptr, 0, eq, fmap, st));
   STTS_RET(run_gemm(c, c.gemm[nm + ".kv"], GC_ISLAND, &tpy, 0, nullptr, 0, mk_epi(EPI_BIAS, tkv, 0), tmap, st));
-  STTS_CK(rope_inplace(pact.f, pact.ld, 0, C, 1, H, D, rd, fmap, st));
-  STTS_CK(rope_inplace(tkv.f, tkv.ld, 0, C, 1, H, D, rd, tmap, st));
   int max_f = 0;
   for (int v : c.LF.seg_len) max_f = std::max(max_f, v);
-  STTS_CK(attention(pact.f, pact.ld, 0, tkv.f, tkv.ld, 0, tkv.f, tkv.ld, C, H, D, 1.0f / std::sqrt((float)D), fmap, tmap,
+  if (max_f > kRopePositions || c.max_t > kRopePositions) return fail(c, -6, "utterance longer than the RoPE table");
+  STTS_CK(attention(pact.f, pact.ld, 0, tkv.f, tkv.ld, 0, tkv.f, tkv.ld, C, H, D, 1.0f / std::sqrt((float)D), rd, rope_tab(c, rd, st), fmap, tmap,
                     max_f, c.max_t, d_idx, d_cu_frames, 5, py1.f, py1.ld, st));
   STTS_RET(run_gemm(c, c.gemm[nm + ".o"], GC_ISLAND, &py1, 0, nullptr, 0, mk_epi(EPI_BIAS, pb, 0), fmap, st));
   STTS_CK(dwconv_rows(pb.f, pb.ld, C, c.vec_len[nm + ".dw_k"], c.vec[nm + ".dw_w"], c.vec[nm + ".dw_b"], fmap, 1, pact.f,

@@ -216,10 +216,259 @@ __global__ void __launch_bounds__(128) attention_kernel(const float* __restrict_
   }
 }
 
+// Tiled variant for the head sizes of the model (D = 16 text encoders, 40 cross attention, 160 prosody
+// encoders).  One CTA = (16 queries, head, utterance); keys / values are staged through shared memory
+// in chunks of 64 rows (coalesced), partial RoPE is applied while staging (rd > 0: the first rd
+// features of the head, half-split form, position = row index inside the utterance; text_encoder.py:
+// 89-168) so Q / K stay un-rotated in memory and the separate rotation pass disappears.
+constexpr int kAttChunk = 64;
+// rope table: tab[pos * (rd / 2) + j] = (cos, sin)(pos * 10000^(-2 j / rd)), same fp32 formula as rope_kernel
+// Stage ROWS rows x D features of a head into shared memory: dst[r][f] (or dst[f][r] when TRANSPOSE),
+// zero beyond nrows.  float4 global loads, issued in independent batches (the kernel is latency-bound:
+// few resident warps, so the loads of a batch must be in flight together).  128 threads.
+template <int D, int ROWS, bool TRANSPOSE>
+__device__ __forceinline__ void stage_rows(const float* __restrict__ src, int ld, int row0, int nrows,
+                                           float* __restrict__ dst, int dst_ld) {
+  constexpr int D4 = D / 4;
+  constexpr int V4 = (ROWS * D4 + 127) / 128;                        // float4 per thread (guarded tail)
+  constexpr int B = (V4 % 5 == 0) ? 5 : ((V4 % 4 == 0) ? 4 : ((V4 % 3 == 0) ? 3 : ((V4 % 2 == 0) ? 2 : 1)));
+#pragma unroll
+  for (int b0 = 0; b0 < V4; b0 += B) {
+    float4 v[B];
+#pragma unroll
+    for (int u = 0; u < B; ++u) {
+      const int i = threadIdx.x + (b0 + u) * 128;
+      const int r = i / D4, f4 = i - r * D4;
+      v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (i < ROWS * D4 && r < nrows) v[u] = *reinterpret_cast<const float4*>(src + (size_t)(row0 + r) * ld + 4 * f4);
+    }
+#pragma unroll
+    for (int u = 0; u < B; ++u) {
+      const int i = threadIdx.x + (b0 + u) * 128;
+      const int r = i / D4, f = 4 * (i - r * D4);
+      if (i < ROWS * D4) {
+        if (TRANSPOSE) {
+          dst[(f + 0) * dst_ld + r] = v[u].x; dst[(f + 1) * dst_ld + r] = v[u].y;
+          dst[(f + 2) * dst_ld + r] = v[u].z; dst[(f + 3) * dst_ld + r] = v[u].w;
+        } else {
+          dst[r * dst_ld + f + 0] = v[u].x; dst[r * dst_ld + f + 1] = v[u].y;
+          dst[r * dst_ld + f + 2] = v[u].z; dst[r * dst_ld + f + 3] = v[u].w;
+        }
+      }
+    }
+  }
+}
+
+// partial RoPE in place on staged rows x[r][f] (row pitch ldx): the first rd features, half-split
+// pairs (j, j + rd/2), position pos0 + r; then an optional scale of the whole row block
+__device__ __forceinline__ void rope_staged(float* x, int ldx, int nrows, int rd, int pos0,
+                                            const float2* __restrict__ tab) {
+  const int h = rd >> 1;
+  for (int i = threadIdx.x; i < nrows * h; i += 128) {
+    const int r = i / h, j = i - r * h;
+    const float2 cs = tab[(size_t)(pos0 + r) * h + j];
+    const float a = x[r * ldx + j], b = x[r * ldx + j + h];
+    x[r * ldx + j] = a * cs.x - b * cs.y;
+    x[r * ldx + j + h] = b * cs.x + a * cs.y;
+  }
+}
+
+__global__ void rope_table_kernel(float2* tab, int n_pos, int rd) {
+  const int h = rd >> 1;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_pos * h; i += gridDim.x * blockDim.x) {
+    const int pos = i / h, j = i - pos * h;
+    const float inv = 1.0f / powf(10000.f, (float)(2 * j) / (float)rd);
+    float sn, cs;
+    sincosf((float)pos * inv, &sn, &cs);
+    tab[i] = make_float2(cs, sn);
+  }
+}
+
+cudaError_t rope_table(float2* tab, int n_pos, int rd, cudaStream_t st) {
+  rope_table_kernel<<<64, 256, 0, st>>>(tab, n_pos, rd);
+  return cudaGetLastError();
+}
+
+template <int D, int QB>
+__global__ void __launch_bounds__(128) attention_tiled_kernel(const float* __restrict__ Q, int ldq, int qcol,
+                                                              const float* __restrict__ K, int ldk, int kcol,
+                                                              const float* __restrict__ V, int ldv, int vcol,
+                                                              float scale, int rd, const float2* __restrict__ tab,
+                                                              RowMap qmap, RowMap kmap,
+                                                              const int* __restrict__ q_tok,
+                                                              const int* __restrict__ q_cu, int band,
+                                                              float* __restrict__ out, int ldo) {
+  extern __shared__ float sh[];
+  constexpr int KLD = D + 1;                  // padded: a column of kv[][] is read by consecutive threads
+  constexpr int VLD = kAttChunk + 4;          // transposed V chunk vt[d][j]: float4 reads along j, conflict-free
+  constexpr int NOUT = QB * D / 128;          // outputs per thread in the P V phase
+  static_assert(QB % 16 == 0 && (QB * D) % 128 == 0 && NOUT <= 20, "attention tile shape");
+  const int seg = blockIdx.z, hd = blockIdx.y;
+  const int Tq = qmap.seg_len[seg], Tk = kmap.seg_len[seg];
+  const int q0 = blockIdx.x * QB;
+  if (q0 >= Tq) return;
+  const int nq = (Tq - q0 < QB) ? (Tq - q0) : QB;
+  const int qrow0 = qmap.seg_start[seg] + q0, krow0 = kmap.seg_start[seg];
+  const int Tkp = (Tk + 3) & ~3;
+  float* sq = sh;                              // [QB][D]  (rows >= nq zero)
+  float* kv = sq + QB * D;                     // K chunk [kAttChunk][KLD] / V chunk transposed [D][VLD]
+  float* sc = kv + (kAttChunk * KLD > D * VLD ? kAttChunk * KLD : D * VLD);   // [QB][Tkp]
+  // ---- queries (rotated, then scaled)
+  stage_rows<D, QB, false>(Q + qcol + hd * D, ldq, qrow0, nq, sq, D);
+  __syncthreads();
+  if (rd > 0) {
+    rope_staged(sq, D, nq, rd, q0, tab);
+    __syncthreads();
+  }
+  for (int i = threadIdx.x; i < QB * D; i += 128) sq[i] *= scale;
+  const int jl = threadIdx.x & 63, ig = threadIdx.x >> 6;     // key inside the chunk, half of the query groups
+  // ---- scores, chunk by chunk
+  for (int c0 = 0; c0 < Tk; c0 += kAttChunk) {
+    const int nk = (Tk - c0 < kAttChunk) ? (Tk - c0) : kAttChunk;
+    __syncthreads();                           // previous chunk consumed (and sq visible)
+    stage_rows<D, kAttChunk, false>(K + kcol + hd * D, ldk, krow0 + c0, nk, kv, KLD);
+    __syncthreads();
+    if (rd > 0) {
+      rope_staged(kv, KLD, nk, rd, c0, tab);
+      __syncthreads();
+    }
+    if (jl < nk) {
+      const float* kr = kv + jl * KLD;
+      const int j = c0 + jl;
+#pragma unroll 1
+      for (int g = ig; g < QB / 8; g += 2) {   // groups of 8 queries
+        if (g * 8 >= nq) break;
+        float acc[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+        const float* qr = sq + g * 8 * D;
+#pragma unroll 2
+        for (int d = 0; d < D; d += 4) {
+          const float k0 = kr[d], k1 = kr[d + 1], k2 = kr[d + 2], k3 = kr[d + 3];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float4 qv = *reinterpret_cast<const float4*>(qr + i * D + d);     // warp-wide broadcast
+            acc[i] = fmaf(qv.x, k0, acc[i]);
+            acc[i] = fmaf(qv.y, k1, acc[i]);
+            acc[i] = fmaf(qv.z, k2, acc[i]);
+            acc[i] = fmaf(qv.w, k3, acc[i]);
+          }
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int qi = g * 8 + i;
+          float b = 0.f;
+          if (band > 0 && qi < nq) {
+            const int tau = q_tok[q_cu[seg] + q0 + qi];
+            if (j >= tau - band && j <= tau + band) b = -1e4f;
+          }
+          sc[qi * Tkp + j] = acc[i] + b;
+        }
+      }
+    }
+  }
+  __syncthreads();
+  // ---- softmax (one warp per query, round robin)
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int i = warp; i < nq; i += 4) {
+    float* row = sc + i * Tkp;
+    float m = -3.0e38f;
+    for (int j = lane; j < Tk; j += 32) m = fmaxf(m, row[j]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    float s = 0.f;
+    for (int j = lane; j < Tk; j += 32) {
+      const float e = expf(row[j] - m);
+      row[j] = e;
+      s += e;
+    }
+    s = warp_sum(s);
+    const float inv = 1.f / s;
+    for (int j = lane; j < Tk; j += 32) row[j] *= inv;
+    for (int j = Tk + lane; j < Tkp; j += 32) row[j] = 0.f;    // pad read by the float4 P V loop
+  }
+  // rows of P that were never written (queries >= nq) must still be finite for the P V loop
+  for (int i = nq * Tkp + threadIdx.x; i < QB * Tkp; i += 128) sc[i] = 0.f;
+  // ---- P V, chunk by chunk; output element idx = threadIdx.x + 128 * o -> (query idx / D, feature idx % D)
+  float acc[NOUT];
+  int poff[NOUT], doff[NOUT];                  // row of P (query) and feature of every output of this thread
+#pragma unroll
+  for (int o = 0; o < NOUT; ++o) {
+    const int idx = threadIdx.x + 128 * o;
+    acc[o] = 0.f;
+    poff[o] = (idx / D) * Tkp;
+    doff[o] = idx % D;
+  }
+  for (int c0 = 0; c0 < Tk; c0 += kAttChunk) {
+    const int nk = (Tk - c0 < kAttChunk) ? (Tk - c0) : kAttChunk;
+    __syncthreads();                           // softmax done / previous chunk consumed
+    stage_rows<D, kAttChunk, true>(V + vcol + hd * D, ldv, krow0 + c0, nk, kv, VLD);   // rows >= nk are zero
+    __syncthreads();
+    const int nk4 = (nk + 3) & ~3;
+    for (int j = 0; j < nk4; j += 4) {         // NOUT independent accumulation chains per thread
+#pragma unroll
+      for (int o = 0; o < NOUT; ++o) {
+        const float4 pv = *reinterpret_cast<const float4*>(sc + poff[o] + c0 + j);
+        const float4 vv = *reinterpret_cast<const float4*>(kv + doff[o] * VLD + j);
+        acc[o] = fmaf(pv.x, vv.x, acc[o]);
+        acc[o] = fmaf(pv.y, vv.y, acc[o]);
+        acc[o] = fmaf(pv.z, vv.z, acc[o]);
+        acc[o] = fmaf(pv.w, vv.w, acc[o]);
+      }
+    }
+  }
+#pragma unroll
+  for (int o = 0; o < NOUT; ++o) {
+    const int idx = threadIdx.x + 128 * o;
+    const int i = idx / D, d = idx - i * D;
+    if (i < nq) out[(size_t)(qrow0 + i) * ldo + hd * D + d] = acc[o];
+  }
+}
+
+template <int D, int QB>
+cudaError_t launch_attention_tiled(const float* Q, int ldq, int qcol, const float* K, int ldk, int kcol, const float* V,
+                                   int ldv, int vcol, int H, float scale, int rd, const float2* tab, const RowMap& qmap,
+                                   const RowMap& kmap, int max_tq, int max_tk, const int* q_tok, const int* q_cu,
+                                   int band, float* out, int ldo, cudaStream_t st) {
+  const int kvn = (kAttChunk * (D + 1) > D * (kAttChunk + 4)) ? kAttChunk * (D + 1) : D * (kAttChunk + 4);
+  const size_t smem = (size_t)(QB * D + kvn + QB * ((max_tk + 3) & ~3)) * sizeof(float);
+  if (smem > 227 * 1024) return cudaErrorInvalidValue;
+  static size_t configured = 0;
+  if (smem > 48 * 1024 && smem > configured) {
+    cudaError_t e = cudaFuncSetAttribute(attention_tiled_kernel<D, QB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)smem);
+    if (e != cudaSuccess) return e;
+    configured = smem;
+  }
+  dim3 grid((max_tq + QB - 1) / QB, H, qmap.n_seg);
+  attention_tiled_kernel<D, QB><<<grid, 128, smem, st>>>(Q, ldq, qcol, K, ldk, kcol, V, ldv, vcol, scale, rd, tab, qmap,
+                                                         kmap, q_tok, q_cu, band, out, ldo);
+  return cudaGetLastError();
+}
+
+// rd: features of every head that still need the RoPE rotation (0: Q / K are used as stored).  The
+// tiled kernels rotate while staging; for other head sizes the generic kernel runs after an in-place
+// rotation pass.
 cudaError_t attention(const float* Q, int ldq, int qcol, const float* K, int ldk, int kcol, const float* V, int ldv,
-                      int vcol, int H, int D, float scale, const RowMap& qmap, const RowMap& kmap, int max_tq,
-                      int max_tk, const int* q_tok, const int* q_cu, int band, float* out, int ldo, cudaStream_t st) {
+                      int vcol, int H, int D, float scale, int rd, const float2* rope_tab, const RowMap& qmap,
+                      const RowMap& kmap, int max_tq, int max_tk, const int* q_tok, const int* q_cu, int band, float* out,
+                      int ldo, cudaStream_t st) {
   if (D % 4 != 0) return cudaErrorInvalidValue;
+  // queries per CTA: as many as keep <= 20 outputs per thread (K / V are staged once per CTA)
+#define STTS_ATT(DD, QQ)                                                                                              \
+  if (D == DD && (rd == 0 || rope_tab != nullptr))                                                                    \
+    return launch_attention_tiled<DD, QQ>(Q, ldq, qcol, K, ldk, kcol, V, ldv, vcol, H, scale, rd, rope_tab, qmap,     \
+                                          kmap, max_tq, max_tk, q_tok, q_cu, band, out, ldo, st);
+  STTS_ATT(16, 16)
+  STTS_ATT(40, 32)
+  STTS_ATT(96, 16)
+  STTS_ATT(160, 16)
+#undef STTS_ATT
+  if (rd != 0) {   // generic head size: rotate q / k in place first
+    cudaError_t e = rope_inplace(const_cast<float*>(Q), ldq, qcol, H * D, 1, H, D, rd, qmap, st);
+    if (e == cudaSuccess) e = rope_inplace(const_cast<float*>(K), ldk, kcol, H * D, 1, H, D, rd, kmap, st);
+    if (e != cudaSuccess) return e;
+  }
   const size_t smem = (size_t)(kAttQ * D + kAttQ * ((max_tk + 3) & ~3)) * sizeof(float);
   static size_t configured = 0;
   if (smem > 48 * 1024 && smem > configured) {
