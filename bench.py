@@ -155,18 +155,24 @@ def run_reference_arm(args, rank: int, world: int):
     print(json.dumps(line), flush=True)
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the largest GEMM of the step (the forward STFT,
+# "stft16") from the `ncu --set full` capture committed under profiles/ (filled in from the capture)
+TRAFFIC_TOP_KERNEL = None
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32", "tf32x3"])
+    ap.add_argument("--precision", default="f16", choices=["f16", "bf16", "fp32", "tf32x3"],
+                    help="f16 = 16-bit mode (fp16 operand twins, fp32 accumulate; \"bf16\" is an alias)")
     ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU work for the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-flush", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="launch every step eagerly (no CUDA graph replay)")
-    ap.add_argument("--lanes", type=int, default=2,
+    ap.add_argument("--lanes", type=int, default=3,
                     help="batches in flight per GPU (SynthesizerPool lanes: own context + CUDA graph + stream each)")
     ap.add_argument("--layers", default=None, help="write the per-layer GEMM table of the eager pass to this file")
     args = ap.parse_args()
@@ -310,7 +316,7 @@ def main():
             "frac": achieved / peak_tf if peak_tf else None,
             # dram__bytes_read.sum + dram__bytes_write.sum of the largest GEMM launch (gen.amp_head) from the
             # `ncu --set full` capture committed as profiles/r1_full_gen.amp_head.ncu-rep (per launch)
-            "traffic": 198.710016e6 + 202.619136e6 if args.precision == "bf16" else None,
+            "traffic": TRAFFIC_TOP_KERNEL if args.precision in ("f16", "bf16") else None,
             "traffic_kernel": "gen.amp_head (algorithmic 161 MB in + 215 MB out)",
             "kernel": "conv_gemm_tc_kernel (tcgen05/TMA implicit-GEMM conv1d), all launches of the timed region"
                       if args.precision != "fp32" else "conv_gemm_simt_kernel",
@@ -329,7 +335,7 @@ def main():
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": {"bf16": "bf16", "fp32": "f32", "tf32x3": "tf32x3"}[args.precision],
+            "scaling": "weak", "vs_baseline": None, "dtype": {"f16": "f16", "bf16": "f16", "fp32": "f32", "tf32x3": "tf32x3"}[args.precision],
             "data": "synthetic",
             "config": {"workload": f"BASELINE configs[1]: batch {BATCH} mixed-length utterances 0.25-10 s per GPU "
                                    f"({audio_s:.1f} audio-s, {sum(int(t.numel()) for t in tokens)} phonemes), default model.yml, "

@@ -232,13 +232,13 @@ int stts_test_conv(stts_ctx* ctx, int backend, const float* d_x, int ldx, int ci
   a.ld = ldx;
   a.rows = c.L4.R;
   // bf16 backend: build a temporary twin of the operand
-  __nv_bfloat16* twin = nullptr;
+  twin_t* twin = nullptr;
   if (backend == 1) {
     if (cudaMalloc(&twin, (size_t)c.L4.R * ldx * 2) != cudaSuccess) { free_pack(pg); return fail(c, -5, "twin alloc"); }
     std::vector<float> hx((size_t)c.L4.R * ldx);
     cudaMemcpy(hx.data(), d_x, hx.size() * 4, cudaMemcpyDeviceToHost);
-    std::vector<__nv_bfloat16> hh(hx.size());
-    for (size_t i = 0; i < hx.size(); ++i) hh[i] = __float2bfloat16_rn(hx[i]);
+    std::vector<twin_t> hh(hx.size());
+    for (size_t i = 0; i < hx.size(); ++i) hh[i] = to_twin(hx[i]);
     cudaMemcpy(twin, hh.data(), hh.size() * 2, cudaMemcpyHostToDevice);
     a.h = twin;
   }

@@ -9,8 +9,17 @@
 // the two ends of the buffer), and every 128-row tile belongs to exactly one segment.
 #pragma once
 #include <cuda_runtime.h>
-#include <cuda_bf16.h>
 #include <cuda_fp16.h>
+
+// 16-bit twin of an activation / weight: the operand type of the one-pass tensor-core GEMMs.  IEEE
+// fp16 (kind::f16 MMAs run fp16 and bf16 at the same rate; fp16 rounds at 2^-12 instead of 2^-9).
+// Conversions saturate at +-65504 instead of producing inf; activations on this path are normalised
+// or gated (|x| << 65504), weights are pre-scaled by a power of two per layer (prepack.cu).
+typedef __half twin_t;
+typedef __half2 twin2_t;
+__host__ __device__ __forceinline__ float sat16(float x) { return x > 65504.f ? 65504.f : (x < -65504.f ? -65504.f : x); }
+__host__ __device__ __forceinline__ twin_t to_twin(float x) { return __float2half_rn(sat16(x)); }
+__device__ __forceinline__ twin2_t to_twin2(float x, float y) { return __floats2half2_rn(sat16(x), sat16(y)); }
 #include <stdint.h>
 
 #define STTS_TILE_M 128
@@ -48,9 +57,9 @@ struct Epi {
   int kind;
   int N;                       // logical output columns of the GEMM (pairs count as 2)
   float* out; int ldo; int col0;
-  __nv_bfloat16* outh; int ldh; int colh0;   // optional bf16 twin of `out`
+  twin_t* outh; int ldh; int colh0;          // optional 16-bit twin of `out`
   float* out2; int ldo2; int col20;
-  __nv_bfloat16* outh2; int ldh2; int colh20;  // optional bf16 twin of `out2` (EPI_STFT)
+  twin_t* outh2; int ldh2; int colh20;       // optional 16-bit twin of `out2`
   // optional fp16 split twins of out / out2 (same ldh / colh geometry): g = fp16(x), l = fp16(x - g).
   // x = g + l to ~2^-22 relative: operands of the f16x3 island GEMMs (g alone: the one-pass fp16 GEMM)
   __half* outg; __half* outl; __half* outg2; __half* outl2;
@@ -108,9 +117,9 @@ __device__ __forceinline__ void epi_apply(const Epi& e, int r, int seg, int n0, 
       for (int i = 0; i < NV; ++i) if (n0 + i < e.N) o[i] = v[i];
     }
     if (e.outh != nullptr) {
-      __nv_bfloat16* oh = e.outh + (size_t)r * e.ldh + e.colh0 + n0;
+      twin_t* oh = e.outh + (size_t)r * e.ldh + e.colh0 + n0;
 #pragma unroll
-      for (int i = 0; i < NV; ++i) if (n0 + i < e.N) oh[i] = __float2bfloat16_rn(v[i]);
+      for (int i = 0; i < NV; ++i) if (n0 + i < e.N) oh[i] = to_twin(v[i]);
     }
   } else if constexpr (KIND == EPI_GATE) {
     const int H = e.N >> 1;
@@ -123,7 +132,7 @@ __device__ __forceinline__ void epi_apply(const Epi& e, int r, int seg, int n0, 
         const float b = acc[i + 1] + e.bias[n + 1] + e.segvec[(size_t)seg * e.ldseg + H + c];
         const float y = tanhf(a) * (1.f / (1.f + expf(-b)));
         e.out[(size_t)r * e.ldo + e.col0 + c] = y;
-        if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = __float2bfloat16_rn(y);
+        if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = to_twin(y);
       }
     }
   } else if constexpr (KIND == EPI_RESSKIP) {
@@ -136,12 +145,12 @@ __device__ __forceinline__ void epi_apply(const Epi& e, int r, int seg, int n0, 
           float* p = e.out + (size_t)r * e.ldo + e.col0 + n;
           const float y = *p + v;
           *p = y;
-          if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + n] = __float2bfloat16_rn(y);
+          if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + n] = to_twin(y);
         } else {
           float* p = e.out2 + (size_t)r * e.ldo2 + e.col20 + (n - e.split);
           const float y = e.accumulate2 ? (*p + v) : v;
           *p = y;
-          if (e.outh2 != nullptr) e.outh2[(size_t)r * e.ldh2 + e.colh20 + (n - e.split)] = __float2bfloat16_rn(y);
+          if (e.outh2 != nullptr) e.outh2[(size_t)r * e.ldh2 + e.colh20 + (n - e.split)] = to_twin(y);
         }
       }
     }
@@ -156,7 +165,7 @@ __device__ __forceinline__ void epi_apply(const Epi& e, int r, int seg, int n0, 
         float* p = e.out + (size_t)r * e.ldo + e.col0 + c;
         const float y = (*p - m) * expf(-logs);
         *p = y;
-        if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = __float2bfloat16_rn(y);
+        if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = to_twin(y);
       }
     }
   } else if constexpr (KIND == EPI_PRIOR) {
@@ -170,7 +179,7 @@ __device__ __forceinline__ void epi_apply(const Epi& e, int r, int seg, int n0, 
         const float nz = e.res[(size_t)r * e.ldr + e.rcol0 + c];
         const float y = mean + nz * expf(logstd);
         e.out[(size_t)r * e.ldo + e.col0 + c] = y;
-        if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = __float2bfloat16_rn(y);
+        if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = to_twin(y);
       }
     }
   } else if constexpr (KIND == EPI_STFT) {
@@ -188,8 +197,8 @@ __device__ __forceinline__ void epi_apply(const Epi& e, int r, int seg, int n0, 
         const float ph = atan2f(im / d, re / d);
         e.out[(size_t)r * e.ldo + e.col0 + c] = mag;
         e.out2[(size_t)r * e.ldo2 + e.col20 + c] = ph;
-        if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = __float2bfloat16_rn(mag);
-        if (e.outh2 != nullptr) e.outh2[(size_t)r * e.ldh2 + e.colh20 + c] = __float2bfloat16_rn(ph);
+        if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = to_twin(mag);
+        if (e.outh2 != nullptr) e.outh2[(size_t)r * e.ldh2 + e.colh20 + c] = to_twin(ph);
       }
     }
   }
@@ -253,11 +262,11 @@ struct EpiPair {
     }
     return t;
   }
-  static __device__ __forceinline__ void store2(float* o, __nv_bfloat16* oh, float x0, float x1, bool both,
+  static __device__ __forceinline__ void store2(float* o, twin_t* oh, float x0, float x1, bool both,
                                                 __half* og = nullptr, __half* ol = nullptr) {
     if (both) {
       if (o != nullptr) *reinterpret_cast<float2*>(o) = make_float2(x0, x1);
-      if (oh != nullptr) *reinterpret_cast<__nv_bfloat162*>(oh) = __floats2bfloat162_rn(x0, x1);
+      if (oh != nullptr) *reinterpret_cast<twin2_t*>(oh) = to_twin2(x0, x1);
       if (og != nullptr) {
         const __half2 g = __floats2half2_rn(x0, x1);
         *reinterpret_cast<__half2*>(og) = g;
@@ -266,7 +275,7 @@ struct EpiPair {
       }
     } else {
       if (o != nullptr) o[0] = x0;
-      if (oh != nullptr) oh[0] = __float2bfloat16_rn(x0);
+      if (oh != nullptr) oh[0] = to_twin(x0);
       if (og != nullptr) { __half lo; f16_split(x0, og, ol != nullptr ? ol : &lo); }
     }
   }
@@ -321,18 +330,18 @@ struct EpiPair {
         const float a = a0 + b0 + g0, b = a1 + b1 + g1;
         const float y = th(a) * dv(1.f, 1.f + ex(-b));
         e.out[(size_t)r * e.ldo + e.col0 + c] = y;
-        if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = __float2bfloat16_rn(y);
+        if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = to_twin(y);
       } else if constexpr (KIND == EPI_COUPLE) {
         const float m = a0 + b0, logs = a1 + b1;
         float* p = e.out + (size_t)r * e.ldo + e.col0 + c;
         const float y = (t.x - m) * ex(-logs);
         *p = y;
-        if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = __float2bfloat16_rn(y);
+        if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = to_twin(y);
       } else if constexpr (KIND == EPI_PRIOR) {
         const float mean = a0 + b0, logstd = a1 + b1;
         const float y = mean + t.x * ex(logstd);
         e.out[(size_t)r * e.ldo + e.col0 + c] = y;
-        if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = __float2bfloat16_rn(y);
+        if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = to_twin(y);
       } else if constexpr (KIND == EPI_STFT) {
         // frame 0 of an utterance is exactly real (see epi_apply)
         const float re = a0, im = (r == seg_first_row) ? 0.f : a1;
@@ -341,8 +350,8 @@ struct EpiPair {
         const float ph = atan2f(im / d, re / d);
         e.out[(size_t)r * e.ldo + e.col0 + c] = mag;
         e.out2[(size_t)r * e.ldo2 + e.col20 + c] = ph;
-        if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = __float2bfloat16_rn(mag);
-        if (e.outh2 != nullptr) e.outh2[(size_t)r * e.ldh2 + e.colh20 + c] = __float2bfloat16_rn(ph);
+        if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = to_twin(mag);
+        if (e.outh2 != nullptr) e.outh2[(size_t)r * e.ldh2 + e.colh20 + c] = to_twin(ph);
         __half lo;
         if (e.outg != nullptr)
           f16_split(mag, e.outg + (size_t)r * e.ldh + e.colh0 + c,
@@ -360,7 +369,7 @@ struct EpiPair {
 // Up to two K-segments (fused 1x1 shortcut, channel concatenation across buffers).
 struct KSeg {
   const float* A; int lda; int col0;         // fp32 operand
-  const __nv_bfloat16* Ah; int ldah; int colh0;  // bf16 twin (tensor-core bf16 mode)
+  const twin_t* Ah; int ldah; int colh0;     // 16-bit twin (one-pass tensor-core mode)
   const __half* Ag; const __half* Al; int ldag;  // fp16 split twins g / l (f16 and f16x3 modes), columns as colh0
   int taps; int pad; int cin_pad;            // cin_pad % 64 == 0
   int rows;                                  // rows allocated in A (bounds for zero fill)
@@ -370,8 +379,7 @@ struct ConvGemm {
   KSeg seg[2];
   int n_kseg;
   const float* W;                 // [Npad, Ktot] fp32, K-major
-  const __nv_bfloat16* Wh;        // bf16 copy
-  const __nv_bfloat16* Wh_seg;    // optional per-utterance bf16 weights [n_seg * Npad, Ktot] (GRN folded into pw2)
+  const twin_t* Wh_seg;           // optional per-utterance fp16 weights [n_seg * Npad, Ktot], unscaled (GRN folded into pw2)
   const __half* Wg;               // fp16(W * wscale)                       (f16 / f16x3 modes)
   const __half* Wl;               // fp16(W * wscale - Wg)                  (f16x3 mode)
   float acc_scale;                // accumulators are multiplied by this before the epilogue (1 / wscale / a-scale)

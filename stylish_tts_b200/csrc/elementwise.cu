@@ -118,7 +118,7 @@ cudaError_t style_fc(const float* W, const float* bias, const float* s, int J, i
 __global__ void __launch_bounds__(256) adain_act_kernel(const float* __restrict__ x, int ldx, int C, RowMap map,
                                                         const float* __restrict__ mean, const float* __restrict__ rstd,
                                                         const float* __restrict__ gb, int ldgb, float slope,
-                                                        float* __restrict__ y, int ldy, __nv_bfloat16* __restrict__ yh,
+                                                        float* __restrict__ y, int ldy, twin_t* __restrict__ yh,
                                                         int ldyh) {
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
@@ -141,12 +141,12 @@ __global__ void __launch_bounds__(256) adain_act_kernel(const float* __restrict_
     a = a > 0.f ? a : a * slope;
     b = b > 0.f ? b : b * slope;
     *reinterpret_cast<float2*>(y + r * ldy + c) = make_float2(a, b);
-    if (yh != nullptr) *reinterpret_cast<__nv_bfloat162*>(yh + r * ldyh + c) = __floats2bfloat162_rn(a, b);
+    if (yh != nullptr) *reinterpret_cast<twin2_t*>(yh + r * ldyh + c) = to_twin2(a, b);
   }
 }
 
 cudaError_t adain_act(const float* x, int ldx, int C, const RowMap& map, const float* mean, const float* rstd,
-                      const float* gb, int ldgb, float slope, float* y, int ldy, __nv_bfloat16* yh, int ldyh,
+                      const float* gb, int ldgb, float slope, float* y, int ldy, twin_t* yh, int ldyh,
                       cudaStream_t st) {
   if ((C & 1) || (ldx & 1) || (ldy & 1) || (ldgb & 1)) return cudaErrorInvalidValue;
   dim3 grid(map.n_tiles, (C + 127) / 128);
@@ -162,7 +162,7 @@ __global__ void __launch_bounds__(256) expand_tokens_kernel(const float* __restr
                                                             const int* __restrict__ idx, const int* __restrict__ cu_f,
                                                             const int* __restrict__ tok_off, int div, RowMap map,
                                                             float* __restrict__ out, int ldo, int col0,
-                                                            __nv_bfloat16* __restrict__ outh, int ldh, int colh0) {
+                                                            twin_t* __restrict__ outh, int ldh, int colh0) {
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
   if (seg < 0) return;
@@ -176,12 +176,12 @@ __global__ void __launch_bounds__(256) expand_tokens_kernel(const float* __restr
     const float v = tok[(size_t)t * C + c];
     const size_t r = (size_t)tile * 128 + lr;
     out[r * ldo + col0 + c] = v;
-    if (outh != nullptr) outh[r * ldh + colh0 + c] = __float2bfloat16_rn(v);
+    if (outh != nullptr) outh[r * ldh + colh0 + c] = to_twin(v);
   }
 }
 
 cudaError_t expand_tokens(const float* tok, int C, const int* idx, const int* cu_f, const int* tok_off, int div,
-                          const RowMap& map, float* out, int ldo, int col0, __nv_bfloat16* outh, int ldh, int colh0,
+                          const RowMap& map, float* out, int ldo, int col0, twin_t* outh, int ldh, int colh0,
                           cudaStream_t st) {
   expand_tokens_kernel<<<map.n_tiles, 256, 0, st>>>(tok, C, idx, cu_f, tok_off, div, map, out, ldo, col0, outh, ldh,
                                                     colh0);
@@ -248,8 +248,8 @@ __global__ void __launch_bounds__(128) f0n_conv_kernel(const float* __restrict__
       d.f[k][(size_t)r * d.ld[k] + d.col[k] + 1] = n;
     }
     if (d.h[k] != nullptr) {
-      d.h[k][(size_t)r * d.ldh[k] + d.col[k]] = __float2bfloat16_rn(f0);
-      d.h[k][(size_t)r * d.ldh[k] + d.col[k] + 1] = __float2bfloat16_rn(n);
+      d.h[k][(size_t)r * d.ldh[k] + d.col[k]] = to_twin(f0);
+      d.h[k][(size_t)r * d.ldh[k] + d.col[k] + 1] = to_twin(n);
     }
   }
 }
@@ -267,7 +267,7 @@ __global__ void __launch_bounds__(256) transpose_in_kernel(const float* __restri
                                                            const long long* __restrict__ off,
                                                            const int* __restrict__ cs, int C, RowMap map,
                                                            float* __restrict__ dst, int ld, int col0,
-                                                           __nv_bfloat16* __restrict__ dsth, int ldh, int colh0) {
+                                                           twin_t* __restrict__ dsth, int ldh, int colh0) {
   __shared__ float t[32][33];
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
@@ -292,7 +292,7 @@ __global__ void __launch_bounds__(256) transpose_in_kernel(const float* __restri
           const size_t r = (size_t)tile * 128 + lr;
           const float v = t[tx][ty + 8 * k];
           dst[r * ld + col0 + c] = v;
-          if (dsth != nullptr) dsth[r * ldh + colh0 + c] = __float2bfloat16_rn(v);
+          if (dsth != nullptr) dsth[r * ldh + colh0 + c] = to_twin(v);
         }
       }
       __syncthreads();
@@ -301,7 +301,7 @@ __global__ void __launch_bounds__(256) transpose_in_kernel(const float* __restri
 }
 
 cudaError_t transpose_in(const float* src, const long long* off, const int* cs, int C, const RowMap& map, float* dst,
-                         int ld, int col0, __nv_bfloat16* dsth, int ldh, int colh0, cudaStream_t st) {
+                         int ld, int col0, twin_t* dsth, int ldh, int colh0, cudaStream_t st) {
   dim3 grid(map.n_tiles, (C + 31) / 32 < 8 ? (C + 31) / 32 : 8);
   transpose_in_kernel<<<grid, 256, 0, st>>>(src, off, cs, C, map, dst, ld, col0, dsth, ldh, colh0);
   return cudaGetLastError();
@@ -380,7 +380,7 @@ __global__ void __launch_bounds__(256) dwconv_adaln_kernel(const float* __restri
                                                            const float* __restrict__ wt, const float* __restrict__ bias,
                                                            const float* __restrict__ gb, int ldgb, float eps,
                                                            float* __restrict__ y, int ldy,
-                                                           __nv_bfloat16* __restrict__ yh, int ldyh) {
+                                                           twin_t* __restrict__ yh, int ldyh) {
   constexpr int C = 512, TR = 16, PAD = (K - 1) / 2;
   __shared__ float red[8][TR];
   __shared__ float stat[TR];
@@ -457,13 +457,13 @@ __global__ void __launch_bounds__(256) dwconv_adaln_kernel(const float* __restri
       const float v1 = (1.f + g.y) * ((a1[o] - m[o]) * rs) + be.y;
       const size_t r = (size_t)r0 + o;
       *reinterpret_cast<float2*>(y + r * ldy + c) = make_float2(v0, v1);
-      if (yh != nullptr) *reinterpret_cast<__nv_bfloat162*>(yh + r * ldyh + c) = __floats2bfloat162_rn(v0, v1);
+      if (yh != nullptr) *reinterpret_cast<twin2_t*>(yh + r * ldyh + c) = to_twin2(v0, v1);
     }
   }
 }
 
 cudaError_t dwconv_adaln(const float* x, int ldx, const RowMap& map, int K, const float* wt, const float* bias,
-                         const float* gb, int ldgb, float eps, float* y, int ldy, __nv_bfloat16* yh, int ldyh,
+                         const float* gb, int ldgb, float eps, float* y, int ldy, twin_t* yh, int ldyh,
                          cudaStream_t st) {
   dim3 grid(map.n_tiles, 8);
   switch (K) {
@@ -605,7 +605,7 @@ cudaError_t grn_scale_partials(const float* colss, int ld, int C, const RowMap& 
 // (pwconv2(x * s + beta) = (W diag(s)) x + W beta: the W beta term is added to the bias at prepack).
 __global__ void __launch_bounds__(256) grn_weights_kernel(const float* __restrict__ W, int N, int K,
                                                           const float* __restrict__ scale,
-                                                          __nv_bfloat16* __restrict__ Wu) {
+                                                          twin_t* __restrict__ Wu) {
   const int u = blockIdx.y;
   const size_t total = (size_t)N * K / 2;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
@@ -613,11 +613,11 @@ __global__ void __launch_bounds__(256) grn_weights_kernel(const float* __restric
     const int k = (int)(e % K);
     const float2 w = *reinterpret_cast<const float2*>(W + e);
     const float2 sc = *reinterpret_cast<const float2*>(scale + (size_t)u * K + k);
-    *reinterpret_cast<__nv_bfloat162*>(Wu + (size_t)u * N * K + e) = __floats2bfloat162_rn(w.x * sc.x, w.y * sc.y);
+    *reinterpret_cast<twin2_t*>(Wu + (size_t)u * N * K + e) = to_twin2(w.x * sc.x, w.y * sc.y);
   }
 }
 
-cudaError_t grn_weights(const float* W, int N, int K, const float* scale, int n_seg, __nv_bfloat16* Wu, cudaStream_t st) {
+cudaError_t grn_weights(const float* W, int N, int K, const float* scale, int n_seg, twin_t* Wu, cudaStream_t st) {
   if (K % 2 != 0) return cudaErrorInvalidValue;
   grn_weights_kernel<<<dim3(148, n_seg), 256, 0, st>>>(W, N, K, scale, Wu);
   return cudaGetLastError();
@@ -626,7 +626,7 @@ cudaError_t grn_weights(const float* W, int N, int K, const float* scale, int n_
 __global__ void __launch_bounds__(256) seg_affine_kernel(float* __restrict__ x, int ldx, int C, RowMap map,
                                                          const float* __restrict__ scale,
                                                          const float* __restrict__ shift,
-                                                         __nv_bfloat16* __restrict__ xh, int ldxh) {
+                                                         twin_t* __restrict__ xh, int ldxh) {
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
   if (seg < 0) return;
@@ -642,14 +642,14 @@ __global__ void __launch_bounds__(256) seg_affine_kernel(float* __restrict__ x, 
     v.x = v.x * sc.x + sf.x; v.y = v.y * sc.y + sf.y; v.z = v.z * sc.z + sf.z; v.w = v.w * sc.w + sf.w;
     *reinterpret_cast<float4*>(x + r * ldx + c) = v;
     if (xh != nullptr) {
-      *reinterpret_cast<__nv_bfloat162*>(xh + r * ldxh + c) = __floats2bfloat162_rn(v.x, v.y);
-      *reinterpret_cast<__nv_bfloat162*>(xh + r * ldxh + c + 2) = __floats2bfloat162_rn(v.z, v.w);
+      *reinterpret_cast<twin2_t*>(xh + r * ldxh + c) = to_twin2(v.x, v.y);
+      *reinterpret_cast<twin2_t*>(xh + r * ldxh + c + 2) = to_twin2(v.z, v.w);
     }
   }
 }
 
 cudaError_t grn_apply(float* x, int ldx, int C, const RowMap& map, const float* gx, const float* gamma,
-                      const float* beta, float* scale_scratch, __nv_bfloat16* xh, int ldxh, cudaStream_t st) {
+                      const float* beta, float* scale_scratch, twin_t* xh, int ldxh, cudaStream_t st) {
   grn_scale_kernel<<<map.n_seg, 256, 0, st>>>(gx, C, gamma, scale_scratch);
   dim3 grid(map.n_tiles, 4);
   seg_affine_kernel<<<grid, 256, 0, st>>>(x, ldx, C, map, scale_scratch, beta, xh, ldxh);

@@ -24,8 +24,7 @@ struct PackedGemm {
   int taps[2] = {0, 0}, pad[2] = {0, 0}, cin_pad[2] = {0, 0};
   float* Wf = nullptr;            // exact fp32                     [Npad, Ktot]
   float* Whl = nullptr;           // tf32 hi rows then lo rows      [2 * Npad, Ktot]
-  __nv_bfloat16* Wh = nullptr;    // bf16                           [Npad, Ktot]
-  __half* Wg = nullptr;           // fp16(W * wscale)               [Npad, Ktot]
+  __half* Wg = nullptr;           // fp16(W * wscale): one-pass 16-bit GEMMs and hi part of f16x3  [Npad, Ktot]
   __half* Wl = nullptr;           // fp16(W * wscale - Wg)          [Npad, Ktot]
   float wscale = 1.f;             // power of two
   float* bias = nullptr;          // [Npad] (zeros when the layer has no bias)
@@ -35,7 +34,7 @@ struct PackedGemm {
 
 struct Act {          // an activation buffer: fp32 + optional bf16 twin, same ld
   float* f = nullptr;
-  __nv_bfloat16* h = nullptr;
+  twin_t* h = nullptr;
   __half* g = nullptr;          // fp16 split twins g = fp16(s x), l = fp16(s x - g): operands of the
   __half* l = nullptr;          //   island GEMMs (f16x3; g alone for the one-pass fp16 GEMM)
   int ldg = 0;                  // row pitch of g / l (elements)
@@ -112,7 +111,7 @@ void build_layout(Layout& L, int n_seg, const int* len);
 int set_layout(Context& c, int n_seg, const int* len_f, const int* len_f4);
 int run_gemm(Context& c, const PackedGemm& pg, int cls, const Act* a0, int a0_col, const Act* a1, int a1_col,
              const Epi& epi, const RowMap& map, cudaStream_t st, int forced_backend = -1,
-             const __nv_bfloat16* seg_weights = nullptr);   // per-utterance bf16 weights [n_seg * Npad, Ktot]
+             const twin_t* seg_weights = nullptr);   // per-utterance bf16 weights [n_seg * Npad, Ktot]
 int run_pe_towers(Context& c, const float* d_x, const float* d_style, float* d_pitch, float* d_energy, cudaStream_t st);
 int run_decoder_core(Context& c, const float* d_style, cudaStream_t st);
 int run_decoder(Context& c, const float* d_asr, const float* d_f0, const float* d_n, const float* d_style, float* d_out,

@@ -6,7 +6,7 @@
 //   warps 2..5  : operand converter during the main loop (fp32 mode only) and epilogue
 //                 (tcgen05.ld 32x32b -> registers -> fused epilogue -> global)
 // Two arithmetic modes:
-//   MODE_BF16   : kind::f16, bf16 operands (bf16 twins of the activations), fp32 accumulate.
+//   MODE_F16   : kind::f16, bf16 operands (bf16 twins of the activations), fp32 accumulate.
 //   MODE_TF32X3 : kind::tf32 with error-compensated operand splitting, x = hi + lo with hi the
 //                 tf32 truncation of x: acc += hi*hi' + hi*lo' + lo*hi'  (~2^-21 relative, i.e.
 //                 fp32-grade).  The activation split is done in shared memory
@@ -143,9 +143,9 @@ __device__ __forceinline__ float rna_tf32(float x) {
   return __uint_as_float(r);
 }
 
-// MODE_BF16 doubles as the one-pass fp16 GEMM (runtime instruction-descriptor formats), MODE_F16X3 is
+// MODE_F16 doubles as the one-pass fp16 GEMM (runtime instruction-descriptor formats), MODE_F16X3 is
 // the three-pass fp16 split (hi*hi + hi*lo + lo*hi, fp32-grade), MODE_TF32X3 the tf32 split on fp32 operands
-enum { MODE_BF16 = 0, MODE_TF32X3 = 1, MODE_F16X3 = 2 };
+enum { MODE_F16 = 0, MODE_TF32X3 = 1, MODE_F16X3 = 2 };
 
 // OCC = 2 (bf16 mode, BN = 128 only): half the pipeline depth so that two CTAs share an SM (2 x 97 KB
 // shared memory, 2 x 128 TMEM columns, 2 x 320 threads x <= 96 registers): the epilogue of one CTA
@@ -154,7 +154,7 @@ enum { MODE_BF16 = 0, MODE_TF32X3 = 1, MODE_F16X3 = 2 };
 template <int MODE, int BN, int OCC = 1>
 struct Cfg {
   static constexpr bool kTF32 = (MODE == MODE_TF32X3);
-  static constexpr bool kSplit = (MODE != MODE_BF16);     // hi / lo operand pairs, 3 MMAs per k-step
+  static constexpr bool kSplit = (MODE != MODE_F16);     // hi / lo operand pairs, 3 MMAs per k-step
   static constexpr int kElem = kTF32 ? 4 : 2;
   static constexpr int kBK = 128 / kElem;                 // elements per 128-byte swizzle row: 32 / 64
   static constexpr int kUmmaK = 32 / kElem;               // 8 (tf32) / 16 (bf16)
@@ -329,7 +329,7 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
     const int seg_first = (epi.seg_start != nullptr) ? epi.seg_start[seg] : -1;
     const int c = (ew >> 2) * 64;
     if (n0 + c < epi.N) {                      // warp-uniform
-      EpiPair<KIND, MODE == MODE_BF16> ep;
+      EpiPair<KIND, MODE == MODE_F16> ep;
       ep.init(epi, seg, n0 + c + 2 * lane);
       {
         float v[64];
@@ -434,7 +434,7 @@ cudaError_t launch_one(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
   p.n_chunks = 0;
   for (int s = 0; s < 2; ++s) {
     const KSeg& ks = g.seg[s < g.n_kseg ? s : 0];
-    const bool f16 = (MODE == MODE_F16X3) || (MODE == MODE_BF16 && g.f16);
+    const bool f16 = (MODE == MODE_F16X3) || (MODE == MODE_F16 && g.f16);
     const void* base = (MODE == MODE_TF32X3) ? (const void*)ks.A : (f16 ? (const void*)ks.Ag : (const void*)ks.Ah);
     const int ld = (MODE == MODE_TF32X3) ? ks.lda : (f16 ? ks.ldag : ks.ldah);
     if (base == nullptr) return cudaErrorInvalidValue;
@@ -453,15 +453,15 @@ cudaError_t launch_one(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
     }
   }
   p.acc_scale = 1.f;
-  if (MODE == MODE_BF16) {
+  if (MODE == MODE_F16) {
     const bool per_seg = !g.f16 && g.Wh_seg != nullptr;
-    const void* w = g.f16 ? (const void*)g.Wg : (per_seg ? (const void*)g.Wh_seg : (const void*)g.Wh);
+    const void* w = per_seg ? (const void*)g.Wh_seg : (const void*)g.Wg;
     if (w == nullptr) return cudaErrorInvalidValue;
     if (!get_map(w, per_seg ? g.Npad * map.n_seg : g.Npad, g.Ktot, 2, BN, &mW)) return cudaErrorNotSupported;
     p.w_seg_rows = per_seg ? g.Npad : 0;
     mWlo = mW;
-    p.ab_fmt = g.f16 ? 0u : 1u;
-    if (g.f16) p.acc_scale = g.acc_scale;
+    p.ab_fmt = 0u;                                     // fp16 operands
+    p.acc_scale = per_seg ? 1.f : g.acc_scale;         // per-utterance weights are stored unscaled
   } else if (MODE == MODE_F16X3) {
     if (g.Wg == nullptr || g.Wl == nullptr) return cudaErrorInvalidValue;
     if (!get_map(g.Wg, g.Npad, g.Ktot, 2, BN, &mW)) return cudaErrorNotSupported;
@@ -498,13 +498,18 @@ int occ2_max_chunks() {
 
 template <int MODE, int KIND>
 cudaError_t launch_bn(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
-  if constexpr (MODE == MODE_BF16) {
+  if constexpr (MODE == MODE_F16) {
     int chunks = 0;
     for (int s = 0; s < g.n_kseg; ++s) chunks += g.seg[s].taps * (g.seg[s].cin_pad / 64);
     if (chunks <= occ2_max_chunks()) return launch_one<MODE, 128, KIND, 2>(g, map, st);
   }
-  // BN = 256 only pays when there are at least two full 128-column tiles to merge.
-  if (MODE == MODE_BF16 && g.epi.N > 128 && g.Npad % 256 == 0) return launch_one<MODE, 256, KIND>(g, map, st);
+  // BN = 256 whenever there is more than one 128-column tile (long-K one-pass GEMMs reach the tensor peak
+  // only with the 128 x 256 tile: measured 64 % vs 36 % pipe-active); the split modes (three operand
+  // tiles per stage) use it for the wide STFT only.
+  static const bool split256 = [] { const char* e = std::getenv("STTS_SPLIT_BN256"); return e == nullptr || e[0] != '0'; }();
+  const bool wide = g.epi.N > 128 && g.Npad % 256 == 0;
+  if (MODE == MODE_F16 && wide) return launch_one<MODE, 256, KIND>(g, map, st);
+  if (MODE != MODE_F16 && wide && split256 && g.epi.N >= 1024) return launch_one<MODE, 256, KIND>(g, map, st);
   return launch_one<MODE, 128, KIND>(g, map, st);
 }
 
@@ -533,8 +538,8 @@ void tc_map_cache_clear() {
   g_map_cache.clear();
 }
 
-cudaError_t conv_gemm_tc_bf16(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
-  return launch_mode<MODE_BF16>(g, map, st);
+cudaError_t conv_gemm_tc_f16(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
+  return launch_mode<MODE_F16>(g, map, st);
 }
 cudaError_t conv_gemm_tc_tf32x3(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
   return launch_mode<MODE_TF32X3>(g, map, st);

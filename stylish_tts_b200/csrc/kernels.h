@@ -7,7 +7,7 @@ namespace stts {
 
 // ---- conv-as-GEMM (gemm_simt.cu / gemm_tc.cu)
 cudaError_t conv_gemm_simt(const ConvGemm& g, const RowMap& map, cudaStream_t st);
-cudaError_t conv_gemm_tc_bf16(const ConvGemm& g, const RowMap& map, cudaStream_t st);
+cudaError_t conv_gemm_tc_f16(const ConvGemm& g, const RowMap& map, cudaStream_t st);
 cudaError_t conv_gemm_tc_tf32x3(const ConvGemm& g, const RowMap& map, cudaStream_t st);
 cudaError_t conv_gemm_tc_f16x3(const ConvGemm& g, const RowMap& map, cudaStream_t st);
 void tc_map_cache_clear();
@@ -18,35 +18,35 @@ cudaError_t colstats(const float* x, int ld, int C, const RowMap& map, int mode,
 cudaError_t style_fc(const float* W, const float* bias, const float* s, int J, int K, int B, float* out,
                      cudaStream_t st);
 cudaError_t adain_act(const float* x, int ldx, int C, const RowMap& map, const float* mean, const float* rstd,
-                      const float* gb, int ldgb, float slope, float* y, int ldy, __nv_bfloat16* yh, int ldyh,
+                      const float* gb, int ldgb, float slope, float* y, int ldy, twin_t* yh, int ldyh,
                       cudaStream_t st);
 cudaError_t expand_tokens(const float* tok, int C, const int* idx, const int* cu_f, const int* tok_off, int div,
-                          const RowMap& map, float* out, int ldo, int col0, __nv_bfloat16* outh, int ldh, int colh0,
+                          const RowMap& map, float* out, int ldo, int col0, twin_t* outh, int ldh, int colh0,
                           cudaStream_t st);
 cudaError_t upsample4(const float* a, const float* b, const int* cu_f, const RowMap& map, float* a4, float* b4,
                       cudaStream_t st);
 struct F0NDst {  // up to three destinations for the (F0, N) channel pair
   float* f[3]; int ld[3]; int col[3];
-  __nv_bfloat16* h[3]; int ldh[3];
+  twin_t* h[3]; int ldh[3];
 };
 cudaError_t f0n_conv(const float* p4, const float* e4, const float* w, const RowMap& map, const F0NDst& d,
                      cudaStream_t st);
 cudaError_t transpose_in(const float* src, const long long* off, const int* cs, int C, const RowMap& map, float* dst,
-                         int ld, int col0, __nv_bfloat16* dsth, int ldh, int colh0, cudaStream_t st);
+                         int ld, int col0, twin_t* dsth, int ldh, int colh0, cudaStream_t st);
 cudaError_t transpose_out(const float* src, int ld, int col0, int C, const RowMap& map, float* dst,
                           const long long* off, const int* cs, int extra, cudaStream_t st);
 cudaError_t rowvec_copy(float* rowv, float* dense, const int* cu, const RowMap& map, int to_rows, cudaStream_t st);
 cudaError_t dwconv_adaln(const float* x, int ldx, const RowMap& map, int K, const float* wt, const float* bias,
-                         const float* gb, int ldgb, float eps, float* y, int ldy, __nv_bfloat16* yh, int ldyh,
+                         const float* gb, int ldgb, float eps, float* y, int ldy, twin_t* yh, int ldyh,
                          cudaStream_t st);
 cudaError_t adaln2(const float* x, int ldx, const RowMap& map, const float* gb1, const float* gb2, int ldgb, float eps,
                    float* y1, float* y2, int ldy, __half* y1g, __half* y2g, int ldyh, __half* y1l, __half* y2l,
                    cudaStream_t st);
 cudaError_t grn_apply(float* x, int ldx, int C, const RowMap& map, const float* gx, const float* gamma,
-                      const float* beta, float* scale_scratch, __nv_bfloat16* xh, int ldxh, cudaStream_t st);
+                      const float* beta, float* scale_scratch, twin_t* xh, int ldxh, cudaStream_t st);
 cudaError_t grn_scale_partials(const float* colss, int ld, int C, const RowMap& map, const float* gamma, float* gx,
                                float* scale, cudaStream_t st);
-cudaError_t grn_weights(const float* W, int N, int K, const float* scale, int n_seg, __nv_bfloat16* Wu, cudaStream_t st);
+cudaError_t grn_weights(const float* W, int N, int K, const float* scale, int n_seg, twin_t* Wu, cudaStream_t st);
 cudaError_t rowdot(const float* x, int ldx, int C, const RowMap& map, const float* w, const float* bias, const int* cu,
                    float* dense, cudaStream_t st);
 cudaError_t fill(float* p, size_t n, float v, cudaStream_t st);

@@ -113,11 +113,11 @@ int set_layout(Context& c, int n_seg, const int* len_f, const int* len_f4) {
   ArenaPlan plan;
   std::map<std::string, size_t> off_f, off_h;
   // fp16 split twins (g = fp16(s x), l = fp16(s x - g)) of the operands of the island GEMMs (f16x3 / f16).
-  // SRC: the STFT operand, 75 samples per row padded to 128 columns (a 16-bit K chunk is 64 columns);
+  // SRC: the STFT operand as explicit frames [row, 1216] (1200 window taps + pad to a multiple of 64);
   // pre-scales: SRC x 2^8 (|source| < ~5: keeps the residuals normal), SPEC x 2^-4 (e^logamp up to 1e6)
   struct GTwin { const char* name; int ldg; float gscale; };
   const GTwin g_names[] = {{"AMPN", 0, 1.f}, {"PHN", 0, 1.f}, {"CATP", 0, 1.f}, {"SPEC", 0, 0.0625f},
-                           {"HS", 0, 1.f},   {"HP", 0, 1.f},  {"SRC", 128, 256.f}};
+                           {"HS", 0, 1.f},   {"HP", 0, 1.f},  {"SRC", 1216, 256.f}};
   auto gtwin = [&](const std::string& n) -> const GTwin* {
     for (const GTwin& q : g_names) if (n == q.name) return &q;
     return nullptr;
@@ -188,7 +188,7 @@ int set_layout(Context& c, int n_seg, const int* len_f, const int* len_f4) {
     a.ld = w.ld;
     a.rows = (w.rate == 4 ? c.L4.R : c.LF.R) + w.extra_rows;
     a.f = reinterpret_cast<float*>(c.arena + off_f[w.name]);
-    a.h = off_h.count(w.name) ? reinterpret_cast<__nv_bfloat16*>(c.arena + off_h[w.name]) : nullptr;
+    a.h = off_h.count(w.name) ? reinterpret_cast<twin_t*>(c.arena + off_h[w.name]) : nullptr;
     if (const GTwin* q = gtwin(w.name)) {
       a.g = reinterpret_cast<__half*>(c.arena + off_g[w.name]);
       a.l = reinterpret_cast<__half*>(c.arena + off_l[w.name]);
@@ -268,7 +268,7 @@ bool one_pass_island(const std::string& name) {
 
 int run_gemm(Context& c, const PackedGemm& pg, int cls, const Act* a0, int a0_col, const Act* a1, int a1_col,
              const Epi& epi_in, const RowMap& map, cudaStream_t st, int forced_backend,
-             const __nv_bfloat16* seg_weights) {
+             const twin_t* seg_weights) {
   int backend = forced_backend;
   // STTS_FORCE_ISLAND=tok1,tok2: layers whose name contains a token run fp32-grade in bf16 mode too
   // (precision experiments; the shipped classification is the `cls` argument)
@@ -321,13 +321,13 @@ int run_gemm(Context& c, const PackedGemm& pg, int cls, const Act* a0, int a0_co
     if (backend == 1 && k.Ah == nullptr) return fail(c, -1, "run_gemm: bf16 twin missing");
   }
   g.W = (backend == 2) ? pg.Whl : pg.Wf;
-  g.Wh = pg.Wh;
   g.Wh_seg = (backend == 1) ? seg_weights : nullptr;
   if (seg_weights != nullptr && backend != 1) return fail(c, -1, "run_gemm: per-utterance weights need the bf16 backend");
   g.Wg = pg.Wg;
   g.Wl = pg.Wl;
   g.f16 = backend == 4;
-  g.acc_scale = f16 ? 1.0f / (pg.wscale * a0->gscale) : 1.f;
+  // 16-bit backends: the weights are stored as fp16(W * wscale), island operands as fp16(x * gscale)
+  g.acc_scale = f16 ? 1.0f / (pg.wscale * a0->gscale) : (backend == 1 ? 1.0f / pg.wscale : 1.f);
   g.Ktot = pg.Ktot;
   g.Npad = pg.Npad;
   g.epi = epi_in;
@@ -352,7 +352,7 @@ int run_gemm(Context& c, const PackedGemm& pg, int cls, const Act* a0, int a0_co
   const bool bracket = prof_layer != nullptr && pg.name == prof_layer;
   if (bracket) { cudaStreamSynchronize(st); cudaProfilerStart(); }
   if (backend == 0) e = conv_gemm_simt(g, map, st);
-  else if (backend == 1 || backend == 4) e = conv_gemm_tc_bf16(g, map, st);   // 4: same kernel, fp16 operands
+  else if (backend == 1 || backend == 4) e = conv_gemm_tc_f16(g, map, st);   // 4: same kernel, fp16 operands
   else if (backend == 3) e = conv_gemm_tc_f16x3(g, map, st);
   else e = conv_gemm_tc_tf32x3(g, map, st);
   if (bracket) { cudaStreamSynchronize(st); cudaProfilerStop(); }
@@ -371,7 +371,7 @@ struct Stage {
   Stage(Context& ctx, cudaStream_t s) : c(ctx), st(s), twins(ctx.precision == 1) {}
   Act& A(const char* n) { return c.act[n]; }
   template <typename T> T* R(const char* n) { return reinterpret_cast<T*>(c.raw[n]); }
-  __nv_bfloat16* tw(const Act& a) const { return twins ? a.h : nullptr; }
+  twin_t* tw(const Act& a) const { return twins ? a.h : nullptr; }
   Epi epi(int kind, const Act& dst, int col0) const {
     Epi e;
     std::memset(&e, 0, sizeof(e));
@@ -614,7 +614,7 @@ int run_generator_core(Context& c, const float* d_style, const float* d_noise, c
     if (one_pass_island("gen.amp_prior")) e.outl = nullptr;      // residual twins only for three-pass consumers
     if (one_pass_island("gen.phase_prior")) e.outl2 = nullptr;
     e.seg_start = c.L4.d_seg_start;
-    // bf16 mode: fp16 split operand (75 samples per row padded to 128 columns) -> the "stft16" pack
+    // bf16 mode: fp16 split operand = explicit frames written by the source kernel -> the "stft16" pack
     STTS_RET(run_gemm(c, c.gemm[S.twins ? "stft16" : "stft"], GC_ISLAND, &src, 0, nullptr, 0, e, map, st));
   }
   return run_generator_tail(c, d_style, d_audio, d_logamp, d_phase, st);
@@ -657,7 +657,7 @@ int run_generator_tail(Context& c, const float* d_style, float* d_audio, float* 
       // leaves per-(tile, quarter) column sums of squares; GRN's per-utterance channel scale is folded
       // into a per-utterance copy of the pw2 weights, its beta into the pw2 bias (prepack).
       float* colss = S.R<float>("COLSS");
-      __nv_bfloat16* wu = S.R<__nv_bfloat16>("WGRN");
+      twin_t* wu = S.R<twin_t>("WGRN");
       Epi e = S.epi(EPI_SILU, h, 0);
       e.out = nullptr;
       e.colss = colss; e.colss_ld = 1536;

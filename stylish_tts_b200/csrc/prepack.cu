@@ -53,7 +53,8 @@ struct Builder {
   std::vector<int> row_k;
   void init(int n, int nk, const int* t, const int* p, const int* cp) {
     N = n;
-    Npad = (n + 127) / 128 * 128;
+    // weight rows padded so that the 256-column tile (BN = 256) never reads past the matrix
+    Npad = n > 128 ? (n + 255) / 256 * 256 : 128;
     n_kseg = nk;
     Ktot = 0;
     for (int s = 0; s < nk; ++s) { taps[s] = t[s]; pad[s] = p[s]; cin_pad[s] = cp[s]; Ktot += t[s] * cp[s]; }
@@ -83,7 +84,6 @@ struct Builder {
     for (int s = 0; s < 2; ++s) { p.taps[s] = taps[s]; p.pad[s] = pad[s]; p.cin_pad[s] = cin_pad[s]; }
     const size_t n = (size_t)Npad * Ktot;
     std::vector<float> hl(2 * n);
-    std::vector<uint16_t> bf(n);
     std::vector<__half> hg(n), hlo(n);
     // fp16 split of W * wscale, wscale the power of two that puts max |W| into [2^13, 2^14): the
     // residuals of all but vanishing weights stay normal fp16 numbers (x = g + l to ~2^-22)
@@ -97,14 +97,12 @@ struct Builder {
       const float hi = trunc_tf32(W[i]);
       hl[i] = hi;
       hl[n + i] = trunc_tf32(W[i] - hi);
-      bf[i] = f2bf(W[i]);
       const float ws = W[i] * wscale;
       hg[i] = __float2half_rn(ws);
       hlo[i] = __float2half_rn(ws - __half2float(hg[i]));
     }
     p.Wf = dev_upload(c, W.data(), n);
     p.Whl = dev_upload(c, hl.data(), 2 * n);
-    p.Wh = reinterpret_cast<__nv_bfloat16*>(dev_upload(c, bf.data(), n));
     p.Wg = reinterpret_cast<__half*>(dev_upload(c, reinterpret_cast<const uint16_t*>(hg.data()), n));
     p.Wl = reinterpret_cast<__half*>(dev_upload(c, reinterpret_cast<const uint16_t*>(hlo.data()), n));
     p.bias = dev_upload(c, bias.data(), (size_t)Npad);
@@ -117,7 +115,7 @@ int pad64(int c) { return (c + 63) / 64 * 64; }
 }  // namespace
 
 void free_pack(PackedGemm& p) {
-  cudaFree(p.Wf); cudaFree(p.Whl); cudaFree(p.Wh); cudaFree(p.Wg); cudaFree(p.Wl); cudaFree(p.bias);
+  cudaFree(p.Wf); cudaFree(p.Whl); cudaFree(p.Wg); cudaFree(p.Wl); cudaFree(p.bias);
   p = PackedGemm();
 }
 
@@ -648,23 +646,23 @@ int finalize_weights(Context& c) {
           default: *c_out = s0; *s_out = -c0; break;
         }
       };
-      // forward: rows (re_k, im_k) interleaved; K = 16 hop-taps x 75 samples, each tap padded to 96
-      // columns for the fp32 / tf32 operand ("stft") and to 128 for the 16-bit operand ("stft16": one
-      // 128-byte swizzle row holds 64 fp16 values, so a tap must be a multiple of 64 columns)
-      for (int cpad : {96, 128}) {
+      // forward: rows (re_k, im_k) interleaved.  "stft" (fp32 / tf32 operand): K = 16 hop-taps x 75
+      // samples, each tap padded to 96 columns of the hop-row buffer.  "stft16" (fp16 split operand, bf16
+      // mode): the source kernel writes explicit frames [row, 1216], so K = 1200 window taps (+16 pad).
+      for (int variant = 0; variant < 2; ++variant) {
         Builder b;
-        const int t[2] = {16, 0}, pd[2] = {0, 0}, cp[2] = {cpad, 0};
+        const int t[2] = {variant == 0 ? 16 : 1, 0}, pd[2] = {0, 0}, cp[2] = {variant == 0 ? 96 : 1216, 0};
         b.init(2050, 1, t, pd, cp);
         for (int k = 0; k <= 1024; ++k)
           for (int n = 0; n < 1200; ++n) {
-            const int j = n / 75, cc = n % 75;
+            const int col = variant == 0 ? (n / 75) * 96 + n % 75 : n;
             double ca, sa;
             cs(k, 424 + n, &ca, &sa);
-            b.W[(size_t)(2 * k) * b.Ktot + j * cpad + cc] = (float)(win[n] * ca);
-            b.W[(size_t)(2 * k + 1) * b.Ktot + j * cpad + cc] = (sa == 0.0) ? 0.f : (float)(-win[n] * sa);
+            b.W[(size_t)(2 * k) * b.Ktot + col] = (float)(win[n] * ca);
+            b.W[(size_t)(2 * k + 1) * b.Ktot + col] = (sa == 0.0) ? 0.f : (float)(-win[n] * sa);
           }
         b.k_real = 1200;
-        c.gemm[cpad == 96 ? "stft" : "stft16"] = b.upload(c);
+        c.gemm[variant == 0 ? "stft" : "stft16"] = b.upload(c);
       }
       {  // inverse: irfft (1/N, Hermitian doubling, imag of DC / Nyquist ignored) x window
         Builder b;

@@ -132,8 +132,22 @@ __global__ void __launch_bounds__(256) pcph_source_kernel(const float* __restric
     }
     val += 0.01f * noise[dense_base + t];
     src[(size_t)(s0 + h + 8) * ld + c] = val;
-    if (srcg != nullptr)   // fp16 split twins of the STFT operand (pre-scaled: |val| < ~5)
-      f16_split(val * gscale, srcg + (size_t)(s0 + h + 8) * ldg + c, srcl + (size_t)(s0 + h + 8) * ldg + c);
+    if (srcg != nullptr) {
+      // fp16 split twins of the STFT operand, written as explicit frames (im2col): frame m of the
+      // utterance holds window tap n = 75 j + c <- hop m + j - 8, so this sample lands in the 16 frames
+      // m = h + 8 - j.  K = 1200 (+16 pad) instead of 16 taps x 128 padded columns: 41 % fewer MMAs.
+      __half g, l;
+      f16_split(val * gscale, &g, &l);                   // pre-scaled: |val| < ~5
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const int m = h + 8 - j;
+        if (m >= 0 && m < len) {
+          const size_t o = (size_t)(s0 + m) * ldg + j * kHop + c;
+          srcg[o] = g;
+          srcl[o] = l;
+        }
+      }
+    }
     if (dense_out != nullptr && interior) dense_out[dense_base + t] = val;
   }
 }

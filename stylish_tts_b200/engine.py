@@ -9,7 +9,9 @@ import torch
 
 from . import _lib
 
-PRECISIONS = {"fp32": 0, "bf16": 1, "tf32x3": 2}
+# "f16": one-pass tensor-core GEMMs on IEEE fp16 operand twins, fp32 accumulate (north-star "bf16 mode":
+# same tcgen05 kind::f16 rate as bf16, 8x finer rounding; "bf16" is kept as an alias of the same mode).
+PRECISIONS = {"fp32": 0, "f16": 1, "bf16": 1, "tf32x3": 2}
 
 
 class SttsError(RuntimeError):

@@ -66,5 +66,5 @@ def test_tc_tf32x3(case):
 
 
 @pytest.mark.parametrize("case", CASES)
-def test_tc_bf16(case):
-    assert _run("bf16", case) <= 1.5e-2
+def test_tc_f16(case):
+    assert _run("f16", case) <= 2e-3      # one pass, fp16 operands (2^-12 rounding), fp32 accumulate

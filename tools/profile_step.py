@@ -13,7 +13,7 @@ from stylish_tts_b200.config import ModelConfig  # noqa: E402
 from stylish_tts_b200.modules import build_model  # noqa: E402
 from stylish_tts_b200.synth import Synthesizer  # noqa: E402
 
-prec = sys.argv[1] if len(sys.argv) > 1 else "bf16"
+prec = sys.argv[1] if len(sys.argv) > 1 else "f16"
 batch = int(sys.argv[2]) if len(sys.argv) > 2 else 32
 sds = fixture.fixture_nets(fixture.load_manifest(), seed=0)
 nets = build_model(ModelConfig())

@@ -15,7 +15,7 @@ sds = fixture.fixture_nets(fixture.load_manifest(), seed=0)
 nets = build_model(ModelConfig())
 for k, m in nets.items():
     m.load_state_dict(sds[k])
-syn = Synthesizer(nets, device="cuda:0", precision="bf16")
+syn = Synthesizer(nets, device="cuda:0", precision="f16")
 tokens, durs, frames = workload(0)
 dev = "cuda:0"
 B = len(tokens); T = [int(t.numel()) for t in tokens]; Tmax = max(T)
