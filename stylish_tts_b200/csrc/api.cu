@@ -231,7 +231,7 @@ int stts_test_conv(stts_ctx* ctx, int backend, const float* d_x, int ldx, int ci
   a.f = const_cast<float*>(d_x);
   a.ld = ldx;
   a.rows = c.L4.R;
-  // bf16 backend: build a temporary twin of the operand
+  // 16-bit backend: build a temporary twin of the operand
   twin_t* twin = nullptr;
   if (backend == 1) {
     if (cudaMalloc(&twin, (size_t)c.L4.R * ldx * 2) != cudaSuccess) { free_pack(pg); return fail(c, -5, "twin alloc"); }

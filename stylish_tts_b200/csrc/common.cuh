@@ -1,7 +1,7 @@
 // Shared declarations for the sm_100a synthesis kernels.
 //
 // Activation layout (DESIGN.md "Data layout in HBM"): every frame-rate tensor is a packed,
-// time-major, channels-last matrix [R, ld] of fp32 (optionally with a bf16 twin used as the
+// time-major, channels-last matrix [R, ld] of fp32 (optionally with a 16-bit twin used as the
 // tensor-core operand).  Utterances ("segments") are stacked along the row axis; every segment
 // starts on a multiple of TILE_M = 128 rows and is followed by >= GUARD = 16 rows that are
 // never written and therefore stay zero.  A conv1d over time is then a row-shifted implicit
@@ -329,7 +329,7 @@ struct EpiPair {
       if constexpr (KIND == EPI_GATE) {
         const float a = a0 + b0 + g0, b = a1 + b1 + g1;
         const float y = th(a) * dv(1.f, 1.f + ex(-b));
-        e.out[(size_t)r * e.ldo + e.col0 + c] = y;
+        if (e.out != nullptr) e.out[(size_t)r * e.ldo + e.col0 + c] = y;
         if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = to_twin(y);
       } else if constexpr (KIND == EPI_COUPLE) {
         const float m = a0 + b0, logs = a1 + b1;
@@ -383,7 +383,7 @@ struct ConvGemm {
   const __half* Wg;               // fp16(W * wscale)                       (f16 / f16x3 modes)
   const __half* Wl;               // fp16(W * wscale - Wg)                  (f16x3 mode)
   float acc_scale;                // accumulators are multiplied by this before the epilogue (1 / wscale / a-scale)
-  int f16;                        // 16-bit operands are the fp16 twins (Ag, Al, Wg, Wl) instead of the bf16 ones
+  int f16;                        // one-pass GEMM on the island twins (Ag) instead of the body twins (Ah)
   int Ktot;                       // sum taps*cin_pad
   int Npad;                       // multiple of 128
   Epi epi;

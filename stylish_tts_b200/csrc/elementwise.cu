@@ -140,7 +140,7 @@ __global__ void __launch_bounds__(256) adain_act_kernel(const float* __restrict_
     float b = ga1 * ((v.y - mu.y) * rs.y) + be1;
     a = a > 0.f ? a : a * slope;
     b = b > 0.f ? b : b * slope;
-    *reinterpret_cast<float2*>(y + r * ldy + c) = make_float2(a, b);
+    if (y != nullptr) *reinterpret_cast<float2*>(y + r * ldy + c) = make_float2(a, b);
     if (yh != nullptr) *reinterpret_cast<twin2_t*>(yh + r * ldyh + c) = to_twin2(a, b);
   }
 }
@@ -456,7 +456,7 @@ __global__ void __launch_bounds__(256) dwconv_adaln_kernel(const float* __restri
       const float v0 = (1.f + g.x) * ((a0[o] - m[o]) * rs) + be.x;
       const float v1 = (1.f + g.y) * ((a1[o] - m[o]) * rs) + be.y;
       const size_t r = (size_t)r0 + o;
-      *reinterpret_cast<float2*>(y + r * ldy + c) = make_float2(v0, v1);
+      if (y != nullptr) *reinterpret_cast<float2*>(y + r * ldy + c) = make_float2(v0, v1);
       if (yh != nullptr) *reinterpret_cast<twin2_t*>(yh + r * ldyh + c) = to_twin2(v0, v1);
     }
   }
@@ -601,7 +601,7 @@ cudaError_t grn_scale_partials(const float* colss, int ld, int C, const RowMap& 
   return cudaGetLastError();
 }
 
-// Per-utterance pw2 weights with the GRN scale folded in: Wu[u, n, k] = bf16(W[n, k] * scale[u, k])
+// Per-utterance pw2 weights with the GRN scale folded in: Wu[u, n, k] = fp16(W[n, k] * scale[u, k])
 // (pwconv2(x * s + beta) = (W diag(s)) x + W beta: the W beta term is added to the bias at prepack).
 __global__ void __launch_bounds__(256) grn_weights_kernel(const float* __restrict__ W, int N, int K,
                                                           const float* __restrict__ scale,

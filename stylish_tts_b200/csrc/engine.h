@@ -32,7 +32,7 @@ struct PackedGemm {
   double k_real = 0;              // un-padded K (algorithmic FLOPs = 2 * rows * N * k_real)
 };
 
-struct Act {          // an activation buffer: fp32 + optional bf16 twin, same ld
+struct Act {          // an activation buffer: fp32 + optional 16-bit twin, same ld
   float* f = nullptr;
   twin_t* h = nullptr;
   __half* g = nullptr;          // fp16 split twins g = fp16(s x), l = fp16(s x - g): operands of the
@@ -111,7 +111,7 @@ void build_layout(Layout& L, int n_seg, const int* len);
 int set_layout(Context& c, int n_seg, const int* len_f, const int* len_f4);
 int run_gemm(Context& c, const PackedGemm& pg, int cls, const Act* a0, int a0_col, const Act* a1, int a1_col,
              const Epi& epi, const RowMap& map, cudaStream_t st, int forced_backend = -1,
-             const twin_t* seg_weights = nullptr);   // per-utterance bf16 weights [n_seg * Npad, Ktot]
+             const twin_t* seg_weights = nullptr);   // per-utterance fp16 weights [n_seg * Npad, Ktot]
 int run_pe_towers(Context& c, const float* d_x, const float* d_style, float* d_pitch, float* d_energy, cudaStream_t st);
 int run_decoder_core(Context& c, const float* d_style, cudaStream_t st);
 int run_decoder(Context& c, const float* d_asr, const float* d_f0, const float* d_n, const float* d_style, float* d_out,

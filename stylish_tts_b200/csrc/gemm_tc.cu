@@ -6,7 +6,7 @@
 //   warps 2..5  : operand converter during the main loop (fp32 mode only) and epilogue
 //                 (tcgen05.ld 32x32b -> registers -> fused epilogue -> global)
 // Two arithmetic modes:
-//   MODE_F16   : kind::f16, bf16 operands (bf16 twins of the activations), fp32 accumulate.
+//   MODE_F16   : kind::f16, fp16 operands (16-bit twins of the activations), fp32 accumulate, one pass.
 //   MODE_TF32X3 : kind::tf32 with error-compensated operand splitting, x = hi + lo with hi the
 //                 tf32 truncation of x: acc += hi*hi' + hi*lo' + lo*hi'  (~2^-21 relative, i.e.
 //                 fp32-grade).  The activation split is done in shared memory
@@ -147,7 +147,7 @@ __device__ __forceinline__ float rna_tf32(float x) {
 // the three-pass fp16 split (hi*hi + hi*lo + lo*hi, fp32-grade), MODE_TF32X3 the tf32 split on fp32 operands
 enum { MODE_F16 = 0, MODE_TF32X3 = 1, MODE_F16X3 = 2 };
 
-// OCC = 2 (bf16 mode, BN = 128 only): half the pipeline depth so that two CTAs share an SM (2 x 97 KB
+// OCC = 2 (16-bit mode, BN = 128 only): half the pipeline depth so that two CTAs share an SM (2 x 97 KB
 // shared memory, 2 x 128 TMEM columns, 2 x 320 threads x <= 96 registers): the epilogue of one CTA
 // overlaps the TMA / MMA main loop of the other -- pays for the short-K GEMMs, whose tiles spend as
 // long in the epilogue as in the main loop.
@@ -157,7 +157,7 @@ struct Cfg {
   static constexpr bool kSplit = (MODE != MODE_F16);     // hi / lo operand pairs, 3 MMAs per k-step
   static constexpr int kElem = kTF32 ? 4 : 2;
   static constexpr int kBK = 128 / kElem;                 // elements per 128-byte swizzle row: 32 / 64
-  static constexpr int kUmmaK = 32 / kElem;               // 8 (tf32) / 16 (bf16)
+  static constexpr int kUmmaK = 32 / kElem;               // 8 (tf32) / 16 (fp16)
   static constexpr int kATile = 128 * 128;                // bytes
   static constexpr int kBTile = BN * 128;                 // bytes
   static constexpr int kStageBytes = kSplit ? (2 * kATile + 2 * kBTile) : (kATile + kBTile);
@@ -486,7 +486,7 @@ cudaError_t launch_one(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
   return cudaGetLastError();
 }
 
-// STTS_OCC2=<n>: bf16-mode GEMMs with at most n K chunks (64 columns each) run as BN = 128, two CTAs
+// STTS_OCC2=<n>: 16-bit-mode GEMMs with at most n K chunks (64 columns each) run as BN = 128, two CTAs
 // per SM (-1 = never).
 int occ2_max_chunks() {
   static const int v = [] {

@@ -144,7 +144,7 @@ int set_layout(Context& c, int n_seg, const int* len_f, const int* len_f4) {
       {"GB_GEN", (size_t)B * std::max(c.J_gen, 1) * 4},                  {"GB_FLOW", (size_t)B * std::max(c.J_flow, 1) * 4},
       {"GB_PE", (size_t)B * std::max(c.J_pe, 1) * 4},                    {"STATUS", 256},
   };
-  if (use4) {   // GRN folded into pw2: sum-of-squares partials of the pw1 epilogue, per-utterance bf16 weights
+  if (use4) {   // GRN folded into pw2: sum-of-squares partials of the pw1 epilogue, per-utterance fp16 weights
     raws.push_back({"COLSS", (size_t)(R4 / 128) * 4 * 1536 * 4});
     raws.push_back({"WGRN", (size_t)B * 512 * 1536 * 2});
   }
@@ -246,12 +246,11 @@ int set_layout(Context& c, int n_seg, const int* len_f, const int* len_f4) {
 
 // ----------------------------------------------------------------------------- GEMM dispatch
 namespace {
-// Islands that run as ONE fp16 pass in bf16 mode: the prior convs, the two output heads and the
-// inverse DFT.  fp16 operands round at 2^-12 (bf16: 2^-9); measured on the golden cases the bf16-mode
-// waveform error is unchanged against three-pass f16x3 (max 1.54e-3 vs 1.47e-3, body bf16 rounding
-// dominates) at a third of the tensor time.  The forward STFT stays three-pass:
-// its phase output is ill-conditioned in the low-magnitude bins.  STTS_ISLAND_1PASS (comma-separated
-// name fragments, "none" = empty) overrides the list for experiments.
+// Islands that run as ONE fp16 pass in 16-bit mode: the prior convs, the two output heads and the
+// inverse DFT (fp16 twins, 2^-12 rounding).  Measured on the golden cases the waveform error does not
+// change against three-pass f16x3 at a third of the tensor time.  The forward
+// STFT stays three-pass: its phase output is ill-conditioned in the low-magnitude bins.
+// STTS_ISLAND_1PASS (comma-separated name fragments, "none" = empty) overrides the list for experiments.
 bool one_pass_island(const std::string& name) {
   static const char* env = std::getenv("STTS_ISLAND_1PASS");
   const std::string toks = env != nullptr ? std::string(env) : std::string("gen.amp_head,gen.phase_head,istft,gen.amp_prior,gen.phase_prior");
@@ -270,7 +269,7 @@ int run_gemm(Context& c, const PackedGemm& pg, int cls, const Act* a0, int a0_co
              const Epi& epi_in, const RowMap& map, cudaStream_t st, int forced_backend,
              const twin_t* seg_weights) {
   int backend = forced_backend;
-  // STTS_FORCE_ISLAND=tok1,tok2: layers whose name contains a token run fp32-grade in bf16 mode too
+  // STTS_FORCE_ISLAND=tok1,tok2: layers whose name contains a token run fp32-grade in 16-bit mode too
   // (precision experiments; the shipped classification is the `cls` argument)
   static const char* force_island = std::getenv("STTS_FORCE_ISLAND");
   if (force_island != nullptr && cls == GC_BODY) {
@@ -287,7 +286,7 @@ int run_gemm(Context& c, const PackedGemm& pg, int cls, const Act* a0, int a0_co
     if (c.precision == 0) backend = 0;
     else if (c.precision == 1) backend = (cls == GC_ISLAND) ? 2 : 1;
     else backend = 2;
-    // bf16 mode: an island whose operands carry fp16 split twins runs as f16x3 (g*g + g*l + l*g on
+    // 16-bit mode: an island whose operands carry fp16 split twins runs as f16x3 (g*g + g*l + l*g on
     // kind::f16 at the bf16 rate, ~2^-22 relative: fp32-grade at half the tensor time of tf32x3), or
     // as ONE fp16 pass (g*g, 2^-12 operand rounding, 8x finer than bf16) for the layers named in
     // STTS_ISLAND_1PASS / the built-in list
@@ -318,11 +317,11 @@ int run_gemm(Context& c, const PackedGemm& pg, int cls, const Act* a0, int a0_co
     if (cols[s] + k.cin_pad > (f16 ? as[s]->ldg : as[s]->ld))
       return fail(c, -2, "run_gemm: K slice exceeds the operand row");
     if (f16 && as[s]->gscale != as[0]->gscale) return fail(c, -2, "run_gemm: K segments with different fp16 pre-scales");
-    if (backend == 1 && k.Ah == nullptr) return fail(c, -1, "run_gemm: bf16 twin missing");
+    if (backend == 1 && k.Ah == nullptr) return fail(c, -1, "run_gemm: 16-bit twin missing");
   }
   g.W = (backend == 2) ? pg.Whl : pg.Wf;
   g.Wh_seg = (backend == 1) ? seg_weights : nullptr;
-  if (seg_weights != nullptr && backend != 1) return fail(c, -1, "run_gemm: per-utterance weights need the bf16 backend");
+  if (seg_weights != nullptr && backend != 1) return fail(c, -1, "run_gemm: per-utterance weights need the 16-bit backend");
   g.Wg = pg.Wg;
   g.Wl = pg.Wl;
   g.f16 = backend == 4;
@@ -398,7 +397,8 @@ int ada_block(Stage& S, const std::string& name, const Act& x, int cin, int cout
   double* stats = S.R<double>("STATS");
   STTS_CK(colstats(x.f, x.ld, cin, map, 0, 1e-5f, stats, mean, rstd, S.st));
   c.launches++;
-  STTS_CK(adain_act(x.f, x.ld, cin, map, mean, rstd, gb + c.fc_off[name + ".norm1"], ldgb, 0.2f, act1.f, act1.ld,
+  // 16-bit mode: the activations are pure GEMM operands, only their twin is read (no fp32 master store)
+  STTS_CK(adain_act(x.f, x.ld, cin, map, mean, rstd, gb + c.fc_off[name + ".norm1"], ldgb, 0.2f, S.twins ? nullptr : act1.f, act1.ld,
                     S.tw(act1), act1.ld, S.st));
   {
     Epi e = S.epi(EPI_BIAS, y1, 0);
@@ -407,7 +407,7 @@ int ada_block(Stage& S, const std::string& name, const Act& x, int cin, int cout
   }
   STTS_CK(colstats(y1.f, y1.ld, cout, map, 0, 1e-5f, stats, mean, rstd, S.st));
   c.launches++;
-  STTS_CK(adain_act(y1.f, y1.ld, cout, map, mean, rstd, gb + c.fc_off[name + ".norm2"], ldgb, 0.2f, act2.f, act2.ld,
+  STTS_CK(adain_act(y1.f, y1.ld, cout, map, mean, rstd, gb + c.fc_off[name + ".norm2"], ldgb, 0.2f, S.twins ? nullptr : act2.f, act2.ld,
                     S.tw(act2), act2.ld, S.st));
   {
     Epi e = S.epi(EPI_RES_SCALE, dst, dst_col);
@@ -529,6 +529,7 @@ int run_prior_flow_core(Context& c, const Act& x, const float* d_style, cudaStre
     for (int l = 0; l < 4; ++l) {
       {  // acts = tanh . sigmoid (in_layer(x) + g_l)
         Epi e = S.epi(EPI_GATE, acts, 0);
+        if (S.twins) e.out = nullptr;          // only the twin of the gated activations is read (res/skip GEMM)
         e.segvec = gi + l * 256;
         e.ldseg = c.J_flow;
         STTS_RET(run_gemm(c, c.gemm[nm + ".in" + std::to_string(l)], GC_BODY, &wh, 0, nullptr, 0, e, map, st));
@@ -614,7 +615,7 @@ int run_generator_core(Context& c, const float* d_style, const float* d_noise, c
     if (one_pass_island("gen.amp_prior")) e.outl = nullptr;      // residual twins only for three-pass consumers
     if (one_pass_island("gen.phase_prior")) e.outl2 = nullptr;
     e.seg_start = c.L4.d_seg_start;
-    // bf16 mode: fp16 split operand = explicit frames written by the source kernel -> the "stft16" pack
+    // 16-bit mode: fp16 split operand = explicit frames written by the source kernel -> the "stft16" pack
     STTS_RET(run_gemm(c, c.gemm[S.twins ? "stft16" : "stft"], GC_ISLAND, &src, 0, nullptr, 0, e, map, st));
   }
   return run_generator_tail(c, d_style, d_audio, d_logamp, d_phase, st);
@@ -633,9 +634,8 @@ int run_generator_tail(Context& c, const float* d_style, float* d_audio, float* 
   float* gb = S.R<float>("GB_GEN");
   (void)d_style;
   {  // amp / phase prior convs (k7) into the concat buffer   (generator.py:412-413)
-    // island class: their operands are the raw |X| / wrapped phase of the source, where bf16 operand
-    // rounding (step 1.6e-2 rad near +-pi) is the largest single contributor to the bf16-mode
-    // waveform error (measured: max over the golden cases 2.46e-3 -> 1.64e-3)
+    // island class: their operands are the raw |X| / wrapped phase of the source (fp16 twins written
+    // by the STFT epilogue)
     Epi e = S.epi(EPI_BIAS, catp, 512);
     if (one_pass_island("gen.amp_head")) e.outl = nullptr;
     STTS_RET(run_gemm(c, c.gemm["gen.amp_prior"], GC_ISLAND, &hs, 0, nullptr, 0, e, map, st));
@@ -651,9 +651,9 @@ int run_generator_tail(Context& c, const float* d_style, float* d_audio, float* 
   for (int i = 0; i < 4; ++i) {  // ConvNeXt blocks (generator.py:469-485)
     const std::string nm = "gen.cnx" + std::to_string(i);
     STTS_CK(dwconv_adaln(xg.f, xg.ld, map, c.vec_len[nm + ".dw_k"], c.vec[nm + ".dw_w"], c.vec[nm + ".dw_b"],
-                         gb + c.fc_off[nm + ".norm"], c.J_gen, 1e-6f, xgn.f, xgn.ld, S.tw(xgn), xgn.ld, st));
+                         gb + c.fc_off[nm + ".norm"], c.J_gen, 1e-6f, S.twins ? nullptr : xgn.f, xgn.ld, S.tw(xgn), xgn.ld, st));
     if (S.twins) {
-      // bf16 mode: GRN without touching H again.  The pw1 epilogue keeps only the bf16 twin of H and
+      // 16-bit mode: GRN without touching H again.  The pw1 epilogue keeps only the 16-bit twin of H and
       // leaves per-(tile, quarter) column sums of squares; GRN's per-utterance channel scale is folded
       // into a per-utterance copy of the pw2 weights, its beta into the pw2 bias (prepack).
       float* colss = S.R<float>("COLSS");
@@ -694,7 +694,7 @@ int run_generator_tail(Context& c, const float* d_style, float* d_audio, float* 
   STTS_CK(adaln2(xg.f, xg.ld, map, gb + c.fc_off["gen.amp_norm"], gb + c.fc_off["gen.phase_norm"], c.J_gen, 1e-5f,
                  S.twins ? nullptr : ampn.f, S.twins ? nullptr : phn.f, ampn.ld, S.twins ? ampn.g : nullptr,
                  S.twins ? phn.g : nullptr, ampn.ld, one_pass_island("gen.amp_head") ? nullptr : ampn.l,
-                 one_pass_island("gen.phase_head") ? nullptr : phn.l, st));   // bf16 mode: only what the heads read
+                 one_pass_island("gen.phase_head") ? nullptr : phn.l, st));   // 16-bit mode: only what the heads read
   {
     Epi e = S.epi(EPI_BIAS, la, 0);
     STTS_RET(run_gemm(c, c.gemm["gen.amp_head"], GC_ISLAND, &ampn, 0, &catp, 512, e, map, st));

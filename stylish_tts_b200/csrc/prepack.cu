@@ -3,7 +3,7 @@
 //     (ada_norm.py:158-163, decoder.py:35-45, pitch_energy_predictor.py:42-54) and legacy
 //     weight_g / weight_v (flow.py:40,52,60);  w = v * g / ||v||, norm over all dims but 0
 //   * re-lays every dense layer as a K-major matrix W[Npad, taps * cin_pad] in three formats
-//     (exact fp32, tf32 hi/lo split, bf16), with the row permutations the fused epilogues need
+//     (exact fp32, tf32 hi/lo split, fp16 hi/lo split of W * 2^s), with the row permutations the fused epilogues need
 //     (tanh/sigmoid pairs, mean/logstd pairs, re/im pairs) and zero padding of K and N
 //   * concatenates the Linear(style) layers of each stage into one matrix
 //   * builds the STFT / iSTFT contraction bases of TorchSTFT (generator.py:23-56)
@@ -587,7 +587,7 @@ int finalize_weights(Context& c) {
           b.rows(0, *w2, 0, 512, 0, 1536, 0, 1);
           b.set_bias(*b2, 0, 512, 0, 1);
           c.gemm[nm + ".pw2"] = b.upload(c);
-          // GRN folded into pw2 (bf16 mode): pw2(x * s + beta) = (W diag(s)) x + (W beta + bias)
+          // GRN folded into pw2 (16-bit mode): pw2(x * s + beta) = (W diag(s)) x + (W beta + bias)
           std::vector<float> bg(512);
           for (int n = 0; n < 512; ++n) {
             double acc = b2->data[n];
@@ -647,7 +647,7 @@ int finalize_weights(Context& c) {
         }
       };
       // forward: rows (re_k, im_k) interleaved.  "stft" (fp32 / tf32 operand): K = 16 hop-taps x 75
-      // samples, each tap padded to 96 columns of the hop-row buffer.  "stft16" (fp16 split operand, bf16
+      // samples, each tap padded to 96 columns of the hop-row buffer.  "stft16" (fp16 split operand, 16-bit
       // mode): the source kernel writes explicit frames [row, 1216], so K = 1200 window taps (+16 pad).
       for (int variant = 0; variant < 2; ++variant) {
         Builder b;
