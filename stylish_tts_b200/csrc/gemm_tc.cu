@@ -374,6 +374,192 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
   }
 }
 
+// ------------------------------------------------------------------ persistent one-pass fp16 GEMM, 128 x 256 tiles
+// One CTA per SM loops over output tiles (tile id = m_tile * n_tiles_n + n_tile, grid-stride).  The
+// TMA producer and the MMA issuer run ahead into the next tile while the 8 epilogue warps drain the
+// previous accumulator: TMEM holds two 256-column accumulators (512 columns), handed over with the
+// tmem_full / tmem_empty mbarrier pairs; the epilogue has its own transpose staging (the pipeline
+// stages are never idle).  For the short-K layers (flow K 640, pwconv1 K 512) a tile spends as long in
+// prologue + epilogue as in the main loop, so the overlap is worth up to 2x; long-K layers gain the
+// removed per-CTA prologue (barrier init, TMEM alloc, first-load latency) of the ~3 waves.
+struct PCfg {
+  static constexpr int kBN = 256;
+  static constexpr int kBK = 64, kUmmaK = 16;
+  static constexpr int kATile = 128 * 128, kBTile = kBN * 128;           // bytes
+  static constexpr int kStageBytes = kATile + kBTile;                    // 48 KB
+  static constexpr int kStages = 3;
+  static constexpr int kEpiWarps = 8;                                    // 4 lane quarters x 2 column halves
+  static constexpr int kThreads = 64 + 32 * kEpiWarps;                   // 320
+  static constexpr int kStagingBytes = kEpiWarps * 32 * kStgLd * 4;      // 67 584
+  static constexpr int kSmem = kStages * kStageBytes + kStagingBytes + 1024 + 256;
+  static constexpr uint32_t kIdesc = (1u << 4) | ((uint32_t)(kBN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);  // f16 x f16 -> f32
+};
+
+template <int KIND>
+__global__ void __launch_bounds__(PCfg::kThreads, 1)
+conv_gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant__ CUtensorMap mapA1,
+                               const __grid_constant__ CUtensorMap mapW, const TcParams p, const Epi epi,
+                               const RowMap map, const int n_tiles_n) {
+  using C = PCfg;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int total_tiles = map.n_tiles * n_tiles_n;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  float* staging = reinterpret_cast<float*>(smem + C::kStages * C::kStageBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::kStages * C::kStageBytes + C::kStagingBytes);
+  uint64_t* full = bars;                         // TMA -> MMA
+  uint64_t* empty = bars + C::kStages;           // MMA commit -> TMA
+  uint64_t* tmem_full = bars + 2 * C::kStages;   // MMA commit -> epilogue      [2]
+  uint64_t* tmem_empty = tmem_full + 2;          // epilogue -> MMA             [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < C::kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], C::kEpiWarps); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"(512u)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  auto stage_ptr = [&](int s) { return smem + (size_t)s * C::kStageBytes; };
+
+  if (warp == 0) {
+    // ------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const int tile = t / n_tiles_n, n0 = (t - tile * n_tiles_n) * C::kBN;
+        const int seg = map.tile_seg[tile];
+        if (seg < 0) continue;
+        const int m0 = tile * 128;
+        const int wrow = n0 + seg * p.w_seg_rows;
+        int ks = 0, tap = 0, cc = 0, kcol = 0;
+        for (int ch = 0; ch < p.n_chunks; ++ch) {
+          mbar_wait(&empty[stage], phase ^ 1, 11);
+          uint8_t* sp = stage_ptr(stage);
+          mbar_expect_tx(&full[stage], C::kStageBytes);
+          const CUtensorMap* ma = (ks == 0) ? &mapA0 : &mapA1;
+          tma_load_2d(sp, ma, &full[stage], p.col0[ks] + cc * C::kBK, m0 + tap - p.pad[ks]);
+          tma_load_2d(sp + C::kATile, &mapW, &full[stage], kcol, wrow);
+          kcol += C::kBK;
+          if (++cc == p.cin_chunks[ks]) { cc = 0; if (++tap == p.taps[ks]) { tap = 0; ++ks; } }
+          if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;                                  // local tile counter (accumulator buffer = it & 1)
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const int tile = t / n_tiles_n;
+        if (map.tile_seg[tile] < 0) continue;
+        const int buf = it & 1, use = it >> 1;
+        if (use > 0) mbar_wait(&tmem_empty[buf], (uint32_t)((use - 1) & 1), 12);   // epilogue drained this buffer
+        tc_fence_after();
+        const uint32_t acc = tmem_base + (uint32_t)(buf * C::kBN);
+        for (int ch = 0; ch < p.n_chunks; ++ch) {
+          mbar_wait(&full[stage], phase, 13);
+          tc_fence_after();
+          const uint32_t a = smem_u32(stage_ptr(stage)), b = a + C::kATile;
+#pragma unroll
+          for (int k = 0; k < C::kBK / C::kUmmaK; ++k)
+            tc_mma<false>(acc, make_sdesc(a + k * 32), make_sdesc(b + k * 32), C::kIdesc, (ch | k) != 0);
+          tc_commit(&empty[stage]);
+          if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+        }
+        tc_commit(&tmem_full[buf]);
+        ++it;
+      }
+    }
+  } else {
+    // ------------------------------------------------------------ epilogue (8 warps)
+    const int ew = warp - 2;                       // 0 .. 7
+    const int q = warp & 3;                        // TMEM lane quarter this warp may read (hardware rule)
+    const int half = ew >> 2;                      // column half: slabs {0, 64} + 128 * half
+    float* stg = staging + ew * (32 * kStgLd);
+    int it = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      const int tile = t / n_tiles_n, n0 = (t - tile * n_tiles_n) * C::kBN;
+      const int seg = map.tile_seg[tile];
+      if (seg < 0) continue;
+      const int nvalid = map.tile_nvalid[tile];
+      const int m0 = tile * 128;
+      const int buf = it & 1, use = it >> 1;
+      mbar_wait(&tmem_full[buf], (uint32_t)(use & 1), 14);
+      tc_fence_after();
+      const int row0 = m0 + q * 32;
+      int nrows = nvalid - q * 32;
+      nrows = nrows < 0 ? 0 : (nrows > 32 ? 32 : nrows);
+      const int seg_first = (epi.seg_start != nullptr) ? epi.seg_start[seg] : -1;
+#pragma unroll 1
+      for (int sl = 0; sl < 2; ++sl) {
+        const int c = half * 128 + sl * 64;
+        const bool live = n0 + c < epi.N;          // warp-uniform
+        if (live) {
+          float v[64];
+          tmem_ld64(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * C::kBN + c), v);
+          __syncwarp();                            // previous slab fully consumed
+#pragma unroll
+          for (int j = 0; j < 64; j += 2)
+            *reinterpret_cast<float2*>(stg + lane * kStgLd + j) = make_float2(v[j] * p.acc_scale, v[j + 1] * p.acc_scale);
+        }
+        if (sl == 1) {                             // last TMEM read of this tile: hand the accumulator back
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tmem_empty[buf]);
+        }
+        if (!live) continue;
+        __syncwarp();
+        EpiPair<KIND, true> ep;
+        ep.init(epi, seg, n0 + c + 2 * lane);
+        if constexpr (EpiPair<KIND, false>::kHasPre) {
+#pragma unroll 1
+          for (int rb = 0; rb < 32; rb += 16) {
+            float2 pre[16];
+#pragma unroll
+            for (int rr = 0; rr < 16; ++rr)
+              if (rb + rr < nrows) pre[rr] = ep.pre(epi, row0 + rb + rr);
+#pragma unroll
+            for (int rr = 0; rr < 16; ++rr) {
+              if (rb + rr < nrows) {
+                const float2 a = *reinterpret_cast<const float2*>(stg + (rb + rr) * kStgLd + 2 * lane);
+                ep.apply(epi, row0 + rb + rr, seg, seg_first, a.x, a.y, pre[rr]);
+              }
+            }
+          }
+        } else {
+#pragma unroll 8
+          for (int rr = 0; rr < nrows; ++rr) {
+            const float2 a = *reinterpret_cast<const float2*>(stg + rr * kStgLd + 2 * lane);
+            ep.apply(epi, row0 + rr, seg, seg_first, a.x, a.y, make_float2(0.f, 0.f));
+          }
+        }
+        ep.finish(epi, tile, q);
+      }
+      ++it;
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+  }
+}
+
 // ------------------------------------------------------------------ host: tensor maps
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -486,6 +672,58 @@ cudaError_t launch_one(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
   return cudaGetLastError();
 }
 
+template <int KIND>
+cudaError_t launch_persistent(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
+  using C = PCfg;
+  CUtensorMap mA[2], mW;
+  TcParams p{};
+  p.n_kseg = g.n_kseg;
+  p.n_chunks = 0;
+  for (int s = 0; s < 2; ++s) {
+    const KSeg& ks = g.seg[s < g.n_kseg ? s : 0];
+    const void* base = g.f16 ? (const void*)ks.Ag : (const void*)ks.Ah;
+    const int ld = g.f16 ? ks.ldag : ks.ldah;
+    if (base == nullptr) return cudaErrorInvalidValue;
+    if (!get_map(base, ks.rows, ld, 2, 128, &mA[s])) return cudaErrorNotSupported;
+    if (s < g.n_kseg) {
+      p.taps[s] = ks.taps;
+      p.pad[s] = ks.pad;
+      p.cin_chunks[s] = ks.cin_pad / C::kBK;
+      p.col0[s] = ks.colh0;
+      p.n_chunks += ks.taps * p.cin_chunks[s];
+    }
+  }
+  const bool per_seg = !g.f16 && g.Wh_seg != nullptr;
+  const void* w = per_seg ? (const void*)g.Wh_seg : (const void*)g.Wg;
+  if (w == nullptr) return cudaErrorInvalidValue;
+  if (!get_map(w, per_seg ? g.Npad * map.n_seg : g.Npad, g.Ktot, 2, C::kBN, &mW)) return cudaErrorNotSupported;
+  p.w_seg_rows = per_seg ? g.Npad : 0;
+  p.ab_fmt = 0u;
+  p.acc_scale = per_seg ? 1.f : g.acc_scale;
+  auto kern = conv_gemm_tc_persistent_kernel<KIND>;
+  static bool attr_done = false;
+  static int n_sm = 0;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmem);
+    if (e != cudaSuccess) return e;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+    attr_done = true;
+  }
+  const int n_tiles_n = (g.epi.N + C::kBN - 1) / C::kBN;
+  const int total = map.n_tiles * n_tiles_n;
+  const int grid = total < n_sm ? total : n_sm;
+  kern<<<grid, C::kThreads, C::kSmem, st>>>(mA[0], mA[1], mW, p, g.epi, map, n_tiles_n);
+  return cudaGetLastError();
+}
+
+// STTS_PERSISTENT=0 falls back to one CTA per tile for the wide one-pass GEMMs
+bool use_persistent() {
+  static const bool v = [] { const char* e = std::getenv("STTS_PERSISTENT"); return e == nullptr || e[0] != '0'; }();
+  return v;
+}
+
 // STTS_OCC2=<n>: 16-bit-mode GEMMs with at most n K chunks (64 columns each) run as BN = 128, two CTAs
 // per SM (-1 = never).
 int occ2_max_chunks() {
@@ -508,6 +746,14 @@ cudaError_t launch_bn(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
   // tiles per stage) use it for the wide STFT only.
   static const bool split256 = [] { const char* e = std::getenv("STTS_SPLIT_BN256"); return e == nullptr || e[0] != '0'; }();
   const bool wide = g.epi.N > 128 && g.Npad % 256 == 0;
+  if constexpr (MODE == MODE_F16) {
+    // persistent variant: measured faster for long-K, multi-column-tile layers (decoder convs -4 .. -17 %,
+    // pwconv2 -7 %, inverse DFT -11 %, output heads -5 %) and slower for the short-K / epilogue-bound ones
+    // (pwconv1 +54 %, flow res/skip +35 %: 8 instead of 16 epilogue warps), which keep one CTA per tile
+    int chunks = 0;
+    for (int s = 0; s < g.n_kseg; ++s) chunks += g.seg[s].taps * (g.seg[s].cin_pad / 64);
+    if (wide && use_persistent() && chunks >= 24 && g.epi.N >= 512) return launch_persistent<KIND>(g, map, st);
+  }
   if (MODE == MODE_F16 && wide) return launch_one<MODE, 256, KIND>(g, map, st);
   if (MODE != MODE_F16 && wide && split256 && g.epi.N >= 1024) return launch_one<MODE, 256, KIND>(g, map, st);
   return launch_one<MODE, 128, KIND>(g, map, st);
