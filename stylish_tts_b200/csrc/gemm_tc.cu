@@ -341,26 +341,31 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
       }
       __syncwarp();
       if constexpr (EpiPair<KIND, false>::kHasPre) {
-        // two batches of 16 rows: 16 independent row loads in flight per warp, registers bounded
+        // batches of RB rows: RB independent residual loads in flight per warp, registers bounded
+        // (576-thread CTAs of the 256-column tile have 113 registers per thread)
+        constexpr int RB = (BN == 256 || OCC == 2) ? 4 : 16;
 #pragma unroll 1
-        for (int rb = 0; rb < 32; rb += 16) {
-          float2 pre[16];
+        for (int rb = 0; rb < 32; rb += RB) {
+          float2 pre[RB];
 #pragma unroll
-          for (int rr = 0; rr < 16; ++rr)
+          for (int rr = 0; rr < RB; ++rr)
             if (rb + rr < nrows) pre[rr] = ep.pre(epi, row0 + rb + rr);
+          float2 av[RB];                               // staged accumulators read up front: the loads must
+#pragma unroll                                         // not be serialised behind the global stores of apply()
+          for (int rr = 0; rr < RB; ++rr) av[rr] = *reinterpret_cast<const float2*>(stg + (rb + rr) * kStgLd + 2 * lane);
 #pragma unroll
-          for (int rr = 0; rr < 16; ++rr) {
-            if (rb + rr < nrows) {
-              const float2 a = *reinterpret_cast<const float2*>(stg + (rb + rr) * kStgLd + 2 * lane);
-              ep.apply(epi, row0 + rb + rr, seg, seg_first, a.x, a.y, pre[rr]);
-            }
-          }
+          for (int rr = 0; rr < RB; ++rr)
+            if (rb + rr < nrows) ep.apply(epi, row0 + rb + rr, seg, seg_first, av[rr].x, av[rr].y, pre[rr]);
         }
       } else {
-#pragma unroll 8
-        for (int rr = 0; rr < nrows; ++rr) {
-          const float2 a = *reinterpret_cast<const float2*>(stg + rr * kStgLd + 2 * lane);
-          ep.apply(epi, row0 + rr, seg, seg_first, a.x, a.y, make_float2(0.f, 0.f));
+#pragma unroll 1
+        for (int rb = 0; rb < nrows; rb += 8) {        // 8 rows per batch: loads first, then the epilogue math + stores
+          float2 av[8];
+#pragma unroll
+          for (int rr = 0; rr < 8; ++rr) av[rr] = *reinterpret_cast<const float2*>(stg + (rb + rr) * kStgLd + 2 * lane);
+#pragma unroll
+          for (int rr = 0; rr < 8; ++rr)
+            if (rb + rr < nrows) ep.apply(epi, row0 + rb + rr, seg, seg_first, av[rr].x, av[rr].y, make_float2(0.f, 0.f));
         }
       }
       ep.finish(epi, tile, q);
@@ -532,19 +537,22 @@ conv_gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap mapA0, const 
 #pragma unroll
             for (int rr = 0; rr < 16; ++rr)
               if (rb + rr < nrows) pre[rr] = ep.pre(epi, row0 + rb + rr);
+            float2 av[16];
 #pragma unroll
-            for (int rr = 0; rr < 16; ++rr) {
-              if (rb + rr < nrows) {
-                const float2 a = *reinterpret_cast<const float2*>(stg + (rb + rr) * kStgLd + 2 * lane);
-                ep.apply(epi, row0 + rb + rr, seg, seg_first, a.x, a.y, pre[rr]);
-              }
-            }
+            for (int rr = 0; rr < 16; ++rr) av[rr] = *reinterpret_cast<const float2*>(stg + (rb + rr) * kStgLd + 2 * lane);
+#pragma unroll
+            for (int rr = 0; rr < 16; ++rr)
+              if (rb + rr < nrows) ep.apply(epi, row0 + rb + rr, seg, seg_first, av[rr].x, av[rr].y, pre[rr]);
           }
         } else {
-#pragma unroll 8
-          for (int rr = 0; rr < nrows; ++rr) {
-            const float2 a = *reinterpret_cast<const float2*>(stg + rr * kStgLd + 2 * lane);
-            ep.apply(epi, row0 + rr, seg, seg_first, a.x, a.y, make_float2(0.f, 0.f));
+#pragma unroll 1
+          for (int rb = 0; rb < nrows; rb += 8) {
+            float2 av[8];
+#pragma unroll
+            for (int rr = 0; rr < 8; ++rr) av[rr] = *reinterpret_cast<const float2*>(stg + (rb + rr) * kStgLd + 2 * lane);
+#pragma unroll
+            for (int rr = 0; rr < 8; ++rr)
+              if (rb + rr < nrows) ep.apply(epi, row0 + rb + rr, seg, seg_first, av[rr].x, av[rr].y, make_float2(0.f, 0.f));
           }
         }
         ep.finish(epi, tile, q);
@@ -752,7 +760,8 @@ cudaError_t launch_bn(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
     // (pwconv1 +54 %, flow res/skip +35 %: 8 instead of 16 epilogue warps), which keep one CTA per tile
     int chunks = 0;
     for (int s = 0; s < g.n_kseg; ++s) chunks += g.seg[s].taps * (g.seg[s].cin_pad / 64);
-    if (wide && use_persistent() && chunks >= 24 && g.epi.N >= 512) return launch_persistent<KIND>(g, map, st);
+    static const bool all = [] { const char* e = std::getenv("STTS_PERSISTENT"); return e != nullptr && e[0] == 'a'; }();
+    if (wide && use_persistent() && (all || (chunks >= 24 && g.epi.N >= 512))) return launch_persistent<KIND>(g, map, st);
   }
   if (MODE == MODE_F16 && wide) return launch_one<MODE, 256, KIND>(g, map, st);
   if (MODE != MODE_F16 && wide && split256 && g.epi.N >= 1024) return launch_one<MODE, 256, KIND>(g, map, st);
