@@ -164,6 +164,11 @@ int stts_speech_frames(stts_ctx* ctx, const float* d_enc_tok, const int32_t* d_c
 /* after a synchronised call: STTS_ERR_UNVOICED_MIN if any utterance hit the reference's error path */
 int stts_check_source_status(stts_ctx* ctx, void* stream);
 
+/* int16 PCM of n device samples: trunc(x * 32768), saturated -- replaces
+ * `np.multiply(outputs[0], 32768).astype(np.int16)` (train/test_onnx.py:79) so that the device -> host
+ * copy of a synthesised batch moves 2 bytes per sample.  d_pcm: int16 [n].                      */
+int stts_pcm16(stts_ctx* ctx, const float* d_audio, int64_t n, int16_t* d_pcm, void* stream);
+
 /* ---- test / profiling hooks -------------------------------------------------------------------
  * Raw conv-as-GEMM on caller buffers (packed [R, ld] layout of the current hop-75 layout):
  * Y[r, n] = bias[n] + sum_j sum_c X[r + j - pad, c] * W[n, c, j];  d_w is [N, cin, taps] fp32

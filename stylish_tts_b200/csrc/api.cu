@@ -219,6 +219,14 @@ int stts_check_source_status(stts_ctx* ctx, void* stream) {
   return STTS_OK;
 }
 
+int stts_pcm16(stts_ctx* ctx, const float* d_audio, int64_t n, int16_t* d_pcm, void* stream) {
+  if (!ctx || n < 0 || (n > 0 && (!d_audio || !d_pcm))) return STTS_ERR_BAD_ARG;
+  Context& c = ctx->c;
+  DeviceGuard g(c.device);
+  STTS_CK(pcm16(d_audio, d_pcm, (long long)n, S(stream)));
+  return STTS_OK;
+}
+
 int stts_test_conv(stts_ctx* ctx, int backend, const float* d_x, int ldx, int cin, int taps, int pad,
                    const float* h_w, const float* h_bias, int n_out, float* d_y, int ldy, void* stream) {
   if (!ctx || !d_x || !h_w || !d_y || backend < 0 || backend > 2) return STTS_ERR_BAD_ARG;

@@ -315,6 +315,10 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
         if (++stage == C::kStages) { stage = 0; phase ^= 1; }
       }
     }
+    if constexpr (!C::kTF32 && EpiPair<KIND, false>::kHasPre) {
+      const int pq = warp & 3, pc = ((warp - 2) >> 2) * 64;
+      if (pq * 32 + lane < nvalid) EpiPair<KIND, false>::prefetch_pre(epi, m0 + pq * 32 + lane, n0 + pc);
+    }
     mbar_wait(accum, 0, 5);
     tc_fence_after();
     // All TMA writes and all MMAs of this CTA have completed: the pipeline stages are free and are
@@ -568,6 +572,262 @@ conv_gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap mapA0, const 
   }
 }
 
+// ------------------------------------------------------------------ fused WaveNet layer (16-bit mode)
+// One launch per WN layer of the reversed flow (flow.py:63-88) instead of two GEMMs:
+//   acc1[128 x 256] = conv k5 (x16; 10 K chunks)                         -> TMEM columns [0, 256)
+//   acts            = tanh(acc1_even + b + g) * sigmoid(acc1_odd + b + g) -> shared memory, fp16, laid out
+//                     as the K-major 128B-swizzled A operand of the second contraction (never in HBM)
+//   acc2[128 x NRS] = acts * Wrs^T (2 K chunks, weights streamed through the same stage ring while the
+//                     gate epilogue runs)                                  -> TMEM columns [256, 256 + NRS)
+//   x += res, skip (+)= skip                                               (EPI_RESSKIP, coalesced)
+// The conv reads +-2 halo rows of neighbouring tiles, so the updated 16-bit twin of x goes to a second
+// buffer (ping-pong per layer); the fp32 master is only touched by the tile that owns the rows.
+// Read-modify-write epilogue of one 32-row x 64-column slab, lane-per-4-columns: lanes 0-15 cover the
+// 64 columns of one row with float4 accesses, lanes 16-31 the next row, so one warp instruction moves two
+// full 256-byte row segments.  dst / dsth point at (first row of the slab, first column of the slab).
+// (The lane-per-column-pair form with its per-row pointer arithmetic and null checks was issue-bound:
+// ncu counted ~67 instructions per row and warp, 52 % of the fused layer's tile time.)
+constexpr int kStgLd4 = 68;   // staging row stride in floats for the float4 form (16-byte aligned rows)
+template <bool HAS_PRE, bool HAS_TWIN>
+__device__ __forceinline__ void rmw_slab4(const float* __restrict__ stg, float* __restrict__ dst, int ld,
+                                          twin_t* __restrict__ dsth, int ldh, float4 bias, int nrows, int lane) {
+  const int sub = lane >> 4, c4 = (lane & 15) * 4;
+  float* p = dst + (size_t)sub * ld + c4;
+  twin_t* ph = HAS_TWIN ? dsth + (size_t)sub * ldh + c4 : nullptr;
+  const float* sp = stg + sub * kStgLd4 + c4;
+#pragma unroll 1
+  for (int rb = 0; rb < 32; rb += 16) {
+    float4 pre[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      pre[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (HAS_PRE && rb + 2 * i + sub < nrows) pre[i] = *reinterpret_cast<const float4*>(p + (size_t)(rb + 2 * i) * ld);
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      if (rb + 2 * i + sub < nrows) {
+        const float4 a = *reinterpret_cast<const float4*>(sp + (rb + 2 * i) * kStgLd4);
+        float4 y;
+        y.x = pre[i].x + (a.x + bias.x); y.y = pre[i].y + (a.y + bias.y);
+        y.z = pre[i].z + (a.z + bias.z); y.w = pre[i].w + (a.w + bias.w);
+        *reinterpret_cast<float4*>(p + (size_t)(rb + 2 * i) * ld) = y;
+        if constexpr (HAS_TWIN) {
+          const twin2_t t0 = to_twin2(y.x, y.y), t1 = to_twin2(y.z, y.w);
+          uint2 w;
+          w.x = *reinterpret_cast<const uint32_t*>(&t0);
+          w.y = *reinterpret_cast<const uint32_t*>(&t1);
+          *reinterpret_cast<uint2*>(ph + (size_t)(rb + 2 * i) * ldh) = w;
+        }
+      }
+    }
+  }
+}
+
+struct WnCfg {
+  static constexpr int kBK = 64, kUmmaK = 16;
+  static constexpr int kATile = 128 * 128, kBTile = 256 * 128;            // bytes
+  static constexpr int kStageBytes = kATile + kBTile;                     // 48 KB
+  static constexpr int kStages = 3;
+  static constexpr int kEpiWarps = 16;                                    // 4 lane quarters x 4 slabs of 64 columns
+  static constexpr int kThreads = 64 + 32 * kEpiWarps;                    // 576
+  static constexpr int kActsBytes = 2 * kATile;                           // gated activations: 2 K chunks
+  static constexpr int kSmem = kStages * kStageBytes + kActsBytes + 1024 /*gate constants*/ + 1024 /*align*/ + 256;
+  static_assert(kStages * kStageBytes >= kEpiWarps * 32 * kStgLd4 * 4, "staging must fit into the stage ring");
+};
+
+struct WnParams {
+  int col0;                    // first column of x16 (elements)
+  float scale_in, scale_rs;    // accumulator scales (power-of-two weight pre-scaling undone)
+  const float* bias_in;        // [256], (tanh, sigmoid) rows interleaved
+  const float* segvec; int ldseg;   // style conditioning g: [n_seg, ldseg], tanh half then sigmoid half
+};
+
+template <int NRS>
+__global__ void __launch_bounds__(WnCfg::kThreads, 1)
+wn_layer_fused_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUtensorMap mapWin,
+                      const __grid_constant__ CUtensorMap mapWrs, const WnParams p, const Epi epi, const RowMap map) {
+  using C = WnCfg;
+  constexpr int kInChunks = 10;      // 5 taps x 128 channels / 64
+  constexpr int kRsChunks = 2;       // 128 gated channels / 64
+  const int tile = blockIdx.x;
+  const int seg = map.tile_seg[tile];
+  if (seg < 0) return;
+  const int nvalid = map.tile_nvalid[tile];
+  const int m0 = tile * 128;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* acts = smem + C::kStages * C::kStageBytes;
+  float* gconst = reinterpret_cast<float*>(acts + C::kActsBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(acts + C::kActsBytes + 1024);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + C::kStages;
+  uint64_t* accum1 = bars + 2 * C::kStages;
+  uint64_t* acts_ready = accum1 + 1;
+  uint64_t* accum2 = accum1 + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum1 + 3);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < C::kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    mbar_init(accum1, 1);
+    mbar_init(acts_ready, C::kEpiWarps);
+    mbar_init(accum2, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"(512u)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  if (threadIdx.x >= 64 && threadIdx.x < 64 + 256) {   // gate constants per accumulator column: bias + style conditioning
+    const int n = threadIdx.x - 64;
+    gconst[n] = p.bias_in[n] + p.segvec[(size_t)seg * p.ldseg + ((n & 1) ? 128 : 0) + (n >> 1)];
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  auto stage_ptr = [&](int s) { return smem + (size_t)s * C::kStageBytes; };
+  constexpr uint32_t kIdescIn = (1u << 4) | ((uint32_t)(256 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+  constexpr uint32_t kIdescRs = (1u << 4) | ((uint32_t)(NRS >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+
+  if (warp == 0) {
+    // ------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int tap = 0, cc = 0;
+      for (int ch = 0; ch < kInChunks + kRsChunks; ++ch) {
+        mbar_wait(&empty[stage], phase ^ 1, 21);
+        uint8_t* sp = stage_ptr(stage);
+        if (ch < kInChunks) {
+          mbar_expect_tx(&full[stage], C::kStageBytes);
+          tma_load_2d(sp, &mapX, &full[stage], p.col0 + cc * C::kBK, m0 + tap - 2);
+          tma_load_2d(sp + C::kATile, &mapWin, &full[stage], ch * C::kBK, 0);
+          if (++cc == 2) { cc = 0; ++tap; }
+        } else {
+          mbar_expect_tx(&full[stage], NRS * 128);
+          tma_load_2d(sp + C::kATile, &mapWrs, &full[stage], (ch - kInChunks) * C::kBK, 0);
+        }
+        if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int ch = 0; ch < kInChunks; ++ch) {
+        mbar_wait(&full[stage], phase, 22);
+        tc_fence_after();
+        const uint32_t a = smem_u32(stage_ptr(stage)), b = a + C::kATile;
+#pragma unroll
+        for (int k = 0; k < C::kBK / C::kUmmaK; ++k)
+          tc_mma<false>(tmem_base, make_sdesc(a + k * 32), make_sdesc(b + k * 32), kIdescIn, (ch | k) != 0);
+        tc_commit(&empty[stage]);
+        if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+      }
+      tc_commit(accum1);
+      mbar_wait(acts_ready, 0, 23);
+      tc_fence_after();
+      for (int ch = 0; ch < kRsChunks; ++ch) {
+        mbar_wait(&full[stage], phase, 24);
+        tc_fence_after();
+        const uint32_t a = smem_u32(acts + ch * C::kATile), b = smem_u32(stage_ptr(stage)) + C::kATile;
+#pragma unroll
+        for (int k = 0; k < C::kBK / C::kUmmaK; ++k)
+          tc_mma<false>(tmem_base + 256u, make_sdesc(a + k * 32), make_sdesc(b + k * 32), kIdescRs, (ch | k) != 0);
+        tc_commit(&empty[stage]);
+        if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+      }
+      tc_commit(accum2);
+    }
+  } else {
+    // ------------------------------------------------------------ gate epilogue -> shared-memory operand
+    const int ew = warp - 2;
+    const int q = warp & 3;            // TMEM lane quarter this warp may read (hardware rule)
+    const int slab = ew >> 2;          // 64 accumulator columns = 32 gated channels
+    using EG = EpiPair<EPI_GATE, true>;
+    if (q * 32 + lane < nvalid) EpiPair<EPI_RESSKIP, true>::prefetch_pre(epi, m0 + q * 32 + lane, slab * 64);
+    mbar_wait(accum1, 0, 25);
+    tc_fence_after();
+    {
+      float v[64];
+      tmem_ld64(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(slab * 64), v);
+      const int r = q * 32 + lane;     // row of the tile = TMEM lane
+      const float* gc = gconst + slab * 64;
+      uint32_t w[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        float y[2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const int j = 4 * i + 2 * h;
+          const float a = fmaf(v[j], p.scale_in, gc[j]), b = fmaf(v[j + 1], p.scale_in, gc[j + 1]);
+          y[h] = EG::th(a) * EG::dv(1.f, 1.f + EG::ex(-b));
+        }
+        const twin2_t t = to_twin2(y[0], y[1]);
+        w[i] = *reinterpret_cast<const uint32_t*>(&t);
+      }
+      // K chunk slab / 2, 16-byte units (slab % 2) * 4 .. + 3 of this row, 128B swizzle: unit ^= row % 8
+      uint8_t* rowp = acts + (slab >> 1) * C::kATile + r * 128;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int unit = ((slab & 1) * 4 + u) ^ (r & 7);
+        *reinterpret_cast<uint4*>(rowp + unit * 16) = make_uint4(w[4 * u], w[4 * u + 1], w[4 * u + 2], w[4 * u + 3]);
+      }
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(acts_ready);
+    // ------------------------------------------------------------ res / skip epilogue
+    mbar_wait(accum2, 0, 26);
+    tc_fence_after();
+    float* stg = reinterpret_cast<float*>(smem) + ew * (32 * kStgLd4);
+    const int row0 = m0 + q * 32;
+    int nrows = nvalid - q * 32;
+    nrows = nrows < 0 ? 0 : (nrows > 32 ? 32 : nrows);
+    const int c = slab * 64;
+    if (c < epi.N) {                             // warp-uniform
+      {
+        float v[64];
+        tmem_ld64(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(256 + c), v);
+#pragma unroll
+        for (int j = 0; j < 64; j += 4)
+          *reinterpret_cast<float4*>(stg + lane * kStgLd4 + j) =
+              make_float4(v[j] * p.scale_rs, v[j + 1] * p.scale_rs, v[j + 2] * p.scale_rs, v[j + 3] * p.scale_rs);
+      }
+      __syncwarp();
+      const float4 bias = *reinterpret_cast<const float4*>(epi.bias + c + (lane & 15) * 4);
+      if (c < epi.split) {                       // x += res, 16-bit twin of the new x into the other buffer
+        rmw_slab4<true, true>(stg, epi.out + (size_t)row0 * epi.ldo + epi.col0 + c, epi.ldo,
+                              epi.outh + (size_t)row0 * epi.ldh + epi.colh0 + c, epi.ldh, bias, nrows, lane);
+      } else {                                   // skip (+)= ; its twin only when the coupling projection follows
+        const int m = c - epi.split;
+        float* d = epi.out2 + (size_t)row0 * epi.ldo2 + epi.col20 + m;
+        twin_t* dh = epi.outh2 != nullptr ? epi.outh2 + (size_t)row0 * epi.ldh2 + epi.colh20 + m : nullptr;
+        if (epi.accumulate2) {
+          if (dh != nullptr) rmw_slab4<true, true>(stg, d, epi.ldo2, dh, epi.ldh2, bias, nrows, lane);
+          else rmw_slab4<true, false>(stg, d, epi.ldo2, nullptr, 0, bias, nrows, lane);
+        } else {
+          if (dh != nullptr) rmw_slab4<false, true>(stg, d, epi.ldo2, dh, epi.ldh2, bias, nrows, lane);
+          else rmw_slab4<false, false>(stg, d, epi.ldo2, nullptr, 0, bias, nrows, lane);
+        }
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+  }
+}
+
 // ------------------------------------------------------------------ host: tensor maps
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -786,6 +1046,33 @@ cudaError_t launch_mode(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
   }
 }
 
+
+template <int NRS>
+cudaError_t launch_wn(const ConvGemm& gin, const ConvGemm& grs, const RowMap& map, cudaStream_t st) {
+  using C = WnCfg;
+  const KSeg& ks = gin.seg[0];
+  CUtensorMap mX, mWin, mWrs;
+  if (ks.Ah == nullptr || gin.Wg == nullptr || grs.Wg == nullptr) return cudaErrorInvalidValue;
+  if (!get_map(ks.Ah, ks.rows, ks.ldah, 2, 128, &mX)) return cudaErrorNotSupported;
+  if (!get_map(gin.Wg, gin.Npad, gin.Ktot, 2, 256, &mWin)) return cudaErrorNotSupported;
+  if (!get_map(grs.Wg, grs.Npad, grs.Ktot, 2, NRS, &mWrs)) return cudaErrorNotSupported;
+  WnParams p;
+  p.col0 = ks.colh0;
+  p.scale_in = gin.acc_scale;
+  p.scale_rs = grs.acc_scale;
+  p.bias_in = gin.epi.bias;
+  p.segvec = gin.epi.segvec;
+  p.ldseg = gin.epi.ldseg;
+  auto kern = wn_layer_fused_kernel<NRS>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmem);
+    if (e != cudaSuccess) return e;
+    attr_done = true;
+  }
+  kern<<<map.n_tiles, C::kThreads, C::kSmem, st>>>(mX, mWin, mWrs, p, grs.epi, map);
+  return cudaGetLastError();
+}
 }  // namespace
 
 void tc_map_cache_clear() {
@@ -801,6 +1088,20 @@ cudaError_t conv_gemm_tc_tf32x3(const ConvGemm& g, const RowMap& map, cudaStream
 }
 cudaError_t conv_gemm_tc_f16x3(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
   return launch_mode<MODE_F16X3>(g, map, st);
+}
+
+
+// Fused WN layer (16-bit mode): gin = the k5 in_layer (EPI_GATE constants in gin.epi), grs = the 1x1
+// res/skip layer (EPI_RESSKIP epilogue in grs.epi).  Shapes are those of the default model (128
+// channels, k5, 256 / 128 res-skip outputs); anything else is rejected.
+cudaError_t wn_layer_fused_f16(const ConvGemm& gin, const ConvGemm& grs, const RowMap& map, cudaStream_t st) {
+  const KSeg& k = gin.seg[0];
+  if (gin.n_kseg != 1 || grs.n_kseg != 1 || k.taps != 5 || k.pad != 2 || k.cin_pad != 128 || gin.epi.N != 256 ||
+      gin.Ktot != 640 || grs.Ktot != 128 || grs.seg[0].taps != 1 || grs.seg[0].cin_pad != 128)
+    return cudaErrorInvalidValue;
+  if (grs.epi.N == 256 && grs.Npad >= 256) return launch_wn<256>(gin, grs, map, st);
+  if (grs.epi.N == 128) return launch_wn<128>(gin, grs, map, st);
+  return cudaErrorInvalidValue;
 }
 
 }  // namespace stts

@@ -10,6 +10,7 @@ cudaError_t conv_gemm_simt(const ConvGemm& g, const RowMap& map, cudaStream_t st
 cudaError_t conv_gemm_tc_f16(const ConvGemm& g, const RowMap& map, cudaStream_t st);
 cudaError_t conv_gemm_tc_tf32x3(const ConvGemm& g, const RowMap& map, cudaStream_t st);
 cudaError_t conv_gemm_tc_f16x3(const ConvGemm& g, const RowMap& map, cudaStream_t st);
+cudaError_t wn_layer_fused_f16(const ConvGemm& gin, const ConvGemm& grs, const RowMap& map, cudaStream_t st);
 void tc_map_cache_clear();
 
 // ---- elementwise.cu
@@ -90,5 +91,6 @@ cudaError_t polar_spec(const float* logamp, const float* phase, int ld, int n_bi
                        int lds, __half* specg, int ldsh, __half* specl, float gscale, cudaStream_t st);
 cudaError_t ola_tanh(const float* frames, int ldf, const float* wsq, const int* cu4, const RowMap& map, float* audio,
                      cudaStream_t st);
+cudaError_t pcm16(const float* x, int16_t* y, long long n, cudaStream_t st);
 
 }  // namespace stts

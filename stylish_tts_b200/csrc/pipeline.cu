@@ -502,6 +502,35 @@ int run_decoder(Context& c, const float* d_asr, const float* d_f0, const float* 
 // ----------------------------------------------------------------------------- prior + flow^-1 + post_flow
 // `x`: decoder output (512 channels at columns 0..511); NOISE holds the packed randn draw.
 // Results: ZP = z_text (prior sample), Z = z after the reversed flow, CATP[:, 0:512] = mel.
+namespace {
+// STTS_WN_FUSED=0: 16-bit mode keeps two GEMM launches per WN layer (A/B comparison)
+bool wn_fused() {
+  static const bool v = [] { const char* e = std::getenv("STTS_WN_FUSED"); return e == nullptr || e[0] != '0'; }();
+  return v;
+}
+// ConvGemm of a one-K-segment body layer in 16-bit mode (what run_gemm builds for backend 1), with an
+// explicit 16-bit operand pointer
+ConvGemm body16(const PackedGemm& pg, const Act& a, const twin_t* ah, const Epi& e) {
+  ConvGemm g;
+  std::memset(&g, 0, sizeof(g));
+  g.n_kseg = 1;
+  KSeg& k = g.seg[0];
+  k.A = a.f; k.lda = a.ld; k.col0 = 0;
+  k.Ah = ah; k.ldah = a.ld; k.colh0 = 0;
+  k.taps = pg.taps[0]; k.pad = pg.pad[0]; k.cin_pad = pg.cin_pad[0];
+  k.rows = a.rows;
+  g.W = pg.Wf;
+  g.Wg = pg.Wg;
+  g.acc_scale = 1.0f / pg.wscale;
+  g.Ktot = pg.Ktot;
+  g.Npad = pg.Npad;
+  g.epi = e;
+  g.epi.N = pg.N;
+  if (g.epi.bias == nullptr) g.epi.bias = pg.bias;
+  return g;
+}
+}  // namespace
+
 int run_prior_flow_core(Context& c, const Act& x, const float* d_style, cudaStream_t st) {
   if (!c.finalized || c.J_flow == 0) return fail(c, -3, "speech_predictor weights not loaded");
   Stage S(c, st);
@@ -527,6 +556,45 @@ int run_prior_flow_core(Context& c, const Act& x, const float* d_style, cudaStre
       STTS_RET(run_gemm(c, c.gemm[nm + ".pre"], GC_BODY, &z, z0col, nullptr, 0, e, map, st));
     }
     for (int l = 0; l < 4; ++l) {
+      if (S.twins && wn_fused()) {
+        // 16-bit mode: the whole WN layer is one launch (gemm_tc.cu, wn_layer_fused_kernel); the gated
+        // activations never leave shared memory and the 16-bit twin of x ping-pongs between WH and ACTS
+        const PackedGemm& pin = c.gemm[nm + ".in" + std::to_string(l)];
+        const PackedGemm& prs = c.gemm[nm + ".rs" + std::to_string(l)];
+        twin_t* tw_in = (l % 2 == 0) ? wh.h : acts.h;
+        twin_t* tw_out = (l % 2 == 0) ? acts.h : wh.h;
+        Epi eg = S.epi(EPI_GATE, acts, 0);
+        eg.segvec = gi + l * 256;
+        eg.ldseg = c.J_flow;
+        Epi er = S.epi(EPI_RESSKIP, wh, 0);
+        er.outh = tw_out; er.outg = nullptr; er.outl = nullptr;
+        er.split = (l < 3) ? 128 : 0;
+        er.out2 = wout.f; er.ldo2 = wout.ld; er.col20 = 0;
+        er.outh2 = (l == 3) ? S.tw(wout) : nullptr; er.ldh2 = wout.ld; er.colh20 = 0;   // only proj reads the twin
+        er.accumulate2 = (l > 0) ? 1 : 0;
+        ConvGemm gin = body16(pin, wh, tw_in, eg), grs = body16(prs, acts, acts.h, er);
+        Context::ProfRec pr;
+        if (c.prof_on) {
+          auto get_ev = [&]() {
+            cudaEvent_t ev;
+            if (!c.ev_pool.empty()) { ev = c.ev_pool.back(); c.ev_pool.pop_back(); }
+            else cudaEventCreate(&ev);
+            return ev;
+          };
+          pr.name = nm + ".wn" + std::to_string(l); pr.e0 = get_ev(); pr.e1 = get_ev(); pr.backend = 5;
+          pr.flops = 2.0 * (double)c.L4.total() * ((double)pin.N * pin.k_real + (double)prs.N * prs.k_real);
+          cudaEventRecord(pr.e0, st);
+        }
+        static const char* prof_layer = std::getenv("STTS_PROFILE_LAYER");
+        const bool bracket = prof_layer != nullptr && (nm + ".wn" + std::to_string(l)) == prof_layer;
+        if (bracket) { cudaStreamSynchronize(st); cudaProfilerStart(); }
+        cudaError_t e = wn_layer_fused_f16(gin, grs, map, st);
+        if (bracket) { cudaStreamSynchronize(st); cudaProfilerStop(); }
+        if (e != cudaSuccess) return cuda_fail(c, e, "wn_layer_fused launch");
+        if (c.prof_on) { cudaEventRecord(pr.e1, st); c.prof.push_back(pr); }
+        c.launches++;
+        continue;
+      }
       {  // acts = tanh . sigmoid (in_layer(x) + g_l)
         Epi e = S.epi(EPI_GATE, acts, 0);
         if (S.twins) e.out = nullptr;          // only the twin of the gated activations is read (res/skip GEMM)

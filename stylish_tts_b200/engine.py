@@ -247,6 +247,13 @@ class Engine:
     def check_source_status(self):
         self._check(self.lib.stts_check_source_status(self.h, self._stream()))
 
+    def pcm16(self, audio: torch.Tensor) -> torch.Tensor:
+        """fp32 device waveform -> int16 PCM on the device (train/test_onnx.py:79)."""
+        a = audio.contiguous()
+        out = torch.empty(a.shape, dtype=torch.int16, device=self.device)
+        self._check(self.lib.stts_pcm16(self.h, _ptr(a), a.numel(), out.data_ptr(), self._stream()))
+        return out
+
     def set_profiling(self, on: bool):
         self._check(self.lib.stts_set_profiling(self.h, 1 if on else 0))
 

@@ -1,0 +1,5 @@
+mkdir -p gpurun_out; rm -f gpurun_out/rc.txt
+timeout 600 python -m pytest tests/ -q -m gpu -x > gpurun_out/pytest_gpu.log 2>&1; echo "pytest_gpu rc=$?" >> gpurun_out/rc.txt
+timeout 300 python bench.py --steps 6 --warmup 3 --no-cpu-baseline --layers gpurun_out/layers_rb16.md > gpurun_out/bench_rb16.json 2> gpurun_out/bench_rb16.err; echo "bench rc=$?" >> gpurun_out/rc.txt
+STTS_WN_FUSED=0 timeout 300 python bench.py --steps 6 --warmup 3 --no-cpu-baseline --layers gpurun_out/layers_rb16off.md > gpurun_out/bench_rb16off.json 2> gpurun_out/bench_rb16off.err; echo "bench rc=$?" >> gpurun_out/rc.txt
+cat gpurun_out/rc.txt; tail -15 gpurun_out/pytest_gpu.log; cut -c1-400 gpurun_out/bench_rb16.json; echo; cut -c1-400 gpurun_out/bench_rb16off.json; tail -3 gpurun_out/bench_rb16.err
