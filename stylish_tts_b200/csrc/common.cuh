@@ -392,6 +392,109 @@ struct EpiPair {
   }
 };
 
+// Lane-per-4-columns form of the "simple" kinds (bias / residual / activation): lanes 0-15 cover the 64
+// columns of one row of the slab with 16-byte accesses, lanes 16-31 the next row, so one warp instruction
+// moves two full row segments and the per-row pointer arithmetic is shared by four columns (the
+// lane-per-pair form was instruction-issue-bound: ncu, profiles/README.md).  Falls back to guarded scalar
+// accesses where the slab crosses the logical N or the destination is not 16-byte aligned.
+template <int KIND, bool FAST>
+struct EpiQuad {
+  static constexpr bool kOk = (KIND == EPI_BIAS || KIND == EPI_RES_SCALE || KIND == EPI_SILU || KIND == EPI_ADD ||
+                               KIND == EPI_RELU || KIND == EPI_GELU);
+  static constexpr bool kHasPre = (KIND == EPI_RES_SCALE || KIND == EPI_ADD);
+  using P = EpiPair<KIND, FAST>;
+  float bias[4];
+  float ss[4];
+  int n, nv;       // first column of this lane, number of its columns inside the logical N (0 .. 4)
+  bool vec;        // all four columns valid and every destination / source row segment 16-byte aligned
+  __device__ __forceinline__ void init(const Epi& e, int n_) {
+    n = n_;
+    nv = e.N - n; nv = nv < 0 ? 0 : (nv > 4 ? 4 : nv);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { bias[i] = (e.bias != nullptr && i < nv) ? e.bias[n + i] : 0.f; ss[i] = 0.f; }
+    auto al = [](const void* base, int ld, int col, int elem) {
+      return base == nullptr || ((((uintptr_t)base + (size_t)col * elem) & (elem * 4 - 1)) == 0 && (ld & 3) == 0);
+    };
+    vec = nv == 4 && al(e.out, e.ldo, e.col0 + n, 4) && al(e.outh, e.ldh, e.colh0 + n, 2) &&
+          al(e.outg, e.ldh, e.colh0 + n, 2) && al(e.outl, e.ldh, e.colh0 + n, 2) &&
+          (!kHasPre || al(e.res, e.ldr, e.rcol0 + n, 4));
+  }
+  __device__ __forceinline__ float4 pre(const Epi& e, int r) const {
+    float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+    if constexpr (kHasPre) {
+      if (e.res == nullptr || nv == 0) return t;
+      const float* rp = e.res + (size_t)r * e.ldr + e.rcol0 + n;
+      if (vec) return *reinterpret_cast<const float4*>(rp);
+      t.x = rp[0];
+      if (nv > 1) t.y = rp[1];
+      if (nv > 2) t.z = rp[2];
+      if (nv > 3) t.w = rp[3];
+    }
+    return t;
+  }
+  __device__ __forceinline__ void apply(const Epi& e, int r, float4 a, float4 t) {
+    if (nv == 0) return;
+    float x[4] = {a.x + bias[0], a.y + bias[1], a.z + bias[2], a.w + bias[3]};
+    const float tt[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      if constexpr (KIND == EPI_RES_SCALE) x[i] = (x[i] + tt[i]) * e.scale;
+      if constexpr (KIND == EPI_SILU) { x[i] = P::dv(x[i], 1.f + P::ex(-x[i])); ss[i] = fmaf(x[i], x[i], ss[i]); }
+      if constexpr (KIND == EPI_ADD) x[i] += tt[i];
+      if constexpr (KIND == EPI_RELU) x[i] = fmaxf(x[i], 0.f);
+      if constexpr (KIND == EPI_GELU) x[i] = 0.5f * x[i] * (1.f + erff(x[i] * 0.70710678118654752440f));
+    }
+    float* o = e.out != nullptr ? e.out + (size_t)r * e.ldo + e.col0 + n : nullptr;
+    twin_t* oh = e.outh != nullptr ? e.outh + (size_t)r * e.ldh + e.colh0 + n : nullptr;
+    __half* og = e.outg != nullptr ? e.outg + (size_t)r * e.ldh + e.colh0 + n : nullptr;
+    __half* ol = (e.outg != nullptr && e.outl != nullptr) ? e.outl + (size_t)r * e.ldh + e.colh0 + n : nullptr;
+    if (vec) {
+      if (o != nullptr) *reinterpret_cast<float4*>(o) = make_float4(x[0], x[1], x[2], x[3]);
+      if (oh != nullptr) {
+        const twin2_t t0 = to_twin2(x[0], x[1]), t1 = to_twin2(x[2], x[3]);
+        uint2 w;
+        w.x = *reinterpret_cast<const uint32_t*>(&t0); w.y = *reinterpret_cast<const uint32_t*>(&t1);
+        *reinterpret_cast<uint2*>(oh) = w;
+      }
+      if (og != nullptr) {
+        const __half2 g0 = __floats2half2_rn(sat16(x[0]), sat16(x[1])), g1 = __floats2half2_rn(sat16(x[2]), sat16(x[3]));
+        uint2 w;
+        w.x = *reinterpret_cast<const uint32_t*>(&g0); w.y = *reinterpret_cast<const uint32_t*>(&g1);
+        *reinterpret_cast<uint2*>(og) = w;
+        if (ol != nullptr) {
+          const __half2 l0 = __floats2half2_rn(sat16(x[0]) - __low2float(g0), sat16(x[1]) - __high2float(g0));
+          const __half2 l1 = __floats2half2_rn(sat16(x[2]) - __low2float(g1), sat16(x[3]) - __high2float(g1));
+          w.x = *reinterpret_cast<const uint32_t*>(&l0); w.y = *reinterpret_cast<const uint32_t*>(&l1);
+          *reinterpret_cast<uint2*>(ol) = w;
+        }
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        if (i < nv) {
+          if (o != nullptr) o[i] = x[i];
+          if (oh != nullptr) oh[i] = to_twin(x[i]);
+          if (og != nullptr) { __half lo; f16_split(x[i], og + i, ol != nullptr ? ol + i : &lo); }
+        }
+      }
+    }
+  }
+  // per-(tile, quarter) column sums of squares (EPI_SILU): the two row-interleaved halves of the warp are
+  // combined with one shuffle; lanes 0-15 write
+  __device__ __forceinline__ void finish(const Epi& e, int tile, int q, int lane) {
+    if constexpr (KIND == EPI_SILU) {
+      if (e.colss == nullptr) return;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) ss[i] += __shfl_xor_sync(0xffffffffu, ss[i], 16);
+      if (lane < 16) {
+        float* p = e.colss + (size_t)(tile * 4 + q) * e.colss_ld + n;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) if (i < nv) p[i] = ss[i];
+      }
+    }
+  }
+};
+
 // ----------------------------------------------------------------------------- conv-as-GEMM
 // Y[r, n] = sum_s sum_j sum_c A_s[r + j - pad_s, col0_s + c] * W[n, koff_s + j * cin_pad_s + c]
 // Up to two K-segments (fused 1x1 shortcut, channel concatenation across buffers).

@@ -123,6 +123,7 @@ __device__ __forceinline__ void tmem_ld64(uint32_t taddr, float* v) {
   for (int i = 0; i < 64; ++i) v[i] = __uint_as_float(r[i]);
 }
 constexpr int kStgLd = 66;   // staging row stride in floats (even: float2 aligned; 66 % 32 = 2: conflict-free 64-bit)
+constexpr int kStgLd4 = 68;  // staging row stride of the float4 (lane-per-4-columns) epilogues: 16-byte aligned rows
 
 // K-major, 128-byte-swizzled shared-memory matrix descriptor (cute::UMMA::SmemDescriptor layout):
 // start>>4 [0,14) | LBO>>4 [16,30) | SBO>>4 [32,46) | version=1 [46,48) | layout SWIZZLE_128B=2 [61,64)
@@ -141,6 +142,77 @@ __device__ __forceinline__ float rna_tf32(float x) {
   uint32_t r;
   asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
   return __uint_as_float(r);
+}
+
+// Read-modify-write epilogue of one 32-row x 64-column slab, lane-per-4-columns: lanes 0-15 cover the
+// 64 columns of one row with float4 accesses, lanes 16-31 the next row, so one warp instruction moves two
+// full 256-byte row segments.  dst / dsth point at (first row of the slab, first column of the slab).
+// (The lane-per-column-pair form with its per-row pointer arithmetic and null checks was issue-bound:
+// ncu counted ~67 instructions per row and warp, 52 % of the fused layer's tile time.)
+template <bool HAS_PRE, bool HAS_TWIN>
+__device__ __forceinline__ void rmw_slab4(const float* __restrict__ stg, float* __restrict__ dst, int ld,
+                                          twin_t* __restrict__ dsth, int ldh, float4 bias, int nrows, int lane) {
+  const int sub = lane >> 4, c4 = (lane & 15) * 4;
+  float* p = dst + (size_t)sub * ld + c4;
+  twin_t* ph = HAS_TWIN ? dsth + (size_t)sub * ldh + c4 : nullptr;
+  const float* sp = stg + sub * kStgLd4 + c4;
+#pragma unroll 1
+  for (int rb = 0; rb < 32; rb += 16) {
+    float4 pre[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      pre[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (HAS_PRE && rb + 2 * i + sub < nrows) pre[i] = *reinterpret_cast<const float4*>(p + (size_t)(rb + 2 * i) * ld);
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      if (rb + 2 * i + sub < nrows) {
+        const float4 a = *reinterpret_cast<const float4*>(sp + (rb + 2 * i) * kStgLd4);
+        float4 y;
+        y.x = pre[i].x + (a.x + bias.x); y.y = pre[i].y + (a.y + bias.y);
+        y.z = pre[i].z + (a.z + bias.z); y.w = pre[i].w + (a.w + bias.w);
+        *reinterpret_cast<float4*>(p + (size_t)(rb + 2 * i) * ld) = y;
+        if constexpr (HAS_TWIN) {
+          const twin2_t t0 = to_twin2(y.x, y.y), t1 = to_twin2(y.z, y.w);
+          uint2 w;
+          w.x = *reinterpret_cast<const uint32_t*>(&t0);
+          w.y = *reinterpret_cast<const uint32_t*>(&t1);
+          *reinterpret_cast<uint2*>(ph + (size_t)(rb + 2 * i) * ldh) = w;
+        }
+      }
+    }
+  }
+}
+
+// One 32-row x 64-column slab of a "simple" epilogue in the lane-per-4-columns form (EpiQuad): NB
+// iterations (2 rows each) of residual loads are issued before the stores of the batch.
+template <int KIND, bool FAST, int NB>
+__device__ __forceinline__ void quad_slab(const Epi& epi, const float* __restrict__ stg, int row0, int nrows, int col,
+                                          int tile, int q, int lane) {
+  EpiQuad<KIND, FAST> eq;
+  eq.init(epi, col + (lane & 15) * 4);
+  const int sub = lane >> 4;
+  const float* sp = stg + sub * kStgLd4 + (lane & 15) * 4;
+#pragma unroll 1
+  for (int rb = 0; rb < 32; rb += 2 * NB) {
+    float4 pre[NB];
+    if constexpr (EpiQuad<KIND, FAST>::kHasPre) {
+#pragma unroll
+      for (int i = 0; i < NB; ++i) {
+        pre[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (rb + 2 * i + sub < nrows) pre[i] = eq.pre(epi, row0 + rb + 2 * i + sub);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < NB; ++i) {
+      if (rb + 2 * i + sub < nrows) {
+        const float4 a = *reinterpret_cast<const float4*>(sp + (rb + 2 * i) * kStgLd4);
+        eq.apply(epi, row0 + rb + 2 * i + sub, a,
+                 EpiQuad<KIND, FAST>::kHasPre ? pre[i] : make_float4(0.f, 0.f, 0.f, 0.f));
+      }
+    }
+  }
+  eq.finish(epi, tile, q, lane);
 }
 
 // MODE_F16 doubles as the one-pass fp16 GEMM (runtime instruction-descriptor formats), MODE_F16X3 is
@@ -326,12 +398,29 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
     // owns TMEM lane quarter q = warp % 4 (hardware rule) and the 64-column slab ew / 4.
     const int ew = warp - 2;
     const int q = warp & 3;
-    float* stg = reinterpret_cast<float*>(smem) + ew * (32 * kStgLd);
+    using EQ = EpiQuad<KIND, MODE == MODE_F16>;
+    constexpr int kLd = EQ::kOk ? kStgLd4 : kStgLd;
+    float* stg = reinterpret_cast<float*>(smem) + ew * (32 * kLd);
     const int row0 = m0 + q * 32;
     int nrows = nvalid - q * 32;
     nrows = nrows < 0 ? 0 : (nrows > 32 ? 32 : nrows);
     const int seg_first = (epi.seg_start != nullptr) ? epi.seg_start[seg] : -1;
     const int c = (ew >> 2) * 64;
+    if constexpr (EQ::kOk) {
+      if (n0 + c < epi.N) {                    // warp-uniform
+        {
+          float v[64];
+          tmem_ld64(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c, v);
+          __syncwarp();
+#pragma unroll
+          for (int j = 0; j < 64; j += 4)
+            *reinterpret_cast<float4*>(stg + lane * kStgLd4 + j) =
+                make_float4(v[j] * p.acc_scale, v[j + 1] * p.acc_scale, v[j + 2] * p.acc_scale, v[j + 3] * p.acc_scale);
+        }
+        __syncwarp();
+        quad_slab<KIND, MODE == MODE_F16, (BN == 256 || OCC == 2) ? 4 : 8>(epi, stg, row0, nrows, n0 + c, tile, q, lane);
+      }
+    } else
     if (n0 + c < epi.N) {                      // warp-uniform
       EpiPair<KIND, MODE == MODE_F16> ep;
       ep.init(epi, seg, n0 + c + 2 * lane);
@@ -399,7 +488,7 @@ struct PCfg {
   static constexpr int kStages = 3;
   static constexpr int kEpiWarps = 8;                                    // 4 lane quarters x 2 column halves
   static constexpr int kThreads = 64 + 32 * kEpiWarps;                   // 320
-  static constexpr int kStagingBytes = kEpiWarps * 32 * kStgLd * 4;      // 67 584
+  static constexpr int kStagingBytes = kEpiWarps * 32 * kStgLd4 * 4;     // 69 632
   static constexpr int kSmem = kStages * kStageBytes + kStagingBytes + 1024 + 256;
   static constexpr uint32_t kIdesc = (1u << 4) | ((uint32_t)(kBN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);  // f16 x f16 -> f32
 };
@@ -498,7 +587,7 @@ conv_gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap mapA0, const 
     const int ew = warp - 2;                       // 0 .. 7
     const int q = warp & 3;                        // TMEM lane quarter this warp may read (hardware rule)
     const int half = ew >> 2;                      // column half: slabs {0, 64} + 128 * half
-    float* stg = staging + ew * (32 * kStgLd);
+    float* stg = staging + ew * (32 * kStgLd4);
     int it = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
       const int tile = t / n_tiles_n, n0 = (t - tile * n_tiles_n) * C::kBN;
@@ -521,9 +610,16 @@ conv_gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap mapA0, const 
           float v[64];
           tmem_ld64(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * C::kBN + c), v);
           __syncwarp();                            // previous slab fully consumed
+          if constexpr (EpiQuad<KIND, true>::kOk) {
 #pragma unroll
-          for (int j = 0; j < 64; j += 2)
-            *reinterpret_cast<float2*>(stg + lane * kStgLd + j) = make_float2(v[j] * p.acc_scale, v[j + 1] * p.acc_scale);
+            for (int j = 0; j < 64; j += 4)
+              *reinterpret_cast<float4*>(stg + lane * kStgLd4 + j) =
+                  make_float4(v[j] * p.acc_scale, v[j + 1] * p.acc_scale, v[j + 2] * p.acc_scale, v[j + 3] * p.acc_scale);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 64; j += 2)
+              *reinterpret_cast<float2*>(stg + lane * kStgLd + j) = make_float2(v[j] * p.acc_scale, v[j + 1] * p.acc_scale);
+          }
         }
         if (sl == 1) {                             // last TMEM read of this tile: hand the accumulator back
           tc_fence_before();
@@ -532,6 +628,10 @@ conv_gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap mapA0, const 
         }
         if (!live) continue;
         __syncwarp();
+        if constexpr (EpiQuad<KIND, true>::kOk) {
+          quad_slab<KIND, true, 8>(epi, stg, row0, nrows, n0 + c, tile, q, lane);
+          continue;
+        }
         EpiPair<KIND, true> ep;
         ep.init(epi, seg, n0 + c + 2 * lane);
         if constexpr (EpiPair<KIND, false>::kHasPre) {
@@ -582,47 +682,6 @@ conv_gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap mapA0, const 
 //   x += res, skip (+)= skip                                               (EPI_RESSKIP, coalesced)
 // The conv reads +-2 halo rows of neighbouring tiles, so the updated 16-bit twin of x goes to a second
 // buffer (ping-pong per layer); the fp32 master is only touched by the tile that owns the rows.
-// Read-modify-write epilogue of one 32-row x 64-column slab, lane-per-4-columns: lanes 0-15 cover the
-// 64 columns of one row with float4 accesses, lanes 16-31 the next row, so one warp instruction moves two
-// full 256-byte row segments.  dst / dsth point at (first row of the slab, first column of the slab).
-// (The lane-per-column-pair form with its per-row pointer arithmetic and null checks was issue-bound:
-// ncu counted ~67 instructions per row and warp, 52 % of the fused layer's tile time.)
-constexpr int kStgLd4 = 68;   // staging row stride in floats for the float4 form (16-byte aligned rows)
-template <bool HAS_PRE, bool HAS_TWIN>
-__device__ __forceinline__ void rmw_slab4(const float* __restrict__ stg, float* __restrict__ dst, int ld,
-                                          twin_t* __restrict__ dsth, int ldh, float4 bias, int nrows, int lane) {
-  const int sub = lane >> 4, c4 = (lane & 15) * 4;
-  float* p = dst + (size_t)sub * ld + c4;
-  twin_t* ph = HAS_TWIN ? dsth + (size_t)sub * ldh + c4 : nullptr;
-  const float* sp = stg + sub * kStgLd4 + c4;
-#pragma unroll 1
-  for (int rb = 0; rb < 32; rb += 16) {
-    float4 pre[8];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      pre[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (HAS_PRE && rb + 2 * i + sub < nrows) pre[i] = *reinterpret_cast<const float4*>(p + (size_t)(rb + 2 * i) * ld);
-    }
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      if (rb + 2 * i + sub < nrows) {
-        const float4 a = *reinterpret_cast<const float4*>(sp + (rb + 2 * i) * kStgLd4);
-        float4 y;
-        y.x = pre[i].x + (a.x + bias.x); y.y = pre[i].y + (a.y + bias.y);
-        y.z = pre[i].z + (a.z + bias.z); y.w = pre[i].w + (a.w + bias.w);
-        *reinterpret_cast<float4*>(p + (size_t)(rb + 2 * i) * ld) = y;
-        if constexpr (HAS_TWIN) {
-          const twin2_t t0 = to_twin2(y.x, y.y), t1 = to_twin2(y.z, y.w);
-          uint2 w;
-          w.x = *reinterpret_cast<const uint32_t*>(&t0);
-          w.y = *reinterpret_cast<const uint32_t*>(&t1);
-          *reinterpret_cast<uint2*>(ph + (size_t)(rb + 2 * i) * ldh) = w;
-        }
-      }
-    }
-  }
-}
-
 struct WnCfg {
   static constexpr int kBK = 64, kUmmaK = 16;
   static constexpr int kATile = 128 * 128, kBTile = 256 * 128;            // bytes
