@@ -73,6 +73,10 @@ struct Epi {
   // EPI_SILU, tcgen05 kernel only: per-(tile, row quarter) column sums of squares of the activated output,
   // [n_tiles * 4, colss_ld] fp32 -- the L2-over-time statistic of GRN without re-reading the tensor
   float* colss; int colss_ld;
+  // EPI_BIAS / EPI_RES_SCALE, tcgen05 kernel only: per-(tile, row quarter) column sums and sums of squares of
+  // the stored output, [n_tiles * 4, colst_ld] fp32 each -- InstanceNorm statistics of the next AdaIN without
+  // re-reading the tensor (16-bit mode)
+  float* colsum; float* colsq; int colst_ld;
 };
 
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + __expf(-x)); }
@@ -403,15 +407,19 @@ struct EpiQuad {
                                KIND == EPI_RELU || KIND == EPI_GELU);
   static constexpr bool kHasPre = (KIND == EPI_RES_SCALE || KIND == EPI_ADD);
   using P = EpiPair<KIND, FAST>;
+  static constexpr bool kStats = (KIND == EPI_BIAS || KIND == EPI_RES_SCALE);
   float bias[4];
-  float ss[4];
+  float ss[4];     // running sums of squares (EPI_SILU: GRN; kStats kinds: InstanceNorm)
+  float sm[4];     // running sums (kStats kinds)
+  bool st;         // statistics requested
   int n, nv;       // first column of this lane, number of its columns inside the logical N (0 .. 4)
   bool vec;        // all four columns valid and every destination / source row segment 16-byte aligned
   __device__ __forceinline__ void init(const Epi& e, int n_) {
     n = n_;
     nv = e.N - n; nv = nv < 0 ? 0 : (nv > 4 ? 4 : nv);
 #pragma unroll
-    for (int i = 0; i < 4; ++i) { bias[i] = (e.bias != nullptr && i < nv) ? e.bias[n + i] : 0.f; ss[i] = 0.f; }
+    for (int i = 0; i < 4; ++i) { bias[i] = (e.bias != nullptr && i < nv) ? e.bias[n + i] : 0.f; ss[i] = 0.f; sm[i] = 0.f; }
+    st = kStats && e.colsum != nullptr;
     auto al = [](const void* base, int ld, int col, int elem) {
       return base == nullptr || ((((uintptr_t)base + (size_t)col * elem) & (elem * 4 - 1)) == 0 && (ld & 3) == 0);
     };
@@ -443,6 +451,12 @@ struct EpiQuad {
       if constexpr (KIND == EPI_ADD) x[i] += tt[i];
       if constexpr (KIND == EPI_RELU) x[i] = fmaxf(x[i], 0.f);
       if constexpr (KIND == EPI_GELU) x[i] = 0.5f * x[i] * (1.f + erff(x[i] * 0.70710678118654752440f));
+    }
+    if constexpr (kStats) {
+      if (st) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { sm[i] += x[i]; ss[i] = fmaf(x[i], x[i], ss[i]); }
+      }
     }
     float* o = e.out != nullptr ? e.out + (size_t)r * e.ldo + e.col0 + n : nullptr;
     twin_t* oh = e.outh != nullptr ? e.outh + (size_t)r * e.ldh + e.colh0 + n : nullptr;
@@ -482,6 +496,19 @@ struct EpiQuad {
   // per-(tile, quarter) column sums of squares (EPI_SILU): the two row-interleaved halves of the warp are
   // combined with one shuffle; lanes 0-15 write
   __device__ __forceinline__ void finish(const Epi& e, int tile, int q, int lane) {
+    if constexpr (kStats) {
+      if (e.colsum == nullptr) return;          // warp-uniform
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        sm[i] += __shfl_xor_sync(0xffffffffu, sm[i], 16);
+        ss[i] += __shfl_xor_sync(0xffffffffu, ss[i], 16);
+      }
+      if (lane < 16) {
+        const size_t o = (size_t)(tile * 4 + q) * e.colst_ld + n;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) if (i < nv) { e.colsum[o + i] = sm[i]; e.colsq[o + i] = ss[i]; }
+      }
+    }
     if constexpr (KIND == EPI_SILU) {
       if (e.colss == nullptr) return;
 #pragma unroll

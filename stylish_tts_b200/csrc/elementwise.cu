@@ -69,6 +69,61 @@ cudaError_t colstats(const float* x, int ld, int C, const RowMap& map, int mode,
   return cudaGetLastError();
 }
 
+// Quarter-tile form of the same statistics, fed by the GEMM epilogues (Epi::colsum / colsq: fp32 sums over the
+// 32 rows of a (tile, quarter), 16-bit mode): colstats_partial_q fills the columns no GEMM produces (the
+// asr_res / F0 / N side channels of the decoder's concatenated input), colstats_final_q reduces in fp64.
+__global__ void __launch_bounds__(128) colstats_partial_q_kernel(const float* __restrict__ x, int ld, int col0, int ncols,
+                                                                 RowMap map, float* __restrict__ psum,
+                                                                 float* __restrict__ psq, int pld) {
+  const int tile = blockIdx.x, q = blockIdx.y;
+  if (map.tile_seg[tile] < 0) return;
+  int nrows = map.tile_nvalid[tile] - q * 32;
+  nrows = nrows < 0 ? 0 : (nrows > 32 ? 32 : nrows);
+  for (int c = threadIdx.x; c < ncols; c += blockDim.x) {
+    const float* p = x + (size_t)(tile * 128 + q * 32) * ld + col0 + c;
+    float s = 0.f, sq = 0.f;
+    for (int i = 0; i < nrows; ++i) { const float v = p[(size_t)i * ld]; s += v; sq = fmaf(v, v, sq); }
+    psum[(size_t)(tile * 4 + q) * pld + col0 + c] = s;
+    psq[(size_t)(tile * 4 + q) * pld + col0 + c] = sq;
+  }
+}
+
+__global__ void __launch_bounds__(128) colstats_final_q_kernel(const float* __restrict__ psum,
+                                                               const float* __restrict__ psq, int pld, int C, RowMap map,
+                                                               float eps, float* __restrict__ mean,
+                                                               float* __restrict__ rstd) {
+  const int seg = blockIdx.x;
+  const int c = blockIdx.y * 128 + threadIdx.x;
+  if (c >= C) return;
+  const int t0 = map.seg_start[seg] / 128;
+  const int len = map.seg_len[seg];
+  const int nq = (len + 31) / 32;              // quarters that hold valid rows (in tile order)
+  double s = 0.0, q = 0.0;
+  for (int k = 0; k < nq; ++k) {
+    s += (double)psum[(size_t)(t0 * 4 + k) * pld + c];
+    q += (double)psq[(size_t)(t0 * 4 + k) * pld + c];
+  }
+  const double m = s / len;
+  double var = q / len - m * m;
+  if (var < 0.0) var = 0.0;
+  mean[(size_t)seg * C + c] = (float)m;
+  rstd[(size_t)seg * C + c] = (float)(1.0 / sqrt(var + (double)eps));
+}
+
+cudaError_t colstats_partial_q(const float* x, int ld, int col0, int ncols, const RowMap& map, float* psum, float* psq,
+                               int pld, cudaStream_t st) {
+  dim3 g(map.n_tiles, 4);
+  colstats_partial_q_kernel<<<g, 128, 0, st>>>(x, ld, col0, ncols, map, psum, psq, pld);
+  return cudaGetLastError();
+}
+
+cudaError_t colstats_final_q(const float* psum, const float* psq, int pld, int C, const RowMap& map, float eps,
+                             float* mean, float* rstd, cudaStream_t st) {
+  dim3 g(map.n_seg, (C + 127) / 128);
+  colstats_final_q_kernel<<<g, 128, 0, st>>>(psum, psq, pld, C, map, eps, mean, rstd);
+  return cudaGetLastError();
+}
+
 // ============================================================================ style FCs
 // out[b, j] = bias[j] + sum_k W[j, k] * s[b, k]  -- all AdaIN / AdaLN / WN-cond Linear(style)
 // layers of a stage concatenated along j (ada_norm.py:133,190; flow.py:39-40).

@@ -16,6 +16,10 @@ void tc_map_cache_clear();
 // ---- elementwise.cu
 cudaError_t colstats(const float* x, int ld, int C, const RowMap& map, int mode, float eps, double* scratch,
                      float* out0, float* out1, cudaStream_t st);
+cudaError_t colstats_partial_q(const float* x, int ld, int col0, int ncols, const RowMap& map, float* psum, float* psq,
+                               int pld, cudaStream_t st);
+cudaError_t colstats_final_q(const float* psum, const float* psq, int pld, int C, const RowMap& map, float eps,
+                             float* mean, float* rstd, cudaStream_t st);
 cudaError_t style_fc(const float* W, const float* bias, const float* s, int J, int K, int B, float* out,
                      cudaStream_t st);
 cudaError_t adain_act(const float* x, int ldx, int C, const RowMap& map, const float* mean, const float* rstd,

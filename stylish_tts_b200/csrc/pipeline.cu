@@ -144,6 +144,10 @@ int set_layout(Context& c, int n_seg, const int* len_f, const int* len_f4) {
       {"GB_GEN", (size_t)B * std::max(c.J_gen, 1) * 4},                  {"GB_FLOW", (size_t)B * std::max(c.J_flow, 1) * 4},
       {"GB_PE", (size_t)B * std::max(c.J_pe, 1) * 4},                    {"STATUS", 256},
   };
+  // InstanceNorm statistics from the conv epilogues (16-bit mode): per-(tile, quarter) fp32 column sums / sums
+  // of squares of a block's input (PSX: conv2 of the previous block + side channels) and of conv1's output (PSY)
+  if (use4) { raws.push_back({"PSX4", (size_t)(R4 / 128) * 4 * 640 * 4 * 2}); raws.push_back({"PSY4", (size_t)(R4 / 128) * 4 * 512 * 4 * 2}); }
+  if (useF) { raws.push_back({"PSXF", (size_t)(RF / 128) * 4 * 320 * 4 * 2}); raws.push_back({"PSYF", (size_t)(RF / 128) * 4 * 320 * 4 * 2}); }
   if (use4) {   // GRN folded into pw2: sum-of-squares partials of the pw1 epilogue, per-utterance fp16 weights
     raws.push_back({"COLSS", (size_t)(R4 / 128) * 4 * 1536 * 4});
     raws.push_back({"WGRN", (size_t)B * 512 * 1536 * 2});
@@ -387,34 +391,59 @@ struct Stage {
 // AdaptiveDecoderBlock on packed rows (ada_norm.py:165-182).
 //   in:  `x` (C_in channels, operand of the optional fused 1x1 shortcut, cin_pad = x pad)
 //   out: dst[:, dst_col : dst_col + C_out] = (conv2(act(norm2(conv1(act(norm1(x)))))) + shortcut(x)) / sqrt(2)
+// 16-bit mode: the InstanceNorm statistics come from the producing GEMM's epilogue instead of a pass over the
+// tensor (STTS_STATS_FUSED=0 switches back).  psx / psy: (sum, sum of squares) quarter partials, see set_layout.
+struct StatsFuse {
+  float* psx = nullptr; int ldx = 0;   // statistics of this block's input; x_ready: already in psx
+  float* psy = nullptr; int ldy = 0;   // scratch for conv1's output
+  size_t nx = 0, ny = 0;               // elements between the sum and the sum-of-squares arrays
+  bool x_ready = false;
+};
+bool stats_fused() {
+  static const bool v = [] { const char* e = std::getenv("STTS_STATS_FUSED"); return e == nullptr || e[0] != '0'; }();
+  return v;
+}
+
 int ada_block(Stage& S, const std::string& name, const Act& x, int cin, int cout, Act& act1, Act& y1, Act& act2,
-              Act& dst, int dst_col, const float* gb, int ldgb, const RowMap& map) {
+              Act& dst, int dst_col, const float* gb, int ldgb, const RowMap& map, StatsFuse* sf = nullptr) {
   Context& c = S.c;
   const PackedGemm& g1 = c.gemm[name + ".conv1"];
   const PackedGemm& g2 = c.gemm[name + ".conv2"];
   float* mean = S.R<float>("MEAN");
   float* rstd = S.R<float>("RSTD");
   double* stats = S.R<double>("STATS");
-  STTS_CK(colstats(x.f, x.ld, cin, map, 0, 1e-5f, stats, mean, rstd, S.st));
-  c.launches++;
+  const bool fuse = sf != nullptr && S.twins && stats_fused() && sf->psx != nullptr && dst_col == 0;
+  if (fuse && sf->x_ready) {
+    STTS_CK(colstats_final_q(sf->psx, sf->psx + sf->nx, sf->ldx, cin, map, 1e-5f, mean, rstd, S.st));
+  } else {
+    STTS_CK(colstats(x.f, x.ld, cin, map, 0, 1e-5f, stats, mean, rstd, S.st));
+    c.launches++;
+  }
   // 16-bit mode: the activations are pure GEMM operands, only their twin is read (no fp32 master store)
   STTS_CK(adain_act(x.f, x.ld, cin, map, mean, rstd, gb + c.fc_off[name + ".norm1"], ldgb, 0.2f, S.twins ? nullptr : act1.f, act1.ld,
                     S.tw(act1), act1.ld, S.st));
   {
     Epi e = S.epi(EPI_BIAS, y1, 0);
     e.outh = nullptr;
+    if (fuse) { e.colsum = sf->psy; e.colsq = sf->psy + sf->ny; e.colst_ld = sf->ldy; }
     STTS_RET(run_gemm(c, g1, GC_BODY, &act1, 0, nullptr, 0, e, map, S.st));
   }
-  STTS_CK(colstats(y1.f, y1.ld, cout, map, 0, 1e-5f, stats, mean, rstd, S.st));
-  c.launches++;
+  if (fuse) {
+    STTS_CK(colstats_final_q(sf->psy, sf->psy + sf->ny, sf->ldy, cout, map, 1e-5f, mean, rstd, S.st));
+  } else {
+    STTS_CK(colstats(y1.f, y1.ld, cout, map, 0, 1e-5f, stats, mean, rstd, S.st));
+    c.launches++;
+  }
   STTS_CK(adain_act(y1.f, y1.ld, cout, map, mean, rstd, gb + c.fc_off[name + ".norm2"], ldgb, 0.2f, S.twins ? nullptr : act2.f, act2.ld,
                     S.tw(act2), act2.ld, S.st));
   {
     Epi e = S.epi(EPI_RES_SCALE, dst, dst_col);
     e.scale = 0.70710678118654752440f;
     if (g2.n_kseg == 1) { e.res = x.f; e.ldr = x.ld; e.rcol0 = 0; }   // identity shortcut
+    if (fuse) { e.colsum = sf->psx; e.colsq = sf->psx + sf->nx; e.colst_ld = sf->ldx; }   // = the next block's input
     STTS_RET(run_gemm(c, g2, GC_BODY, &act2, 0, (g2.n_kseg == 2) ? &x : nullptr, 0, e, map, S.st));
   }
+  if (fuse) sf->x_ready = true;
   return 0;
 }
 
@@ -436,9 +465,12 @@ int run_pe_towers(Context& c, const float* d_x, const float* d_style, float* d_p
   const char* tw[2] = {"F0", "N"};
   for (int t = 0; t < 2; ++t) {
     const std::string base = std::string("pe.") + tw[t];
-    STTS_RET(ada_block(S, base + "0", px, 320, 320, pact, py1, pact, pa, 0, gb, c.J_pe, map));
-    STTS_RET(ada_block(S, base + "1", pa, 320, 320, pact, py1, pact, pb, 0, gb, c.J_pe, map));
-    STTS_RET(ada_block(S, base + "2", pb, 320, 320, pact, py1, pact, pa, 0, gb, c.J_pe, map));
+    StatsFuse sf;    // the tower's first input (PX) is not a conv2 output: x_ready starts false
+    sf.psx = S.R<float>("PSXF"); sf.ldx = 320; sf.nx = (size_t)c.LF.n_tiles * 4 * 320;
+    sf.psy = S.R<float>("PSYF"); sf.ldy = 320; sf.ny = (size_t)c.LF.n_tiles * 4 * 320;
+    STTS_RET(ada_block(S, base + "0", px, 320, 320, pact, py1, pact, pa, 0, gb, c.J_pe, map, &sf));
+    STTS_RET(ada_block(S, base + "1", pa, 320, 320, pact, py1, pact, pb, 0, gb, c.J_pe, map, &sf));
+    STTS_RET(ada_block(S, base + "2", pb, 320, 320, pact, py1, pact, pa, 0, gb, c.J_pe, map, &sf));
     STTS_CK(rowdot(pa.f, pa.ld, 320, map, c.vec[t == 0 ? "pe.F0_proj_w" : "pe.N_proj_w"],
                    c.vec[t == 0 ? "pe.F0_proj_b" : "pe.N_proj_b"], c.LF.d_cu, t == 0 ? d_pitch : d_energy, st));
   }
@@ -460,11 +492,17 @@ int run_decoder_core(Context& c, const float* d_style, cudaStream_t st) {
     Epi e = S.epi(EPI_BIAS, *dst, 512);
     STTS_RET(run_gemm(c, c.gemm["dec.asr_res"], GC_BODY, &x0, 0, nullptr, 0, e, map, st));
   }
-  STTS_RET(ada_block(S, "dec.encode", x0, 130, 512, act0, y1, act, xa, 0, gb, c.J_dec, map));
+  StatsFuse sf;
+  sf.psx = S.R<float>("PSX4"); sf.ldx = 640; sf.nx = (size_t)c.L4.n_tiles * 4 * 640;
+  sf.psy = S.R<float>("PSY4"); sf.ldy = 512; sf.ny = (size_t)c.L4.n_tiles * 4 * 512;
+  if (S.twins && stats_fused()) {   // side channels (asr_res, F0, N: columns 512 .. 577) never change between the blocks
+    STTS_CK(colstats_partial_q(xa.f, xa.ld, 512, 66, map, sf.psx, sf.psx + sf.nx, sf.ldx, st));
+  }
+  STTS_RET(ada_block(S, "dec.encode", x0, 130, 512, act0, y1, act, xa, 0, gb, c.J_dec, map, &sf));
   for (int i = 0; i < 4; ++i) {
     Act& src = (i % 2 == 0) ? xa : xb;
     Act& dst = (i % 2 == 0) ? xb : xa;
-    STTS_RET(ada_block(S, "dec.decode" + std::to_string(i), src, 578, 512, act, y1, act, dst, 0, gb, c.J_dec, map));
+    STTS_RET(ada_block(S, "dec.decode" + std::to_string(i), src, 578, 512, act, y1, act, dst, 0, gb, c.J_dec, map, &sf));
   }
   return 0;
 }
