@@ -427,6 +427,64 @@ struct EpiQuad {
           al(e.outg, e.ldh, e.colh0 + n, 2) && al(e.outl, e.ldh, e.colh0 + n, 2) &&
           (!kHasPre || al(e.res, e.ldr, e.rcol0 + n, 4));
   }
+  // ---- vector path (vec == true): row pointers are set up once per slab (bind) and advanced by a constant
+  // stride, so an iteration is one 16-byte staging read, the math and the stores -- no per-row 64-bit
+  // pointer arithmetic, no null / range checks (they cost more than the math: ~150 instructions per row pair)
+  float* p_o; twin_t* p_oh; __half* p_og; __half* p_ol; const float* p_r;
+  long long s_o, s_h, s_r;     // element strides between consecutive iterations of this lane (2 rows)
+  float scale_;
+  __device__ __forceinline__ void bind(const Epi& e, int r_first) {
+    p_o = e.out != nullptr ? e.out + (size_t)r_first * e.ldo + e.col0 + n : nullptr;
+    p_oh = e.outh != nullptr ? e.outh + (size_t)r_first * e.ldh + e.colh0 + n : nullptr;
+    p_og = e.outg != nullptr ? e.outg + (size_t)r_first * e.ldh + e.colh0 + n : nullptr;
+    p_ol = (e.outg != nullptr && e.outl != nullptr) ? e.outl + (size_t)r_first * e.ldh + e.colh0 + n : nullptr;
+    p_r = (kHasPre && e.res != nullptr) ? e.res + (size_t)r_first * e.ldr + e.rcol0 + n : nullptr;
+    s_o = 2LL * e.ldo; s_h = 2LL * e.ldh; s_r = 2LL * e.ldr;
+    scale_ = e.scale;
+  }
+  __device__ __forceinline__ float4 pre_vec(int k) const {
+    if constexpr (kHasPre) {
+      if (p_r != nullptr) return *reinterpret_cast<const float4*>(p_r + k * s_r);
+    }
+    return make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  __device__ __forceinline__ void apply_vec(int k, float4 a, float4 t) {
+    float x[4] = {a.x + bias[0], a.y + bias[1], a.z + bias[2], a.w + bias[3]};
+    const float tt[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      if constexpr (KIND == EPI_RES_SCALE) x[i] = (x[i] + tt[i]) * scale_;
+      if constexpr (KIND == EPI_SILU) { x[i] = P::dv(x[i], 1.f + P::ex(-x[i])); ss[i] = fmaf(x[i], x[i], ss[i]); }
+      if constexpr (KIND == EPI_ADD) x[i] += tt[i];
+      if constexpr (KIND == EPI_RELU) x[i] = fmaxf(x[i], 0.f);
+      if constexpr (KIND == EPI_GELU) x[i] = 0.5f * x[i] * (1.f + erff(x[i] * 0.70710678118654752440f));
+    }
+    if constexpr (kStats) {
+      if (st) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { sm[i] += x[i]; ss[i] = fmaf(x[i], x[i], ss[i]); }
+      }
+    }
+    if (p_o != nullptr) *reinterpret_cast<float4*>(p_o + k * s_o) = make_float4(x[0], x[1], x[2], x[3]);
+    if (p_oh != nullptr) {
+      const twin2_t t0 = to_twin2(x[0], x[1]), t1 = to_twin2(x[2], x[3]);
+      uint2 w;
+      w.x = *reinterpret_cast<const uint32_t*>(&t0); w.y = *reinterpret_cast<const uint32_t*>(&t1);
+      *reinterpret_cast<uint2*>(p_oh + k * s_h) = w;
+    }
+    if (p_og != nullptr) {
+      const __half2 g0 = __floats2half2_rn(sat16(x[0]), sat16(x[1])), g1 = __floats2half2_rn(sat16(x[2]), sat16(x[3]));
+      uint2 w;
+      w.x = *reinterpret_cast<const uint32_t*>(&g0); w.y = *reinterpret_cast<const uint32_t*>(&g1);
+      *reinterpret_cast<uint2*>(p_og + k * s_h) = w;
+      if (p_ol != nullptr) {
+        const __half2 l0 = __floats2half2_rn(sat16(x[0]) - __low2float(g0), sat16(x[1]) - __high2float(g0));
+        const __half2 l1 = __floats2half2_rn(sat16(x[2]) - __low2float(g1), sat16(x[3]) - __high2float(g1));
+        w.x = *reinterpret_cast<const uint32_t*>(&l0); w.y = *reinterpret_cast<const uint32_t*>(&l1);
+        *reinterpret_cast<uint2*>(p_ol + k * s_h) = w;
+      }
+    }
+  }
   __device__ __forceinline__ float4 pre(const Epi& e, int r) const {
     float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
     if constexpr (kHasPre) {

@@ -193,6 +193,28 @@ __device__ __forceinline__ void quad_slab(const Epi& epi, const float* __restric
   eq.init(epi, col + (lane & 15) * 4);
   const int sub = lane >> 4;
   const float* sp = stg + sub * kStgLd4 + (lane & 15) * 4;
+  if (eq.vec) {                                 // uniform for all slabs but the one that crosses the logical N
+    eq.bind(epi, row0 + sub);
+    const int nit = (nrows - sub + 1) >> 1;     // iterations (2 rows each) with a valid row for this lane
+#pragma unroll 1
+    for (int kb = 0; kb < 16; kb += NB) {
+      float4 pre[NB];
+#pragma unroll
+      for (int i = 0; i < NB; ++i) {
+        pre[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (EpiQuad<KIND, FAST>::kHasPre && kb + i < nit) pre[i] = eq.pre_vec(kb + i);
+      }
+#pragma unroll
+      for (int i = 0; i < NB; ++i) {
+        if (kb + i < nit) {
+          const float4 a = *reinterpret_cast<const float4*>(sp + (kb + i) * (2 * kStgLd4));
+          eq.apply_vec(kb + i, a, pre[i]);
+        }
+      }
+    }
+    eq.finish(epi, tile, q, lane);
+    return;
+  }
 #pragma unroll 1
   for (int rb = 0; rb < 32; rb += 2 * NB) {
     float4 pre[NB];
