@@ -380,8 +380,8 @@ struct EpiPair {
         const float mag = hypotf(re, im);
         const float d = mag + 1e-9f;
         const float ph = atan2f(im / d, re / d);
-        e.out[(size_t)r * e.ldo + e.col0 + c] = mag;
-        e.out2[(size_t)r * e.ldo2 + e.col20 + c] = ph;
+        if (e.out != nullptr) e.out[(size_t)r * e.ldo + e.col0 + c] = mag;
+        if (e.out2 != nullptr) e.out2[(size_t)r * e.ldo2 + e.col20 + c] = ph;
         if (e.outh != nullptr) e.outh[(size_t)r * e.ldh + e.colh0 + c] = to_twin(mag);
         if (e.outh2 != nullptr) e.outh2[(size_t)r * e.ldh2 + e.colh20 + c] = to_twin(ph);
         __half lo;

@@ -122,7 +122,7 @@ int run_prior_flow(Context& c, const float* d_x, const float* d_noise, const flo
 int run_source(Context& c, const float* d_pitch4_dense, const float* d_noise, const float* d_init_phase, float* d_out,
                cudaStream_t st);
 int run_generator_core(Context& c, const float* d_style, const float* d_noise, const float* d_init_phase,
-                       float* d_audio, float* d_logamp, float* d_phase, cudaStream_t st);
+                       float* d_audio, float* d_logamp, float* d_phase, cudaStream_t st, bool lean = false);
 int run_generator_tail(Context& c, const float* d_style, float* d_audio, float* d_logamp, float* d_phase,
                        cudaStream_t st);
 int run_generator_from_stft(Context& c, const float* d_mel, const float* d_style, const float* d_har_spec,

@@ -237,6 +237,59 @@ __device__ __forceinline__ void quad_slab(const Epi& epi, const float* __restric
   eq.finish(epi, tile, q, lane);
 }
 
+// EPI_STFT slab with row pointers bound once (lane = one (re, im) accumulator pair = one bin; staging in the
+// lane-per-pair layout, stride kStgLd): |X| and atan2 phase to whichever of the fp32 masters / fp16 split twins
+// the caller asked for.  Frame 0 of an utterance is exactly real (see epi_apply).
+__device__ __forceinline__ void stft_slab(const Epi& e, const float* __restrict__ stg, int row0, int nrows, int col,
+                                          int seg_first_row, int lane) {
+  const int n = col + 2 * lane;
+  if (n >= e.N) return;
+  const int c = n >> 1;
+  float* p_m = e.out != nullptr ? e.out + (size_t)row0 * e.ldo + e.col0 + c : nullptr;
+  float* p_p = e.out2 != nullptr ? e.out2 + (size_t)row0 * e.ldo2 + e.col20 + c : nullptr;
+  twin_t* p_mh = e.outh != nullptr ? e.outh + (size_t)row0 * e.ldh + e.colh0 + c : nullptr;
+  twin_t* p_ph = e.outh2 != nullptr ? e.outh2 + (size_t)row0 * e.ldh2 + e.colh20 + c : nullptr;
+  __half* p_mg = e.outg != nullptr ? e.outg + (size_t)row0 * e.ldh + e.colh0 + c : nullptr;
+  __half* p_ml = (e.outg != nullptr && e.outl != nullptr) ? e.outl + (size_t)row0 * e.ldh + e.colh0 + c : nullptr;
+  __half* p_pg = e.outg2 != nullptr ? e.outg2 + (size_t)row0 * e.ldh2 + e.colh20 + c : nullptr;
+  __half* p_pl = (e.outg2 != nullptr && e.outl2 != nullptr) ? e.outl2 + (size_t)row0 * e.ldh2 + e.colh20 + c : nullptr;
+  const long long so = e.ldo, so2 = e.ldo2, sh = e.ldh, sh2 = e.ldh2;
+  const int r_real = seg_first_row - row0;      // row of the slab that is frame 0 of its utterance (or outside)
+  const float* sp = stg + 2 * lane;
+#pragma unroll 1
+  for (int rb = 0; rb < nrows; rb += 8) {
+    float2 av[8];
+#pragma unroll
+    for (int rr = 0; rr < 8; ++rr) av[rr] = *reinterpret_cast<const float2*>(sp + (rb + rr) * kStgLd);
+#pragma unroll
+    for (int rr = 0; rr < 8; ++rr) {
+      const int r = rb + rr;
+      if (r < nrows) {
+        const float re = av[rr].x, im = (r == r_real) ? 0.f : av[rr].y;
+        const float mag = hypotf(re, im);
+        const float d = mag + 1e-9f;
+        const float ph = atan2f(im / d, re / d);
+        if (p_m != nullptr) p_m[r * so] = mag;
+        if (p_p != nullptr) p_p[r * so2] = ph;
+        if (p_mh != nullptr) p_mh[r * sh] = to_twin(mag);
+        if (p_ph != nullptr) p_ph[r * sh2] = to_twin(ph);
+        if (p_mg != nullptr) {
+          __half g, l;
+          f16_split(mag, &g, &l);
+          p_mg[r * sh] = g;
+          if (p_ml != nullptr) p_ml[r * sh] = l;
+        }
+        if (p_pg != nullptr) {
+          __half g, l;
+          f16_split(ph, &g, &l);
+          p_pg[r * sh2] = g;
+          if (p_pl != nullptr) p_pl[r * sh2] = l;
+        }
+      }
+    }
+  }
+}
+
 // MODE_F16 doubles as the one-pass fp16 GEMM (runtime instruction-descriptor formats), MODE_F16X3 is
 // the three-pass fp16 split (hi*hi + hi*lo + lo*hi, fp32-grade), MODE_TF32X3 the tf32 split on fp32 operands
 enum { MODE_F16 = 0, MODE_TF32X3 = 1, MODE_F16X3 = 2 };
@@ -455,6 +508,9 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
           *reinterpret_cast<float2*>(stg + lane * kStgLd + j) = make_float2(v[j] * p.acc_scale, v[j + 1] * p.acc_scale);
       }
       __syncwarp();
+      if constexpr (KIND == EPI_STFT) {
+        stft_slab(epi, stg, row0, nrows, n0 + c, seg_first, lane);
+      } else
       if constexpr (EpiPair<KIND, false>::kHasPre) {
         // batches of RB rows: RB independent residual loads in flight per warp, registers bounded
         // (576-thread CTAs of the 256-column tile have 113 registers per thread)
@@ -1074,11 +1130,11 @@ bool use_persistent() {
 }
 
 // STTS_OCC2=<n>: 16-bit-mode GEMMs with at most n K chunks (64 columns each) run as BN = 128, two CTAs
-// per SM (-1 = never).
+// per SM (-1 = never; default 8: pwconv1, prior, the 1x1 flow / decoder projections).
 int occ2_max_chunks() {
   static const int v = [] {
     const char* e = std::getenv("STTS_OCC2");
-    return e != nullptr ? std::atoi(e) : -1;
+    return e != nullptr ? std::atoi(e) : 8;   // measured with the float4 epilogue: pwconv1 -5 %, flow proj -24 %, asr_res -21 %
   }();
   return v;
 }

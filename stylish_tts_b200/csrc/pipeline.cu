@@ -700,8 +700,11 @@ int run_source(Context& c, const float* d_pitch4_dense, const float* d_noise, co
 
 // ----------------------------------------------------------------------------- generator
 // expects CATP[:, 0:512] = mel and P4 = pitch (packed rows)
+// lean: 16-bit mode keeps only what the prior convs read of the source spectrum (the fp16 twins of |X| and
+// phase; their fp32 masters are 430 MB of stores per bench step that nothing consumes).  The module-level
+// entry (stts_generator) keeps the masters: the stage tests read them back.
 int run_generator_core(Context& c, const float* d_style, const float* d_noise, const float* d_init_phase,
-                       float* d_audio, float* d_logamp, float* d_phase, cudaStream_t st) {
+                       float* d_audio, float* d_logamp, float* d_phase, cudaStream_t st, bool lean) {
   if (!c.finalized || c.J_gen == 0) return fail(c, -3, "speech_predictor weights not loaded");
   Stage S(c, st);
   const RowMap map = c.L4.map();
@@ -721,6 +724,7 @@ int run_generator_core(Context& c, const float* d_style, const float* d_noise, c
     if (one_pass_island("gen.amp_prior")) e.outl = nullptr;      // residual twins only for three-pass consumers
     if (one_pass_island("gen.phase_prior")) e.outl2 = nullptr;
     e.seg_start = c.L4.d_seg_start;
+    if (lean && S.twins && e.outg != nullptr && e.outg2 != nullptr) { e.out = nullptr; e.out2 = nullptr; }
     // 16-bit mode: fp16 split operand = explicit frames written by the source kernel -> the "stft16" pack
     STTS_RET(run_gemm(c, c.gemm[S.twins ? "stft16" : "stft"], GC_ISLAND, &src, 0, nullptr, 0, e, map, st));
   }
@@ -868,7 +872,7 @@ int run_speech_frames(Context& c, const float* d_enc_tok, const int* d_cu_tok, c
   STTS_CK(transpose_in(d_noise_prior, c.L4.d_off[0], c.L4.d_cs, 128, map, noise.f, noise.ld, 0, nullptr, 0, 0, st));
   STTS_RET(run_decoder_core(c, d_style, st));
   STTS_RET(run_prior_flow_core(c, xa, d_style, st));
-  return run_generator_core(c, d_style, d_noise_source, d_init_phase, d_audio, d_logamp, d_phase, st);
+  return run_generator_core(c, d_style, d_noise_source, d_init_phase, d_audio, d_logamp, d_phase, st, /*lean=*/true);
 }
 
 }  // namespace stts
