@@ -266,9 +266,10 @@ __device__ __forceinline__ void stft_slab(const Epi& e, const float* __restrict_
       const int r = rb + rr;
       if (r < nrows) {
         const float re = av[rr].x, im = (r == r_real) ? 0.f : av[rr].y;
-        const float mag = hypotf(re, im);
-        const float d = mag + 1e-9f;
-        const float ph = atan2f(im / d, re / d);
+        // |X| without hypot's overflow guard (|X| < 1e5 here) and the phase without the reference's common
+        // positive divisor (re, im) / (|X| + 1e-9): atan2 depends on the ratio and the signs only
+        const float mag = sqrtf(fmaf(re, re, im * im));
+        const float ph = atan2f(im, re);
         if (p_m != nullptr) p_m[r * so] = mag;
         if (p_p != nullptr) p_p[r * so2] = ph;
         if (p_mh != nullptr) p_mh[r * sh] = to_twin(mag);
