@@ -88,26 +88,46 @@ __global__ void __launch_bounds__(128) colstats_partial_q_kernel(const float* __
   }
 }
 
-__global__ void __launch_bounds__(128) colstats_final_q_kernel(const float* __restrict__ psum,
+// block = 32 channels x 8 slices of the utterance's quarters (a long utterance has hundreds of quarters: one
+// thread per channel walking all of them is a serial chain of L2 latencies); fixed-order fp64 combine
+__global__ void __launch_bounds__(256) colstats_final_q_kernel(const float* __restrict__ psum,
                                                                const float* __restrict__ psq, int pld, int C, RowMap map,
                                                                float eps, float* __restrict__ mean,
                                                                float* __restrict__ rstd) {
+  __shared__ double sh_s[8][32], sh_q[8][32];
   const int seg = blockIdx.x;
-  const int c = blockIdx.y * 128 + threadIdx.x;
-  if (c >= C) return;
+  const int c = blockIdx.y * 32 + threadIdx.x;
+  const int sl = threadIdx.y;
   const int t0 = map.seg_start[seg] / 128;
   const int len = map.seg_len[seg];
   const int nq = (len + 31) / 32;              // quarters that hold valid rows (in tile order)
   double s = 0.0, q = 0.0;
-  for (int k = 0; k < nq; ++k) {
-    s += (double)psum[(size_t)(t0 * 4 + k) * pld + c];
-    q += (double)psq[(size_t)(t0 * 4 + k) * pld + c];
+  if (c < C) {
+    const float* ps = psum + (size_t)t0 * 4 * pld + c;
+    const float* pq = psq + (size_t)t0 * 4 * pld + c;
+    int k = sl;
+    for (; k + 24 < nq; k += 32) {             // four independent loads in flight per array
+      const float a0 = ps[(size_t)k * pld], a1 = ps[(size_t)(k + 8) * pld], a2 = ps[(size_t)(k + 16) * pld],
+                  a3 = ps[(size_t)(k + 24) * pld];
+      const float b0 = pq[(size_t)k * pld], b1 = pq[(size_t)(k + 8) * pld], b2 = pq[(size_t)(k + 16) * pld],
+                  b3 = pq[(size_t)(k + 24) * pld];
+      s += ((double)a0 + (double)a1) + ((double)a2 + (double)a3);
+      q += ((double)b0 + (double)b1) + ((double)b2 + (double)b3);
+    }
+    for (; k < nq; k += 8) { s += (double)ps[(size_t)k * pld]; q += (double)pq[(size_t)k * pld]; }
   }
-  const double m = s / len;
-  double var = q / len - m * m;
-  if (var < 0.0) var = 0.0;
-  mean[(size_t)seg * C + c] = (float)m;
-  rstd[(size_t)seg * C + c] = (float)(1.0 / sqrt(var + (double)eps));
+  sh_s[sl][threadIdx.x] = s;
+  sh_q[sl][threadIdx.x] = q;
+  __syncthreads();
+  if (sl == 0 && c < C) {
+#pragma unroll
+    for (int j = 1; j < 8; ++j) { s += sh_s[j][threadIdx.x]; q += sh_q[j][threadIdx.x]; }
+    const double m = s / len;
+    double var = q / len - m * m;
+    if (var < 0.0) var = 0.0;
+    mean[(size_t)seg * C + c] = (float)m;
+    rstd[(size_t)seg * C + c] = (float)(1.0 / sqrt(var + (double)eps));
+  }
 }
 
 cudaError_t colstats_partial_q(const float* x, int ld, int col0, int ncols, const RowMap& map, float* psum, float* psq,
@@ -119,8 +139,8 @@ cudaError_t colstats_partial_q(const float* x, int ld, int col0, int ncols, cons
 
 cudaError_t colstats_final_q(const float* psum, const float* psq, int pld, int C, const RowMap& map, float eps,
                              float* mean, float* rstd, cudaStream_t st) {
-  dim3 g(map.n_seg, (C + 127) / 128);
-  colstats_final_q_kernel<<<g, 128, 0, st>>>(psum, psq, pld, C, map, eps, mean, rstd);
+  dim3 g(map.n_seg, (C + 31) / 32), b(32, 8);
+  colstats_final_q_kernel<<<g, b, 0, st>>>(psum, psq, pld, C, map, eps, mean, rstd);
   return cudaGetLastError();
 }
 
