@@ -156,9 +156,9 @@ def run_reference_arm(args, rank: int, world: int):
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the largest GEMM of the step (the forward STFT,
-# "stft16") from the `ncu --set full` capture summarised in profiles/r1_full_stft16.txt: 290.8 MB read + 651.5 MB
-# written, against 272 MB (fp16 frame operand, hi + lo) + 663 MB (|X| and phase: fp32 + fp16 hi / lo twins) algorithmic
-TRAFFIC_TOP_KERNEL = 290.849536e6 + 651.486464e6
+# "stft16") from the `ncu --set full` capture summarised in profiles/r1_full_stft16.txt: 285.9 MB read + 205.7 MB
+# written, against 272 MB (fp16 frame operand, hi + lo) + 215 MB (fp16 twins of |X| and phase) algorithmic
+TRAFFIC_TOP_KERNEL = 285.899776e6 + 205.674496e6
 
 
 _JSON_FD = None
@@ -338,7 +338,7 @@ def main():
             "frac": achieved / peak_tf if peak_tf else None,
             # dram__bytes_read.sum + dram__bytes_write.sum of the largest GEMM launch of the step (bytes per launch)
             "traffic": TRAFFIC_TOP_KERNEL if args.precision in ("f16", "bf16") else None,
-            "traffic_kernel": "stft16, the largest launch (algorithmic 272 MB in + 663 MB out), profiles/r1_full_stft16.txt",
+            "traffic_kernel": "stft16, the largest launch (algorithmic 272 MB in + 215 MB out), profiles/r1_full_stft16.txt",
             "kernel": "conv_gemm_tc_kernel (tcgen05/TMA implicit-GEMM conv1d), all launches of the timed region"
                       if args.precision != "fp32" else "conv_gemm_simt_kernel",
             "peak_source": pk["source"] + " bf16_tflops_sustained",
