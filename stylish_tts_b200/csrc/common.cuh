@@ -266,34 +266,6 @@ struct EpiPair {
     }
     return t;
   }
-  // First element pre() reads for row r of the 64-column slab starting at accumulator column c0 (null:
-  // nothing is read).  The epilogue warps are idle during the main loop: they pull these rows into L2
-  // (prefetch.global.L2, one row per lane) so that the epilogue's residual loads do not wait on HBM.
-  static __device__ __forceinline__ const float* pre_base(const Epi& e, int r, int c0, int* n_floats) {
-    *n_floats = 64;
-    if (c0 >= e.N) return nullptr;
-    if constexpr (KIND == EPI_RES_SCALE || KIND == EPI_ADD) {
-      return e.res != nullptr ? e.res + (size_t)r * e.ldr + e.rcol0 + c0 : nullptr;
-    } else if constexpr (KIND == EPI_RESSKIP) {
-      if (c0 < e.split) return e.out + (size_t)r * e.ldo + e.col0 + c0;
-      return e.accumulate2 ? e.out2 + (size_t)r * e.ldo2 + e.col20 + (c0 - e.split) : nullptr;
-    } else if constexpr (KIND == EPI_COUPLE) {
-      *n_floats = 32;
-      return e.out + (size_t)r * e.ldo + e.col0 + (c0 >> 1);
-    } else if constexpr (KIND == EPI_PRIOR) {
-      *n_floats = 32;
-      return e.res + (size_t)r * e.ldr + e.rcol0 + (c0 >> 1);
-    }
-    return nullptr;
-  }
-  static __device__ __forceinline__ void prefetch_pre(const Epi& e, int r, int c0) {
-    int nf;
-    const float* p = pre_base(e, r, c0, &nf);
-    if (p == nullptr) return;
-    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
-    asm volatile("prefetch.global.L2 [%0];" ::"l"(p + nf - 1));
-    if (nf > 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + 32));
-  }
   static __device__ __forceinline__ void store2(float* o, twin_t* oh, float x0, float x1, bool both,
                                                 __half* og = nullptr, __half* ol = nullptr) {
     if (both) {

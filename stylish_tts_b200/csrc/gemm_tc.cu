@@ -333,6 +333,7 @@ __global__ void __launch_bounds__(64 + 2 * BN, OCC)
 conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant__ CUtensorMap mapA1,
                     const __grid_constant__ CUtensorMap mapA0lo, const __grid_constant__ CUtensorMap mapA1lo,
                     const __grid_constant__ CUtensorMap mapW, const __grid_constant__ CUtensorMap mapWlo,
+                    const __grid_constant__ CUtensorMap mapWt, const __grid_constant__ CUtensorMap mapWtlo,
                     const TcParams p, const Epi epi, const RowMap map) {
   using C = Cfg<MODE, BN, OCC>;
   const int tile = blockIdx.y;
@@ -342,6 +343,10 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
   const int m0 = tile * 128;
   const int n0 = blockIdx.x * BN;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // Tail column tile with <= 16 live columns (N = 1 025 output heads, N = 2 050 STFT): 16-row weight boxes and
+  // N = 16 MMAs instead of a full BN-wide tile of padding (mapWt / mapWtlo: the same weights, box of 16 rows)
+  const bool tail = !C::kTF32 && (epi.N - n0) <= 16;
+  constexpr uint32_t kTailBytes = 16 * 128;
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -372,7 +377,8 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t idesc = C::kIdescBase | (p.ab_fmt << 7) | (p.ab_fmt << 10);
+  const uint32_t idesc_full = C::kIdescBase | (p.ab_fmt << 7) | (p.ab_fmt << 10);
+  const uint32_t idesc = tail ? ((idesc_full & ~(0x3Fu << 17)) | ((16u >> 3) << 17)) : idesc_full;
 
   auto stage_ptr = [&](int s) { return smem + (size_t)s * C::kStageBytes; };
 
@@ -384,10 +390,13 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
       int ks = 0, tap = 0, cc = 0;
       int kcol = 0;
       const int wrow = n0 + seg * p.w_seg_rows;
+      const CUtensorMap* mw = tail ? &mapWt : &mapW;
+      const CUtensorMap* mwlo = tail ? &mapWtlo : &mapWlo;
+      const uint32_t tx = tail ? C::kTxBytes - (C::kSplit ? 2u : 1u) * ((uint32_t)C::kBTile - kTailBytes) : C::kTxBytes;
       for (int ch = 0; ch < p.n_chunks; ++ch) {
         mbar_wait(&empty[stage], phase ^ 1, 1);
         uint8_t* sp = stage_ptr(stage);
-        mbar_expect_tx(&full[stage], C::kTxBytes);
+        mbar_expect_tx(&full[stage], tx);
         const CUtensorMap* ma = (ks == 0) ? &mapA0 : &mapA1;
         tma_load_2d(sp, ma, &full[stage], p.col0[ks] + cc * C::kBK, m0 + tap - p.pad[ks]);
         if constexpr (C::kSplit) {
@@ -395,10 +404,10 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
             const CUtensorMap* ml = (ks == 0) ? &mapA0lo : &mapA1lo;
             tma_load_2d(sp + C::kATile, ml, &full[stage], p.col0[ks] + cc * C::kBK, m0 + tap - p.pad[ks]);
           }
-          tma_load_2d(sp + 2 * C::kATile, &mapW, &full[stage], kcol, wrow);
-          tma_load_2d(sp + 2 * C::kATile + C::kBTile, &mapWlo, &full[stage], kcol, wrow);
+          tma_load_2d(sp + 2 * C::kATile, mw, &full[stage], kcol, wrow);
+          tma_load_2d(sp + 2 * C::kATile + C::kBTile, mwlo, &full[stage], kcol, wrow);
         } else {
-          tma_load_2d(sp + C::kATile, &mapW, &full[stage], kcol, wrow);
+          tma_load_2d(sp + C::kATile, mw, &full[stage], kcol, wrow);
         }
         kcol += C::kBK;
         if (++cc == p.cin_chunks[ks]) { cc = 0; if (++tap == p.taps[ks]) { tap = 0; ++ks; } }
@@ -462,10 +471,6 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
         if (lane == 0) mbar_arrive(&conv[stage]);
         if (++stage == C::kStages) { stage = 0; phase ^= 1; }
       }
-    }
-    if constexpr (!C::kTF32 && EpiPair<KIND, false>::kHasPre) {
-      const int pq = warp & 3, pc = ((warp - 2) >> 2) * 64;
-      if (pq * 32 + lane < nvalid) EpiPair<KIND, false>::prefetch_pre(epi, m0 + pq * 32 + lane, n0 + pc);
     }
     mbar_wait(accum, 0, 5);
     tc_fence_after();
@@ -575,8 +580,8 @@ struct PCfg {
 template <int KIND>
 __global__ void __launch_bounds__(PCfg::kThreads, 1)
 conv_gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant__ CUtensorMap mapA1,
-                               const __grid_constant__ CUtensorMap mapW, const TcParams p, const Epi epi,
-                               const RowMap map, const int n_tiles_n) {
+                               const __grid_constant__ CUtensorMap mapW, const __grid_constant__ CUtensorMap mapWt,
+                               const TcParams p, const Epi epi, const RowMap map, const int n_tiles_n) {
   using C = PCfg;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int total_tiles = map.n_tiles * n_tiles_n;
@@ -620,14 +625,17 @@ conv_gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap mapA0, const 
         if (seg < 0) continue;
         const int m0 = tile * 128;
         const int wrow = n0 + seg * p.w_seg_rows;
+        const bool tail = (epi.N - n0) <= 16;      // <= 16 live columns: 16-row weight box, N = 16 MMAs
+        const CUtensorMap* mw = tail ? &mapWt : &mapW;
+        const uint32_t tx = tail ? C::kATile + 16 * 128 : C::kStageBytes;
         int ks = 0, tap = 0, cc = 0, kcol = 0;
         for (int ch = 0; ch < p.n_chunks; ++ch) {
           mbar_wait(&empty[stage], phase ^ 1, 11);
           uint8_t* sp = stage_ptr(stage);
-          mbar_expect_tx(&full[stage], C::kStageBytes);
+          mbar_expect_tx(&full[stage], tx);
           const CUtensorMap* ma = (ks == 0) ? &mapA0 : &mapA1;
           tma_load_2d(sp, ma, &full[stage], p.col0[ks] + cc * C::kBK, m0 + tap - p.pad[ks]);
-          tma_load_2d(sp + C::kATile, &mapW, &full[stage], kcol, wrow);
+          tma_load_2d(sp + C::kATile, mw, &full[stage], kcol, wrow);
           kcol += C::kBK;
           if (++cc == p.cin_chunks[ks]) { cc = 0; if (++tap == p.taps[ks]) { tap = 0; ++ks; } }
           if (++stage == C::kStages) { stage = 0; phase ^= 1; }
@@ -643,6 +651,8 @@ conv_gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap mapA0, const 
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
         const int tile = t / n_tiles_n;
         if (map.tile_seg[tile] < 0) continue;
+        const bool tail = (epi.N - (t - tile * n_tiles_n) * C::kBN) <= 16;
+        const uint32_t idesc = tail ? ((C::kIdesc & ~(0x3Fu << 17)) | ((16u >> 3) << 17)) : C::kIdesc;
         const int buf = it & 1, use = it >> 1;
         if (use > 0) mbar_wait(&tmem_empty[buf], (uint32_t)((use - 1) & 1), 12);   // epilogue drained this buffer
         tc_fence_after();
@@ -653,7 +663,7 @@ conv_gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap mapA0, const 
           const uint32_t a = smem_u32(stage_ptr(stage)), b = a + C::kATile;
 #pragma unroll
           for (int k = 0; k < C::kBK / C::kUmmaK; ++k)
-            tc_mma<false>(acc, make_sdesc(a + k * 32), make_sdesc(b + k * 32), C::kIdesc, (ch | k) != 0);
+            tc_mma<false>(acc, make_sdesc(a + k * 32), make_sdesc(b + k * 32), idesc, (ch | k) != 0);
           tc_commit(&empty[stage]);
           if (++stage == C::kStages) { stage = 0; phase ^= 1; }
         }
@@ -889,7 +899,6 @@ wn_layer_fused_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_con
     const int q = warp & 3;            // TMEM lane quarter this warp may read (hardware rule)
     const int slab = ew >> 2;          // 64 accumulator columns = 32 gated channels
     using EG = EpiPair<EPI_GATE, true>;
-    if (q * 32 + lane < nvalid) EpiPair<EPI_RESSKIP, true>::prefetch_pre(epi, m0 + q * 32 + lane, slab * 64);
     mbar_wait(accum1, 0, 25);
     tc_fence_after();
     {
@@ -1066,6 +1075,15 @@ cudaError_t launch_one(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
     if (!get_map(g.W, g.Npad, g.Ktot, 4, BN, &mW)) return cudaErrorNotSupported;
     if (!get_map(g.W + (size_t)g.Npad * g.Ktot, g.Npad, g.Ktot, 4, BN, &mWlo)) return cudaErrorNotSupported;
   }
+  // 16-row boxes of the same weights for a tail column tile (unused unless N leaves <= 16 columns in the last tile)
+  CUtensorMap mWt = mW, mWtlo = mWlo;
+  if (MODE != MODE_TF32X3 && g.epi.N % BN != 0 && g.epi.N % BN <= 16) {
+    const bool per_seg = MODE == MODE_F16 && !g.f16 && g.Wh_seg != nullptr;
+    const void* w = per_seg ? (const void*)g.Wh_seg : (const void*)g.Wg;
+    if (!get_map(w, per_seg ? g.Npad * map.n_seg : g.Npad, g.Ktot, 2, 16, &mWt)) return cudaErrorNotSupported;
+    mWtlo = mWt;
+    if (MODE == MODE_F16X3 && !get_map(g.Wl, g.Npad, g.Ktot, 2, 16, &mWtlo)) return cudaErrorNotSupported;
+  }
   auto kern = conv_gemm_tc_kernel<MODE, BN, KIND, OCC>;
   static bool attr_done = false;
   if (!attr_done) {
@@ -1074,7 +1092,7 @@ cudaError_t launch_one(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
     attr_done = true;
   }
   dim3 grid((g.epi.N + BN - 1) / BN, map.n_tiles);
-  kern<<<grid, C::kThreads, C::kSmem, st>>>(mA[0], mA[1], mAlo[0], mAlo[1], mW, mWlo, p, g.epi, map);
+  kern<<<grid, C::kThreads, C::kSmem, st>>>(mA[0], mA[1], mAlo[0], mAlo[1], mW, mWlo, mWt, mWtlo, p, g.epi, map);
   return cudaGetLastError();
 }
 
@@ -1106,6 +1124,10 @@ cudaError_t launch_persistent(const ConvGemm& g, const RowMap& map, cudaStream_t
   p.w_seg_rows = per_seg ? g.Npad : 0;
   p.ab_fmt = 0u;
   p.acc_scale = per_seg ? 1.f : g.acc_scale;
+  CUtensorMap mWt = mW;
+  if (g.epi.N % C::kBN != 0 && g.epi.N % C::kBN <= 16 &&
+      !get_map(w, per_seg ? g.Npad * map.n_seg : g.Npad, g.Ktot, 2, 16, &mWt))
+    return cudaErrorNotSupported;
   auto kern = conv_gemm_tc_persistent_kernel<KIND>;
   static bool attr_done = false;
   static int n_sm = 0;
@@ -1120,7 +1142,7 @@ cudaError_t launch_persistent(const ConvGemm& g, const RowMap& map, cudaStream_t
   const int n_tiles_n = (g.epi.N + C::kBN - 1) / C::kBN;
   const int total = map.n_tiles * n_tiles_n;
   const int grid = total < n_sm ? total : n_sm;
-  kern<<<grid, C::kThreads, C::kSmem, st>>>(mA[0], mA[1], mW, p, g.epi, map, n_tiles_n);
+  kern<<<grid, C::kThreads, C::kSmem, st>>>(mA[0], mA[1], mW, mWt, p, g.epi, map, n_tiles_n);
   return cudaGetLastError();
 }
 
