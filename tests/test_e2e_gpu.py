@@ -178,3 +178,33 @@ def test_cuda_graph_replay_matches_eager_launches():
     o2 = syn.synthesize(toks2, durations=durs, frames=frames, graph=True)
     for i in range(3):
         assert torch.equal(o2["pitch"][i], e2["pitch"][i])
+
+
+def test_full_size_batch_properties_f16():
+    """BASELINE configs[1] at full size (32 mixed 0.25-10 s utterances, 437 hop-75 tiles) in 16-bit mode, through
+    size-independent properties: run-to-run bit stability (fused WaveNet layer, epilogue statistics, persistent and
+    tail tiles are all deterministic), utterances do not interact (an utterance synthesised alone equals its slot
+    of the batch), output length / range / finiteness."""
+    from bench import workload
+    from stylish_tts_b200 import fixture
+    syn = synthesizer("f16")
+    tokens, durs, frames = workload(0)
+    g = torch.Generator().manual_seed(2024)
+    noise = [fixture.draw_noise(f, g) for f in frames]
+    a = syn.synthesize(tokens, durations=durs, noise=noise)
+    syn.check()
+    pe = [(a["pitch"][i].clone(), a["energy"][i].clone()) for i in range(len(tokens))]
+    audio_a = [x.clone() for x in a["audio"]]
+    b = syn.synthesize(tokens, durations=durs, noise=noise, pitch_energy=pe)
+    c = syn.synthesize(tokens, durations=durs, noise=noise, pitch_energy=pe)
+    for i, f in enumerate(frames):
+        assert audio_a[i].numel() == 300 * f
+        assert bool(torch.isfinite(audio_a[i]).all()) and float(audio_a[i].abs().max()) <= 1.0
+        assert torch.equal(b["audio"][i], c["audio"][i]), i                  # run-to-run bit stable
+    worst = 0.0
+    for i in (0, 7, 19, 31, int(max(range(len(frames)), key=lambda k: frames[k])),
+              int(min(range(len(frames)), key=lambda k: frames[k]))):
+        one = syn.synthesize([tokens[i]], durations=[durs[i]], noise=[noise[i]], pitch_energy=[pe[i]])
+        worst = max(worst, maxabs(one["audio"][0], c["audio"][i]))
+    _log("f16.fullsize.alone_vs_batch", worst)
+    assert worst <= 2e-5, worst                                              # utterances do not interact
