@@ -13,6 +13,9 @@ namespace stts {
 // twin `specg` and its residual `specl` may be null (only what the inverse-DFT GEMM of the current
 // precision mode reads is written).  Row seg_end (one past the last
 // frame, a guard row of the layout) receives the replicate-padded frame.
+// FAST (16-bit mode, only the fp16 twin is written: 2^-12 operand rounding): __expf and MUFU sin / cos after a
+// Cody-Waite reduction to [-pi, pi] (absolute error ~5e-7) instead of the libm paths.
+template <bool FAST>
 __global__ void __launch_bounds__(256) polar_kernel(const float* __restrict__ la, const float* __restrict__ ph, int ld,
                                                     int n_bins, RowMap map, float* __restrict__ spec, int lds,
                                                     __half* __restrict__ specg, int ldsh,
@@ -24,32 +27,45 @@ __global__ void __launch_bounds__(256) polar_kernel(const float* __restrict__ la
   const int m0 = tile * 128;
   const bool last = (m0 + nvalid == map.seg_start[seg] + map.seg_len[seg]);
   const int rows = nvalid + (last ? 1 : 0);
-  const int total = rows * n_bins;
-  for (int i = blockIdx.y * blockDim.x + threadIdx.x; i < total; i += gridDim.y * blockDim.x) {
-    const int lr = i / n_bins, k = i - lr * n_bins;
+  for (int lr = blockIdx.y; lr < rows; lr += gridDim.y) {
     const int srow = m0 + (lr < nvalid ? lr : nvalid - 1);
-    const float a = expf(la[(size_t)srow * ld + k]);
-    const float p = ph[(size_t)srow * ld + k];
-    float sn, cs;
-    sincosf(p, &sn, &cs);
-    const float re = a * cs, im = a * sn;
-    const size_t o = (size_t)(m0 + lr) * lds + 2 * k;
-    if (spec != nullptr) *reinterpret_cast<float2*>(spec + o) = make_float2(re, im);
-    if (specg != nullptr) {   // fp16 twins (pre-scaled by gscale: e^logamp may exceed the fp16 range)
-      const size_t og = (size_t)(m0 + lr) * ldsh + 2 * k;
-      const float sr = fminf(fmaxf(re * gscale, -65504.f), 65504.f), si = fminf(fmaxf(im * gscale, -65504.f), 65504.f);
-      const __half2 g = __floats2half2_rn(sr, si);
-      *reinterpret_cast<__half2*>(specg + og) = g;
-      if (specl != nullptr)
-        *reinterpret_cast<__half2*>(specl + og) = __floats2half2_rn(sr - __low2float(g), si - __high2float(g));
+    const float* lap = la + (size_t)srow * ld;
+    const float* php = ph + (size_t)srow * ld;
+    for (int k = threadIdx.x; k < n_bins; k += blockDim.x) {
+      float a, sn, cs;
+      const float p = php[k];
+      if constexpr (FAST) {
+        a = __expf(lap[k]);
+        const float n = rintf(p * 0.15915494309189535f);
+        float r = fmaf(n, -6.28318548202514648f, p);        // 2 pi = hi + lo (fp32 split)
+        r = fmaf(n, 1.74845553e-7f, r);
+        __sincosf(r, &sn, &cs);
+      } else {
+        a = expf(lap[k]);
+        sincosf(p, &sn, &cs);
+      }
+      const float re = a * cs, im = a * sn;
+      const size_t o = (size_t)(m0 + lr) * lds + 2 * k;
+      if (spec != nullptr) *reinterpret_cast<float2*>(spec + o) = make_float2(re, im);
+      if (specg != nullptr) {   // fp16 twins (pre-scaled by gscale: e^logamp may exceed the fp16 range)
+        const size_t og = (size_t)(m0 + lr) * ldsh + 2 * k;
+        const float sr = fminf(fmaxf(re * gscale, -65504.f), 65504.f), si = fminf(fmaxf(im * gscale, -65504.f), 65504.f);
+        const __half2 g = __floats2half2_rn(sr, si);
+        *reinterpret_cast<__half2*>(specg + og) = g;
+        if (specl != nullptr)
+          *reinterpret_cast<__half2*>(specl + og) = __floats2half2_rn(sr - __low2float(g), si - __high2float(g));
+      }
     }
   }
 }
 
 cudaError_t polar_spec(const float* logamp, const float* phase, int ld, int n_bins, const RowMap& map, float* spec,
                        int lds, __half* specg, int ldsh, __half* specl, float gscale, cudaStream_t st) {
-  dim3 grid(map.n_tiles, 4);
-  polar_kernel<<<grid, 256, 0, st>>>(logamp, phase, ld, n_bins, map, spec, lds, specg, ldsh, specl, gscale);
+  dim3 grid(map.n_tiles, 16);
+  if (spec == nullptr && specl == nullptr && specg != nullptr)
+    polar_kernel<true><<<grid, 256, 0, st>>>(logamp, phase, ld, n_bins, map, spec, lds, specg, ldsh, specl, gscale);
+  else
+    polar_kernel<false><<<grid, 256, 0, st>>>(logamp, phase, ld, n_bins, map, spec, lds, specg, ldsh, specl, gscale);
   return cudaGetLastError();
 }
 
