@@ -13,6 +13,9 @@ namespace stts {
 
 // ------------------------------------------------------------------------------ embedding
 // x[row(seg, t), :] = table[tok[cu_tok[seg] + t], :]   (table already scaled by sqrt(C))
+// The copy / gather kernels of the token layout have only n_tiles (~50, or 1 for a single utterance) row tiles:
+// kCopySplit CTAs share a tile's elements so that the launch is not one long serial loop per SM
+constexpr int kCopySplit = 8;
 __global__ void __launch_bounds__(128) embed_kernel(const int* __restrict__ tok, const int* __restrict__ cu_tok,
                                                     const float* __restrict__ table, int C, int n_vocab, RowMap map,
                                                     float* __restrict__ x, int ldx) {
@@ -21,7 +24,7 @@ __global__ void __launch_bounds__(128) embed_kernel(const int* __restrict__ tok,
   if (seg < 0) return;
   const int nvalid = map.tile_nvalid[tile];
   const int t0 = tile * 128 - map.seg_start[seg];
-  for (int i = threadIdx.x; i < nvalid * C; i += blockDim.x) {
+  for (int i = blockIdx.y * blockDim.x + threadIdx.x; i < nvalid * C; i += gridDim.y * blockDim.x) {
     const int lr = i / C, c = i - lr * C;
     int id = tok[cu_tok[seg] + t0 + lr];
     id = id < 0 ? 0 : (id >= n_vocab ? n_vocab - 1 : id);
@@ -31,7 +34,7 @@ __global__ void __launch_bounds__(128) embed_kernel(const int* __restrict__ tok,
 
 cudaError_t embed_tokens(const int* tok, const int* cu_tok, const float* table, int C, int n_vocab, const RowMap& map,
                          float* x, int ldx, cudaStream_t st) {
-  embed_kernel<<<map.n_tiles, 128, 0, st>>>(tok, cu_tok, table, C, n_vocab, map, x, ldx);
+  embed_kernel<<<dim3(map.n_tiles, kCopySplit), 128, 0, st>>>(tok, cu_tok, table, C, n_vocab, map, x, ldx);
   return cudaGetLastError();
 }
 
@@ -491,7 +494,7 @@ __global__ void __launch_bounds__(256) rows_to_dense_kernel(const float* __restr
   if (seg < 0) return;
   const int nvalid = map.tile_nvalid[tile];
   const int t0 = tile * 128 - map.seg_start[seg];
-  for (int i = threadIdx.x; i < nvalid * C; i += blockDim.x) {
+  for (int i = blockIdx.y * blockDim.x + threadIdx.x; i < nvalid * C; i += gridDim.y * blockDim.x) {
     const int lr = i / C, c = i - lr * C;
     dst[(size_t)(cu[seg] + t0 + lr) * C + c] = src[(size_t)(tile * 128 + lr) * ld + c];
   }
@@ -499,7 +502,7 @@ __global__ void __launch_bounds__(256) rows_to_dense_kernel(const float* __restr
 
 cudaError_t rows_to_dense(const float* src, int ld, int C, const RowMap& map, const int* cu, float* dst,
                           cudaStream_t st) {
-  rows_to_dense_kernel<<<map.n_tiles, 256, 0, st>>>(src, ld, C, map, cu, dst);
+  rows_to_dense_kernel<<<dim3(map.n_tiles, kCopySplit), 256, 0, st>>>(src, ld, C, map, cu, dst);
   return cudaGetLastError();
 }
 
@@ -544,7 +547,7 @@ __global__ void __launch_bounds__(256) dense_to_rows_kernel(const float* __restr
   if (seg < 0) return;
   const int nvalid = map.tile_nvalid[tile];
   const int t0 = tile * 128 - map.seg_start[seg];
-  for (int i = threadIdx.x; i < nvalid * C; i += blockDim.x) {
+  for (int i = blockIdx.y * blockDim.x + threadIdx.x; i < nvalid * C; i += gridDim.y * blockDim.x) {
     const int lr = i / C, c = i - lr * C;
     dst[(size_t)(tile * 128 + lr) * ld + col0 + c] = src[(size_t)(cu[seg] + t0 + lr) * C + c];
   }
@@ -552,7 +555,7 @@ __global__ void __launch_bounds__(256) dense_to_rows_kernel(const float* __restr
 
 cudaError_t dense_to_rows(const float* src, int C, const RowMap& map, const int* cu, float* dst, int ld, int col0,
                           cudaStream_t st) {
-  dense_to_rows_kernel<<<map.n_tiles, 256, 0, st>>>(src, C, map, cu, dst, ld, col0);
+  dense_to_rows_kernel<<<dim3(map.n_tiles, kCopySplit), 256, 0, st>>>(src, C, map, cu, dst, ld, col0);
   return cudaGetLastError();
 }
 
@@ -563,14 +566,14 @@ __global__ void __launch_bounds__(256) seg_broadcast_kernel(const float* __restr
   const int seg = map.tile_seg[tile];
   if (seg < 0) return;
   const int nvalid = map.tile_nvalid[tile];
-  for (int i = threadIdx.x; i < nvalid * C; i += blockDim.x) {
+  for (int i = blockIdx.y * blockDim.x + threadIdx.x; i < nvalid * C; i += gridDim.y * blockDim.x) {
     const int lr = i / C, c = i - lr * C;
     dst[(size_t)(tile * 128 + lr) * ld + col0 + c] = vec[(size_t)seg * C + c];
   }
 }
 
 cudaError_t seg_broadcast(const float* vec, int C, const RowMap& map, float* dst, int ld, int col0, cudaStream_t st) {
-  seg_broadcast_kernel<<<map.n_tiles, 256, 0, st>>>(vec, C, map, dst, ld, col0);
+  seg_broadcast_kernel<<<dim3(map.n_tiles, kCopySplit), 256, 0, st>>>(vec, C, map, dst, ld, col0);
   return cudaGetLastError();
 }
 
