@@ -251,7 +251,7 @@ __global__ void __launch_bounds__(256) expand_tokens_kernel(const float* __restr
   const int nvalid = map.tile_nvalid[tile];
   const int f_base = tile * 128 - map.seg_start[seg];
   const int total = nvalid * C;
-  for (int i = threadIdx.x; i < total; i += blockDim.x) {
+  for (int i = blockIdx.y * blockDim.x + threadIdx.x; i < total; i += gridDim.y * blockDim.x) {
     const int lr = i / C, c = i - lr * C;
     const int f = (f_base + lr) / div;
     const int t = tok_off[seg] + idx[cu_f[seg] + f];
@@ -265,7 +265,7 @@ __global__ void __launch_bounds__(256) expand_tokens_kernel(const float* __restr
 cudaError_t expand_tokens(const float* tok, int C, const int* idx, const int* cu_f, const int* tok_off, int div,
                           const RowMap& map, float* out, int ldo, int col0, twin_t* outh, int ldh, int colh0,
                           cudaStream_t st) {
-  expand_tokens_kernel<<<map.n_tiles, 256, 0, st>>>(tok, C, idx, cu_f, tok_off, div, map, out, ldo, col0, outh, ldh,
+  expand_tokens_kernel<<<dim3(map.n_tiles, 4), 256, 0, st>>>(tok, C, idx, cu_f, tok_off, div, map, out, ldo, col0, outh, ldh,
                                                     colh0);
   return cudaGetLastError();
 }
@@ -748,7 +748,7 @@ __global__ void __launch_bounds__(256) rowdot_kernel(const float* __restrict__ x
   if (seg < 0) return;
   const int nvalid = map.tile_nvalid[tile];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int lr = warp; lr < nvalid; lr += 8) {
+  for (int lr = warp + 8 * blockIdx.y; lr < nvalid; lr += 8 * gridDim.y) {
     const size_t r = (size_t)tile * 128 + lr;
     float s = 0.f;
     for (int c = lane; c < C; c += 32) s = fmaf(x[r * ldx + c], w[c], s);
@@ -759,7 +759,7 @@ __global__ void __launch_bounds__(256) rowdot_kernel(const float* __restrict__ x
 
 cudaError_t rowdot(const float* x, int ldx, int C, const RowMap& map, const float* w, const float* bias, const int* cu,
                    float* dense, cudaStream_t st) {
-  rowdot_kernel<<<map.n_tiles, 256, 0, st>>>(x, ldx, C, map, w, bias, cu, dense);
+  rowdot_kernel<<<dim3(map.n_tiles, 4), 256, 0, st>>>(x, ldx, C, map, w, bias, cu, dense);
   return cudaGetLastError();
 }
 
