@@ -11,27 +11,38 @@ namespace stts {
 // nn.InstanceNorm1d eps 1e-5, biased variance); GRN needs the L2 norm over time
 // (generator.py:496-498).  Two deterministic stages (no float atomics): per-tile partial sums in
 // fp64, then a per-segment reduction in tile order.
-__global__ void __launch_bounds__(128) colstats_partial_kernel(const float* __restrict__ x, int ld, int C,
+// block = 128 channels x 4 row groups (rows lr = g, g + 4, ...): a quarter of the serial chain of one thread per
+// channel; the four fp64 partials are combined in fixed order
+__global__ void __launch_bounds__(512) colstats_partial_kernel(const float* __restrict__ x, int ld, int C,
                                                                RowMap map, double* __restrict__ psum,
                                                                double* __restrict__ psq) {
+  __shared__ double sh_s[4][128], sh_q[4][128];
   const int tile = blockIdx.x;
   if (map.tile_seg[tile] < 0) return;
   const int nvalid = map.tile_nvalid[tile];
   const int c = blockIdx.y * 128 + threadIdx.x;
-  if (c >= C) return;
-  const float* p = x + (size_t)tile * 128 * ld + c;
+  const int g = threadIdx.y;
   double s = 0.0, q = 0.0;
-  int i = 0;
-  for (; i + 8 <= nvalid; i += 8) {
-    float v[8];
+  if (c < C) {
+    const float* p = x + (size_t)tile * 128 * ld + c;
+    int i = g;
+    for (; i + 28 < nvalid; i += 32) {
+      float v[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) v[j] = p[(size_t)(i + j) * ld];
+      for (int j = 0; j < 8; ++j) v[j] = p[(size_t)(i + 4 * j) * ld];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) { const double d = v[j]; s += d; q = fma(d, d, q); }
+      for (int j = 0; j < 8; ++j) { const double d = v[j]; s += d; q = fma(d, d, q); }
+    }
+    for (; i < nvalid; i += 4) { const double d = p[(size_t)i * ld]; s += d; q = fma(d, d, q); }
   }
-  for (; i < nvalid; ++i) { const double d = p[(size_t)i * ld]; s += d; q = fma(d, d, q); }
-  psum[(size_t)tile * C + c] = s;
-  psq[(size_t)tile * C + c] = q;
+  sh_s[g][threadIdx.x] = s;
+  sh_q[g][threadIdx.x] = q;
+  __syncthreads();
+  if (g == 0 && c < C) {
+    for (int j = 1; j < 4; ++j) { s += sh_s[j][threadIdx.x]; q += sh_q[j][threadIdx.x]; }
+    psum[(size_t)tile * C + c] = s;
+    psq[(size_t)tile * C + c] = q;
+  }
 }
 
 // mode 0: out0 = mean, out1 = 1/sqrt(var + eps)   mode 1: out0 = sqrt(sum x^2)
@@ -63,7 +74,7 @@ cudaError_t colstats(const float* x, int ld, int C, const RowMap& map, int mode,
   double* psum = scratch;
   double* psq = scratch + (size_t)map.n_tiles * C;
   dim3 g1(map.n_tiles, (C + 127) / 128);
-  colstats_partial_kernel<<<g1, 128, 0, st>>>(x, ld, C, map, psum, psq);
+  colstats_partial_kernel<<<g1, dim3(128, 4), 0, st>>>(x, ld, C, map, psum, psq);
   dim3 g2(map.n_seg, (C + 127) / 128);
   colstats_final_kernel<<<g2, 128, 0, st>>>(psum, psq, C, map, mode, eps, out0, out1);
   return cudaGetLastError();
