@@ -38,10 +38,11 @@ enum stts_status {
 
 /* arithmetic of the dense contractions */
 enum stts_precision {
-  STTS_FP32 = 0,   /* CUDA-core fp32 FMA (parity reference on device)                       */
-  STTS_BF16 = 1,   /* tcgen05 kind::f16, bf16 operands, fp32 accumulate; STFT / output heads /
-                      iSTFT stay on the fp32-grade path                                     */
-  STTS_TF32X3 = 2  /* tcgen05 kind::tf32, error-compensated 3-pass split (fp32-grade)       */
+  STTS_FP32 = 0,   /* CUDA-core fp32 FMA everywhere (parity reference on device)                      */
+  STTS_F16 = 1,    /* 16-bit mode: tcgen05 kind::f16 on IEEE fp16 operand twins, fp32 accumulate, one
+                      pass; the forward STFT and the token-rate encoders run the three-pass fp16 split
+                      (f16x3, fp32-grade); statistics fp32 / fp64                                      */
+  STTS_TF32X3 = 2  /* tcgen05 kind::tf32, error-compensated 3-pass split (fp32-grade) everywhere      */
 };
 
 /* ---- lifetime ------------------------------------------------------------------------------ */
@@ -51,12 +52,12 @@ const char* stts_last_error(const stts_ctx* ctx);
 const char* stts_version(void);
 
 /* ---- weights: state_dict() of the reference modules, key by key -------------------------------
- * module in {"speech_predictor", "pitch_energy_predictor"}; key is the reference state_dict key
- * (SURVEY 8b "Checkpoint layout"); h_data is a HOST fp32 buffer, copied.  Unknown keys are kept
- * but unused (token-rate encoders are served by the Python layer in this round).              */
+ * key is the reference state_dict key (SURVEY 8b "Checkpoint layout"); h_data is a HOST fp32 buffer, copied;
+ * module in {"speech_predictor", "pitch_energy_predictor", "pe_text_encoder", "pe_text_style_encoder",
+ * "duration_predictor"}.  Unknown keys are kept but unused.                                       */
 int stts_load_tensor(stts_ctx* ctx, const char* module, const char* key, const float* h_data,
                      const int64_t* shape, int ndim);
-/* folds both weight-norm dialects, builds the K-major fp32 / tf32 hi-lo / bf16 packs and the
+/* folds both weight-norm dialects, builds the K-major fp32 / tf32 hi-lo / fp16 hi-lo packs and the
  * STFT / iSTFT bases.  Replaces nothing in the reference (it re-parametrises on every forward). */
 int stts_finalize_weights(stts_ctx* ctx);
 int stts_set_precision(stts_ctx* ctx, int precision);
@@ -74,7 +75,8 @@ int stts_set_token_layout(stts_ctx* ctx, int n_seg, const int* len_t);
  * "pe_text_encoder", "duration_predictor" (its text_encoder.*) -- the module the weights were
  * loaded under.  d_tokens int32 [sum T] (utterances concatenated).  Outputs, token-major dense and
  * either may be NULL: d_mu_tok [sum T, inter_dim] (= mu.transpose(1,2)), d_x_tok [sum T, 128].
- * Always fp32-grade arithmetic (the duration logits decide integer durations).                     */
+ * Always fp32-grade arithmetic (the duration logits decide integer durations): fp32 FMA in STTS_FP32,
+ * tf32x3 in STTS_TF32X3, f16x3 in STTS_F16.                                                         */
 int stts_text_encoder(stts_ctx* ctx, const char* which, const int32_t* d_tokens, float* d_mu_tok,
                       float* d_x_tok, void* stream);
 
@@ -163,6 +165,13 @@ int stts_speech_frames(stts_ctx* ctx, const float* d_enc_tok, const int32_t* d_c
                        float* d_logamp, float* d_phase, void* stream);
 /* after a synchronised call: STTS_ERR_UNVOICED_MIN if any utterance hit the reference's error path */
 int stts_check_source_status(stts_ctx* ctx, void* stream);
+
+/* 16-bit mode range audit (synchronises): number of elements of the workspace's fp16 operand twins that sit
+ * at the saturation value +-65504 after the last run.  The fp16 twins clip where the reference's fp32 (or a
+ * true bfloat16 path) would not; a non-zero count means the checkpoint's activations left the range the
+ * 16-bit mode was validated for and an fp32-grade mode (STTS_TF32X3) should be used.  Replaces nothing in
+ * the reference (it has no reduced-precision inference mode, config/config.yml:12).                  */
+int64_t stts_saturation_count(stts_ctx* ctx, void* stream);
 
 /* int16 PCM of n device samples: trunc(x * 32768), saturated -- replaces
  * `np.multiply(outputs[0], 32768).astype(np.int16)` (train/test_onnx.py:79) so that the device -> host

@@ -36,6 +36,7 @@ SIGNATURES = {
     "stts_generator_from_stft": (_i, [_vp, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _vp]),
     "stts_speech_frames": (_i, [_vp] + [_fp] * 13 + [_vp]),
     "stts_check_source_status": (_i, [_vp, _vp]),
+    "stts_saturation_count": (_i64, [_vp, _vp]),
     "stts_pcm16": (_i, [_vp, _fp, _i64, _vp, _vp]),
     "stts_test_conv": (_i, [_vp, _i, _fp, _i, _i, _i, _i, _fp, _fp, _i, _fp, _i, _vp]),
     "stts_debug_read": (_i64, [_vp, C.c_char_p, _fp, _i64, C.POINTER(_i), C.POINTER(_i), _vp]),

@@ -219,6 +219,27 @@ int stts_check_source_status(stts_ctx* ctx, void* stream) {
   return STTS_OK;
 }
 
+int64_t stts_saturation_count(stts_ctx* ctx, void* stream) {
+  if (!ctx) return STTS_ERR_BAD_ARG;
+  Context& c = ctx->c;
+  if (c.raw.count("STATUS") == 0) return fail(c, -4, "no layout set");
+  DeviceGuard g(c.device);
+  unsigned long long* cnt = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(c.raw["STATUS"]) + 128);
+  cudaError_t e = cudaMemsetAsync(cnt, 0, sizeof(unsigned long long), S(stream));
+  if (e != cudaSuccess) return cuda_fail(c, e, "saturation counter reset");
+  for (auto* acts : {&c.act, &c.tact})
+    for (auto& kv : *acts) {
+      const Act& a = kv.second;
+      if (a.h != nullptr) STTS_CK(saturation_count(a.h, (size_t)a.rows * a.ld, cnt, S(stream)));
+      if (a.g != nullptr) STTS_CK(saturation_count(a.g, (size_t)a.rows * a.ldg, cnt, S(stream)));
+    }
+  unsigned long long h = 0;
+  e = cudaMemcpyAsync(&h, cnt, sizeof(h), cudaMemcpyDeviceToHost, S(stream));
+  if (e == cudaSuccess) e = cudaStreamSynchronize(S(stream));
+  if (e != cudaSuccess) return cuda_fail(c, e, "saturation counter read");
+  return (int64_t)h;
+}
+
 int stts_pcm16(stts_ctx* ctx, const float* d_audio, int64_t n, int16_t* d_pcm, void* stream) {
   if (!ctx || n < 0 || (n > 0 && (!d_audio || !d_pcm))) return STTS_ERR_BAD_ARG;
   Context& c = ctx->c;

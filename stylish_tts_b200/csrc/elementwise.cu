@@ -793,6 +793,24 @@ cudaError_t twin_refresh(const float* f, int ld, int C, const RowMap& map, __hal
   return cudaGetLastError();
 }
 
+// ============================================================================ saturation audit
+// The fp16 operand twins saturate at +-65504 (to_twin / f16_split) where the reference's fp32 -- or a true
+// bfloat16 path -- would not.  Counts the saturated elements of one twin buffer (not on the hot path:
+// stts_saturation_count walks every twin of the workspace after a run).
+__global__ void __launch_bounds__(256) saturation_kernel(const uint16_t* __restrict__ h, size_t n,
+                                                         unsigned long long* __restrict__ count) {
+  unsigned long long c = 0;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    c += ((h[i] & 0x7FFFu) == 0x7BFFu) ? 1ull : 0ull;
+  for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+  if ((threadIdx.x & 31) == 0 && c) atomicAdd(count, c);
+}
+cudaError_t saturation_count(const twin_t* h, size_t n, unsigned long long* count, cudaStream_t st) {
+  if (n == 0) return cudaSuccess;
+  saturation_kernel<<<592, 256, 0, st>>>(reinterpret_cast<const uint16_t*>(h), n, count);
+  return cudaGetLastError();
+}
+
 // zero-fill of valid rows of a column block (WN "output" accumulator is rebuilt by EPI_RESSKIP's
 // accumulate2 = 0 path, so this is only needed by tests)
 __global__ void fill_kernel(float* p, size_t n, float v) {

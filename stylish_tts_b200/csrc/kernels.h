@@ -55,6 +55,7 @@ cudaError_t grn_weights(const float* W, int N, int K, const float* scale, int n_
 cudaError_t rowdot(const float* x, int ldx, int C, const RowMap& map, const float* w, const float* bias, const int* cu,
                    float* dense, cudaStream_t st);
 cudaError_t fill(float* p, size_t n, float v, cudaStream_t st);
+cudaError_t saturation_count(const twin_t* h, size_t n, unsigned long long* count, cudaStream_t st);
 cudaError_t twin_refresh(const float* f, int ld, int C, const RowMap& map, __half* h, __half* l, cudaStream_t st);
 
 // ---- token_rate.cu

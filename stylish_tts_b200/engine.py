@@ -9,9 +9,11 @@ import torch
 
 from . import _lib
 
-# "f16": one-pass tensor-core GEMMs on IEEE fp16 operand twins, fp32 accumulate (north-star "bf16 mode":
-# same tcgen05 kind::f16 rate as bf16, 8x finer rounding; "bf16" is kept as an alias of the same mode).
-PRECISIONS = {"fp32": 0, "f16": 1, "bf16": 1, "tf32x3": 2}
+# "f16": the 16-bit mode -- one-pass tensor-core GEMMs on IEEE fp16 operand twins, fp32 accumulate.  It is
+# what the north star calls "bf16 mode" (same tcgen05 kind::f16 rate, 8x finer rounding), but it is NOT
+# bfloat16: fp16 saturates at 65504 where bf16 keeps fp32's range, so the name "bf16" is rejected instead
+# of being silently aliased (stts_saturation_count / Synthesizer.check(audit=True) report clipped twins).
+PRECISIONS = {"fp32": 0, "f16": 1, "tf32x3": 2}
 
 
 class SttsError(RuntimeError):
@@ -86,6 +88,9 @@ class Engine:
         self.n_seg = 0
 
     def set_precision(self, name: str):
+        if name not in PRECISIONS:
+            raise ValueError(f"unknown precision {name!r}: choose one of {sorted(PRECISIONS)} "
+                             "(the 16-bit mode is 'f16' = IEEE fp16 operand twins; there is no bfloat16 mode)")
         self._check(self.lib.stts_set_precision(self.h, PRECISIONS[name]))
         self.precision = name
 
@@ -179,7 +184,8 @@ class Engine:
     def frame_index(self, dur: torch.Tensor, cu_tok: torch.Tensor, cap: int):
         n_seg = cu_tok.numel() - 1
         cu_frames = torch.empty(n_seg + 1, dtype=torch.int32, device=self.device)
-        idx = torch.empty(max(cap, 1), dtype=torch.int32, device=self.device)
+        # zero-filled: if the durations sum to less than `cap` the tail still names a valid token
+        idx = torch.zeros(max(cap, 1), dtype=torch.int32, device=self.device)
         status = torch.zeros(1, dtype=torch.int32, device=self.device)
         self._check(self.lib.stts_frame_index(self.h, _ptr(dur, torch.int32), _ptr(cu_tok, torch.int32), n_seg,
                                               _ptr(cu_frames, torch.int32), _ptr(idx, torch.int32), cap,
@@ -246,6 +252,10 @@ class Engine:
 
     def check_source_status(self):
         self._check(self.lib.stts_check_source_status(self.h, self._stream()))
+
+    def saturation_count(self) -> int:
+        """Elements of the fp16 operand twins at +-65504 after the last run (synchronises)."""
+        return int(self._check(self.lib.stts_saturation_count(self.h, self._stream())))
 
     def pcm16(self, audio: torch.Tensor) -> torch.Tensor:
         """fp32 device waveform -> int16 PCM on the device (train/test_onnx.py:79)."""

@@ -18,12 +18,10 @@ batches go through ``stylish_tts_b200.synth.Synthesizer``.  There is no PyTorch 
 """
 from __future__ import annotations
 
-import math
 import warnings
 from typing import Dict, Optional
 
 import torch
-import torch.nn.functional as F
 from torch import nn
 from torch.nn.utils.parametrizations import weight_norm
 
@@ -280,39 +278,9 @@ class PitchEnergyPredictor(_EngineOwner):
         self.F0_proj = nn.Conv1d(cc, 1, 1, 1, 0)
         self.N_proj = nn.Conv1d(cc, 1, 1, 1, 0)
 
-    def compute_cross(self, prosody, frame_token, style, text_lengths, frame_lengths=None):
-        """pitch_energy_predictor.py:83-102 with the alignment given as frame -> token indices
-        [B, F].  The band mask keeps the reference's inverted polarity: the
-        attention sees every token EXCEPT the +-5 band.  ``frame_lengths`` (ragged batches only)
-        switches to per-utterance semantics: padded tokens are never attended and padded frames
-        are zero before the depthwise conv, i.e. exactly the B = 1 result for each utterance."""
-        b, t, _ = prosody.shape
-        base = torch.gather(prosody.transpose(1, 2), 2, frame_token[:, None, :].expand(-1, prosody.shape[2], -1))
-        query = self.query_norm(base.transpose(1, 2), style).transpose(1, 2)
-        key = self.key_norm(prosody, style).transpose(1, 2)
-        tok = torch.arange(t, device=prosody.device)[None, None, :]
-        tau = frame_token[:, :, None]
-        band = (tok >= tau - self.cross_window) & (tok <= tau + self.cross_window)
-        pad = tok >= text_lengths[:, None, None]
-        if frame_lengths is None:
-            bias = torch.zeros(band.shape, dtype=prosody.dtype, device=prosody.device)
-            bias.masked_fill_(~((~band) | pad), -1e4)          # reference polarity, padded tokens "allowed"
-            att = self.cross_attention(query, key, attn_bias=bias[:, None])
-        else:
-            bias = torch.zeros(band.shape, dtype=prosody.dtype, device=prosody.device)
-            bias.masked_fill_(band, -1e4)
-            bias.masked_fill_(pad.expand_as(band), float("-inf"))
-            att = self.cross_attention(query, key, attn_bias=bias[:, None])
-            fm = (torch.arange(base.shape[2], device=base.device)[None, :] < frame_lengths[:, None])[:, None, :]
-            att = att * fm
-            base = base * fm
-        att = self.cross_post(att)
-        return (base + att) / math.sqrt(2.0)
-
     def forward(self, text_encoding, text_lengths, alignment, style):
         """pitch_energy_predictor.py:104-119 in libstts_b200: prosody encoder, cross-attention block
-        (stts_pe_cross) and the two towers.  ``compute_cross`` above is the torch statement of the
-        cross block, kept for the CPU host tests."""
+        (stts_pe_cross) and the two towers."""
         b, _, t = text_encoding.shape
         f = alignment.shape[2]
         dev = text_encoding.device

@@ -35,6 +35,8 @@ class Synthesizer:
         self.use_graphs = use_graphs
         self.model_config = model_config or ModelConfig()
         self._graphs, self._packs, self._finfo = {}, {}, {}
+        self._layout_key = None        # (token counts, frame counts) the engine workspace is planned for
+        self._last_index = None        # (status, cu_frames, frame counts) of the last eager frame_index call
         self.reload_weights()
         self.engine.set_precision(precision)
 
@@ -76,6 +78,10 @@ class Synthesizer:
         Returns dict(audio=[...[300 F_b]], duration_pred=[...], pitch=[...], energy=[...], ...)."""
         dev = self.device
         T = [int(t.numel()) for t in tokens]
+        n_vocab = int(self.model_config.text_encoder.tokens)
+        for b, t in enumerate(tokens):           # nn.Embedding raises IndexError on an out-of-range id
+            if not t.is_cuda and t.numel() and (int(t.min()) < 0 or int(t.max()) >= n_vocab):
+                raise IndexError(f"utterance {b}: token id outside [0, {n_vocab})")
         pack = self._token_pack(T, max(T))
         # one H2D copy of the concatenated tokens: every stage works on the packed [sum T] token order
         tok = torch.cat([t.reshape(-1) for t in tokens]).to(dev, torch.int32, non_blocking=True)
@@ -118,6 +124,11 @@ class Synthesizer:
         """One CUDA graph per batch shape: the whole step (three token-rate chains on forked streams,
         length regulation, frame-rate path) is replayed with no host work between kernels."""
         key = (tuple(pack.lengths), tuple(F_list), bool(want_spec))
+        # A captured graph bakes the arena pointers, layout tables and TMA maps of the workspace plan it was
+        # captured under, and the context holds ONE plan: any call with another shape (graph or eager)
+        # re-plans it.  Graphs of other shapes are therefore dropped as soon as the plan moves on.
+        if self._layout_key != key[:2]:
+            self._graphs.clear()
         ent = self._graphs.get(key)
         if ent is None:
             if len(self._graphs) >= 8:
@@ -187,8 +198,14 @@ class Synthesizer:
             per_utt = torch.zeros(B, dtype=torch.int64, device=dev).index_add_(0, pack.seg_id, dur_pred.to(torch.int64))
             F_list = [int(v) for v in per_utt.tolist()]                         # the one unavoidable D2H
         F_tot = sum(F_list)
-        cu_frames, idx, _ = eng.frame_index(dur_used, pack.cu, F_tot)
+        cu_frames, idx, status = eng.frame_index(dur_used, pack.cu, F_tot)
+        if not capturing:
+            self._last_index = (status, cu_frames, list(F_list))
         eng.set_layout(F_list, [4 * f for f in F_list])
+        if self._layout_key != (tuple(pack.lengths), tuple(F_list)):
+            self._layout_key = (tuple(pack.lengths), tuple(F_list))
+            if not capturing:
+                self._graphs.clear()
 
         # ---- pitch / energy frame-rate part: cross attention over the alignment, then the two towers
         x = eng.pe_cross(None, pe_style, idx, cu_frames, want_dense=want_intermediates)
@@ -251,9 +268,27 @@ class Synthesizer:
                 out[k] = res[k]
         return out
 
-    def check(self):
-        """Raises RuntimeError if an utterance hit the reference's torch.min-of-empty error path."""
+    def check(self, audit: bool = False):
+        """Synchronising post-call validation.  ``audit`` (16-bit mode): also raise OverflowError if any fp16
+        operand twin of the last run saturated at +-65504 (a checkpoint outside the validated range).  Raises RuntimeError if an utterance hit the reference's
+        torch.min-of-empty error path, ValueError if the durations given to the last eager call do not
+        sum to the frame counts it was laid out for (the reference's `text_encoding @ alignment` shape
+        error)."""
         self.engine.check_source_status()
+        if self._last_index is not None:
+            status, cu_frames, F_list = self._last_index
+            self._last_index = None
+            got = cu_frames.cpu().tolist()
+            want = [0]
+            for f in F_list:
+                want.append(want[-1] + f)
+            if int(status.item()) != 0 or got != want:
+                raise ValueError(f"durations do not sum to the given frame counts: cumulative frames {got} vs {want}")
+        if audit and self.engine.precision == "f16":
+            n = self.engine.saturation_count()
+            if n:
+                raise OverflowError(f"{n} fp16 operand values saturated at +-65504: use precision='tf32x3' for this "
+                                    "checkpoint")
 
 
 class SynthesizerPool:
