@@ -13,6 +13,10 @@ the pin is "outputs of the reference itself run here": ``oracle/make_golden.py``
 reference, runs it on seeded fixture weights and inputs, checks that this port reproduces it
 (max-abs printed, required <= 2e-6 on every recorded tensor) and writes ``tests/golden/*``.
 
+Every tensor constructor takes its device from an input, so the same functions also serve as the
+"stock PyTorch kernels on the B200" baseline of bench.py (state dicts and inputs moved to cuda);
+on CPU tensors the arithmetic is unchanged.
+
 Conventions: ``sd`` is a mapping key -> tensor using the reference ``state_dict()`` names,
 ``p`` is a key prefix ("decoder.", "flow.flows.14.", ...).  Tensors use the reference layout
 ([B, C, time]) unless stated otherwise.  Stochastic draws are *inputs* (``noise`` dict).
@@ -88,8 +92,8 @@ def rope(x: Tensor, d: int, base: int = 10_000) -> Tensor:
     """text_encoder.py:89-168 -- rotate the first ``d`` features of every head; x is [b,h,t,c]."""
     x = torch.permute(x, (2, 0, 1, 3))
     seq_len = x.shape[0]
-    theta = 1.0 / (base ** (torch.arange(0, d, 2).float() / d))
-    seq_idx = torch.arange(seq_len).float()
+    theta = 1.0 / (base ** (torch.arange(0, d, 2, device=x.device).float() / d))
+    seq_idx = torch.arange(seq_len, device=x.device).float()
     idx_theta = torch.einsum("n,d->nd", seq_idx, theta)
     idx_theta2 = torch.cat([idx_theta, idx_theta], dim=1)
     cos, sin = idx_theta2.cos()[:, None, None, :], idx_theta2.sin()[:, None, None, :]
@@ -223,7 +227,7 @@ def duration_predictor(sd: SD, tokens: Tensor, lengths: Tensor, n_layer: int = 4
 # ----------------------------------------------------------------------------- length regulation
 def prediction_to_duration(pred: Tensor) -> Tensor:
     """utils.py:468-474 -- [T,16] logits -> integer-valued fp32 durations [T]."""
-    table = torch.tensor(CLASS_TO_DUR, dtype=torch.float32)
+    table = torch.tensor(CLASS_TO_DUR, dtype=torch.float32, device=pred.device)
     soft = (torch.softmax(pred, dim=-1) * table).sum(dim=-1).round().clamp(min=1)
     arg = table[torch.argmax(pred, dim=-1).long().clamp(min=0, max=16)]
     return (arg * (arg < 7)) + (soft * (arg >= 7))
@@ -231,14 +235,14 @@ def prediction_to_duration(pred: Tensor) -> Tensor:
 
 def duration_to_indices(duration: Tensor) -> Tensor:
     """utils.py:481-484 -- frame -> token index (the non-zero row of every alignment column)."""
-    return torch.repeat_interleave(torch.arange(duration.shape[0]), duration.to(torch.int))
+    return torch.repeat_interleave(torch.arange(duration.shape[0], device=duration.device), duration.to(torch.int))
 
 
 def duration_to_alignment(duration: Tensor) -> Tensor:
     """utils.py:476-489 -- dense one-hot [T, sum(dur)]."""
     idx = duration_to_indices(duration)
-    out = torch.zeros((duration.shape[0], idx.shape[0]))
-    out[idx, torch.arange(idx.shape[0])] = 1
+    out = torch.zeros((duration.shape[0], idx.shape[0]), device=duration.device)
+    out[idx, torch.arange(idx.shape[0], device=duration.device)] = 1
     return out
 
 
@@ -285,7 +289,7 @@ def band_mask(alignment: Tensor, text_mask: Tensor, window: int) -> Tensor:
     (text_encoder.py:255-262) treats truthy as *allowed*: the inverted polarity is reproduced."""
     b, t, f = alignment.shape
     tau = alignment.argmax(dim=1)
-    t_idx = torch.arange(t).view(1, 1, t)
+    t_idx = torch.arange(t, device=alignment.device).view(1, 1, t)
     tau_exp = tau.unsqueeze(-1)
     band = (t_idx >= (tau_exp - window)) & (t_idx <= (tau_exp + window))
     full = (~band) | text_mask.unsqueeze(1).expand(b, f, t)
@@ -296,7 +300,7 @@ def pitch_energy_predictor(sd: SD, enc: Tensor, lengths: Tensor, alignment: Tens
                            style: Tensor, taps: Optional[Dict[str, Tensor]] = None):
     """pitch_energy_predictor.py:83-121 -> (F0 [B,F], N [B,F])."""
     t = enc.shape[2]
-    mask = torch.gt(torch.arange(t).unsqueeze(0).expand(lengths.shape[0], -1).type_as(lengths) + 1,
+    mask = torch.gt(torch.arange(t, device=enc.device).unsqueeze(0).expand(lengths.shape[0], -1).type_as(lengths) + 1,
                     lengths.unsqueeze(1))  # utils.py:59-67
     pros = prosody_encoder(sd, "prosody_encoder.", enc, style, lengths, 3)
     base = torch.matmul(pros.transpose(1, 2), alignment)
@@ -379,7 +383,7 @@ def generate_pcph(f0: Tensor, voiced: Tensor, noise: Tensor, init_phase: Tensor,
     max_h = min(16, int((sr / 2) / min_f0))
     n_h = torch.ones_like(f0, dtype=torch.float)
     n_h[vuv] = sr / 2.0 / f0[vuv]
-    idx = torch.arange(1, max_h + 1).reshape(1, -1, 1)
+    idx = torch.arange(1, max_h + 1, device=f0.device).reshape(1, -1, 1)
     hmask = torch.repeat_interleave((f0 * idx) <= (sr / 2.0), hop, dim=2)
     amp = torch.repeat_interleave(vuv * power_factor * torch.sqrt(2.0 / n_h), hop, dim=2)
     f0r = torch.repeat_interleave(f0, hop, dim=2)
@@ -393,7 +397,7 @@ def generate_pcph(f0: Tensor, voiced: Tensor, noise: Tensor, init_phase: Tensor,
 
 def stft_mag_phase(x: Tensor) -> Tuple[Tensor, Tensor]:
     """generator.py:32-44 + 407-410: |X| and atan2 phase of the source, last frame dropped."""
-    window = torch.hann_window(WIN)
+    window = torch.hann_window(WIN, device=x.device)
     spec = torch.stft(x, N_FFT, HOP, WIN, window=window, return_complex=True)
     mag = torch.abs(spec) + 1e-9
     re = torch.real(spec) / mag
@@ -403,7 +407,7 @@ def stft_mag_phase(x: Tensor) -> Tuple[Tensor, Tensor]:
 
 def istft_tanh(logamp: Tensor, phase: Tensor) -> Tensor:
     """generator.py:425-433 + 46-56 -- logamp/phase already replicate-padded to L+1 frames."""
-    window = torch.hann_window(WIN)
+    window = torch.hann_window(WIN, device=logamp.device)
     spec = torch.exp(logamp)
     audio = torch.istft(spec * (torch.cos(phase) + torch.sin(phase) * 1j), N_FFT, HOP, WIN, window=window)
     return torch.tanh(audio.unsqueeze(-2))

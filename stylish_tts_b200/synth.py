@@ -97,6 +97,29 @@ class Synthesizer:
             res = self._core(tok, pack, dur_used, F_list, noise, pitch_energy, want_spec, want_intermediates)
         return self._package(res, T, want_spec)
 
+    @torch.no_grad()
+    def predict_durations(self, tokens: Sequence[torch.Tensor]) -> List[torch.Tensor]:
+        """DurationPredictor.forward + DurationProcessor.prediction_to_duration (duration_predictor.py:30-36,
+        utils.py:468-474) for a ragged batch: int32 durations per utterance, on the device.  The sharded
+        path (shard.synthesize_sharded) needs the frame counts before it can partition the batch."""
+        T = [int(t.numel()) for t in tokens]
+        pack = self._token_pack(T, max(T))
+        tok = torch.cat([t.reshape(-1) for t in tokens]).to(self.device, torch.int32, non_blocking=True)
+        eng, mc = self.engine, self.model_config
+        eng.set_token_layout(pack.lengths)
+        if self._layout_key is not None and self._layout_key[0] != tuple(pack.lengths):
+            self._layout_key = None
+            self._graphs.clear()
+        dp_mu, _ = eng.text_encoder("duration_predictor", tok, mc.inter_dim, want_x=False)
+        dp_style = eng.text_style_encoder("duration_predictor", None)
+        _, logits = eng.prosody_encoder("duration_predictor", dp_mu, dp_style, mc.inter_dim + mc.style_dim,
+                                        want_logits=True, want_out=False)
+        dur = eng.durations(logits)
+        off = [0]
+        for n in T:
+            off.append(off[-1] + n)
+        return [dur[off[b]: off[b + 1]] for b in range(len(T))]
+
     def _token_pack(self, T, Tmax) -> TokenPack:
         key = (tuple(T), Tmax)
         if key not in self._packs:
@@ -308,9 +331,11 @@ class SynthesizerPool:
         self._done = [None] * lanes
         self._next = 0
 
-    def submit(self, tokens, durations=None, frames=None, out_host: Optional[torch.Tensor] = None, **kw):
+    def submit(self, tokens, durations=None, frames=None, out_host: Optional[torch.Tensor] = None, after=None, **kw):
         """Enqueue one batch on the next lane.  ``out_host``: pinned [sum 300 F] buffer that receives the
-        concatenated waveform.  Returns (result dict, event recorded after the batch's last operation)."""
+        concatenated waveform.  ``after(lane, out)``: extra work enqueued on the lane's stream behind the batch
+        (the sharded path's waveform gather).  Returns (result dict, event recorded after the batch's last
+        operation)."""
         i = self._next
         self._next = (i + 1) % len(self.lanes)
         if self._done[i] is not None:
@@ -321,6 +346,8 @@ class SynthesizerPool:
             out = self.lanes[i].synthesize(tokens, durations=durations, frames=frames, **kw)
             if out_host is not None:
                 out_host.copy_(out["audio_flat"], non_blocking=True)
+            if after is not None:
+                after(i, out)
             ev = torch.cuda.Event()
             ev.record(s)
         self._done[i] = ev

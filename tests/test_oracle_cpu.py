@@ -80,6 +80,54 @@ def test_durations_bit_exact():
     assert al.shape == (64, int(d[:64].sum())) and float(al.sum()) == al.shape[1]
 
 
+def test_durations_million_rows_and_adversarial_ties():
+    """The reference DurationProcessor's own results (oracle/make_golden_durations.py) on 2^20 seeded rows and
+    on the exact-tie / tie -+ k ulp rows: the port must reproduce them bit for bit on this host."""
+    from oracle.durations_cases import adversarial_logits, random_logits, tie_distance
+    g = gold("durations_adv")
+    assert torch.equal(adversarial_logits(), g["logits"])
+    assert torch.equal(port.prediction_to_duration(g["logits"]).to(torch.int32), g["duration"])
+    # exact ties round half to even: classes (7, 12) -> 9.5 -> 10, (9, 12) -> 10.5 -> 10
+    row = torch.full((2, 16), -1e4)
+    row[0, 6] = row[0, 8] = 0.0
+    row[1, 7] = row[1, 8] = 0.0
+    assert port.prediction_to_duration(row).tolist() == [10.0, 10.0]
+    g = gold("durations_1m")
+    logits = random_logits(seed=int(g["seed"]))
+    d = port.prediction_to_duration(logits)
+    bad = torch.nonzero(d.to(torch.uint8) != g["duration"]).flatten()
+    near = set(g["near_tie_rows"].tolist())        # another host's libm may move these (and only these) rows
+    assert all(int(i) in near for i in bad)
+    dist, soft_path = tie_distance(logits)
+    assert sorted(near) == torch.nonzero((dist < 1e-5) & soft_path).flatten().tolist()
+
+
+def test_frame0_stft_phase_of_the_reference_is_rounding_noise():
+    """Pins the "defined deviation" of DESIGN.md section 4: torch.stft(center=True, reflect) centres frame 0 on
+    sample 0, the windowed frame is even, X_k is exactly real -- so the reference's atan2 phase there is the sign
+    of FFT rounding noise.  Evidence: the SAME torch.stft in fp32 and in fp64 disagrees by +-pi sign flips on a
+    large share of frame-0 bins and on none of the other frames' bins; the exact value (Im = 0) is what the CUDA
+    path returns and what the "audio_x0" target encodes."""
+    g = gold("tiny")
+    src = g["tap.source"]
+    win32, win64 = torch.hann_window(1200), torch.hann_window(1200, dtype=torch.float64)
+    s32 = torch.stft(src, 2048, 75, 1200, window=win32, return_complex=True)[:, :, :-1]
+    s64 = torch.stft(src.double(), 2048, 75, 1200, window=win64, return_complex=True)[:, :, :-1]
+    p32, p64 = torch.angle(s32).double(), torch.angle(s64)
+    flips = ((p32 - p64).abs() > 3.0)[0]                     # [1025 bins, frames]
+    assert int(flips[:, 1:].sum()) == 0                       # no other frame flips
+    assert int(flips[:, 0].sum()) >= 50                       # frame 0: a large share of the 1025 bins
+    # frame 0 is numerically real: |Im| is at rounding level of |Re| in fp64
+    assert float((s64.imag[0, :, 0].abs() / (s64.real[0, :, 0].abs() + 1e-30)).median()) < 1e-9
+    # the golden phase of the reference shows both signs of pi in frame 0
+    f0 = g["tap.har_phase"][0, :, 0]
+    assert int((f0 > 3.0).sum()) > 20 and int((f0 < -3.0).sum()) > 20
+    # the exact-frame-0 variant differs from the raw reference only in that frame
+    x0 = port.exact_frame0_phase(g["tap.har_phase"])
+    assert torch.equal(x0[:, :, 1:], g["tap.har_phase"][:, :, 1:])
+    assert set(x0[0, :, 0].unique().tolist()) <= {0.0, float(torch.tensor(3.141592653589793, dtype=torch.float32))}
+
+
 def test_known_answers():
     # SURVEY 8c: facts usable without the oracle
     assert port.CLASS_TO_DUR == [1, 2, 3, 4, 5, 6, 7, 9, 12, 15, 18, 22, 27, 32, 38, 46]
