@@ -51,7 +51,8 @@ def test_golden_single_utterances(precision, tol):
         perr = maxabs(out["pitch"][0], g["out.pitch"].reshape(-1))
         _log(f"{precision}.{name}", {"audio_x0": err, "audio_raw_after_7500": raw, "pitch": perr})
         assert raw <= 1.5 * tol, (precision, name, raw)
-        assert perr <= (2e-5 if precision == "fp32" else (1e-4 if precision == "tf32x3" else 2e-2)) * 300, (name, perr)
+        # predicted pitch (~100-270 Hz): fp32 measured 9e-4 Hz, tf32x3 2.2e-3 Hz, f16 0.22 Hz on B200
+        assert perr <= {"fp32": 6e-3, "tf32x3": 1.5e-2, "f16": 1.0}[precision], (name, perr)
         assert torch.equal(out["duration_pred"][0].cpu().to(torch.int32), g["duration_pred"]), name
         assert out["audio"][0].numel() == 300 * int(dur.sum())
         assert err <= tol, (precision, name, err)
@@ -122,13 +123,22 @@ def test_module_api_matches_reference_signatures():
     nets["speech_predictor"].noise_override = noise
     audio = em(tokens[None].to(dev), torch.tensor([tokens.numel()], device=dev), al)
     assert audio.shape == (300 * int(dur.sum()),)
-    # ExportModel feeds its own predicted pitch to the source, which integrates it (see module doc):
-    # the waveform is only loosely comparable; the strict comparison uses the reference pitch
     pred = nets["speech_predictor"](tokens[None].to(dev), torch.tensor([tokens.numel()], device=dev), al,
                                     g["out.pitch"].to(dev), g["out.energy"].to(dev))
-    nets["speech_predictor"].noise_override = None
     assert maxabs(pred.audio, g["out.audio_x0"]) <= 1e-4
-    assert maxabs(audio, g["out.audio_x0"].reshape(-1)) <= 0.1
+    # ExportModel feeds its OWN predicted pitch to the source, which integrates it (see module doc): its waveform
+    # is held to the oracle's speech stage run on exactly those predicted curves, and the curves to the reference's
+    pe_enc, _, _ = nets["pe_text_encoder"](tokens[None].to(dev), torch.tensor([tokens.numel()], device=dev))
+    pe_style = nets["pe_text_style_encoder"](pe_enc, torch.tensor([tokens.numel()], device=dev))
+    pitch, energy = nets["pitch_energy_predictor"](pe_enc, torch.tensor([tokens.numel()], device=dev), al, pe_style)
+    nets["speech_predictor"].noise_override = None
+    assert maxabs(pitch, g["out.pitch"]) <= 6e-3 and maxabs(energy, g["out.energy"]) <= 1e-4
+    from oracle import stylish_port as port
+    from tests.util import fixture_sds
+    with torch.no_grad():
+        want, _, _ = port.speech_predictor(fixture_sds()["speech_predictor"], tokens[None], torch.tensor([tokens.numel()]),
+                                           al.cpu(), pitch.cpu(), energy.cpu(), noise, exact_frame0=True)
+    assert maxabs(audio, want.reshape(-1)) <= 1e-4
 
 
 def test_reference_error_path_voiced_without_f0_above_20():

@@ -13,7 +13,17 @@ FP32_REL = {
     "pe_towers.pitch": 2e-5, "pe_towers.energy": 2e-5, "PitchEnergyPredictor.pitch": 5e-5,
     "decoder": 2e-5, "z_prior": 2e-5, "z_flow": 5e-5, "mel": 5e-5, "source": 2e-5,
     "har_spec": 2e-5, "logamp_prior": 5e-5,   # K = 7 175 contraction of OUR |X| (chained STFT error)
-    "strict.gen_convnext": 5e-5, "strict.logamp": 5e-5,
+    "strict.gen_convnext": 5e-5, "strict.logamp": 5e-5, "strict.phase": 5e-5,
+    "phase_prior_from4": 5e-4,                # K = 7 175 contraction of OUR wrapped phase (<= 7e-5 abs off per bin)
+}
+# 16-bit mode ("f16"): every recorded intermediate, bounds = ~5x the values measured on B200 (profiles/README.md);
+# the token-rate stack and the forward STFT run the three-pass fp16 split (fp32-grade) in this mode
+F16_REL = {
+    "sp_text": 5e-5, "pe_text": 5e-5, "dur_logits": 5e-5, "pe_prosody": 5e-5, "sp_style": 5e-5, "pe_style": 5e-5,
+    "pe_cross": 5e-5, "pe_towers.pitch": 5e-3, "pe_towers.energy": 5e-3, "PitchEnergyPredictor.pitch": 5e-3,
+    "decoder": 4e-3, "z_prior": 2e-3, "z_flow": 2e-3, "mel": 2e-3, "source": 2e-5, "har_spec": 5e-5,
+    "logamp_prior": 2e-3, "phase_prior_from4": 3e-3, "strict.gen_convnext": 3e-3, "strict.logamp": 3e-3,
+    "strict.phase": 3e-3,
 }
 # "strict.*": generator fed the reference's own STFT -> compared with the raw reference output.
 # "*_x0": full path compared with the reference run with the exact (real) frame-0 phase, because the
@@ -53,4 +63,9 @@ def test_stages_f16():
     assert res["strict.audio"]["max_abs"] <= 1e-3, res["strict.audio"]
     assert res["gen.audio_x0"]["max_abs"] <= 1e-3, res["gen.audio_x0"]
     assert res["SpeechPredictor.audio_x0"]["max_abs"] <= 1e-3, res["SpeechPredictor.audio_x0"]
-    assert res["duration_pred"]["max_abs"] == 0.0
+    assert res["gen.audio_after_7500"]["max_abs"] <= 1.5e-3, res["gen.audio_after_7500"]
+    assert res["duration_pred"]["max_abs"] == 0.0 and res["alignment"]["max_abs"] == 0.0
+    for k, tol in F16_REL.items():
+        assert res[k]["rel"] <= tol, (k, res[k])
+    assert res["har_phase(wrapped)"]["max_abs"] <= 1e-3, res["har_phase(wrapped)"]
+    assert res["har_phase.unwrapped_flips"]["max_abs"] <= 1025, res["har_phase.unwrapped_flips"]
