@@ -180,6 +180,16 @@ def parity_against_oracle(syn, tokens, durs, frames, modes, n_utts: int = 6):
                            pitch_energy=[(ref[i][0]["pitch"], ref[i][0]["energy"]) for i in pick])
         syn.check()
         r = {"n_utts": len(pick), "seconds": [round(300.0 * frames[i] / 24000.0, 2) for i in pick]}
+        err = torch.cat([(o["audio"][k].double().cpu() - ref[i][1]["audio"].double().reshape(-1)).abs()
+                         for k, i in enumerate(pick)])
+        # utterances beyond ~5 s contain isolated atan2 phase-wrap events of the source STFT (DESIGN.md section 4,
+        # spot 3) that move ~7 frames of ANY implementation by 5e-3 .. 8e-3: max-abs is reported with the robust
+        # statistics that bound everything outside those events
+        r["mean_abs_x0"] = float(err.mean())
+        r["q99_abs_x0"] = float(torch.quantile(err[::7].float(), 0.99))
+        r["share_gt_2e-3"] = float((err > 2e-3).double().mean())
+        r["max_abs_x0_le_5s"] = max([maxabs(o["audio"][k], ref[i][1]["audio"]) for k, i in enumerate(pick)
+                                     if frames[i] <= 400] or [0.0])
         r["max_abs_x0"] = max(maxabs(o["audio"][k], ref[i][1]["audio"]) for k, i in enumerate(pick))
         r["max_abs_after_7500"] = max(maxabs(o["audio"][k][7500:], ref[i][0]["audio"].reshape(-1)[7500:])
                                       for k, i in enumerate(pick) if 300 * frames[i] > 7500)

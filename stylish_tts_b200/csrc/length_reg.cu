@@ -25,16 +25,19 @@ __global__ void __launch_bounds__(256) durations_kernel(const float* __restrict_
   int am = 0;
 #pragma unroll
   for (int i = 1; i < 16; ++i) if (x[i] > m) { m = x[i]; am = i; }   // first maximum, like torch.argmax
-  // fp32 softmax in torch's formulation (exp(x - max), sum, divide).  exp is evaluated in fp64 and rounded once:
+  // fp32 softmax in ATen's CPU formulation: exp(x - max), sum, multiply by the reciprocal of the sum; then
+  // p * table rounded, then added -- every product / sum rounded separately (no FMA contraction: the adversarial
+  // tie rows of tests/golden/durations_adv.safetensors tell the formulations apart).  exp is evaluated in fp64 and rounded once:
   // the correctly rounded fp32 value, which is what a 1-ulp libm (the reference's CPU expf) returns for all but a
   // few percent of arguments -- the hardware ex2.approx path of expf() is 2 ulp.  What remains implementation-
   // defined is the last ulp of `soft` next to an x.5 tie (~2 rows per million, tests/test_durations_gpu.py).
   float e[16], s = 0.f;
 #pragma unroll
-  for (int i = 0; i < 16; ++i) { e[i] = (float)exp((double)(x[i] - m)); s += e[i]; }
+  for (int i = 0; i < 16; ++i) { e[i] = (float)exp((double)(x[i] - m)); s = __fadd_rn(s, e[i]); }
+  const float inv = __fdiv_rn(1.f, s);
   float soft = 0.f;
 #pragma unroll
-  for (int i = 0; i < 16; ++i) soft += __fdiv_rn(e[i], s) * kClassToDur[i];
+  for (int i = 0; i < 16; ++i) soft = __fadd_rn(soft, __fmul_rn(__fmul_rn(e[i], inv), kClassToDur[i]));
   soft = fmaxf(rintf(soft), 1.f);                 // torch.round = half to even
   const float arg = kClassToDur[am];
   dur[t] = (int)((arg < 7.f) ? arg : soft);

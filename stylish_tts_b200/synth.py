@@ -235,8 +235,8 @@ class Synthesizer:
         pitch, energy = eng.pe_towers(None, pe_style)
         pitch_in, energy_in = pitch, energy
         if pitch_energy is not None:
-            pitch_in = torch.cat([pe[0].reshape(-1) for pe in pitch_energy]).to(dev, torch.float32).contiguous()
-            energy_in = torch.cat([pe[1].reshape(-1) for pe in pitch_energy]).to(dev, torch.float32).contiguous()
+            pitch_in = torch.cat([pe[0].reshape(-1).to(dev, torch.float32) for pe in pitch_energy]).contiguous()
+            energy_in = torch.cat([pe[1].reshape(-1).to(dev, torch.float32) for pe in pitch_energy]).contiguous()
 
         # ---- speech frame-rate path
         cur.wait_stream(s_sp)

@@ -198,7 +198,7 @@ def test_full_size_batch_properties_f16():
     from bench import workload
     from stylish_tts_b200 import fixture
     syn = synthesizer("f16")
-    tokens, durs, frames = workload(0)
+    tokens, durs, frames = workload(1)
     g = torch.Generator().manual_seed(2024)
     noise = [fixture.draw_noise(f, g) for f in frames]
     a = syn.synthesize(tokens, durations=durs, noise=noise)
