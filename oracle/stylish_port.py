@@ -227,7 +227,7 @@ def duration_predictor(sd: SD, tokens: Tensor, lengths: Tensor, n_layer: int = 4
 # ----------------------------------------------------------------------------- length regulation
 def prediction_to_duration(pred: Tensor) -> Tensor:
     """utils.py:468-474 -- [T,16] logits -> integer-valued fp32 durations [T]."""
-    table = torch.tensor(CLASS_TO_DUR, dtype=torch.float32, device=pred.device)
+    table = torch.tensor(CLASS_TO_DUR, dtype=pred.dtype, device=pred.device)
     soft = (torch.softmax(pred, dim=-1) * table).sum(dim=-1).round().clamp(min=1)
     arg = table[torch.argmax(pred, dim=-1).long().clamp(min=0, max=16)]
     return (arg * (arg < 7)) + (soft * (arg >= 7))
@@ -241,7 +241,7 @@ def duration_to_indices(duration: Tensor) -> Tensor:
 def duration_to_alignment(duration: Tensor) -> Tensor:
     """utils.py:476-489 -- dense one-hot [T, sum(dur)]."""
     idx = duration_to_indices(duration)
-    out = torch.zeros((duration.shape[0], idx.shape[0]), device=duration.device)
+    out = torch.zeros((duration.shape[0], idx.shape[0]), device=duration.device, dtype=duration.dtype)
     out[idx, torch.arange(idx.shape[0], device=duration.device)] = 1
     return out
 
@@ -397,7 +397,7 @@ def generate_pcph(f0: Tensor, voiced: Tensor, noise: Tensor, init_phase: Tensor,
 
 def stft_mag_phase(x: Tensor) -> Tuple[Tensor, Tensor]:
     """generator.py:32-44 + 407-410: |X| and atan2 phase of the source, last frame dropped."""
-    window = torch.hann_window(WIN, device=x.device)
+    window = torch.hann_window(WIN, device=x.device).to(x.dtype)
     spec = torch.stft(x, N_FFT, HOP, WIN, window=window, return_complex=True)
     mag = torch.abs(spec) + 1e-9
     re = torch.real(spec) / mag
@@ -407,7 +407,7 @@ def stft_mag_phase(x: Tensor) -> Tuple[Tensor, Tensor]:
 
 def istft_tanh(logamp: Tensor, phase: Tensor) -> Tensor:
     """generator.py:425-433 + 46-56 -- logamp/phase already replicate-padded to L+1 frames."""
-    window = torch.hann_window(WIN, device=logamp.device)
+    window = torch.hann_window(WIN, device=logamp.device).to(logamp.dtype)
     spec = torch.exp(logamp)
     audio = torch.istft(spec * (torch.cos(phase) + torch.sin(phase) * 1j), N_FFT, HOP, WIN, window=window)
     return torch.tanh(audio.unsqueeze(-2))
@@ -445,7 +445,9 @@ def generator(sd: SD, p: str, mel: Tensor, style: Tensor, pitch: Tensor,
     """generator.py:402-438 -> (audio [B,1,75L], logamp [B,1025,L+1], phase [B,1025,L+1]).
     The ``energy`` argument of the reference is unused."""
     pit = pitch.unsqueeze(1)
-    prior = generate_pcph(pit, (pit > 10.0).float(), noise, init_phase).squeeze(1)
+    # the source is always evaluated in the reference's own arithmetic (fp32 with an fp64 phase); a float64 run of
+    # this port (tests: "the reference against itself in higher precision") differs from it downstream only
+    prior = generate_pcph(pit.float(), (pit > 10.0).float(), noise.float(), init_phase.float()).squeeze(1).to(mel.dtype)
     har_spec, har_phase = stft_mag_phase(prior)
     if stft_override is not None:
         har_spec, har_phase = stft_override
@@ -490,7 +492,8 @@ def speech_predictor(sd: SD, tokens: Tensor, lengths: Tensor, alignment: Tensor,
     enc, _, _ = text_encoder(sd, "text_encoder.", tokens, lengths)
     style = text_style_encoder(sd, "style_encoder.", enc, lengths)
     al4 = alignment.repeat_interleave(4, dim=2)
-    pitch4, energy4 = upsample4(pitch), upsample4(energy)
+    # fp32 upsample whatever the run's dtype: the source integrates pitch4, one ulp of it moves the waveform by 8e-3
+    pitch4, energy4 = upsample4(pitch.float()).to(pitch.dtype), upsample4(energy.float()).to(energy.dtype)
     x = decoder(sd, "decoder.", enc @ al4, pitch4, energy4, style)
     cond = style.unsqueeze(-1)
     z, _, _ = prior_encoder(sd, "prior_encoder.", x, noise["prior"])

@@ -91,6 +91,13 @@ cudaError_t pcph_source(const float* p4, const double* prefix, const SourceMeta*
                         const float* init_phase, const int* cu4, const RowMap& map, float* src, int ld,
                         __half* srcg, __half* srcl, int ldg, float gscale, float* dense_out, cudaStream_t st);
 
+// ---- stft_fft.cu
+cudaError_t stft_twiddles(double2* tw, double2* tw2, cudaStream_t st);
+// forward STFT of the hop-row source buffer -> |X| / atan2 phase rows [R, ldo] (fp32 masters and / or fp16 split twins)
+cudaError_t stft_fft(const float* src, int lds, const float* window, const double2* tw, const double2* tw2,
+                     const RowMap& map, float* mag, float* pha, int ldo, __half* magg, __half* magl, __half* phag,
+                     __half* phal, int ldh, cudaStream_t st);
+
 // ---- istft.cu
 cudaError_t polar_spec(const float* logamp, const float* phase, int ld, int n_bins, const RowMap& map, float* spec,
                        int lds, __half* specg, int ldsh, __half* specl, float gscale, cudaStream_t st);

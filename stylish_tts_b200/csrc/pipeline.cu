@@ -113,11 +113,10 @@ int set_layout(Context& c, int n_seg, const int* len_f, const int* len_f4) {
   ArenaPlan plan;
   std::map<std::string, size_t> off_f, off_h;
   // fp16 split twins (g = fp16(s x), l = fp16(s x - g)) of the operands of the island GEMMs (f16x3 / f16).
-  // SRC: the STFT operand as explicit frames [row, 1216] (1200 window taps + pad to a multiple of 64);
-  // pre-scales: SRC x 2^8 (|source| < ~5: keeps the residuals normal), SPEC x 2^-4 (e^logamp up to 1e6)
+  // pre-scale: SPEC x 2^-4 (e^logamp up to 1e6)
   struct GTwin { const char* name; int ldg; float gscale; };
   const GTwin g_names[] = {{"AMPN", 0, 1.f}, {"PHN", 0, 1.f}, {"CATP", 0, 1.f}, {"SPEC", 0, 0.0625f},
-                           {"HS", 0, 1.f},   {"HP", 0, 1.f},  {"SRC", 1216, 256.f}};
+                           {"HS", 0, 1.f},   {"HP", 0, 1.f}};
   auto gtwin = [&](const std::string& n) -> const GTwin* {
     for (const GTwin& q : g_names) if (n == q.name) return &q;
     return nullptr;
@@ -685,8 +684,7 @@ static int source_core(Context& c, Stage& S, const float* d_noise, const float* 
   Act& src = S.A("SRC");
   STTS_CK(pcph_prefix(S.R<float>("P4"), map, S.R<double>("PREFIX"), S.R<SourceMeta>("META"), st));
   STTS_CK(pcph_source(S.R<float>("P4"), S.R<double>("PREFIX"), S.R<SourceMeta>("META"), d_noise, d_init_phase,
-                      c.L4.d_cu, map, src.f, src.ld, S.twins ? src.g : nullptr, src.l, src.ldg, src.gscale,
-                      d_dense_out, st));
+                      c.L4.d_cu, map, src.f, src.ld, nullptr, nullptr, 0, 1.f, d_dense_out, st));
   return 0;
 }
 
@@ -715,18 +713,13 @@ int run_generator_core(Context& c, const float* d_style, const float* d_noise, c
   float* gb = S.R<float>("GB_GEN");
   STTS_CK(style_fc(c.vec["gen.fc_W"], c.vec["gen.fc_b"], d_style, c.J_gen, 64, c.L4.n_seg, gb, st));
   STTS_RET(source_core(c, S, d_noise, d_init_phase, nullptr, st));
-  {  // STFT of the source -> |X|, atan2 phase   (generator.py:407-410)
-    Epi e = S.epi(EPI_STFT, hs, 0);
-    e.out2 = hp.f; e.ldo2 = hp.ld; e.col20 = 0;
-    e.outh2 = S.tw(hp); e.ldh2 = hp.ld; e.colh20 = 0;
-    e.outg2 = S.twins ? hp.g : nullptr;
-    e.outl2 = S.twins ? hp.l : nullptr;
-    if (one_pass_island("gen.amp_prior")) e.outl = nullptr;      // residual twins only for three-pass consumers
-    if (one_pass_island("gen.phase_prior")) e.outl2 = nullptr;
-    e.seg_start = c.L4.d_seg_start;
-    if (lean && S.twins && e.outg != nullptr && e.outg2 != nullptr) { e.out = nullptr; e.out2 = nullptr; }
-    // 16-bit mode: fp16 split operand = explicit frames written by the source kernel -> the "stft16" pack
-    STTS_RET(run_gemm(c, c.gemm[S.twins ? "stft16" : "stft"], GC_ISLAND, &src, 0, nullptr, 0, e, map, st));
+  {  // STFT of the source -> |X|, atan2 phase   (generator.py:407-410): shared-memory FFT, stft_fft.cu
+    const bool keep32 = !(lean && S.twins);        // 16-bit fused path: only the fp16 twins the prior convs read
+    const double2* tw = reinterpret_cast<const double2*>(c.vec["stft_tw"]);
+    STTS_CK(stft_fft(src.f, src.ld, c.vec["win"], tw, tw + 1024, map, keep32 ? hs.f : nullptr, keep32 ? hp.f : nullptr,
+                     hs.ld, S.twins ? hs.g : nullptr, (S.twins && !one_pass_island("gen.amp_prior")) ? hs.l : nullptr,
+                     S.twins ? hp.g : nullptr, (S.twins && !one_pass_island("gen.phase_prior")) ? hp.l : nullptr, hs.ldg,
+                     st));
   }
   return run_generator_tail(c, d_style, d_audio, d_logamp, d_phase, st);
 }

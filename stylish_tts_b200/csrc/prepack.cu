@@ -646,23 +646,19 @@ int finalize_weights(Context& c) {
           default: *c_out = s0; *s_out = -c0; break;
         }
       };
-      // forward: rows (re_k, im_k) interleaved.  "stft" (fp32 / tf32 operand): K = 16 hop-taps x 75
-      // samples, each tap padded to 96 columns of the hop-row buffer.  "stft16" (fp16 split operand, 16-bit
-      // mode): the source kernel writes explicit frames [row, 1216], so K = 1200 window taps (+16 pad).
-      for (int variant = 0; variant < 2; ++variant) {
-        Builder b;
-        const int t[2] = {variant == 0 ? 16 : 1, 0}, pd[2] = {0, 0}, cp[2] = {variant == 0 ? 96 : 1216, 0};
-        b.init(2050, 1, t, pd, cp);
-        for (int k = 0; k <= 1024; ++k)
-          for (int n = 0; n < 1200; ++n) {
-            const int col = variant == 0 ? (n / 75) * 96 + n % 75 : n;
-            double ca, sa;
-            cs(k, 424 + n, &ca, &sa);
-            b.W[(size_t)(2 * k) * b.Ktot + col] = (float)(win[n] * ca);
-            b.W[(size_t)(2 * k + 1) * b.Ktot + col] = (sa == 0.0) ? 0.f : (float)(-win[n] * sa);
-          }
-        b.k_real = 1200;
-        c.gemm[variant == 0 ? "stft" : "stft16"] = b.upload(c);
+      // forward STFT: a shared-memory FFT (stft_fft.cu), not a contraction -- twiddle tables + the analysis window.
+      // The window is torch.hann_window(1200) as the reference's non-persistent `generator.stft.window` buffer holds it
+      // (generator.py:30) when the host passed it, else the correctly rounded formula.
+      {
+        std::vector<float> w32(1200);
+        const HostTensor* hw = c.has("speech_predictor/generator.stft.window") ? L.get("generator.stft.window") : nullptr;
+        for (int n = 0; n < 1200; ++n) w32[n] = (hw != nullptr && hw->numel() == 1200) ? hw->data[n] : (float)win[n];
+        put_vec(c, "win", w32);
+        std::vector<float> z(2 * (2 * 1024 + 2 * 513), 0.f);      // double2 tables: exp(-2 pi i m / 1024), exp(-2 pi i k / 2048)
+        put_vec(c, "stft_tw", z);
+        if (stft_twiddles(reinterpret_cast<double2*>(c.vec["stft_tw"]), reinterpret_cast<double2*>(c.vec["stft_tw"]) + 1024,
+                          nullptr) != cudaSuccess)
+          return fail(c, -5, "stft twiddle kernel launch failed");
       }
       {  // inverse: irfft (1/N, Hermitian doubling, imag of DC / Nyquist ignored) x window
         Builder b;

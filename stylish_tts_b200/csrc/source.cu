@@ -121,16 +121,18 @@ __global__ void __launch_bounds__(256) pcph_source_kernel(const float* __restric
       double sh = s1, ch = c1;
       float sum = 0.f;
       for (int hh = 1; hh <= mt.max_h; ++hh) {
-        if ((float)hh * p <= 12000.f) sum += (float)sh;
+        if (__fmul_rn((float)hh, p) <= 12000.f) sum = __fadd_rn(sum, (float)sh);
         const double sn = sh * c1 + ch * s1;
         ch = ch * c1 - sh * s1;
         sh = sn;
       }
-      const float nh = 12000.f / p;
-      const float amp = 0.1f * sqrtf(2.f / nh);
-      val = amp * sum;
+      const float nh = __fdiv_rn(12000.f, p);
+      const float amp = __fmul_rn(0.1f, __fsqrt_rn(__fdiv_rn(2.f, nh)));
+      val = __fmul_rn(amp, sum);
     }
-    val += 0.01f * noise[dense_base + t];
+    // harm + 0.01 * noise with both roundings of the reference (an FMA here is a 1-ulp difference of the source, which
+    // the STFT phase of near-real bins then amplifies)
+    val = __fadd_rn(val, __fmul_rn(0.01f, noise[dense_base + t]));
     src[(size_t)(s0 + h + 8) * ld + c] = val;
     if (srcg != nullptr) {
       // fp16 split twins of the STFT operand, written as explicit frames (im2col): frame m of the

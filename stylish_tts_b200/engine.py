@@ -84,6 +84,9 @@ class Engine:
                                                   t.dim()))
 
     def finalize(self):
+        # the analysis window of TorchSTFT is a non-persistent buffer of the reference module (generator.py:30), so it
+        # is not in any state_dict: hand over torch's own hann_window values (the forward STFT multiplies by them)
+        self.load_state("speech_predictor", {"generator.stft.window": torch.hann_window(1200, dtype=torch.float32)})
         self._check(self.lib.stts_finalize_weights(self.h))
         self.n_seg = 0
 
