@@ -11,6 +11,7 @@ for what in "$@"; do
     ref) timeout 600 python bench.py --impl reference --steps 2 --warmup 0 > gpurun_out/${tag}_ref.json 2> gpurun_out/${tag}_ref.err; echo "ref rc=$?" ;;
     smoke) timeout 600 python __graft_entry__.py smoke > gpurun_out/${tag}_smoke.log 2>&1; echo "smoke rc=$?" ;;
     launches) timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 2500 --csv --log-file gpurun_out/${tag}_launches.csv python bench.py --steps 1 --warmup 3 --lanes 1 --no-graph --no-extras --no-cpu-baseline > gpurun_out/${tag}_ncu.log 2>&1; echo "launches rc=$?" ;;
+    kern) timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"${KERN:-stft}" -c 12 --csv --log-file gpurun_out/${tag}_kern.csv python bench.py --steps 1 --warmup 3 --lanes 1 --no-graph --no-extras --no-cpu-baseline > gpurun_out/${tag}_kern.log 2>&1; echo "kern rc=$?"; grep -v "^==" gpurun_out/${tag}_kern.csv | awk -F'","' 'NR>1{print $5, $(NF)}' | tail -6 ;;
     *) echo "unknown step $what" ;;
   esac
 done
