@@ -68,7 +68,7 @@ cudaError_t rope_inplace(float* x, int ldx, int col0, int blk, int n_blocks, int
 cudaError_t attention(const float* Q, int ldq, int qcol, const float* K, int ldk, int kcol, const float* V, int ldv,
                       int vcol, int H, int D, float scale, int rd, const float2* rope_tab, const RowMap& qmap,
                       const RowMap& kmap, int max_tq, int max_tk, const int* q_tok, const int* q_cu, int band, float* out,
-                      int ldo, cudaStream_t st);
+                      int ldo, cudaStream_t st, __half* outg = nullptr, __half* outl = nullptr, int ldh = 0);
 cudaError_t rope_table(float2* tab, int n_pos, int rd, cudaStream_t st);
 cudaError_t dense_to_rows(const float* src, int C, const RowMap& map, const int* cu, float* dst, int ld, int col0,
                           cudaStream_t st);

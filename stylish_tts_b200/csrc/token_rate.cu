@@ -7,6 +7,8 @@
 // only what is not a GEMM lives here.  A packed token buffer has the same geometry as the
 // frame-rate buffers (common.cuh): utterances start on multiples of 128 rows, guard rows stay zero,
 // so `x * x_mask` of the reference is the identity and conv zero padding is free.
+#include <cstdlib>
+
 #include "kernels.h"
 
 namespace stts {
@@ -229,25 +231,25 @@ constexpr int kAttChunk = 64;
 // Stage ROWS rows x D features of a head into shared memory: dst[r][f] (or dst[f][r] when TRANSPOSE),
 // zero beyond nrows.  float4 global loads, issued in independent batches (the kernel is latency-bound:
 // few resident warps, so the loads of a batch must be in flight together).  128 threads.
-template <int D, int ROWS, bool TRANSPOSE>
+template <int D, int ROWS, bool TRANSPOSE, int NT = 128>
 __device__ __forceinline__ void stage_rows(const float* __restrict__ src, int ld, int row0, int nrows,
                                            float* __restrict__ dst, int dst_ld) {
   constexpr int D4 = D / 4;
-  constexpr int V4 = (ROWS * D4 + 127) / 128;                        // float4 per thread (guarded tail)
+  constexpr int V4 = (ROWS * D4 + NT - 1) / NT;                      // float4 per thread (guarded tail)
   constexpr int B = (V4 % 5 == 0) ? 5 : ((V4 % 4 == 0) ? 4 : ((V4 % 3 == 0) ? 3 : ((V4 % 2 == 0) ? 2 : 1)));
 #pragma unroll
   for (int b0 = 0; b0 < V4; b0 += B) {
     float4 v[B];
 #pragma unroll
     for (int u = 0; u < B; ++u) {
-      const int i = threadIdx.x + (b0 + u) * 128;
+      const int i = threadIdx.x + (b0 + u) * NT;
       const int r = i / D4, f4 = i - r * D4;
       v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
       if (i < ROWS * D4 && r < nrows) v[u] = *reinterpret_cast<const float4*>(src + (size_t)(row0 + r) * ld + 4 * f4);
     }
 #pragma unroll
     for (int u = 0; u < B; ++u) {
-      const int i = threadIdx.x + (b0 + u) * 128;
+      const int i = threadIdx.x + (b0 + u) * NT;
       const int r = i / D4, f = 4 * (i - r * D4);
       if (i < ROWS * D4) {
         if (TRANSPOSE) {
@@ -264,10 +266,11 @@ __device__ __forceinline__ void stage_rows(const float* __restrict__ src, int ld
 
 // partial RoPE in place on staged rows x[r][f] (row pitch ldx): the first rd features, half-split
 // pairs (j, j + rd/2), position pos0 + r; then an optional scale of the whole row block
+template <int NT = 128>
 __device__ __forceinline__ void rope_staged(float* x, int ldx, int nrows, int rd, int pos0,
                                             const float2* __restrict__ tab) {
   const int h = rd >> 1;
-  for (int i = threadIdx.x; i < nrows * h; i += 128) {
+  for (int i = threadIdx.x; i < nrows * h; i += NT) {
     const int r = i / h, j = i - r * h;
     const float2 cs = tab[(size_t)(pos0 + r) * h + j];
     const float a = x[r * ldx + j], b = x[r * ldx + j + h];
@@ -428,6 +431,195 @@ __global__ void __launch_bounds__(128) attention_tiled_kernel(const float* __res
   }
 }
 
+// ------------------------------------------------------------------------------ attention, single pass
+// One CTA = (128 / LPQ queries, head, utterance).  A query is owned by LPQ adjacent lanes, each holding D / LPQ
+// features of q and of the output accumulator in registers; keys / values stream through shared memory in chunks of
+// 64 rows (partial RoPE applied while staging, like above) and the softmax is the running-max form, so neither the
+// score matrix nor a second pass over V exists: K and V are staged once per CTA instead of once per 16 queries, and
+// the per-key work of a lane is 2 D / LPQ FMAs + one exp per 4 keys of rescaling.  fp32 throughout (accurate expf).
+//   band > 0: additive bias -1e4 where |key - q_tok[query]| <= band (inverted monotonic band).
+// Optional fp16 split twins of the output (operand of the following f16x3 projection GEMM).
+template <int D, int LPQ, int QPT, int NT, int KP>
+__global__ void __launch_bounds__(NT) attention_stream_kernel(const float* __restrict__ Q, int ldq, int qcol,
+                                                              const float* __restrict__ K, int ldk, int kcol,
+                                                              const float* __restrict__ V, int ldv, int vcol,
+                                                              float scale, int rd, const float2* __restrict__ tab,
+                                                              RowMap qmap, RowMap kmap, const int* __restrict__ q_tok,
+                                                              const int* __restrict__ q_cu, int band,
+                                                              float* __restrict__ out, int ldo,
+                                                              __half* __restrict__ outg, __half* __restrict__ outl,
+                                                              int ldh) {
+  extern __shared__ float sh[];
+  // A query group = LPQ x KP adjacent lanes: LPQ lanes split the head's features, KP lane sets split the keys of
+  // every chunk (key j of the chunk goes to set j % KP) and are merged once at the end (flash-decoding style), and
+  // the group owns QPT queries (register blocking: one shared-memory K / V read feeds QPT FMAs).  KP > 1 is for
+  // the short-sequence / small-head case (text encoders: ~126 tokens x 16 features), which is otherwise one
+  // dependent chain per thread on a handful of warps per SM.
+  constexpr int QPB = NT / (LPQ * KP) * QPT;     // queries per CTA
+  constexpr int DL = D / LPQ;
+  constexpr int KLD = D + 4;                     // row pitch of the staged K / V chunks (16-byte aligned rows)
+  static_assert(D % (4 * LPQ) == 0, "attention lane split");
+  const int seg = blockIdx.z, hd = blockIdx.y;
+  const int Tq = qmap.seg_len[seg], Tk = kmap.seg_len[seg];
+  const int q0 = blockIdx.x * QPB;
+  if (q0 >= Tq) return;
+  const int nq = (Tq - q0 < QPB) ? (Tq - q0) : QPB;
+  const int qrow0 = qmap.seg_start[seg] + q0, krow0 = kmap.seg_start[seg];
+  constexpr int KROWS = kAttChunk + 4 * KP;      // rows past the chunk are read (and masked) by the last key group
+  float* sq = sh;                                // [QPB][D]
+  float* sk = sq + QPB * D;                      // [KROWS][KLD]
+  float* sv = sk + KROWS * KLD;                  // [KROWS][KLD]
+  for (int i = threadIdx.x; i < 4 * KP * KLD; i += NT) {      // the pad rows must hold finite numbers (0 * p = 0)
+    sk[kAttChunk * KLD + i] = 0.f;
+    sv[kAttChunk * KLD + i] = 0.f;
+  }
+  // ---- queries: stage, rotate, scale; then every lane keeps its slices in registers
+  stage_rows<D, QPB, false, NT>(Q + qcol + hd * D, ldq, qrow0, nq, sq, D);
+  __syncthreads();
+  if (rd > 0) {
+    rope_staged<NT>(sq, D, nq, rd, q0, tab);
+    __syncthreads();
+  }
+  const int grp = threadIdx.x / (LPQ * KP), kp = (threadIdx.x / LPQ) % KP, part = threadIdx.x % LPQ;
+  float q[QPT][DL], acc[QPT][DL], m[QPT], l[QPT];
+  int tau[QPT];
+#pragma unroll
+  for (int a = 0; a < QPT; ++a) {
+    const int qi = grp * QPT + a;
+#pragma unroll
+    for (int i = 0; i < DL; ++i) { q[a][i] = sq[qi * D + part * DL + i] * scale; acc[a][i] = 0.f; }
+    tau[a] = (band > 0) ? q_tok[q_cu[seg] + q0 + (qi < nq ? qi : 0)] : 0;
+    m[a] = -3.0e38f;
+    l[a] = 0.f;
+  }
+  for (int c0 = 0; c0 < Tk; c0 += kAttChunk) {
+    const int nk = (Tk - c0 < kAttChunk) ? (Tk - c0) : kAttChunk;
+    __syncthreads();                             // previous chunk consumed
+    stage_rows<D, kAttChunk, false, NT>(K + kcol + hd * D, ldk, krow0 + c0, nk, sk, KLD);
+    stage_rows<D, kAttChunk, false, NT>(V + vcol + hd * D, ldv, krow0 + c0, nk, sv, KLD);
+    __syncthreads();
+    if (rd > 0) {
+      rope_staged<NT>(sk, KLD, nk, rd, c0, tab);
+      __syncthreads();
+    }
+#pragma unroll 1
+    for (int jb = 0; jb < nk; jb += 4 * KP) {    // this lane set's keys of the group: jb + u * KP + kp, u = 0 .. 3
+      float s[QPT][4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int jj = jb + u * KP + kp;         // < 64 + 4 KP: rows past the chunk are masked below, smem is padded
+        const float* kr = sk + jj * KLD + part * DL;
+        float d[QPT];
+#pragma unroll
+        for (int a = 0; a < QPT; ++a) d[a] = 0.f;
+#pragma unroll
+        for (int i = 0; i < DL; i += 4) {
+          const float4 kv = *reinterpret_cast<const float4*>(kr + i);
+#pragma unroll
+          for (int a = 0; a < QPT; ++a) {
+            d[a] = fmaf(q[a][i], kv.x, d[a]); d[a] = fmaf(q[a][i + 1], kv.y, d[a]);
+            d[a] = fmaf(q[a][i + 2], kv.z, d[a]); d[a] = fmaf(q[a][i + 3], kv.w, d[a]);
+          }
+        }
+        const int j = c0 + jj;
+#pragma unroll
+        for (int a = 0; a < QPT; ++a) {
+#pragma unroll
+          for (int o = 1; o < LPQ; o <<= 1) d[a] += __shfl_xor_sync(0xffffffffu, d[a], o);
+          if (band > 0 && j >= tau[a] - band && j <= tau[a] + band) d[a] += -1e4f;
+          s[a][u] = (jj < nk) ? d[a] : -3.0e38f;
+        }
+      }
+      float p[QPT][4];
+#pragma unroll
+      for (int a = 0; a < QPT; ++a) {
+        const float mn = fmaxf(fmaxf(fmaxf(s[a][0], s[a][1]), fmaxf(s[a][2], s[a][3])), m[a]);
+        const float corr = expf(m[a] - mn);      // first group: exp(-3e38 - finite) = 0 (and 1 if the set saw no key yet)
+#pragma unroll
+        for (int u = 0; u < 4; ++u) p[a][u] = (jb + u * KP + kp < nk) ? expf(s[a][u] - mn) : 0.f;
+        l[a] = fmaf(l[a], corr, (p[a][0] + p[a][1]) + (p[a][2] + p[a][3]));
+        m[a] = mn;
+#pragma unroll
+        for (int i = 0; i < DL; ++i) acc[a][i] *= corr;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const float* vr = sv + (jb + u * KP + kp) * KLD + part * DL;
+#pragma unroll
+        for (int i = 0; i < DL; i += 4) {
+          const float4 vv = *reinterpret_cast<const float4*>(vr + i);
+#pragma unroll
+          for (int a = 0; a < QPT; ++a) {
+            acc[a][i] = fmaf(p[a][u], vv.x, acc[a][i]); acc[a][i + 1] = fmaf(p[a][u], vv.y, acc[a][i + 1]);
+            acc[a][i + 2] = fmaf(p[a][u], vv.z, acc[a][i + 2]); acc[a][i + 3] = fmaf(p[a][u], vv.w, acc[a][i + 3]);
+          }
+        }
+      }
+    }
+  }
+  if constexpr (KP > 1) {                        // merge the KP partial softmaxes of every query
+#pragma unroll
+    for (int a = 0; a < QPT; ++a) {
+      float mt = m[a];
+#pragma unroll
+      for (int o = LPQ; o < LPQ * KP; o <<= 1) mt = fmaxf(mt, __shfl_xor_sync(0xffffffffu, mt, o));
+      const float f = expf(m[a] - mt);           // a set without keys has m = -3e38, l = 0: f = 0 (or 1 * 0)
+      float lt = l[a] * f;
+#pragma unroll
+      for (int o = LPQ; o < LPQ * KP; o <<= 1) lt += __shfl_xor_sync(0xffffffffu, lt, o);
+      l[a] = lt;
+#pragma unroll
+      for (int i = 0; i < DL; ++i) {
+        float v = acc[a][i] * f;
+#pragma unroll
+        for (int o = LPQ; o < LPQ * KP; o <<= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        acc[a][i] = v;
+      }
+    }
+  }
+#pragma unroll
+  for (int a = 0; a < QPT; ++a) {
+    const int qi = grp * QPT + a;
+    if (qi >= nq || kp != 0) continue;
+    const float inv = 1.f / l[a];
+    const size_t o = (size_t)(qrow0 + qi) * ldo + hd * D + part * DL;
+#pragma unroll
+    for (int i = 0; i < DL; i += 4) {
+      const float y[4] = {acc[a][i] * inv, acc[a][i + 1] * inv, acc[a][i + 2] * inv, acc[a][i + 3] * inv};
+      *reinterpret_cast<float4*>(out + o + i) = make_float4(y[0], y[1], y[2], y[3]);
+      if (outg != nullptr) {
+        const size_t og = (size_t)(qrow0 + qi) * ldh + hd * D + part * DL + i;
+        __half g[4], lo[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) f16_split(y[u], &g[u], &lo[u]);
+        *reinterpret_cast<uint2*>(outg + og) = *reinterpret_cast<const uint2*>(g);
+        if (outl != nullptr) *reinterpret_cast<uint2*>(outl + og) = *reinterpret_cast<const uint2*>(lo);
+      }
+    }
+  }
+}
+
+template <int D, int LPQ, int QPT, int NT, int KP>
+cudaError_t launch_attention_stream(const float* Q, int ldq, int qcol, const float* K, int ldk, int kcol, const float* V,
+                                    int ldv, int vcol, int H, float scale, int rd, const float2* tab, const RowMap& qmap,
+                                    const RowMap& kmap, int max_tq, const int* q_tok, const int* q_cu, int band,
+                                    float* out, int ldo, __half* outg, __half* outl, int ldh, cudaStream_t st) {
+  constexpr int QPB = NT / (LPQ * KP) * QPT;
+  const size_t smem = (size_t)(QPB * D + 2 * (kAttChunk + 4 * KP) * (D + 4)) * sizeof(float);
+  static bool configured = false;
+  if (smem > 48 * 1024 && !configured) {
+    cudaError_t e = cudaFuncSetAttribute(attention_stream_kernel<D, LPQ, QPT, NT, KP>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  dim3 grid((max_tq + QPB - 1) / QPB, H, qmap.n_seg);
+  attention_stream_kernel<D, LPQ, QPT, NT, KP><<<grid, NT, smem, st>>>(Q, ldq, qcol, K, ldk, kcol, V, ldv, vcol, scale, rd,
+                                                                   tab, qmap, kmap, q_tok, q_cu, band, out, ldo, outg,
+                                                                   outl, ldh);
+  return cudaGetLastError();
+}
+
 template <int D, int QB>
 cudaError_t launch_attention_tiled(const float* Q, int ldq, int qcol, const float* K, int ldk, int kcol, const float* V,
                                    int ldv, int vcol, int H, float scale, int rd, const float2* tab, const RowMap& qmap,
@@ -449,14 +641,30 @@ cudaError_t launch_attention_tiled(const float* Q, int ldq, int qcol, const floa
   return cudaGetLastError();
 }
 
-// rd: features of every head that still need the RoPE rotation (0: Q / K are used as stored).  The
-// tiled kernels rotate while staging; for other head sizes the generic kernel runs after an in-place
-// rotation pass.
+// rd: features of every head that still need the RoPE rotation (0: Q / K are used as stored).  The head sizes of
+// the model (16 text encoders, 40 cross attention, 96 / 160 prosody encoders) run the single-pass streaming kernel
+// (STTS_ATT_TILED=1 switches back to the two-pass tiled kernel for A/B runs); other head sizes take the generic
+// kernel after an in-place rotation pass.  outg / outl: optional fp16 split twins of the output.
 cudaError_t attention(const float* Q, int ldq, int qcol, const float* K, int ldk, int kcol, const float* V, int ldv,
                       int vcol, int H, int D, float scale, int rd, const float2* rope_tab, const RowMap& qmap,
                       const RowMap& kmap, int max_tq, int max_tk, const int* q_tok, const int* q_cu, int band, float* out,
-                      int ldo, cudaStream_t st) {
+                      int ldo, cudaStream_t st, __half* outg, __half* outl, int ldh) {
   if (D % 4 != 0) return cudaErrorInvalidValue;
+  static const bool tiled = [] { const char* e = std::getenv("STTS_ATT_TILED"); return e != nullptr && e[0] == '1'; }();
+  const bool twins = outg != nullptr;
+  if (!tiled && (rd == 0 || rope_tab != nullptr)) {
+#define STTS_ATTS(DD, LL, QQ, NN, KK)                                                                                 \
+  if (D == DD)                                                                                                        \
+    return launch_attention_stream<DD, LL, QQ, NN, KK>(Q, ldq, qcol, K, ldk, kcol, V, ldv, vcol, H, scale, rd,        \
+                                                       rope_tab, qmap, kmap, max_tq, q_tok, q_cu, band, out, ldo,     \
+                                                       outg, outl, ldh, st);
+    STTS_ATTS(16, 1, 1, 128, 4)    // text encoders: 32 queries per CTA, 4 key sets per query
+    STTS_ATTS(40, 1, 2, 64, 1)     // cross attention: 128 frames per CTA
+    STTS_ATTS(96, 4, 2, 128, 1)    // duration prosody encoder: 64 queries per CTA
+    STTS_ATTS(160, 8, 2, 128, 1)    // 32 queries per CTA, 8 lanes x 20 features per query
+#undef STTS_ATTS
+  }
+  if (twins) return cudaErrorInvalidValue;       // the fallback kernels do not write twins
   // queries per CTA: as many as keep <= 20 outputs per thread (K / V are staged once per CTA)
 #define STTS_ATT(DD, QQ)                                                                                              \
   if (D == DD && (rd == 0 || rope_tab != nullptr))                                                                    \

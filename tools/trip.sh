@@ -12,6 +12,7 @@ for what in "$@"; do
     smoke) timeout 600 python __graft_entry__.py smoke > gpurun_out/${tag}_smoke.log 2>&1; echo "smoke rc=$?" ;;
     launches) timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 2500 --csv --log-file gpurun_out/${tag}_launches.csv python bench.py --steps 1 --warmup 3 --lanes 1 --no-graph --no-extras --no-cpu-baseline > gpurun_out/${tag}_ncu.log 2>&1; echo "launches rc=$?" ;;
     kern) timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"${KERN:-stft}" -c 12 --csv --log-file gpurun_out/${tag}_kern.csv python bench.py --steps 1 --warmup 3 --lanes 1 --no-graph --no-extras --no-cpu-baseline > gpurun_out/${tag}_kern.log 2>&1; echo "kern rc=$?"; grep -v "^==" gpurun_out/${tag}_kern.csv | awk -F'","' 'NR>1{print $5, $(NF)}' | tail -6 ;;
+    full) timeout 900 ncu --set full --import-source on --clock-control none -k regex:"${KERN:-stft}" -s ${SKIP:-4} -c ${COUNT:-1} -o gpurun_out/${tag}_full -f python bench.py --steps 1 --warmup 3 --lanes 1 --no-graph --no-extras --no-cpu-baseline > gpurun_out/${tag}_full.log 2>&1; echo "full rc=$?"; ncu -i gpurun_out/${tag}_full.ncu-rep --page details > gpurun_out/${tag}_full.txt 2>&1 ;;
     *) echo "unknown step $what" ;;
   esac
 done
