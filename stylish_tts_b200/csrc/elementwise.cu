@@ -719,7 +719,8 @@ cudaError_t grn_weights(const float* W, int N, int K, const float* scale, int n_
 __global__ void __launch_bounds__(256) seg_affine_kernel(float* __restrict__ x, int ldx, int C, RowMap map,
                                                          const float* __restrict__ scale,
                                                          const float* __restrict__ shift,
-                                                         twin_t* __restrict__ xh, int ldxh) {
+                                                         twin_t* __restrict__ xh, int ldxh,
+                                                         __half* __restrict__ xg, __half* __restrict__ xl) {
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
   if (seg < 0) return;
@@ -738,14 +739,20 @@ __global__ void __launch_bounds__(256) seg_affine_kernel(float* __restrict__ x, 
       *reinterpret_cast<twin2_t*>(xh + r * ldxh + c) = to_twin2(v.x, v.y);
       *reinterpret_cast<twin2_t*>(xh + r * ldxh + c + 2) = to_twin2(v.z, v.w);
     }
+    if (xg != nullptr) {                         // fp16 split twins (same pitch as x): operand of an f16x3 GEMM
+      const float vv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) f16_split(vv[j], xg + r * ldx + c + j, xl + r * ldx + c + j);
+    }
   }
 }
 
 cudaError_t grn_apply(float* x, int ldx, int C, const RowMap& map, const float* gx, const float* gamma,
-                      const float* beta, float* scale_scratch, twin_t* xh, int ldxh, cudaStream_t st) {
+                      const float* beta, float* scale_scratch, twin_t* xh, int ldxh, cudaStream_t st, __half* xg,
+                      __half* xl) {
   grn_scale_kernel<<<map.n_seg, 256, 0, st>>>(gx, C, gamma, scale_scratch);
   dim3 grid(map.n_tiles, 4);
-  seg_affine_kernel<<<grid, 256, 0, st>>>(x, ldx, C, map, scale_scratch, beta, xh, ldxh);
+  seg_affine_kernel<<<grid, 256, 0, st>>>(x, ldx, C, map, scale_scratch, beta, xh, ldxh, xg, xl);
   return cudaGetLastError();
 }
 

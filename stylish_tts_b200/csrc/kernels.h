@@ -48,7 +48,8 @@ cudaError_t adaln2(const float* x, int ldx, const RowMap& map, const float* gb1,
                    float* y1, float* y2, int ldy, __half* y1g, __half* y2g, int ldyh, __half* y1l, __half* y2l,
                    cudaStream_t st);
 cudaError_t grn_apply(float* x, int ldx, int C, const RowMap& map, const float* gx, const float* gamma,
-                      const float* beta, float* scale_scratch, twin_t* xh, int ldxh, cudaStream_t st);
+                      const float* beta, float* scale_scratch, twin_t* xh, int ldxh, cudaStream_t st,
+                      __half* xg = nullptr, __half* xl = nullptr);
 cudaError_t grn_scale_partials(const float* colss, int ld, int C, const RowMap& map, const float* gamma, float* gx,
                                float* scale, cudaStream_t st);
 cudaError_t grn_weights(const float* W, int N, int K, const float* scale, int n_seg, twin_t* Wu, cudaStream_t st);
@@ -60,9 +61,10 @@ cudaError_t twin_refresh(const float* f, int ld, int C, const RowMap& map, __hal
 
 // ---- token_rate.cu
 cudaError_t embed_tokens(const int* tok, const int* cu_tok, const float* table, int C, int n_vocab, const RowMap& map,
-                         float* x, int ldx, cudaStream_t st);
+                         float* x, int ldx, cudaStream_t st, __half* xg = nullptr, __half* xl = nullptr);
 cudaError_t row_ln(const float* x, int ldx, int C, const RowMap& map, const float* gamma, const float* beta,
-                   int seg_stride, float eps, int relu, float* y, int ldy, cudaStream_t st);
+                   int seg_stride, float eps, int relu, float* y, int ldy, cudaStream_t st, __half* yg = nullptr,
+                   __half* yl = nullptr);
 cudaError_t rope_inplace(float* x, int ldx, int col0, int blk, int n_blocks, int H, int D, int rd, const RowMap& map,
                          cudaStream_t st);
 cudaError_t attention(const float* Q, int ldq, int qcol, const float* K, int ldk, int kcol, const float* V, int ldv,
@@ -71,10 +73,11 @@ cudaError_t attention(const float* Q, int ldq, int qcol, const float* K, int ldk
                       int ldo, cudaStream_t st, __half* outg = nullptr, __half* outl = nullptr, int ldh = 0);
 cudaError_t rope_table(float2* tab, int n_pos, int rd, cudaStream_t st);
 cudaError_t dense_to_rows(const float* src, int C, const RowMap& map, const int* cu, float* dst, int ld, int col0,
-                          cudaStream_t st);
-cudaError_t seg_broadcast(const float* vec, int C, const RowMap& map, float* dst, int ld, int col0, cudaStream_t st);
+                          cudaStream_t st, __half* dg = nullptr, __half* dl = nullptr);
+cudaError_t seg_broadcast(const float* vec, int C, const RowMap& map, float* dst, int ld, int col0, cudaStream_t st,
+                          __half* dg = nullptr, __half* dl = nullptr);
 cudaError_t dwconv_rows(const float* x, int ldx, int C, int K, const float* w, const float* b, const RowMap& map,
-                        int act, float* y, int ldy, cudaStream_t st);
+                        int act, float* y, int ldy, cudaStream_t st, __half* yg = nullptr, __half* yl = nullptr);
 cudaError_t rows_to_dense(const float* src, int ld, int C, const RowMap& map, const int* cu, float* dst,
                           cudaStream_t st);
 

@@ -116,7 +116,9 @@ int set_layout(Context& c, int n_seg, const int* len_f, const int* len_f4) {
   // pre-scale: SPEC x 2^-4 (e^logamp up to 1e6)
   struct GTwin { const char* name; int ldg; float gscale; };
   const GTwin g_names[] = {{"AMPN", 0, 1.f}, {"PHN", 0, 1.f}, {"CATP", 0, 1.f}, {"SPEC", 0, 0.0625f},
-                           {"HS", 0, 1.f},   {"HP", 0, 1.f}};
+                           {"HS", 0, 1.f},   {"HP", 0, 1.f},
+                           // frame x token cross-attention block (token_pipeline.cu run_pe_cross): f16x3 operands
+                           {"PB", 0, 1.f},   {"PACT", 0, 1.f}, {"PY1", 0, 1.f}};
   auto gtwin = [&](const std::string& n) -> const GTwin* {
     for (const GTwin& q : g_names) if (n == q.name) return &q;
     return nullptr;
@@ -423,7 +425,7 @@ int ada_block(Stage& S, const std::string& name, const Act& x, int cin, int cout
                     S.tw(act1), act1.ld, S.st));
   {
     Epi e = S.epi(EPI_BIAS, y1, 0);
-    e.outh = nullptr;
+    e.outh = nullptr; e.outg = nullptr; e.outl = nullptr;
     if (fuse) { e.colsum = sf->psy; e.colsq = sf->psy + sf->ny; e.colst_ld = sf->ldy; }
     STTS_RET(run_gemm(c, g1, GC_BODY, &act1, 0, nullptr, 0, e, map, S.st));
   }
@@ -437,6 +439,7 @@ int ada_block(Stage& S, const std::string& name, const Act& x, int cin, int cout
                     S.tw(act2), act2.ld, S.st));
   {
     Epi e = S.epi(EPI_RES_SCALE, dst, dst_col);
+    e.outg = nullptr; e.outl = nullptr;          // body GEMMs read the one-pass twin (outh) only
     e.scale = 0.70710678118654752440f;
     if (g2.n_kseg == 1) { e.res = x.f; e.ldr = x.ld; e.rcol0 = 0; }   // identity shortcut
     if (fuse) { e.colsum = sf->psx; e.colsq = sf->psx + sf->nx; e.colst_ld = sf->ldx; }   // = the next block's input

@@ -40,12 +40,19 @@ int set_token_layout(Context& c, int n_seg, const int* len_t) {
                         {"SX", 64}, {"SY", 64}, {"SH", 256}};
   // three independent buffer sets ("slots"): the speech / pitch-energy / duration chains only share
   // the tokens, so the host may enqueue them on three streams (synth.py) without aliasing scratch
+  // every buffer also carries fp16 split twins g / l (same pitch): in 16-bit mode the token-rate GEMMs run the
+  // three-pass fp16 split (f16x3, ~2^-22: fp32-grade, the duration logits decide integer durations) on them
   size_t used = 0;
   std::map<std::string, size_t> off;
   for (int slot = 0; slot < 3; ++slot)
     for (const Want& w : wants) {
-      off[std::string(w.name) + "#" + std::to_string(slot)] = used;
+      const std::string key = std::string(w.name) + "#" + std::to_string(slot);
+      off[key] = used;
       used += up1k((size_t)R * w.ld * 4);
+      off[key + ".g"] = used;
+      used += up1k((size_t)R * w.ld * 2);
+      off[key + ".l"] = used;
+      used += up1k((size_t)R * w.ld * 2);
     }
   const char* ints[] = {"tile_seg", "tile_nvalid", "seg_start", "seg_len", "cu"};
   const size_t int_bytes[] = {(size_t)nt * 4, (size_t)nt * 4, (size_t)B * 4, (size_t)B * 4, (size_t)(B + 1) * 4};
@@ -76,6 +83,9 @@ int set_token_layout(Context& c, int n_seg, const int* len_t) {
     for (const Want& w : wants) {
       const std::string key = std::string(w.name) + "#" + std::to_string(slot);
       Act a; a.ld = w.ld; a.rows = R; a.f = reinterpret_cast<float*>(c.tarena + off[key]); a.h = nullptr;
+      a.g = reinterpret_cast<__half*>(c.tarena + off[key + ".g"]);
+      a.l = reinterpret_cast<__half*>(c.tarena + off[key + ".l"]);
+      a.ldg = w.ld; a.gscale = 1.f;
       c.tact[key] = a;
     }
   Layout& L = c.LT;
@@ -110,12 +120,18 @@ const float2* rope_tab(Context& c, int rd, cudaStream_t st) {
   return tab;
 }
 
-Epi mk_epi(int kind, const Act& dst, int col0) {
+// tw: also write the fp16 split twins of the output (16-bit mode, when a GEMM reads it next)
+Epi mk_epi(int kind, const Act& dst, int col0, bool tw = false) {
   Epi e;
   std::memset(&e, 0, sizeof(e));
   e.kind = kind; e.out = dst.f; e.ldo = dst.ld; e.col0 = col0; e.scale = 1.f;
+  if (tw && dst.g != nullptr) { e.outg = dst.g; e.outl = dst.l; e.ldh = dst.ldg; e.colh0 = col0; }
   return e;
 }
+struct Tw {                      // twin pointers of an Act in 16-bit mode, nulls otherwise
+  __half* g; __half* l;
+  Tw(const Context& c, const Act& a) : g(c.precision == 1 ? a.g : nullptr), l(c.precision == 1 ? a.l : nullptr) {}
+};
 }  // namespace
 
 // d_tokens: int32 [sum T] utterances concatenated.  Outputs (either may be null), token-major dense:
@@ -129,7 +145,9 @@ int run_text_encoder(Context& c, const std::string& nm, const int* d_tokens, flo
   Act &ta = c.tact["TA" + sl], &tb = c.tact["TB" + sl], &tcb = c.tact["TC" + sl], &tx = c.tact["TX" + sl];
   Act &to = c.tact["TO" + sl], &tqkv = c.tact["TQKV" + sl], &th = c.tact["TH" + sl], &tmu = c.tact["TMU" + sl];
   const int C = 128, H = 8, D = C / H, rd = D / 2;
-  STTS_CK(embed_tokens(d_tokens, c.LT.d_cu, c.vec[nm + ".emb"], C, c.vec_len[nm + ".vocab"], map, ta.f, ta.ld, st));
+  const bool t16 = c.precision == 1;             // 16-bit mode: every GEMM operand below carries fp16 split twins
+  STTS_CK(embed_tokens(d_tokens, c.LT.d_cu, c.vec[nm + ".emb"], C, c.vec_len[nm + ".vocab"], map, ta.f, ta.ld, st,
+                       Tw(c, ta).g, Tw(c, ta).l));
   // ---- prenet: 3 x (conv k5 -> channel LayerNorm (eps 1e-4) -> ReLU), then x + proj(y)
   const Act* y = &ta;
   Act* pp[2] = {&tb, &tcb};
@@ -137,11 +155,12 @@ int run_text_encoder(Context& c, const std::string& nm, const int* d_tokens, flo
     const std::string n = nm + ".pre" + std::to_string(i);
     Act& dst = *pp[i & 1];
     STTS_RET(run_gemm(c, c.gemm[n], GC_ISLAND, y, 0, nullptr, 0, mk_epi(EPI_BIAS, dst, 0), map, st));
-    STTS_CK(row_ln(dst.f, dst.ld, C, map, c.vec[n + ".g"], c.vec[n + ".b"], 0, 1e-4f, 1, dst.f, dst.ld, st));
+    STTS_CK(row_ln(dst.f, dst.ld, C, map, c.vec[n + ".g"], c.vec[n + ".b"], 0, 1e-4f, 1, dst.f, dst.ld, st,
+                   Tw(c, dst).g, Tw(c, dst).l));
     y = &dst;
   }
   {
-    Epi e = mk_epi(EPI_ADD, tx, 0);
+    Epi e = mk_epi(EPI_ADD, tx, 0, t16);
     e.res = ta.f; e.ldr = ta.ld; e.rcol0 = 0;
     STTS_RET(run_gemm(c, c.gemm[nm + ".preproj"], GC_ISLAND, y, 0, nullptr, 0, e, map, st));
   }
@@ -153,23 +172,25 @@ int run_text_encoder(Context& c, const std::string& nm, const int* d_tokens, flo
     STTS_RET(run_gemm(c, c.gemm[n + ".qkv"], GC_ISLAND, &tx, 0, nullptr, 0, mk_epi(EPI_BIAS, tqkv, 0), map, st));
     // partial RoPE of q / k is applied inside the attention kernel while it stages the rows
     STTS_CK(attention(tqkv.f, tqkv.ld, 0, tqkv.f, tqkv.ld, C, tqkv.f, tqkv.ld, 2 * C, H, D, scale, rd, rope_tab(c, rd, st), map, map, c.max_t,
-                      c.max_t, nullptr, nullptr, 0, to.f, to.ld, st));
+                      c.max_t, nullptr, nullptr, 0, to.f, to.ld, st, Tw(c, to).g, Tw(c, to).l, to.ldg));
     {
       Epi e = mk_epi(EPI_ADD, tb, 0);
       e.res = tx.f; e.ldr = tx.ld; e.rcol0 = 0;
       STTS_RET(run_gemm(c, c.gemm[n + ".o"], GC_ISLAND, &to, 0, nullptr, 0, e, map, st));
     }
-    STTS_CK(row_ln(tb.f, tb.ld, C, map, c.vec[n + ".n1.g"], c.vec[n + ".n1.b"], 0, 1e-4f, 0, tx.f, tx.ld, st));
-    STTS_RET(run_gemm(c, c.gemm[n + ".ff1"], GC_ISLAND, &tx, 0, nullptr, 0, mk_epi(EPI_RELU, th, 0), map, st));
+    STTS_CK(row_ln(tb.f, tb.ld, C, map, c.vec[n + ".n1.g"], c.vec[n + ".n1.b"], 0, 1e-4f, 0, tx.f, tx.ld, st,
+                   Tw(c, tx).g, Tw(c, tx).l));
+    STTS_RET(run_gemm(c, c.gemm[n + ".ff1"], GC_ISLAND, &tx, 0, nullptr, 0, mk_epi(EPI_RELU, th, 0, t16), map, st));
     {
       Epi e = mk_epi(EPI_ADD, tb, 0);
       e.res = tx.f; e.ldr = tx.ld; e.rcol0 = 0;
       STTS_RET(run_gemm(c, c.gemm[n + ".ff2"], GC_ISLAND, &th, 0, nullptr, 0, e, map, st));
     }
-    STTS_CK(row_ln(tb.f, tb.ld, C, map, c.vec[n + ".n2.g"], c.vec[n + ".n2.b"], 0, 1e-4f, 0, tx.f, tx.ld, st));
+    STTS_CK(row_ln(tb.f, tb.ld, C, map, c.vec[n + ".n2.g"], c.vec[n + ".n2.b"], 0, 1e-4f, 0, tx.f, tx.ld, st,
+                   Tw(c, tx).g, Tw(c, tx).l));
   }
   const PackedGemm& pm = c.gemm[nm + ".projm"];
-  STTS_RET(run_gemm(c, pm, GC_ISLAND, &tx, 0, nullptr, 0, mk_epi(EPI_BIAS, tmu, 0), map, st));
+  STTS_RET(run_gemm(c, pm, GC_ISLAND, &tx, 0, nullptr, 0, mk_epi(EPI_BIAS, tmu, 0, t16), map, st));   // mu feeds the style conv
   if (d_mu_tok) STTS_CK(rows_to_dense(tmu.f, tmu.ld, pm.N, map, c.LT.d_cu, d_mu_tok, st));
   if (d_x_tok) STTS_CK(rows_to_dense(tx.f, tx.ld, C, map, c.LT.d_cu, d_x_tok, st));
   return 0;
@@ -191,29 +212,32 @@ int run_prosody_encoder(Context& c, const std::string& nm, const float* d_enc_to
   Act &pqkv = c.tact["PQKV" + sl], &ph = c.tact["PH" + sl], &pl = c.tact["PL" + sl];
   float* gb = reinterpret_cast<float*>(c.traw["GBT" + sl]);
   STTS_CK(style_fc(c.vec[nm + ".fc_W"], c.vec[nm + ".fc_b"], d_style, J, 64, c.LT.n_seg, gb, st));
-  STTS_CK(dense_to_rows(d_enc_tok, dm, map, c.LT.d_cu, px.f, px.ld, 0, st));
-  STTS_CK(seg_broadcast(d_style, sty, map, px.f, px.ld, dm, st));
+  const bool t16 = c.precision == 1;
+  STTS_CK(dense_to_rows(d_enc_tok, dm, map, c.LT.d_cu, px.f, px.ld, 0, st, Tw(c, px).g, Tw(c, px).l));
+  STTS_CK(seg_broadcast(d_style, sty, map, px.f, px.ld, dm, st, Tw(c, px).g, Tw(c, px).l));
   const float scale = 1.0f / std::sqrt((float)D);
   for (int l = 0; l < n_layers; ++l) {
     const std::string n = nm + ".l" + std::to_string(l);
     STTS_RET(run_gemm(c, c.gemm[n + ".qkv"], GC_ISLAND, &px, 0, nullptr, 0, mk_epi(EPI_BIAS, pqkv, 0), map, st));
     STTS_CK(attention(pqkv.f, pqkv.ld, 0, pqkv.f, pqkv.ld, hid, pqkv.f, pqkv.ld, 2 * hid, H, D, scale, rd, rope_tab(c, rd, st), map, map,
-                      c.max_t, c.max_t, nullptr, nullptr, 0, po.f, po.ld, st));
+                      c.max_t, c.max_t, nullptr, nullptr, 0, po.f, po.ld, st, Tw(c, po).g, Tw(c, po).l, po.ldg));
     {
       Epi e = mk_epi(EPI_ADD, pb, 0);
       e.res = px.f; e.ldr = px.ld; e.rcol0 = 0;
       STTS_RET(run_gemm(c, c.gemm[n + ".o"], GC_ISLAND, &po, 0, nullptr, 0, e, map, st));
     }
-    STTS_CK(row_ln(pb.f, pb.ld, hid, map, gb + c.fc_off[n + ".n1"], nullptr, J, 1e-5f, 0, py.f, py.ld, st));
-    STTS_RET(run_gemm(c, c.gemm[n + ".ff1"], GC_ISLAND, &py, 0, nullptr, 0, mk_epi(EPI_RELU, ph, 0), map, st));
+    STTS_CK(row_ln(pb.f, pb.ld, hid, map, gb + c.fc_off[n + ".n1"], nullptr, J, 1e-5f, 0, py.f, py.ld, st,
+                   Tw(c, py).g, Tw(c, py).l));
+    STTS_RET(run_gemm(c, c.gemm[n + ".ff1"], GC_ISLAND, &py, 0, nullptr, 0, mk_epi(EPI_RELU, ph, 0, t16), map, st));
     {
       Epi e = mk_epi(EPI_ADD, pb, 0);
       e.res = py.f; e.ldr = py.ld; e.rcol0 = 0;
       STTS_RET(run_gemm(c, c.gemm[n + ".ff2"], GC_ISLAND, &ph, 0, nullptr, 0, e, map, st));
     }
-    STTS_CK(row_ln(pb.f, pb.ld, hid, map, gb + c.fc_off[n + ".n2"], nullptr, J, 1e-5f, 0, py.f, py.ld, st));
-    // x = cat([proj(x), style]): the style columns of PX are still in place
-    STTS_RET(run_gemm(c, c.gemm[n + ".proj"], GC_ISLAND, &py, 0, nullptr, 0, mk_epi(EPI_BIAS, px, 0), map, st));
+    STTS_CK(row_ln(pb.f, pb.ld, hid, map, gb + c.fc_off[n + ".n2"], nullptr, J, 1e-5f, 0, py.f, py.ld, st,
+                   Tw(c, py).g, Tw(c, py).l));
+    // x = cat([proj(x), style]): the style columns of PX (and of its twins) are still in place
+    STTS_RET(run_gemm(c, c.gemm[n + ".proj"], GC_ISLAND, &py, 0, nullptr, 0, mk_epi(EPI_BIAS, px, 0, t16), map, st));
   }
   if (d_out_tok) STTS_CK(rows_to_dense(px.f, px.ld, hid, map, c.LT.d_cu, d_out_tok, st));
   if (d_logits_tok) {
@@ -236,7 +260,8 @@ int run_style_encoder(Context& c, const std::string& nm, const float* d_enc_tok,
   Act &tmu = c.tact["TMU" + sl], &sx = c.tact["SX" + sl], &sy = c.tact["SY" + sl], &sh = c.tact["SH" + sl];
   const PackedGemm& gin = c.gemm[nm + ".in"];
   const int inter = (int)(gin.k_real / gin.taps[0] + 0.5);
-  if (d_enc_tok) STTS_CK(dense_to_rows(d_enc_tok, inter, map, c.LT.d_cu, tmu.f, tmu.ld, 0, st));
+  const bool t16 = c.precision == 1;
+  if (d_enc_tok) STTS_CK(dense_to_rows(d_enc_tok, inter, map, c.LT.d_cu, tmu.f, tmu.ld, 0, st, Tw(c, tmu).g, Tw(c, tmu).l));
   STTS_RET(run_gemm(c, gin, GC_ISLAND, &tmu, 0, nullptr, 0, mk_epi(EPI_BIAS, sx, 0), map, st));
   double* stat = reinterpret_cast<double*>(c.traw["SSTAT" + sl]);
   float* vec = reinterpret_cast<float*>(c.traw["SVEC" + sl]);
@@ -247,11 +272,13 @@ int run_style_encoder(Context& c, const std::string& nm, const float* d_enc_tok,
     const std::string n = nm + ".b" + std::to_string(i);
     STTS_CK(dwconv_rows(sx.f, sx.ld, 64, c.vec_len[n + ".dw_k"], c.vec[n + ".dw_w"], c.vec[n + ".dw_b"], map, 0, sy.f,
                         sy.ld, st));
-    STTS_CK(row_ln(sy.f, sy.ld, 64, map, c.vec[n + ".ln_g"], c.vec[n + ".ln_b"], 0, 1e-6f, 0, sy.f, sy.ld, st));
+    STTS_CK(row_ln(sy.f, sy.ld, 64, map, c.vec[n + ".ln_g"], c.vec[n + ".ln_b"], 0, 1e-6f, 0, sy.f, sy.ld, st,
+                   Tw(c, sy).g, Tw(c, sy).l));
     STTS_RET(run_gemm(c, c.gemm[n + ".pw1"], GC_ISLAND, &sy, 0, nullptr, 0, mk_epi(EPI_GELU, sh, 0), map, st));
     STTS_CK(colstats(sh.f, sh.ld, 256, map, 1, 0.f, stat, gx, nullptr, st));
     c.launches++;
-    STTS_CK(grn_apply(sh.f, sh.ld, 256, map, gx, c.vec[n + ".grn_gamma"], c.vec[n + ".grn_beta"], gscale, nullptr, 0, st));
+    STTS_CK(grn_apply(sh.f, sh.ld, 256, map, gx, c.vec[n + ".grn_gamma"], c.vec[n + ".grn_beta"], gscale, nullptr, 0, st,
+                      Tw(c, sh).g, Tw(c, sh).l));
     c.launches++;
     {
       Epi e = mk_epi(EPI_ADD, sx, 0);
@@ -286,11 +313,14 @@ int run_pe_cross(Context& c, const float* d_prosody_tok, const float* d_style, c
   if (J > 2048) return fail(c, -6, "cross-attention: style FC too wide");
   STTS_CK(style_fc(c.vec[nm + ".fc_W"], c.vec[nm + ".fc_b"], d_style, J, 64, c.LT.n_seg, gb, st));
   if (d_prosody_tok) STTS_CK(dense_to_rows(d_prosody_tok, C, tmap, c.LT.d_cu, tpx.f, tpx.ld, 0, st));
+  const bool t16 = c.precision == 1;
   // base: gather tokens -> frames.  expand_tokens reads a token-major dense matrix; the packed rows of
   // an utterance are contiguous, so the packed buffer is addressed with seg_start as the token offset
   STTS_CK(expand_tokens(tpx.f, tpx.ld, d_idx, d_cu_frames, c.LT.d_seg_start, 1, fmap, pa.f, pa.ld, 0, nullptr, 0, 0, st));
-  STTS_CK(row_ln(pa.f, pa.ld, C, fmap, gb + c.fc_off[nm + ".qn"], nullptr, J, 1e-5f, 0, pb.f, pb.ld, st));
-  STTS_CK(row_ln(tpx.f, tpx.ld, C, tmap, gb + c.fc_off[nm + ".kn"], nullptr, J, 1e-5f, 0, tpy.f, tpy.ld, st));
+  STTS_CK(row_ln(pa.f, pa.ld, C, fmap, gb + c.fc_off[nm + ".qn"], nullptr, J, 1e-5f, 0, pb.f, pb.ld, st,
+                 Tw(c, pb).g, Tw(c, pb).l));
+  STTS_CK(row_ln(tpx.f, tpx.ld, C, tmap, gb + c.fc_off[nm + ".kn"], nullptr, J, 1e-5f, 0, tpy.f, tpy.ld, st,
+                 Tw(c, tpy).g, Tw(c, tpy).l));
   Epi eq = mk_epi(EPI_BIAS, pact, 0);
   STTS_RET(run_gemm(c, c.gemm[nm + ".q"], GC_ISLAND, &pb, 0, nullptr, 0, eq, fmap, st));
   STTS_RET(run_gemm(c, c.gemm[nm + ".kv"], GC_ISLAND, &tpy, 0, nullptr, 0, mk_epi(EPI_BIAS, tkv, 0), tmap, st));
@@ -298,10 +328,10 @@ int run_pe_cross(Context& c, const float* d_prosody_tok, const float* d_style, c
   for (int v : c.LF.seg_len) max_f = std::max(max_f, v);
   if (max_f > kRopePositions || c.max_t > kRopePositions) return fail(c, -6, "utterance longer than the RoPE table");
   STTS_CK(attention(pact.f, pact.ld, 0, tkv.f, tkv.ld, 0, tkv.f, tkv.ld, C, H, D, 1.0f / std::sqrt((float)D), rd, rope_tab(c, rd, st), fmap, tmap,
-                    max_f, c.max_t, d_idx, d_cu_frames, 5, py1.f, py1.ld, st));
+                    max_f, c.max_t, d_idx, d_cu_frames, 5, py1.f, py1.ld, st, Tw(c, py1).g, Tw(c, py1).l, py1.ldg));
   STTS_RET(run_gemm(c, c.gemm[nm + ".o"], GC_ISLAND, &py1, 0, nullptr, 0, mk_epi(EPI_BIAS, pb, 0), fmap, st));
   STTS_CK(dwconv_rows(pb.f, pb.ld, C, c.vec_len[nm + ".dw_k"], c.vec[nm + ".dw_w"], c.vec[nm + ".dw_b"], fmap, 1, pact.f,
-                      pact.ld, st));
+                      pact.ld, st, Tw(c, pact).g, Tw(c, pact).l));
   {
     Epi e = mk_epi(EPI_RES_SCALE, px, 0);
     e.res = pa.f; e.ldr = pa.ld; e.rcol0 = 0;

@@ -20,7 +20,8 @@ namespace stts {
 constexpr int kCopySplit = 8;
 __global__ void __launch_bounds__(128) embed_kernel(const int* __restrict__ tok, const int* __restrict__ cu_tok,
                                                     const float* __restrict__ table, int C, int n_vocab, RowMap map,
-                                                    float* __restrict__ x, int ldx) {
+                                                    float* __restrict__ x, int ldx, __half* __restrict__ xg,
+                                                    __half* __restrict__ xl) {
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
   if (seg < 0) return;
@@ -30,13 +31,16 @@ __global__ void __launch_bounds__(128) embed_kernel(const int* __restrict__ tok,
     const int lr = i / C, c = i - lr * C;
     int id = tok[cu_tok[seg] + t0 + lr];
     id = id < 0 ? 0 : (id >= n_vocab ? n_vocab - 1 : id);
-    x[(size_t)(tile * 128 + lr) * ldx + c] = table[(size_t)id * C + c];
+    const float v = table[(size_t)id * C + c];
+    const size_t o = (size_t)(tile * 128 + lr) * ldx + c;
+    x[o] = v;
+    if (xg != nullptr) f16_split(v, xg + o, xl + o);
   }
 }
 
 cudaError_t embed_tokens(const int* tok, const int* cu_tok, const float* table, int C, int n_vocab, const RowMap& map,
-                         float* x, int ldx, cudaStream_t st) {
-  embed_kernel<<<dim3(map.n_tiles, kCopySplit), 128, 0, st>>>(tok, cu_tok, table, C, n_vocab, map, x, ldx);
+                         float* x, int ldx, cudaStream_t st, __half* xg, __half* xl) {
+  embed_kernel<<<dim3(map.n_tiles, kCopySplit), 128, 0, st>>>(tok, cu_tok, table, C, n_vocab, map, x, ldx, xg, xl);
   return cudaGetLastError();
 }
 
@@ -48,7 +52,8 @@ cudaError_t embed_tokens(const int* tok, const int* cu_tok, const float* table, 
 __global__ void __launch_bounds__(256) row_ln_kernel(const float* x, int ldx, int C, RowMap map,
                                                      const float* __restrict__ gamma, const float* __restrict__ beta,
                                                      int seg_stride, float eps, int relu, float* y,
-                                                     int ldy) {  // x may alias y (in place)
+                                                     int ldy, __half* __restrict__ yg,
+                                                     __half* __restrict__ yl) {  // x may alias y (in place)
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
   if (seg < 0) return;
@@ -83,15 +88,17 @@ __global__ void __launch_bounds__(256) row_ln_kernel(const float* x, int ldx, in
         float o = seg_stride ? (1.f + ga[c]) * n + be[c] : n * ga[c] + be[c];
         if (relu) o = fmaxf(o, 0.f);
         y[r * ldy + c] = o;
+        if (yg != nullptr) f16_split(o, yg + r * ldy + c, yl + r * ldy + c);   // operand twins of the next f16x3 GEMM
       }
     }
   }
 }
 
 cudaError_t row_ln(const float* x, int ldx, int C, const RowMap& map, const float* gamma, const float* beta,
-                   int seg_stride, float eps, int relu, float* y, int ldy, cudaStream_t st) {
+                   int seg_stride, float eps, int relu, float* y, int ldy, cudaStream_t st, __half* yg, __half* yl) {
   if (C > 512) return cudaErrorInvalidValue;
-  row_ln_kernel<<<dim3(map.n_tiles, 4), 256, 0, st>>>(x, ldx, C, map, gamma, beta, seg_stride, eps, relu, y, ldy);
+  row_ln_kernel<<<dim3(map.n_tiles, 4), 256, 0, st>>>(x, ldx, C, map, gamma, beta, seg_stride, eps, relu, y, ldy, yg,
+                                                      yl);
   return cudaGetLastError();
 }
 
@@ -720,7 +727,8 @@ cudaError_t rows_to_dense(const float* src, int ld, int C, const RowMap& map, co
 // (pitch_energy_predictor.py:56-78).  act: 0 = none, 1 = SiLU.
 __global__ void __launch_bounds__(256) dwconv_rows_kernel(const float* __restrict__ x, int ldx, int C, int K,
                                                           const float* __restrict__ w, const float* __restrict__ b,
-                                                          RowMap map, int act, float* __restrict__ y, int ldy) {
+                                                          RowMap map, int act, float* __restrict__ y, int ldy,
+                                                          __half* __restrict__ yg, __half* __restrict__ yl) {
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
   if (seg < 0) return;
@@ -737,19 +745,21 @@ __global__ void __launch_bounds__(256) dwconv_rows_kernel(const float* __restric
     }
     if (act == 1) acc = acc / (1.f + expf(-acc));
     y[(size_t)r * ldy + c] = acc;
+    if (yg != nullptr) f16_split(acc, yg + (size_t)r * ldy + c, yl + (size_t)r * ldy + c);
   }
 }
 
 cudaError_t dwconv_rows(const float* x, int ldx, int C, int K, const float* w, const float* b, const RowMap& map,
-                        int act, float* y, int ldy, cudaStream_t st) {
-  dwconv_rows_kernel<<<dim3(map.n_tiles, 4), 256, 0, st>>>(x, ldx, C, K, w, b, map, act, y, ldy);
+                        int act, float* y, int ldy, cudaStream_t st, __half* yg, __half* yl) {
+  dwconv_rows_kernel<<<dim3(map.n_tiles, 4), 256, 0, st>>>(x, ldx, C, K, w, b, map, act, y, ldy, yg, yl);
   return cudaGetLastError();
 }
 
 // token-major dense [sum T, C] -> packed rows, columns [col0, col0 + C)
 __global__ void __launch_bounds__(256) dense_to_rows_kernel(const float* __restrict__ src, int C, RowMap map,
                                                             const int* __restrict__ cu, float* __restrict__ dst,
-                                                            int ld, int col0) {
+                                                            int ld, int col0, __half* __restrict__ dg,
+                                                            __half* __restrict__ dl) {
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
   if (seg < 0) return;
@@ -757,31 +767,39 @@ __global__ void __launch_bounds__(256) dense_to_rows_kernel(const float* __restr
   const int t0 = tile * 128 - map.seg_start[seg];
   for (int i = blockIdx.y * blockDim.x + threadIdx.x; i < nvalid * C; i += gridDim.y * blockDim.x) {
     const int lr = i / C, c = i - lr * C;
-    dst[(size_t)(tile * 128 + lr) * ld + col0 + c] = src[(size_t)(cu[seg] + t0 + lr) * C + c];
+    const float v = src[(size_t)(cu[seg] + t0 + lr) * C + c];
+    const size_t o = (size_t)(tile * 128 + lr) * ld + col0 + c;
+    dst[o] = v;
+    if (dg != nullptr) f16_split(v, dg + o, dl + o);
   }
 }
 
 cudaError_t dense_to_rows(const float* src, int C, const RowMap& map, const int* cu, float* dst, int ld, int col0,
-                          cudaStream_t st) {
-  dense_to_rows_kernel<<<dim3(map.n_tiles, kCopySplit), 256, 0, st>>>(src, C, map, cu, dst, ld, col0);
+                          cudaStream_t st, __half* dg, __half* dl) {
+  dense_to_rows_kernel<<<dim3(map.n_tiles, kCopySplit), 256, 0, st>>>(src, C, map, cu, dst, ld, col0, dg, dl);
   return cudaGetLastError();
 }
 
 // dst[row, col0 + j] = vec[seg, j]  (style broadcast to every token: torch.cat([x, style.expand]), prosody_encoder.py:66-67)
 __global__ void __launch_bounds__(256) seg_broadcast_kernel(const float* __restrict__ vec, int C, RowMap map,
-                                                            float* __restrict__ dst, int ld, int col0) {
+                                                            float* __restrict__ dst, int ld, int col0,
+                                                            __half* __restrict__ dg, __half* __restrict__ dl) {
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
   if (seg < 0) return;
   const int nvalid = map.tile_nvalid[tile];
   for (int i = blockIdx.y * blockDim.x + threadIdx.x; i < nvalid * C; i += gridDim.y * blockDim.x) {
     const int lr = i / C, c = i - lr * C;
-    dst[(size_t)(tile * 128 + lr) * ld + col0 + c] = vec[(size_t)seg * C + c];
+    const float v = vec[(size_t)seg * C + c];
+    const size_t o = (size_t)(tile * 128 + lr) * ld + col0 + c;
+    dst[o] = v;
+    if (dg != nullptr) f16_split(v, dg + o, dl + o);
   }
 }
 
-cudaError_t seg_broadcast(const float* vec, int C, const RowMap& map, float* dst, int ld, int col0, cudaStream_t st) {
-  seg_broadcast_kernel<<<dim3(map.n_tiles, kCopySplit), 256, 0, st>>>(vec, C, map, dst, ld, col0);
+cudaError_t seg_broadcast(const float* vec, int C, const RowMap& map, float* dst, int ld, int col0, cudaStream_t st,
+                          __half* dg, __half* dl) {
+  seg_broadcast_kernel<<<dim3(map.n_tiles, kCopySplit), 256, 0, st>>>(vec, C, map, dst, ld, col0, dg, dl);
   return cudaGetLastError();
 }
 
