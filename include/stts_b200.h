@@ -105,6 +105,18 @@ int stts_durations(stts_ctx* ctx, const float* d_logits, int n_tokens, int32_t* 
  * alignment column).  d_cu_tok [n_seg+1] are token offsets.  *d_status != 0 if cap too small.   */
 int stts_frame_index(stts_ctx* ctx, const int32_t* d_dur, const int32_t* d_cu_tok, int n_seg,
                      int32_t* d_cu_frames, int32_t* d_idx, int idx_cap, int32_t* d_status, void* stream);
+/* No counterpart in the reference: added for callers that
+ * cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * Same result as stts_frame_index, but the scratch the kernels need (the n_seg + 1 exclusive frame
+ * offsets, d_cu_frames above) lives in a file-scope `static __device__` array of 4 352 bytes that
+ * every GPU loading the library holds until exit; the call performs no cudaMalloc / cudaFree and
+ * calls no allocating routine.  Limit: 1 <= n_seg <= 1024 (STTS_ERR_BAD_ARG with a message beyond
+ * it).  d_idx [idx_cap] and d_status [1] are the caller's; *d_status must be 0 on entry and is
+ * set to 1 if idx_cap is too small (same contract as stts_frame_index).  Every call on a device
+ * shares the one array: calls that overlap on the GPU (different streams) race; calls on one
+ * stream are ordered and never see the previous call's contents.                               */
+int stts_frame_index_static(stts_ctx* ctx, const int32_t* d_dur, const int32_t* d_cu_tok, int n_seg,
+                            int32_t* d_idx, int idx_cap, int32_t* d_status, void* stream);
 
 /* ---- pitch / energy towers --------------------------------------------------------------------
  * PitchEnergyPredictor.forward lines 111-119 (pitch_energy_predictor.py): 2 x 3

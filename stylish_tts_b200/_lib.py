@@ -28,6 +28,7 @@ SIGNATURES = {
     "stts_pe_cross": (_i, [_vp, _fp, _fp, _fp, _fp, _fp, _vp]),
     "stts_durations": (_i, [_vp, _fp, _i, _fp, _vp]),
     "stts_frame_index": (_i, [_vp, _fp, _fp, _i, _fp, _fp, _i, _fp, _vp]),
+    "stts_frame_index_static": (_i, [_vp, _fp, _fp, _i, _fp, _i, _fp, _vp]),
     "stts_pe_towers": (_i, [_vp, _fp, _fp, _fp, _fp, _vp]),
     "stts_decoder": (_i, [_vp, _fp, _fp, _fp, _fp, _fp, _vp]),
     "stts_prior_flow": (_i, [_vp, _fp, _fp, _fp, _fp, _fp, _fp, _vp]),

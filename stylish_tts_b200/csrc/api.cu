@@ -1,6 +1,7 @@
 // extern "C" surface declared in include/stts_b200.h
 #include <cstdio>
 #include <cstring>
+#include <string>
 
 #include "../../include/stts_b200.h"
 #include "engine.h"
@@ -142,6 +143,21 @@ int stts_frame_index(stts_ctx* ctx, const int32_t* d_dur, const int32_t* d_cu_to
   Context& c = ctx->c;
   DeviceGuard g(c.device);
   STTS_CK(frame_index(d_dur, d_cu_tok, n_seg, d_cu_frames, d_idx, idx_cap, d_status, S(stream)));
+  c.launches++;
+  return STTS_OK;
+}
+
+int stts_frame_index_static(stts_ctx* ctx, const int32_t* d_dur, const int32_t* d_cu_tok, int n_seg, int32_t* d_idx,
+                            int idx_cap, int32_t* d_status, void* stream) {
+  if (!ctx) return STTS_ERR_BAD_ARG;
+  Context& c = ctx->c;
+  if (!d_dur || !d_cu_tok || !d_idx || !d_status) return fail(c, STTS_ERR_BAD_ARG, "stts_frame_index_static: null pointer");
+  if (n_seg <= 0 || n_seg > frame_index_static_max_seg())
+    return fail(c, STTS_ERR_BAD_ARG, "stts_frame_index_static: n_seg = " + std::to_string(n_seg) + " is outside 1 .. " +
+                                         std::to_string(frame_index_static_max_seg()) +
+                                         " (the static scratch array holds n_seg + 1 <= 1025 int32 frame offsets)");
+  DeviceGuard g(c.device);
+  STTS_CK(frame_index_static(c.device, d_dur, d_cu_tok, n_seg, d_idx, idx_cap, d_status, S(stream)));
   c.launches++;
   return STTS_OK;
 }

@@ -85,6 +85,10 @@ cudaError_t rows_to_dense(const float* src, int ld, int C, const RowMap& map, co
 cudaError_t durations_from_logits(const float* logits, int n_tokens, int* dur, cudaStream_t st);
 cudaError_t frame_index(const int* dur, const int* cu_tok, int n_seg, int* cu_frames, int* idx, int idx_cap,
                         int* status, cudaStream_t st);
+// allocation-free variant: cu_frames lives in a file-scope __device__ array (length_reg.cu); n_seg <= frame_index_static_max_seg()
+int frame_index_static_max_seg();
+cudaError_t frame_index_static(int device, const int* dur, const int* cu_tok, int n_seg, int* idx, int idx_cap,
+                               int* status, cudaStream_t st);
 
 // ---- source.cu
 struct SourceMeta { int any_voiced; int max_h; int error; int pad; };

@@ -4,6 +4,8 @@
 // The reference materialises a dense one-hot [T, F] matrix and multiplies with it; here the
 // alignment is the int32 index vector (its argmax over tokens), which is what every consumer
 // needs.  Integer work: bit-exact by construction once the durations agree.
+#include <mutex>
+
 #include "common.cuh"
 #include "kernels.h"
 
@@ -103,6 +105,56 @@ __global__ void __launch_bounds__(512) frame_index_kernel(const int* __restrict_
 cudaError_t frame_index(const int* dur, const int* cu_tok, int n_seg, int* cu_frames, int* idx, int idx_cap,
                         int* status, cudaStream_t st) {
   if (n_seg <= 0 || n_seg > 1024) return cudaErrorInvalidValue;
+  seg_totals_kernel<<<1, 1024, 0, st>>>(dur, cu_tok, n_seg, cu_frames);
+  frame_index_kernel<<<n_seg, 512, 0, st>>>(dur, cu_tok, cu_frames, idx, idx_cap, status);
+  return cudaGetLastError();
+}
+
+// ---- allocation-free variant of frame_index (stts_frame_index_static) -------------------------------------------
+// frame_index needs one piece of scratch, the exclusive scan of per-utterance frame totals (cu_frames).  Callers
+// that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc) get it from this
+// file-scope array instead.  Every device that loads the library holds kStaticScratchBytes until exit.  The array is
+// shared by every call on a device: calls that overlap on the GPU (different streams) race on it.  Nothing in it has
+// to start at zero: seg_totals_kernel overwrites entries 0 .. n_seg before frame_index_kernel reads them (same
+// stream), so the previous call's contents are never observed.
+constexpr int kStaticMaxSeg = 1024;                                      // utterances per call (= frame_index's own limit)
+constexpr size_t kStaticScratchBytes = 4352;                             // (1024 + 1) int32, rounded up to 256 B
+static __device__ __align__(256) unsigned char g_frame_index_scratch[kStaticScratchBytes];
+static_assert((kStaticMaxSeg + 1) * sizeof(int) <= kStaticScratchBytes, "scratch too small");
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_scratch_mu;
+int* g_scratch_ptr[kMaxDevices] = {};   // device address of g_frame_index_scratch per device (the symbol's name is a
+                                        // host-side stand-in, not a device address)
+}  // namespace
+
+// once per device, with that device current
+cudaError_t frame_index_static_setup(int device, int** out) {
+  if (device < 0 || device >= kMaxDevices) return cudaErrorInvalidDevice;
+  std::lock_guard<std::mutex> lk(g_scratch_mu);
+  if (g_scratch_ptr[device] == nullptr) {
+    int cur = -1;
+    cudaError_t e = cudaGetDevice(&cur);
+    if (e != cudaSuccess) return e;
+    if (cur != device) return cudaErrorInvalidDevice;
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_frame_index_scratch);
+    if (e != cudaSuccess) return e;
+    g_scratch_ptr[device] = static_cast<int*>(p);
+  }
+  *out = g_scratch_ptr[device];
+  return cudaSuccess;
+}
+
+int frame_index_static_max_seg() { return kStaticMaxSeg; }
+
+cudaError_t frame_index_static(int device, const int* dur, const int* cu_tok, int n_seg, int* idx, int idx_cap,
+                               int* status, cudaStream_t st) {
+  if (n_seg <= 0 || n_seg > kStaticMaxSeg) return cudaErrorInvalidValue;
+  int* cu_frames = nullptr;
+  const cudaError_t e = frame_index_static_setup(device, &cu_frames);
+  if (e != cudaSuccess) return e;
   seg_totals_kernel<<<1, 1024, 0, st>>>(dur, cu_tok, n_seg, cu_frames);
   frame_index_kernel<<<n_seg, 512, 0, st>>>(dur, cu_tok, cu_frames, idx, idx_cap, status);
   return cudaGetLastError();

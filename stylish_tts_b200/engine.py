@@ -195,6 +195,15 @@ class Engine:
                                               _ptr(status, torch.int32), self._stream()))
         return cu_frames, idx, status
 
+    def frame_index_static(self, dur: torch.Tensor, cu_tok: torch.Tensor, idx: torch.Tensor, status: torch.Tensor):
+        """stts_frame_index_static: same indices as ``frame_index`` written into the caller's ``idx`` / ``status``
+        (``status`` zeroed by the caller); the frame-offset scratch is a static device array inside the library,
+        so neither this method nor the library allocates.  At most 1024 utterances per call; calls that overlap on
+        the GPU share the array and race."""
+        self._check(self.lib.stts_frame_index_static(self.h, _ptr(dur, torch.int32), _ptr(cu_tok, torch.int32),
+                                                     cu_tok.numel() - 1, _ptr(idx, torch.int32), idx.numel(),
+                                                     _ptr(status, torch.int32), self._stream()))
+
     # ------------------------------------------------------------------ stages (dense tensors, see header)
     def pe_towers(self, x: torch.Tensor, style: torch.Tensor):
         tot = sum(self.len_f)
