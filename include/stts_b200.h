@@ -118,6 +118,32 @@ int stts_frame_index(stts_ctx* ctx, const int32_t* d_dur, const int32_t* d_cu_to
 int stts_frame_index_static(stts_ctx* ctx, const int32_t* d_dur, const int32_t* d_cu_tok, int n_seg,
                             int32_t* d_idx, int idx_cap, int32_t* d_status, void* stream);
 
+/* ---- source / activation variants outside the default model.yml -------
+ * SineGenerator.forward, train/models/cfm/cfm_mel_decoder.py:16-101 (incl. _f02sine :58-83 and
+ * _f02uv :52-56) on a ragged batch.  d_f0: per-SAMPLE f0 in Hz, the utterances back to back
+ * (sum(len) floats; the reference's [B, L, 1]); len [n_seg] HOST lengths in samples;
+ * d_rand_ini [n_seg, dim] the uniform initial-phase draws (column 0 is ignored, :69) and d_noise
+ * [sum(len), dim] the normal draws the reference makes inside forward (:66, :97), dim =
+ * harmonic_num + 1 <= 16; merge_weight [dim] HOST = merge[0].weight (Linear without bias, :47-50).
+ * d_out [sum(len)] = tanh(merge(...)); d_phase (optional, may be NULL) [sum(len), dim] = the
+ * wrap-corrected cumulative phase in cycles (the argument of :78 before * 2 pi), bit-equal to the
+ * reference's: torch's CPU cumsum accumulates in fp64 and rounds each output to fp32.            */
+int stts_source_sinegen(stts_ctx* ctx, const float* d_f0, const int* len, int n_seg, const float* d_rand_ini,
+                        const float* d_noise, const float* merge_weight, int harmonic_num, float samp_rate,
+                        float sine_amp, float noise_std, float voiced_threshold, float* d_out, float* d_phase,
+                        void* stream);
+/* AdaptiveGeneratorBlock.forward, train/models/ada_norm.py:109-120 (AdaptiveInstance :130-140,
+ * Snake1D x + sin^2(a x) / a, dilated convs :14-83; built by UpsampleGenerator generator.py:114-163
+ * with k in {3, 7, 11}, dilation (1, 3, 5)).  Weights: stts_load_tensor(ctx, module, key, ...) with
+ * the block's own state_dict keys (convs1.i.*, convs2.i.*, adain1.i.fc.*, adain2.i.fc.*,
+ * alpha1.i, alpha2.i; both weight-norm dialects), packed on the first call.  d_x / d_out: the
+ * utterances' dense [channels, len_b] tensors back to back; len [n_seg] HOST; d_style [n_seg, 64].
+ * channels % 64 == 0, kernel_size odd <= 15, padding (k d - d) / 2 <= 32.  The GEMM arithmetic
+ * follows stts_set_precision.  Re-plans its private workspace (cudaMalloc) when len changes.    */
+int stts_generator_block_snake(stts_ctx* ctx, const char* module, int channels, int kernel_size,
+                               const int* dilation /*[3]*/, int n_seg, const int* len, const float* d_x,
+                               const float* d_style, float* d_out, void* stream);
+
 /* ---- pitch / energy towers --------------------------------------------------------------------
  * PitchEnergyPredictor.forward lines 111-119 (pitch_energy_predictor.py): 2 x 3
  * AdaptiveDecoderBlock(320) + 1x1 projections on the cross-attended frames.

@@ -12,7 +12,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libstts_b200.so")
 SOURCES = ["api.cu", "pipeline.cu", "prepack.cu", "gemm_simt.cu", "gemm_tc.cu", "elementwise.cu",
-           "length_reg.cu", "source.cu", "stft_fft.cu", "istft.cu", "token_rate.cu", "token_pipeline.cu"]
+           "length_reg.cu", "source.cu", "stft_fft.cu", "istft.cu", "token_rate.cu", "token_pipeline.cu", "variants.cu"]
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
          "-Xcompiler", "-fPIC"]
 

@@ -43,6 +43,7 @@ void stts_destroy(stts_ctx* ctx) {
   if (ctx == nullptr) return;
   DeviceGuard g(ctx->c.device);
   cudaDeviceSynchronize();
+  free_variant_work(ctx->c);
   for (void* p : ctx->c.weight_allocs) cudaFree(p);
   if (ctx->c.arena) cudaFree(ctx->c.arena);
   if (ctx->c.tarena) cudaFree(ctx->c.tarena);
@@ -61,6 +62,7 @@ int stts_load_tensor(stts_ctx* ctx, const char* module, const char* key, const f
   t.data.assign(h_data, h_data + n);
   ctx->c.tensors[std::string(module) + "/" + key] = std::move(t);
   ctx->c.finalized = false;
+  ctx->c.snake.erase(module);      // a lazily packed AdaptiveGeneratorBlock of this name is stale now
   return STTS_OK;
 }
 
@@ -160,6 +162,30 @@ int stts_frame_index_static(stts_ctx* ctx, const int32_t* d_dur, const int32_t* 
   STTS_CK(frame_index_static(c.device, d_dur, d_cu_tok, n_seg, d_idx, idx_cap, d_status, S(stream)));
   c.launches++;
   return STTS_OK;
+}
+
+int stts_source_sinegen(stts_ctx* ctx, const float* d_f0, const int* len, int n_seg, const float* d_rand_ini,
+                        const float* d_noise, const float* merge_weight, int harmonic_num, float samp_rate,
+                        float sine_amp, float noise_std, float voiced_threshold, float* d_out, float* d_phase,
+                        void* stream) {
+  if (!ctx) return STTS_ERR_BAD_ARG;
+  Context& c = ctx->c;
+  if (!d_f0 || !len || !d_rand_ini || !d_noise || !merge_weight || !d_out)
+    return fail(c, STTS_ERR_BAD_ARG, "stts_source_sinegen: null pointer");
+  DeviceGuard g(c.device);
+  return run_sinegen(c, d_f0, len, n_seg, d_rand_ini, d_noise, merge_weight, harmonic_num, samp_rate, sine_amp, noise_std,
+                     voiced_threshold, d_out, d_phase, S(stream));
+}
+
+int stts_generator_block_snake(stts_ctx* ctx, const char* module, int channels, int kernel_size, const int* dilation,
+                               int n_seg, const int* len, const float* d_x, const float* d_style, float* d_out,
+                               void* stream) {
+  if (!ctx) return STTS_ERR_BAD_ARG;
+  Context& c = ctx->c;
+  if (!module || !dilation || !len || !d_x || !d_style || !d_out)
+    return fail(c, STTS_ERR_BAD_ARG, "stts_generator_block_snake: null pointer");
+  DeviceGuard g(c.device);
+  return run_snake_block(c, module, channels, kernel_size, dilation, n_seg, len, d_x, d_style, d_out, S(stream));
 }
 
 int stts_pe_towers(stts_ctx* ctx, const float* d_x, const float* d_style, float* d_pitch, float* d_energy,

@@ -553,13 +553,14 @@ struct EpiQuad {
 };
 
 // ----------------------------------------------------------------------------- conv-as-GEMM
-// Y[r, n] = sum_s sum_j sum_c A_s[r + j - pad_s, col0_s + c] * W[n, koff_s + j * cin_pad_s + c]
+// Y[r, n] = sum_s sum_j sum_c A_s[r + j * dil_s - pad_s, col0_s + c] * W[n, koff_s + j * cin_pad_s + c]
 // Up to two K-segments (fused 1x1 shortcut, channel concatenation across buffers).
 struct KSeg {
   const float* A; int lda; int col0;         // fp32 operand
   const twin_t* Ah; int ldah; int colh0;     // 16-bit twin (one-pass tensor-core mode)
   const __half* Ag; const __half* Al; int ldag;  // fp16 split twins g / l (f16 and f16x3 modes), columns as colh0
   int taps; int pad; int cin_pad;            // cin_pad % 64 == 0
+  int dil;                                   // tap j reads row r + j * dil - pad; 0 is read as 1 (no dilation)
   int rows;                                  // rows allocated in A (bounds for zero fill)
 };
 

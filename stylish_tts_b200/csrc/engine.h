@@ -22,6 +22,7 @@ struct PackedGemm {
   int N = 0, Npad = 0, Ktot = 0;
   int n_kseg = 0;
   int taps[2] = {0, 0}, pad[2] = {0, 0}, cin_pad[2] = {0, 0};
+  int dil[2] = {1, 1};            // row step between taps (dilated convs)
   float* Wf = nullptr;            // exact fp32                     [Npad, Ktot]
   float* Whl = nullptr;           // tf32 hi rows then lo rows      [2 * Npad, Ktot]
   __half* Wg = nullptr;           // fp16(W * wscale): one-pass 16-bit GEMMs and hi part of f16x3  [Npad, Ktot]
@@ -56,6 +57,9 @@ struct Layout {       // host + device description of one frame rate
   RowMap map_p1() const { return RowMap{R, n_tiles, n_seg, d_tile_seg_p1, d_tile_nvalid_p1, d_seg_start, d_seg_len_p1}; }
   int total() const { return cu.empty() ? 0 : cu.back(); }
 };
+
+struct SnakeCfg { int C = 0, k = 0, dil[3] = {1, 1, 1}, J = 0; };   // a packed AdaptiveGeneratorBlock (prepack.cu)
+struct VariantWork;                                                  // workspace of the section-8 f2 operators (variants.cu)
 
 enum GemmClass { GC_BODY = 0, GC_ISLAND = 1 };  // ISLAND: STFT, output heads, iSTFT stay fp32-grade
 
@@ -98,6 +102,10 @@ struct Context {
   std::vector<ProfRec> prof;
   std::vector<cudaEvent_t> ev_pool;
 
+  // ---- SURVEY section 8 f2 operators (SineGenerator, Snake AdaptiveGeneratorBlock): own layout + workspace
+  std::map<std::string, SnakeCfg> snake;
+  VariantWork* vwork = nullptr;
+
   bool has(const std::string& k) const { return tensors.count(k) != 0; }
 };
 
@@ -105,9 +113,10 @@ struct Context {
 int finalize_weights(Context& c);
 PackedGemm pack_from_conv_weight(Context& c, const float* w, const float* bias, int n_out, int cin, int taps, int pad);
 void free_pack(PackedGemm& p);
+int pack_snake_block(Context& c, const std::string& module, int channels, int k, const int* dil);
 
 // pipeline.cu
-void build_layout(Layout& L, int n_seg, const int* len);
+void build_layout(Layout& L, int n_seg, const int* len, int guard = 0);   // guard: zero rows after every utterance (0 = STTS_GUARD)
 int set_layout(Context& c, int n_seg, const int* len_f, const int* len_f4);
 int run_gemm(Context& c, const PackedGemm& pg, int cls, const Act* a0, int a0_col, const Act* a1, int a1_col,
              const Epi& epi, const RowMap& map, cudaStream_t st, int forced_backend = -1,
@@ -147,6 +156,14 @@ int run_style_encoder(Context& c, const std::string& name, const float* d_enc_to
                       cudaStream_t st);
 int run_pe_cross(Context& c, const float* d_prosody_tok, const float* d_style, const int* d_idx, const int* d_cu_frames,
                  float* d_x_out, cudaStream_t st);
+
+// variants.cu
+int run_sinegen(Context& c, const float* d_f0, const int* h_len, int n_seg, const float* d_rand_ini, const float* d_noise,
+                const float* h_merge_w, int harmonic_num, float samp_rate, float sine_amp, float noise_std,
+                float voiced_threshold, float* d_out, float* d_phase, cudaStream_t st);
+int run_snake_block(Context& c, const std::string& module, int channels, int k, const int* dil, int n_seg,
+                    const int* h_len, const float* d_x, const float* d_style, float* d_out, cudaStream_t st);
+void free_variant_work(Context& c);
 
 int fail(Context& c, int code, const std::string& msg);
 int cuda_fail(Context& c, cudaError_t e, const char* where);

@@ -57,7 +57,7 @@ __global__ void __launch_bounds__(256) conv_gemm_simt_kernel(const ConvGemm g, c
     for (int i = 0; i < 2; ++i) {
       const int idx = tid + i * 256;
       const int row = idx >> 2, kq = idx & 3;
-      const int ar = m0 + row + tap - ks.pad;
+      const int ar = m0 + row + tap * (ks.dil > 0 ? ks.dil : 1) - ks.pad;
       if (ar >= 0 && ar < ks.rows)
         ra[i] = *reinterpret_cast<const float4*>(ks.A + (size_t)ar * ks.lda + ks.col0 + c0 + kq * 4);
       else

@@ -322,6 +322,7 @@ struct Cfg {
 struct TcParams {
   int n_kseg;
   int taps[2], pad[2], cin_chunks[2], col0[2];   // col0 in elements of the operand dtype
+  int dil[2];           // row step between taps (dilated convs of the snake generator block), >= 1
   int n_chunks;
   int w_seg_rows;       // > 0: the weights are per utterance, utterance u at rows [u * w_seg_rows, ...)
   uint32_t ab_fmt;      // operand format of the MMAs: 0 = f16, 1 = bf16, 2 = tf32
@@ -398,11 +399,11 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
         uint8_t* sp = stage_ptr(stage);
         mbar_expect_tx(&full[stage], tx);
         const CUtensorMap* ma = (ks == 0) ? &mapA0 : &mapA1;
-        tma_load_2d(sp, ma, &full[stage], p.col0[ks] + cc * C::kBK, m0 + tap - p.pad[ks]);
+        tma_load_2d(sp, ma, &full[stage], p.col0[ks] + cc * C::kBK, m0 + tap * p.dil[ks] - p.pad[ks]);
         if constexpr (C::kSplit) {
           if constexpr (!C::kTF32) {
             const CUtensorMap* ml = (ks == 0) ? &mapA0lo : &mapA1lo;
-            tma_load_2d(sp + C::kATile, ml, &full[stage], p.col0[ks] + cc * C::kBK, m0 + tap - p.pad[ks]);
+            tma_load_2d(sp + C::kATile, ml, &full[stage], p.col0[ks] + cc * C::kBK, m0 + tap * p.dil[ks] - p.pad[ks]);
           }
           tma_load_2d(sp + 2 * C::kATile, mw, &full[stage], kcol, wrow);
           tma_load_2d(sp + 2 * C::kATile + C::kBTile, mwlo, &full[stage], kcol, wrow);
@@ -634,7 +635,7 @@ conv_gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap mapA0, const 
           uint8_t* sp = stage_ptr(stage);
           mbar_expect_tx(&full[stage], tx);
           const CUtensorMap* ma = (ks == 0) ? &mapA0 : &mapA1;
-          tma_load_2d(sp, ma, &full[stage], p.col0[ks] + cc * C::kBK, m0 + tap - p.pad[ks]);
+          tma_load_2d(sp, ma, &full[stage], p.col0[ks] + cc * C::kBK, m0 + tap * p.dil[ks] - p.pad[ks]);
           tma_load_2d(sp + C::kATile, mw, &full[stage], kcol, wrow);
           kcol += C::kBK;
           if (++cc == p.cin_chunks[ks]) { cc = 0; if (++tap == p.taps[ks]) { tap = 0; ++ks; } }
@@ -1048,6 +1049,7 @@ cudaError_t launch_one(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
     if (s < g.n_kseg) {
       p.taps[s] = ks.taps;
       p.pad[s] = ks.pad;
+      p.dil[s] = ks.dil > 0 ? ks.dil : 1;
       p.cin_chunks[s] = ks.cin_pad / C::kBK;
       p.col0[s] = (MODE == MODE_TF32X3) ? ks.col0 : ks.colh0;
       p.n_chunks += ks.taps * p.cin_chunks[s];
@@ -1112,6 +1114,7 @@ cudaError_t launch_persistent(const ConvGemm& g, const RowMap& map, cudaStream_t
     if (s < g.n_kseg) {
       p.taps[s] = ks.taps;
       p.pad[s] = ks.pad;
+      p.dil[s] = ks.dil > 0 ? ks.dil : 1;
       p.cin_chunks[s] = ks.cin_pad / C::kBK;
       p.col0[s] = ks.colh0;
       p.n_chunks += ks.taps * p.cin_chunks[s];

@@ -36,7 +36,7 @@ struct ArenaPlan {
   }
 };
 
-void build_layout_impl(Layout& L, int n_seg, const int* len) {
+void build_layout_impl(Layout& L, int n_seg, const int* len, int guard) {
   L = Layout();
   L.n_seg = n_seg;
   L.seg_start.resize(n_seg);
@@ -46,7 +46,7 @@ void build_layout_impl(Layout& L, int n_seg, const int* len) {
   for (int b = 0; b < n_seg; ++b) {
     L.seg_start[b] = pos;
     L.cu[b + 1] = L.cu[b] + len[b];
-    pos = (pos + len[b] + STTS_GUARD + 127) / 128 * 128;
+    pos = (pos + len[b] + guard + 127) / 128 * 128;
   }
   L.R = pos;
   L.n_tiles = pos / 128;
@@ -70,7 +70,9 @@ void build_layout_impl(Layout& L, int n_seg, const int* len) {
 
 }  // namespace
 
-void build_layout(Layout& L, int n_seg, const int* len) { build_layout_impl(L, n_seg, len); }
+void build_layout(Layout& L, int n_seg, const int* len, int guard) {
+  build_layout_impl(L, n_seg, len, guard > 0 ? guard : STTS_GUARD);
+}
 
 // ----------------------------------------------------------------------------- layout + workspace
 int set_layout(Context& c, int n_seg, const int* len_f, const int* len_f4) {
@@ -317,7 +319,7 @@ int run_gemm(Context& c, const PackedGemm& pg, int cls, const Act* a0, int a0_co
     k.A = as[s]->f; k.lda = as[s]->ld; k.col0 = cols[s];
     k.Ah = as[s]->h; k.ldah = as[s]->ld; k.colh0 = cols[s];
     k.Ag = as[s]->g; k.Al = as[s]->l; k.ldag = as[s]->ldg;
-    k.taps = pg.taps[s]; k.pad = pg.pad[s]; k.cin_pad = pg.cin_pad[s];
+    k.taps = pg.taps[s]; k.pad = pg.pad[s]; k.cin_pad = pg.cin_pad[s]; k.dil = pg.dil[s];
     k.rows = as[s]->rows;
     if (cols[s] + k.cin_pad > (f16 ? as[s]->ldg : as[s]->ld))
       return fail(c, -2, "run_gemm: K slice exceeds the operand row");

@@ -408,7 +408,7 @@ bool pack_pe_cross(Context& c, Loader& L, const std::string& nm) {
 int finalize_weights(Context& c) {
   for (void* p : c.weight_allocs) cudaFree(p);
   c.weight_allocs.clear();
-  c.gemm.clear(); c.vec.clear(); c.vec_len.clear(); c.fc_off.clear();
+  c.gemm.clear(); c.vec.clear(); c.vec_len.clear(); c.fc_off.clear(); c.snake.clear();
   c.finalized = false;
 
   // ======================================================================= speech_predictor
@@ -740,6 +740,60 @@ int finalize_weights(Context& c) {
   for (auto& kv : c.gemm) kv.second.name = kv.first;
   if (cudaDeviceSynchronize() != cudaSuccess) return fail(c, -5, "cuda error while uploading weights");
   c.finalized = true;
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Snake AdaptiveGeneratorBlock (ada_norm.py:11-127): three (AdaIN, snake, dilated conv k,
+// AdaIN, snake, conv k) residual stages.  Packed on first use by stts_generator_block_snake from the tensors loaded
+// under `module` with the reference's state_dict keys:
+//   gemm  <module>.c1.<i> (dilation d_i, pad (k d_i - d_i) / 2), <module>.c2.<i> (dilation 1)
+//   vec   <module>.fc_W / fc_b: the six style Linear layers stacked in the order n1.0, n2.0, n1.1, ... (fc_off);
+//         <module>.a1.<i> / a2.<i>: alpha [C]
+int pack_snake_block(Context& c, const std::string& module, int channels, int k, const int* dil) {
+  if (channels <= 0 || channels % 64 != 0 || channels > 1024) return fail(c, -2, "snake block: channels must be a multiple of 64, <= 1024");
+  if (k < 1 || (k & 1) == 0 || k > 15) return fail(c, -2, "snake block: kernel_size must be odd, <= 15");
+  Loader L{c, module};
+  FcCat fc;
+  SnakeCfg cfg;
+  cfg.C = channels; cfg.k = k;
+  for (int i = 0; i < 3; ++i) {
+    const std::string si = std::to_string(i);
+    if (dil[i] < 1 || (k * dil[i] - dil[i]) / 2 > 32) return fail(c, -2, "snake block: padding (k d - d) / 2 must be <= 32 rows");
+    cfg.dil[i] = dil[i];
+    for (int which = 0; which < 2; ++which) {
+      const std::string grp = which == 0 ? "convs1." : "convs2.";
+      const HostTensor w = L.weight(grp + si + ".");
+      const HostTensor* b = L.get(grp + si + ".bias");
+      if (!L.ok) return fail(c, -3, "missing weight " + L.missing);
+      if (w.dim(0) != channels || w.dim(1) != channels || w.dim(2) != k)
+        return fail(c, -2, "snake block: " + module + "/" + grp + si + " is not [C, C, k]");
+      const int d = which == 0 ? dil[i] : 1;
+      Builder bd;
+      const int t[2] = {k, 0}, pd[2] = {(k * d - d) / 2, 0}, cp[2] = {channels, 0};
+      bd.init(channels, 1, t, pd, cp);
+      bd.rows(0, w, 0, channels, 0, channels, 0, 1);
+      bd.set_bias(*b, 0, channels, 0, 1);
+      PackedGemm pg = bd.upload(c);
+      pg.dil[0] = d;
+      const std::string name = module + (which == 0 ? ".c1." : ".c2.") + si;
+      pg.name = name;
+      c.gemm[name] = pg;
+      const std::string an = which == 0 ? "adain1." : "adain2.";
+      const HostTensor *fw = L.get(an + si + ".fc.weight"), *fb = L.get(an + si + ".fc.bias");
+      const HostTensor* al = L.get((which == 0 ? "alpha1." : "alpha2.") + si);
+      if (!L.ok) return fail(c, -3, "missing weight " + L.missing);
+      if (fw->dim(0) != 2 * channels || fw->dim(1) != 64 || al->numel() != channels)
+        return fail(c, -2, "snake block: AdaIN fc must be [2 C, 64] and alpha [1, C, 1]");
+      c.fc_off[module + (which == 0 ? ".n1." : ".n2.") + si] = fc.add(*fw, *fb);
+      put_vec(c, module + (which == 0 ? ".a1." : ".a2.") + si, al->data);
+    }
+  }
+  cfg.J = fc.J;
+  put_vec(c, module + ".fc_W", fc.W);
+  put_vec(c, module + ".fc_b", fc.b);
+  if (cudaDeviceSynchronize() != cudaSuccess) return fail(c, -5, "cuda error while uploading the snake block");
+  c.snake[module] = cfg;
   return 0;
 }
 

@@ -204,6 +204,43 @@ class Engine:
                                                      cu_tok.numel() - 1, _ptr(idx, torch.int32), idx.numel(),
                                                      _ptr(status, torch.int32), self._stream()))
 
+    # ------------------------------------------------------------------ variants outside the default model.yml
+    def sinegen(self, f0: torch.Tensor, lengths: Sequence[int], rand_ini: torch.Tensor, noise: torch.Tensor,
+                merge_weight: torch.Tensor, harmonic_num: int, samp_rate: float, sine_amp: float = 0.1,
+                noise_std: float = 0.003, voiced_threshold: float = 0.0, want_phase: bool = False):
+        """SineGenerator.forward (cfm/cfm_mel_decoder.py:85-101) on a ragged batch.  f0 [sum L] per-sample Hz, the
+        utterances back to back; rand_ini [B, dim]; noise [sum L, dim].  Returns (out [sum L], phase [sum L, dim] | None),
+        phase = the wrap-corrected cumulative phase in cycles (cfm_mel_decoder.py:78 before * 2 pi)."""
+        lens = [int(x) for x in lengths]
+        dim = harmonic_num + 1
+        tot = sum(lens)
+        if f0.numel() != tot or noise.numel() != tot * dim or rand_ini.numel() != len(lens) * dim:
+            raise ValueError("sinegen: f0 / noise / rand_ini do not match the lengths")
+        w = merge_weight.detach().to("cpu", torch.float32).reshape(-1).contiguous()
+        if w.numel() != dim:
+            raise ValueError("sinegen: merge weight must have harmonic_num + 1 entries")
+        out = torch.empty(tot, dtype=torch.float32, device=self.device)
+        phase = torch.empty((tot, dim), dtype=torch.float32, device=self.device) if want_phase else None
+        self._check(self.lib.stts_source_sinegen(
+            self.h, _ptr(f0), (C.c_int * len(lens))(*lens), len(lens), _ptr(rand_ini), _ptr(noise),
+            (C.c_float * dim)(*w.tolist()), harmonic_num, float(samp_rate), float(sine_amp), float(noise_std),
+            float(voiced_threshold), _ptr(out), _ptr(phase), self._stream()))
+        return out, phase
+
+    def snake_block(self, module: str, channels: int, kernel_size: int, dilation: Sequence[int], x: torch.Tensor,
+                    lengths: Sequence[int], style: torch.Tensor):
+        """AdaptiveGeneratorBlock.forward (ada_norm.py:109-120) on a ragged batch; weights loaded under ``module`` with
+        ``load_state``.  x: the utterances' dense [channels, L_b] tensors back to back; style [B, 64]."""
+        lens = [int(v) for v in lengths]
+        if x.numel() != channels * sum(lens) or style.numel() != 64 * len(lens):
+            raise ValueError("snake_block: x / style do not match the lengths")
+        out = torch.empty_like(x)
+        with torch.cuda.device(self.device):
+            self._check(self.lib.stts_generator_block_snake(
+                self.h, module.encode(), channels, kernel_size, (C.c_int * 3)(*[int(d) for d in dilation]), len(lens),
+                (C.c_int * len(lens))(*lens), _ptr(x), _ptr(style), _ptr(out), self._stream()))
+        return out
+
     # ------------------------------------------------------------------ stages (dense tensors, see header)
     def pe_towers(self, x: torch.Tensor, style: torch.Tensor):
         tot = sum(self.len_f)
