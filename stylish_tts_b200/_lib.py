@@ -19,6 +19,7 @@ SIGNATURES = {
     "stts_load_tensor": (_i, [_vp, C.c_char_p, C.c_char_p, _fp, C.POINTER(_i64), _i]),
     "stts_finalize_weights": (_i, [_vp]),
     "stts_set_precision": (_i, [_vp, _i]),
+    "stts_set_pdl": (_i, [_vp, _i]),
     "stts_set_layout": (_i, [_vp, _i, C.POINTER(_i), C.POINTER(_i)]),
     "stts_workspace_bytes": (_i64, [_vp]),
     "stts_set_token_layout": (_i, [_vp, _i, C.POINTER(_i)]),

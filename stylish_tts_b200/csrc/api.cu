@@ -15,7 +15,12 @@ struct stts_ctx {
 namespace {
 struct DeviceGuard {
   int prev = 0;
-  explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
+  explicit DeviceGuard(const Context& c) {      // also: this context's programmatic-dependent-launch choice for the call
+    const int dev = c.device;
+    cudaGetDevice(&prev);
+    if (prev != dev) cudaSetDevice(dev); else prev = -1;
+    pdl_set(c.pdl);
+  }
   ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
 };
 inline cudaStream_t S(void* s) { return reinterpret_cast<cudaStream_t>(s); }
@@ -41,7 +46,7 @@ int stts_create(stts_ctx** out, int device) {
 
 void stts_destroy(stts_ctx* ctx) {
   if (ctx == nullptr) return;
-  DeviceGuard g(ctx->c.device);
+  DeviceGuard g(ctx->c);
   cudaDeviceSynchronize();
   free_variant_work(ctx->c);
   for (void* p : ctx->c.weight_allocs) cudaFree(p);
@@ -68,7 +73,7 @@ int stts_load_tensor(stts_ctx* ctx, const char* module, const char* key, const f
 
 int stts_finalize_weights(stts_ctx* ctx) {
   if (!ctx) return STTS_ERR_BAD_ARG;
-  DeviceGuard g(ctx->c.device);
+  DeviceGuard g(ctx->c);
   ctx->c.sig.clear();  // style-FC scratch sizes depend on the packs: force a re-plan
   return finalize_weights(ctx->c);
 }
@@ -79,16 +84,22 @@ int stts_set_precision(stts_ctx* ctx, int precision) {
   return STTS_OK;
 }
 
+int stts_set_pdl(stts_ctx* ctx, int on) {
+  if (!ctx) return STTS_ERR_BAD_ARG;
+  ctx->c.pdl = on ? 1 : 0;
+  return STTS_OK;
+}
+
 int stts_set_token_layout(stts_ctx* ctx, int n_seg, const int* len_t) {
   if (!ctx) return STTS_ERR_BAD_ARG;
-  DeviceGuard g(ctx->c.device);
+  DeviceGuard g(ctx->c);
   return set_token_layout(ctx->c, n_seg, len_t);
 }
 
 int stts_text_encoder(stts_ctx* ctx, const char* which, const int32_t* d_tokens, float* d_mu_tok, float* d_x_tok,
                       void* stream) {
   if (!ctx || !which || !d_tokens) return STTS_ERR_BAD_ARG;
-  DeviceGuard g(ctx->c.device);
+  DeviceGuard g(ctx->c);
   const std::string w(which);
   const char* nm = w == "speech_predictor" ? "te.sp" : (w == "pe_text_encoder" ? "te.pe"
                    : (w == "duration_predictor" ? "te.dp" : nullptr));
@@ -99,7 +110,7 @@ int stts_text_encoder(stts_ctx* ctx, const char* which, const int32_t* d_tokens,
 int stts_prosody_encoder(stts_ctx* ctx, const char* which, const float* d_enc_tok, const float* d_style,
                          float* d_out_tok, float* d_logits_tok, void* stream) {
   if (!ctx || !which || !d_enc_tok || !d_style) return STTS_ERR_BAD_ARG;
-  DeviceGuard g(ctx->c.device);
+  DeviceGuard g(ctx->c);
   const std::string w(which);
   const char* nm = w == "duration_predictor" ? "pr.dp" : (w == "pitch_energy_predictor" ? "pr.pe" : nullptr);
   if (nm == nullptr) return fail(ctx->c, STTS_ERR_BAD_ARG, "stts_prosody_encoder: unknown module " + w);
@@ -108,7 +119,7 @@ int stts_prosody_encoder(stts_ctx* ctx, const char* which, const float* d_enc_to
 
 int stts_text_style_encoder(stts_ctx* ctx, const char* which, const float* d_enc_tok, float* d_style, void* stream) {
   if (!ctx || !which || !d_style) return STTS_ERR_BAD_ARG;
-  DeviceGuard g(ctx->c.device);
+  DeviceGuard g(ctx->c);
   const std::string w(which);
   const char* nm = w == "speech_predictor" ? "se.sp" : (w == "pe_text_style_encoder" ? "se.pe"
                    : (w == "duration_predictor" ? "se.dp" : nullptr));
@@ -119,13 +130,13 @@ int stts_text_style_encoder(stts_ctx* ctx, const char* which, const float* d_enc
 int stts_pe_cross(stts_ctx* ctx, const float* d_prosody_tok, const float* d_style, const int32_t* d_idx,
                   const int32_t* d_cu_frames, float* d_x, void* stream) {
   if (!ctx || !d_style || !d_idx || !d_cu_frames) return STTS_ERR_BAD_ARG;
-  DeviceGuard g(ctx->c.device);
+  DeviceGuard g(ctx->c);
   return run_pe_cross(ctx->c, d_prosody_tok, d_style, d_idx, d_cu_frames, d_x, S(stream));
 }
 
 int stts_set_layout(stts_ctx* ctx, int n_seg, const int* len_f, const int* len_f4) {
   if (!ctx) return STTS_ERR_BAD_ARG;
-  DeviceGuard g(ctx->c.device);
+  DeviceGuard g(ctx->c);
   return set_layout(ctx->c, n_seg, len_f, len_f4);
 }
 
@@ -134,7 +145,7 @@ int64_t stts_workspace_bytes(const stts_ctx* ctx) { return ctx ? (int64_t)ctx->c
 int stts_durations(stts_ctx* ctx, const float* d_logits, int n_tokens, int32_t* d_dur, void* stream) {
   if (!ctx || !d_logits || !d_dur || n_tokens < 0) return STTS_ERR_BAD_ARG;
   Context& c = ctx->c;
-  DeviceGuard g(c.device);
+  DeviceGuard g(c);
   STTS_CK(durations_from_logits(d_logits, n_tokens, d_dur, S(stream)));
   return STTS_OK;
 }
@@ -143,7 +154,7 @@ int stts_frame_index(stts_ctx* ctx, const int32_t* d_dur, const int32_t* d_cu_to
                      int32_t* d_idx, int idx_cap, int32_t* d_status, void* stream) {
   if (!ctx || !d_dur || !d_cu_tok || !d_cu_frames || !d_idx || !d_status) return STTS_ERR_BAD_ARG;
   Context& c = ctx->c;
-  DeviceGuard g(c.device);
+  DeviceGuard g(c);
   STTS_CK(frame_index(d_dur, d_cu_tok, n_seg, d_cu_frames, d_idx, idx_cap, d_status, S(stream)));
   c.launches++;
   return STTS_OK;
@@ -158,7 +169,7 @@ int stts_frame_index_static(stts_ctx* ctx, const int32_t* d_dur, const int32_t* 
     return fail(c, STTS_ERR_BAD_ARG, "stts_frame_index_static: n_seg = " + std::to_string(n_seg) + " is outside 1 .. " +
                                          std::to_string(frame_index_static_max_seg()) +
                                          " (the static scratch array holds n_seg + 1 <= 1025 int32 frame offsets)");
-  DeviceGuard g(c.device);
+  DeviceGuard g(c);
   STTS_CK(frame_index_static(c.device, d_dur, d_cu_tok, n_seg, d_idx, idx_cap, d_status, S(stream)));
   c.launches++;
   return STTS_OK;
@@ -172,7 +183,7 @@ int stts_source_sinegen(stts_ctx* ctx, const float* d_f0, const int* len, int n_
   Context& c = ctx->c;
   if (!d_f0 || !len || !d_rand_ini || !d_noise || !merge_weight || !d_out)
     return fail(c, STTS_ERR_BAD_ARG, "stts_source_sinegen: null pointer");
-  DeviceGuard g(c.device);
+  DeviceGuard g(c);
   return run_sinegen(c, d_f0, len, n_seg, d_rand_ini, d_noise, merge_weight, harmonic_num, samp_rate, sine_amp, noise_std,
                      voiced_threshold, d_out, d_phase, S(stream));
 }
@@ -184,35 +195,35 @@ int stts_generator_block_snake(stts_ctx* ctx, const char* module, int channels, 
   Context& c = ctx->c;
   if (!module || !dilation || !len || !d_x || !d_style || !d_out)
     return fail(c, STTS_ERR_BAD_ARG, "stts_generator_block_snake: null pointer");
-  DeviceGuard g(c.device);
+  DeviceGuard g(c);
   return run_snake_block(c, module, channels, kernel_size, dilation, n_seg, len, d_x, d_style, d_out, S(stream));
 }
 
 int stts_pe_towers(stts_ctx* ctx, const float* d_x, const float* d_style, float* d_pitch, float* d_energy,
                    void* stream) {
   if (!ctx || !d_style || !d_pitch || !d_energy) return STTS_ERR_BAD_ARG;
-  DeviceGuard g(ctx->c.device);
+  DeviceGuard g(ctx->c);
   return run_pe_towers(ctx->c, d_x, d_style, d_pitch, d_energy, S(stream));
 }
 
 int stts_decoder(stts_ctx* ctx, const float* d_asr, const float* d_f0, const float* d_n, const float* d_style,
                  float* d_out, void* stream) {
   if (!ctx || !d_asr || !d_f0 || !d_n || !d_style || !d_out) return STTS_ERR_BAD_ARG;
-  DeviceGuard g(ctx->c.device);
+  DeviceGuard g(ctx->c);
   return run_decoder(ctx->c, d_asr, d_f0, d_n, d_style, d_out, S(stream));
 }
 
 int stts_prior_flow(stts_ctx* ctx, const float* d_x, const float* d_noise, const float* d_style, float* d_mel,
                     float* d_z_prior, float* d_z_flow, void* stream) {
   if (!ctx || !d_x || !d_noise || !d_style || !d_mel) return STTS_ERR_BAD_ARG;
-  DeviceGuard g(ctx->c.device);
+  DeviceGuard g(ctx->c);
   return run_prior_flow(ctx->c, d_x, d_noise, d_style, d_mel, d_z_prior, d_z_flow, S(stream));
 }
 
 int stts_source_pcph(stts_ctx* ctx, const float* d_pitch4, const float* d_noise, const float* d_init_phase,
                      float* d_out, void* stream) {
   if (!ctx || !d_pitch4 || !d_noise || !d_init_phase || !d_out) return STTS_ERR_BAD_ARG;
-  DeviceGuard g(ctx->c.device);
+  DeviceGuard g(ctx->c);
   return run_source(ctx->c, d_pitch4, d_noise, d_init_phase, d_out, S(stream));
 }
 
@@ -220,14 +231,14 @@ int stts_generator(stts_ctx* ctx, const float* d_mel, const float* d_style, cons
                    const float* d_noise, const float* d_init_phase, float* d_audio, float* d_logamp, float* d_phase,
                    void* stream) {
   if (!ctx || !d_mel || !d_style || !d_pitch4 || !d_noise || !d_init_phase || !d_audio) return STTS_ERR_BAD_ARG;
-  DeviceGuard g(ctx->c.device);
+  DeviceGuard g(ctx->c);
   return run_generator(ctx->c, d_mel, d_style, d_pitch4, d_noise, d_init_phase, d_audio, d_logamp, d_phase, S(stream));
 }
 
 int stts_generator_from_stft(stts_ctx* ctx, const float* d_mel, const float* d_style, const float* d_har_spec,
                              const float* d_har_phase, float* d_audio, float* d_logamp, float* d_phase, void* stream) {
   if (!ctx || !d_mel || !d_style || !d_har_spec || !d_har_phase || !d_audio) return STTS_ERR_BAD_ARG;
-  DeviceGuard g(ctx->c.device);
+  DeviceGuard g(ctx->c);
   return run_generator_from_stft(ctx->c, d_mel, d_style, d_har_spec, d_har_phase, d_audio, d_logamp, d_phase,
                                  S(stream));
 }
@@ -239,7 +250,7 @@ int stts_speech_frames(stts_ctx* ctx, const float* d_enc_tok, const int32_t* d_c
   if (!ctx || !d_enc_tok || !d_cu_tok || !d_idx || !d_cu_frames || !d_pitch || !d_energy || !d_style ||
       !d_noise_prior || !d_noise_source || !d_init_phase || !d_audio)
     return STTS_ERR_BAD_ARG;
-  DeviceGuard g(ctx->c.device);
+  DeviceGuard g(ctx->c);
   return run_speech_frames(ctx->c, d_enc_tok, d_cu_tok, d_idx, d_cu_frames, d_pitch, d_energy, d_style, d_noise_prior,
                            d_noise_source, d_init_phase, d_audio, d_logamp, d_phase, S(stream));
 }
@@ -248,7 +259,7 @@ int stts_check_source_status(stts_ctx* ctx, void* stream) {
   if (!ctx) return STTS_ERR_BAD_ARG;
   Context& c = ctx->c;
   if (c.raw.count("META") == 0 || c.h_meta == nullptr) return fail(c, -4, "no layout set");
-  DeviceGuard g(c.device);
+  DeviceGuard g(c);
   const int B = c.L4.n_seg;
   cudaError_t e = cudaMemcpyAsync(c.h_meta, c.raw["META"], (size_t)B * sizeof(SourceMeta), cudaMemcpyDeviceToHost,
                                   S(stream));
@@ -265,7 +276,7 @@ int64_t stts_saturation_count(stts_ctx* ctx, void* stream) {
   if (!ctx) return STTS_ERR_BAD_ARG;
   Context& c = ctx->c;
   if (c.raw.count("STATUS") == 0) return fail(c, -4, "no layout set");
-  DeviceGuard g(c.device);
+  DeviceGuard g(c);
   unsigned long long* cnt = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(c.raw["STATUS"]) + 128);
   cudaError_t e = cudaMemsetAsync(cnt, 0, sizeof(unsigned long long), S(stream));
   if (e != cudaSuccess) return cuda_fail(c, e, "saturation counter reset");
@@ -285,7 +296,7 @@ int64_t stts_saturation_count(stts_ctx* ctx, void* stream) {
 int stts_pcm16(stts_ctx* ctx, const float* d_audio, int64_t n, int16_t* d_pcm, void* stream) {
   if (!ctx || n < 0 || (n > 0 && (!d_audio || !d_pcm))) return STTS_ERR_BAD_ARG;
   Context& c = ctx->c;
-  DeviceGuard g(c.device);
+  DeviceGuard g(c);
   STTS_CK(pcm16(d_audio, d_pcm, (long long)n, S(stream)));
   return STTS_OK;
 }
@@ -295,7 +306,7 @@ int stts_test_conv(stts_ctx* ctx, int backend, const float* d_x, int ldx, int ci
   if (!ctx || !d_x || !h_w || !d_y || backend < 0 || backend > 2) return STTS_ERR_BAD_ARG;
   Context& c = ctx->c;
   if (c.L4.total() == 0) return fail(c, -4, "no hop-75 layout set");
-  DeviceGuard g(c.device);
+  DeviceGuard g(c);
   PackedGemm pg = pack_from_conv_weight(c, h_w, h_bias, n_out, cin, taps, pad);
   if (pg.cin_pad[0] > ldx) { free_pack(pg); return fail(c, -2, "ldx must cover cin padded to 64"); }
   Act a;
@@ -332,7 +343,7 @@ int64_t stts_debug_read(stts_ctx* ctx, const char* name, float* d_dst, int64_t c
                         void* stream) {
   if (!ctx || !name) return STTS_ERR_BAD_ARG;
   Context& c = ctx->c;
-  DeviceGuard g(c.device);
+  DeviceGuard g(c);
   auto it = c.act.find(name);
   const float* src = nullptr;
   int64_t n = 0;
@@ -368,7 +379,7 @@ int stts_layout_info(const stts_ctx* ctx, int rate, int* rows, int* seg_start) {
 int stts_set_profiling(stts_ctx* ctx, int on) {
   if (!ctx) return STTS_ERR_BAD_ARG;
   Context& c = ctx->c;
-  DeviceGuard g(c.device);
+  DeviceGuard g(c);
   cudaDeviceSynchronize();
   for (auto& r : c.prof) { c.ev_pool.push_back(r.e0); c.ev_pool.push_back(r.e1); }
   c.prof.clear();
@@ -379,7 +390,7 @@ int stts_set_profiling(stts_ctx* ctx, int on) {
 const char* stts_profile_json(stts_ctx* ctx) {
   if (!ctx) return "[]";
   Context& c = ctx->c;
-  DeviceGuard g(c.device);
+  DeviceGuard g(c);
   cudaDeviceSynchronize();
   struct Agg { double ms = 0, flops = 0; long n = 0; int backend = 0; };
   std::map<std::string, Agg> agg;

@@ -27,6 +27,40 @@ __device__ __forceinline__ twin2_t to_twin2(float x, float y) { return __floats2
 
 namespace stts {
 
+// ----------------------------------------------------------------------------- programmatic dependent launch
+// Every kernel of the library is enqueued through launch_k with the programmatic-stream-serialization attribute and
+// starts with pdl_enter(): `griddepcontrol.wait` blocks until the previous kernel of the stream has completed and its
+// writes are visible (the ordinary stream guarantee), then `griddepcontrol.launch_dependents` lets the NEXT kernel's
+// CTAs be scheduled while this one runs.  So the launch latency, CTA scheduling and pre-wait prologue (barrier init,
+// TMEM allocation, tensor-map prefetch in the GEMM kernels) of kernel N + 1 overlap kernel N instead of following it;
+// the look-ahead is exactly one kernel per stream (N + 2 cannot start before N + 1 has passed its own wait).  The
+// step is ~500 dependent launches of 5-50 us each, also inside a CUDA graph (the capture records programmatic edges).
+// No kernel reads or writes global memory that another kernel touches before its pdl_enter().  Measured (B200):
+// one 5 s utterance, graph replay 3.64 -> 3.27 ms; with three batches in flight on three streams the look-ahead CTAs
+// take SM slots from the other lanes (-1 .. -2 %), so the choice is per context (stts_set_pdl; SynthesizerPool turns it
+// off for lanes > 1).  STTS_PDL=0 forces the attribute off (the two instructions are then no-ops).
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_enter() { pdl_wait(); pdl_trigger(); }
+
+bool pdl_enabled();     // pipeline.cu: the calling context's choice (stts_set_pdl), STTS_PDL=0 forces it off
+void pdl_set(int on);   // -1: default (on)
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg;
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<Args&&>(args)...);
+}
+
 // Device view of a packed layout (one per frame rate).
 struct RowMap {
   int R;                 // rows (multiple of 128)

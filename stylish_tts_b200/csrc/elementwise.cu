@@ -16,6 +16,7 @@ namespace stts {
 __global__ void __launch_bounds__(512) colstats_partial_kernel(const float* __restrict__ x, int ld, int C,
                                                                RowMap map, double* __restrict__ psum,
                                                                double* __restrict__ psq) {
+  pdl_enter();
   __shared__ double sh_s[4][128], sh_q[4][128];
   const int tile = blockIdx.x;
   if (map.tile_seg[tile] < 0) return;
@@ -50,6 +51,7 @@ __global__ void __launch_bounds__(128) colstats_final_kernel(const double* __res
                                                              const double* __restrict__ psq, int C, RowMap map,
                                                              int mode, float eps, float* __restrict__ out0,
                                                              float* __restrict__ out1) {
+  pdl_enter();
   const int seg = blockIdx.x;
   const int c = blockIdx.y * 128 + threadIdx.x;
   if (c >= C) return;
@@ -74,9 +76,9 @@ cudaError_t colstats(const float* x, int ld, int C, const RowMap& map, int mode,
   double* psum = scratch;
   double* psq = scratch + (size_t)map.n_tiles * C;
   dim3 g1(map.n_tiles, (C + 127) / 128);
-  colstats_partial_kernel<<<g1, dim3(128, 4), 0, st>>>(x, ld, C, map, psum, psq);
+  launch_k(colstats_partial_kernel, g1, dim3(128, 4), 0, st, x, ld, C, map, psum, psq);
   dim3 g2(map.n_seg, (C + 127) / 128);
-  colstats_final_kernel<<<g2, 128, 0, st>>>(psum, psq, C, map, mode, eps, out0, out1);
+  launch_k(colstats_final_kernel, g2, 128, 0, st, psum, psq, C, map, mode, eps, out0, out1);
   return cudaGetLastError();
 }
 
@@ -86,6 +88,7 @@ cudaError_t colstats(const float* x, int ld, int C, const RowMap& map, int mode,
 __global__ void __launch_bounds__(128) colstats_partial_q_kernel(const float* __restrict__ x, int ld, int col0, int ncols,
                                                                  RowMap map, float* __restrict__ psum,
                                                                  float* __restrict__ psq, int pld) {
+  pdl_enter();
   const int tile = blockIdx.x, q = blockIdx.y;
   if (map.tile_seg[tile] < 0) return;
   int nrows = map.tile_nvalid[tile] - q * 32;
@@ -105,6 +108,7 @@ __global__ void __launch_bounds__(256) colstats_final_q_kernel(const float* __re
                                                                const float* __restrict__ psq, int pld, int C, RowMap map,
                                                                float eps, float* __restrict__ mean,
                                                                float* __restrict__ rstd) {
+  pdl_enter();
   __shared__ double sh_s[8][32], sh_q[8][32];
   const int seg = blockIdx.x;
   const int c = blockIdx.y * 32 + threadIdx.x;
@@ -144,14 +148,14 @@ __global__ void __launch_bounds__(256) colstats_final_q_kernel(const float* __re
 cudaError_t colstats_partial_q(const float* x, int ld, int col0, int ncols, const RowMap& map, float* psum, float* psq,
                                int pld, cudaStream_t st) {
   dim3 g(map.n_tiles, 4);
-  colstats_partial_q_kernel<<<g, 128, 0, st>>>(x, ld, col0, ncols, map, psum, psq, pld);
+  launch_k(colstats_partial_q_kernel, g, 128, 0, st, x, ld, col0, ncols, map, psum, psq, pld);
   return cudaGetLastError();
 }
 
 cudaError_t colstats_final_q(const float* psum, const float* psq, int pld, int C, const RowMap& map, float eps,
                              float* mean, float* rstd, cudaStream_t st) {
   dim3 g(map.n_seg, (C + 31) / 32), b(32, 8);
-  colstats_final_q_kernel<<<g, b, 0, st>>>(psum, psq, pld, C, map, eps, mean, rstd);
+  launch_k(colstats_final_q_kernel, g, b, 0, st, psum, psq, pld, C, map, eps, mean, rstd);
   return cudaGetLastError();
 }
 
@@ -164,6 +168,7 @@ constexpr int kFcBatch = 4;
 __global__ void __launch_bounds__(128) style_fc_kernel(const float* __restrict__ W, const float* __restrict__ bias,
                                                        const float* __restrict__ s, int J, int K, int B,
                                                        float* __restrict__ out) {
+  pdl_enter();
   extern __shared__ float sh[];  // W tile [128][K + 1] (coalesced load, conflict-free rows) + s [kFcBatch, K]
   float* sw = sh;
   float* ss = sh + 128 * (K + 1);
@@ -199,7 +204,7 @@ cudaError_t style_fc(const float* W, const float* bias, const float* s, int J, i
   const size_t smem = (size_t)(128 * (K + 1) + kFcBatch * K) * sizeof(float);
   if (smem > 48 * 1024) return cudaErrorInvalidValue;
   dim3 grid((J + 127) / 128, (B + kFcBatch - 1) / kFcBatch);
-  style_fc_kernel<<<grid, 128, smem, st>>>(W, bias, s, J, K, B, out);
+  launch_k(style_fc_kernel, grid, 128, smem, st, W, bias, s, J, K, B, out);
   return cudaGetLastError();
 }
 
@@ -213,6 +218,7 @@ __global__ void __launch_bounds__(256) adain_act_kernel(const float* __restrict_
                                                         const float* __restrict__ gb, int ldgb, float slope,
                                                         float* __restrict__ y, int ldy, twin_t* __restrict__ yh,
                                                         int ldyh) {
+  pdl_enter();
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
   if (seg < 0) return;
@@ -243,7 +249,7 @@ cudaError_t adain_act(const float* x, int ldx, int C, const RowMap& map, const f
                       cudaStream_t st) {
   if ((C & 1) || (ldx & 1) || (ldy & 1) || (ldgb & 1)) return cudaErrorInvalidValue;
   dim3 grid(map.n_tiles, (C + 127) / 128);
-  adain_act_kernel<<<grid, 256, 0, st>>>(x, ldx, C, map, mean, rstd, gb, ldgb, slope, y, ldy, yh, ldyh);
+  launch_k(adain_act_kernel, grid, 256, 0, st, x, ldx, C, map, mean, rstd, gb, ldgb, slope, y, ldy, yh, ldyh);
   return cudaGetLastError();
 }
 
@@ -256,6 +262,7 @@ __global__ void __launch_bounds__(256) expand_tokens_kernel(const float* __restr
                                                             const int* __restrict__ tok_off, int div, RowMap map,
                                                             float* __restrict__ out, int ldo, int col0,
                                                             twin_t* __restrict__ outh, int ldh, int colh0) {
+  pdl_enter();
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
   if (seg < 0) return;
@@ -276,7 +283,7 @@ __global__ void __launch_bounds__(256) expand_tokens_kernel(const float* __restr
 cudaError_t expand_tokens(const float* tok, int C, const int* idx, const int* cu_f, const int* tok_off, int div,
                           const RowMap& map, float* out, int ldo, int col0, twin_t* outh, int ldh, int colh0,
                           cudaStream_t st) {
-  expand_tokens_kernel<<<dim3(map.n_tiles, 4), 256, 0, st>>>(tok, C, idx, cu_f, tok_off, div, map, out, ldo, col0, outh, ldh,
+  launch_k(expand_tokens_kernel, dim3(map.n_tiles, 4), 256, 0, st, tok, C, idx, cu_f, tok_off, div, map, out, ldo, col0, outh, ldh,
                                                     colh0);
   return cudaGetLastError();
 }
@@ -287,6 +294,7 @@ cudaError_t expand_tokens(const float* tok, int C, const int* idx, const int* cu
 __global__ void __launch_bounds__(256) upsample4_kernel(const float* __restrict__ a, const float* __restrict__ b,
                                                         const int* __restrict__ cu_f, RowMap map,
                                                         float* __restrict__ a4, float* __restrict__ b4) {
+  pdl_enter();
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
   if (seg < 0) return;
@@ -312,7 +320,7 @@ __global__ void __launch_bounds__(256) upsample4_kernel(const float* __restrict_
 
 cudaError_t upsample4(const float* a, const float* b, const int* cu_f, const RowMap& map, float* a4, float* b4,
                       cudaStream_t st) {
-  upsample4_kernel<<<map.n_tiles, 128, 0, st>>>(a, b, cu_f, map, a4, b4);
+  launch_k(upsample4_kernel, map.n_tiles, 128, 0, st, a, b, cu_f, map, a4, b4);
   return cudaGetLastError();
 }
 
@@ -322,6 +330,7 @@ cudaError_t upsample4(const float* a, const float* b, const int* cu_f, const Row
 // w = {f0_w0, f0_w1, f0_w2, f0_b, n_w0, n_w1, n_w2, n_b}
 __global__ void __launch_bounds__(128) f0n_conv_kernel(const float* __restrict__ p4, const float* __restrict__ e4,
                                                        const float* __restrict__ w, RowMap map, F0NDst d) {
+  pdl_enter();
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
   if (seg < 0) return;
@@ -349,7 +358,7 @@ __global__ void __launch_bounds__(128) f0n_conv_kernel(const float* __restrict__
 
 cudaError_t f0n_conv(const float* p4, const float* e4, const float* w, const RowMap& map, const F0NDst& d,
                      cudaStream_t st) {
-  f0n_conv_kernel<<<map.n_tiles, 128, 0, st>>>(p4, e4, w, map, d);
+  launch_k(f0n_conv_kernel, map.n_tiles, 128, 0, st, p4, e4, w, map, d);
   return cudaGetLastError();
 }
 
@@ -361,6 +370,7 @@ __global__ void __launch_bounds__(256) transpose_in_kernel(const float* __restri
                                                            const int* __restrict__ cs, int C, RowMap map,
                                                            float* __restrict__ dst, int ld, int col0,
                                                            twin_t* __restrict__ dsth, int ldh, int colh0) {
+  pdl_enter();
   __shared__ float t[32][33];
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
@@ -396,7 +406,7 @@ __global__ void __launch_bounds__(256) transpose_in_kernel(const float* __restri
 cudaError_t transpose_in(const float* src, const long long* off, const int* cs, int C, const RowMap& map, float* dst,
                          int ld, int col0, twin_t* dsth, int ldh, int colh0, cudaStream_t st) {
   dim3 grid(map.n_tiles, (C + 31) / 32 < 8 ? (C + 31) / 32 : 8);
-  transpose_in_kernel<<<grid, 256, 0, st>>>(src, off, cs, C, map, dst, ld, col0, dsth, ldh, colh0);
+  launch_k(transpose_in_kernel, grid, 256, 0, st, src, off, cs, C, map, dst, ld, col0, dsth, ldh, colh0);
   return cudaGetLastError();
 }
 
@@ -406,6 +416,7 @@ __global__ void __launch_bounds__(256) transpose_out_kernel(const float* __restr
                                                             RowMap map, float* __restrict__ dst,
                                                             const long long* __restrict__ off,
                                                             const int* __restrict__ cs, int extra) {
+  pdl_enter();
   __shared__ float t[32][33];
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
@@ -442,13 +453,14 @@ __global__ void __launch_bounds__(256) transpose_out_kernel(const float* __restr
 cudaError_t transpose_out(const float* src, int ld, int col0, int C, const RowMap& map, float* dst,
                           const long long* off, const int* cs, int extra, cudaStream_t st) {
   dim3 grid(map.n_tiles, (C + 31) / 32 < 8 ? (C + 31) / 32 : 8);
-  transpose_out_kernel<<<grid, 256, 0, st>>>(src, ld, col0, C, map, dst, off, cs, extra);
+  launch_k(transpose_out_kernel, grid, 256, 0, st, src, ld, col0, C, map, dst, off, cs, extra);
   return cudaGetLastError();
 }
 
 // dense per-row vector <-> concatenated per-utterance vector ([sum L])
 __global__ void __launch_bounds__(128) rowvec_kernel(float* __restrict__ rowv, float* __restrict__ dense,
                                                      const int* __restrict__ cu, RowMap map, int to_rows) {
+  pdl_enter();
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
   if (seg < 0) return;
@@ -460,7 +472,7 @@ __global__ void __launch_bounds__(128) rowvec_kernel(float* __restrict__ rowv, f
 }
 
 cudaError_t rowvec_copy(float* rowv, float* dense, const int* cu, const RowMap& map, int to_rows, cudaStream_t st) {
-  rowvec_kernel<<<map.n_tiles, 128, 0, st>>>(rowv, dense, cu, map, to_rows);
+  launch_k(rowvec_kernel, map.n_tiles, 128, 0, st, rowv, dense, cu, map, to_rows);
   return cudaGetLastError();
 }
 
@@ -474,6 +486,7 @@ __global__ void __launch_bounds__(256) dwconv_adaln_kernel(const float* __restri
                                                            const float* __restrict__ gb, int ldgb, float eps,
                                                            float* __restrict__ y, int ldy,
                                                            twin_t* __restrict__ yh, int ldyh) {
+  pdl_enter();
   constexpr int C = 512, TR = 16, PAD = (K - 1) / 2;
   __shared__ float red[8][TR];
   __shared__ float stat[TR];
@@ -560,10 +573,10 @@ cudaError_t dwconv_adaln(const float* x, int ldx, const RowMap& map, int K, cons
                          cudaStream_t st) {
   dim3 grid(map.n_tiles, 8);
   switch (K) {
-    case 31: dwconv_adaln_kernel<31><<<grid, 256, 0, st>>>(x, ldx, map, wt, bias, gb, ldgb, eps, y, ldy, yh, ldyh); break;
-    case 15: dwconv_adaln_kernel<15><<<grid, 256, 0, st>>>(x, ldx, map, wt, bias, gb, ldgb, eps, y, ldy, yh, ldyh); break;
-    case 7: dwconv_adaln_kernel<7><<<grid, 256, 0, st>>>(x, ldx, map, wt, bias, gb, ldgb, eps, y, ldy, yh, ldyh); break;
-    case 3: dwconv_adaln_kernel<3><<<grid, 256, 0, st>>>(x, ldx, map, wt, bias, gb, ldgb, eps, y, ldy, yh, ldyh); break;
+    case 31: launch_k(dwconv_adaln_kernel<31>, grid, 256, 0, st, x, ldx, map, wt, bias, gb, ldgb, eps, y, ldy, yh, ldyh); break;
+    case 15: launch_k(dwconv_adaln_kernel<15>, grid, 256, 0, st, x, ldx, map, wt, bias, gb, ldgb, eps, y, ldy, yh, ldyh); break;
+    case 7: launch_k(dwconv_adaln_kernel<7>, grid, 256, 0, st, x, ldx, map, wt, bias, gb, ldgb, eps, y, ldy, yh, ldyh); break;
+    case 3: launch_k(dwconv_adaln_kernel<3>, grid, 256, 0, st, x, ldx, map, wt, bias, gb, ldgb, eps, y, ldy, yh, ldyh); break;
     default: return cudaErrorInvalidValue;
   }
   return cudaGetLastError();
@@ -597,6 +610,7 @@ __global__ void __launch_bounds__(256) adaln2_kernel(const float* __restrict__ x
                                                      float* __restrict__ y2, int ldy, __half* __restrict__ y1g,
                                                      __half* __restrict__ y2g, int ldyh,
                                                      __half* __restrict__ y1l, __half* __restrict__ y2l) {
+  pdl_enter();
   constexpr int C = 512;
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
@@ -645,7 +659,7 @@ __global__ void __launch_bounds__(256) adaln2_kernel(const float* __restrict__ x
 cudaError_t adaln2(const float* x, int ldx, const RowMap& map, const float* gb1, const float* gb2, int ldgb, float eps,
                    float* y1, float* y2, int ldy, __half* y1g, __half* y2g, int ldyh, __half* y1l, __half* y2l,
                    cudaStream_t st) {
-  adaln2_kernel<<<map.n_tiles, 256, 0, st>>>(x, ldx, map, gb1, gb2, ldgb, eps, y1, y2, ldy, y1g, y2g, ldyh, y1l, y2l);
+  launch_k(adaln2_kernel, map.n_tiles, 256, 0, st, x, ldx, map, gb1, gb2, ldgb, eps, y1, y2, ldy, y1g, y2g, ldyh, y1l, y2l);
   return cudaGetLastError();
 }
 
@@ -654,6 +668,7 @@ cudaError_t adaln2(const float* x, int ldx, const RowMap& map, const float* gb1,
 // y = gamma * (x * Nx) + beta + x  ==  x * (1 + gamma * Nx) + beta.
 __global__ void __launch_bounds__(256) grn_scale_kernel(const float* __restrict__ gx, int C,
                                                         const float* __restrict__ gamma, float* __restrict__ scale) {
+  pdl_enter();
   __shared__ float red[8];
   const int seg = blockIdx.x;
   float s = 0.f;
@@ -674,6 +689,7 @@ __global__ void __launch_bounds__(256) grn_scale_kernel(const float* __restrict_
 // Deterministic: fixed summation order, fp64 accumulation.  CTA = 64 channels x 4 interleaved row parts.
 __global__ void __launch_bounds__(256) grn_gx_partials_kernel(const float* __restrict__ colss, int ld, int C,
                                                               RowMap map, float* __restrict__ gx) {
+  pdl_enter();
   __shared__ double part[4][64];
   const int seg = blockIdx.x;
   const int cl = threadIdx.x & 63, pt = threadIdx.x >> 6;
@@ -689,8 +705,8 @@ __global__ void __launch_bounds__(256) grn_gx_partials_kernel(const float* __res
 
 cudaError_t grn_scale_partials(const float* colss, int ld, int C, const RowMap& map, const float* gamma, float* gx,
                                float* scale, cudaStream_t st) {
-  grn_gx_partials_kernel<<<dim3(map.n_seg, (C + 63) / 64), 256, 0, st>>>(colss, ld, C, map, gx);
-  grn_scale_kernel<<<map.n_seg, 256, 0, st>>>(gx, C, gamma, scale);
+  launch_k(grn_gx_partials_kernel, dim3(map.n_seg, (C + 63) / 64), 256, 0, st, colss, ld, C, map, gx);
+  launch_k(grn_scale_kernel, map.n_seg, 256, 0, st, gx, C, gamma, scale);
   return cudaGetLastError();
 }
 
@@ -699,6 +715,7 @@ cudaError_t grn_scale_partials(const float* colss, int ld, int C, const RowMap& 
 __global__ void __launch_bounds__(256) grn_weights_kernel(const float* __restrict__ W, int N, int K,
                                                           const float* __restrict__ scale,
                                                           twin_t* __restrict__ Wu) {
+  pdl_enter();
   const int u = blockIdx.y;
   const size_t total = (size_t)N * K / 2;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
@@ -712,7 +729,7 @@ __global__ void __launch_bounds__(256) grn_weights_kernel(const float* __restric
 
 cudaError_t grn_weights(const float* W, int N, int K, const float* scale, int n_seg, twin_t* Wu, cudaStream_t st) {
   if (K % 2 != 0) return cudaErrorInvalidValue;
-  grn_weights_kernel<<<dim3(148, n_seg), 256, 0, st>>>(W, N, K, scale, Wu);
+  launch_k(grn_weights_kernel, dim3(148, n_seg), 256, 0, st, W, N, K, scale, Wu);
   return cudaGetLastError();
 }
 
@@ -721,6 +738,7 @@ __global__ void __launch_bounds__(256) seg_affine_kernel(float* __restrict__ x, 
                                                          const float* __restrict__ shift,
                                                          twin_t* __restrict__ xh, int ldxh,
                                                          __half* __restrict__ xg, __half* __restrict__ xl) {
+  pdl_enter();
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
   if (seg < 0) return;
@@ -750,9 +768,9 @@ __global__ void __launch_bounds__(256) seg_affine_kernel(float* __restrict__ x, 
 cudaError_t grn_apply(float* x, int ldx, int C, const RowMap& map, const float* gx, const float* gamma,
                       const float* beta, float* scale_scratch, twin_t* xh, int ldxh, cudaStream_t st, __half* xg,
                       __half* xl) {
-  grn_scale_kernel<<<map.n_seg, 256, 0, st>>>(gx, C, gamma, scale_scratch);
+  launch_k(grn_scale_kernel, map.n_seg, 256, 0, st, gx, C, gamma, scale_scratch);
   dim3 grid(map.n_tiles, 4);
-  seg_affine_kernel<<<grid, 256, 0, st>>>(x, ldx, C, map, scale_scratch, beta, xh, ldxh, xg, xl);
+  launch_k(seg_affine_kernel, grid, 256, 0, st, x, ldx, C, map, scale_scratch, beta, xh, ldxh, xg, xl);
   return cudaGetLastError();
 }
 
@@ -761,6 +779,7 @@ cudaError_t grn_apply(float* x, int ldx, int C, const RowMap& map, const float* 
 __global__ void __launch_bounds__(256) rowdot_kernel(const float* __restrict__ x, int ldx, int C, RowMap map,
                                                      const float* __restrict__ w, const float* __restrict__ bias,
                                                      const int* __restrict__ cu, float* __restrict__ dense) {
+  pdl_enter();
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
   if (seg < 0) return;
@@ -777,13 +796,14 @@ __global__ void __launch_bounds__(256) rowdot_kernel(const float* __restrict__ x
 
 cudaError_t rowdot(const float* x, int ldx, int C, const RowMap& map, const float* w, const float* bias, const int* cu,
                    float* dense, cudaStream_t st) {
-  rowdot_kernel<<<dim3(map.n_tiles, 4), 256, 0, st>>>(x, ldx, C, map, w, bias, cu, dense);
+  launch_k(rowdot_kernel, dim3(map.n_tiles, 4), 256, 0, st, x, ldx, C, map, w, bias, cu, dense);
   return cudaGetLastError();
 }
 
 // fp16 split twins of the first C columns of the valid rows, recomputed from the fp32 master
 __global__ void __launch_bounds__(256) twin_refresh_kernel(const float* __restrict__ f, int ld, int C, RowMap map,
                                                            __half* __restrict__ h, __half* __restrict__ l) {
+  pdl_enter();
   const int tile = blockIdx.x;
   if (map.tile_seg[tile] < 0) return;
   const int nvalid = map.tile_nvalid[tile];
@@ -796,7 +816,7 @@ __global__ void __launch_bounds__(256) twin_refresh_kernel(const float* __restri
 }
 cudaError_t twin_refresh(const float* f, int ld, int C, const RowMap& map, __half* h, __half* l, cudaStream_t st) {
   dim3 grid(map.n_tiles, 4);
-  twin_refresh_kernel<<<grid, 256, 0, st>>>(f, ld, C, map, h, l);
+  launch_k(twin_refresh_kernel, grid, 256, 0, st, f, ld, C, map, h, l);
   return cudaGetLastError();
 }
 
@@ -806,6 +826,7 @@ cudaError_t twin_refresh(const float* f, int ld, int C, const RowMap& map, __hal
 // stts_saturation_count walks every twin of the workspace after a run).
 __global__ void __launch_bounds__(256) saturation_kernel(const uint16_t* __restrict__ h, size_t n,
                                                          unsigned long long* __restrict__ count) {
+  pdl_enter();
   unsigned long long c = 0;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
     c += ((h[i] & 0x7FFFu) == 0x7BFFu) ? 1ull : 0ull;
@@ -814,17 +835,18 @@ __global__ void __launch_bounds__(256) saturation_kernel(const uint16_t* __restr
 }
 cudaError_t saturation_count(const twin_t* h, size_t n, unsigned long long* count, cudaStream_t st) {
   if (n == 0) return cudaSuccess;
-  saturation_kernel<<<592, 256, 0, st>>>(reinterpret_cast<const uint16_t*>(h), n, count);
+  launch_k(saturation_kernel, 592, 256, 0, st, reinterpret_cast<const uint16_t*>(h), n, count);
   return cudaGetLastError();
 }
 
 // zero-fill of valid rows of a column block (WN "output" accumulator is rebuilt by EPI_RESSKIP's
 // accumulate2 = 0 path, so this is only needed by tests)
 __global__ void fill_kernel(float* p, size_t n, float v) {
+  pdl_enter();
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) p[i] = v;
 }
 cudaError_t fill(float* p, size_t n, float v, cudaStream_t st) {
-  fill_kernel<<<592, 256, 0, st>>>(p, n, v);
+  launch_k(fill_kernel, 592, 256, 0, st, p, n, v);
   return cudaGetLastError();
 }
 

@@ -17,6 +17,7 @@ constexpr int APAD = 4;
 
 template <int BN, int KIND>
 __global__ void __launch_bounds__(256) conv_gemm_simt_kernel(const ConvGemm g, const RowMap map) {
+  pdl_enter();
   constexpr int TN = BN / 16;           // columns per thread: 4 or 8
   constexpr int BLOADS = BN / 64;       // float4 B loads per thread: 1 or 2
   __shared__ __align__(16) float As[2][BK][BM + APAD];
@@ -137,10 +138,10 @@ cudaError_t launch_kind(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
   const int n_cols = g.epi.N;
   if (n_cols > 64) {
     dim3 grid(map.n_tiles, (n_cols + 127) / 128);
-    conv_gemm_simt_kernel<128, KIND><<<grid, 256, 0, st>>>(g, map);
+    launch_k(conv_gemm_simt_kernel<128, KIND>, grid, 256, 0, st, g, map);
   } else {
     dim3 grid(map.n_tiles, 1);
-    conv_gemm_simt_kernel<64, KIND><<<grid, 256, 0, st>>>(g, map);
+    launch_k(conv_gemm_simt_kernel<64, KIND>, grid, 256, 0, st, g, map);
   }
   return cudaGetLastError();
 }

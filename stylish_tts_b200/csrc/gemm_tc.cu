@@ -377,6 +377,7 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_enter();   // everything above (barrier init, TMEM allocation) overlaps the previous kernel of the stream
   const uint32_t tmem_base = *tmem_slot;
   const uint32_t idesc_full = C::kIdescBase | (p.ab_fmt << 7) | (p.ab_fmt << 10);
   const uint32_t idesc = tail ? ((idesc_full & ~(0x3Fu << 17)) | ((16u >> 3) << 17)) : idesc_full;
@@ -612,6 +613,7 @@ conv_gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap mapA0, const 
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_enter();   // everything above (barrier init, TMEM allocation) overlaps the previous kernel of the stream
   const uint32_t tmem_base = *tmem_slot;
   auto stage_ptr = [&](int s) { return smem + (size_t)s * C::kStageBytes; };
 
@@ -831,6 +833,7 @@ wn_layer_fused_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_con
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
+  pdl_enter();   // everything above (barrier init, TMEM allocation) overlaps the previous kernel of the stream
   if (threadIdx.x >= 64 && threadIdx.x < 64 + 256) {   // gate constants per accumulator column: bias + style conditioning
     const int n = threadIdx.x - 64;
     gconst[n] = p.bias_in[n] + p.segvec[(size_t)seg * p.ldseg + ((n & 1) ? 128 : 0) + (n >> 1)];
@@ -1094,7 +1097,7 @@ cudaError_t launch_one(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
     attr_done = true;
   }
   dim3 grid((g.epi.N + BN - 1) / BN, map.n_tiles);
-  kern<<<grid, C::kThreads, C::kSmem, st>>>(mA[0], mA[1], mAlo[0], mAlo[1], mW, mWlo, mWt, mWtlo, p, g.epi, map);
+  launch_k(kern, grid, C::kThreads, C::kSmem, st, mA[0], mA[1], mAlo[0], mAlo[1], mW, mWlo, mWt, mWtlo, p, g.epi, map);
   return cudaGetLastError();
 }
 
@@ -1145,7 +1148,7 @@ cudaError_t launch_persistent(const ConvGemm& g, const RowMap& map, cudaStream_t
   const int n_tiles_n = (g.epi.N + C::kBN - 1) / C::kBN;
   const int total = map.n_tiles * n_tiles_n;
   const int grid = total < n_sm ? total : n_sm;
-  kern<<<grid, C::kThreads, C::kSmem, st>>>(mA[0], mA[1], mW, mWt, p, g.epi, map, n_tiles_n);
+  launch_k(kern, grid, C::kThreads, C::kSmem, st, mA[0], mA[1], mW, mWt, p, g.epi, map, n_tiles_n);
   return cudaGetLastError();
 }
 
@@ -1233,7 +1236,7 @@ cudaError_t launch_wn(const ConvGemm& gin, const ConvGemm& grs, const RowMap& ma
     if (e != cudaSuccess) return e;
     attr_done = true;
   }
-  kern<<<map.n_tiles, C::kThreads, C::kSmem, st>>>(mX, mWin, mWrs, p, grs.epi, map);
+  launch_k(kern, map.n_tiles, C::kThreads, C::kSmem, st, mX, mWin, mWrs, p, grs.epi, map);
   return cudaGetLastError();
 }
 }  // namespace

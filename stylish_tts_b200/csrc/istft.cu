@@ -20,6 +20,7 @@ __global__ void __launch_bounds__(256) polar_kernel(const float* __restrict__ la
                                                     int n_bins, RowMap map, float* __restrict__ spec, int lds,
                                                     __half* __restrict__ specg, int ldsh,
                                                     __half* __restrict__ specl, float gscale) {
+  pdl_enter();
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
   if (seg < 0) return;
@@ -63,9 +64,9 @@ cudaError_t polar_spec(const float* logamp, const float* phase, int ld, int n_bi
                        int lds, __half* specg, int ldsh, __half* specl, float gscale, cudaStream_t st) {
   dim3 grid(map.n_tiles, 16);
   if (spec == nullptr && specl == nullptr && specg != nullptr)
-    polar_kernel<true><<<grid, 256, 0, st>>>(logamp, phase, ld, n_bins, map, spec, lds, specg, ldsh, specl, gscale);
+    launch_k(polar_kernel<true>, grid, 256, 0, st, logamp, phase, ld, n_bins, map, spec, lds, specg, ldsh, specl, gscale);
   else
-    polar_kernel<false><<<grid, 256, 0, st>>>(logamp, phase, ld, n_bins, map, spec, lds, specg, ldsh, specl, gscale);
+    launch_k(polar_kernel<false>, grid, 256, 0, st, logamp, phase, ld, n_bins, map, spec, lds, specg, ldsh, specl, gscale);
   return cudaGetLastError();
 }
 
@@ -76,6 +77,7 @@ cudaError_t polar_spec(const float* logamp, const float* phase, int ld, int n_bi
 __global__ void __launch_bounds__(256) ola_tanh_kernel(const float* __restrict__ frames, int ldf,
                                                        const float* __restrict__ wsq, const int* __restrict__ cu4,
                                                        RowMap map, float* __restrict__ audio) {
+  pdl_enter();
   __shared__ float s_wsq[1200];
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
@@ -107,7 +109,7 @@ __global__ void __launch_bounds__(256) ola_tanh_kernel(const float* __restrict__
 cudaError_t ola_tanh(const float* frames, int ldf, const float* wsq, const int* cu4, const RowMap& map, float* audio,
                      cudaStream_t st) {
   dim3 grid(map.n_tiles, 4);
-  ola_tanh_kernel<<<grid, 256, 0, st>>>(frames, ldf, wsq, cu4, map, audio);
+  launch_k(ola_tanh_kernel, grid, 256, 0, st, frames, ldf, wsq, cu4, map, audio);
   return cudaGetLastError();
 }
 
@@ -115,6 +117,7 @@ cudaError_t ola_tanh(const float* frames, int ldf, const float* wsq, const int* 
 // (train/test_onnx.py:79), saturated at the int16 range (the reference cast is undefined for x = +1.0).
 // 8 samples per thread: two float4 loads, one 16-byte store; the tail is scalar.
 __global__ void __launch_bounds__(256) pcm16_kernel(const float* __restrict__ x, int16_t* __restrict__ y, long long n) {
+  pdl_enter();
   const long long i8 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 8;
   if (i8 >= n) return;
   auto q = [](float v) {
@@ -135,7 +138,7 @@ __global__ void __launch_bounds__(256) pcm16_kernel(const float* __restrict__ x,
 cudaError_t pcm16(const float* x, int16_t* y, long long n, cudaStream_t st) {
   if (n <= 0) return cudaSuccess;
   const long long threads = (n + 7) / 8;
-  pcm16_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(x, y, n);
+  launch_k(pcm16_kernel, (unsigned)((threads + 255) / 256), 256, 0, st, x, y, n);
   return cudaGetLastError();
 }
 

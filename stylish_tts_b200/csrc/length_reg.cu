@@ -14,6 +14,7 @@ namespace stts {
 __constant__ float kClassToDur[16] = {1, 2, 3, 4, 5, 6, 7, 9, 12, 15, 18, 22, 27, 32, 38, 46};  // utils.py:391-393
 
 __global__ void __launch_bounds__(256) durations_kernel(const float* __restrict__ logits, int n, int* __restrict__ dur) {
+  pdl_enter();
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= n) return;
   float x[16];
@@ -47,13 +48,14 @@ __global__ void __launch_bounds__(256) durations_kernel(const float* __restrict_
 
 cudaError_t durations_from_logits(const float* logits, int n_tokens, int* dur, cudaStream_t st) {
   if (n_tokens <= 0) return cudaSuccess;
-  durations_kernel<<<(n_tokens + 255) / 256, 256, 0, st>>>(logits, n_tokens, dur);
+  launch_k(durations_kernel, (n_tokens + 255) / 256, 256, 0, st, logits, n_tokens, dur);
   return cudaGetLastError();
 }
 
 // cu_frames[b] = sum of the durations of utterances < b (exclusive scan over utterances)
 __global__ void __launch_bounds__(1024) seg_totals_kernel(const int* __restrict__ dur, const int* __restrict__ cu_tok,
                                                           int n_seg, int* __restrict__ cu_frames) {
+  pdl_enter();
   __shared__ int tot[1024];
   const int b = threadIdx.x;
   int s = 0;
@@ -72,6 +74,7 @@ __global__ void __launch_bounds__(1024) seg_totals_kernel(const int* __restrict_
 __global__ void __launch_bounds__(512) frame_index_kernel(const int* __restrict__ dur, const int* __restrict__ cu_tok,
                                                           const int* __restrict__ cu_frames, int* __restrict__ idx,
                                                           int idx_cap, int* __restrict__ status) {
+  pdl_enter();
   __shared__ int sc[512];
   __shared__ int carry;
   const int b = blockIdx.x;
@@ -105,8 +108,8 @@ __global__ void __launch_bounds__(512) frame_index_kernel(const int* __restrict_
 cudaError_t frame_index(const int* dur, const int* cu_tok, int n_seg, int* cu_frames, int* idx, int idx_cap,
                         int* status, cudaStream_t st) {
   if (n_seg <= 0 || n_seg > 1024) return cudaErrorInvalidValue;
-  seg_totals_kernel<<<1, 1024, 0, st>>>(dur, cu_tok, n_seg, cu_frames);
-  frame_index_kernel<<<n_seg, 512, 0, st>>>(dur, cu_tok, cu_frames, idx, idx_cap, status);
+  launch_k(seg_totals_kernel, 1, 1024, 0, st, dur, cu_tok, n_seg, cu_frames);
+  launch_k(frame_index_kernel, n_seg, 512, 0, st, dur, cu_tok, cu_frames, idx, idx_cap, status);
   return cudaGetLastError();
 }
 
@@ -155,8 +158,8 @@ cudaError_t frame_index_static(int device, const int* dur, const int* cu_tok, in
   int* cu_frames = nullptr;
   const cudaError_t e = frame_index_static_setup(device, &cu_frames);
   if (e != cudaSuccess) return e;
-  seg_totals_kernel<<<1, 1024, 0, st>>>(dur, cu_tok, n_seg, cu_frames);
-  frame_index_kernel<<<n_seg, 512, 0, st>>>(dur, cu_tok, cu_frames, idx, idx_cap, status);
+  launch_k(seg_totals_kernel, 1, 1024, 0, st, dur, cu_tok, n_seg, cu_frames);
+  launch_k(frame_index_kernel, n_seg, 512, 0, st, dur, cu_tok, cu_frames, idx, idx_cap, status);
   return cudaGetLastError();
 }
 

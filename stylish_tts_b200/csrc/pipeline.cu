@@ -14,6 +14,13 @@
 
 namespace stts {
 
+namespace { thread_local int tl_pdl = -1; }
+void pdl_set(int on) { tl_pdl = on; }
+bool pdl_enabled() {
+  static const bool env_on = [] { const char* e = std::getenv("STTS_PDL"); return e == nullptr || e[0] != '0'; }();
+  return env_on && tl_pdl != 0;
+}
+
 int fail(Context& c, int code, const std::string& msg) {
   c.err = msg;
   return code;

@@ -24,6 +24,7 @@ constexpr double kSampleRate = 24000.0;
 
 __global__ void __launch_bounds__(256) pcph_prefix_kernel(const float* __restrict__ p4, RowMap map,
                                                           double* __restrict__ prefix, SourceMeta* __restrict__ meta) {
+  pdl_enter();
   __shared__ double part[256];
   __shared__ float mins[256];
   __shared__ int anyv[256];
@@ -77,7 +78,7 @@ __global__ void __launch_bounds__(256) pcph_prefix_kernel(const float* __restric
 }
 
 cudaError_t pcph_prefix(const float* p4, const RowMap& map, double* prefix, SourceMeta* meta, cudaStream_t st) {
-  pcph_prefix_kernel<<<map.n_seg, 256, 0, st>>>(p4, map, prefix, meta);
+  launch_k(pcph_prefix_kernel, map.n_seg, 256, 0, st, p4, map, prefix, meta);
   return cudaGetLastError();
 }
 
@@ -90,6 +91,7 @@ __global__ void __launch_bounds__(256) pcph_source_kernel(const float* __restric
                                                           float* __restrict__ src, int ld,
                                                           __half* __restrict__ srcg, __half* __restrict__ srcl,
                                                           int ldg, float gscale, float* __restrict__ dense_out) {
+  pdl_enter();
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
   if (seg < 0) return;
@@ -157,7 +159,7 @@ __global__ void __launch_bounds__(256) pcph_source_kernel(const float* __restric
 cudaError_t pcph_source(const float* p4, const double* prefix, const SourceMeta* meta, const float* noise,
                         const float* init_phase, const int* cu4, const RowMap& map, float* src, int ld,
                         __half* srcg, __half* srcl, int ldg, float gscale, float* dense_out, cudaStream_t st) {
-  pcph_source_kernel<<<map.n_tiles, 256, 0, st>>>(p4, prefix, meta, noise, init_phase, cu4, map, src, ld, srcg, srcl,
+  launch_k(pcph_source_kernel, map.n_tiles, 256, 0, st, p4, prefix, meta, noise, init_phase, cu4, map, src, ld, srcg, srcl,
                                                   ldg, gscale, dense_out);
   return cudaGetLastError();
 }

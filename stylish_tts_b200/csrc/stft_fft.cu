@@ -73,6 +73,7 @@ __device__ __forceinline__ void dft16(cplx* x) {
 
 // twiddle tables computed once in fp64 (correctly rounded values)
 __global__ void stft_twiddle_kernel(double2* __restrict__ tw, double2* __restrict__ tw2) {
+  pdl_enter();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < kH) {
     double s, c;
@@ -87,7 +88,7 @@ __global__ void stft_twiddle_kernel(double2* __restrict__ tw, double2* __restric
 }
 
 cudaError_t stft_twiddles(double2* tw, double2* tw2, cudaStream_t st) {
-  stft_twiddle_kernel<<<(kH + 255) / 256, 256, 0, st>>>(tw, tw2);
+  launch_k(stft_twiddle_kernel, (kH + 255) / 256, 256, 0, st, tw, tw2);
   return cudaGetLastError();
 }
 
@@ -95,6 +96,7 @@ __global__ void __launch_bounds__(64 * kGroups, 4) stft_fft_kernel(
     const float* __restrict__ src, int lds, const float* __restrict__ window, const double2* __restrict__ g_tw,
     const double2* __restrict__ g_tw2, RowMap map, float* __restrict__ mag, float* __restrict__ pha, int ldo,
     __half* __restrict__ magg, __half* __restrict__ magl, __half* __restrict__ phag, __half* __restrict__ phal, int ldh) {
+  pdl_enter();
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
@@ -207,7 +209,7 @@ cudaError_t stft_fft(const float* src, int lds, const float* window, const doubl
     if (e != cudaSuccess) return e;
     attr_done = true;
   }
-  stft_fft_kernel<<<grid, 64 * kGroups, kSmem, st>>>(src, lds, window, tw, tw2, map, mag, pha, ldo, magg, magl, phag, phal,
+  launch_k(stft_fft_kernel, grid, 64 * kGroups, kSmem, st, src, lds, window, tw, tw2, map, mag, pha, ldo, magg, magl, phag, phal,
                                                    ldh);
   return cudaGetLastError();
 }

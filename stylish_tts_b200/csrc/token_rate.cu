@@ -22,6 +22,7 @@ __global__ void __launch_bounds__(128) embed_kernel(const int* __restrict__ tok,
                                                     const float* __restrict__ table, int C, int n_vocab, RowMap map,
                                                     float* __restrict__ x, int ldx, __half* __restrict__ xg,
                                                     __half* __restrict__ xl) {
+  pdl_enter();
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
   if (seg < 0) return;
@@ -40,7 +41,7 @@ __global__ void __launch_bounds__(128) embed_kernel(const int* __restrict__ tok,
 
 cudaError_t embed_tokens(const int* tok, const int* cu_tok, const float* table, int C, int n_vocab, const RowMap& map,
                          float* x, int ldx, cudaStream_t st, __half* xg, __half* xl) {
-  embed_kernel<<<dim3(map.n_tiles, kCopySplit), 128, 0, st>>>(tok, cu_tok, table, C, n_vocab, map, x, ldx, xg, xl);
+  launch_k(embed_kernel, dim3(map.n_tiles, kCopySplit), 128, 0, st, tok, cu_tok, table, C, n_vocab, map, x, ldx, xg, xl);
   return cudaGetLastError();
 }
 
@@ -53,7 +54,8 @@ __global__ void __launch_bounds__(256) row_ln_kernel(const float* x, int ldx, in
                                                      const float* __restrict__ gamma, const float* __restrict__ beta,
                                                      int seg_stride, float eps, int relu, float* y,
                                                      int ldy, __half* __restrict__ yg,
-                                                     __half* __restrict__ yl) {  // x may alias y (in place)
+                                                     __half* __restrict__ yl) {
+  pdl_enter();  // x may alias y (in place)
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
   if (seg < 0) return;
@@ -97,7 +99,7 @@ __global__ void __launch_bounds__(256) row_ln_kernel(const float* x, int ldx, in
 cudaError_t row_ln(const float* x, int ldx, int C, const RowMap& map, const float* gamma, const float* beta,
                    int seg_stride, float eps, int relu, float* y, int ldy, cudaStream_t st, __half* yg, __half* yl) {
   if (C > 512) return cudaErrorInvalidValue;
-  row_ln_kernel<<<dim3(map.n_tiles, 4), 256, 0, st>>>(x, ldx, C, map, gamma, beta, seg_stride, eps, relu, y, ldy, yg,
+  launch_k(row_ln_kernel, dim3(map.n_tiles, 4), 256, 0, st, x, ldx, C, map, gamma, beta, seg_stride, eps, relu, y, ldy, yg,
                                                       yl);
   return cudaGetLastError();
 }
@@ -108,6 +110,7 @@ cudaError_t row_ln(const float* x, int ldx, int C, const RowMap& map, const floa
 // position = row index inside the utterance.  text_encoder.py:89-168,200-201.
 __global__ void __launch_bounds__(256) rope_kernel(float* __restrict__ x, int ldx, int col0, int blk, int n_blocks,
                                                    int H, int D, int rd, RowMap map) {
+  pdl_enter();
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
   if (seg < 0) return;
@@ -134,7 +137,7 @@ __global__ void __launch_bounds__(256) rope_kernel(float* __restrict__ x, int ld
 
 cudaError_t rope_inplace(float* x, int ldx, int col0, int blk, int n_blocks, int H, int D, int rd, const RowMap& map,
                          cudaStream_t st) {
-  rope_kernel<<<dim3(map.n_tiles, 8), 256, 0, st>>>(x, ldx, col0, blk, n_blocks, H, D, rd, map);
+  launch_k(rope_kernel, dim3(map.n_tiles, 8), 256, 0, st, x, ldx, col0, blk, n_blocks, H, D, rd, map);
   return cudaGetLastError();
 }
 
@@ -150,6 +153,7 @@ __global__ void __launch_bounds__(128) attention_kernel(const float* __restrict_
                                                         float scale, RowMap qmap, RowMap kmap,
                                                         const int* __restrict__ q_tok, const int* __restrict__ q_cu,
                                                         int band, float* __restrict__ out, int ldo) {
+  pdl_enter();
   extern __shared__ float sh[];
   const int seg = blockIdx.z, hd = blockIdx.y;
   const int Tq = qmap.seg_len[seg], Tk = kmap.seg_len[seg];
@@ -287,6 +291,7 @@ __device__ __forceinline__ void rope_staged(float* x, int ldx, int nrows, int rd
 }
 
 __global__ void rope_table_kernel(float2* tab, int n_pos, int rd) {
+  pdl_enter();
   const int h = rd >> 1;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_pos * h; i += gridDim.x * blockDim.x) {
     const int pos = i / h, j = i - pos * h;
@@ -298,7 +303,7 @@ __global__ void rope_table_kernel(float2* tab, int n_pos, int rd) {
 }
 
 cudaError_t rope_table(float2* tab, int n_pos, int rd, cudaStream_t st) {
-  rope_table_kernel<<<64, 256, 0, st>>>(tab, n_pos, rd);
+  launch_k(rope_table_kernel, 64, 256, 0, st, tab, n_pos, rd);
   return cudaGetLastError();
 }
 
@@ -311,6 +316,7 @@ __global__ void __launch_bounds__(128) attention_tiled_kernel(const float* __res
                                                               const int* __restrict__ q_tok,
                                                               const int* __restrict__ q_cu, int band,
                                                               float* __restrict__ out, int ldo) {
+  pdl_enter();
   extern __shared__ float sh[];
   constexpr int KLD = D + 1;                  // padded: a column of kv[][] is read by consecutive threads
   constexpr int VLD = kAttChunk + 4;          // transposed V chunk vt[d][j]: float4 reads along j, conflict-free
@@ -456,6 +462,7 @@ __global__ void __launch_bounds__(NT) attention_stream_kernel(const float* __res
                                                               float* __restrict__ out, int ldo,
                                                               __half* __restrict__ outg, __half* __restrict__ outl,
                                                               int ldh) {
+  pdl_enter();
   extern __shared__ float sh[];
   // A query group = LPQ x KP adjacent lanes: LPQ lanes split the head's features, KP lane sets split the keys of
   // every chunk (key j of the chunk goes to set j % KP) and are merged once at the end (flash-decoding style), and
@@ -621,7 +628,7 @@ cudaError_t launch_attention_stream(const float* Q, int ldq, int qcol, const flo
     configured = true;
   }
   dim3 grid((max_tq + QPB - 1) / QPB, H, qmap.n_seg);
-  attention_stream_kernel<D, LPQ, QPT, NT, KP><<<grid, NT, smem, st>>>(Q, ldq, qcol, K, ldk, kcol, V, ldv, vcol, scale, rd,
+  launch_k(attention_stream_kernel<D, LPQ, QPT, NT, KP>, grid, NT, smem, st, Q, ldq, qcol, K, ldk, kcol, V, ldv, vcol, scale, rd,
                                                                    tab, qmap, kmap, q_tok, q_cu, band, out, ldo, outg,
                                                                    outl, ldh);
   return cudaGetLastError();
@@ -643,7 +650,7 @@ cudaError_t launch_attention_tiled(const float* Q, int ldq, int qcol, const floa
     configured = smem;
   }
   dim3 grid((max_tq + QB - 1) / QB, H, qmap.n_seg);
-  attention_tiled_kernel<D, QB><<<grid, 128, smem, st>>>(Q, ldq, qcol, K, ldk, kcol, V, ldv, vcol, scale, rd, tab, qmap,
+  launch_k(attention_tiled_kernel<D, QB>, grid, 128, smem, st, Q, ldq, qcol, K, ldk, kcol, V, ldv, vcol, scale, rd, tab, qmap,
                                                          kmap, q_tok, q_cu, band, out, ldo);
   return cudaGetLastError();
 }
@@ -695,7 +702,7 @@ cudaError_t attention(const float* Q, int ldq, int qcol, const float* K, int ldk
     configured = smem;
   }
   dim3 grid((max_tq + kAttQ - 1) / kAttQ, H, qmap.n_seg);
-  attention_kernel<<<grid, 128, smem, st>>>(Q, ldq, qcol, K, ldk, kcol, V, ldv, vcol, D, scale, qmap, kmap, q_tok, q_cu,
+  launch_k(attention_kernel, grid, 128, smem, st, Q, ldq, qcol, K, ldk, kcol, V, ldv, vcol, D, scale, qmap, kmap, q_tok, q_cu,
                                             band, out, ldo);
   return cudaGetLastError();
 }
@@ -704,6 +711,7 @@ cudaError_t attention(const float* Q, int ldq, int qcol, const float* K, int ldk
 // dst[(cu[seg] + t) * C + c] = src[row(seg, t), c]: the utterances' rows concatenated without gaps
 __global__ void __launch_bounds__(256) rows_to_dense_kernel(const float* __restrict__ src, int ld, int C, RowMap map,
                                                             const int* __restrict__ cu, float* __restrict__ dst) {
+  pdl_enter();
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
   if (seg < 0) return;
@@ -717,7 +725,7 @@ __global__ void __launch_bounds__(256) rows_to_dense_kernel(const float* __restr
 
 cudaError_t rows_to_dense(const float* src, int ld, int C, const RowMap& map, const int* cu, float* dst,
                           cudaStream_t st) {
-  rows_to_dense_kernel<<<dim3(map.n_tiles, kCopySplit), 256, 0, st>>>(src, ld, C, map, cu, dst);
+  launch_k(rows_to_dense_kernel, dim3(map.n_tiles, kCopySplit), 256, 0, st, src, ld, C, map, cu, dst);
   return cudaGetLastError();
 }
 
@@ -729,6 +737,7 @@ __global__ void __launch_bounds__(256) dwconv_rows_kernel(const float* __restric
                                                           const float* __restrict__ w, const float* __restrict__ b,
                                                           RowMap map, int act, float* __restrict__ y, int ldy,
                                                           __half* __restrict__ yg, __half* __restrict__ yl) {
+  pdl_enter();
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
   if (seg < 0) return;
@@ -751,7 +760,7 @@ __global__ void __launch_bounds__(256) dwconv_rows_kernel(const float* __restric
 
 cudaError_t dwconv_rows(const float* x, int ldx, int C, int K, const float* w, const float* b, const RowMap& map,
                         int act, float* y, int ldy, cudaStream_t st, __half* yg, __half* yl) {
-  dwconv_rows_kernel<<<dim3(map.n_tiles, 4), 256, 0, st>>>(x, ldx, C, K, w, b, map, act, y, ldy, yg, yl);
+  launch_k(dwconv_rows_kernel, dim3(map.n_tiles, 4), 256, 0, st, x, ldx, C, K, w, b, map, act, y, ldy, yg, yl);
   return cudaGetLastError();
 }
 
@@ -760,6 +769,7 @@ __global__ void __launch_bounds__(256) dense_to_rows_kernel(const float* __restr
                                                             const int* __restrict__ cu, float* __restrict__ dst,
                                                             int ld, int col0, __half* __restrict__ dg,
                                                             __half* __restrict__ dl) {
+  pdl_enter();
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
   if (seg < 0) return;
@@ -776,7 +786,7 @@ __global__ void __launch_bounds__(256) dense_to_rows_kernel(const float* __restr
 
 cudaError_t dense_to_rows(const float* src, int C, const RowMap& map, const int* cu, float* dst, int ld, int col0,
                           cudaStream_t st, __half* dg, __half* dl) {
-  dense_to_rows_kernel<<<dim3(map.n_tiles, kCopySplit), 256, 0, st>>>(src, C, map, cu, dst, ld, col0, dg, dl);
+  launch_k(dense_to_rows_kernel, dim3(map.n_tiles, kCopySplit), 256, 0, st, src, C, map, cu, dst, ld, col0, dg, dl);
   return cudaGetLastError();
 }
 
@@ -784,6 +794,7 @@ cudaError_t dense_to_rows(const float* src, int C, const RowMap& map, const int*
 __global__ void __launch_bounds__(256) seg_broadcast_kernel(const float* __restrict__ vec, int C, RowMap map,
                                                             float* __restrict__ dst, int ld, int col0,
                                                             __half* __restrict__ dg, __half* __restrict__ dl) {
+  pdl_enter();
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
   if (seg < 0) return;
@@ -799,7 +810,7 @@ __global__ void __launch_bounds__(256) seg_broadcast_kernel(const float* __restr
 
 cudaError_t seg_broadcast(const float* vec, int C, const RowMap& map, float* dst, int ld, int col0, cudaStream_t st,
                           __half* dg, __half* dl) {
-  seg_broadcast_kernel<<<dim3(map.n_tiles, kCopySplit), 256, 0, st>>>(vec, C, map, dst, ld, col0, dg, dl);
+  launch_k(seg_broadcast_kernel, dim3(map.n_tiles, kCopySplit), 256, 0, st, vec, C, map, dst, ld, col0, dg, dl);
   return cudaGetLastError();
 }
 

@@ -54,6 +54,7 @@ __global__ void __launch_bounds__(256) adain_snake_kernel(const float* __restric
                                                           const float* __restrict__ gb, int ldgb,
                                                           const float* __restrict__ alpha, float* __restrict__ y, int ldy,
                                                           twin_t* __restrict__ yh, int ldyh) {
+  pdl_enter();
   const int tile = blockIdx.x;
   const int seg = map.tile_seg[tile];
   if (seg < 0) return;
@@ -85,7 +86,7 @@ cudaError_t adain_snake(const float* x, int ldx, int C, const RowMap& map, const
                         const float* gb, int ldgb, const float* alpha, float* y, int ldy, twin_t* yh, int ldyh,
                         cudaStream_t st) {
   dim3 grid(map.n_tiles, (C + 127) / 128);
-  adain_snake_kernel<<<grid, 256, 0, st>>>(x, ldx, C, map, mean, rstd, gb, ldgb, alpha, y, ldy, yh, ldyh);
+  launch_k(adain_snake_kernel, grid, 256, 0, st, x, ldx, C, map, mean, rstd, gb, ldgb, alpha, y, ldy, yh, ldyh);
   return cudaGetLastError();
 }
 
@@ -262,6 +263,7 @@ __global__ void __launch_bounds__(kSgThreads) sinegen_pass_kernel(
     const int* __restrict__ chunk_start, const float* __restrict__ rand_ini, const double* __restrict__ P1,
     const double* __restrict__ P2, double* __restrict__ T, const SgParams p, const float* __restrict__ noise,
     float* __restrict__ out, float* __restrict__ phase) {
+  pdl_enter();
   __shared__ double ws[kSgThreads / 32];
   const int chunk = blockIdx.x;
   const int seg = chunk_seg[chunk];
@@ -342,6 +344,7 @@ __global__ void __launch_bounds__(kSgThreads) sinegen_pass_kernel(
 // P[chunk, h] = sum of T over the earlier chunks of the same utterance
 __global__ void sinegen_prefix_kernel(const double* __restrict__ T, double* __restrict__ P, const int* __restrict__ seg_chunk0,
                                       int dim) {
+  pdl_enter();
   const int seg = blockIdx.x, h = threadIdx.x;
   if (h >= dim) return;
   double run = 0.0;
@@ -403,17 +406,17 @@ int run_sinegen(Context& c, const float* d_f0, const int* h_len, int n_seg, cons
   p.noise_voiced = noise_std;                                    // uv * noise_std + (1 - uv) * sine_amp / 3, uv = 1
   p.noise_unvoiced = sine_amp / 3.f;                             // ... uv = 0 (fp32 division, like the tensor op)
   for (int h = 0; h < dim; ++h) p.w[h] = h_merge_w[h];
-  sinegen_pass_kernel<0><<<nch, kSgThreads, 0, st>>>(d_f0, d_cu, d_cs, d_ct, d_rand_ini, nullptr, nullptr, T, p, d_noise,
+  launch_k(sinegen_pass_kernel<0>, nch, kSgThreads, 0, st, d_f0, d_cu, d_cs, d_ct, d_rand_ini, nullptr, nullptr, T, p, d_noise,
                                                       nullptr, nullptr);
   STTS_CK(cudaGetLastError());
-  sinegen_prefix_kernel<<<n_seg, 32, 0, st>>>(T, P1, d_sc, dim);
+  launch_k(sinegen_prefix_kernel, n_seg, 32, 0, st, T, P1, d_sc, dim);
   STTS_CK(cudaGetLastError());
-  sinegen_pass_kernel<1><<<nch, kSgThreads, 0, st>>>(d_f0, d_cu, d_cs, d_ct, d_rand_ini, P1, nullptr, T, p, d_noise,
+  launch_k(sinegen_pass_kernel<1>, nch, kSgThreads, 0, st, d_f0, d_cu, d_cs, d_ct, d_rand_ini, P1, nullptr, T, p, d_noise,
                                                       nullptr, nullptr);
   STTS_CK(cudaGetLastError());
-  sinegen_prefix_kernel<<<n_seg, 32, 0, st>>>(T, P2, d_sc, dim);
+  launch_k(sinegen_prefix_kernel, n_seg, 32, 0, st, T, P2, d_sc, dim);
   STTS_CK(cudaGetLastError());
-  sinegen_pass_kernel<2><<<nch, kSgThreads, 0, st>>>(d_f0, d_cu, d_cs, d_ct, d_rand_ini, P1, P2, T, p, d_noise, d_out,
+  launch_k(sinegen_pass_kernel<2>, nch, kSgThreads, 0, st, d_f0, d_cu, d_cs, d_ct, d_rand_ini, P1, P2, T, p, d_noise, d_out,
                                                       d_phase);
   STTS_CK(cudaGetLastError());
   return 0;

@@ -97,6 +97,10 @@ class Engine:
         self._check(self.lib.stts_set_precision(self.h, PRECISIONS[name]))
         self.precision = name
 
+    def set_pdl(self, on: bool):
+        """Programmatic dependent launch of this context's kernels (default on; see stts_set_pdl)."""
+        self._check(self.lib.stts_set_pdl(self.h, 1 if on else 0))
+
     # ------------------------------------------------------------------ layout
     def set_layout(self, len_f: Optional[Iterable[int]], len_f4: Optional[Iterable[int]]):
         lf = [int(x) for x in len_f] if len_f is not None else None

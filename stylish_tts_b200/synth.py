@@ -328,6 +328,10 @@ class SynthesizerPool:
         self.lanes = [first] + [Synthesizer(first.nets, device, precision, model_config, use_graphs)
                                 for _ in range(lanes - 1)]
         self.streams = [torch.cuda.Stream(self.device) for _ in range(lanes)]
+        if lanes > 1:       # concurrent lanes: look-ahead CTAs of one lane would take SM slots from the others
+            for lane in self.lanes:
+                lane.engine.set_pdl(False)
+                lane._graphs.clear()
         self._done = [None] * lanes
         self._next = 0
 
