@@ -85,6 +85,9 @@ enum EpiKind : int {
   EPI_STFT = 8,        // (re,im) interleaved -> out = |X|, out2 = atan2            (generator.py:32-44,407-410)
   EPI_RELU = 9,        // out = relu(acc + bias)                    (FFN conv_1, text_encoder.py:305-329)
   EPI_GELU = 10,       // out = gelu(acc + bias), exact erf form   (BasicConvNeXtBlock, conv_next.py:18-51)
+  EPI_LN = 11,         // out = act(affine(LayerNorm_row(acc + bias + res)))  tcgen05 kernels only, N <= 256: the
+                       //   channel LayerNorm / AdaptiveLayerNorm that follows the attention / FFN projections of the
+                       //   token-rate encoders (text_encoder.py:171-221, prosody_encoder.py:33-60), see ln_epilogue
 };
 
 struct Epi {
@@ -111,6 +114,9 @@ struct Epi {
   // the stored output, [n_tiles * 4, colst_ld] fp32 each -- InstanceNorm statistics of the next AdaIN without
   // re-reading the tensor (16-bit mode)
   float* colsum; float* colsq; int colst_ld;
+  // EPI_LN: ln_seg_stride == 0: affine = ln_g[n] * x + ln_b[n]; > 0: (1 + g[seg, n]) * x + g[seg, N + n] with
+  // g = ln_g + seg * ln_seg_stride (AdaptiveLayerNorm, the style FC row of the utterance)
+  const float* ln_g; const float* ln_b; int ln_seg_stride; float ln_eps; int ln_relu;
 };
 
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + __expf(-x)); }

@@ -291,6 +291,83 @@ __device__ __forceinline__ void stft_slab(const Epi& e, const float* __restrict_
   }
 }
 
+// EPI_LN: row LayerNorm fused into the epilogue.  A 128-row tile sees whole rows (N <= BN, one column tile), but a
+// row's columns are spread over the N / 64 epilogue warps of its lane quarter: each thread (= one row of one 64-column
+// slab, straight from TMEM) forms x = acc * scale + bias + res, the partial sums go through shared memory (lnbuf:
+// [2][4 slabs][128 rows]) with a named barrier per quarter, two passes (mean, then centred squares: the same biased
+// two-pass variance as row_ln_kernel).  The normalised values are transposed through the staging block so that the
+// affine / ReLU / stores run lane-per-column: coalesced fp32 rows and fp16 split twins.  `res` may alias `out`
+// (a row is read and written by this warp group only, writes follow the second barrier).
+__device__ __forceinline__ void ln_epilogue(const Epi& e, float acc_scale, uint32_t taddr, float* stg, float* lnbuf, int slab,
+                                            int q, int lane, int row0, int nrows, int seg, int n_live) {
+  const int c0 = slab * 64;
+  const int rl = q * 32 + lane;                       // row inside the tile
+  const bool live = lane < nrows;
+  float v[64];
+  tmem_ld64(taddr, v);
+  const float* rp = (e.res != nullptr && live) ? e.res + (size_t)(row0 + lane) * e.ldr + e.rcol0 + c0 : nullptr;
+  float s = 0.f;
+#pragma unroll
+  for (int j = 0; j < 64; j += 4) {
+    float4 r4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (rp != nullptr && c0 + j < e.N) r4 = *reinterpret_cast<const float4*>(rp + j);     // N % 4 == 0 (launch guard)
+    const float rr[4] = {r4.x, r4.y, r4.z, r4.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int n = c0 + j + i;
+      const float x = (n < e.N) ? v[j + i] * acc_scale + (e.bias != nullptr ? e.bias[n] : 0.f) + rr[i] : 0.f;
+      v[j + i] = x;
+      s += x;
+    }
+  }
+  const int bar = 1 + q, cnt = 32 * n_live;
+  lnbuf[slab * 128 + rl] = s;
+  asm volatile("bar.sync %0, %1;" ::"r"(bar), "r"(cnt) : "memory");
+  float tot = 0.f;
+  for (int k = 0; k < n_live; ++k) tot += lnbuf[k * 128 + rl];
+  const float mean = tot / (float)e.N;
+  float sq = 0.f;
+#pragma unroll
+  for (int j = 0; j < 64; ++j) {
+    const float d = (c0 + j < e.N) ? v[j] - mean : 0.f;
+    v[j] = d;
+    sq += d * d;
+  }
+  lnbuf[512 + slab * 128 + rl] = sq;
+  asm volatile("bar.sync %0, %1;" ::"r"(bar), "r"(cnt) : "memory");
+  float tq = 0.f;
+  for (int k = 0; k < n_live; ++k) tq += lnbuf[512 + k * 128 + rl];
+  const float rstd = rsqrtf(tq / (float)e.N + e.ln_eps);
+#pragma unroll
+  for (int j = 0; j < 64; j += 2) *reinterpret_cast<float2*>(stg + lane * kStgLd + j) = make_float2(v[j] * rstd, v[j + 1] * rstd);
+  __syncwarp();
+  // lane-per-column-pair: columns c0 + 2 lane, + 1
+  const int n = c0 + 2 * lane;
+  if (n < e.N) {
+    float g0, g1, b0, b1;
+    if (e.ln_seg_stride > 0) {
+      const float* g = e.ln_g + (size_t)seg * e.ln_seg_stride;
+      g0 = 1.f + g[n]; g1 = 1.f + g[n + 1]; b0 = g[e.N + n]; b1 = g[e.N + n + 1];
+    } else {
+      g0 = e.ln_g[n]; g1 = e.ln_g[n + 1]; b0 = e.ln_b[n]; b1 = e.ln_b[n + 1];
+    }
+    for (int r = 0; r < nrows; ++r) {
+      const float2 a = *reinterpret_cast<const float2*>(stg + r * kStgLd + 2 * lane);
+      float o0 = a.x * g0 + b0, o1 = a.y * g1 + b1;
+      if (e.ln_relu) { o0 = fmaxf(o0, 0.f); o1 = fmaxf(o1, 0.f); }
+      const size_t row = (size_t)(row0 + r);
+      *reinterpret_cast<float2*>(e.out + row * e.ldo + e.col0 + n) = make_float2(o0, o1);
+      if (e.outg != nullptr) {
+        __half g0h, l0h, g1h, l1h;
+        f16_split(o0, &g0h, &l0h);
+        f16_split(o1, &g1h, &l1h);
+        *reinterpret_cast<__half2*>(e.outg + row * e.ldh + e.colh0 + n) = __halves2half2(g0h, g1h);
+        if (e.outl != nullptr) *reinterpret_cast<__half2*>(e.outl + row * e.ldh + e.colh0 + n) = __halves2half2(l0h, l1h);
+      }
+    }
+  }
+}
+
 // MODE_F16 doubles as the one-pass fp16 GEMM (runtime instruction-descriptor formats), MODE_F16X3 is
 // the three-pass fp16 split (hi*hi + hi*lo + lo*hi, fp32-grade), MODE_TF32X3 the tf32 split on fp32 operands
 enum { MODE_F16 = 0, MODE_TF32X3 = 1, MODE_F16X3 = 2 };
@@ -489,6 +566,14 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
     nrows = nrows < 0 ? 0 : (nrows > 32 ? 32 : nrows);
     const int seg_first = (epi.seg_start != nullptr) ? epi.seg_start[seg] : -1;
     const int c = (ew >> 2) * 64;
+    if constexpr (KIND == EPI_LN) {
+      if (c < epi.N) {                         // warp-uniform; one column tile (n0 == 0)
+        float* lnbuf = reinterpret_cast<float*>(smem) + C::kEpiWarps * (32 * kStgLd4);
+        ln_epilogue(epi, p.acc_scale, tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c,
+                    reinterpret_cast<float*>(smem) + ew * (32 * kStgLd4), lnbuf, ew >> 2, q, lane, row0, nrows, seg,
+                    (epi.N + 63) / 64);
+      }
+    } else
     if constexpr (EQ::kOk) {
       if (n0 + c < epi.N) {                    // warp-uniform
         {
@@ -1033,6 +1118,15 @@ template <int MODE, int BN, int KIND, int OCC = 1>
 cudaError_t launch_one(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
   using C = Cfg<MODE, BN, OCC>;
   constexpr int elem = C::kElem;
+  if constexpr (KIND == EPI_LN) {
+    // whole rows in one column tile; float4 residual loads and half2 twin stores; staging + lnbuf inside the stage ring
+    static_assert(C::kStages * C::kStageBytes >= C::kEpiWarps * 32 * kStgLd4 * 4 + 2 * 4 * 128 * 4, "EPI_LN staging");
+    const Epi& e = g.epi;
+    if (e.N > BN || (e.N & 3) || e.ln_g == nullptr || (e.ln_seg_stride == 0 && e.ln_b == nullptr) || (e.ldo & 1) ||
+        (e.col0 & 1) || (e.res != nullptr && ((e.ldr & 3) || (e.rcol0 & 3))) ||
+        (e.outg != nullptr && ((e.ldh & 1) || (e.colh0 & 1))))
+      return cudaErrorInvalidValue;
+  }
   CUtensorMap mA[2], mAlo[2], mW, mWlo;
   TcParams p{};
   p.n_kseg = g.n_kseg;
@@ -1170,6 +1264,11 @@ int occ2_max_chunks() {
 
 template <int MODE, int KIND>
 cudaError_t launch_bn(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
+  if constexpr (KIND == EPI_LN) {            // one column tile must hold the whole row
+    if (g.epi.N <= 128) return launch_one<MODE, 128, KIND>(g, map, st);
+    if (g.epi.N <= 256 && g.Npad % 256 == 0) return launch_one<MODE, 256, KIND>(g, map, st);
+    return cudaErrorInvalidValue;
+  }
   if constexpr (MODE == MODE_F16) {
     int chunks = 0;
     for (int s = 0; s < g.n_kseg; ++s) chunks += g.seg[s].taps * (g.seg[s].cin_pad / 64);
@@ -1208,6 +1307,9 @@ cudaError_t launch_mode(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
     case EPI_STFT: return launch_bn<MODE, EPI_STFT>(g, map, st);
     case EPI_RELU: return launch_bn<MODE, EPI_RELU>(g, map, st);
     case EPI_GELU: return launch_bn<MODE, EPI_GELU>(g, map, st);
+    case EPI_LN:
+      if constexpr (MODE == MODE_F16) return cudaErrorInvalidValue;   // fp32-grade modes only (token-rate islands)
+      else return launch_bn<MODE, EPI_LN>(g, map, st);
     default: return cudaErrorInvalidValue;
   }
 }

@@ -128,6 +128,22 @@ Epi mk_epi(int kind, const Act& dst, int col0, bool tw = false) {
   if (tw && dst.g != nullptr) { e.outg = dst.g; e.outl = dst.l; e.ldh = dst.ldg; e.colh0 = col0; }
   return e;
 }
+// LayerNorm / AdaptiveLayerNorm fused into the epilogue of the GEMM that produces its input (EPI_LN, gemm_tc.cu):
+// tensor-core modes, rows of <= 256 channels.  STTS_LN_FUSED=0 keeps the separate row_ln launch (A/B runs).
+bool ln_fused(const Context& c, int width) {
+  static const bool on = [] { const char* e = std::getenv("STTS_LN_FUSED"); return e == nullptr || e[0] != '0'; }();
+  return on && c.precision != 0 && width <= 256 && width % 4 == 0;
+}
+// out = act(affine(LN(acc + bias + res))); res may be the destination itself
+Epi mk_ln_epi(const Act& dst, bool tw, const float* g, const float* b, int seg_stride, float eps, int relu, const Act* res) {
+  Epi e;
+  std::memset(&e, 0, sizeof(e));
+  e.kind = EPI_LN; e.out = dst.f; e.ldo = dst.ld; e.col0 = 0; e.scale = 1.f;
+  if (tw && dst.g != nullptr) { e.outg = dst.g; e.outl = dst.l; e.ldh = dst.ldg; e.colh0 = 0; }
+  e.ln_g = g; e.ln_b = b; e.ln_seg_stride = seg_stride; e.ln_eps = eps; e.ln_relu = relu;
+  if (res != nullptr) { e.res = res->f; e.ldr = res->ld; e.rcol0 = 0; }
+  return e;
+}
 struct Tw {                      // twin pointers of an Act in 16-bit mode, nulls otherwise
   __half* g; __half* l;
   Tw(const Context& c, const Act& a) : g(c.precision == 1 ? a.g : nullptr), l(c.precision == 1 ? a.l : nullptr) {}
@@ -154,9 +170,14 @@ int run_text_encoder(Context& c, const std::string& nm, const int* d_tokens, flo
   for (int i = 0; i < 3; ++i) {
     const std::string n = nm + ".pre" + std::to_string(i);
     Act& dst = *pp[i & 1];
-    STTS_RET(run_gemm(c, c.gemm[n], GC_ISLAND, y, 0, nullptr, 0, mk_epi(EPI_BIAS, dst, 0), map, st));
-    STTS_CK(row_ln(dst.f, dst.ld, C, map, c.vec[n + ".g"], c.vec[n + ".b"], 0, 1e-4f, 1, dst.f, dst.ld, st,
-                   Tw(c, dst).g, Tw(c, dst).l));
+    if (ln_fused(c, C)) {
+      STTS_RET(run_gemm(c, c.gemm[n], GC_ISLAND, y, 0, nullptr, 0,
+                        mk_ln_epi(dst, t16, c.vec[n + ".g"], c.vec[n + ".b"], 0, 1e-4f, 1, nullptr), map, st));
+    } else {
+      STTS_RET(run_gemm(c, c.gemm[n], GC_ISLAND, y, 0, nullptr, 0, mk_epi(EPI_BIAS, dst, 0), map, st));
+      STTS_CK(row_ln(dst.f, dst.ld, C, map, c.vec[n + ".g"], c.vec[n + ".b"], 0, 1e-4f, 1, dst.f, dst.ld, st,
+                     Tw(c, dst).g, Tw(c, dst).l));
+    }
     y = &dst;
   }
   {
@@ -173,21 +194,27 @@ int run_text_encoder(Context& c, const std::string& nm, const int* d_tokens, flo
     // partial RoPE of q / k is applied inside the attention kernel while it stages the rows
     STTS_CK(attention(tqkv.f, tqkv.ld, 0, tqkv.f, tqkv.ld, C, tqkv.f, tqkv.ld, 2 * C, H, D, scale, rd, rope_tab(c, rd, st), map, map, c.max_t,
                       c.max_t, nullptr, nullptr, 0, to.f, to.ld, st, Tw(c, to).g, Tw(c, to).l, to.ldg));
-    {
+    if (ln_fused(c, C)) {       // x = LN(x + proj(...)) in the projection's epilogue, in place
+      STTS_RET(run_gemm(c, c.gemm[n + ".o"], GC_ISLAND, &to, 0, nullptr, 0,
+                        mk_ln_epi(tx, t16, c.vec[n + ".n1.g"], c.vec[n + ".n1.b"], 0, 1e-4f, 0, &tx), map, st));
+    } else {
       Epi e = mk_epi(EPI_ADD, tb, 0);
       e.res = tx.f; e.ldr = tx.ld; e.rcol0 = 0;
       STTS_RET(run_gemm(c, c.gemm[n + ".o"], GC_ISLAND, &to, 0, nullptr, 0, e, map, st));
+      STTS_CK(row_ln(tb.f, tb.ld, C, map, c.vec[n + ".n1.g"], c.vec[n + ".n1.b"], 0, 1e-4f, 0, tx.f, tx.ld, st,
+                     Tw(c, tx).g, Tw(c, tx).l));
     }
-    STTS_CK(row_ln(tb.f, tb.ld, C, map, c.vec[n + ".n1.g"], c.vec[n + ".n1.b"], 0, 1e-4f, 0, tx.f, tx.ld, st,
-                   Tw(c, tx).g, Tw(c, tx).l));
     STTS_RET(run_gemm(c, c.gemm[n + ".ff1"], GC_ISLAND, &tx, 0, nullptr, 0, mk_epi(EPI_RELU, th, 0, t16), map, st));
-    {
+    if (ln_fused(c, C)) {       // x = LN(x + proj(...)) in the projection's epilogue, in place
+      STTS_RET(run_gemm(c, c.gemm[n + ".ff2"], GC_ISLAND, &th, 0, nullptr, 0,
+                        mk_ln_epi(tx, t16, c.vec[n + ".n2.g"], c.vec[n + ".n2.b"], 0, 1e-4f, 0, &tx), map, st));
+    } else {
       Epi e = mk_epi(EPI_ADD, tb, 0);
       e.res = tx.f; e.ldr = tx.ld; e.rcol0 = 0;
       STTS_RET(run_gemm(c, c.gemm[n + ".ff2"], GC_ISLAND, &th, 0, nullptr, 0, e, map, st));
+      STTS_CK(row_ln(tb.f, tb.ld, C, map, c.vec[n + ".n2.g"], c.vec[n + ".n2.b"], 0, 1e-4f, 0, tx.f, tx.ld, st,
+                     Tw(c, tx).g, Tw(c, tx).l));
     }
-    STTS_CK(row_ln(tb.f, tb.ld, C, map, c.vec[n + ".n2.g"], c.vec[n + ".n2.b"], 0, 1e-4f, 0, tx.f, tx.ld, st,
-                   Tw(c, tx).g, Tw(c, tx).l));
   }
   const PackedGemm& pm = c.gemm[nm + ".projm"];
   STTS_RET(run_gemm(c, pm, GC_ISLAND, &tx, 0, nullptr, 0, mk_epi(EPI_BIAS, tmu, 0, t16), map, st));   // mu feeds the style conv
@@ -221,21 +248,27 @@ int run_prosody_encoder(Context& c, const std::string& nm, const float* d_enc_to
     STTS_RET(run_gemm(c, c.gemm[n + ".qkv"], GC_ISLAND, &px, 0, nullptr, 0, mk_epi(EPI_BIAS, pqkv, 0), map, st));
     STTS_CK(attention(pqkv.f, pqkv.ld, 0, pqkv.f, pqkv.ld, hid, pqkv.f, pqkv.ld, 2 * hid, H, D, scale, rd, rope_tab(c, rd, st), map, map,
                       c.max_t, c.max_t, nullptr, nullptr, 0, po.f, po.ld, st, Tw(c, po).g, Tw(c, po).l, po.ldg));
-    {
+    if (ln_fused(c, hid)) {
+      STTS_RET(run_gemm(c, c.gemm[n + ".o"], GC_ISLAND, &po, 0, nullptr, 0,
+                        mk_ln_epi(py, t16, gb + c.fc_off[n + ".n1"], nullptr, J, 1e-5f, 0, &px), map, st));
+    } else {
       Epi e = mk_epi(EPI_ADD, pb, 0);
       e.res = px.f; e.ldr = px.ld; e.rcol0 = 0;
       STTS_RET(run_gemm(c, c.gemm[n + ".o"], GC_ISLAND, &po, 0, nullptr, 0, e, map, st));
+      STTS_CK(row_ln(pb.f, pb.ld, hid, map, gb + c.fc_off[n + ".n1"], nullptr, J, 1e-5f, 0, py.f, py.ld, st,
+                     Tw(c, py).g, Tw(c, py).l));
     }
-    STTS_CK(row_ln(pb.f, pb.ld, hid, map, gb + c.fc_off[n + ".n1"], nullptr, J, 1e-5f, 0, py.f, py.ld, st,
-                   Tw(c, py).g, Tw(c, py).l));
     STTS_RET(run_gemm(c, c.gemm[n + ".ff1"], GC_ISLAND, &py, 0, nullptr, 0, mk_epi(EPI_RELU, ph, 0, t16), map, st));
-    {
+    if (ln_fused(c, hid)) {
+      STTS_RET(run_gemm(c, c.gemm[n + ".ff2"], GC_ISLAND, &ph, 0, nullptr, 0,
+                        mk_ln_epi(py, t16, gb + c.fc_off[n + ".n2"], nullptr, J, 1e-5f, 0, &py), map, st));
+    } else {
       Epi e = mk_epi(EPI_ADD, pb, 0);
       e.res = py.f; e.ldr = py.ld; e.rcol0 = 0;
       STTS_RET(run_gemm(c, c.gemm[n + ".ff2"], GC_ISLAND, &ph, 0, nullptr, 0, e, map, st));
+      STTS_CK(row_ln(pb.f, pb.ld, hid, map, gb + c.fc_off[n + ".n2"], nullptr, J, 1e-5f, 0, py.f, py.ld, st,
+                     Tw(c, py).g, Tw(c, py).l));
     }
-    STTS_CK(row_ln(pb.f, pb.ld, hid, map, gb + c.fc_off[n + ".n2"], nullptr, J, 1e-5f, 0, py.f, py.ld, st,
-                   Tw(c, py).g, Tw(c, py).l));
     // x = cat([proj(x), style]): the style columns of PX (and of its twins) are still in place
     STTS_RET(run_gemm(c, c.gemm[n + ".proj"], GC_ISLAND, &py, 0, nullptr, 0, mk_epi(EPI_BIAS, px, 0, t16), map, st));
   }
