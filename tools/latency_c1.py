@@ -17,4 +17,4 @@ nets = build_model(ModelConfig())
 for k, m in nets.items():
     m.load_state_dict(sds[k])
     m.eval()
-print(json.dumps(c1_latency(nets, dev, sys.argv[1] if len(sys.argv) > 1 else "f16", iters=60)))
+print(json.dumps(c1_latency(nets, dev, sys.argv[1] if len(sys.argv) > 1 else "f16", iters=int(os.environ.get("ITERS", "60")))))
