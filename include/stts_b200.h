@@ -150,6 +150,23 @@ int stts_generator_block_snake(stts_ctx* ctx, const char* module, int channels, 
                                const int* dilation /*[3]*/, int n_seg, const int* len, const float* d_x,
                                const float* d_style, float* d_out, void* stream);
 
+/* STFT.transform / STFT.inverse, train/models/stft.py:98-136 / :138-186 -- the conv1d / conv_transpose1d DFT module
+ * swapped in for the ONNX export (convert_to_onnx.py:31-36).  Basis matrices: the module's
+ * own buffers weight_forward_real / weight_forward_imag / weight_backward_real / weight_backward_imag
+ * ([filter_length / 2 + 1, 1, filter_length], stft.py:69-96) loaded under `module` with stts_load_tensor.
+ * transform: d_wave = the utterances back to back, len [n_seg] HOST samples; pad_mode 0 = replicate (the module's
+ * default), 1 = constant; outputs per utterance a dense [bins, frames_b] block (frames_b = len_b / hop + 1), blocks
+ * back to back: magnitude = sqrt(re^2 + im^2 + 1e-14), re / magnitude, im / magnitude.
+ * inverse: same block layout in; writes out_len[b] <= (n_frames[b] - 1) * hop samples per utterance (NULL = all; the
+ * module's `length` argument).  filter_length even, ceil(win_length / hop_length) <= 33.  fp32-grade arithmetic
+ * (CUDA cores in fp32 mode, three-pass tf32 otherwise).                                                              */
+int stts_stft_conv_transform(stts_ctx* ctx, const char* module, int filter_length, int hop_length, int win_length,
+                             int pad_mode, int n_seg, const int* len, const float* d_wave, float* d_mag, float* d_x,
+                             float* d_y, void* stream);
+int stts_stft_conv_inverse(stts_ctx* ctx, const char* module, int filter_length, int hop_length, int win_length,
+                           int n_seg, const int* n_frames, const int* out_len, const float* d_mag, const float* d_x,
+                           const float* d_y, float* d_wave, void* stream);
+
 /* ---- pitch / energy towers --------------------------------------------------------------------
  * PitchEnergyPredictor.forward lines 111-119 (pitch_energy_predictor.py): 2 x 3
  * AdaptiveDecoderBlock(320) + 1x1 projections on the cross-attended frames.

@@ -76,6 +76,26 @@ def main():
         with torch.no_grad():
             got = vp.snake_block(sd_old, xs[0][None], s[:1], k, dil)[0]
         _pin(f"snake.k{k}.legacy_keys", got, out[f"snake.k{k}.0"])
+    # ---------------------------------------------------------------- conv-DFT STFT module (stft.py:6-195)
+    from stylish_tts.train.models.stft import STFT
+    for n_fft, hop, win, lengths, seed in vc.STFT_GOLDEN:
+        ref = STFT(filter_length=n_fft, hop_length=hop, win_length=win).eval()
+        for b, x in enumerate(vc.wave_case(lengths, seed)):
+            with torch.no_grad():
+                mag, cx, cy = ref.transform(x[None])
+                wave = ref.inverse(mag, cx, cy)
+                wave_len = ref.inverse(mag, cx, cy, length=x.numel() - 7)
+            got = vp.stft_conv_transform(x[None], n_fft, hop, win)
+            tag = f"stft.{n_fft}.{hop}.{win}.{b}"
+            _pin(tag + ".mag", got[0], mag)
+            _pin(tag + ".x", got[1], cx)
+            _pin(tag + ".y", got[2], cy)
+            _pin(tag + ".inverse", vp.stft_conv_inverse(mag, cx, cy, n_fft, hop, win), wave)
+            _pin(tag + ".inverse_len", vp.stft_conv_inverse(mag, cx, cy, n_fft, hop, win, length=x.numel() - 7), wave_len)
+            out[tag + ".mag_s4"] = mag[0, ::4].contiguous()
+            out[tag + ".re_s4"] = (mag * cx)[0, ::4].contiguous()
+            out[tag + ".im_s4"] = (mag * cy)[0, ::4].contiguous()
+            out[tag + ".inverse"] = wave.reshape(-1).contiguous()
     path = os.path.join(ROOT, "tests", "golden", "variants.safetensors")
     save_file(out, path)
     print("wrote", path, {k: tuple(v.shape) for k, v in out.items()})

@@ -90,3 +90,23 @@ SNAKE_GOLDEN = [  # (channels, kernel, dilation, lengths, seed)
     (128, 7, (1, 3, 5), (150, 37), 12),
     (128, 11, (1, 3, 5), (150, 64), 13),
 ]
+
+
+def wave_case(lengths: Sequence[int], seed: int) -> List[torch.Tensor]:
+    """Speech-like test waveforms: a few decaying harmonics of a drifting f0 plus noise, |x| < 1."""
+    g = torch.Generator().manual_seed(seed)
+    out = []
+    for n in lengths:
+        t = torch.arange(n, dtype=torch.float64) / SAMP_RATE
+        f0 = 110.0 + 90.0 * float(torch.rand(1, generator=g)) + 20.0 * torch.sin(2 * math.pi * 1.7 * t)
+        ph = 2 * math.pi * torch.cumsum(f0, 0) / SAMP_RATE
+        x = sum((0.5 / h) * torch.sin(h * ph + float(torch.rand(1, generator=g))) for h in range(1, 9))
+        x = 0.4 * x + 0.02 * torch.randn(n, generator=g, dtype=torch.float64)
+        out.append(x.float().contiguous())
+    return out
+
+
+STFT_GOLDEN = [  # (filter_length, hop_length, win_length, lengths, seed); the module's defaults and the export's sizes
+    (800, 200, 800, (3000, 1234), 41),
+    (2048, 300, 1200, (6000, 2500), 42),
+]

@@ -104,3 +104,59 @@ def snake_block(sd: Dict[str, torch.Tensor], x: torch.Tensor, s: torch.Tensor, k
         if trace is not None:
             trace[f"x.{i}"] = x
     return x
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# STFT (conv1d / conv_transpose1d DFT, the ONNX-export stand-in)      train/models/stft.py:6-195
+# ----------------------------------------------------------------------------------------------------------------
+def stft_conv_weights(filter_length: int, win_length: int) -> Dict[str, torch.Tensor]:
+    """The four registered buffers of STFT.__init__ (stft.py:38-96): periodic hann window zero-padded AT THE END to
+    n_fft, forward basis window * (cos, -sin), backward basis window / n_fft * (cos, sin); built in float64 numpy and
+    cast to float32 exactly like the reference."""
+    import numpy as np
+    n_fft = filter_length
+    bins = n_fft // 2 + 1
+    window = torch.hann_window(win_length, periodic=True, dtype=torch.float32)
+    if win_length < n_fft:
+        window = F.pad(window, (0, n_fft - win_length))                            # :43-46
+    elif win_length > n_fft:
+        window = window[:n_fft]                                                   # :47-48
+    n, k = np.arange(n_fft), np.arange(bins)
+    angle = 2 * np.pi * np.outer(k, n) / n_fft                                    # :55
+    w = window.numpy()
+    fwd_real = torch.from_numpy(np.cos(angle) * w).float().unsqueeze(1)           # :56-70
+    fwd_imag = torch.from_numpy(-np.sin(angle) * w).float().unsqueeze(1)
+    angle_t = 2 * np.pi * np.outer(n, k) / n_fft                                  # :79
+    inv_w = w * (1.0 / n_fft)                                                     # :85
+    bwd_real = torch.from_numpy(np.cos(angle_t).T * inv_w).float().unsqueeze(1)   # :80-96
+    bwd_imag = torch.from_numpy(np.sin(angle_t).T * inv_w).float().unsqueeze(1)
+    return {"window": window, "fwd_real": fwd_real, "fwd_imag": fwd_imag, "bwd_real": bwd_real, "bwd_imag": bwd_imag}
+
+
+def stft_conv_transform(waveform: torch.Tensor, filter_length: int, hop_length: int, win_length: int,
+                        pad_mode: str = "replicate"):
+    """STFT.transform (stft.py:98-136): waveform [B, T] -> (magnitude, re / magnitude, im / magnitude), each
+    [B, n_fft / 2 + 1, frames]; center padding n_fft / 2 in `pad_mode`; magnitude = sqrt(re^2 + im^2 + 1e-14)."""
+    wts = stft_conv_weights(filter_length, win_length)
+    pad_len = filter_length // 2
+    x = F.pad(waveform.unsqueeze(1), (pad_len, pad_len), mode=pad_mode)            # :105-109 (pad on the 3-D view)
+    real = F.conv1d(x, wts["fwd_real"], bias=None, stride=hop_length, padding=0)
+    imag = F.conv1d(x, wts["fwd_imag"], bias=None, stride=hop_length, padding=0)
+    mag = torch.sqrt(real ** 2 + imag ** 2 + 1e-14)                               # :127
+    return mag, real / mag, imag / mag, real, imag
+
+
+def stft_conv_inverse(magnitude: torch.Tensor, x: torch.Tensor, y: torch.Tensor, filter_length: int, hop_length: int,
+                      win_length: int, length: Optional[int] = None) -> torch.Tensor:
+    """STFT.inverse (stft.py:138-186): conv_transpose1d with the windowed / n_fft-scaled basis, real minus imaginary
+    part, n_fft / 2 samples trimmed at both ends (no window-envelope normalisation, no DC / Nyquist weighting: the
+    reference calls it an approximate reconstruction, :73-77)."""
+    wts = stft_conv_weights(filter_length, win_length)
+    real_rec = F.conv_transpose1d(magnitude * x, wts["bwd_real"], bias=None, stride=hop_length)
+    imag_rec = F.conv_transpose1d(magnitude * y, wts["bwd_imag"], bias=None, stride=hop_length)
+    wave = real_rec - imag_rec                                                    # :170
+    pad_len = filter_length // 2
+    wave = wave[..., pad_len:-pad_len]                                            # :173-177
+    if length is not None:
+        wave = wave[..., :length]
+    return wave

@@ -33,6 +33,9 @@ SIGNATURES = {
     "stts_source_sinegen": (_i, [_vp, _fp, C.POINTER(_i), _i, _fp, _fp, C.POINTER(C.c_float), _i, C.c_float, C.c_float,
                                  C.c_float, C.c_float, _fp, _fp, _vp]),
     "stts_generator_block_snake": (_i, [_vp, C.c_char_p, _i, _i, C.POINTER(_i), _i, C.POINTER(_i), _fp, _fp, _fp, _vp]),
+    "stts_stft_conv_transform": (_i, [_vp, C.c_char_p, _i, _i, _i, _i, _i, C.POINTER(_i), _fp, _fp, _fp, _fp, _vp]),
+    "stts_stft_conv_inverse": (_i, [_vp, C.c_char_p, _i, _i, _i, _i, C.POINTER(_i), C.POINTER(_i), _fp, _fp, _fp, _fp,
+                                    _vp]),
     "stts_pe_towers": (_i, [_vp, _fp, _fp, _fp, _fp, _vp]),
     "stts_decoder": (_i, [_vp, _fp, _fp, _fp, _fp, _fp, _vp]),
     "stts_prior_flow": (_i, [_vp, _fp, _fp, _fp, _fp, _fp, _fp, _vp]),

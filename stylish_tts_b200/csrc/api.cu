@@ -199,6 +199,28 @@ int stts_generator_block_snake(stts_ctx* ctx, const char* module, int channels, 
   return run_snake_block(c, module, channels, kernel_size, dilation, n_seg, len, d_x, d_style, d_out, S(stream));
 }
 
+int stts_stft_conv_transform(stts_ctx* ctx, const char* module, int filter_length, int hop_length, int win_length,
+                             int pad_mode, int n_seg, const int* len, const float* d_wave, float* d_mag, float* d_x,
+                             float* d_y, void* stream) {
+  if (!ctx) return STTS_ERR_BAD_ARG;
+  Context& c = ctx->c;
+  if (!module || !len || !d_wave || !d_mag || !d_x || !d_y) return fail(c, STTS_ERR_BAD_ARG, "stts_stft_conv_transform: null pointer");
+  DeviceGuard g(c);
+  return run_stft_conv_transform(c, module, filter_length, hop_length, win_length, pad_mode, n_seg, len, d_wave, d_mag, d_x,
+                                 d_y, S(stream));
+}
+
+int stts_stft_conv_inverse(stts_ctx* ctx, const char* module, int filter_length, int hop_length, int win_length, int n_seg,
+                           const int* n_frames, const int* out_len, const float* d_mag, const float* d_x, const float* d_y,
+                           float* d_wave, void* stream) {
+  if (!ctx) return STTS_ERR_BAD_ARG;
+  Context& c = ctx->c;
+  if (!module || !n_frames || !d_wave || !d_mag || !d_x || !d_y) return fail(c, STTS_ERR_BAD_ARG, "stts_stft_conv_inverse: null pointer");
+  DeviceGuard g(c);
+  return run_stft_conv_inverse(c, module, filter_length, hop_length, win_length, n_seg, n_frames, out_len, d_mag, d_x, d_y,
+                               d_wave, S(stream));
+}
+
 int stts_pe_towers(stts_ctx* ctx, const float* d_x, const float* d_style, float* d_pitch, float* d_energy,
                    void* stream) {
   if (!ctx || !d_style || !d_pitch || !d_energy) return STTS_ERR_BAD_ARG;

@@ -164,6 +164,11 @@ int run_sinegen(Context& c, const float* d_f0, const int* h_len, int n_seg, cons
                 float voiced_threshold, float* d_out, float* d_phase, cudaStream_t st);
 int run_snake_block(Context& c, const std::string& module, int channels, int k, const int* dil, int n_seg,
                     const int* h_len, const float* d_x, const float* d_style, float* d_out, cudaStream_t st);
+int run_stft_conv_transform(Context& c, const std::string& module, int n_fft, int hop, int win, int pad_mode, int n_seg,
+                            const int* h_len, const float* d_wave, float* d_mag, float* d_x, float* d_y, cudaStream_t st);
+int run_stft_conv_inverse(Context& c, const std::string& module, int n_fft, int hop, int win, int n_seg,
+                          const int* h_frames, const int* h_out_len, const float* d_mag, const float* d_x, const float* d_y,
+                          float* d_wave, cudaStream_t st);
 void free_variant_work(Context& c);
 
 int fail(Context& c, int code, const std::string& msg);

@@ -7,6 +7,8 @@
 // (row step `dil` between taps); its zero guard after every utterance is 32 rows (>= the widest padding, k 11 d 5 = 25).
 #include <algorithm>
 #include <cstring>
+#include <map>
+#include <string>
 #include <vector>
 
 #include "engine.h"
@@ -27,12 +29,16 @@ struct VariantWork {
   // ---- sinegen
   char* sg = nullptr;
   size_t sg_bytes = 0;
+  // ---- conv-DFT STFT modules by name
+  std::map<std::string, struct StftConvPlan*> stft;
 };
+void free_stft_plans(VariantWork& w);
 
 void free_variant_work(Context& c) {
   if (c.vwork == nullptr) return;
   if (c.vwork->arena) cudaFree(c.vwork->arena);
   if (c.vwork->sg) cudaFree(c.vwork->sg);
+  free_stft_plans(*c.vwork);
   delete c.vwork;
   c.vwork = nullptr;
 }
@@ -419,6 +425,340 @@ int run_sinegen(Context& c, const float* d_f0, const int* h_len, int n_seg, cons
   launch_k(sinegen_pass_kernel<2>, nch, kSgThreads, 0, st, d_f0, d_cu, d_cs, d_ct, d_rand_ini, P1, P2, T, p, d_noise, d_out,
                                                       d_phase);
   STTS_CK(cudaGetLastError());
+  return 0;
+}
+
+// =====================================================================================================================
+// STFT / iSTFT as convolutions with a windowed DFT basis (train/models/stft.py:6-195, the module swapped in for the
+// ONNX export, convert_to_onnx.py:31-36): SURVEY.md section 8 (f) rank 4.
+//
+//   transform: center padding n_fft / 2 (replicate | constant), frames = conv1d(stride hop) with the basis
+//              window[n] * (cos, -sin)(2 pi k n / n_fft); returns |X| = sqrt(re^2 + im^2 + 1e-14), re / |X|, im / |X|
+//   inverse:   conv_transpose1d(stride hop) with window[n] / n_fft * (cos, sin), real minus imaginary part, n_fft / 2
+//              samples trimmed at both ends (the reference's "approximate" inverse: no envelope normalisation)
+//
+// The window is zero beyond win_length, so a frame is taps = ceil(win / hop) consecutive rows of `hop` samples: both
+// directions are conv-as-GEMMs of the live path on a private packed layout (forward: K = taps x hop, N = 2 bins with
+// (re, im) interleaved; inverse: K = 2 bins, N = taps x hop followed by an overlap-add gather).  Basis matrices are
+// the module's own registered buffers (weight_forward_real / _imag, weight_backward_real / _imag), loaded with
+// stts_load_tensor like any other state_dict entry.  fp32-grade GEMMs only (CUDA cores in fp32 mode, tf32x3 otherwise).
+struct StftConvPlan {
+  int n_fft = 0, hop = 0, win = 0, bins = 0, taps = 0, hop_pad = 0, ld_spec = 0, ld_y = 0;
+  PackedGemm fwd, bwd;
+  bool packed = false;
+  // layout + workspace for (lengths)
+  Layout L;
+  std::vector<int> sig;
+  char* arena = nullptr;
+  size_t arena_bytes = 0;
+  Act XR, SPEC, YF;
+  long long* d_off_w = nullptr;      // dense sample offset of every utterance (waveform side)
+  long long* d_off_s = nullptr;      // dense element offset of every utterance's [bins, frames] block
+  int* d_len_w = nullptr;            // samples per utterance (waveform side)
+};
+
+namespace {
+
+// rows of `hop` samples of the center-padded waveform: XR[row(seg, r), c] = padded[r * hop + c]
+__global__ void __launch_bounds__(256) stftc_rowify_kernel(const float* __restrict__ wave, const long long* __restrict__ off,
+                                                           const int* __restrict__ len, RowMap map, int hop, int pad_len,
+                                                           int extra_rows, int pad_mode, float* __restrict__ xr, int ld) {
+  pdl_enter();
+  const int seg = blockIdx.y;
+  const int T = len[seg];
+  const int rows = map.seg_len[seg] + extra_rows;
+  const float* w = wave + off[seg];
+  const size_t r0 = map.seg_start[seg];
+  const int total = rows * hop;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int r = i / hop, c = i - r * hop;
+    int s = i - pad_len;                       // sample index in the unpadded waveform
+    float v = 0.f;
+    if (s >= -pad_len && s < T + pad_len) {
+      if (s < 0) v = pad_mode == 0 ? w[0] : 0.f;
+      else if (s >= T) v = pad_mode == 0 ? w[T - 1] : 0.f;
+      else v = w[s];
+    }
+    xr[(r0 + r) * ld + c] = v;
+  }
+}
+
+// (re, im) interleaved rows -> dense [bins, frames] magnitude, re / mag, im / mag      stft.py:127-136
+__global__ void __launch_bounds__(256) stftc_finish_kernel(const float* __restrict__ spec, int ld, RowMap map, int bins,
+                                                           const long long* __restrict__ off, float* __restrict__ mag,
+                                                           float* __restrict__ xo, float* __restrict__ yo) {
+  pdl_enter();
+  __shared__ float2 t[32][33];
+  const int tile = blockIdx.x;
+  const int seg = map.tile_seg[tile];
+  if (seg < 0) return;
+  const int nvalid = map.tile_nvalid[tile];
+  const int f_base = tile * 128 - map.seg_start[seg];
+  const int frames = map.seg_len[seg];
+  const long long o = off[seg];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int k0 = blockIdx.y * 32; k0 < bins; k0 += gridDim.y * 32) {
+    for (int r0 = 0; r0 < nvalid; r0 += 32) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int lr = r0 + ty + 8 * q, k = k0 + tx;
+        float2 v = make_float2(0.f, 0.f);
+        if (lr < nvalid && k < bins) v = *reinterpret_cast<const float2*>(spec + (size_t)(tile * 128 + lr) * ld + 2 * k);
+        t[ty + 8 * q][tx] = v;
+      }
+      __syncthreads();
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int k = k0 + ty + 8 * q, lr = r0 + tx;
+        if (k < bins && lr < nvalid) {
+          const float2 v = t[tx][ty + 8 * q];
+          const float m = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(v.x, v.x), __fmul_rn(v.y, v.y)), 1e-14f));
+          const size_t d = (size_t)o + (size_t)k * frames + f_base + lr;
+          mag[d] = m;
+          xo[d] = __fdiv_rn(v.x, m);
+          yo[d] = __fdiv_rn(v.y, m);
+        }
+      }
+      __syncthreads();
+    }
+  }
+}
+
+// dense [bins, frames] (mag, x, y) -> rows [frames, 2 bins]: (mag x, mag y) interleaved        stft.py:147-148
+__global__ void __launch_bounds__(256) stftc_prep_kernel(const float* __restrict__ mag, const float* __restrict__ xi,
+                                                         const float* __restrict__ yi, const long long* __restrict__ off,
+                                                         RowMap map, int bins, float* __restrict__ a, int ld) {
+  pdl_enter();
+  __shared__ float2 t[32][33];
+  const int tile = blockIdx.x;
+  const int seg = map.tile_seg[tile];
+  if (seg < 0) return;
+  const int nvalid = map.tile_nvalid[tile];
+  const int f_base = tile * 128 - map.seg_start[seg];
+  const int frames = map.seg_len[seg];
+  const long long o = off[seg];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int k0 = blockIdx.y * 32; k0 < bins; k0 += gridDim.y * 32) {
+    for (int r0 = 0; r0 < nvalid; r0 += 32) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int k = k0 + ty + 8 * q, lr = r0 + tx;
+        float2 v = make_float2(0.f, 0.f);
+        if (k < bins && lr < nvalid) {
+          const size_t d = (size_t)o + (size_t)k * frames + f_base + lr;
+          const float m = mag[d];
+          v = make_float2(__fmul_rn(m, xi[d]), __fmul_rn(m, yi[d]));
+        }
+        t[ty + 8 * q][tx] = v;
+      }
+      __syncthreads();
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int lr = r0 + ty + 8 * q, k = k0 + tx;
+        if (lr < nvalid && k < bins)
+          *reinterpret_cast<float2*>(a + (size_t)(tile * 128 + lr) * ld + 2 * k) = t[tx][ty + 8 * q];
+      }
+      __syncthreads();
+    }
+  }
+}
+
+// overlap-add of the per-frame segments (conv_transpose1d, stride hop) and the trim of pad_len samples    stft.py:155-181
+__global__ void __launch_bounds__(256) stftc_ola_kernel(const float* __restrict__ yf, int ld, RowMap map, int hop, int taps,
+                                                        int pad_len, const long long* __restrict__ off,
+                                                        const int* __restrict__ len, float* __restrict__ wave) {
+  pdl_enter();
+  const int seg = blockIdx.y;
+  const int T = len[seg];
+  const int frames = map.seg_len[seg];
+  const size_t r0 = map.seg_start[seg];
+  float* w = wave + off[seg];
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < T; i += gridDim.x * blockDim.x) {
+    const int s = i + pad_len;
+    const int tq = s / hop, c = s - tq * hop;
+    float acc = 0.f;
+    for (int j = taps - 1; j >= 0; --j) {       // ascending frame index, like the scatter order of conv_transpose1d
+      const int t = tq - j;
+      if (t >= 0 && t < frames) acc += yf[(r0 + t) * ld + j * hop + c];
+    }
+    w[i] = acc;
+  }
+}
+
+StftConvPlan& stft_plan(Context& c, const std::string& module) {
+  VariantWork& w = work(c);
+  auto it = w.stft.find(module);
+  if (it == w.stft.end()) it = w.stft.emplace(module, new StftConvPlan()).first;
+  return *it->second;
+}
+
+int pack_stft_conv(Context& c, StftConvPlan& pl, const std::string& module, int n_fft, int hop, int win) {
+  if (pl.packed && pl.n_fft == n_fft && pl.hop == hop && pl.win == win) return 0;
+  if (n_fft < 2 || (n_fft & 1) || hop < 1 || win < 1) return fail(c, -2, "stft conv: filter_length must be even, hop / win positive");
+  const int weff = std::min(win, n_fft), taps = (weff + hop - 1) / hop, bins = n_fft / 2 + 1;
+  if (taps - 1 > kSnakeGuard) return fail(c, -2, "stft conv: ceil(win_length / hop_length) must be <= 33");
+  const char* keys[4] = {"weight_forward_real", "weight_forward_imag", "weight_backward_real", "weight_backward_imag"};
+  const HostTensor* t[4];
+  for (int i = 0; i < 4; ++i) {
+    auto it = c.tensors.find(module + "/" + keys[i]);
+    if (it == c.tensors.end()) return fail(c, -3, "missing weight " + module + "/" + keys[i]);
+    t[i] = &it->second;
+    if (t[i]->numel() != (int64_t)bins * n_fft) return fail(c, -2, std::string("stft conv: ") + keys[i] + " is not [n_fft / 2 + 1, 1, n_fft]");
+  }
+  if (pl.packed) { free_pack(pl.fwd); free_pack(pl.bwd); pl.packed = false; }
+  const int span = taps * hop;
+  {  // forward: conv weight [2 bins, hop, taps], w[2k + part][c][j] = basis_part[k][j hop + c]
+    std::vector<float> w((size_t)2 * bins * hop * taps, 0.f);
+    for (int k = 0; k < bins; ++k)
+      for (int part = 0; part < 2; ++part) {
+        const float* b = t[part]->data.data() + (size_t)k * n_fft;
+        float* d = w.data() + (size_t)(2 * k + part) * hop * taps;
+        for (int n = 0; n < span && n < n_fft; ++n) d[(size_t)(n % hop) * taps + n / hop] = b[n];
+      }
+    pl.fwd = pack_from_conv_weight(c, w.data(), nullptr, 2 * bins, hop, taps, 0);
+    pl.fwd.name = module + ".fwd";
+  }
+  {  // inverse: 1x1 "conv" [span, 2 bins, 1], w[n][2k] = bwd_real[k][n], w[n][2k + 1] = -bwd_imag[k][n]
+    std::vector<float> w((size_t)span * 2 * bins, 0.f);
+    for (int n = 0; n < span && n < n_fft; ++n)
+      for (int k = 0; k < bins; ++k) {
+        w[(size_t)n * 2 * bins + 2 * k] = t[2]->data[(size_t)k * n_fft + n];
+        w[(size_t)n * 2 * bins + 2 * k + 1] = -t[3]->data[(size_t)k * n_fft + n];
+      }
+    pl.bwd = pack_from_conv_weight(c, w.data(), nullptr, span, 2 * bins, 1, 0);
+    pl.bwd.name = module + ".bwd";
+  }
+  if (cudaDeviceSynchronize() != cudaSuccess) return fail(c, -5, "cuda error while uploading the STFT basis");
+  pl.n_fft = n_fft; pl.hop = hop; pl.win = win; pl.bins = bins; pl.taps = taps;
+  pl.hop_pad = (hop + 63) / 64 * 64;
+  pl.ld_spec = (2 * bins + 63) / 64 * 64;
+  pl.ld_y = (span + 63) / 64 * 64;
+  pl.packed = true;
+  pl.sig.clear();
+  // the window beyond taps * hop samples must be zero, or the frame would not fit its rows
+  for (int part = 0; part < 2; ++part)
+    for (int k = 0; k < bins; k += bins - 1)
+      for (int n = span; n < n_fft; ++n)
+        if (t[part]->data[(size_t)k * n_fft + n] != 0.f) return fail(c, -2, "stft conv: basis is not zero beyond win_length");
+  return 0;
+}
+
+// layout (rows = frames per utterance) + workspace; len_w = samples per utterance on the waveform side
+int plan_stft_conv(Context& c, StftConvPlan& pl, int n_seg, const int* frames, const int* len_w) {
+  std::vector<int> sig = {n_seg};
+  sig.insert(sig.end(), frames, frames + n_seg);
+  sig.insert(sig.end(), len_w, len_w + n_seg);
+  if (sig == pl.sig && pl.arena != nullptr) return 0;
+  cudaError_t e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) return cuda_fail(c, e, "stft conv: sync before re-planning");
+  tc_map_cache_clear();
+  build_layout(pl.L, n_seg, frames, kSnakeGuard);
+  Layout& L = pl.L;
+  size_t used = 0;
+  auto take = [&](size_t bytes) { const size_t o = used; used += (bytes + 255) / 256 * 256; return o; };
+  const size_t o_xr = take((size_t)L.R * pl.hop_pad * 4), o_sp = take((size_t)L.R * pl.ld_spec * 4);
+  const size_t o_yf = take((size_t)L.R * pl.ld_y * 4);
+  const size_t o_ts = take((size_t)L.n_tiles * 4), o_tn = take((size_t)L.n_tiles * 4), o_ss = take((size_t)n_seg * 4);
+  const size_t o_sl = take((size_t)n_seg * 4), o_ow = take((size_t)n_seg * 8), o_os = take((size_t)n_seg * 8);
+  const size_t o_lw = take((size_t)n_seg * 4);
+  if (used > pl.arena_bytes) {
+    if (pl.arena) cudaFree(pl.arena);
+    pl.arena = nullptr; pl.arena_bytes = 0; pl.sig.clear();
+    e = cudaMalloc(&pl.arena, used);
+    if (e != cudaSuccess) return cuda_fail(c, e, "stft conv: workspace cudaMalloc");
+    pl.arena_bytes = used;
+  }
+  e = cudaMemset(pl.arena, 0, used);
+  if (e != cudaSuccess) return cuda_fail(c, e, "stft conv: workspace memset");
+  auto act = [&](size_t of, int ld) { Act a; a.f = reinterpret_cast<float*>(pl.arena + of); a.ld = ld; a.rows = L.R; return a; };
+  pl.XR = act(o_xr, pl.hop_pad); pl.SPEC = act(o_sp, pl.ld_spec); pl.YF = act(o_yf, pl.ld_y);
+  L.d_tile_seg = reinterpret_cast<int*>(pl.arena + o_ts);
+  L.d_tile_nvalid = reinterpret_cast<int*>(pl.arena + o_tn);
+  L.d_seg_start = reinterpret_cast<int*>(pl.arena + o_ss);
+  L.d_seg_len = reinterpret_cast<int*>(pl.arena + o_sl);
+  pl.d_off_w = reinterpret_cast<long long*>(pl.arena + o_ow);
+  pl.d_off_s = reinterpret_cast<long long*>(pl.arena + o_os);
+  pl.d_len_w = reinterpret_cast<int*>(pl.arena + o_lw);
+  std::vector<long long> ow(n_seg), os(n_seg);
+  long long aw = 0, as = 0;
+  for (int b = 0; b < n_seg; ++b) { ow[b] = aw; os[b] = as; aw += len_w[b]; as += (long long)pl.bins * frames[b]; }
+  cudaMemcpy(L.d_tile_seg, L.tile_seg.data(), (size_t)L.n_tiles * 4, cudaMemcpyHostToDevice);
+  cudaMemcpy(L.d_tile_nvalid, L.tile_nvalid.data(), (size_t)L.n_tiles * 4, cudaMemcpyHostToDevice);
+  cudaMemcpy(L.d_seg_start, L.seg_start.data(), (size_t)n_seg * 4, cudaMemcpyHostToDevice);
+  cudaMemcpy(L.d_seg_len, L.seg_len.data(), (size_t)n_seg * 4, cudaMemcpyHostToDevice);
+  cudaMemcpy(pl.d_off_w, ow.data(), (size_t)n_seg * 8, cudaMemcpyHostToDevice);
+  cudaMemcpy(pl.d_off_s, os.data(), (size_t)n_seg * 8, cudaMemcpyHostToDevice);
+  cudaMemcpy(pl.d_len_w, len_w, (size_t)n_seg * 4, cudaMemcpyHostToDevice);
+  e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) return cuda_fail(c, e, "stft conv: layout upload");
+  pl.sig = sig;
+  return 0;
+}
+
+Epi plain_epi(const Act& dst) {
+  Epi e;
+  std::memset(&e, 0, sizeof(e));
+  e.kind = EPI_BIAS; e.out = dst.f; e.ldo = dst.ld; e.scale = 1.f;
+  return e;
+}
+
+}  // namespace
+
+void free_stft_plans(VariantWork& w) {
+  for (auto& kv : w.stft) {
+    StftConvPlan* pl = kv.second;
+    if (pl->packed) { free_pack(pl->fwd); free_pack(pl->bwd); }
+    if (pl->arena) cudaFree(pl->arena);
+    delete pl;
+  }
+  w.stft.clear();
+}
+
+// STFT.transform (stft.py:98-136).  d_wave: utterances back to back, len [n_seg] samples (host).  Outputs: per
+// utterance a dense [bins, frames_b] block, frames_b = len_b / hop + 1, blocks back to back.
+int run_stft_conv_transform(Context& c, const std::string& module, int n_fft, int hop, int win, int pad_mode, int n_seg,
+                            const int* h_len, const float* d_wave, float* d_mag, float* d_x, float* d_y, cudaStream_t st) {
+  if (n_seg <= 0 || n_seg > 1024) return fail(c, -1, "stft conv: n_seg must be in [1, 1024]");
+  if (pad_mode != 0 && pad_mode != 1) return fail(c, -2, "stft conv: pad_mode is 0 (replicate) or 1 (constant)");
+  StftConvPlan& pl = stft_plan(c, module);
+  STTS_RET(pack_stft_conv(c, pl, module, n_fft, hop, win));
+  std::vector<int> frames(n_seg);
+  for (int b = 0; b < n_seg; ++b) {
+    if (h_len[b] <= 0) return fail(c, -2, "stft conv: utterance length must be > 0");
+    frames[b] = h_len[b] / hop + 1;                       // (T + 2 (n_fft / 2) - n_fft) / hop + 1
+  }
+  STTS_RET(plan_stft_conv(c, pl, n_seg, frames.data(), h_len));
+  const RowMap map = pl.L.map();
+  STTS_CK(launch_k(stftc_rowify_kernel, dim3(64, n_seg), 256, 0, st, d_wave, pl.d_off_w, pl.d_len_w, map, hop, n_fft / 2,
+                   pl.taps - 1, pad_mode, pl.XR.f, pl.XR.ld));
+  STTS_RET(run_gemm(c, pl.fwd, GC_BODY, &pl.XR, 0, nullptr, 0, plain_epi(pl.SPEC), map, st, c.precision == 0 ? 0 : 2));
+  STTS_CK(launch_k(stftc_finish_kernel, dim3(map.n_tiles, 8), 256, 0, st, pl.SPEC.f, pl.SPEC.ld, map, pl.bins, pl.d_off_s,
+                   d_mag, d_x, d_y));
+  return 0;
+}
+
+// STFT.inverse (stft.py:138-186).  Inputs: dense [bins, frames_b] blocks; h_out_len[b] <= (frames_b - 1) * hop samples
+// are written per utterance (NULL: all of them), utterances back to back.
+int run_stft_conv_inverse(Context& c, const std::string& module, int n_fft, int hop, int win, int n_seg,
+                          const int* h_frames, const int* h_out_len, const float* d_mag, const float* d_x, const float* d_y,
+                          float* d_wave, cudaStream_t st) {
+  if (n_seg <= 0 || n_seg > 1024) return fail(c, -1, "stft conv: n_seg must be in [1, 1024]");
+  StftConvPlan& pl = stft_plan(c, module);
+  STTS_RET(pack_stft_conv(c, pl, module, n_fft, hop, win));
+  std::vector<int> len(n_seg);
+  for (int b = 0; b < n_seg; ++b) {
+    if (h_frames[b] <= 0) return fail(c, -2, "stft conv: frame count must be > 0");
+    const int full = (h_frames[b] - 1) * hop;             // (frames - 1) hop + n_fft - 2 (n_fft / 2)
+    len[b] = h_out_len != nullptr ? h_out_len[b] : full;
+    if (len[b] < 0 || len[b] > full) return fail(c, -2, "stft conv: requested length exceeds (frames - 1) * hop");
+  }
+  STTS_RET(plan_stft_conv(c, pl, n_seg, h_frames, len.data()));
+  const RowMap map = pl.L.map();
+  STTS_CK(launch_k(stftc_prep_kernel, dim3(map.n_tiles, 8), 256, 0, st, d_mag, d_x, d_y, pl.d_off_s, map, pl.bins, pl.SPEC.f,
+                   pl.SPEC.ld));
+  STTS_RET(run_gemm(c, pl.bwd, GC_BODY, &pl.SPEC, 0, nullptr, 0, plain_epi(pl.YF), map, st, c.precision == 0 ? 0 : 2));
+  STTS_CK(launch_k(stftc_ola_kernel, dim3(64, n_seg), 256, 0, st, pl.YF.f, pl.YF.ld, map, hop, pl.taps, n_fft / 2, pl.d_off_w,
+                   pl.d_len_w, d_wave));
   return 0;
 }
 

@@ -245,6 +245,39 @@ class Engine:
                 (C.c_int * len(lens))(*lens), _ptr(x), _ptr(style), _ptr(out), self._stream()))
         return out
 
+    def stft_conv_transform(self, module: str, n_fft: int, hop: int, win: int, wave: torch.Tensor,
+                            lengths: Sequence[int], pad_mode: str = "replicate"):
+        """STFT.transform (train/models/stft.py:98-136) on a ragged batch; returns (mag, x, y) flat, per utterance a
+        dense [n_fft // 2 + 1, len // hop + 1] block."""
+        lens = [int(v) for v in lengths]
+        if wave.numel() != sum(lens):
+            raise ValueError("stft_conv_transform: waveform does not match the lengths")
+        if pad_mode not in ("replicate", "constant"):
+            raise ValueError("pad_mode must be 'replicate' or 'constant'")
+        bins = n_fft // 2 + 1
+        tot = sum(bins * (n // hop + 1) for n in lens)
+        mag, x, y = (torch.empty(tot, dtype=torch.float32, device=self.device) for _ in range(3))
+        with torch.cuda.device(self.device):
+            self._check(self.lib.stts_stft_conv_transform(
+                self.h, module.encode(), n_fft, hop, win, 0 if pad_mode == "replicate" else 1, len(lens),
+                (C.c_int * len(lens))(*lens), _ptr(wave), _ptr(mag), _ptr(x), _ptr(y), self._stream()))
+        return mag, x, y
+
+    def stft_conv_inverse(self, module: str, n_fft: int, hop: int, win: int, mag: torch.Tensor, x: torch.Tensor,
+                          y: torch.Tensor, frames: Sequence[int], out_len: Optional[Sequence[int]] = None):
+        """STFT.inverse (train/models/stft.py:138-186): flat [bins, frames_b] blocks in, waveforms back to back out."""
+        fr = [int(v) for v in frames]
+        bins = n_fft // 2 + 1
+        if not (mag.numel() == x.numel() == y.numel() == bins * sum(fr)):
+            raise ValueError("stft_conv_inverse: inputs do not match the frame counts")
+        ol = [int(v) for v in out_len] if out_len is not None else [(f - 1) * hop for f in fr]
+        wave = torch.empty(max(sum(ol), 1), dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            self._check(self.lib.stts_stft_conv_inverse(
+                self.h, module.encode(), n_fft, hop, win, len(fr), (C.c_int * len(fr))(*fr), (C.c_int * len(fr))(*ol),
+                _ptr(mag), _ptr(x), _ptr(y), _ptr(wave), self._stream()))
+        return wave[: sum(ol)], ol
+
     # ------------------------------------------------------------------ stages (dense tensors, see header)
     def pe_towers(self, x: torch.Tensor, style: torch.Tensor):
         tot = sum(self.len_f)

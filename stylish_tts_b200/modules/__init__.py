@@ -2,9 +2,9 @@
 from .frame_rate import (AdaptiveDecoderBlock, Decoder, DecoderPrediction, DurationProcessor, ExportModel, Generator,
                          PitchEnergyPredictor, PriorEncoder, ResidualCouplingBlock, SpeechPredictor, build_model)
 from .token_rate import DurationPredictor, ProsodyEncoder, TextEncoder, TextStyleEncoder
-from .variants import AdaptiveGeneratorBlock, SineGenerator
+from .variants import STFT, AdaptiveGeneratorBlock, SineGenerator
 
 __all__ = ["AdaptiveDecoderBlock", "Decoder", "DecoderPrediction", "DurationProcessor", "ExportModel", "Generator",
            "PitchEnergyPredictor", "PriorEncoder", "ResidualCouplingBlock", "SpeechPredictor", "build_model",
            "DurationPredictor", "ProsodyEncoder", "TextEncoder", "TextStyleEncoder", "AdaptiveGeneratorBlock",
-           "SineGenerator"]
+           "SineGenerator", "STFT"]

@@ -132,3 +132,81 @@ class AdaptiveGeneratorBlock(nn.Module):
 
     def forward(self, x: torch.Tensor, s: torch.Tensor):
         return torch.stack(self.forward_ragged([x[i] for i in range(x.shape[0])], s))
+
+
+class STFT(nn.Module):
+    """train/models/stft.py:6-195 -- STFT / iSTFT as conv1d / conv_transpose1d with a windowed DFT basis (the module the
+    reference swaps in for its ONNX export).  Same constructor, the same five registered buffers (built the same way:
+    float64 numpy, cast to float32), ``transform(waveform [B, T]) -> (magnitude, x, y)`` each [B, bins, frames] and
+    ``inverse(magnitude, x, y, length=None) -> [B, 1, T]``; ``*_ragged`` take lists of utterances."""
+
+    def __init__(self, filter_length=800, hop_length=200, win_length=800, window="hann", center=True,
+                 pad_mode="replicate"):
+        super().__init__()
+        import numpy as np
+        import torch.nn.functional as F
+        if window != "hann" or not center:
+            raise NotImplementedError("the kernels implement the hann window with center=True (the module's defaults)")
+        self.filter_length, self.hop_length, self.win_length = filter_length, hop_length, win_length
+        self.n_fft, self.center, self.pad_mode = filter_length, center, pad_mode
+        self.freq_bins = self.n_fft // 2 + 1
+        win = torch.hann_window(win_length, periodic=True, dtype=torch.float32)
+        if win_length < self.n_fft:
+            win = F.pad(win, (0, self.n_fft - win_length))
+        elif win_length > self.n_fft:
+            win = win[: self.n_fft]
+        self.register_buffer("window", win)
+        n, k = np.arange(self.n_fft), np.arange(self.freq_bins)
+        ang = 2 * np.pi * np.outer(k, n) / self.n_fft
+        w = win.numpy()
+        self.register_buffer("weight_forward_real", torch.from_numpy(np.cos(ang) * w).float().unsqueeze(1))
+        self.register_buffer("weight_forward_imag", torch.from_numpy(-np.sin(ang) * w).float().unsqueeze(1))
+        ang_t = 2 * np.pi * np.outer(n, k) / self.n_fft
+        inv_w = w * (1.0 / self.n_fft)
+        self.register_buffer("weight_backward_real", torch.from_numpy(np.cos(ang_t).T * inv_w).float().unsqueeze(1))
+        self.register_buffer("weight_backward_imag", torch.from_numpy(np.sin(ang_t).T * inv_w).float().unsqueeze(1))
+        object.__setattr__(self, "_loaded", None)
+        object.__setattr__(self, "_name", f"stft_conv_{next(_ids)}")
+
+    def load_state_dict(self, state_dict, strict: bool = True, assign: bool = False):
+        object.__setattr__(self, "_loaded", None)
+        return super().load_state_dict(state_dict, strict=strict, assign=assign)
+
+    def _engine(self) -> Engine:
+        eng = _engine_for(self.window.device)
+        if self._loaded is not eng:
+            eng.load_state(self._name, {k: v for k, v in self.state_dict().items() if k.startswith("weight_")})
+            object.__setattr__(self, "_loaded", eng)
+        return eng
+
+    def transform_ragged(self, waves: Sequence[torch.Tensor]):
+        eng = self._engine()
+        lens = [int(w.numel()) for w in waves]
+        flat = torch.cat([w.detach().to(eng.device, torch.float32).reshape(-1) for w in waves])
+        mag, x, y = eng.stft_conv_transform(self._name, self.n_fft, self.hop_length, self.win_length, flat, lens,
+                                            self.pad_mode)
+        sizes = [self.freq_bins * (n // self.hop_length + 1) for n in lens]
+        shape = [(self.freq_bins, n // self.hop_length + 1) for n in lens]
+        return tuple([p.view(sh) for p, sh in zip(t.split(sizes), shape)] for t in (mag, x, y))
+
+    def transform(self, waveform: torch.Tensor):
+        mag, x, y = self.transform_ragged([waveform[i] for i in range(waveform.shape[0])])
+        return torch.stack(mag), torch.stack(x), torch.stack(y)
+
+    def inverse_ragged(self, magnitude: Sequence[torch.Tensor], x: Sequence[torch.Tensor], y: Sequence[torch.Tensor],
+                       length: Optional[Sequence[int]] = None):
+        eng = self._engine()
+        frames = [int(m.shape[1]) for m in magnitude]
+        cat = lambda ts: torch.cat([t.detach().to(eng.device, torch.float32).contiguous().view(-1) for t in ts])
+        ol = None
+        if length is not None:
+            ol = [min(int(n), (f - 1) * self.hop_length) for n, f in zip(length, frames)]
+        wave, ol = eng.stft_conv_inverse(self._name, self.n_fft, self.hop_length, self.win_length, cat(magnitude), cat(x),
+                                         cat(y), frames, ol)
+        return list(wave.split(ol))
+
+    def inverse(self, magnitude: torch.Tensor, x: torch.Tensor, y: torch.Tensor, length=None):
+        b = magnitude.shape[0]
+        outs = self.inverse_ragged([magnitude[i] for i in range(b)], [x[i] for i in range(b)], [y[i] for i in range(b)],
+                                   None if length is None else [length] * b)
+        return torch.stack(outs).unsqueeze(1)

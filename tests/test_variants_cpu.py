@@ -70,3 +70,31 @@ def test_mirror_modules_have_the_reference_state_dict_keys():
     assert list(sg.state_dict().keys()) == ["merge.0.weight"] and sg.merge[0].weight.shape == (1, 9)
     with pytest.raises(RuntimeError):                               # no CPU fallback
         blk(torch.zeros(1, 128, 8), torch.zeros(1, 64))
+
+
+def test_stft_conv_port_reproduces_the_reference_goldens_bit_exactly():
+    g = gold("variants")
+    for n_fft, hop, win, lengths, seed in vc.STFT_GOLDEN:
+        for b, x in enumerate(vc.wave_case(lengths, seed)):
+            mag, cx, cy, re, im = vp.stft_conv_transform(x[None], n_fft, hop, win)
+            tag = f"stft.{n_fft}.{hop}.{win}.{b}"
+            assert mag.shape == (1, n_fft // 2 + 1, x.numel() // hop + 1)
+            assert torch.equal(mag[0, ::4], g[tag + ".mag_s4"])
+            assert torch.equal((mag * cx)[0, ::4], g[tag + ".re_s4"])
+            assert torch.equal((mag * cy)[0, ::4], g[tag + ".im_s4"])
+            wave = vp.stft_conv_inverse(mag, cx, cy, n_fft, hop, win)
+            assert torch.equal(wave.reshape(-1), g[tag + ".inverse"])
+            assert wave.shape[-1] == (mag.shape[2] - 1) * hop
+
+
+def test_stft_mirror_module_has_the_reference_buffers():
+    from stylish_tts_b200.modules import STFT
+    m = STFT(filter_length=2048, hop_length=300, win_length=1200)
+    w = vp.stft_conv_weights(2048, 1200)
+    assert list(m.state_dict().keys()) == ["window", "weight_forward_real", "weight_forward_imag", "weight_backward_real",
+                                           "weight_backward_imag"]
+    for k_mod, k_port in (("window", "window"), ("weight_forward_real", "fwd_real"), ("weight_forward_imag", "fwd_imag"),
+                          ("weight_backward_real", "bwd_real"), ("weight_backward_imag", "bwd_imag")):
+        assert torch.equal(getattr(m, k_mod), w[k_port]), k_mod
+    with pytest.raises(RuntimeError):                               # no CPU fallback
+        m.transform(torch.zeros(1, 4000))

@@ -136,3 +136,55 @@ def test_snake_block_larger_ragged_batch_and_module_call_against_oracle():
     got = blk(x.to(DEV), s[:2].to(DEV))
     assert got.shape == want.shape
     assert float((got.cpu() - want).abs().max() / want.abs().max()) <= SNAKE_REL["fp32"]
+
+
+STFT_REL = {"fp32": 5e-6, "tf32x3": 2e-5}      # relative to max |reference|; measured 1e-6 / 6e-6 (the fp32-grade bar is 1e-4)
+
+
+@pytest.mark.parametrize("mode", ["fp32", "tf32x3"])
+def test_stft_conv_module_goldens_and_oracle(mode):
+    """STFT.transform / inverse (train/models/stft.py) for the module's default sizes and the export's (2048 / 300 /
+    1200): ragged batch in one call against the reference goldens (every 4th bin) and the full oracle tensors; the
+    inverse is fed the reference's own (magnitude, x, y)."""
+    from oracle import variants_port as vp
+    from stylish_tts_b200.modules import STFT
+    from stylish_tts_b200.modules.variants import variant_engine
+    g = gold("variants")
+    variant_engine(torch.device(DEV)).set_precision(mode)
+    for n_fft, hop, win, lengths, seed in vc.STFT_GOLDEN:
+        m = STFT(filter_length=n_fft, hop_length=hop, win_length=win).to(DEV)
+        waves = vc.wave_case(lengths, seed)
+        mag, cx, cy = m.transform_ragged([w.to(DEV) for w in waves])
+        ref = [vp.stft_conv_transform(w[None], n_fft, hop, win) for w in waves]
+        for b, w in enumerate(waves):
+            tag = f"stft.{n_fft}.{hop}.{win}.{b}"
+            rmag, rx, ry, rre, rim = (t[0] for t in ref[b])
+            scale = float(rmag.max())
+            assert mag[b].shape == rmag.shape
+            e_mag = float((mag[b].cpu() - rmag).abs().max()) / scale
+            e_re = float((mag[b].cpu() * cx[b].cpu() - rre).abs().max()) / scale
+            e_im = float((mag[b].cpu() * cy[b].cpu() - rim).abs().max()) / scale
+            _log(f"stft.{mode}.{tag}.rel", [e_mag, e_re, e_im])
+            assert max(e_mag, e_re, e_im) <= STFT_REL[mode], (tag, e_mag, e_re, e_im)
+            assert float((mag[b].cpu()[::4] - g[tag + ".mag_s4"]).abs().max()) / scale <= STFT_REL[mode]
+            # the unit vectors are well conditioned only where the bin carries energy
+            strong = rmag > 1e-3 * scale
+            assert float(((cx[b].cpu() - rx)[strong]).abs().max()) <= 1e-3
+            assert float(((cy[b].cpu() - ry)[strong]).abs().max()) <= 1e-3
+        outs = m.inverse_ragged([r[0][0].to(DEV) for r in ref], [r[1][0].to(DEV) for r in ref],
+                                [r[2][0].to(DEV) for r in ref])
+        for b, o in enumerate(outs):
+            want = g[f"stft.{n_fft}.{hop}.{win}.{b}.inverse"]
+            assert o.numel() == want.numel()
+            e = float((o.cpu() - want).abs().max()) / float(want.abs().max())
+            _log(f"stft.{mode}.{n_fft}.{hop}.{win}.{b}.inverse_rel", e)
+            assert e <= STFT_REL[mode] * 5, (b, e)
+        # the reference's dense call shapes, with `length`
+        x = torch.stack([waves[0][:2000], waves[0][500:2500]])
+        mg, xx, yy = m.transform(x.to(DEV))
+        assert mg.shape == (2, n_fft // 2 + 1, 2000 // hop + 1)
+        want = vp.stft_conv_inverse(*vp.stft_conv_transform(x, n_fft, hop, win)[:3], n_fft, hop, win, length=1500)
+        got = m.inverse(mg, xx, yy, length=1500)
+        assert got.shape == want.shape == (2, 1, 1500)
+        assert float((got.cpu() - want).abs().max()) / float(want.abs().max()) <= STFT_REL[mode] * 20
+    variant_engine(torch.device(DEV)).set_precision("fp32")
