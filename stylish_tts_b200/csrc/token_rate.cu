@@ -238,6 +238,7 @@ __global__ void __launch_bounds__(128) attention_kernel(const float* __restrict_
 // features of the head, half-split form, position = row index inside the utterance; text_encoder.py:
 // 89-168) so Q / K stay un-rotated in memory and the separate rotation pass disappears.
 constexpr int kAttChunk = 64;
+constexpr float kLog2e = 1.4426950408889634f;
 // rope table: tab[pos * (rd / 2) + j] = (cos, sin)(pos * 10000^(-2 j / rd)), same fp32 formula as rope_kernel
 // Stage ROWS rows x D features of a head into shared memory: dst[r][f] (or dst[f][r] when TRANSPOSE),
 // zero beyond nrows.  float4 global loads, issued in independent batches (the kernel is latency-bound:
@@ -449,10 +450,14 @@ __global__ void __launch_bounds__(128) attention_tiled_kernel(const float* __res
 // features of q and of the output accumulator in registers; keys / values stream through shared memory in chunks of
 // 64 rows (partial RoPE applied while staging, like above) and the softmax is the running-max form, so neither the
 // score matrix nor a second pass over V exists: K and V are staged once per CTA instead of once per 16 queries, and
-// the per-key work of a lane is 2 D / LPQ FMAs + one exp per 4 keys of rescaling.  fp32 throughout (accurate expf).
+// the per-key work of a lane is 2 D / LPQ FMAs + one exp2 (the rescale of the accumulators runs only when the running
+// maximum moves).  fp32 throughout; exp(x) is exp2f(x * log2 e) (2 ulp + 6e-8 |x| relative: |x| is the distance to
+// the running maximum, so the weights that matter are exact to ~1e-7) -- a handful of instructions instead of expf.
+// Folding log2 e into q instead costs parity: q * scale is exact for the text encoders (scale 2^-2) and the scores of
+// the fixture weights reach ~1e3, where one more rounding of q is an ulp of the score.
 //   band > 0: additive bias -1e4 where |key - q_tok[query]| <= band (inverted monotonic band).
 // Optional fp16 split twins of the output (operand of the following f16x3 projection GEMM).
-template <int D, int LPQ, int QPT, int NT, int KP>
+template <int D, int LPQ, int QPT, int NT, int KP, int CH>
 __global__ void __launch_bounds__(NT) attention_stream_kernel(const float* __restrict__ Q, int ldq, int qcol,
                                                               const float* __restrict__ K, int ldk, int kcol,
                                                               const float* __restrict__ V, int ldv, int vcol,
@@ -479,13 +484,13 @@ __global__ void __launch_bounds__(NT) attention_stream_kernel(const float* __res
   if (q0 >= Tq) return;
   const int nq = (Tq - q0 < QPB) ? (Tq - q0) : QPB;
   const int qrow0 = qmap.seg_start[seg] + q0, krow0 = kmap.seg_start[seg];
-  constexpr int KROWS = kAttChunk + 4 * KP;      // rows past the chunk are read (and masked) by the last key group
+  constexpr int KROWS = CH + 4 * KP;      // rows past the chunk are read (and masked) by the last key group
   float* sq = sh;                                // [QPB][D]
   float* sk = sq + QPB * D;                      // [KROWS][KLD]
   float* sv = sk + KROWS * KLD;                  // [KROWS][KLD]
   for (int i = threadIdx.x; i < 4 * KP * KLD; i += NT) {      // the pad rows must hold finite numbers (0 * p = 0)
-    sk[kAttChunk * KLD + i] = 0.f;
-    sv[kAttChunk * KLD + i] = 0.f;
+    sk[CH * KLD + i] = 0.f;
+    sv[CH * KLD + i] = 0.f;
   }
   // ---- queries: stage, rotate, scale; then every lane keeps its slices in registers
   stage_rows<D, QPB, false, NT>(Q + qcol + hd * D, ldq, qrow0, nq, sq, D);
@@ -501,16 +506,19 @@ __global__ void __launch_bounds__(NT) attention_stream_kernel(const float* __res
   for (int a = 0; a < QPT; ++a) {
     const int qi = grp * QPT + a;
 #pragma unroll
-    for (int i = 0; i < DL; ++i) { q[a][i] = sq[qi * D + part * DL + i] * scale; acc[a][i] = 0.f; }
+    for (int i = 0; i < DL; ++i) {
+      q[a][i] = sq[qi * D + part * DL + i] * scale;
+      acc[a][i] = 0.f;
+    }
     tau[a] = (band > 0) ? q_tok[q_cu[seg] + q0 + (qi < nq ? qi : 0)] : 0;
     m[a] = -3.0e38f;
     l[a] = 0.f;
   }
-  for (int c0 = 0; c0 < Tk; c0 += kAttChunk) {
-    const int nk = (Tk - c0 < kAttChunk) ? (Tk - c0) : kAttChunk;
+  for (int c0 = 0; c0 < Tk; c0 += CH) {
+    const int nk = (Tk - c0 < CH) ? (Tk - c0) : CH;
     __syncthreads();                             // previous chunk consumed
-    stage_rows<D, kAttChunk, false, NT>(K + kcol + hd * D, ldk, krow0 + c0, nk, sk, KLD);
-    stage_rows<D, kAttChunk, false, NT>(V + vcol + hd * D, ldv, krow0 + c0, nk, sv, KLD);
+    stage_rows<D, CH, false, NT>(K + kcol + hd * D, ldk, krow0 + c0, nk, sk, KLD);
+    stage_rows<D, CH, false, NT>(V + vcol + hd * D, ldv, krow0 + c0, nk, sv, KLD);
     __syncthreads();
     if (rd > 0) {
       rope_staged<NT>(sk, KLD, nk, rd, c0, tab);
@@ -548,13 +556,16 @@ __global__ void __launch_bounds__(NT) attention_stream_kernel(const float* __res
 #pragma unroll
       for (int a = 0; a < QPT; ++a) {
         const float mn = fmaxf(fmaxf(fmaxf(s[a][0], s[a][1]), fmaxf(s[a][2], s[a][3])), m[a]);
-        const float corr = expf(m[a] - mn);      // first group: exp(-3e38 - finite) = 0 (and 1 if the set saw no key yet)
+        if (mn > m[a]) {                         // the running maximum moved (rare after the first groups): rescale
+          const float corr = exp2f((m[a] - mn) * kLog2e);    // first group: exp(-3e38 - finite) = 0
+          l[a] *= corr;
 #pragma unroll
-        for (int u = 0; u < 4; ++u) p[a][u] = (jb + u * KP + kp < nk) ? expf(s[a][u] - mn) : 0.f;
-        l[a] = fmaf(l[a], corr, (p[a][0] + p[a][1]) + (p[a][2] + p[a][3]));
-        m[a] = mn;
+          for (int i = 0; i < DL; ++i) acc[a][i] *= corr;
+          m[a] = mn;
+        }
 #pragma unroll
-        for (int i = 0; i < DL; ++i) acc[a][i] *= corr;
+        for (int u = 0; u < 4; ++u) p[a][u] = (jb + u * KP + kp < nk) ? exp2f((s[a][u] - mn) * kLog2e) : 0.f;
+        l[a] += (p[a][0] + p[a][1]) + (p[a][2] + p[a][3]);
       }
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
@@ -577,7 +588,7 @@ __global__ void __launch_bounds__(NT) attention_stream_kernel(const float* __res
       float mt = m[a];
 #pragma unroll
       for (int o = LPQ; o < LPQ * KP; o <<= 1) mt = fmaxf(mt, __shfl_xor_sync(0xffffffffu, mt, o));
-      const float f = expf(m[a] - mt);           // a set without keys has m = -3e38, l = 0: f = 0 (or 1 * 0)
+      const float f = exp2f((m[a] - mt) * kLog2e);           // a set without keys has m = -3e38, l = 0: f = 0 (or 1 * 0)
       float lt = l[a] * f;
 #pragma unroll
       for (int o = LPQ; o < LPQ * KP; o <<= 1) lt += __shfl_xor_sync(0xffffffffu, lt, o);
@@ -613,22 +624,22 @@ __global__ void __launch_bounds__(NT) attention_stream_kernel(const float* __res
   }
 }
 
-template <int D, int LPQ, int QPT, int NT, int KP>
+template <int D, int LPQ, int QPT, int NT, int KP, int CH>
 cudaError_t launch_attention_stream(const float* Q, int ldq, int qcol, const float* K, int ldk, int kcol, const float* V,
                                     int ldv, int vcol, int H, float scale, int rd, const float2* tab, const RowMap& qmap,
                                     const RowMap& kmap, int max_tq, const int* q_tok, const int* q_cu, int band,
                                     float* out, int ldo, __half* outg, __half* outl, int ldh, cudaStream_t st) {
   constexpr int QPB = NT / (LPQ * KP) * QPT;
-  const size_t smem = (size_t)(QPB * D + 2 * (kAttChunk + 4 * KP) * (D + 4)) * sizeof(float);
+  const size_t smem = (size_t)(QPB * D + 2 * (CH + 4 * KP) * (D + 4)) * sizeof(float);
   static bool configured = false;
   if (smem > 48 * 1024 && !configured) {
-    cudaError_t e = cudaFuncSetAttribute(attention_stream_kernel<D, LPQ, QPT, NT, KP>,
+    cudaError_t e = cudaFuncSetAttribute(attention_stream_kernel<D, LPQ, QPT, NT, KP, CH>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     configured = true;
   }
   dim3 grid((max_tq + QPB - 1) / QPB, H, qmap.n_seg);
-  launch_k(attention_stream_kernel<D, LPQ, QPT, NT, KP>, grid, NT, smem, st, Q, ldq, qcol, K, ldk, kcol, V, ldv, vcol, scale, rd,
+  launch_k(attention_stream_kernel<D, LPQ, QPT, NT, KP, CH>, grid, NT, smem, st, Q, ldq, qcol, K, ldk, kcol, V, ldv, vcol, scale, rd,
                                                                    tab, qmap, kmap, q_tok, q_cu, band, out, ldo, outg,
                                                                    outl, ldh);
   return cudaGetLastError();
@@ -667,15 +678,17 @@ cudaError_t attention(const float* Q, int ldq, int qcol, const float* K, int ldk
   static const bool tiled = [] { const char* e = std::getenv("STTS_ATT_TILED"); return e != nullptr && e[0] == '1'; }();
   const bool twins = outg != nullptr;
   if (!tiled && (rd == 0 || rope_tab != nullptr)) {
-#define STTS_ATTS(DD, LL, QQ, NN, KK)                                                                                 \
+    // last parameter: keys staged per round trip.  The token-rate sequences are <= ~256 keys: the small heads stage
+    // them all at once (one global -> shared round trip and one barrier pair instead of four per CTA)
+#define STTS_ATTS(DD, LL, QQ, NN, KK, CC)                                                                             \
   if (D == DD)                                                                                                        \
-    return launch_attention_stream<DD, LL, QQ, NN, KK>(Q, ldq, qcol, K, ldk, kcol, V, ldv, vcol, H, scale, rd,        \
-                                                       rope_tab, qmap, kmap, max_tq, q_tok, q_cu, band, out, ldo,     \
-                                                       outg, outl, ldh, st);
-    STTS_ATTS(16, 1, 1, 128, 4)    // text encoders: 32 queries per CTA, 4 key sets per query
-    STTS_ATTS(40, 1, 2, 64, 1)     // cross attention: 128 frames per CTA
-    STTS_ATTS(96, 4, 2, 128, 1)    // duration prosody encoder: 64 queries per CTA
-    STTS_ATTS(160, 8, 2, 128, 1)    // 32 queries per CTA, 8 lanes x 20 features per query
+    return launch_attention_stream<DD, LL, QQ, NN, KK, CC>(Q, ldq, qcol, K, ldk, kcol, V, ldv, vcol, H, scale, rd,    \
+                                                           rope_tab, qmap, kmap, max_tq, q_tok, q_cu, band, out, ldo, \
+                                                           outg, outl, ldh, st);
+    STTS_ATTS(16, 1, 2, 128, 4, 64)    // text encoders: 64 queries per CTA (2 per lane group), 4 key sets per query
+    STTS_ATTS(40, 1, 2, 64, 1, 64)     // cross attention: 128 frames per CTA
+    STTS_ATTS(96, 4, 2, 128, 1, 128)   // duration prosody encoder: 64 queries per CTA
+    STTS_ATTS(160, 8, 2, 128, 1, 64)   // 32 queries per CTA, 8 lanes x 20 features per query
 #undef STTS_ATTS
   }
   if (twins) return cudaErrorInvalidValue;       // the fallback kernels do not write twins

@@ -28,14 +28,17 @@ def test_static_scratch_frame_index_equals_frame_index_twice_in_a_row():
     # outputs are the caller's, allocated up front; the entry point itself allocates nothing
     outs = [(torch.full((tot,), -1, dtype=torch.int32, device=DEV), torch.zeros(1, dtype=torch.int32, device=DEV))
             for _, _, tot in calls]
+    import gc
+    gc.collect()                                          # tensors of earlier tests must not be freed mid-measurement
     torch.cuda.synchronize()
     for k, ((dur, cu_tok, tot), (idx, status)) in enumerate(zip(calls, outs)):
         reserved, allocated = torch.cuda.memory_reserved(), torch.cuda.memory_allocated()
         free_before = torch.cuda.mem_get_info()[0]
         eng.frame_index_static(dur, cu_tok, idx, status)
         torch.cuda.synchronize()
-        assert (torch.cuda.memory_reserved(), torch.cuda.memory_allocated()) == (reserved, allocated)
-        if k > 0:                                         # first call may load the module lazily; later ones add nothing
+        # nothing allocated through torch (a decrease would only mean the garbage collector ran in between) ...
+        assert torch.cuda.memory_reserved() <= reserved and torch.cuda.memory_allocated() <= allocated
+        if k > 0:       # ... nor behind its back (the first call may load the module lazily; later ones add nothing)
             assert torch.cuda.mem_get_info()[0] >= free_before
         _, want_idx, want_status = eng.frame_index(dur, cu_tok, tot)
         assert int(status.item()) == int(want_status.item()) == 0
