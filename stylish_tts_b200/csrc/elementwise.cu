@@ -510,11 +510,36 @@ __global__ void __launch_bounds__(256) dwconv_adaln_kernel(const float* __restri
   const float2 b = *reinterpret_cast<const float2*>(bias + c);
 #pragma unroll
   for (int o = 0; o < TR; ++o) { a0[o] = b.x; a1[o] = b.y; }
+  // k >= 15: the TR + K - 1 input rows go through shared memory with 16-byte cp.async copies, all in flight at once
+  // (46 / 30 rows x 2 KB per CTA, two CTAs per SM), instead of one dependent 8-byte load per row and thread: the k = 31
+  // layer was latency-bound at 1.1 TB/s.  Small k keeps the direct loads (7 / 3 extra rows).
+  constexpr bool kSlab = K >= 15;
+  extern __shared__ __align__(16) float slab[];
+  if constexpr (kSlab) {
+    for (int idx = threadIdx.x; idx < (TR + K - 1) * (C / 4); idx += 256) {
+      const int row = idx / (C / 4), c4 = (idx - row * (C / 4)) * 4;
+      const int r = r0 - PAD + row;
+      float* d = slab + row * C + c4;
+      if (r >= 0 && r < map.R) {
+        const uint32_t da = (uint32_t)__cvta_generic_to_shared(d);
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(da), "l"(x + (size_t)r * ldx + c4) : "memory");
+      } else {
+        *reinterpret_cast<float4*>(d) = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+  }
 #pragma unroll
   for (int i = 0; i < TR + K - 1; ++i) {
     const int r = r0 - PAD + i;
     float2 v = make_float2(0.f, 0.f);
-    if (r >= 0 && r < map.R) v = *reinterpret_cast<const float2*>(x + (size_t)r * ldx + c);
+    if constexpr (kSlab) {
+      v = *reinterpret_cast<const float2*>(slab + i * C + c);
+    } else {
+      if (r >= 0 && r < map.R) v = *reinterpret_cast<const float2*>(x + (size_t)r * ldx + c);
+    }
 #pragma unroll
     for (int o = 0; o < TR; ++o) {
       const int j = i - o;
@@ -573,8 +598,20 @@ cudaError_t dwconv_adaln(const float* x, int ldx, const RowMap& map, int K, cons
                          cudaStream_t st) {
   dim3 grid(map.n_tiles, 8);
   switch (K) {
-    case 31: launch_k(dwconv_adaln_kernel<31>, grid, 256, 0, st, x, ldx, map, wt, bias, gb, ldgb, eps, y, ldy, yh, ldyh); break;
-    case 15: launch_k(dwconv_adaln_kernel<15>, grid, 256, 0, st, x, ldx, map, wt, bias, gb, ldgb, eps, y, ldy, yh, ldyh); break;
+    case 31: {
+      constexpr int smem = (16 + 30) * 512 * 4;
+      static bool done = false;
+      if (!done) { cudaFuncSetAttribute(dwconv_adaln_kernel<31>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem); done = true; }
+      launch_k(dwconv_adaln_kernel<31>, grid, 256, smem, st, x, ldx, map, wt, bias, gb, ldgb, eps, y, ldy, yh, ldyh);
+      break;
+    }
+    case 15: {
+      constexpr int smem = (16 + 14) * 512 * 4;
+      static bool done = false;
+      if (!done) { cudaFuncSetAttribute(dwconv_adaln_kernel<15>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem); done = true; }
+      launch_k(dwconv_adaln_kernel<15>, grid, 256, smem, st, x, ldx, map, wt, bias, gb, ldgb, eps, y, ldy, yh, ldyh);
+      break;
+    }
     case 7: launch_k(dwconv_adaln_kernel<7>, grid, 256, 0, st, x, ldx, map, wt, bias, gb, ldgb, eps, y, ldy, yh, ldyh); break;
     case 3: launch_k(dwconv_adaln_kernel<3>, grid, 256, 0, st, x, ldx, map, wt, bias, gb, ldgb, eps, y, ldy, yh, ldyh); break;
     default: return cudaErrorInvalidValue;
