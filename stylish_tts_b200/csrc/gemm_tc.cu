@@ -39,24 +39,45 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
-__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+// try_wait with a suspend-time hint: the hardware parks the thread until the phase completes or the hint expires,
+// instead of returning after a few dozen cycles.  Used by the MANY-thread waits (8-16 epilogue warps waiting for the
+// accumulator and, with two CTAs per SM, through the other CTA's whole main loop): without it more than half of the
+// warp instructions of the short-K GEMMs were polls competing with the working epilogue warps for issue slots
+// (persistent decoder convs -9 %, pwconv1 -6 %).  The single-thread pipeline waits of the TMA producer and the MMA
+// issuer keep the plain poll: waking from a parked wait costs a little latency, which one 5 s utterance (one CTA
+// per kernel) showed as +1.5 %.
+constexpr uint32_t kMbarSuspendHint = 0x989680u;
+template <bool PARK>
+__device__ __forceinline__ bool mbar_try_wait_t(uint64_t* bar, uint32_t parity) {
   uint32_t ok;
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-      "selp.u32 %0, 1, 0, p;\n\t}"
-      : "=r"(ok)
-      : "r"(smem_u32(bar)), "r"(parity)
-      : "memory");
+  if constexpr (PARK) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity), "r"(kMbarSuspendHint)
+        : "memory");
+  } else {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+  }
   return ok != 0;
 }
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) { return mbar_try_wait_t<false>(bar, parity); }
 // Bounded wait: a protocol bug must trap (launch error) instead of hanging the GPU box.
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int tag) {
-  if (mbar_try_wait(bar, parity)) return;
+// park: use the suspend-time hint (see above); a kernel-uniform runtime choice (STTS_MBAR_PARK, mbar_park_mode())
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int tag, bool park = false) {
+  if (park ? mbar_try_wait_t<true>(bar, parity) : mbar_try_wait_t<false>(bar, parity)) return;
   uint64_t t0;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
   for (;;) {
-    if (mbar_try_wait(bar, parity)) return;
+    if (park ? mbar_try_wait_t<true>(bar, parity) : mbar_try_wait_t<false>(bar, parity)) return;
     uint64_t t1;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
     if (t1 - t0 > 2000000000ull) break;  // 2 s
@@ -404,6 +425,7 @@ struct TcParams {
   int w_seg_rows;       // > 0: the weights are per utterance, utterance u at rows [u * w_seg_rows, ...)
   uint32_t ab_fmt;      // operand format of the MMAs: 0 = f16, 1 = bf16, 2 = tf32
   float acc_scale;      // accumulators * acc_scale before the epilogue (power-of-two operand scaling undone)
+  int park;             // mbarrier waits with a suspend hint: 1 = the epilogue warps' accumulator waits, 2 = all
 };
 
 template <int MODE, int BN, int KIND, int OCC = 1>
@@ -473,7 +495,7 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
       const CUtensorMap* mwlo = tail ? &mapWtlo : &mapWlo;
       const uint32_t tx = tail ? C::kTxBytes - (C::kSplit ? 2u : 1u) * ((uint32_t)C::kBTile - kTailBytes) : C::kTxBytes;
       for (int ch = 0; ch < p.n_chunks; ++ch) {
-        mbar_wait(&empty[stage], phase ^ 1, 1);
+        mbar_wait(&empty[stage], phase ^ 1, 1, p.park >= 2);
         uint8_t* sp = stage_ptr(stage);
         mbar_expect_tx(&full[stage], tx);
         const CUtensorMap* ma = (ks == 0) ? &mapA0 : &mapA1;
@@ -499,8 +521,8 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
       int stage = 0;
       uint32_t phase = 0;
       for (int ch = 0; ch < p.n_chunks; ++ch) {
-        mbar_wait(&full[stage], phase, 2);
-        if constexpr (C::kTF32) mbar_wait(&conv[stage], phase, 3);
+        mbar_wait(&full[stage], phase, 2, p.park >= 2);
+        if constexpr (C::kTF32) mbar_wait(&conv[stage], phase, 3, p.park >= 2);
         tc_fence_after();
         const uint32_t a_hi = smem_u32(stage_ptr(stage));
 #pragma unroll
@@ -530,7 +552,7 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
       int stage = 0;
       uint32_t phase = 0;
       for (int ch = 0; ch < p.n_chunks; ++ch) {
-        mbar_wait(&full[stage], phase, 4);
+        mbar_wait(&full[stage], phase, 4, p.park >= 1);
         float4* hi = reinterpret_cast<float4*>(stage_ptr(stage));
         float4* lo = reinterpret_cast<float4*>(stage_ptr(stage) + C::kATile);
 #pragma unroll
@@ -551,7 +573,7 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
         if (++stage == C::kStages) { stage = 0; phase ^= 1; }
       }
     }
-    mbar_wait(accum, 0, 5);
+    mbar_wait(accum, 0, 5, p.park >= 1);
     tc_fence_after();
     // All TMA writes and all MMAs of this CTA have completed: the pipeline stages are free and are
     // reused as the transpose staging area (one 32 x 66-float block per epilogue warp).  Warp ew
@@ -718,7 +740,7 @@ conv_gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap mapA0, const 
         const uint32_t tx = tail ? C::kATile + 16 * 128 : C::kStageBytes;
         int ks = 0, tap = 0, cc = 0, kcol = 0;
         for (int ch = 0; ch < p.n_chunks; ++ch) {
-          mbar_wait(&empty[stage], phase ^ 1, 11);
+          mbar_wait(&empty[stage], phase ^ 1, 11, p.park >= 2);
           uint8_t* sp = stage_ptr(stage);
           mbar_expect_tx(&full[stage], tx);
           const CUtensorMap* ma = (ks == 0) ? &mapA0 : &mapA1;
@@ -746,7 +768,7 @@ conv_gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap mapA0, const 
         tc_fence_after();
         const uint32_t acc = tmem_base + (uint32_t)(buf * C::kBN);
         for (int ch = 0; ch < p.n_chunks; ++ch) {
-          mbar_wait(&full[stage], phase, 13);
+          mbar_wait(&full[stage], phase, 13, p.park >= 2);
           tc_fence_after();
           const uint32_t a = smem_u32(stage_ptr(stage)), b = a + C::kATile;
 #pragma unroll
@@ -773,7 +795,7 @@ conv_gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap mapA0, const 
       const int nvalid = map.tile_nvalid[tile];
       const int m0 = tile * 128;
       const int buf = it & 1, use = it >> 1;
-      mbar_wait(&tmem_full[buf], (uint32_t)(use & 1), 14);
+      mbar_wait(&tmem_full[buf], (uint32_t)(use & 1), 14, p.park >= 1);
       tc_fence_after();
       const int row0 = m0 + q * 32;
       int nrows = nvalid - q * 32;
@@ -876,6 +898,7 @@ struct WnParams {
   float scale_in, scale_rs;    // accumulator scales (power-of-two weight pre-scaling undone)
   const float* bias_in;        // [256], (tanh, sigmoid) rows interleaved
   const float* segvec; int ldseg;   // style conditioning g: [n_seg, ldseg], tanh half then sigmoid half
+  int park;                    // see TcParams::park
 };
 
 template <int NRS>
@@ -938,7 +961,7 @@ wn_layer_fused_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_con
       uint32_t phase = 0;
       int tap = 0, cc = 0;
       for (int ch = 0; ch < kInChunks + kRsChunks; ++ch) {
-        mbar_wait(&empty[stage], phase ^ 1, 21);
+        mbar_wait(&empty[stage], phase ^ 1, 21, p.park >= 2);
         uint8_t* sp = stage_ptr(stage);
         if (ch < kInChunks) {
           mbar_expect_tx(&full[stage], C::kStageBytes);
@@ -958,7 +981,7 @@ wn_layer_fused_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_con
       int stage = 0;
       uint32_t phase = 0;
       for (int ch = 0; ch < kInChunks; ++ch) {
-        mbar_wait(&full[stage], phase, 22);
+        mbar_wait(&full[stage], phase, 22, p.park >= 2);
         tc_fence_after();
         const uint32_t a = smem_u32(stage_ptr(stage)), b = a + C::kATile;
 #pragma unroll
@@ -968,10 +991,10 @@ wn_layer_fused_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_con
         if (++stage == C::kStages) { stage = 0; phase ^= 1; }
       }
       tc_commit(accum1);
-      mbar_wait(acts_ready, 0, 23);
+      mbar_wait(acts_ready, 0, 23, p.park >= 2);
       tc_fence_after();
       for (int ch = 0; ch < kRsChunks; ++ch) {
-        mbar_wait(&full[stage], phase, 24);
+        mbar_wait(&full[stage], phase, 24, p.park >= 2);
         tc_fence_after();
         const uint32_t a = smem_u32(acts + ch * C::kATile), b = smem_u32(stage_ptr(stage)) + C::kATile;
 #pragma unroll
@@ -988,7 +1011,7 @@ wn_layer_fused_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_con
     const int q = warp & 3;            // TMEM lane quarter this warp may read (hardware rule)
     const int slab = ew >> 2;          // 64 accumulator columns = 32 gated channels
     using EG = EpiPair<EPI_GATE, true>;
-    mbar_wait(accum1, 0, 25);
+    mbar_wait(accum1, 0, 25, p.park >= 1);
     tc_fence_after();
     {
       float v[64];
@@ -1021,7 +1044,7 @@ wn_layer_fused_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_con
     __syncwarp();
     if (lane == 0) mbar_arrive(acts_ready);
     // ------------------------------------------------------------ res / skip epilogue
-    mbar_wait(accum2, 0, 26);
+    mbar_wait(accum2, 0, 26, p.park >= 1);
     tc_fence_after();
     float* stg = reinterpret_cast<float*>(smem) + ew * (32 * kStgLd4);
     const int row0 = m0 + q * 32;
@@ -1114,6 +1137,8 @@ bool get_map(const void* base, int rows, int ld, int elem, int box_rows, CUtenso
   return true;
 }
 
+int mbar_park_mode();
+
 template <int MODE, int BN, int KIND, int OCC = 1>
 cudaError_t launch_one(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
   using C = Cfg<MODE, BN, OCC>;
@@ -1130,6 +1155,7 @@ cudaError_t launch_one(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
   CUtensorMap mA[2], mAlo[2], mW, mWlo;
   TcParams p{};
   p.n_kseg = g.n_kseg;
+  p.park = mbar_park_mode();
   p.n_chunks = 0;
   for (int s = 0; s < 2; ++s) {
     const KSeg& ks = g.seg[s < g.n_kseg ? s : 0];
@@ -1201,6 +1227,7 @@ cudaError_t launch_persistent(const ConvGemm& g, const RowMap& map, cudaStream_t
   CUtensorMap mA[2], mW;
   TcParams p{};
   p.n_kseg = g.n_kseg;
+  p.park = mbar_park_mode();
   p.n_chunks = 0;
   for (int s = 0; s < 2; ++s) {
     const KSeg& ks = g.seg[s < g.n_kseg ? s : 0];
@@ -1249,6 +1276,11 @@ cudaError_t launch_persistent(const ConvGemm& g, const RowMap& map, cudaStream_t
 // STTS_PERSISTENT=0 falls back to one CTA per tile for the wide one-pass GEMMs
 bool use_persistent() {
   static const bool v = [] { const char* e = std::getenv("STTS_PERSISTENT"); return e == nullptr || e[0] != '0'; }();
+  return v;
+}
+
+int mbar_park_mode() {
+  static const int v = [] { const char* e = std::getenv("STTS_MBAR_PARK"); return e != nullptr ? std::atoi(e) : 1; }();
   return v;
 }
 
@@ -1325,6 +1357,7 @@ cudaError_t launch_wn(const ConvGemm& gin, const ConvGemm& grs, const RowMap& ma
   if (!get_map(gin.Wg, gin.Npad, gin.Ktot, 2, 256, &mWin)) return cudaErrorNotSupported;
   if (!get_map(grs.Wg, grs.Npad, grs.Ktot, 2, NRS, &mWrs)) return cudaErrorNotSupported;
   WnParams p;
+  p.park = mbar_park_mode();
   p.col0 = ks.colh0;
   p.scale_in = gin.acc_scale;
   p.scale_rs = grs.acc_scale;
