@@ -665,6 +665,205 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
   }
 }
 
+// ------------------------------------------------------------------ one-pass fp16 GEMM, 256 x 256 tiles
+// TWO row tiles against the same weight stage: two M = 128 MMAs per k-step share one B descriptor, two 256-column
+// accumulators fill the 512 TMEM columns, and the L2 -> SM operand traffic per output drops by a third
+// ((256 + 256) / 65 536 vs (128 + 256) / 32 768 bytes per K-element).  One CTA per tile pair x column tile, 16 epilogue
+// warps (no TMEM left to double-buffer, so no persistent overlap).  Row tiles are independent (own utterance, own
+// valid-row count); per-utterance weight matrices (GRN-folded pwconv2) stay on the other kernels.  Written to test the
+// hypothesis that the long-K GEMMs are L2-traffic-bound (their times match a 81 KB/us-per-SM model to 1 %): they are
+// not -- the output heads already run at 84 % of the sustained cuBLAS bf16 rate (1 175 of 1 396 TF/s) and gained 3 %;
+// the kernel pays where the 8-warp persistent epilogue or the 128-row tile was the limiter (see launch_bn).
+struct M2Cfg {
+  static constexpr int kBN = 256;
+  static constexpr int kBK = 64, kUmmaK = 16;
+  static constexpr int kATile = 128 * 128, kBTile = kBN * 128;           // bytes
+  static constexpr int kStageBytes = 2 * kATile + kBTile;                // 64 KB
+  static constexpr int kStages = 3;
+  static constexpr int kEpiWarps = 16;
+  static constexpr int kThreads = 64 + 32 * kEpiWarps;                   // 576
+  static constexpr int kSmem = kStages * kStageBytes + 1024 + 256;
+  static constexpr uint32_t kIdesc = (1u << 4) | ((uint32_t)(kBN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+  static_assert(kStages * kStageBytes >= kEpiWarps * 32 * kStgLd4 * 4, "staging must fit into the stage ring");
+};
+
+template <int KIND>
+__global__ void __launch_bounds__(M2Cfg::kThreads, 1)
+conv_gemm_tc_m256_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant__ CUtensorMap mapA1,
+                         const __grid_constant__ CUtensorMap mapW, const __grid_constant__ CUtensorMap mapWt,
+                         const TcParams p, const Epi epi, const RowMap map) {
+  using C = M2Cfg;
+  const int pair = blockIdx.y;
+  const int t0 = 2 * pair, t1 = 2 * pair + 1;
+  const bool live0 = map.tile_seg[t0] >= 0, live1 = t1 < map.n_tiles && map.tile_seg[t1] >= 0;
+  if (!live0 && !live1) return;
+  const int n0 = blockIdx.x * C::kBN;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const bool tail = (epi.N - n0) <= 16;
+  constexpr uint32_t kTailBytes = 16 * 128;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::kStages * C::kStageBytes);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + C::kStages;
+  uint64_t* accum = bars + 2 * C::kStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * C::kStages + 1);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < C::kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    mbar_init(accum, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"(512u)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  pdl_enter();   // everything above (barrier init, TMEM allocation) overlaps the previous kernel of the stream
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t idesc = tail ? ((C::kIdesc & ~(0x3Fu << 17)) | ((16u >> 3) << 17)) : C::kIdesc;
+  auto stage_ptr = [&](int s) { return smem + (size_t)s * C::kStageBytes; };
+
+  if (warp == 0) {
+    // ------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int ks = 0, tap = 0, cc = 0, kcol = 0;
+      const CUtensorMap* mw = tail ? &mapWt : &mapW;
+      const uint32_t tx = tail ? 2 * C::kATile + kTailBytes : C::kStageBytes;
+      for (int ch = 0; ch < p.n_chunks; ++ch) {
+        mbar_wait(&empty[stage], phase ^ 1, 31, p.park >= 2);
+        uint8_t* sp = stage_ptr(stage);
+        mbar_expect_tx(&full[stage], tx);
+        const CUtensorMap* ma = (ks == 0) ? &mapA0 : &mapA1;
+        const int row = t0 * 128 + tap * p.dil[ks] - p.pad[ks];
+        tma_load_2d(sp, ma, &full[stage], p.col0[ks] + cc * C::kBK, row);
+        tma_load_2d(sp + C::kATile, ma, &full[stage], p.col0[ks] + cc * C::kBK, row + 128);   // past the buffer: zero fill
+        tma_load_2d(sp + 2 * C::kATile, mw, &full[stage], kcol, n0);
+        kcol += C::kBK;
+        if (++cc == p.cin_chunks[ks]) { cc = 0; if (++tap == p.taps[ks]) { tap = 0; ++ks; } }
+        if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------ MMA issuer: two row tiles per weight stage
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int ch = 0; ch < p.n_chunks; ++ch) {
+        mbar_wait(&full[stage], phase, 32, p.park >= 2);
+        tc_fence_after();
+        const uint32_t a0 = smem_u32(stage_ptr(stage)), a1 = a0 + C::kATile, b = a0 + 2 * C::kATile;
+#pragma unroll
+        for (int k = 0; k < C::kBK / C::kUmmaK; ++k) {
+          tc_mma<false>(tmem_base, make_sdesc(a0 + k * 32), make_sdesc(b + k * 32), idesc, (ch | k) != 0);
+          tc_mma<false>(tmem_base + (uint32_t)C::kBN, make_sdesc(a1 + k * 32), make_sdesc(b + k * 32), idesc, (ch | k) != 0);
+        }
+        tc_commit(&empty[stage]);
+        if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+      }
+      tc_commit(accum);
+    }
+  } else {
+    // ------------------------------------------------------------ epilogue: accumulator 0, then accumulator 1
+    mbar_wait(accum, 0, 35, p.park >= 1);
+    tc_fence_after();
+    const int ew = warp - 2;
+    const int q = warp & 3;
+#pragma unroll 1
+    for (int h = 0; h < 2; ++h) {                // accumulator h = row tile 2 * pair + h
+      const int tile = 2 * pair + h;
+      if (tile >= map.n_tiles) break;
+      const int seg = map.tile_seg[tile];
+      if (seg < 0) continue;
+      const int nvalid = map.tile_nvalid[tile];
+      const int m0 = tile * 128;
+      __syncwarp();
+      using EQ = EpiQuad<KIND, true>;
+      constexpr int kLd = EQ::kOk ? kStgLd4 : kStgLd;
+      float* stg = reinterpret_cast<float*>(smem) + ew * (32 * kLd);
+      const int row0 = m0 + q * 32;
+      int nrows = nvalid - q * 32;
+      nrows = nrows < 0 ? 0 : (nrows > 32 ? 32 : nrows);
+      const int seg_first = (epi.seg_start != nullptr) ? epi.seg_start[seg] : -1;
+      const int c = (ew >> 2) * 64;
+      if constexpr (EQ::kOk) {
+        if (n0 + c < epi.N) {                    // warp-uniform
+          {
+            float v[64];
+            tmem_ld64(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(h * C::kBN + c), v);
+            __syncwarp();
+  #pragma unroll
+            for (int j = 0; j < 64; j += 4)
+              *reinterpret_cast<float4*>(stg + lane * kStgLd4 + j) =
+                  make_float4(v[j] * p.acc_scale, v[j + 1] * p.acc_scale, v[j + 2] * p.acc_scale, v[j + 3] * p.acc_scale);
+          }
+          __syncwarp();
+          quad_slab<KIND, true, 4>(epi, stg, row0, nrows, n0 + c, tile, q, lane);
+        }
+      } else
+      if (n0 + c < epi.N) {                      // warp-uniform
+        EpiPair<KIND, true> ep;
+        ep.init(epi, seg, n0 + c + 2 * lane);
+        {
+          float v[64];
+          tmem_ld64(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(h * C::kBN + c), v);
+          __syncwarp();                            // previous slab fully consumed
+  #pragma unroll
+          for (int j = 0; j < 64; j += 2)
+            *reinterpret_cast<float2*>(stg + lane * kStgLd + j) = make_float2(v[j] * p.acc_scale, v[j + 1] * p.acc_scale);
+        }
+        __syncwarp();
+        if constexpr (KIND == EPI_STFT) {
+          stft_slab(epi, stg, row0, nrows, n0 + c, seg_first, lane);
+        } else
+        if constexpr (EpiPair<KIND, false>::kHasPre) {
+          // batches of RB rows: RB independent residual loads in flight per warp, registers bounded
+          // (576-thread CTAs of the 256-column tile have 113 registers per thread)
+          constexpr int RB = 4;
+  #pragma unroll 1
+          for (int rb = 0; rb < 32; rb += RB) {
+            float2 pre[RB];
+  #pragma unroll
+            for (int rr = 0; rr < RB; ++rr)
+              if (rb + rr < nrows) pre[rr] = ep.pre(epi, row0 + rb + rr);
+            float2 av[RB];                               // staged accumulators read up front: the loads must
+  #pragma unroll                                         // not be serialised behind the global stores of apply()
+            for (int rr = 0; rr < RB; ++rr) av[rr] = *reinterpret_cast<const float2*>(stg + (rb + rr) * kStgLd + 2 * lane);
+  #pragma unroll
+            for (int rr = 0; rr < RB; ++rr)
+              if (rb + rr < nrows) ep.apply(epi, row0 + rb + rr, seg, seg_first, av[rr].x, av[rr].y, pre[rr]);
+          }
+        } else {
+  #pragma unroll 1
+          for (int rb = 0; rb < nrows; rb += 8) {        // 8 rows per batch: loads first, then the epilogue math + stores
+            float2 av[8];
+  #pragma unroll
+            for (int rr = 0; rr < 8; ++rr) av[rr] = *reinterpret_cast<const float2*>(stg + (rb + rr) * kStgLd + 2 * lane);
+  #pragma unroll
+            for (int rr = 0; rr < 8; ++rr)
+              if (rb + rr < nrows) ep.apply(epi, row0 + rb + rr, seg, seg_first, av[rr].x, av[rr].y, make_float2(0.f, 0.f));
+          }
+        }
+        ep.finish(epi, tile, q);
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+  }
+}
+
 // ------------------------------------------------------------------ persistent one-pass fp16 GEMM, 128 x 256 tiles
 // One CTA per SM loops over output tiles (tile id = m_tile * n_tiles_n + n_tile, grid-stride).  The
 // TMA producer and the MMA issuer run ahead into the next tile while the 8 epilogue warps drain the
@@ -1273,6 +1472,54 @@ cudaError_t launch_persistent(const ConvGemm& g, const RowMap& map, cudaStream_t
   return cudaGetLastError();
 }
 
+template <int KIND>
+cudaError_t launch_m256(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
+  using C = M2Cfg;
+  CUtensorMap mA[2], mW;
+  TcParams p{};
+  p.n_kseg = g.n_kseg;
+  p.park = mbar_park_mode();
+  p.n_chunks = 0;
+  for (int s = 0; s < 2; ++s) {
+    const KSeg& ks = g.seg[s < g.n_kseg ? s : 0];
+    const void* base = g.f16 ? (const void*)ks.Ag : (const void*)ks.Ah;
+    const int ld = g.f16 ? ks.ldag : ks.ldah;
+    if (base == nullptr) return cudaErrorInvalidValue;
+    if (!get_map(base, ks.rows, ld, 2, 128, &mA[s])) return cudaErrorNotSupported;
+    if (s < g.n_kseg) {
+      p.taps[s] = ks.taps;
+      p.pad[s] = ks.pad;
+      p.dil[s] = ks.dil > 0 ? ks.dil : 1;
+      p.cin_chunks[s] = ks.cin_pad / C::kBK;
+      p.col0[s] = ks.colh0;
+      p.n_chunks += ks.taps * p.cin_chunks[s];
+    }
+  }
+  const bool per_seg = !g.f16 && g.Wh_seg != nullptr;
+  const void* w = per_seg ? (const void*)g.Wh_seg : (const void*)g.Wg;
+  if (w == nullptr) return cudaErrorInvalidValue;
+  if (!get_map(w, per_seg ? g.Npad * map.n_seg : g.Npad, g.Ktot, 2, C::kBN, &mW)) return cudaErrorNotSupported;
+  p.w_seg_rows = per_seg ? g.Npad : 0;
+  p.ab_fmt = 0u;
+  p.acc_scale = per_seg ? 1.f : g.acc_scale;
+  CUtensorMap mWt = mW;
+  if (g.epi.N % C::kBN != 0 && g.epi.N % C::kBN <= 16 &&
+      !get_map(w, per_seg ? g.Npad * map.n_seg : g.Npad, g.Ktot, 2, 16, &mWt))
+    return cudaErrorNotSupported;
+  auto kern = conv_gemm_tc_m256_kernel<KIND>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmem);
+    if (e != cudaSuccess) return e;
+    attr_done = true;
+  }
+  if (per_seg) return cudaErrorInvalidValue;     // the two row tiles of a CTA share one weight stage
+  const int n_tiles_n = (g.epi.N + C::kBN - 1) / C::kBN;
+  dim3 grid(n_tiles_n, (map.n_tiles + 1) / 2);
+  launch_k(kern, grid, C::kThreads, C::kSmem, st, mA[0], mA[1], mW, mWt, p, g.epi, map);
+  return cudaGetLastError();
+}
+
 // STTS_PERSISTENT=0 falls back to one CTA per tile for the wide one-pass GEMMs
 bool use_persistent() {
   static const bool v = [] { const char* e = std::getenv("STTS_PERSISTENT"); return e == nullptr || e[0] != '0'; }();
@@ -1304,6 +1551,11 @@ cudaError_t launch_bn(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
   if constexpr (MODE == MODE_F16) {
     int chunks = 0;
     for (int s = 0; s < g.n_kseg; ++s) chunks += g.seg[s].taps * (g.seg[s].cin_pad / 64);
+    // very wide short-K layers (pwconv1: K 512, N 1 536): STTS_M256_WIDE=<min k-chunks> sends them to the 256 x 256 kernel
+    static const int m256_wide = [] { const char* e = std::getenv("STTS_M256_WIDE"); return e != nullptr ? std::atoi(e) : 8; }();
+    if (m256_wide >= 0 && chunks >= m256_wide && g.epi.N >= 1024 && g.Npad % 256 == 0 && (g.f16 || g.Wh_seg == nullptr) &&
+        map.n_tiles >= 2)
+      return launch_m256<KIND>(g, map, st);
     if (chunks <= occ2_max_chunks()) return launch_one<MODE, 128, KIND, 2>(g, map, st);
   }
   // BN = 256 whenever there is more than one 128-column tile (long-K one-pass GEMMs reach the tensor peak
@@ -1317,6 +1569,16 @@ cudaError_t launch_bn(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
     // (pwconv1 +54 %, flow res/skip +35 %: 8 instead of 16 epilogue warps), which keep one CTA per tile
     int chunks = 0;
     for (int s = 0; s < g.n_kseg; ++s) chunks += g.seg[s].taps * (g.seg[s].cin_pad / 64);
+    // 256 x 256 tiles (two row tiles per weight stage) for the long-K wide GEMMs without per-utterance weights: they are
+    // bound by L2 -> SM operand traffic, which this tile shape cuts by a third.  STTS_M256=<min k-chunks>, -1 = off.
+    static const int m256_min = [] { const char* e = std::getenv("STTS_M256"); return e != nullptr ? std::atoi(e) : 16; }();
+    // Measured per layer against the persistent kernel (same box): output heads -2 .. -3.5 %, inverse DFT -2 %, the
+    // 1x1 projector (16 chunks, not persistent before) -20 %; prior convs (N = 512, 119 chunks) +12 %, decoder convs
+    // +-1 %: so it takes the very wide outputs and the wide layers the persistent kernel does not.
+    const bool pers = use_persistent() && chunks >= 24 && g.epi.N >= 512;
+    if (wide && m256_min >= 0 && chunks >= m256_min && g.epi.N >= 256 && (g.f16 || g.Wh_seg == nullptr) && map.n_tiles >= 2 &&
+        (g.epi.N >= 1024 || !pers))
+      return launch_m256<KIND>(g, map, st);
     static const bool all = [] { const char* e = std::getenv("STTS_PERSISTENT"); return e != nullptr && e[0] == 'a'; }();
     if (wide && use_persistent() && (all || (chunks >= 24 && g.epi.N >= 512))) return launch_persistent<KIND>(g, map, st);
   }
