@@ -1337,6 +1337,7 @@ bool get_map(const void* base, int rows, int ld, int elem, int box_rows, CUtenso
 }
 
 int mbar_park_mode();
+bool m256_fills_gpu(const ConvGemm& g, const RowMap& map);
 
 template <int MODE, int BN, int KIND, int OCC = 1>
 cudaError_t launch_one(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
@@ -1526,6 +1527,12 @@ bool use_persistent() {
   return v;
 }
 
+// the 256-row tile halves the CTA count: only when the tile pairs still fill the machine (a single 5 s utterance has
+// 13 row tiles; latency mode keeps the 128-row kernels)
+bool m256_fills_gpu(const ConvGemm& g, const RowMap& map) {
+  return (long long)((map.n_tiles + 1) / 2) * ((g.epi.N + 255) / 256) >= 148;
+}
+
 int mbar_park_mode() {
   static const int v = [] { const char* e = std::getenv("STTS_MBAR_PARK"); return e != nullptr ? std::atoi(e) : 1; }();
   return v;
@@ -1554,7 +1561,7 @@ cudaError_t launch_bn(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
     // very wide short-K layers (pwconv1: K 512, N 1 536): STTS_M256_WIDE=<min k-chunks> sends them to the 256 x 256 kernel
     static const int m256_wide = [] { const char* e = std::getenv("STTS_M256_WIDE"); return e != nullptr ? std::atoi(e) : 8; }();
     if (m256_wide >= 0 && chunks >= m256_wide && g.epi.N >= 1024 && g.Npad % 256 == 0 && (g.f16 || g.Wh_seg == nullptr) &&
-        map.n_tiles >= 2)
+        m256_fills_gpu(g, map))
       return launch_m256<KIND>(g, map, st);
     if (chunks <= occ2_max_chunks()) return launch_one<MODE, 128, KIND, 2>(g, map, st);
   }
@@ -1576,7 +1583,7 @@ cudaError_t launch_bn(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
     // 1x1 projector (16 chunks, not persistent before) -20 %; prior convs (N = 512, 119 chunks) +12 %, decoder convs
     // +-1 %: so it takes the very wide outputs and the wide layers the persistent kernel does not.
     const bool pers = use_persistent() && chunks >= 24 && g.epi.N >= 512;
-    if (wide && m256_min >= 0 && chunks >= m256_min && g.epi.N >= 256 && (g.f16 || g.Wh_seg == nullptr) && map.n_tiles >= 2 &&
+    if (wide && m256_min >= 0 && chunks >= m256_min && g.epi.N >= 256 && (g.f16 || g.Wh_seg == nullptr) && m256_fills_gpu(g, map) &&
         (g.epi.N >= 1024 || !pers))
       return launch_m256<KIND>(g, map, st);
     static const bool all = [] { const char* e = std::getenv("STTS_PERSISTENT"); return e != nullptr && e[0] == 'a'; }();

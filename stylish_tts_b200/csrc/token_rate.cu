@@ -685,10 +685,11 @@ cudaError_t attention(const float* Q, int ldq, int qcol, const float* K, int ldk
     return launch_attention_stream<DD, LL, QQ, NN, KK, CC>(Q, ldq, qcol, K, ldk, kcol, V, ldv, vcol, H, scale, rd,    \
                                                            rope_tab, qmap, kmap, max_tq, q_tok, q_cu, band, out, ldo, \
                                                            outg, outl, ldh, st);
-    STTS_ATTS(16, 1, 2, 128, 4, 64)    // text encoders: 64 queries per CTA (2 per lane group), 4 key sets per query
-    STTS_ATTS(40, 1, 2, 64, 1, 64)     // cross attention: 128 frames per CTA
-    STTS_ATTS(96, 4, 2, 128, 1, 128)   // duration prosody encoder: 64 queries per CTA
-    STTS_ATTS(160, 8, 2, 128, 1, 64)   // 32 queries per CTA, 8 lanes x 20 features per query
+    // measured per launch on the C2 batch (ncu): more key sets / queries per lane group than these are slower
+    STTS_ATTS(16, 1, 2, 128, 4, 64)    // text encoders: 64 queries per CTA (2 per lane), 4 key sets          30.5 us
+    STTS_ATTS(40, 1, 2, 128, 2, 64)    // cross attention: 128 frames per CTA, 2 key sets                     145 us
+    STTS_ATTS(96, 4, 2, 256, 2, 128)   // duration prosody encoder: 64 queries per CTA, 2 key sets             57 us
+    STTS_ATTS(160, 8, 4, 256, 2, 64)   // 64 queries per CTA, 8 lanes x 20 features, 4 queries per lane group   78 us
 #undef STTS_ATTS
   }
   if (twins) return cudaErrorInvalidValue;       // the fallback kernels do not write twins
