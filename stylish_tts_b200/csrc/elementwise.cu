@@ -223,24 +223,55 @@ __global__ void __launch_bounds__(256) adain_act_kernel(const float* __restrict_
   const int seg = map.tile_seg[tile];
   if (seg < 0) return;
   const int nvalid = map.tile_nvalid[tile];
-  const int c = blockIdx.y * 128 + 2 * (threadIdx.x & 63);
+  // thread = (row group 0..7, 4 channels): a warp access is 512 contiguous bytes of one row (16-byte loads, 8-byte twin
+  // stores); C is even, so a row's tail is either a full quad or one pair
+  const int c = blockIdx.y * 128 + 4 * (threadIdx.x & 31);
   if (c >= C) return;
-  const int rg = threadIdx.x >> 6;
-  const float2 mu = *reinterpret_cast<const float2*>(mean + (size_t)seg * C + c);
-  const float2 rs = *reinterpret_cast<const float2*>(rstd + (size_t)seg * C + c);
+  const bool quad = c + 4 <= C;
+  const int rg = threadIdx.x >> 5;
   const float* g = gb + (size_t)seg * ldgb;
-  const float ga0 = 1.f + g[c], ga1 = 1.f + g[c + 1], be0 = g[C + c], be1 = g[C + c + 1];
+  float mu[4], rs[4], ga[4], be[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int ci = (quad || i < 2) ? c + i : c;
+    mu[i] = mean[(size_t)seg * C + ci]; rs[i] = rstd[(size_t)seg * C + ci];
+    ga[i] = 1.f + g[ci]; be[i] = g[C + ci];
+  }
   const size_t base = (size_t)tile * 128;
+  if (quad && ((ldx | ldy | ldyh) & 3) == 0) {
 #pragma unroll 4
-  for (int lr = rg; lr < nvalid; lr += 4) {
-    const size_t r = base + lr;
-    const float2 v = *reinterpret_cast<const float2*>(x + r * ldx + c);
-    float a = ga0 * ((v.x - mu.x) * rs.x) + be0;
-    float b = ga1 * ((v.y - mu.y) * rs.y) + be1;
-    a = a > 0.f ? a : a * slope;
-    b = b > 0.f ? b : b * slope;
-    if (y != nullptr) *reinterpret_cast<float2*>(y + r * ldy + c) = make_float2(a, b);
-    if (yh != nullptr) *reinterpret_cast<twin2_t*>(yh + r * ldyh + c) = to_twin2(a, b);
+    for (int lr = rg; lr < nvalid; lr += 8) {
+      const size_t r = base + lr;
+      const float4 v = *reinterpret_cast<const float4*>(x + r * ldx + c);
+      float o[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float a = ga[i] * ((o[i] - mu[i]) * rs[i]) + be[i];
+        o[i] = a > 0.f ? a : a * slope;
+      }
+      if (y != nullptr) *reinterpret_cast<float4*>(y + r * ldy + c) = make_float4(o[0], o[1], o[2], o[3]);
+      if (yh != nullptr) {
+        const twin2_t t0 = to_twin2(o[0], o[1]), t1 = to_twin2(o[2], o[3]);
+        uint2 w;
+        w.x = *reinterpret_cast<const uint32_t*>(&t0); w.y = *reinterpret_cast<const uint32_t*>(&t1);
+        *reinterpret_cast<uint2*>(yh + r * ldyh + c) = w;
+      }
+    }
+  } else {
+    const int np = quad ? 2 : 1;                   // channel pairs of this thread
+#pragma unroll 2
+    for (int lr = rg; lr < nvalid; lr += 8) {
+      const size_t r = base + lr;
+      for (int h = 0; h < np; ++h) {
+        const float2 v = *reinterpret_cast<const float2*>(x + r * ldx + c + 2 * h);
+        float a = ga[2 * h] * ((v.x - mu[2 * h]) * rs[2 * h]) + be[2 * h];
+        float b2 = ga[2 * h + 1] * ((v.y - mu[2 * h + 1]) * rs[2 * h + 1]) + be[2 * h + 1];
+        a = a > 0.f ? a : a * slope;
+        b2 = b2 > 0.f ? b2 : b2 * slope;
+        if (y != nullptr) *reinterpret_cast<float2*>(y + r * ldy + c + 2 * h) = make_float2(a, b2);
+        if (yh != nullptr) *reinterpret_cast<twin2_t*>(yh + r * ldyh + c + 2 * h) = to_twin2(a, b2);
+      }
+    }
   }
 }
 
