@@ -85,7 +85,7 @@ class ClockSampler:
              "clocks_event_reasons.sw_power_cap")
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._read, daemon=True).start()
         except Exception:
@@ -111,7 +111,8 @@ class ClockSampler:
                     reasons.add(n)
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm),
+                "window": "nvidia-smi -lms 20 over the last untimed warm-up steps and the timed region"}
 
 
 # ------------------------------------------------------------------------------------ baseline legs (oracle)
@@ -467,9 +468,12 @@ def main():
 
     warm(step_resident, max(args.warmup, len(pool.lanes)))       # every lane warms up (and captures its graph)
     pool.check()
+    # clocks / throttle reasons: nvidia-smi every 20 ms from two more untimed steps of the same load (the sampler
+    # needs ~0.1 s to start; the timed region itself is ~0.1 s at the default K) through the timed region
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
+    warm(step_resident, 2 * len(pool.lanes))
     ms_total = timed(step_resident, args.steps)
     clocks = sampler.stop() if rank == 0 else None
     # Per-GEMM CUDA events cannot be recorded inside a graph replay: the roofline pass times the same
