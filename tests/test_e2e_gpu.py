@@ -52,7 +52,7 @@ def test_golden_single_utterances(precision, tol):
         _log(f"{precision}.{name}", {"audio_x0": err, "audio_raw_after_7500": raw, "pitch": perr})
         assert raw <= 1.5 * tol, (precision, name, raw)
         # predicted pitch (~100-270 Hz): fp32 measured 9e-4 Hz, tf32x3 2.2e-3 Hz, f16 0.22 Hz on B200
-        assert perr <= {"fp32": 6e-3, "tf32x3": 1.5e-2, "f16": 1.0}[precision], (name, perr)
+        assert perr <= {"fp32": 6e-3, "tf32x3": 1.5e-2, "f16": 0.6}[precision], (name, perr)   # f16: 2-3 x measured
         assert torch.equal(out["duration_pred"][0].cpu().to(torch.int32), g["duration_pred"]), name
         assert out["audio"][0].numel() == 300 * int(dur.sum())
         assert err <= tol, (precision, name, err)
