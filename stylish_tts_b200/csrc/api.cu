@@ -53,6 +53,9 @@ void stts_destroy(stts_ctx* ctx) {
   if (ctx->c.arena) cudaFree(ctx->c.arena);
   if (ctx->c.tarena) cudaFree(ctx->c.tarena);
   if (ctx->c.h_meta) cudaFreeHost(ctx->c.h_meta);
+  if (ctx->c.ev_fork) cudaEventDestroy(ctx->c.ev_fork);
+  if (ctx->c.ev_join) cudaEventDestroy(ctx->c.ev_join);
+  if (ctx->c.st_aux) cudaStreamDestroy(ctx->c.st_aux);
   delete ctx;
 }
 

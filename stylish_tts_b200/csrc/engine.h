@@ -97,6 +97,8 @@ struct Context {
   std::map<std::string, void*> raw;            // other named scratch
   std::map<std::string, size_t> raw_bytes;
   SourceMeta* h_meta = nullptr;                // pinned
+  cudaStream_t st_aux = nullptr;               // second branch of fork / join stages (the energy tower), with its events
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   // ---- optional per-GEMM CUDA-event profiling (bench.py roofline)
   bool prof_on = false;
   struct ProfRec { std::string name; cudaEvent_t e0, e1; double flops; int backend; };

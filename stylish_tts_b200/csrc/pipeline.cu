@@ -115,8 +115,10 @@ int set_layout(Context& c, int n_seg, const int* len_f, const int* len_f4) {
              {"YF", 4, 1216, 0, false}, {"DIN", 4, 512, 0, true}};
   }
   if (useF) {
+    // "...2": scratch of the energy tower, which runs on the auxiliary stream next to the pitch tower
     std::vector<Want> wf = {{"PX", 1, 320, 0, true},  {"PACT", 1, 320, 0, true}, {"PY1", 1, 320, 0, false},
-                            {"PA", 1, 320, 0, true},  {"PB", 1, 320, 0, true}};
+                            {"PA", 1, 320, 0, true},  {"PB", 1, 320, 0, true},   {"PACT2", 1, 320, 0, true},
+                            {"PY12", 1, 320, 0, false}, {"PA2", 1, 320, 0, true}, {"PB2", 1, 320, 0, true}};
     wants.insert(wants.end(), wf.begin(), wf.end());
   }
   ArenaPlan plan;
@@ -157,7 +159,12 @@ int set_layout(Context& c, int n_seg, const int* len_f, const int* len_f4) {
   // InstanceNorm statistics from the conv epilogues (16-bit mode): per-(tile, quarter) fp32 column sums / sums
   // of squares of a block's input (PSX: conv2 of the previous block + side channels) and of conv1's output (PSY)
   if (use4) { raws.push_back({"PSX4", (size_t)(R4 / 128) * 4 * 640 * 4 * 2}); raws.push_back({"PSY4", (size_t)(R4 / 128) * 4 * 512 * 4 * 2}); }
-  if (useF) { raws.push_back({"PSXF", (size_t)(RF / 128) * 4 * 320 * 4 * 2}); raws.push_back({"PSYF", (size_t)(RF / 128) * 4 * 320 * 4 * 2}); }
+  if (useF) {
+    raws.push_back({"PSXF", (size_t)(RF / 128) * 4 * 320 * 4 * 2}); raws.push_back({"PSYF", (size_t)(RF / 128) * 4 * 320 * 4 * 2});
+    raws.push_back({"PSXF2", (size_t)(RF / 128) * 4 * 320 * 4 * 2}); raws.push_back({"PSYF2", (size_t)(RF / 128) * 4 * 320 * 4 * 2});
+    raws.push_back({"STATS2", (size_t)(RF / 128) * 320 * 2 * 8});
+    raws.push_back({"MEAN2", (size_t)B * 320 * 4}); raws.push_back({"RSTD2", (size_t)B * 320 * 4});
+  }
   if (use4) {   // GRN folded into pw2: sum-of-squares partials of the pw1 epilogue, per-utterance fp16 weights
     raws.push_back({"COLSS", (size_t)(R4 / 128) * 4 * 1536 * 4});
     raws.push_back({"WGRN", (size_t)B * 512 * 1536 * 2});
@@ -381,7 +388,9 @@ struct Stage {
   Context& c;
   cudaStream_t st;
   bool twins;
-  Stage(Context& ctx, cudaStream_t s) : c(ctx), st(s), twins(ctx.precision == 1) {}
+  const char* sfx = "";          // "2": the statistics scratch of a branch that runs next to another one (energy tower)
+  Stage(Context& ctx, cudaStream_t s, const char* suffix = "") : c(ctx), st(s), twins(ctx.precision == 1), sfx(suffix) {}
+  template <typename T> T* Rs(const char* n) { return reinterpret_cast<T*>(c.raw[std::string(n) + sfx]); }
   Act& A(const char* n) { return c.act[n]; }
   template <typename T> T* R(const char* n) { return reinterpret_cast<T*>(c.raw[n]); }
   twin_t* tw(const Act& a) const { return twins ? a.h : nullptr; }
@@ -419,9 +428,9 @@ int ada_block(Stage& S, const std::string& name, const Act& x, int cin, int cout
   Context& c = S.c;
   const PackedGemm& g1 = c.gemm[name + ".conv1"];
   const PackedGemm& g2 = c.gemm[name + ".conv2"];
-  float* mean = S.R<float>("MEAN");
-  float* rstd = S.R<float>("RSTD");
-  double* stats = S.R<double>("STATS");
+  float* mean = S.Rs<float>("MEAN");
+  float* rstd = S.Rs<float>("RSTD");
+  double* stats = S.Rs<double>("STATS");
   const bool fuse = sf != nullptr && S.twins && stats_fused() && sf->psx != nullptr && dst_col == 0;
   if (fuse && sf->x_ready) {
     STTS_CK(colstats_final_q(sf->psx, sf->psx + sf->nx, sf->ldx, cin, map, 1e-5f, mean, rstd, S.st));
@@ -473,17 +482,40 @@ int run_pe_towers(Context& c, const float* d_x, const float* d_style, float* d_p
   // d_x == NULL: the cross-attention block (run_pe_cross) already left its rows in PX
   if (d_x != nullptr)
     STTS_CK(transpose_in(d_x, c.LF.d_off[3], c.LF.d_cs, 320, map, px.f, px.ld, 0, S.tw(px), px.ld, 0, st));
+  // The two towers only share their input (PX) and the style FC rows: the energy tower runs on the context's auxiliary
+  // stream with its own scratch, forked from / joined to `st` by events (under stream capture the fork becomes two
+  // branches of the graph).  Their launches are small (124 tiles at hop 300): side by side they halve this stage.
+  static const bool par = [] { const char* e = std::getenv("STTS_TOWERS_PAR"); return e == nullptr || e[0] != '0'; }();
+  if (par && c.st_aux == nullptr) {
+    if (cudaStreamCreateWithFlags(&c.st_aux, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c.ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c.ev_join, cudaEventDisableTiming) != cudaSuccess)
+      return fail(c, -5, "auxiliary stream / events");
+  }
   const char* tw[2] = {"F0", "N"};
+  if (par) {
+    STTS_CK(cudaEventRecord(c.ev_fork, st));
+    STTS_CK(cudaStreamWaitEvent(c.st_aux, c.ev_fork, 0));
+    c.launches -= 2;
+  }
   for (int t = 0; t < 2; ++t) {
+    const bool aux = par && t == 1;
+    Stage T(c, aux ? c.st_aux : st, aux ? "2" : "");
+    Act &act = aux ? S.A("PACT2") : pact, &y1 = aux ? S.A("PY12") : py1, &a = aux ? S.A("PA2") : pa, &b = aux ? S.A("PB2") : pb;
     const std::string base = std::string("pe.") + tw[t];
     StatsFuse sf;    // the tower's first input (PX) is not a conv2 output: x_ready starts false
-    sf.psx = S.R<float>("PSXF"); sf.ldx = 320; sf.nx = (size_t)c.LF.n_tiles * 4 * 320;
-    sf.psy = S.R<float>("PSYF"); sf.ldy = 320; sf.ny = (size_t)c.LF.n_tiles * 4 * 320;
-    STTS_RET(ada_block(S, base + "0", px, 320, 320, pact, py1, pact, pa, 0, gb, c.J_pe, map, &sf));
-    STTS_RET(ada_block(S, base + "1", pa, 320, 320, pact, py1, pact, pb, 0, gb, c.J_pe, map, &sf));
-    STTS_RET(ada_block(S, base + "2", pb, 320, 320, pact, py1, pact, pa, 0, gb, c.J_pe, map, &sf));
-    STTS_CK(rowdot(pa.f, pa.ld, 320, map, c.vec[t == 0 ? "pe.F0_proj_w" : "pe.N_proj_w"],
-                   c.vec[t == 0 ? "pe.F0_proj_b" : "pe.N_proj_b"], c.LF.d_cu, t == 0 ? d_pitch : d_energy, st));
+    sf.psx = T.Rs<float>("PSXF"); sf.ldx = 320; sf.nx = (size_t)c.LF.n_tiles * 4 * 320;
+    sf.psy = T.Rs<float>("PSYF"); sf.ldy = 320; sf.ny = (size_t)c.LF.n_tiles * 4 * 320;
+    STTS_RET(ada_block(T, base + "0", px, 320, 320, act, y1, act, a, 0, gb, c.J_pe, map, &sf));
+    STTS_RET(ada_block(T, base + "1", a, 320, 320, act, y1, act, b, 0, gb, c.J_pe, map, &sf));
+    STTS_RET(ada_block(T, base + "2", b, 320, 320, act, y1, act, a, 0, gb, c.J_pe, map, &sf));
+    STTS_CK(rowdot(a.f, a.ld, 320, map, c.vec[t == 0 ? "pe.F0_proj_w" : "pe.N_proj_w"],
+                   c.vec[t == 0 ? "pe.F0_proj_b" : "pe.N_proj_b"], c.LF.d_cu, t == 0 ? d_pitch : d_energy, T.st));
+  }
+  if (par) {
+    STTS_CK(cudaEventRecord(c.ev_join, c.st_aux));
+    STTS_CK(cudaStreamWaitEvent(st, c.ev_join, 0));
+    c.launches -= 2;
   }
   return 0;
 }
