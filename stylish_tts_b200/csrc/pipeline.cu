@@ -469,6 +469,17 @@ int ada_block(Stage& S, const std::string& name, const Act& x, int cin, int cout
 
 }  // namespace
 
+// auxiliary stream + fork / join events of a context (created on first use: the warm-up passes of a graph capture
+// run eagerly, so nothing is created while capturing)
+static int ensure_aux(Context& c) {
+  if (c.st_aux != nullptr) return 0;
+  if (cudaStreamCreateWithFlags(&c.st_aux, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreateWithFlags(&c.ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&c.ev_join, cudaEventDisableTiming) != cudaSuccess)
+    return fail(c, -5, "auxiliary stream / events");
+  return 0;
+}
+
 // ----------------------------------------------------------------------------- pitch / energy towers
 int run_pe_towers(Context& c, const float* d_x, const float* d_style, float* d_pitch, float* d_energy,
                   cudaStream_t st) {
@@ -486,12 +497,7 @@ int run_pe_towers(Context& c, const float* d_x, const float* d_style, float* d_p
   // stream with its own scratch, forked from / joined to `st` by events (under stream capture the fork becomes two
   // branches of the graph).  Their launches are small (124 tiles at hop 300): side by side they halve this stage.
   static const bool par = [] { const char* e = std::getenv("STTS_TOWERS_PAR"); return e == nullptr || e[0] != '0'; }();
-  if (par && c.st_aux == nullptr) {
-    if (cudaStreamCreateWithFlags(&c.st_aux, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaEventCreateWithFlags(&c.ev_fork, cudaEventDisableTiming) != cudaSuccess ||
-        cudaEventCreateWithFlags(&c.ev_join, cudaEventDisableTiming) != cudaSuccess)
-      return fail(c, -5, "auxiliary stream / events");
-  }
+  if (par) STTS_RET(ensure_aux(c));
   const char* tw[2] = {"F0", "N"};
   if (par) {
     STTS_CK(cudaEventRecord(c.ev_fork, st));
@@ -740,6 +746,22 @@ int run_source(Context& c, const float* d_pitch4_dense, const float* d_noise, co
   return source_core(c, S, d_noise, d_init_phase, d_out, st);
 }
 
+// harmonic-plus-noise source from P4 (packed pitch rows) and its STFT -> HS / HP   (generator.py:402-410)
+static int source_stft(Context& c, const float* d_noise, const float* d_init_phase, bool lean, cudaStream_t st) {
+  Stage S(c, st);
+  const RowMap map = c.L4.map();
+  Act &src = S.A("SRC"), &hs = S.A("HS"), &hp = S.A("HP");
+  STTS_RET(source_core(c, S, d_noise, d_init_phase, nullptr, st));
+  // STFT of the source -> |X|, atan2 phase: shared-memory FFT, stft_fft.cu
+  const bool keep32 = !(lean && S.twins);          // 16-bit fused path: only the fp16 twins the prior convs read
+  const double2* tw = reinterpret_cast<const double2*>(c.vec["stft_tw"]);
+  STTS_CK(stft_fft(src.f, src.ld, c.vec["win"], tw, tw + 1024, map, keep32 ? hs.f : nullptr, keep32 ? hp.f : nullptr,
+                   hs.ld, S.twins ? hs.g : nullptr, (S.twins && !one_pass_island("gen.amp_prior")) ? hs.l : nullptr,
+                   S.twins ? hp.g : nullptr, (S.twins && !one_pass_island("gen.phase_prior")) ? hp.l : nullptr, hs.ldg,
+                   st));
+  return 0;
+}
+
 // ----------------------------------------------------------------------------- generator
 // expects CATP[:, 0:512] = mel and P4 = pitch (packed rows)
 // lean: 16-bit mode keeps only what the prior convs read of the source spectrum (the fp16 twins of |X| and
@@ -756,15 +778,7 @@ int run_generator_core(Context& c, const float* d_style, const float* d_noise, c
   Act& yf = S.A("YF");
   float* gb = S.R<float>("GB_GEN");
   STTS_CK(style_fc(c.vec["gen.fc_W"], c.vec["gen.fc_b"], d_style, c.J_gen, 64, c.L4.n_seg, gb, st));
-  STTS_RET(source_core(c, S, d_noise, d_init_phase, nullptr, st));
-  {  // STFT of the source -> |X|, atan2 phase   (generator.py:407-410): shared-memory FFT, stft_fft.cu
-    const bool keep32 = !(lean && S.twins);        // 16-bit fused path: only the fp16 twins the prior convs read
-    const double2* tw = reinterpret_cast<const double2*>(c.vec["stft_tw"]);
-    STTS_CK(stft_fft(src.f, src.ld, c.vec["win"], tw, tw + 1024, map, keep32 ? hs.f : nullptr, keep32 ? hp.f : nullptr,
-                     hs.ld, S.twins ? hs.g : nullptr, (S.twins && !one_pass_island("gen.amp_prior")) ? hs.l : nullptr,
-                     S.twins ? hp.g : nullptr, (S.twins && !one_pass_island("gen.phase_prior")) ? hp.l : nullptr, hs.ldg,
-                     st));
-  }
+  STTS_RET(source_stft(c, d_noise, d_init_phase, lean, st));
   return run_generator_tail(c, d_style, d_audio, d_logamp, d_phase, st);
 }
 
@@ -907,9 +921,28 @@ int run_speech_frames(Context& c, const float* d_enc_tok, const int* d_cu_tok, c
   STTS_CK(upsample4(d_pitch, d_energy, d_cu_frames, map, S.R<float>("P4"), S.R<float>("E4"), st));
   STTS_RET(assemble_f0n(c, S, st));
   STTS_CK(transpose_in(d_noise_prior, c.L4.d_off[0], c.L4.d_cs, 128, map, noise.f, noise.ld, 0, nullptr, 0, 0, st));
+  // The source and its STFT depend on the pitch only: they run on the auxiliary stream next to the decoder and the
+  // flow (the fp64 FFT is instruction-bound at a quarter occupancy and leaves the tensor pipe to the decoder GEMMs)
+  // and join before the generator's prior convs read |X| / phase.
+  static const bool par = [] { const char* e = std::getenv("STTS_SRC_PAR"); return e == nullptr || e[0] != '0'; }();
+  if (!par) {
+    STTS_RET(run_decoder_core(c, d_style, st));
+    STTS_RET(run_prior_flow_core(c, xa, d_style, st));
+    return run_generator_core(c, d_style, d_noise_source, d_init_phase, d_audio, d_logamp, d_phase, st, /*lean=*/true);
+  }
+  if (!c.finalized || c.J_gen == 0) return fail(c, -3, "speech_predictor weights not loaded");
+  STTS_RET(ensure_aux(c));
+  STTS_CK(cudaEventRecord(c.ev_fork, st));
+  STTS_CK(cudaStreamWaitEvent(c.st_aux, c.ev_fork, 0));
+  STTS_RET(source_stft(c, d_noise_source, d_init_phase, /*lean=*/true, c.st_aux));
+  STTS_CK(cudaEventRecord(c.ev_join, c.st_aux));
+  c.launches -= 3;
   STTS_RET(run_decoder_core(c, d_style, st));
   STTS_RET(run_prior_flow_core(c, xa, d_style, st));
-  return run_generator_core(c, d_style, d_noise_source, d_init_phase, d_audio, d_logamp, d_phase, st, /*lean=*/true);
+  STTS_CK(style_fc(c.vec["gen.fc_W"], c.vec["gen.fc_b"], d_style, c.J_gen, 64, c.L4.n_seg, S.R<float>("GB_GEN"), st));
+  STTS_CK(cudaStreamWaitEvent(st, c.ev_join, 0));
+  c.launches -= 1;
+  return run_generator_tail(c, d_style, d_audio, d_logamp, d_phase, st);
 }
 
 }  // namespace stts
