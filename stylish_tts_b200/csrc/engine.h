@@ -136,7 +136,7 @@ int run_source(Context& c, const float* d_pitch4_dense, const float* d_noise, co
 int run_generator_core(Context& c, const float* d_style, const float* d_noise, const float* d_init_phase,
                        float* d_audio, float* d_logamp, float* d_phase, cudaStream_t st, bool lean = false);
 int run_generator_tail(Context& c, const float* d_style, float* d_audio, float* d_logamp, float* d_phase,
-                       cudaStream_t st);
+                       cudaStream_t st, bool priors_done = false);
 int run_generator_from_stft(Context& c, const float* d_mel, const float* d_style, const float* d_har_spec,
                             const float* d_har_phase, float* d_audio, float* d_logamp, float* d_phase,
                             cudaStream_t st);

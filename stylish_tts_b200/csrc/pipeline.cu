@@ -746,6 +746,21 @@ int run_source(Context& c, const float* d_pitch4_dense, const float* d_noise, co
   return source_core(c, S, d_noise, d_init_phase, d_out, st);
 }
 
+// amp / phase prior convs (k7) of |X| and the wrapped phase into columns 512 .. 1023 of the concat buffer
+// (generator.py:412-413).  Island class: their operands are the raw spectrum of the source (fp16 twins from the STFT).
+static int prior_convs(Context& c, cudaStream_t st) {
+  Stage S(c, st);
+  const RowMap map = c.L4.map();
+  Act &hs = S.A("HS"), &hp = S.A("HP"), &catp = S.A("CATP");
+  Epi e = S.epi(EPI_BIAS, catp, 512);
+  if (one_pass_island("gen.amp_head")) e.outl = nullptr;
+  STTS_RET(run_gemm(c, c.gemm["gen.amp_prior"], GC_ISLAND, &hs, 0, nullptr, 0, e, map, st));
+  Epi e2 = S.epi(EPI_BIAS, catp, 768);
+  if (one_pass_island("gen.phase_head")) e2.outl = nullptr;
+  STTS_RET(run_gemm(c, c.gemm["gen.phase_prior"], GC_ISLAND, &hp, 0, nullptr, 0, e2, map, st));
+  return 0;
+}
+
 // harmonic-plus-noise source from P4 (packed pitch rows) and its STFT -> HS / HP   (generator.py:402-410)
 static int source_stft(Context& c, const float* d_noise, const float* d_init_phase, bool lean, cudaStream_t st) {
   Stage S(c, st);
@@ -785,7 +800,7 @@ int run_generator_core(Context& c, const float* d_style, const float* d_noise, c
 // Generator.forward from the prior convs on (generator.py:412-433): expects HS / HP (|X| and phase of
 // the source), CATP[:, 0:512] = mel and GB_GEN (style FCs).
 int run_generator_tail(Context& c, const float* d_style, float* d_audio, float* d_logamp, float* d_phase,
-                       cudaStream_t st) {
+                       cudaStream_t st, bool priors_done) {
   Stage S(c, st);
   const RowMap map = c.L4.map();
   const RowMap map_p1 = c.L4.map_p1();
@@ -794,16 +809,7 @@ int run_generator_tail(Context& c, const float* d_style, float* d_audio, float* 
   Act& yf = S.A("YF");
   float* gb = S.R<float>("GB_GEN");
   (void)d_style;
-  {  // amp / phase prior convs (k7) into the concat buffer   (generator.py:412-413)
-    // island class: their operands are the raw |X| / wrapped phase of the source (fp16 twins written
-    // by the STFT epilogue)
-    Epi e = S.epi(EPI_BIAS, catp, 512);
-    if (one_pass_island("gen.amp_head")) e.outl = nullptr;
-    STTS_RET(run_gemm(c, c.gemm["gen.amp_prior"], GC_ISLAND, &hs, 0, nullptr, 0, e, map, st));
-    Epi e2 = S.epi(EPI_BIAS, catp, 768);
-    if (one_pass_island("gen.phase_head")) e2.outl = nullptr;
-    STTS_RET(run_gemm(c, c.gemm["gen.phase_prior"], GC_ISLAND, &hp, 0, nullptr, 0, e2, map, st));
-  }
+  if (!priors_done) STTS_RET(prior_convs(c, st));
   {  // projector 1x1 on cat[mel, logamp_prior, phase_prior]   (generator.py:414)
     Epi e = S.epi(EPI_BIAS, xg, 0);
     e.outh = nullptr;
@@ -923,7 +929,7 @@ int run_speech_frames(Context& c, const float* d_enc_tok, const int* d_cu_tok, c
   STTS_CK(transpose_in(d_noise_prior, c.L4.d_off[0], c.L4.d_cs, 128, map, noise.f, noise.ld, 0, nullptr, 0, 0, st));
   // The source and its STFT depend on the pitch only: they run on the auxiliary stream next to the decoder and the
   // flow (the fp64 FFT is instruction-bound at a quarter occupancy and leaves the tensor pipe to the decoder GEMMs)
-  // and join before the generator's prior convs read |X| / phase.
+  // together with the prior convs that read |X| / phase, and join before the generator's projector.
   static const bool par = [] { const char* e = std::getenv("STTS_SRC_PAR"); return e == nullptr || e[0] != '0'; }();
   if (!par) {
     STTS_RET(run_decoder_core(c, d_style, st));
@@ -935,6 +941,7 @@ int run_speech_frames(Context& c, const float* d_enc_tok, const int* d_cu_tok, c
   STTS_CK(cudaEventRecord(c.ev_fork, st));
   STTS_CK(cudaStreamWaitEvent(c.st_aux, c.ev_fork, 0));
   STTS_RET(source_stft(c, d_noise_source, d_init_phase, /*lean=*/true, c.st_aux));
+  STTS_RET(prior_convs(c, c.st_aux));              // columns 512 .. 1023 of CATP; the flow's post_flow writes 0 .. 511
   STTS_CK(cudaEventRecord(c.ev_join, c.st_aux));
   c.launches -= 3;
   STTS_RET(run_decoder_core(c, d_style, st));
@@ -942,7 +949,7 @@ int run_speech_frames(Context& c, const float* d_enc_tok, const int* d_cu_tok, c
   STTS_CK(style_fc(c.vec["gen.fc_W"], c.vec["gen.fc_b"], d_style, c.J_gen, 64, c.L4.n_seg, S.R<float>("GB_GEN"), st));
   STTS_CK(cudaStreamWaitEvent(st, c.ev_join, 0));
   c.launches -= 1;
-  return run_generator_tail(c, d_style, d_audio, d_logamp, d_phase, st);
+  return run_generator_tail(c, d_style, d_audio, d_logamp, d_phase, st, /*priors_done=*/true);
 }
 
 }  // namespace stts
