@@ -863,10 +863,26 @@ int run_generator_tail(Context& c, const float* d_style, float* d_audio, float* 
                  S.twins ? phn.g : nullptr, ampn.ld, one_pass_island("gen.amp_head") ? nullptr : ampn.l,
                  one_pass_island("gen.phase_head") ? nullptr : phn.l, st));   // 16-bit mode: only what the heads read
   {
+    // small batches (fewer row tiles than SMs: latency mode): the two heads run side by side on two streams
+    static const bool hpar = [] { const char* e = std::getenv("STTS_HEADS_PAR"); return e == nullptr || e[0] != '0'; }();
+    const bool fork = hpar && c.L4.n_tiles < 148;
     Epi e = S.epi(EPI_BIAS, la, 0);
-    STTS_RET(run_gemm(c, c.gemm["gen.amp_head"], GC_ISLAND, &ampn, 0, &catp, 512, e, map, st));
     Epi e2 = S.epi(EPI_BIAS, ph, 0);
-    STTS_RET(run_gemm(c, c.gemm["gen.phase_head"], GC_ISLAND, &phn, 0, &catp, 768, e2, map, st));
+    if (fork) {
+      STTS_RET(ensure_aux(c));
+      STTS_CK(cudaEventRecord(c.ev_fork, st));
+      STTS_CK(cudaStreamWaitEvent(c.st_aux, c.ev_fork, 0));
+      STTS_RET(run_gemm(c, c.gemm["gen.phase_head"], GC_ISLAND, &phn, 0, &catp, 768, e2, map, c.st_aux));
+      STTS_CK(cudaEventRecord(c.ev_join, c.st_aux));
+      c.launches -= 3;
+    }
+    STTS_RET(run_gemm(c, c.gemm["gen.amp_head"], GC_ISLAND, &ampn, 0, &catp, 512, e, map, st));
+    if (fork) {
+      STTS_CK(cudaStreamWaitEvent(st, c.ev_join, 0));
+      c.launches -= 1;
+    } else {
+      STTS_RET(run_gemm(c, c.gemm["gen.phase_head"], GC_ISLAND, &phn, 0, &catp, 768, e2, map, st));
+    }
   }
   // replicate pad + exp / cos / sin -> inverse DFT x window -> overlap-add, envelope, tanh
   STTS_CK(polar_spec(la.f, ph.f, la.ld, 1025, map, S.twins ? nullptr : spec.f, spec.ld, S.twins ? spec.g : nullptr,
