@@ -67,6 +67,14 @@ int stts_set_precision(stts_ctx* ctx, int precision);
  * several contexts feeding one GPU concurrently the waiting CTAs cost 1-2 %, so turn it off
  * there.  No reference counterpart (launch mechanics).                                          */
 int stts_set_pdl(stts_ctx* ctx, int on);
+/* Small-batch kernel shapes (on by default): when a batch is so small that the throughput shapes
+ * would occupy a fraction of the SMs (one 5 s utterance: 13 row tiles, 4-32 attention CTAs), the
+ * GEMMs take 128- instead of 256-column tiles and the attention kernels one query per lane group
+ * with 4-16 key sets (one utterance: 2.77 -> 2.56 ms with the split-K LayerNorm GEMM).  The shapes
+ * differ in summation order: a small batch and the same utterances inside a large batch agree to
+ * rounding (16-bit mode: to its operand rounding), not bit for bit; off = one shape per layer
+ * whatever the batch.  No reference counterpart (launch mechanics).                              */
+int stts_set_small_batch_shapes(stts_ctx* ctx, int on);
 
 /* ---- packed layout ---------------------------------------------------------------------------
  * len_f[b]  = frames at hop 300 (F), len_f4[b] = frames at hop 75 (normally 4 F).  Either may be

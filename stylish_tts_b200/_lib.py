@@ -20,6 +20,7 @@ SIGNATURES = {
     "stts_finalize_weights": (_i, [_vp]),
     "stts_set_precision": (_i, [_vp, _i]),
     "stts_set_pdl": (_i, [_vp, _i]),
+    "stts_set_small_batch_shapes": (_i, [_vp, _i]),
     "stts_set_layout": (_i, [_vp, _i, C.POINTER(_i), C.POINTER(_i)]),
     "stts_workspace_bytes": (_i64, [_vp]),
     "stts_set_token_layout": (_i, [_vp, _i, C.POINTER(_i)]),

@@ -20,6 +20,7 @@ struct DeviceGuard {
     cudaGetDevice(&prev);
     if (prev != dev) cudaSetDevice(dev); else prev = -1;
     pdl_set(c.pdl);
+    small_shapes_set(c.small_shapes);
   }
   ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
 };
@@ -90,6 +91,12 @@ int stts_set_precision(stts_ctx* ctx, int precision) {
 int stts_set_pdl(stts_ctx* ctx, int on) {
   if (!ctx) return STTS_ERR_BAD_ARG;
   ctx->c.pdl = on ? 1 : 0;
+  return STTS_OK;
+}
+
+int stts_set_small_batch_shapes(stts_ctx* ctx, int on) {
+  if (!ctx) return STTS_ERR_BAD_ARG;
+  ctx->c.small_shapes = on ? 1 : 0;
   return STTS_OK;
 }
 

@@ -52,6 +52,12 @@ __device__ __forceinline__ void pdl_enter() { pdl_wait(); pdl_trigger(); }
 
 bool pdl_enabled();     // pipeline.cu: the calling context's choice (stts_set_pdl), STTS_PDL=0 forces it off
 void pdl_set(int on);   // -1: default (on)
+// Small-batch kernel shapes (narrower GEMM column tiles, more key sets per attention query when the default shape
+// would leave most SMs idle): the calling context's choice (stts_set_small_batch_shapes), default on.  The shapes
+// differ in summation order, so results of a small batch and of the same utterances inside a large batch agree to
+// rounding, not bit for bit; a caller that needs the latter turns them off.
+bool small_shapes_enabled();
+void small_shapes_set(int on);   // -1: default (on)
 
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
@@ -65,6 +71,27 @@ inline cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, siz
   at[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = at;
   cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<Args&&>(args)...);
+}
+
+// the same with a thread-block cluster of `cluster_x` CTAs along x (grid.x must be a multiple of it)
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_k_cluster(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, int cluster_x,
+                                    Args&&... args) {
+  cudaLaunchConfig_t cfg;
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[2];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = (unsigned)cluster_x;
+  at[0].val.clusterDim.y = 1;
+  at[0].val.clusterDim.z = 1;
+  at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl_enabled() ? 2 : 1;
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<Args&&>(args)...);
 }
 

@@ -66,6 +66,7 @@ enum GemmClass { GC_BODY = 0, GC_ISLAND = 1 };  // ISLAND: STFT, output heads, i
 struct Context {
   int device = 0;
   int precision = 0;
+  int small_shapes = -1;                       // small-batch kernel shapes (stts_set_small_batch_shapes): -1 / 1 on, 0 off
   int pdl = -1;                                // programmatic dependent launch: -1 default (on), 0 off, 1 on
   std::string err;
   int64_t launches = 0;

@@ -319,13 +319,12 @@ __device__ __forceinline__ void stft_slab(const Epi& e, const float* __restrict_
 // two-pass variance as row_ln_kernel).  The normalised values are transposed through the staging block so that the
 // affine / ReLU / stores run lane-per-column: coalesced fp32 rows and fp16 split twins.  `res` may alias `out`
 // (a row is read and written by this warp group only, writes follow the second barrier).
-__device__ __forceinline__ void ln_epilogue(const Epi& e, float acc_scale, uint32_t taddr, float* stg, float* lnbuf, int slab,
-                                            int q, int lane, int row0, int nrows, int seg, int n_live) {
+// v: this lane's row of raw accumulators, columns [64 slab, 64 slab + 64)
+__device__ __forceinline__ void ln_tail(const Epi& e, float acc_scale, float (&v)[64], float* stg, float* lnbuf, int slab,
+                                        int q, int lane, int row0, int nrows, int seg, int n_live) {
   const int c0 = slab * 64;
   const int rl = q * 32 + lane;                       // row inside the tile
   const bool live = lane < nrows;
-  float v[64];
-  tmem_ld64(taddr, v);
   const float* rp = (e.res != nullptr && live) ? e.res + (size_t)(row0 + lane) * e.ldr + e.rcol0 + c0 : nullptr;
   float s = 0.f;
 #pragma unroll
@@ -389,6 +388,26 @@ __device__ __forceinline__ void ln_epilogue(const Epi& e, float acc_scale, uint3
   }
 }
 
+__device__ __forceinline__ void ln_epilogue(const Epi& e, float acc_scale, uint32_t taddr, float* stg, float* lnbuf, int slab,
+                                            int q, int lane, int row0, int nrows, int seg, int n_live) {
+  float v[64];
+  tmem_ld64(taddr, v);
+  ln_tail(e, acc_scale, v, stg, lnbuf, slab, q, lane, row0, nrows, seg, n_live);
+}
+
+// thread-block cluster helpers of the split-K LayerNorm GEMM (SK = 4 below)
+__device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release;" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire;" ::: "memory"); }
+__device__ __forceinline__ uint32_t cluster_map(uint32_t local_smem_addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_smem_addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void st_cluster_f4(uint32_t addr, float a, float b, float c, float d) {
+  asm volatile("st.shared::cluster.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+constexpr int kSkPitch = 132;   // floats per row of the exchanged partial accumulators (16-byte rows, 132 % 32 = 4)
+
 // MODE_F16 doubles as the one-pass fp16 GEMM (runtime instruction-descriptor formats), MODE_F16X3 is
 // the three-pass fp16 split (hi*hi + hi*lo + lo*hi, fp32-grade), MODE_TF32X3 the tf32 split on fp32 operands
 enum { MODE_F16 = 0, MODE_TF32X3 = 1, MODE_F16X3 = 2 };
@@ -428,7 +447,14 @@ struct TcParams {
   int park;             // mbarrier waits with a suspend hint: 1 = the epilogue warps' accumulator waits, 2 = all
 };
 
-template <int MODE, int BN, int KIND, int OCC = 1>
+// SK = 4 (EPI_LN, BN = 128 only): split-K over a cluster of four CTAs.  The LayerNorm GEMMs have ONE column tile (the
+// whole row is normalised), so a long-K layer (text-encoder ffn2: K = 1 536, three MMAs per k-step in the split modes)
+// was one CTA per row tile streaming 1.5 MB of operands through one SM: 28 us per launch however small the batch.
+// Here CTA r of the cluster runs chunks [r n / 4, (r + 1) n / 4) of the K loop; then the four 128 x 128 fp32 partial
+// accumulators are reduce-scattered by row quarter through distributed shared memory (quarter q of every CTA goes to
+// CTA q), and CTA q finishes its 32 rows (sum in rank order, bias, residual, LayerNorm, twins): K loop and epilogue are
+// both four times shorter, no operand is loaded twice, and the result does not depend on timing.
+template <int MODE, int BN, int KIND, int OCC = 1, int SK = 1>
 __global__ void __launch_bounds__(64 + 2 * BN, OCC)
 conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant__ CUtensorMap mapA1,
                     const __grid_constant__ CUtensorMap mapA0lo, const __grid_constant__ CUtensorMap mapA1lo,
@@ -441,7 +467,11 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
   if (seg < 0) return;
   const int nvalid = map.tile_nvalid[tile];
   const int m0 = tile * 128;
-  const int n0 = blockIdx.x * BN;
+  static_assert(SK == 1 || (SK == 4 && KIND == EPI_LN && BN == 128 && OCC == 1), "split-K: LayerNorm epilogue only");
+  const int n0 = (SK > 1) ? 0 : blockIdx.x * BN;
+  const int krank = (SK > 1) ? blockIdx.x : 0;            // cluster (SK, 1, 1), gridDim.x == SK: rank in the cluster
+  const int ch_begin = (SK > 1) ? (p.n_chunks * krank) / SK : 0;
+  const int ch_end = (SK > 1) ? (p.n_chunks * (krank + 1)) / SK : p.n_chunks;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // Tail column tile with <= 16 live columns (N = 1 025 output heads, N = 2 050 STFT): 16-row weight boxes and
   // N = 16 MMAs instead of a full BN-wide tile of padding (mapWt / mapWtlo: the same weights, box of 16 rows)
@@ -494,7 +524,8 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
       const CUtensorMap* mw = tail ? &mapWt : &mapW;
       const CUtensorMap* mwlo = tail ? &mapWtlo : &mapWlo;
       const uint32_t tx = tail ? C::kTxBytes - (C::kSplit ? 2u : 1u) * ((uint32_t)C::kBTile - kTailBytes) : C::kTxBytes;
-      for (int ch = 0; ch < p.n_chunks; ++ch) {
+      for (int ch = 0; ch < ch_end; ++ch) {
+        if (SK == 1 || ch >= ch_begin) {
         mbar_wait(&empty[stage], phase ^ 1, 1, p.park >= 2);
         uint8_t* sp = stage_ptr(stage);
         mbar_expect_tx(&full[stage], tx);
@@ -510,17 +541,19 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
         } else {
           tma_load_2d(sp + C::kATile, mw, &full[stage], kcol, wrow);
         }
+        if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+        }
         kcol += C::kBK;
         if (++cc == p.cin_chunks[ks]) { cc = 0; if (++tap == p.taps[ks]) { tap = 0; ++ks; } }
-        if (++stage == C::kStages) { stage = 0; phase ^= 1; }
       }
     }
+    if constexpr (SK > 1) { cluster_arrive(); cluster_wait(); cluster_arrive(); cluster_wait(); }
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int ch = 0; ch < p.n_chunks; ++ch) {
+      for (int ch = ch_begin; ch < ch_end; ++ch) {
         mbar_wait(&full[stage], phase, 2, p.park >= 2);
         if constexpr (C::kTF32) mbar_wait(&conv[stage], phase, 3, p.park >= 2);
         tc_fence_after();
@@ -531,12 +564,12 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
           if constexpr (C::kSplit) {
             const uint32_t a_lo = a_hi + C::kATile, b_hi = a_hi + 2 * C::kATile, b_lo = b_hi + C::kBTile;
             // small terms first, then the leading term
-            tc_mma<C::kTF32>(tmem_base, make_sdesc(a_lo + koff), make_sdesc(b_hi + koff), idesc, (ch | k) != 0);
+            tc_mma<C::kTF32>(tmem_base, make_sdesc(a_lo + koff), make_sdesc(b_hi + koff), idesc, ((ch - ch_begin) | k) != 0);
             tc_mma<C::kTF32>(tmem_base, make_sdesc(a_hi + koff), make_sdesc(b_lo + koff), idesc, 1);
             tc_mma<C::kTF32>(tmem_base, make_sdesc(a_hi + koff), make_sdesc(b_hi + koff), idesc, 1);
           } else {
             const uint32_t b = a_hi + C::kATile;
-            tc_mma<false>(tmem_base, make_sdesc(a_hi + koff), make_sdesc(b + koff), idesc, (ch | k) != 0);
+            tc_mma<false>(tmem_base, make_sdesc(a_hi + koff), make_sdesc(b + koff), idesc, ((ch - ch_begin) | k) != 0);
           }
         }
         tc_commit(&empty[stage]);
@@ -544,6 +577,7 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
       }
       tc_commit(accum);
     }
+    if constexpr (SK > 1) { cluster_arrive(); cluster_wait(); cluster_arrive(); cluster_wait(); }
   } else {
     // ------------------------------------------------------------ converter (tf32x3) + epilogue
     if constexpr (C::kTF32) {
@@ -551,7 +585,7 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
       constexpr int kConvThreads = 32 * C::kEpiWarps;
       int stage = 0;
       uint32_t phase = 0;
-      for (int ch = 0; ch < p.n_chunks; ++ch) {
+      for (int ch = ch_begin; ch < ch_end; ++ch) {
         mbar_wait(&full[stage], phase, 4, p.park >= 1);
         float4* hi = reinterpret_cast<float4*>(stage_ptr(stage));
         float4* lo = reinterpret_cast<float4*>(stage_ptr(stage) + C::kATile);
@@ -588,6 +622,43 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
     nrows = nrows < 0 ? 0 : (nrows > 32 ? 32 : nrows);
     const int seg_first = (epi.seg_start != nullptr) ? epi.seg_start[seg] : -1;
     const int c = (ew >> 2) * 64;
+    if constexpr (KIND == EPI_LN && SK > 1) {
+      // every CTA of the cluster has finished its K range: all four operand rings are free and take the partials
+      cluster_arrive();
+      cluster_wait();
+      float* part = reinterpret_cast<float*>(smem);            // [SK source CTAs][32 rows][kSkPitch]
+      const int slab = ew >> 2;
+      if (c < epi.N) {
+        float v[64];
+        tmem_ld64(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c, v);
+        const uint32_t dst = cluster_map(smem_u32(part + (krank * 32 + lane) * kSkPitch + c), (uint32_t)q);
+#pragma unroll
+        for (int j = 0; j < 64; j += 4) st_cluster_f4(dst + j * 4, v[j], v[j + 1], v[j + 2], v[j + 3]);
+      }
+      cluster_arrive();
+      cluster_wait();
+      const int n_live = (epi.N + 63) / 64;
+      if (ew < n_live) {                       // warps ew = 0 .. n_live - 1 finish this CTA's row quarter (= krank)
+        const int c0 = ew * 64;
+        float v[64];
+#pragma unroll
+        for (int j = 0; j < 64; j += 4) {
+          float4 a = *reinterpret_cast<const float4*>(part + lane * kSkPitch + c0 + j);
+#pragma unroll
+          for (int sr = 1; sr < SK; ++sr) {
+            const float4 b = *reinterpret_cast<const float4*>(part + (sr * 32 + lane) * kSkPitch + c0 + j);
+            a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+          }
+          v[j] = a.x; v[j + 1] = a.y; v[j + 2] = a.z; v[j + 3] = a.w;
+        }
+        float* tail_smem = part + SK * 32 * kSkPitch;
+        int nr = nvalid - krank * 32;
+        nr = nr < 0 ? 0 : (nr > 32 ? 32 : nr);
+        ln_tail(epi, p.acc_scale, v, tail_smem + ew * (32 * kStgLd4), tail_smem + 2 * (32 * kStgLd4), ew, krank, lane,
+                m0 + krank * 32, nr, seg, n_live);
+      }
+      (void)slab;
+    } else
     if constexpr (KIND == EPI_LN) {
       if (c < epi.N) {                         // warp-uniform; one column tile (n0 == 0)
         float* lnbuf = reinterpret_cast<float*>(smem) + C::kEpiWarps * (32 * kStgLd4);
@@ -1339,7 +1410,7 @@ bool get_map(const void* base, int rows, int ld, int elem, int box_rows, CUtenso
 int mbar_park_mode();
 bool m256_fills_gpu(const ConvGemm& g, const RowMap& map);
 
-template <int MODE, int BN, int KIND, int OCC = 1>
+template <int MODE, int BN, int KIND, int OCC = 1, int SK = 1>
 cudaError_t launch_one(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
   using C = Cfg<MODE, BN, OCC>;
   constexpr int elem = C::kElem;
@@ -1409,12 +1480,20 @@ cudaError_t launch_one(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
     mWtlo = mWt;
     if (MODE == MODE_F16X3 && !get_map(g.Wl, g.Npad, g.Ktot, 2, 16, &mWtlo)) return cudaErrorNotSupported;
   }
-  auto kern = conv_gemm_tc_kernel<MODE, BN, KIND, OCC>;
+  auto kern = conv_gemm_tc_kernel<MODE, BN, KIND, OCC, SK>;
   static bool attr_done = false;
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmem);
     if (e != cudaSuccess) return e;
     attr_done = true;
+  }
+  if constexpr (SK > 1) {
+    static_assert(C::kStages * C::kStageBytes >= (SK * 32 * kSkPitch + 2 * 32 * kStgLd4 + 2 * 4 * 128) * 4, "split-K staging");
+    if (p.n_chunks < 2 * SK || g.epi.N > BN) return cudaErrorInvalidValue;
+    dim3 grid(SK, map.n_tiles);
+    launch_k_cluster(kern, grid, C::kThreads, C::kSmem, st, SK, mA[0], mA[1], mAlo[0], mAlo[1], mW, mWlo, mWt, mWtlo, p, g.epi,
+                     map);
+    return cudaGetLastError();
   }
   dim3 grid((g.epi.N + BN - 1) / BN, map.n_tiles);
   launch_k(kern, grid, C::kThreads, C::kSmem, st, mA[0], mA[1], mAlo[0], mAlo[1], mW, mWlo, mWt, mWtlo, p, g.epi, map);
@@ -1551,6 +1630,14 @@ int occ2_max_chunks() {
 template <int MODE, int KIND>
 cudaError_t launch_bn(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
   if constexpr (KIND == EPI_LN) {            // one column tile must hold the whole row
+    if constexpr (MODE != MODE_F16) {
+      // long-K LayerNorm GEMMs (text-encoder ffn2 / conv prelude): split-K over a cluster of four CTAs.
+      // STTS_LN_SPLITK=<min K>: smallest reduction length (elements) that takes it, 0 = never; default 512
+      static const int min_k = [] { const char* e = std::getenv("STTS_LN_SPLITK"); return e != nullptr ? std::atoi(e) : 512; }();
+      int ktot = 0;
+      for (int s = 0; s < g.n_kseg; ++s) ktot += g.seg[s].taps * g.seg[s].cin_pad;
+      if (min_k > 0 && ktot >= min_k && g.epi.N <= 128) return launch_one<MODE, 128, KIND, 1, 4>(g, map, st);
+    }
     if (g.epi.N <= 128) return launch_one<MODE, 128, KIND>(g, map, st);
     if (g.epi.N <= 256 && g.Npad % 256 == 0) return launch_one<MODE, 256, KIND>(g, map, st);
     return cudaErrorInvalidValue;
@@ -1570,6 +1657,14 @@ cudaError_t launch_bn(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
   // tiles per stage) use it for the wide STFT only.
   static const bool split256 = [] { const char* e = std::getenv("STTS_SPLIT_BN256"); return e == nullptr || e[0] != '0'; }();
   const bool wide = g.epi.N > 128 && g.Npad % 256 == 0;
+  if constexpr (MODE == MODE_F16) {
+    // Small batches (one 5 s utterance = 13 row tiles): with 256-column tiles a long-K conv is 26 CTAs of ~13 us of
+    // tensor work each on 148 SMs.  128-column tiles double the CTAs and halve the per-CTA main loop.
+    // STTS_SMALL_GRID=<n>: grids of fewer than n 256-column CTAs take the 128-column kernel (0 = never)
+    static const int small_grid = [] { const char* e = std::getenv("STTS_SMALL_GRID"); return e != nullptr ? std::atoi(e) : 74; }();
+    if (wide && small_shapes_enabled() && (long long)map.n_tiles * ((g.epi.N + 255) / 256) < small_grid)
+      return launch_one<MODE, 128, KIND>(g, map, st);
+  }
   if constexpr (MODE == MODE_F16) {
     // persistent variant: measured faster for long-K, multi-column-tile layers (decoder convs -4 .. -17 %,
     // pwconv2 -7 %, inverse DFT -11 %, output heads -5 %) and slower for the short-K / epilogue-bound ones

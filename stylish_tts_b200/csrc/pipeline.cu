@@ -21,6 +21,10 @@ bool pdl_enabled() {
   return env_on && tl_pdl != 0;
 }
 
+namespace { thread_local int tl_small = -1; }
+void small_shapes_set(int on) { tl_small = on; }
+bool small_shapes_enabled() { return tl_small != 0; }
+
 int fail(Context& c, int code, const std::string& msg) {
   c.err = msg;
   return code;

@@ -685,6 +685,18 @@ cudaError_t attention(const float* Q, int ldq, int qcol, const float* K, int ldk
     return launch_attention_stream<DD, LL, QQ, NN, KK, CC>(Q, ldq, qcol, K, ldk, kcol, V, ldv, vcol, H, scale, rd,    \
                                                            rope_tab, qmap, kmap, max_tq, q_tok, q_cu, band, out, ldo, \
                                                            outg, outl, ldh, st);
+    // Small batches (one utterance: 4 .. 32 CTAs with the throughput shapes below, each a serial walk over the keys):
+    // one query per lane group and 4 .. 16 key sets, i.e. 8 .. 16 queries per CTA -- four to eight times as many CTAs,
+    // each with a quarter of the serial chain.  STTS_ATT_SMALL=<n>: taken when the throughput shape would launch
+    // fewer than n CTAs (default 74 = half the SMs; 0 = never).
+    static const int small = [] { const char* e = std::getenv("STTS_ATT_SMALL"); return e != nullptr ? std::atoi(e) : 74; }();
+    const int qpb_default = (D == 40) ? 128 : 64;
+    if (small_shapes_enabled() && (long long)((max_tq + qpb_default - 1) / qpb_default) * H * qmap.n_seg < small) {
+      STTS_ATTS(16, 1, 1, 128, 16, 128)  // 8 queries per CTA, 16 key sets
+      STTS_ATTS(40, 1, 1, 128, 8, 64)    // 16 frames per CTA, 8 key sets
+      STTS_ATTS(96, 4, 1, 256, 8, 64)    // 8 queries per CTA, 4 lanes x 24 features, 8 key sets
+      STTS_ATTS(160, 8, 1, 256, 4, 64)   // 8 queries per CTA, 8 lanes x 20 features, 4 key sets
+    }
     // measured per launch on the C2 batch (ncu): more key sets / queries per lane group than these are slower
     STTS_ATTS(16, 1, 2, 128, 4, 64)    // text encoders: 64 queries per CTA (2 per lane), 4 key sets          30.5 us
     STTS_ATTS(40, 1, 2, 128, 2, 64)    // cross attention: 128 frames per CTA, 2 key sets                     145 us

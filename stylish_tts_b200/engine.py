@@ -101,6 +101,10 @@ class Engine:
         """Programmatic dependent launch of this context's kernels (default on; see stts_set_pdl)."""
         self._check(self.lib.stts_set_pdl(self.h, 1 if on else 0))
 
+    def set_small_batch_shapes(self, on: bool):
+        """Small-batch kernel shapes of this context (default on; see stts_set_small_batch_shapes)."""
+        self._check(self.lib.stts_set_small_batch_shapes(self.h, 1 if on else 0))
+
     # ------------------------------------------------------------------ layout
     def set_layout(self, len_f: Optional[Iterable[int]], len_f4: Optional[Iterable[int]]):
         lf = [int(x) for x in len_f] if len_f is not None else None

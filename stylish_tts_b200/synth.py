@@ -10,6 +10,7 @@ only draws the three noise tensors).
 """
 from __future__ import annotations
 
+import os
 from typing import Dict, List, Optional, Sequence
 
 import torch
@@ -19,6 +20,9 @@ from .config import ModelConfig
 from .engine import Engine
 from .modules.frame_rate import build_model
 from .modules.token_rate import TokenPack
+
+
+_CHAIN_ORDER = tuple(os.environ.get("STTS_CHAIN_ORDER", "pe,dp,sp").split(","))
 
 
 class Synthesizer:
@@ -194,23 +198,37 @@ class Synthesizer:
         s_dp.wait_stream(cur)
         s_sp.wait_stream(cur)
 
-        # ---- durations: text encoder -> style -> prosody + duration_proj -> argmax rule   [stream s_dp]
-        with torch.cuda.stream(s_dp):
-            dp_mu, _ = eng.text_encoder("duration_predictor", tok, mc.inter_dim, want_x=False)
-            dp_style = eng.text_style_encoder("duration_predictor", None)
-            _, logits = eng.prosody_encoder("duration_predictor", dp_mu, dp_style, mc.inter_dim + mc.style_dim,
-                                            want_logits=True, want_out=False)
-            dur_pred = eng.durations(logits)                                    # int32 [sum T]
-        # ---- speech text / style encoders                                                 [stream s_sp]
-        with torch.cuda.stream(s_sp):
-            enc_tok, _ = eng.text_encoder("speech_predictor", tok, mc.inter_dim, want_x=False)
-            style = eng.text_style_encoder("speech_predictor", None)
-        # ---- pitch / energy token-rate part                                               [current stream]
         pe_inter = mc.pitch_energy_predictor.inter_dim
-        pe_mu, _ = eng.text_encoder("pe_text_encoder", tok, pe_inter, want_x=False)
-        pe_style = eng.text_style_encoder("pe_text_style_encoder", None)
-        prosody, _ = eng.prosody_encoder("pitch_energy_predictor", pe_mu, pe_style, pe_inter + mc.style_dim,
-                                         want_out=want_intermediates)
+        out = {}
+
+        def chain_dp():      # durations: text encoder -> style -> prosody + duration_proj -> argmax rule   [stream s_dp]
+            with torch.cuda.stream(s_dp):
+                dp_mu, _ = eng.text_encoder("duration_predictor", tok, mc.inter_dim, want_x=False)
+                dp_style = eng.text_style_encoder("duration_predictor", None)
+                _, logits = eng.prosody_encoder("duration_predictor", dp_mu, dp_style, mc.inter_dim + mc.style_dim,
+                                                want_logits=True, want_out=False)
+                out["dp"] = (dp_mu, dp_style, logits, eng.durations(logits))        # durations: int32 [sum T]
+
+        def chain_sp():      # speech text / style encoders                                                [stream s_sp]
+            with torch.cuda.stream(s_sp):
+                enc_tok, _ = eng.text_encoder("speech_predictor", tok, mc.inter_dim, want_x=False)
+                out["sp"] = (enc_tok, eng.text_style_encoder("speech_predictor", None))
+
+        def chain_pe():      # pitch / energy token-rate part                                            [current stream]
+            pe_mu, _ = eng.text_encoder("pe_text_encoder", tok, pe_inter, want_x=False)
+            pe_style = eng.text_style_encoder("pe_text_style_encoder", None)
+            prosody, _ = eng.prosody_encoder("pitch_energy_predictor", pe_mu, pe_style, pe_inter + mc.style_dim,
+                                             want_out=want_intermediates)
+            out["pe"] = (pe_mu, pe_style, prosody)
+
+        # Enqueue order = node order of a captured graph, and a replay releases the branches in that order, tens of
+        # microseconds apart: the two chains the length regulation waits for go first, the speech encoders (needed
+        # only after the pitch towers) last.
+        for name in _CHAIN_ORDER:
+            {"dp": chain_dp, "sp": chain_sp, "pe": chain_pe}[name]()
+        dp_mu, dp_style, logits, dur_pred = out["dp"]
+        enc_tok, style = out["sp"]
+        pe_mu, pe_style, prosody = out["pe"]
 
         cur.wait_stream(s_dp)
         if not capturing:

@@ -211,13 +211,27 @@ def test_full_size_batch_properties_f16():
         assert audio_a[i].numel() == 300 * f
         assert bool(torch.isfinite(audio_a[i]).all()) and float(audio_a[i].abs().max()) <= 1.0
         assert torch.equal(b["audio"][i], c["audio"][i]), i                  # run-to-run bit stable
-    worst = 0.0
-    for i in (0, 7, 19, 31, int(max(range(len(frames)), key=lambda k: frames[k])),
-              int(min(range(len(frames)), key=lambda k: frames[k]))):
+    # Utterances do not interact.  A batch of one takes the small-batch kernel shapes (other summation orders in the
+    # attention kernels: fp32 rounding noise that the fp16 operand rounding of the 16-bit mode amplifies to its own
+    # error level), so the strict comparison is made with one shape per layer whatever the batch ...
+    worst, worst_small = 0.0, 0.0
+    picks = (0, 7, 19, 31, int(max(range(len(frames)), key=lambda k: frames[k])),
+             int(min(range(len(frames)), key=lambda k: frames[k])))
+    syn.engine.set_small_batch_shapes(False)
+    try:
+        for i in picks:
+            one = syn.synthesize([tokens[i]], durations=[durs[i]], noise=[noise[i]], pitch_energy=[pe[i]])
+            worst = max(worst, maxabs(one["audio"][0], c["audio"][i]))
+    finally:
+        syn.engine.set_small_batch_shapes(True)
+    # ... and the small-batch shapes are held to the 16-bit mode's own tolerance against the batch result
+    for i in picks:
         one = syn.synthesize([tokens[i]], durations=[durs[i]], noise=[noise[i]], pitch_energy=[pe[i]])
-        worst = max(worst, maxabs(one["audio"][0], c["audio"][i]))
+        worst_small = max(worst_small, maxabs(one["audio"][0], c["audio"][i]))
     _log("f16.fullsize.alone_vs_batch", worst)
-    assert worst <= 2e-5, worst                                              # utterances do not interact
+    _log("f16.fullsize.alone_small_shapes_vs_batch", worst_small)
+    assert worst <= 2e-5, worst
+    assert worst_small <= 1e-3, worst_small
 
 
 def test_long_form_60s_16bit_against_fp32_grade_modes():
