@@ -1151,14 +1151,24 @@ conv_gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap mapA0, const 
 //   x += res, skip (+)= skip                                               (EPI_RESSKIP, coalesced)
 // The conv reads +-2 halo rows of neighbouring tiles, so the updated 16-bit twin of x goes to a second
 // buffer (ping-pong per layer); the fp32 master is only touched by the tile that owns the rows.
-struct WnCfg {
+// OCC = 2: two CTAs per SM, so that the gate / res-skip epilogues of one tile overlap the loads and MMAs of another
+// (the phases of ONE tile are strictly sequential: ~5 us of loads + MMA, ~2 us gate, ~4 us read-modify-write of x / skip).
+// What makes it fit: two stages instead of three (two CTAs = four in flight per SM), eight epilogue warps with two
+// column slabs each (2 x 320 threads x <= 102 registers), the gated activations in the A slots of the two stages that
+// only carry res/skip WEIGHTS at that point (all conv MMAs have completed), and the second accumulator over the
+// columns of the first (the gate epilogue has read them): 98 KB of shared memory and 256 TMEM columns per CTA.
+template <int OCC>
+struct WnCfgT {
   static constexpr int kBK = 64, kUmmaK = 16;
   static constexpr int kATile = 128 * 128, kBTile = 256 * 128;            // bytes
   static constexpr int kStageBytes = kATile + kBTile;                     // 48 KB
-  static constexpr int kStages = 3;
-  static constexpr int kEpiWarps = 16;                                    // 4 lane quarters x 4 slabs of 64 columns
-  static constexpr int kThreads = 64 + 32 * kEpiWarps;                    // 576
-  static constexpr int kActsBytes = 2 * kATile;                           // gated activations: 2 K chunks
+  static constexpr int kStages = OCC == 2 ? 2 : 3;
+  static constexpr int kEpiWarps = OCC == 2 ? 8 : 16;                     // 4 lane quarters x 2 or 4 slabs of 64 columns at a time
+  static constexpr int kSlabStep = kEpiWarps / 4;
+  static constexpr int kThreads = 64 + 32 * kEpiWarps;                    // 320 / 576
+  static constexpr int kActsBytes = OCC == 2 ? 0 : 2 * kATile;            // gated activations: 2 K chunks
+  static constexpr uint32_t kTmemCols = OCC == 2 ? 256u : 512u;
+  static constexpr uint32_t kAcc2Col = OCC == 2 ? 0u : 256u;
   static constexpr int kSmem = kStages * kStageBytes + kActsBytes + 1024 /*gate constants*/ + 1024 /*align*/ + 256;
   static_assert(kStages * kStageBytes >= kEpiWarps * 32 * kStgLd4 * 4, "staging must fit into the stage ring");
 };
@@ -1171,11 +1181,11 @@ struct WnParams {
   int park;                    // see TcParams::park
 };
 
-template <int NRS>
-__global__ void __launch_bounds__(WnCfg::kThreads, 1)
+template <int NRS, int OCC>
+__global__ void __launch_bounds__(WnCfgT<OCC>::kThreads, OCC)
 wn_layer_fused_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUtensorMap mapWin,
                       const __grid_constant__ CUtensorMap mapWrs, const WnParams p, const Epi epi, const RowMap map) {
-  using C = WnCfg;
+  using C = WnCfgT<OCC>;
   constexpr int kInChunks = 10;      // 5 taps x 128 channels / 64
   constexpr int kRsChunks = 2;       // 128 gated channels / 64
   const int tile = blockIdx.x;
@@ -1207,11 +1217,12 @@ wn_layer_fused_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_con
   }
   if (warp == 1) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
-                 "r"(512u)
+                 "r"(C::kTmemCols)
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   pdl_enter();   // everything above (barrier init, TMEM allocation) overlaps the previous kernel of the stream
+  static_assert(C::kThreads >= 64 + 256, "gate constants: one thread per accumulator column");
   if (threadIdx.x >= 64 && threadIdx.x < 64 + 256) {   // gate constants per accumulator column: bias + style conditioning
     const int n = threadIdx.x - 64;
     gconst[n] = p.bias_in[n] + p.segvec[(size_t)seg * p.ldseg + ((n & 1) ? 128 : 0) + (n >> 1)];
@@ -1221,6 +1232,9 @@ wn_layer_fused_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_con
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   auto stage_ptr = [&](int s) { return smem + (size_t)s * C::kStageBytes; };
+  // OCC 2: res/skip weight chunk ch arrives in the B slot of stage ch (10 conv chunks, 2 stages), its A slot is free
+  static_assert(OCC != 2 || (kInChunks % C::kStages == 0 && kRsChunks <= C::kStages), "activation chunks alias the A slots");
+  auto acts_chunk = [&](int ch) { return OCC == 2 ? stage_ptr(ch) : acts + (size_t)ch * C::kATile; };
   constexpr uint32_t kIdescIn = (1u << 4) | ((uint32_t)(256 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
   constexpr uint32_t kIdescRs = (1u << 4) | ((uint32_t)(NRS >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
 
@@ -1266,10 +1280,10 @@ wn_layer_fused_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_con
       for (int ch = 0; ch < kRsChunks; ++ch) {
         mbar_wait(&full[stage], phase, 24, p.park >= 2);
         tc_fence_after();
-        const uint32_t a = smem_u32(acts + ch * C::kATile), b = smem_u32(stage_ptr(stage)) + C::kATile;
+        const uint32_t a = smem_u32(acts_chunk(ch)), b = smem_u32(stage_ptr(stage)) + C::kATile;
 #pragma unroll
         for (int k = 0; k < C::kBK / C::kUmmaK; ++k)
-          tc_mma<false>(tmem_base + 256u, make_sdesc(a + k * 32), make_sdesc(b + k * 32), kIdescRs, (ch | k) != 0);
+          tc_mma<false>(tmem_base + C::kAcc2Col, make_sdesc(a + k * 32), make_sdesc(b + k * 32), kIdescRs, (ch | k) != 0);
         tc_commit(&empty[stage]);
         if (++stage == C::kStages) { stage = 0; phase ^= 1; }
       }
@@ -1279,11 +1293,11 @@ wn_layer_fused_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_con
     // ------------------------------------------------------------ gate epilogue -> shared-memory operand
     const int ew = warp - 2;
     const int q = warp & 3;            // TMEM lane quarter this warp may read (hardware rule)
-    const int slab = ew >> 2;          // 64 accumulator columns = 32 gated channels
     using EG = EpiPair<EPI_GATE, true>;
     mbar_wait(accum1, 0, 25, p.park >= 1);
     tc_fence_after();
-    {
+#pragma unroll 1
+    for (int slab = ew >> 2; slab < 4; slab += C::kSlabStep) {   // 64 accumulator columns = 32 gated channels
       float v[64];
       tmem_ld64(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(slab * 64), v);
       const int r = q * 32 + lane;     // row of the tile = TMEM lane
@@ -1302,7 +1316,7 @@ wn_layer_fused_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_con
         w[i] = *reinterpret_cast<const uint32_t*>(&t);
       }
       // K chunk slab / 2, 16-byte units (slab % 2) * 4 .. + 3 of this row, 128B swizzle: unit ^= row % 8
-      uint8_t* rowp = acts + (slab >> 1) * C::kATile + r * 128;
+      uint8_t* rowp = acts_chunk(slab >> 1) + r * 128;
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
         const int unit = ((slab & 1) * 4 + u) ^ (r & 7);
@@ -1320,11 +1334,12 @@ wn_layer_fused_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_con
     const int row0 = m0 + q * 32;
     int nrows = nvalid - q * 32;
     nrows = nrows < 0 ? 0 : (nrows > 32 ? 32 : nrows);
-    const int c = slab * 64;
-    if (c < epi.N) {                             // warp-uniform
+#pragma unroll 1
+    for (int c = (ew >> 2) * 64; c < epi.N; c += C::kSlabStep * 64) {     // warp-uniform
+      __syncwarp();                              // the staging block of the previous slab is consumed
       {
         float v[64];
-        tmem_ld64(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(256 + c), v);
+        tmem_ld64(tmem_base + ((uint32_t)(q * 32) << 16) + C::kAcc2Col + (uint32_t)c, v);
 #pragma unroll
         for (int j = 0; j < 64; j += 4)
           *reinterpret_cast<float4*>(stg + lane * kStgLd4 + j) =
@@ -1353,7 +1368,7 @@ wn_layer_fused_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_con
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(C::kTmemCols) : "memory");
   }
 }
 
@@ -1636,7 +1651,10 @@ cudaError_t launch_bn(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
       static const int min_k = [] { const char* e = std::getenv("STTS_LN_SPLITK"); return e != nullptr ? std::atoi(e) : 512; }();
       int ktot = 0;
       for (int s = 0; s < g.n_kseg; ++s) ktot += g.seg[s].taps * g.seg[s].cin_pad;
-      if (min_k > 0 && ktot >= min_k && g.epi.N <= 128) return launch_one<MODE, 128, KIND, 1, 4>(g, map, st);
+      // only while the four-fold grid still fits the SMs in one wave (a 32-utterance batch has 47 token tiles: 188 CTAs
+      // of 193 KB shared memory = two waves, measured 30 -> 42 us per launch); a small-batch shape (summation order)
+      if (min_k > 0 && ktot >= min_k && g.epi.N <= 128 && small_shapes_enabled() && map.n_tiles * 4 <= 148)
+        return launch_one<MODE, 128, KIND, 1, 4>(g, map, st);
     }
     if (g.epi.N <= 128) return launch_one<MODE, 128, KIND>(g, map, st);
     if (g.epi.N <= 256 && g.Npad % 256 == 0) return launch_one<MODE, 256, KIND>(g, map, st);
@@ -1711,9 +1729,9 @@ cudaError_t launch_mode(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
 }
 
 
-template <int NRS>
+template <int NRS, int OCC>
 cudaError_t launch_wn(const ConvGemm& gin, const ConvGemm& grs, const RowMap& map, cudaStream_t st) {
-  using C = WnCfg;
+  using C = WnCfgT<OCC>;
   const KSeg& ks = gin.seg[0];
   CUtensorMap mX, mWin, mWrs;
   if (ks.Ah == nullptr || gin.Wg == nullptr || grs.Wg == nullptr) return cudaErrorInvalidValue;
@@ -1728,7 +1746,7 @@ cudaError_t launch_wn(const ConvGemm& gin, const ConvGemm& grs, const RowMap& ma
   p.bias_in = gin.epi.bias;
   p.segvec = gin.epi.segvec;
   p.ldseg = gin.epi.ldseg;
-  auto kern = wn_layer_fused_kernel<NRS>;
+  auto kern = wn_layer_fused_kernel<NRS, OCC>;
   static bool attr_done = false;
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmem);
@@ -1764,8 +1782,13 @@ cudaError_t wn_layer_fused_f16(const ConvGemm& gin, const ConvGemm& grs, const R
   if (gin.n_kseg != 1 || grs.n_kseg != 1 || k.taps != 5 || k.pad != 2 || k.cin_pad != 128 || gin.epi.N != 256 ||
       gin.Ktot != 640 || grs.Ktot != 128 || grs.seg[0].taps != 1 || grs.seg[0].cin_pad != 128)
     return cudaErrorInvalidValue;
-  if (grs.epi.N == 256 && grs.Npad >= 256) return launch_wn<256>(gin, grs, map, st);
-  if (grs.epi.N == 128) return launch_wn<128>(gin, grs, map, st);
+  // STTS_WN_OCC=1: the one-CTA-per-SM variant (three stages, 16 epilogue warps) for A/B runs
+  // (also taken when the tiles do not fill the SMs once: nothing to overlap with, and its 16 epilogue warps finish a
+  // tile sooner -- one 5 s utterance 2.56 vs 2.65 ms; same arithmetic, bit-identical results)
+  static const bool occ2_env = [] { const char* e = std::getenv("STTS_WN_OCC"); return e == nullptr || e[0] != '1'; }();
+  const bool occ2 = occ2_env && map.n_tiles > 148;
+  if (grs.epi.N == 256 && grs.Npad >= 256) return occ2 ? launch_wn<256, 2>(gin, grs, map, st) : launch_wn<256, 1>(gin, grs, map, st);
+  if (grs.epi.N == 128) return occ2 ? launch_wn<128, 2>(gin, grs, map, st) : launch_wn<128, 1>(gin, grs, map, st);
   return cudaErrorInvalidValue;
 }
 
