@@ -163,6 +163,18 @@ __device__ __forceinline__ void f16_split(float x, __half* g, __half* l) {
   *l = __float2half_rn(x - __half2float(h));
 }
 
+// the same for a pair, bit-identical to two f16_split calls: the packed conversion (F2FP) and the half2 -> float2
+// unpack run on the main pipes, the scalar F2F conversions on the quarter-rate one (six of them per pair made the
+// store loop of the LayerNorm epilogue conversion-bound)
+__device__ __forceinline__ void f16_split2(float x0, float x1, __half2* g, __half2* l) {
+  x0 = fminf(fmaxf(x0, -65504.f), 65504.f);
+  x1 = fminf(fmaxf(x1, -65504.f), 65504.f);
+  const __half2 h = __floats2half2_rn(x0, x1);
+  const float2 hf = __half22float2(h);
+  *g = h;
+  *l = __floats2half2_rn(x0 - hf.x, x1 - hf.y);
+}
+
 // One thread owns row r (valid, segment seg) and NV consecutive output columns starting at n0
 // (n0 % NV == 0, NV even).  Shared by the SIMT and the tcgen05 kernels.
 template <int KIND, int NV>

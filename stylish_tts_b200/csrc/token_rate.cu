@@ -614,9 +614,9 @@ __global__ void __launch_bounds__(NT) attention_stream_kernel(const float* __res
       *reinterpret_cast<float4*>(out + o + i) = make_float4(y[0], y[1], y[2], y[3]);
       if (outg != nullptr) {
         const size_t og = (size_t)(qrow0 + qi) * ldh + hd * D + part * DL + i;
-        __half g[4], lo[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) f16_split(y[u], &g[u], &lo[u]);
+        __half2 g[2], lo[2];
+        f16_split2(y[0], y[1], &g[0], &lo[0]);
+        f16_split2(y[2], y[3], &g[1], &lo[1]);
         *reinterpret_cast<uint2*>(outg + og) = *reinterpret_cast<const uint2*>(g);
         if (outl != nullptr) *reinterpret_cast<uint2*>(outl + og) = *reinterpret_cast<const uint2*>(lo);
       }
