@@ -95,6 +95,16 @@ inline cudaError_t launch_k_cluster(void (*kernel)(KArgs...), dim3 grid, dim3 bl
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<Args&&>(args)...);
 }
 
+// grid.y of the row-loop kernels (CTAs sharing a 128-row tile through a blockIdx.y-strided loop): `base` for batches
+// that fill the GPU anyway, more for small ones -- one utterance is 1-13 tiles, and `base` CTAs per tile made each
+// thread walk a serial chain of dependent L2 round trips (depthwise conv of the cross attention: 37 us for 400 frames;
+// polar: 45 us).  Same arithmetic per element whatever the split.
+inline int split_rows(int n_tiles, int base, int cap) {
+  if (n_tiles <= 0) return base;
+  const int y = (1184 + n_tiles - 1) / n_tiles;          // ~8 CTAs of 256 threads per SM
+  return y < base ? base : (y > cap ? cap : y);
+}
+
 // Device view of a packed layout (one per frame rate).
 struct RowMap {
   int R;                 // rows (multiple of 128)

@@ -314,7 +314,7 @@ __global__ void __launch_bounds__(256) expand_tokens_kernel(const float* __restr
 cudaError_t expand_tokens(const float* tok, int C, const int* idx, const int* cu_f, const int* tok_off, int div,
                           const RowMap& map, float* out, int ldo, int col0, twin_t* outh, int ldh, int colh0,
                           cudaStream_t st) {
-  launch_k(expand_tokens_kernel, dim3(map.n_tiles, 4), 256, 0, st, tok, C, idx, cu_f, tok_off, div, map, out, ldo, col0, outh, ldh,
+  launch_k(expand_tokens_kernel, dim3(map.n_tiles, split_rows(map.n_tiles, 4, 64)), 256, 0, st, tok, C, idx, cu_f, tok_off, div, map, out, ldo, col0, outh, ldh,
                                                     colh0);
   return cudaGetLastError();
 }
@@ -864,7 +864,7 @@ __global__ void __launch_bounds__(256) rowdot_kernel(const float* __restrict__ x
 
 cudaError_t rowdot(const float* x, int ldx, int C, const RowMap& map, const float* w, const float* bias, const int* cu,
                    float* dense, cudaStream_t st) {
-  launch_k(rowdot_kernel, dim3(map.n_tiles, 4), 256, 0, st, x, ldx, C, map, w, bias, cu, dense);
+  launch_k(rowdot_kernel, dim3(map.n_tiles, split_rows(map.n_tiles, 4, 16)), 256, 0, st, x, ldx, C, map, w, bias, cu, dense);
   return cudaGetLastError();
 }
 

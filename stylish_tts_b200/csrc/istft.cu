@@ -85,7 +85,7 @@ __global__ void __launch_bounds__(256) polar_kernel(const float* __restrict__ la
 
 cudaError_t polar_spec(const float* logamp, const float* phase, int ld, int n_bins, const RowMap& map, float* spec,
                        int lds, __half* specg, int ldsh, __half* specl, float gscale, cudaStream_t st) {
-  dim3 grid(map.n_tiles, 16);
+  dim3 grid(map.n_tiles, split_rows(map.n_tiles, 16, 129));
   if (spec == nullptr && specl == nullptr && specg != nullptr)
     launch_k(polar_kernel<true>, grid, 256, 0, st, logamp, phase, ld, n_bins, map, spec, lds, specg, ldsh, specl, gscale);
   else
@@ -131,7 +131,7 @@ __global__ void __launch_bounds__(256) ola_tanh_kernel(const float* __restrict__
 
 cudaError_t ola_tanh(const float* frames, int ldf, const float* wsq, const int* cu4, const RowMap& map, float* audio,
                      cudaStream_t st) {
-  dim3 grid(map.n_tiles, 4);
+  dim3 grid(map.n_tiles, split_rows(map.n_tiles, 4, 38));
   launch_k(ola_tanh_kernel, grid, 256, 0, st, frames, ldf, wsq, cu4, map, audio);
   return cudaGetLastError();
 }

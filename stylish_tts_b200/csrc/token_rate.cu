@@ -41,7 +41,7 @@ __global__ void __launch_bounds__(128) embed_kernel(const int* __restrict__ tok,
 
 cudaError_t embed_tokens(const int* tok, const int* cu_tok, const float* table, int C, int n_vocab, const RowMap& map,
                          float* x, int ldx, cudaStream_t st, __half* xg, __half* xl) {
-  launch_k(embed_kernel, dim3(map.n_tiles, kCopySplit), 128, 0, st, tok, cu_tok, table, C, n_vocab, map, x, ldx, xg, xl);
+  launch_k(embed_kernel, dim3(map.n_tiles, split_rows(map.n_tiles, kCopySplit, 64)), 128, 0, st, tok, cu_tok, table, C, n_vocab, map, x, ldx, xg, xl);
   return cudaGetLastError();
 }
 
@@ -99,7 +99,7 @@ __global__ void __launch_bounds__(256) row_ln_kernel(const float* x, int ldx, in
 cudaError_t row_ln(const float* x, int ldx, int C, const RowMap& map, const float* gamma, const float* beta,
                    int seg_stride, float eps, int relu, float* y, int ldy, cudaStream_t st, __half* yg, __half* yl) {
   if (C > 512) return cudaErrorInvalidValue;
-  launch_k(row_ln_kernel, dim3(map.n_tiles, 4), 256, 0, st, x, ldx, C, map, gamma, beta, seg_stride, eps, relu, y, ldy, yg,
+  launch_k(row_ln_kernel, dim3(map.n_tiles, split_rows(map.n_tiles, 4, 16)), 256, 0, st, x, ldx, C, map, gamma, beta, seg_stride, eps, relu, y, ldy, yg,
                                                       yl);
   return cudaGetLastError();
 }
@@ -751,7 +751,7 @@ __global__ void __launch_bounds__(256) rows_to_dense_kernel(const float* __restr
 
 cudaError_t rows_to_dense(const float* src, int ld, int C, const RowMap& map, const int* cu, float* dst,
                           cudaStream_t st) {
-  launch_k(rows_to_dense_kernel, dim3(map.n_tiles, kCopySplit), 256, 0, st, src, ld, C, map, cu, dst);
+  launch_k(rows_to_dense_kernel, dim3(map.n_tiles, split_rows(map.n_tiles, kCopySplit, 32)), 256, 0, st, src, ld, C, map, cu, dst);
   return cudaGetLastError();
 }
 
@@ -786,7 +786,7 @@ __global__ void __launch_bounds__(256) dwconv_rows_kernel(const float* __restric
 
 cudaError_t dwconv_rows(const float* x, int ldx, int C, int K, const float* w, const float* b, const RowMap& map,
                         int act, float* y, int ldy, cudaStream_t st, __half* yg, __half* yl) {
-  launch_k(dwconv_rows_kernel, dim3(map.n_tiles, 4), 256, 0, st, x, ldx, C, K, w, b, map, act, y, ldy, yg, yl);
+  launch_k(dwconv_rows_kernel, dim3(map.n_tiles, split_rows(map.n_tiles, 4, 64)), 256, 0, st, x, ldx, C, K, w, b, map, act, y, ldy, yg, yl);
   return cudaGetLastError();
 }
 
@@ -812,7 +812,7 @@ __global__ void __launch_bounds__(256) dense_to_rows_kernel(const float* __restr
 
 cudaError_t dense_to_rows(const float* src, int C, const RowMap& map, const int* cu, float* dst, int ld, int col0,
                           cudaStream_t st, __half* dg, __half* dl) {
-  launch_k(dense_to_rows_kernel, dim3(map.n_tiles, kCopySplit), 256, 0, st, src, C, map, cu, dst, ld, col0, dg, dl);
+  launch_k(dense_to_rows_kernel, dim3(map.n_tiles, split_rows(map.n_tiles, kCopySplit, 32)), 256, 0, st, src, C, map, cu, dst, ld, col0, dg, dl);
   return cudaGetLastError();
 }
 

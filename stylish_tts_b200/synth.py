@@ -87,15 +87,23 @@ class Synthesizer:
             if not t.is_cuda and t.numel() and (int(t.min()) < 0 or int(t.max()) >= n_vocab):
                 raise IndexError(f"utterance {b}: token id outside [0, {n_vocab})")
         pack = self._token_pack(T, max(T))
-        # one H2D copy of the concatenated tokens: every stage works on the packed [sum T] token order
-        tok = torch.cat([t.reshape(-1) for t in tokens]).to(dev, torch.int32, non_blocking=True)
-        dur_used, F_list = None, None
+        use_graph = self.use_graphs if graph is None else graph
+        use_graph = use_graph and durations is not None and noise is None and pitch_energy is None and not want_intermediates
+        F_list = None
         if durations is not None:
-            dur_used = torch.cat([d.reshape(-1) for d in durations]).to(dev, torch.int32, non_blocking=True)
             # host-known frame counts: no device sync (pass `frames` when the durations live on the device)
             F_list = [int(f) for f in frames] if frames is not None else [int(d.sum()) for d in durations]
-        use_graph = self.use_graphs if graph is None else graph
-        if (use_graph and F_list is not None and noise is None and pitch_energy is None and not want_intermediates):
+        if use_graph and not any(t.is_cuda for t in tokens) and not any(d.is_cuda for d in durations):
+            # inputs on the host: they are written into the graph's pinned staging buffers and the H2D copies are
+            # nodes of the graph -- no device work outside the replay
+            res = self._graphed(None, pack, None, F_list, want_spec, host=(tokens, durations))
+            return self._package(res, T, want_spec)
+        # one H2D copy of the concatenated tokens: every stage works on the packed [sum T] token order
+        tok = torch.cat([t.reshape(-1) for t in tokens]).to(dev, torch.int32, non_blocking=True)
+        dur_used = None
+        if durations is not None:
+            dur_used = torch.cat([d.reshape(-1) for d in durations]).to(dev, torch.int32, non_blocking=True)
+        if use_graph:
             res = self._graphed(tok, pack, dur_used, F_list, want_spec)
         else:
             res = self._core(tok, pack, dur_used, F_list, noise, pitch_energy, want_spec, want_intermediates)
@@ -147,10 +155,12 @@ class Synthesizer:
             self._finfo[key] = torch.tensor(F_list, dtype=torch.int64).to(self.device)
         return self._finfo[key]
 
-    def _graphed(self, tok, pack, dur_used, F_list, want_spec):
+    def _graphed(self, tok, pack, dur_used, F_list, want_spec, host=None):
         """One CUDA graph per batch shape: the whole step (three token-rate chains on forked streams,
-        length regulation, frame-rate path) is replayed with no host work between kernels."""
-        key = (tuple(pack.lengths), tuple(F_list), bool(want_spec))
+        length regulation, frame-rate path) is replayed with no host work between kernels.
+        host = (tokens, durations) on the CPU: the graph starts with the H2D copies from its own pinned staging
+        buffers (rewritten here once the previous replay of this graph has finished)."""
+        key = (tuple(pack.lengths), tuple(F_list), bool(want_spec), host is not None)
         # A captured graph bakes the arena pointers, layout tables and TMA maps of the workspace plan it was
         # captured under, and the context holds ONE plan: any call with another shape (graph or eager)
         # re-plans it.  Graphs of other shapes are therefore dropped as soon as the plan moves on.
@@ -160,7 +170,14 @@ class Synthesizer:
         if ent is None:
             if len(self._graphs) >= 8:
                 self._graphs.clear()
-            s_tok, s_dur = tok.clone(), dur_used.clone()
+            if host is not None:
+                n_tok = sum(pack.lengths)
+                h_tok = torch.empty(n_tok, dtype=torch.int32).pin_memory()
+                h_dur = torch.empty(n_tok, dtype=torch.int32).pin_memory()
+                self._stage_host(h_tok, h_dur, host)
+                s_tok, s_dur = h_tok.to(self.device), h_dur.to(self.device)
+            else:
+                s_tok, s_dur = tok.clone(), dur_used.clone()
             self._frame_info(F_list)
             cur = torch.cuda.current_stream(self.device)
             warm = torch.cuda.Stream(self.device)
@@ -172,14 +189,36 @@ class Synthesizer:
             torch.cuda.synchronize(self.device)
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
+                if host is not None:
+                    s_tok.copy_(h_tok, non_blocking=True)
+                    s_dur.copy_(h_dur, non_blocking=True)
                 res = self._core(s_tok, pack, s_dur, F_list, None, None, want_spec, False)
-            ent = (g, s_tok, s_dur, res)
+            ent = (g, s_tok, s_dur, res) if host is None else (g, h_tok, h_dur, res, [torch.cuda.Event(), False])
             self._graphs[key] = ent
+        if host is not None:
+            g, h_tok, h_dur, res, busy = ent
+            if busy[1]:
+                busy[0].synchronize()            # the previous replay has read the staging buffers
+            self._stage_host(h_tok, h_dur, host)
+            g.replay()
+            busy[0].record()
+            busy[1] = True
+            return res
         g, s_tok, s_dur, res = ent
         s_tok.copy_(tok)
         s_dur.copy_(dur_used)
         g.replay()
         return res
+
+    @staticmethod
+    def _stage_host(h_tok, h_dur, host):
+        tokens, durations = host
+        if len(tokens) == 1:
+            h_tok.copy_(tokens[0].reshape(-1))
+            h_dur.copy_(durations[0].reshape(-1))
+        else:
+            h_tok.copy_(torch.cat([t.reshape(-1) for t in tokens]))
+            h_dur.copy_(torch.cat([d.reshape(-1) for d in durations]))
 
     def _core(self, tok, pack, dur_used, F_list, noise, pitch_energy, want_spec, want_intermediates):
         """The device work of one step: every stage is a libstts_b200 call on the packed layouts.
