@@ -25,6 +25,35 @@ def short(name: str) -> str:
     return name.replace("stts::", "")[:80]
 
 
+def pool_timeline(nets, dev, precision, lanes=3, steps=6):
+    """Three batches in flight (the bench's throughput mode): every kernel of `steps` steady-state steps with its
+    stream, so that the overlap of one lane's token-rate chain with the other lanes' frame-rate grids can be read."""
+    import bench
+    from stylish_tts_b200.synth import SynthesizerPool
+    from torch.profiler import ProfilerActivity, profile
+    pool = SynthesizerPool(nets, device=dev, precision=precision, lanes=lanes, use_graphs=True)
+    toks, durs, frames = bench.workload(1)
+    toks = [t.to(dev) for t in toks]
+    durs = [d.to(dev, torch.int32) for d in durs]
+    for _ in range(2 * lanes):
+        pool.submit(toks, durations=durs, frames=frames)
+    pool.synchronize()
+    with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
+        for _ in range(steps):
+            pool.submit(toks, durations=durs, frames=frames)
+        pool.drain()
+        torch.cuda.synchronize()
+    path = os.path.join(tempfile.mkdtemp(), "trace.json")
+    prof.export_chrome_trace(path)
+    ev = [e for e in json.load(open(path))["traceEvents"] if e.get("cat") == "kernel"]
+    ev.sort(key=lambda e: e["ts"])
+    t0 = ev[0]["ts"]
+    print(f"# pool {precision}: {len(ev)} kernels over {steps} steps, span {ev[-1]['ts'] + ev[-1]['dur'] - t0:.1f} us")
+    print("# start_us dur_us stream name")
+    for e in ev:
+        print(f"{e['ts'] - t0:10.1f} {e['dur']:8.1f} {e['args'].get('stream', -1):4d} {short(e['name'])}")
+
+
 def main():
     which = sys.argv[1] if len(sys.argv) > 1 else "c1"
     precision = sys.argv[2] if len(sys.argv) > 2 else "f16"
@@ -34,6 +63,8 @@ def main():
     for k, m in nets.items():
         m.load_state_dict(sds[k])
         m.eval()
+    if which == "pool":
+        return pool_timeline(nets, dev, precision)
     syn = Synthesizer(nets, device=dev, precision=precision, use_graphs=True)
     g = torch.Generator().manual_seed(13)
     if which == "c1":
