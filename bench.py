@@ -271,8 +271,10 @@ def run_reference_arm(args, rank: int, world: int):
     tokens, durs, frames = workload(1)
     vals = []
     sample = ""
+    # per-step sample sized so that the whole --steps K --warmup W run stays within ~2.5 minutes of CPU work
+    budget = max(2.0, min(args.cpu_budget / 2, 150.0 / max(1, args.warmup + args.steps)))
     for s in range(args.warmup + args.steps):
-        v, cores, sample = cpu_port_throughput(tokens, durs, frames, budget_s=args.cpu_budget / 2, seed=s)
+        v, cores, sample = cpu_port_throughput(tokens, durs, frames, budget_s=budget, seed=s)
         if s >= args.warmup:
             vals.append(v)
     v = sum(vals) / len(vals)
@@ -346,7 +348,7 @@ def main():
     claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--precision", default="f16", choices=["f16", "fp32", "tf32x3"],
