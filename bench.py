@@ -470,6 +470,7 @@ def main():
 
     warm(step_resident, max(args.warmup, len(pool.lanes)))       # every lane warms up (and captures its graph)
     pool.check()
+    ws_bytes = eng.workspace_bytes()              # of the timed workload's plan (later legs re-plan the context)
     # clocks / throttle reasons: nvidia-smi every 20 ms from two more untimed steps of the same load (the sampler
     # needs ~0.1 s to start; the timed region itself is ~0.1 s at the default K) through the timed region
     sampler = ClockSampler(local)
@@ -615,7 +616,7 @@ def main():
                               f"{len(pool.lanes)} batches in flight, each with a working set (GBs) >> the 126 MB L2")
                              if flush_buf is not None else "no flush; per-step working set (GBs) >> the 126 MB L2",
                        "parity_target": "audio_x0 (reference with the exact frame-0 STFT phase), oracle pitch injected",
-                       "workspace_bytes": eng.workspace_bytes()},
+                       "workspace_bytes": ws_bytes},
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
                     "h2d_bytes_per_step": int(sum(t.numel() * 8 for t in g_tokens) + sum(d.numel() * 4 for d in g_durs)),
