@@ -1772,6 +1772,14 @@ cudaError_t launch_bn(const ConvGemm& g, const RowMap& map, cudaStream_t st) {
   }
   if (MODE == MODE_F16 && wide) return launch_one<MODE, 256, KIND>(g, map, st);
   if (MODE != MODE_F16 && wide && split256 && g.epi.N >= 1024) return launch_one<MODE, 256, KIND>(g, map, st);
+  if constexpr (MODE != MODE_F16) {
+    // Wave quantisation: the split-mode kernels are one CTA per SM (193 KB of shared memory).  A 32-utterance batch has
+    // 47 token tiles: the text encoders' ffn1 (N = 512) is 188 CTAs with 128-column tiles -- two waves, the second a
+    // quarter full -- and 94 with 256-column tiles: one wave.  STTS_SPLIT_WAVE=0 switches the rule off.
+    static const bool wave = [] { const char* e = std::getenv("STTS_SPLIT_WAVE"); return e == nullptr || e[0] != '0'; }();
+    const long long c128 = (long long)map.n_tiles * ((g.epi.N + 127) / 128), c256 = (long long)map.n_tiles * ((g.epi.N + 255) / 256);
+    if (wave && wide && split256 && c128 > 148 && c256 <= 148) return launch_one<MODE, 256, KIND>(g, map, st);
+  }
   return launch_one<MODE, 128, KIND>(g, map, st);
 }
 
