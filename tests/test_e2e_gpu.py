@@ -188,6 +188,17 @@ def test_cuda_graph_replay_matches_eager_launches():
     o2 = syn.synthesize(toks2, durations=durs, frames=frames, graph=True)
     for i in range(3):
         assert torch.equal(o2["pitch"][i], e2["pitch"][i])
+    # inputs already on the device take the other graph of the shape (device-side copies into its static buffers
+    # instead of the pinned staging buffers + in-graph H2D copies of host inputs): same results
+    dev = o2["pitch"][0].device
+    o3 = syn.synthesize([t.to(dev) for t in toks2], durations=[d.to(dev) for d in durs], frames=frames, graph=True)
+    for i in range(3):
+        assert torch.equal(o3["pitch"][i], e2["pitch"][i])
+        assert torch.equal(o3["duration_pred"][i], e2["duration_pred"][i])
+    # and host inputs again right after: the staging buffers are rewritten only behind the previous replay
+    o4 = syn.synthesize(toks, durations=durs, frames=frames, graph=True)
+    for i in range(3):
+        assert torch.equal(o4["pitch"][i], eager["pitch"][i])
 
 
 def test_full_size_batch_properties_f16():
